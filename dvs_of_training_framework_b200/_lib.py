@@ -1,0 +1,147 @@
+"""ctypes binding of libdvsof.so (include/dvsof.h).  No CPU fallback: if the CUDA library is
+missing or a tensor is not on a CUDA device, the call fails loudly."""
+import ctypes as C
+from pathlib import Path
+
+import torch
+
+_LIB_PATH = Path(__file__).resolve().parent / 'libdvsof.so'
+_lib = None
+
+MAX_SCALES = 8
+ST_BAD_POLARITY, ST_NOT_GROUPED, ST_BAD_SAMPLE, ST_BAD_PIXEL, ST_NO_MATCH, ST_BAD_LUT = \
+    0x1, 0x2, 0x4, 0x8, 0x10, 0x20
+_ST_TEXT = {ST_BAD_POLARITY: 'polarity must be +1/-1 (EV_FlowNet/net.py:124)',
+            ST_NOT_GROUPED: 'events must be grouped by ascending sample_index (net.py:131-134)',
+            ST_BAD_SAMPLE: 'sample_index outside [0, batch)',
+            ST_BAD_PIXEL: 'event coordinate outside the image',
+            ST_NO_MATCH: 'each prediction needs exactly one image per timestamp (utils/loss.py:193)',
+            ST_BAD_LUT: 'map: src/dst index outside the image'}
+
+
+class LossScales(C.Structure):
+    _fields_ = [('n_scales', C.c_int32), ('n_pred', C.c_int32),
+                ('H', C.c_int32 * MAX_SCALES), ('W', C.c_int32 * MAX_SCALES),
+                ('flow', C.c_void_p * MAX_SCALES), ('images', C.c_void_p * MAX_SCALES),
+                ('grad_flow', C.c_void_p * MAX_SCALES)]
+
+
+_SIGNATURES = {
+    'dvsof_last_error': (C.c_char_p, []),
+    'dvsof_version': (C.c_int, []),
+    'dvsof_encode_workspace_bytes': (C.c_size_t, [C.c_int64]),
+    'dvsof_encode_event_image': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p, C.c_int64,
+                                            C.c_int32, C.c_int32] + [C.c_void_p] * 4),
+    'dvsof_encode_event_image_compact': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p,
+                                                    C.c_int64, C.c_int32, C.c_int32] + [C.c_void_p] * 4),
+    'dvsof_count_image': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                    C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_compact_workspace_bytes': (C.c_size_t, [C.c_int64]),
+    'dvsof_event_crop': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_double,
+                                   C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_void_p,
+                                   C.c_void_p, C.c_void_p]),
+    'dvsof_map_lut_workspace_bytes': (C.c_size_t, [C.c_int32, C.c_int32, C.c_int64]),
+    'dvsof_map_events_build': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_map_events_count': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_map_events_write': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_match_timestamps': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
+                                         C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_resize_bilinear': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                        C.c_int32, C.c_int32, C.c_void_p]),
+    'dvsof_loss_workspace_bytes': (C.c_size_t, [C.POINTER(LossScales)]),
+    'dvsof_warp_loss_forward': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p]),
+    'dvsof_warp_loss_backward': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_void_p]),
+}
+
+
+def lib_path():
+    return _LIB_PATH
+
+
+def load():
+    """Load libdvsof.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not _LIB_PATH.exists():
+            raise RuntimeError(f'{_LIB_PATH} is missing: run `python -c "import __graft_entry__ as g; '
+                               'g.build()"` (nvcc, sm_100a). There is no CPU fallback.')
+        lib = C.CDLL(str(_LIB_PATH))
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def call(name, *args):
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        msg = lib.dvsof_last_error().decode()
+        raise (ValueError if rc == -1 else RuntimeError)(f'{name}: {msg} (code {rc})')
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None and t.numel() else C.c_void_p(0)
+
+
+def stream_ptr(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(t, name, dtype=None):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError(f'{name}: expected a CUDA tensor (libdvsof has no CPU path), got '
+                           f'{type(t).__name__}{"" if not isinstance(t, torch.Tensor) else " on " + str(t.device)}')
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f'{name}: expected {dtype}, got {t.dtype}')
+    return t.contiguous()
+
+
+class Status:
+    """Device status word the kernels OR error bits into.
+
+    mode 'sync'     -- check right after the call (reference behaviour: AssertionError raised
+                       by the call itself; one host sync per call);
+    mode 'deferred' -- the word is checked at the next call that uses this object or at
+                       `flush()`; no sync on the hot path.
+    """
+    mode = 'sync'
+
+    def __init__(self, device):
+        self.word = torch.zeros(1, dtype=torch.int32, device=device)
+        self.pending = False
+
+    def check(self, exc=AssertionError):
+        bits = int(self.word.item()) & 0xffffffff
+        self.pending = False
+        if bits:
+            self.word.zero_()
+            raise exc('; '.join(t for b, t in _ST_TEXT.items() if bits & b))
+
+    def after_call(self, exc=AssertionError):
+        if Status.mode == 'sync':
+            self.check(exc)
+        else:
+            self.pending = True
+
+    def flush(self, exc=AssertionError):
+        if self.pending:
+            self.check(exc)
+
+
+_status = {}
+
+
+def status_for(device):
+    device = torch.device(device)
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    st = _status.get(key)
+    if st is None:
+        st = _status[key] = Status(device)
+    return st

@@ -1,0 +1,331 @@
+// encode.cu -- event stream -> 4-channel event image (counts + last normalised timestamp per
+// polarity).  Replaces EV_FlowNet/net.py:88-150 of the reference (see include/dvsof.h).
+//
+// Data layout in HBM: events are structure-of-arrays exactly as the reference's collate
+// delivers them (x,y,polarity,sample_index int64; timestamp fp32 => 36 B/event), streamed once
+// with 16-byte evict-first loads.  The output (B,4,H,W) fp32 is zeroed, then updated with
+// no-return L2 reductions: RED.ADD.F32 for the counts (exact: integer-valued fp32 sums) and
+// RED.MAX.S32 on the bit pattern for the timestamps (signed-int order == float order for
+// t^ >= 0, and any negative t^ loses against the initial +0.0, which is exactly
+// scatter_max(..., out=zeros)).  Both are order independent => bit-exact vs the oracle.
+#include "common.cuh"
+
+namespace dvsof {
+
+// ---------------------------------------------------------------------------------------
+// per-sample (start, dt): one warp per sample, 32-ary upper-bound search in sample_index
+// ---------------------------------------------------------------------------------------
+template <typename GetKey>
+__device__ __forceinline__ int64_t warp_upper_bound(GetKey key_at, int64_t n, int64_t s, int lane) {
+    // first index i in [0,n) with key(i) > s (n if none).  All 32 lanes cooperate.
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const int64_t step = (hi - lo + 31) / 32;
+        const int64_t pos = lo + (int64_t)(lane + 1) * step - 1;
+        const bool gt = (pos < hi) ? (key_at(pos) > s) : true;
+        const unsigned m = __ballot_sync(0xffffffffu, gt);
+        if (m == 0) { lo = hi; break; }
+        const int first = __ffs(m) - 1;
+        const int64_t seg_end = lo + (int64_t)(first + 1) * step - 1;
+        lo = lo + (int64_t)first * step;
+        hi = seg_end < hi ? seg_end : hi;
+    }
+    return lo;
+}
+
+__global__ void sample_bounds_kernel(const int64_t* __restrict__ b, const float* __restrict__ t,
+                                     int64_t n, const float* __restrict__ timestamps,
+                                     int n_samples, float2* __restrict__ sd) {
+    const int lane = threadIdx.x & 31;
+    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (s >= n_samples) return;
+    auto key = [&](int64_t i) { return b[i]; };
+    const int64_t end = warp_upper_bound(key, n, (int64_t)s, lane);
+    const int64_t begin = (s == 0) ? 0 : warp_upper_bound(key, n, (int64_t)s - 1, lane);
+    if (lane == 0) {
+        const float start = timestamps[2 * s];
+        float dt = 0.f;
+        if (end > begin) dt = __fsub_rn(t[end - 1], start);   // net.py:136-137
+        dt = fmaxf(dt, 1e-9f);                               // net.py:138
+        sd[s] = make_float2(start, dt);
+    }
+}
+
+__global__ void sample_bounds_compact_kernel(const int64_t* __restrict__ sample_begin,
+                                             const float* __restrict__ t, int64_t n,
+                                             const float* __restrict__ timestamps, int n_samples,
+                                             float2* __restrict__ sd,
+                                             uint32_t* __restrict__ status) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_samples) return;
+    int64_t begin = sample_begin[s], end = sample_begin[s + 1];
+    if (begin < 0 || end < begin || end > n || (s == 0 && begin != 0) ||
+        (s == n_samples - 1 && end != n)) {
+        atomicOr(status, DVSOF_ST_NOT_GROUPED);
+        begin = end = 0;
+    }
+    const float start = timestamps[2 * s];
+    float dt = 0.f;
+    if (end > begin) dt = __fsub_rn(t[end - 1], start);
+    sd[s] = make_float2(start, fmaxf(dt, 1e-9f));
+}
+
+// ---------------------------------------------------------------------------------------
+// scatter of one event
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned scatter_event(int64_t xi, int64_t yi, float ti, int64_t pi,
+                                                  int64_t bi, const float2* __restrict__ sd,
+                                                  int n_samples, int H, int W,
+                                                  float* __restrict__ out) {
+    if (pi != 1 && pi != -1) return DVSOF_ST_BAD_POLARITY;
+    if ((uint64_t)bi >= (uint64_t)n_samples) return DVSOF_ST_BAD_SAMPLE;
+    if ((uint64_t)xi >= (uint64_t)W || (uint64_t)yi >= (uint64_t)H) return DVSOF_ST_BAD_PIXEL;
+    const float2 s = __ldg(sd + bi);
+    const float tn = __fdiv_rn(__fsub_rn(ti, s.x), s.y);           // net.py:141
+    const int c = (int)((1 - pi) >> 1);                             // net.py:142
+    const size_t plane = (size_t)H * W;
+    const size_t cell = ((size_t)bi * 4 + c) * plane + (size_t)yi * W + xi;  // net.py:144
+    atomicAdd(out + cell, 1.0f);                                    // scatter_sum, net.py:147
+    atomicMax(reinterpret_cast<int*>(out + cell + 2 * plane), __float_as_int(tn));  // net.py:149
+    return 0u;
+}
+
+// ---------------------------------------------------------------------------------------
+// int64 structure-of-arrays stream, 4 events per thread per iteration (16 B loads)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                   const float* __restrict__ t, const int64_t* __restrict__ p,
+                   const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
+                   int n_samples, int H, int W, float* __restrict__ out,
+                   uint32_t* __restrict__ status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nvec = n >> 2;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned flags = 0;
+    // warp-uniform trip count so the shuffle below is always convergent
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < nvec;
+         base += stride) {
+        const int64_t i = base + lane;
+        const bool valid = i < nvec;
+        longlong2 xa, xb, ya, yb, pa, pb, ba, bb;
+        float4 tt;
+        if (valid) {
+            const longlong2* x2 = reinterpret_cast<const longlong2*>(x) + 2 * i;
+            const longlong2* y2 = reinterpret_cast<const longlong2*>(y) + 2 * i;
+            const longlong2* p2 = reinterpret_cast<const longlong2*>(p) + 2 * i;
+            const longlong2* b2 = reinterpret_cast<const longlong2*>(b) + 2 * i;
+            xa = __ldcs(x2); xb = __ldcs(x2 + 1);
+            ya = __ldcs(y2); yb = __ldcs(y2 + 1);
+            pa = __ldcs(p2); pb = __ldcs(p2 + 1);
+            ba = __ldcs(b2); bb = __ldcs(b2 + 1);
+            tt = __ldcs(reinterpret_cast<const float4*>(t) + i);
+        } else {
+            ba = bb = make_longlong2(0, 0);
+        }
+        // grouping check (net.py:131-134): sample_index must be non-decreasing
+        long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
+        if (valid) {
+            const int64_t nxt = 4 * (i + 1);
+            if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : bb.y;
+            if (ba.x > ba.y || ba.y > bb.x || bb.x > bb.y || bb.y > bnext)
+                flags |= DVSOF_ST_NOT_GROUPED;
+            flags |= scatter_event(xa.x, ya.x, tt.x, pa.x, ba.x, sd, n_samples, H, W, out);
+            flags |= scatter_event(xa.y, ya.y, tt.y, pa.y, ba.y, sd, n_samples, H, W, out);
+            flags |= scatter_event(xb.x, yb.x, tt.z, pb.x, bb.x, sd, n_samples, H, W, out);
+            flags |= scatter_event(xb.y, yb.y, tt.w, pb.y, bb.y, sd, n_samples, H, W, out);
+        }
+    }
+    // tail (n % 4 events): first threads of block 0
+    if (blockIdx.x == 0) {
+        const int64_t i = (nvec << 2) + threadIdx.x;
+        if (i < n) {
+            if (i + 1 < n && b[i] > b[i + 1]) flags |= DVSOF_ST_NOT_GROUPED;
+            flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
+        }
+    }
+    if (flags) atomicOr(status, flags);
+}
+
+// unaligned views (e.g. a DDP shard that starts at an odd event index): scalar loads
+__global__ void __launch_bounds__(256)
+encode_scalar_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                     const float* __restrict__ t, const int64_t* __restrict__ p,
+                     const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
+                     int n_samples, int H, int W, float* __restrict__ out,
+                     uint32_t* __restrict__ status) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned flags = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int64_t bi = __ldcs(b + i);
+        if (i + 1 < n && bi > b[i + 1]) flags |= DVSOF_ST_NOT_GROUPED;
+        flags |= scatter_event(__ldcs(x + i), __ldcs(y + i), __ldcs(t + i), __ldcs(p + i), bi, sd,
+                               n_samples, H, W, out);
+    }
+    if (flags) atomicOr(status, flags);
+}
+
+// ---------------------------------------------------------------------------------------
+// compact storage form (utils/dataset.py:286-289): x,y int16, polarity bool, t fp32 = 9 B/event;
+// sample membership from the per-sample prefix `sample_begin` (B+1).  8 events per thread.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned scatter_compact(int xi, int yi, float ti, int c, int s,
+                                                    const float2* __restrict__ sd, int H, int W,
+                                                    float* __restrict__ out) {
+    if ((unsigned)xi >= (unsigned)W || (unsigned)yi >= (unsigned)H) return DVSOF_ST_BAD_PIXEL;
+    const float2 v = __ldg(sd + s);
+    const float tn = __fdiv_rn(__fsub_rn(ti, v.x), v.y);
+    const size_t plane = (size_t)H * W;
+    const size_t cell = ((size_t)s * 4 + c) * plane + (size_t)yi * W + xi;
+    atomicAdd(out + cell, 1.0f);
+    atomicMax(reinterpret_cast<int*>(out + cell + 2 * plane), __float_as_int(tn));
+    return 0u;
+}
+
+__device__ __forceinline__ int find_sample(const int64_t* __restrict__ sample_begin, int n_samples,
+                                           int64_t e) {
+    // largest s with sample_begin[s] <= e
+    int lo = 0, hi = n_samples;  // answer in [lo, hi)
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(sample_begin + mid) <= e) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+encode_compact_kernel(const int16_t* __restrict__ x, const int16_t* __restrict__ y,
+                      const float* __restrict__ t, const uint8_t* __restrict__ p,
+                      const int64_t* __restrict__ sample_begin, int64_t n,
+                      const float2* __restrict__ sd, int n_samples, int H, int W,
+                      float* __restrict__ out, uint32_t* __restrict__ status) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned flags = 0;
+    int64_t done = 0;
+    if (VEC) {
+        const int64_t nvec = n >> 3;
+        done = nvec << 3;
+        for (int64_t i = tid; i < nvec; i += stride) {
+            const int4 xv = __ldcs(reinterpret_cast<const int4*>(x) + i);
+            const int4 yv = __ldcs(reinterpret_cast<const int4*>(y) + i);
+            const uint2 pv = __ldcs(reinterpret_cast<const uint2*>(p) + i);
+            const float4 ta = __ldcs(reinterpret_cast<const float4*>(t) + 2 * i);
+            const float4 tb = __ldcs(reinterpret_cast<const float4*>(t) + 2 * i + 1);
+            const int xw[4] = {xv.x, xv.y, xv.z, xv.w};
+            const int yw[4] = {yv.x, yv.y, yv.z, yv.w};
+            const float tv[8] = {ta.x, ta.y, ta.z, ta.w, tb.x, tb.y, tb.z, tb.w};
+            int64_t e = i << 3;
+            int s = find_sample(sample_begin, n_samples, e);
+            int64_t next = __ldg(sample_begin + s + 1);
+#pragma unroll
+            for (int k = 0; k < 8; ++k, ++e) {
+                while (e >= next && s + 1 < n_samples) { ++s; next = __ldg(sample_begin + s + 1); }
+                const int xi = (int)(short)((k & 1) ? (xw[k >> 1] >> 16) : (xw[k >> 1] & 0xffff));
+                const int yi = (int)(short)((k & 1) ? (yw[k >> 1] >> 16) : (yw[k >> 1] & 0xffff));
+                const unsigned pw = (k < 4) ? pv.x : pv.y;
+                const int pos = (pw >> (8 * (k & 3))) & 0xff;
+                flags |= scatter_compact(xi, yi, tv[k], pos ? 0 : 1, s, sd, H, W, out);
+            }
+        }
+    }
+    for (int64_t e = done + tid; e < n; e += stride) {
+        const int s = find_sample(sample_begin, n_samples, e);
+        flags |= scatter_compact(x[e], y[e], t[e], p[e] ? 0 : 1, s, sd, H, W, out);
+    }
+    if (flags) atomicOr(status, flags);
+}
+
+}  // namespace dvsof
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+using namespace dvsof;
+
+static int encode_grid(int64_t work_items, int threads, int ctas_per_sm) {
+    int64_t blocks = (work_items + threads - 1) / threads;
+    const int64_t cap = (int64_t)kNumSMs * ctas_per_sm;  // persistent: multiple of the SM count
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+static int check_encode_args(int64_t n, int64_t B, int H, int W, const void* out, const void* ws,
+                             const void* status) {
+    if (n < 0 || B <= 0 || H <= 0 || W <= 0)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: bad sizes n=%lld B=%lld H=%d W=%d",
+                    (long long)n, (long long)B, H, W);
+    if (B > INT32_MAX / 8) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: too many samples");
+    if (!out || !ws || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: out/workspace/status must be non-null");
+    return DVSOF_OK;
+}
+
+extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_samples) {
+    return round_up((size_t)(n_samples > 0 ? n_samples : 1) * sizeof(float2), 256);
+}
+
+extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
+                                        const int64_t* p, const int64_t* b, int64_t n,
+                                        const float* timestamps, int64_t B, int32_t H, int32_t W,
+                                        float* out, void* workspace, uint32_t* status,
+                                        void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
+    cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
+    if (n == 0) return DVSOF_OK;                                    // net.py:115-116
+    if (!x || !y || !t || !p || !b || !timestamps)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    float2* sd = reinterpret_cast<float2*>(workspace);
+    {
+        const int threads = 128;  // 4 samples per CTA
+        const int blocks = (int)((B * 32 + threads - 1) / threads);
+        sample_bounds_kernel<<<blocks, threads, 0, stream>>>(b, t, n, timestamps, (int)B, sd);
+        if (int rc = check_launch("sample_bounds_kernel")) return rc;
+    }
+    const bool vec = aligned16(x) && aligned16(y) && aligned16(t) && aligned16(p) && aligned16(b);
+    if (vec) {
+        const int grid = encode_grid((n >> 2) + 1, 256, 8);
+        encode_vec4_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
+    } else {
+        const int grid = encode_grid(n, 256, 8);
+        encode_scalar_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
+    }
+    return check_launch("encode_kernel");
+}
+
+extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,
+                                                const uint8_t* polarity01,
+                                                const int64_t* sample_begin, int64_t n,
+                                                const float* timestamps, int64_t B, int32_t H,
+                                                int32_t W, float* out, void* workspace,
+                                                uint32_t* status, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
+    cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
+    if (n == 0) return DVSOF_OK;
+    if (!x || !y || !t || !polarity01 || !sample_begin || !timestamps)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_compact: null event array");
+    float2* sd = reinterpret_cast<float2*>(workspace);
+    sample_bounds_compact_kernel<<<(int)((B + 127) / 128), 128, 0, stream>>>(
+        sample_begin, t, n, timestamps, (int)B, sd, status);
+    if (int rc = check_launch("sample_bounds_compact_kernel")) return rc;
+    const bool vec = aligned16(x) && aligned16(y) && aligned16(t) &&
+                     ((reinterpret_cast<uintptr_t>(polarity01) & 7u) == 0);
+    if (vec) {
+        const int grid = encode_grid((n >> 3) + 1, 256, 8);
+        encode_compact_kernel<true><<<grid, 256, 0, stream>>>(x, y, t, polarity01, sample_begin, n,
+                                                              sd, (int)B, H, W, out, status);
+    } else {
+        const int grid = encode_grid(n, 256, 8);
+        encode_compact_kernel<false><<<grid, 256, 0, stream>>>(x, y, t, polarity01, sample_begin,
+                                                               n, sd, (int)B, H, W, out, status);
+    }
+    return check_launch("encode_compact_kernel");
+}

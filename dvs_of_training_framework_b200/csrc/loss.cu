@@ -1,0 +1,400 @@
+// loss.cu -- multiscale self-supervised warp loss (utils/loss.py of the reference), forward and
+// analytic backward.  One launch covers ALL scales and predictions: a CTA owns one 32x32 pixel
+// tile of one (scale, prediction), stages the flow tile (+1 halo) in shared memory, gathers the
+// bilinear taps of the `next` pyramid level, and reduces the Charbonnier terms to one partial
+// record per CTA.  A single-CTA-per-scale finalize kernel sums the records in a fixed order in
+// fp64 => deterministic results, and the per-sample out-of-border counts n_i the backward needs.
+//
+// HBM traffic per pixel: forward 8 B flow + 4 B prev + 4 B next (taps hit L1/L2); backward the
+// same + 8 B grad_flow written once.  Arithmetic follows the reference's CPU path: the sampling
+// grid is g = (pix + flow) / ((S-1)/2) - 1 with IEEE division (utils/loss.py:150-156), then
+// ix = (g + 1) * ((S-1)/2) as ATen's CPU grid_sampler does for align_corners=True.
+#include "common.cuh"
+
+namespace dvsof {
+
+constexpr float kAlpha = 0.45f;    // utils/loss.py:25
+constexpr float kEps2 = 1e-3f * 1e-3f;  // utils/loss.py:26,31
+constexpr int kTile = 32;          // tile edge (pixels)
+constexpr int kLossThreads = 256;  // 32 x 8 threads, 4 rows per thread
+constexpr int kRec = 8;            // floats per CTA partial record
+
+// Charbonnier c(d) = (d^2 + eps^2)^alpha and c'(d) = 2 alpha d (d^2+eps^2)^(alpha-1).
+// lg2/ex2 on the SFU: relative error ~3e-7, inside the 1e-5 budget of the path.
+__device__ __forceinline__ float charb(float d) {
+    const float s = fmaf(d, d, kEps2);
+    return exp2f(kAlpha * __log2f(s));
+}
+__device__ __forceinline__ float charb_grad(float d) {
+    const float s = fmaf(d, d, kEps2);
+    return 2.f * kAlpha * d * exp2f((kAlpha - 1.f) * __log2f(s));
+}
+
+struct ScaleTable {
+    int n_scales, n_pred;
+    int H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
+    int tiles_x[DVSOF_MAX_SCALES], tiles_y[DVSOF_MAX_SCALES];
+    int cta_begin[DVSOF_MAX_SCALES + 1];
+    const float* flow[DVSOF_MAX_SCALES];
+    const float* images[DVSOF_MAX_SCALES];
+    float* grad_flow[DVSOF_MAX_SCALES];
+};
+
+struct TileCoord { int s, n, y0, x0; };
+__device__ __forceinline__ TileCoord decode_cta(const ScaleTable& tab) {
+    int s = 0;
+    while (s + 1 < tab.n_scales && (int)blockIdx.x >= tab.cta_begin[s + 1]) ++s;
+    const int local = blockIdx.x - tab.cta_begin[s];
+    const int per = tab.tiles_x[s] * tab.tiles_y[s];
+    const int n = local / per, tile = local - n * per;
+    const int ty = tile / tab.tiles_x[s];
+    return TileCoord{s, n, ty * kTile, (tile - ty * tab.tiles_x[s]) * kTile};
+}
+
+// bilinear sample of `img` (H x W) at the position the reference's grid_sample visits for
+// pixel (x,y) displaced by (u,v); also returns the normalised grid (for the border mask) and the
+// spatial derivatives of the sample.
+struct Warp { float val, ddx, ddy, gx, gy; };
+__device__ __forceinline__ Warp warp_sample(const float* __restrict__ img, int H, int W, int x,
+                                            int y, float u, float v) {
+    const float hx = (float)(W - 1) / 2.f, hy = (float)(H - 1) / 2.f;
+    Warp r;
+    r.gx = __fsub_rn(__fdiv_rn(__fadd_rn((float)x, u), hx), 1.f);    // utils/loss.py:150-156
+    r.gy = __fsub_rn(__fdiv_rn(__fadd_rn((float)y, v), hy), 1.f);
+    const float ix = __fmul_rn(__fadd_rn(r.gx, 1.f), hx);            // ATen CPU unnormalize
+    const float iy = __fmul_rn(__fadd_rn(r.gy, 1.f), hy);
+    const float xw = floorf(ix), yn = floorf(iy);
+    const float wx = ix - xw, wy = iy - yn;                          // weight of east / south
+    const float ex = 1.f - wx, ey = 1.f - wy;
+    // taps outside the image contribute zero (padding_mode='zeros'); range test in float so
+    // huge / non-finite coordinates never reach an int conversion
+    const bool x0ok = xw >= 0.f && xw <= (float)(W - 1);
+    const bool x1ok = xw >= -1.f && xw <= (float)(W - 2);
+    const bool y0ok = yn >= 0.f && yn <= (float)(H - 1);
+    const bool y1ok = yn >= -1.f && yn <= (float)(H - 2);
+    float nw = 0.f, ne = 0.f, sw = 0.f, se = 0.f;
+    if (x0ok || x1ok) {
+        const int xi = (int)xw, yi = (int)yn;
+        if (y0ok) {
+            const float* row = img + (size_t)yi * W;
+            if (x0ok) nw = __ldg(row + xi);
+            if (x1ok) ne = __ldg(row + xi + 1);
+        }
+        if (y1ok) {
+            const float* row = img + (size_t)(yi + 1) * W;
+            if (x0ok) sw = __ldg(row + xi);
+            if (x1ok) se = __ldg(row + xi + 1);
+        }
+    }
+    r.val = nw * (ey * ex) + ne * (ey * wx) + sw * (wy * ex) + se * (wy * wx);
+    r.ddx = (ne - nw) * ey + (se - sw) * wy;
+    r.ddy = (sw - nw) * ex + (se - ne) * wx;
+    return r;
+}
+
+// ------------------------------ timestamp matching -------------------------------------
+__global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
+                                        const int64_t* __restrict__ flow_sample_idx, int P,
+                                        const float* __restrict__ timestamps,
+                                        const int64_t* __restrict__ sample_idx, int D,
+                                        int32_t* __restrict__ match_idx,
+                                        uint32_t* __restrict__ status) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;   // i = k * P + p
+    if (i >= 2 * P) return;
+    const int k = i / P, p = i - k * P;
+    const float want = flow_ts[2 * p + k];
+    const int64_t smp = flow_sample_idx[p];
+    int hits = 0, idx = 0;
+    for (int d = 0; d < D; ++d)
+        if (timestamps[d] == want && sample_idx[d] == smp) { ++hits; idx = d; }   // loss.py:187-191
+    if (hits != 1) atomicOr(status, DVSOF_ST_NO_MATCH);                           // loss.py:193
+    match_idx[i] = idx;
+}
+
+// ------------------------------ bilinear resize (align_corners) ------------------------
+__global__ void __launch_bounds__(256)
+resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
+                       int Hout, int Wout, int64_t total) {
+    const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
+    const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const int x = (int)(i % Wout);
+        const int64_t r = i / Wout;
+        const int y = (int)(r % Hout);
+        const int64_t d = r / Hout;
+        const float fy = sy * (float)y, fx = sx * (float)x;
+        int y0 = (int)fy, x0 = (int)fx;
+        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+        x0 = x0 < Win - 1 ? x0 : Win - 1;
+        const int y1 = y0 + (y0 < Hin - 1), x1 = x0 + (x0 < Win - 1);
+        const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), lx = fminf(fmaxf(fx - (float)x0, 0.f), 1.f);
+        const float hy = 1.f - ly, hx = 1.f - lx;
+        const float* im = src + (size_t)d * Hin * Win;
+        const float a = __ldg(im + (size_t)y0 * Win + x0), b = __ldg(im + (size_t)y0 * Win + x1);
+        const float c = __ldg(im + (size_t)y1 * Win + x0), e = __ldg(im + (size_t)y1 * Win + x1);
+        dst[i] = hy * (hx * a + lx * b) + ly * (hx * c + lx * e);
+    }
+}
+
+// ------------------------------ forward ------------------------------------------------
+// record: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
+__global__ void __launch_bounds__(kLossThreads)
+warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
+                     float* __restrict__ partials) {
+    __shared__ float F[2][kTile + 1][kTile + 2];
+    __shared__ float red[kLossThreads / 32][kRec];
+    const TileCoord tc = decode_cta(tab);
+    const int H = tab.H[tc.s], W = tab.W[tc.s], P = tab.n_pred;
+    const size_t plane = (size_t)H * W;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    for (int i = threadIdx.x; i < 2 * (kTile + 1) * (kTile + 1); i += kLossThreads) {
+        const int ch = i / ((kTile + 1) * (kTile + 1));
+        const int rem = i - ch * (kTile + 1) * (kTile + 1);
+        const int ly = rem / (kTile + 1), lx = rem - ly * (kTile + 1);
+        const int y = tc.y0 + ly, x = tc.x0 + lx;
+        F[ch][ly][lx] = (y < H && x < W) ? __ldg(flow + ch * plane + (size_t)y * W + x) : 0.f;
+    }
+    __syncthreads();
+    const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
+    const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
+    const int lx = threadIdx.x & 31, lyb = threadIdx.x >> 5;
+    const int x = tc.x0 + lx;
+    float acc[kRec] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < kTile / 8; ++r) {
+        const int ly = lyb + 8 * r, y = tc.y0 + ly;
+        if (y >= H || x >= W) continue;
+        const float u = F[0][ly][lx], v = F[1][ly][lx];
+        const Warp wp = warp_sample(next, H, W, x, y, u, v);
+        acc[0] += charb(wp.val - __ldg(prev + (size_t)y * W + x));         // loss.py:72-74
+        const bool right = x + 1 < W, down = y + 1 < H;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {                                    // loss.py:76-90
+            const float f = F[ch][ly][lx];
+            if (right) acc[1] += charb(F[ch][ly][lx + 1] - f);
+            if (down) acc[2] += charb(F[ch][ly + 1][lx] - f);
+            if (right && down) {
+                acc[3] += charb(F[ch][ly + 1][lx + 1] - f);
+                acc[4] += charb(F[ch][ly][lx + 1] - F[ch][ly + 1][lx]);
+            }
+        }
+        if (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f) {   // loss.py:92-94
+            acc[5] += charb(u) + charb(v);
+            acc[6] += 1.f;
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 7; ++k) acc[k] = warp_sum(acc[k]);
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 7; ++k) red[threadIdx.x >> 5][k] = acc[k];
+    __syncthreads();
+    if (threadIdx.x < 7) {
+        float t = 0.f;
+        for (int w = 0; w < kLossThreads / 32; ++w) t += red[w][threadIdx.x];
+        partials[(size_t)blockIdx.x * kRec + threadIdx.x] = t;
+    }
+}
+
+// one CTA per scale, one warp per prediction: fixed-order fp64 sums of the tile records
+__global__ void __launch_bounds__(1024)
+warp_loss_finalize_kernel(const __grid_constant__ ScaleTable tab, const float* __restrict__ partials,
+                          float* __restrict__ terms, int32_t* __restrict__ n_bad) {
+    __shared__ double wacc[32][6];
+    const int s = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int P = tab.n_pred, H = tab.H[s], W = tab.W[s];
+    const int per = tab.tiles_x[s] * tab.tiles_y[s];
+    double tot[6] = {0, 0, 0, 0, 0, 0};   // photo, h, v, d_a, d_b, outborder
+    for (int n = warp; n < P; n += 32) {
+        double a[7] = {0, 0, 0, 0, 0, 0, 0};
+        const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
+        for (int t = lane; t < per; t += 32)
+#pragma unroll
+            for (int k = 0; k < 7; ++k) a[k] += (double)rec[(size_t)t * kRec + k];
+#pragma unroll
+        for (int k = 0; k < 7; ++k)
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+        for (int k = 0; k < 5; ++k) tot[k] += a[k];
+        const double nb = a[6];
+        if (nb > 0) tot[5] += a[5] / (2.0 * nb * (double)P);               // loss.py:99-113
+        if (lane == 0) n_bad[s * P + n] = (int32_t)nb;
+    }
+    if (lane == 0)
+        for (int k = 0; k < 6; ++k) wacc[warp][k] = tot[k];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t[6] = {0, 0, 0, 0, 0, 0};
+        for (int w = 0; w < 32; ++w)
+            for (int k = 0; k < 6; ++k) t[k] += wacc[w][k];
+        const double N2 = 2.0 * P;
+        const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
+        double sm = 0;
+        if (ch > 0) sm += t[1] / ch;
+        if (cv > 0) sm += t[2] / cv;
+        if (cd > 0) sm += (t[3] + t[4]) / cd;
+        const int S = tab.n_scales;
+        terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
+        terms[S + s] = (float)(t[0] / ((double)P * H * W));                  // loss.py:33
+        terms[2 * S + s] = (float)t[5];
+    }
+}
+
+// ------------------------------ backward -----------------------------------------------
+// d(terms)/d(flow), contracted with grad_terms.  Every pixel gathers its own gradient (no
+// atomics): photometric via the bilinear tap differences, out-of-border via c'(flow)/(2 n_i N),
+// smoothness from the 8 neighbour differences it takes part in.
+__global__ void __launch_bounds__(kLossThreads)
+warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
+                     const float* __restrict__ grad_terms, const int32_t* __restrict__ n_bad) {
+    __shared__ float F[2][kTile + 2][kTile + 3];   // halo of 1 on every side; F[.][ly+1][lx+1]
+    const TileCoord tc = decode_cta(tab);
+    const int S = tab.n_scales, P = tab.n_pred;
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const size_t plane = (size_t)H * W;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    float* grad = tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane;
+    for (int i = threadIdx.x; i < 2 * (kTile + 2) * (kTile + 2); i += kLossThreads) {
+        const int ch = i / ((kTile + 2) * (kTile + 2));
+        const int rem = i - ch * (kTile + 2) * (kTile + 2);
+        const int ly = rem / (kTile + 2), lx = rem - ly * (kTile + 2);
+        const int y = tc.y0 + ly - 1, x = tc.x0 + lx - 1;
+        F[ch][ly][lx] = (y >= 0 && y < H && x >= 0 && x < W)
+                            ? __ldg(flow + ch * plane + (size_t)y * W + x) : 0.f;
+    }
+    __syncthreads();
+    const float g_sm = grad_terms[tc.s], g_ph = grad_terms[S + tc.s], g_ob = grad_terms[2 * S + tc.s];
+    const float N2 = 2.f * (float)P;
+    const float ch_n = N2 * (float)H * (float)(W - 1), cv_n = N2 * (float)(H - 1) * (float)W;
+    const float cd_n = N2 * (float)(H - 1) * (float)(W - 1);
+    const float k_h = ch_n > 0.f ? 0.25f * g_sm / ch_n : 0.f;
+    const float k_v = cv_n > 0.f ? 0.25f * g_sm / cv_n : 0.f;
+    const float k_d = cd_n > 0.f ? 0.25f * g_sm / cd_n : 0.f;
+    const float k_ph = g_ph / ((float)P * (float)H * (float)W);
+    const int nb = n_bad[tc.s * P + tc.n];
+    const float k_ob = nb > 0 ? g_ob / (2.f * (float)nb * (float)P) : 0.f;
+    const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
+    const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
+    const int lx = (threadIdx.x & 31) + 1, lyb = threadIdx.x >> 5;
+    const int x = tc.x0 + lx - 1;
+#pragma unroll
+    for (int r = 0; r < kTile / 8; ++r) {
+        const int ly = lyb + 8 * r + 1, y = tc.y0 + ly - 1;
+        if (y >= H || x >= W) continue;
+        const float u = F[0][ly][lx], v = F[1][ly][lx];
+        const Warp wp = warp_sample(next, H, W, x, y, u, v);
+        const float cp = k_ph * charb_grad(wp.val - __ldg(prev + (size_t)y * W + x));
+        float g[2] = {cp * wp.ddx, cp * wp.ddy};
+        if (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f) {
+            g[0] += k_ob * charb_grad(u);
+            g[1] += k_ob * charb_grad(v);
+        }
+        const bool L = x > 0, R = x + 1 < W, U = y > 0, Dn = y + 1 < H;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            const float f = F[ch][ly][lx];
+            float a = 0.f;
+            if (L) a += k_h * charb_grad(f - F[ch][ly][lx - 1]);
+            if (R) a -= k_h * charb_grad(F[ch][ly][lx + 1] - f);
+            if (U) a += k_v * charb_grad(f - F[ch][ly - 1][lx]);
+            if (Dn) a -= k_v * charb_grad(F[ch][ly + 1][lx] - f);
+            if (U && L) a += k_d * charb_grad(f - F[ch][ly - 1][lx - 1]);
+            if (Dn && R) a -= k_d * charb_grad(F[ch][ly + 1][lx + 1] - f);
+            if (Dn && L) a += k_d * charb_grad(f - F[ch][ly + 1][lx - 1]);
+            if (U && R) a -= k_d * charb_grad(F[ch][ly - 1][lx + 1] - f);
+            g[ch] += a;
+        }
+        grad[(size_t)y * W + x] = g[0];
+        grad[plane + (size_t)y * W + x] = g[1];
+    }
+}
+
+}  // namespace dvsof
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+using namespace dvsof;
+
+static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need_grad) {
+    if (!sc) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: null scale table");
+    if (sc->n_scales < 1 || sc->n_scales > DVSOF_MAX_SCALES || sc->n_pred < 1)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: n_scales=%d n_pred=%d", sc->n_scales, sc->n_pred);
+    tab->n_scales = sc->n_scales;
+    tab->n_pred = sc->n_pred;
+    int64_t begin = 0;
+    for (int s = 0; s < sc->n_scales; ++s) {
+        if (sc->H[s] < 1 || sc->W[s] < 1 || !sc->flow[s] || !sc->images[s] ||
+            (need_grad && !sc->grad_flow[s]))
+            return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: bad scale %d", s);
+        tab->H[s] = sc->H[s];
+        tab->W[s] = sc->W[s];
+        tab->tiles_x[s] = (sc->W[s] + kTile - 1) / kTile;
+        tab->tiles_y[s] = (sc->H[s] + kTile - 1) / kTile;
+        tab->flow[s] = sc->flow[s];
+        tab->images[s] = sc->images[s];
+        tab->grad_flow[s] = sc->grad_flow[s];
+        tab->cta_begin[s] = (int)begin;
+        begin += (int64_t)tab->tiles_x[s] * tab->tiles_y[s] * sc->n_pred;
+        if (begin > INT32_MAX) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: too many tiles");
+    }
+    for (int s = sc->n_scales; s <= DVSOF_MAX_SCALES; ++s) tab->cta_begin[s] = (int)begin;
+    return DVSOF_OK;
+}
+
+extern "C" size_t dvsof_loss_workspace_bytes(const dvsof_loss_scales_t* sc) {
+    ScaleTable tab;
+    if (build_table(sc, &tab, false)) return 0;
+    return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
+}
+
+extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
+                                       float* terms, int32_t* n_bad, void* workspace,
+                                       void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, false)) return rc;
+    if (!match_idx || !terms || !n_bad || !workspace)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_forward: null buffer");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    float* partials = reinterpret_cast<float*>(workspace);
+    warp_loss_fwd_kernel<<<tab.cta_begin[DVSOF_MAX_SCALES], kLossThreads, 0, stream>>>(tab, match_idx, partials);
+    if (int rc = check_launch("warp_loss_fwd_kernel")) return rc;
+    warp_loss_finalize_kernel<<<tab.n_scales, 1024, 0, stream>>>(tab, partials, terms, n_bad);
+    return check_launch("warp_loss_finalize_kernel");
+}
+
+extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
+                                        const float* grad_terms, const int32_t* n_bad,
+                                        void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, true)) return rc;
+    if (!match_idx || !grad_terms || !n_bad)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_backward: null buffer");
+    warp_loss_bwd_kernel<<<tab.cta_begin[DVSOF_MAX_SCALES], kLossThreads, 0, (cudaStream_t)stream_>>>(
+        tab, match_idx, grad_terms, n_bad);
+    return check_launch("warp_loss_bwd_kernel");
+}
+
+extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_sample_idx,
+                                      int64_t P, const float* timestamps,
+                                      const int64_t* sample_idx, int64_t D, int32_t* match_idx,
+                                      uint32_t* status, void* stream_) {
+    if (P < 1 || D < 1 || P > (1 << 24) || D > (1 << 24) || !flow_ts || !flow_sample_idx ||
+        !timestamps || !sample_idx || !match_idx || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "match_timestamps: bad arguments");
+    const int threads = 128, blocks = (int)((2 * P + threads - 1) / threads);
+    match_timestamps_kernel<<<blocks, threads, 0, (cudaStream_t)stream_>>>(
+        flow_ts, flow_sample_idx, (int)P, timestamps, sample_idx, (int)D, match_idx, status);
+    return check_launch("match_timestamps_kernel");
+}
+
+extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
+                                     float* dst, int32_t Hout, int32_t Wout, void* stream_) {
+    if (D < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || !src || !dst)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: bad arguments");
+    const int64_t total = D * Hout * Wout;
+    int64_t blocks = (total + 255) / 256;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+    resize_bilinear_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(src, Hin, Win, dst, Hout, Wout, total);
+    return check_launch("resize_bilinear_kernel");
+}

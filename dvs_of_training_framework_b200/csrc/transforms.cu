@@ -1,0 +1,331 @@
+// transforms.cu -- event transforms around the encoder: count image (utils/data.py:120-136),
+// EventCrop (utils/data.py:24-42) and the native LUT remap `map_events`
+// (utils/modules_to_build/transformations/src/transformation.cpp:35-85).
+//
+// All three are integer / data-movement work, bit-exact by construction.  The two with a
+// data-dependent output size use the same ordered-compaction skeleton:
+//   pass 1  per-1024-row chunk fan-out sums            -> chunk_sums[nb]
+//   pass 2  single-CTA exclusive scan of chunk sums    -> chunk offsets, total (*n_out)
+//   pass 3  recompute fan-out, CTA-local scan, write rows at chunk offset + local offset
+// so the input is read twice and nothing per-row is materialised in HBM.
+#include "common.cuh"
+
+namespace dvsof {
+
+constexpr int kCompactThreads = 256;
+constexpr int kRowsPerThread = 4;
+constexpr int kChunk = kCompactThreads * kRowsPerThread;  // rows per CTA
+
+// exclusive scan of one int per thread across the CTA; returns the exclusive prefix, *total = sum
+__device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* total) {
+    __shared__ int64_t warp_tot[kCompactThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int64_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int64_t up = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += up;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    int64_t warp_prefix = 0, sum = 0;
+#pragma unroll
+    for (int w = 0; w < kCompactThreads / 32; ++w) {
+        if (w == warp) warp_prefix = sum;
+        sum += warp_tot[w];
+    }
+    __syncthreads();
+    *total = sum;
+    return warp_prefix + inc - v;
+}
+
+template <class Count>
+__global__ void __launch_bounds__(kCompactThreads)
+chunk_sums_kernel(Count count, int64_t n, int64_t* __restrict__ chunk_sums) {
+    const int64_t base = (int64_t)blockIdx.x * kChunk + (int64_t)threadIdx.x * kRowsPerThread;
+    int64_t c = 0;
+#pragma unroll
+    for (int k = 0; k < kRowsPerThread; ++k)
+        if (base + k < n) c += count(base + k);
+    int64_t total;
+    block_exclusive_scan(c, &total);
+    if (threadIdx.x == 0) chunk_sums[blockIdx.x] = total;
+}
+
+// in-place exclusive scan of chunk_sums[0..nb), total -> *n_out.  One CTA, sequential carry.
+__global__ void __launch_bounds__(kCompactThreads)
+scan_chunk_sums_kernel(int64_t* __restrict__ chunk_sums, int64_t nb, int64_t* __restrict__ n_out) {
+    int64_t carry = 0;
+    for (int64_t base = 0; base < nb; base += kCompactThreads) {
+        const int64_t i = base + threadIdx.x;
+        const int64_t v = (i < nb) ? chunk_sums[i] : 0;
+        int64_t total;
+        const int64_t ex = block_exclusive_scan(v, &total);
+        if (i < nb) chunk_sums[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) *n_out = carry;
+}
+
+template <class Count, class Write>
+__global__ void __launch_bounds__(kCompactThreads)
+compact_write_kernel(Count count, Write write, int64_t n, const int64_t* __restrict__ chunk_offsets) {
+    const int64_t base = (int64_t)blockIdx.x * kChunk + (int64_t)threadIdx.x * kRowsPerThread;
+    int64_t cnt[kRowsPerThread];
+    int64_t c = 0;
+#pragma unroll
+    for (int k = 0; k < kRowsPerThread; ++k) {
+        cnt[k] = (base + k < n) ? count(base + k) : 0;
+        c += cnt[k];
+    }
+    int64_t total;
+    int64_t pos = chunk_offsets[blockIdx.x] + block_exclusive_scan(c, &total);
+#pragma unroll
+    for (int k = 0; k < kRowsPerThread; ++k) {
+        if (cnt[k]) write(base + k, pos, cnt[k]);
+        pos += cnt[k];
+    }
+}
+
+// ------------------------------ count image -------------------------------------------
+__global__ void __launch_bounds__(256)
+count_image_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y, int64_t n, int H,
+                   int W, unsigned long long* __restrict__ out, uint32_t* __restrict__ status) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned flags = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int64_t xi = __ldcs(x + i), yi = __ldcs(y + i);
+        if ((uint64_t)xi >= (uint64_t)W || (uint64_t)yi >= (uint64_t)H) {
+            flags |= DVSOF_ST_BAD_PIXEL;
+            continue;
+        }
+        atomicAdd(out + (size_t)yi * W + xi, 1ull);
+    }
+    if (flags) atomicOr(status, flags);
+}
+
+// ------------------------------ event crop --------------------------------------------
+template <typename T>
+struct CropCount {
+    const T* ev; int E; double y0, x0, y1, x1;
+    __device__ int64_t operator()(int64_t r) const {
+        const double x = (double)ev[r * E], y = (double)ev[r * E + 1];
+        return (x >= x0 && x < x1 && y >= y0 && y < y1) ? 1 : 0;   // utils/data.py:35-38
+    }
+};
+template <typename T>
+struct CropWrite {
+    const T* ev; T* out; int E; double y0, x0;
+    __device__ void operator()(int64_t r, int64_t pos, int64_t) const {
+        const T* src = ev + r * E;
+        T* dst = out + pos * E;
+        dst[0] = (T)((double)src[0] - x0);                          // utils/data.py:41
+        dst[1] = (T)((double)src[1] - y0);
+        for (int c = 2; c < E; ++c) dst[c] = src[c];
+    }
+};
+
+// ------------------------------ map_events --------------------------------------------
+// lut_ws layout: off[HW+1] | cnt[HW] | cursor[HW] | (int64) chunk sums | total | lut_dst[M] | tmp[M]
+struct LutView {
+    int32_t* off; int32_t* cnt; int32_t* cursor; int32_t* tmp; int32_t* lut_dst; int64_t* chunks; int64_t* total; char* end;
+};
+__host__ __device__ inline LutView lut_view(void* ws, int64_t HW, int64_t M) {
+    LutView v;
+    char* p = reinterpret_cast<char*>(ws);
+    auto take = [&](size_t bytes) { char* q = p; p += (bytes + 255) / 256 * 256; return q; };
+    v.off = reinterpret_cast<int32_t*>(take((HW + 1) * 4));
+    v.cnt = reinterpret_cast<int32_t*>(take(HW * 4));
+    v.cursor = reinterpret_cast<int32_t*>(take(HW * 4));
+    v.chunks = reinterpret_cast<int64_t*>(take(((HW + kChunk - 1) / kChunk + 1) * 8));
+    v.total = reinterpret_cast<int64_t*>(take(8));
+    v.lut_dst = reinterpret_cast<int32_t*>(take((M > 0 ? M : 1) * 4));  // position independent of M
+    v.tmp = reinterpret_cast<int32_t*>(take((M > 0 ? M : 1) * 4));
+    v.end = p;
+    return v;
+}
+
+__global__ void lut_hist_kernel(const uint64_t* __restrict__ src, const uint64_t* __restrict__ dst,
+                                int64_t M, int64_t HW, int32_t* __restrict__ cnt,
+                                uint32_t* __restrict__ status) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    if (src[k] >= (uint64_t)HW || dst[k] >= (uint64_t)HW) { atomicOr(status, DVSOF_ST_BAD_LUT); return; }
+    atomicAdd(cnt + src[k], 1);
+}
+struct LutCount {
+    const int32_t* cnt;
+    __device__ int64_t operator()(int64_t r) const { return cnt[r]; }
+};
+struct LutOffWrite {   // exclusive offsets of the per-pixel lists
+    int32_t* off;
+    __device__ void operator()(int64_t r, int64_t pos, int64_t) const { off[r] = (int32_t)pos; }
+};
+__global__ void lut_fill_kernel(const uint64_t* __restrict__ src, const uint64_t* __restrict__ dst,
+                                int64_t M, int64_t HW, const int32_t* __restrict__ off,
+                                int32_t* __restrict__ cursor, int32_t* __restrict__ tmp) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    const uint64_t s = src[k];
+    if (s >= (uint64_t)HW || dst[k] >= (uint64_t)HW) return;
+    const int slot = atomicAdd(cursor + s, 1);
+    tmp[off[s] + slot] = (int32_t)k;
+}
+// restore LUT (insertion) order inside every pixel list: rank of k among its list-mates
+__global__ void lut_rank_kernel(const uint64_t* __restrict__ src, const uint64_t* __restrict__ dst,
+                                int64_t M, int64_t HW, const int32_t* __restrict__ off,
+                                const int32_t* __restrict__ cnt, const int32_t* __restrict__ tmp,
+                                int32_t* __restrict__ lut_dst) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= M) return;
+    const uint64_t s = src[k];
+    if (s >= (uint64_t)HW || dst[k] >= (uint64_t)HW) return;
+    const int begin = off[s], len = cnt[s];
+    int rank = 0;
+    for (int j = 0; j < len; ++j) rank += (tmp[begin + j] < (int32_t)k);
+    lut_dst[begin + rank] = (int32_t)dst[k];
+}
+
+__device__ __forceinline__ int event_pixel_key(const float* ev, int W) {
+    // transformation.cpp:62,74: ravel(int(y), int(x)) with float->int truncation
+    return __float2int_rz(ev[1]) * W + __float2int_rz(ev[0]);
+}
+struct MapCount {
+    const float* ev; int E; int W; int64_t HW; const int32_t* cnt;
+    __device__ int64_t operator()(int64_t r) const {
+        const int key = event_pixel_key(ev + r * E, W);
+        return (key >= 0 && key < HW) ? cnt[key] : 0;
+    }
+};
+struct MapWrite {
+    const float* ev; float* out; int E; int W; const int32_t* off; const int32_t* lut_dst;
+    __device__ void operator()(int64_t r, int64_t pos, int64_t c) const {
+        const float* src = ev + r * E;
+        const int key = event_pixel_key(src, W);
+        const int32_t* d = lut_dst + off[key];
+        for (int64_t j = 0; j < c; ++j) {
+            float* dst = out + (pos + j) * E;
+            dst[0] = (float)(d[j] % W);                             // transformation.cpp:78-80
+            dst[1] = (float)(d[j] / W);
+            for (int col = 2; col < E; ++col) dst[col] = src[col];  // :81 memcpy
+        }
+    }
+};
+
+template <class Count>
+static int run_scan(Count count, int64_t n, int64_t* chunks, int64_t* n_out, cudaStream_t stream) {
+    const int64_t nb = (n + kChunk - 1) / kChunk;
+    if (nb > 0) chunk_sums_kernel<<<(unsigned)nb, kCompactThreads, 0, stream>>>(count, n, chunks);
+    scan_chunk_sums_kernel<<<1, kCompactThreads, 0, stream>>>(chunks, nb, n_out);
+    return check_launch("compaction scan");
+}
+
+}  // namespace dvsof
+
+// ---------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------
+using namespace dvsof;
+
+extern "C" int dvsof_count_image(const int64_t* x, const int64_t* y, int64_t n, int32_t H,
+                                 int32_t W, unsigned long long* out, uint32_t* status,
+                                 void* stream_) {
+    if (n < 0 || H <= 0 || W <= 0 || !out || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "count_image: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    cudaError_t e = cudaMemsetAsync(out, 0, (size_t)H * W * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "count_image memset: %s", cudaGetErrorString(e));
+    if (n == 0) return DVSOF_OK;
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+    count_image_kernel<<<(unsigned)blocks, 256, 0, stream>>>(x, y, n, H, W, out, status);
+    return check_launch("count_image_kernel");
+}
+
+extern "C" size_t dvsof_compact_workspace_bytes(int64_t n_rows) {
+    const int64_t nb = (n_rows + kChunk - 1) / kChunk;
+    return round_up((size_t)(nb + 1) * sizeof(int64_t), 256);
+}
+
+template <typename T>
+static int event_crop_t(const void* events, int64_t n, int E, double y0, double x0, double h,
+                        double w, void* out, int64_t* n_out, void* ws, cudaStream_t stream) {
+    CropCount<T> count{(const T*)events, E, y0, x0, y0 + h, x0 + w};
+    CropWrite<T> write{(const T*)events, (T*)out, E, y0, x0};
+    int64_t* chunks = reinterpret_cast<int64_t*>(ws);
+    if (int rc = run_scan(count, n, chunks, n_out, stream)) return rc;
+    const int64_t nb = (n + kChunk - 1) / kChunk;
+    if (nb > 0)
+        compact_write_kernel<<<(unsigned)nb, kCompactThreads, 0, stream>>>(count, write, n, chunks);
+    return check_launch("event_crop write");
+}
+
+extern "C" int dvsof_event_crop(const void* events, int64_t n, int32_t n_cols, int32_t elem_size,
+                                double y0, double x0, double h, double w, void* out,
+                                int64_t* n_out, void* workspace, void* stream_) {
+    if (n < 0 || n_cols < 2 || !n_out || !workspace || (n > 0 && (!events || !out)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "event_crop: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (elem_size == 4) return event_crop_t<float>(events, n, n_cols, y0, x0, h, w, out, n_out, workspace, stream);
+    if (elem_size == 8) return event_crop_t<double>(events, n, n_cols, y0, x0, h, w, out, n_out, workspace, stream);
+    return fail(DVSOF_ERR_INVALID_ARGUMENT, "event_crop: elem_size must be 4 or 8, got %d", elem_size);
+}
+
+extern "C" size_t dvsof_map_lut_workspace_bytes(int32_t H, int32_t W, int64_t M) {
+    const int64_t HW = (int64_t)H * W;
+    LutView v = lut_view(nullptr, HW, M);
+    return (size_t)(v.end - (char*)nullptr);
+}
+
+extern "C" int dvsof_map_events_build(const uint64_t* src, const uint64_t* dst, int64_t M,
+                                      int32_t H, int32_t W, void* lut_ws, uint32_t* status,
+                                      void* stream_) {
+    if (M < 0 || H <= 0 || W <= 0 || !lut_ws || !status || (M > 0 && (!src || !dst)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "map_events_build: bad arguments");
+    const int64_t HW = (int64_t)H * W;
+    if (HW >= INT32_MAX || M >= INT32_MAX)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "map_events_build: image or LUT too large");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    LutView v = lut_view(lut_ws, HW, M);
+    // cnt and cursor are adjacent in the workspace: one memset clears both
+    cudaError_t e = cudaMemsetAsync(v.cnt, 0, (size_t)((char*)v.chunks - (char*)v.cnt), stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "map build memset: %s", cudaGetErrorString(e));
+    const unsigned mb = (unsigned)((M + 255) / 256);
+    if (M > 0) lut_hist_kernel<<<mb, 256, 0, stream>>>(src, dst, M, HW, v.cnt, status);
+    LutCount count{v.cnt};
+    if (int rc = run_scan(count, HW, v.chunks, v.total, stream)) return rc;
+    const int64_t nb = (HW + kChunk - 1) / kChunk;
+    compact_write_kernel<<<(unsigned)nb, kCompactThreads, 0, stream>>>(count, LutOffWrite{v.off}, HW, v.chunks);
+    if (M > 0) {
+        lut_fill_kernel<<<mb, 256, 0, stream>>>(src, dst, M, HW, v.off, v.cursor, v.tmp);
+        lut_rank_kernel<<<mb, 256, 0, stream>>>(src, dst, M, HW, v.off, v.cnt, v.tmp, v.lut_dst);
+    }
+    return check_launch("map_events_build");
+}
+
+extern "C" int dvsof_map_events_count(const float* events, int64_t n, int32_t n_cols, int32_t H,
+                                      int32_t W, const void* lut_ws, void* ev_ws, int64_t* n_out,
+                                      void* stream_) {
+    if (n < 0 || n_cols < 2 || !lut_ws || !ev_ws || !n_out || (n > 0 && !events))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "map_events_count: bad arguments");
+    const int64_t HW = (int64_t)H * W;
+    LutView v = lut_view(const_cast<void*>(lut_ws), HW, 0);
+    MapCount count{events, n_cols, W, HW, v.cnt};
+    return run_scan(count, n, reinterpret_cast<int64_t*>(ev_ws), n_out, (cudaStream_t)stream_);
+}
+
+extern "C" int dvsof_map_events_write(const float* events, int64_t n, int32_t n_cols, int32_t H,
+                                      int32_t W, const void* lut_ws, const void* ev_ws, float* out,
+                                      void* stream_) {
+    if (n < 0 || n_cols < 2 || !lut_ws || !ev_ws)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "map_events_write: bad arguments");
+    if (n == 0) return DVSOF_OK;
+    const int64_t HW = (int64_t)H * W;
+    LutView v = lut_view(const_cast<void*>(lut_ws), HW, 0);
+    MapCount count{events, n_cols, W, HW, v.cnt};
+    MapWrite write{events, out, n_cols, W, v.off, v.lut_dst};
+    const int64_t nb = (n + kChunk - 1) / kChunk;
+    compact_write_kernel<<<(unsigned)nb, kCompactThreads, 0, (cudaStream_t)stream_>>>(
+        count, write, n, reinterpret_cast<const int64_t*>(ev_ws));
+    return check_launch("map_events_write");
+}

@@ -1,0 +1,195 @@
+"""Self-supervised multiscale warp loss -- drop-in for the reference's `utils/loss.py`
+(`Loss` :38-171, `Losses` :174-214, `init_losses` :217-240, `charbonier_loss` :24-35,
+`interpolate` :20-21), forward AND backward on the fused sm_100a kernels of csrc/loss.cu.
+
+Same names, positional order, defaults and return structure as the reference; results are
+autograd-connected 0-dim tensors.  There is no CPU path: inputs must be CUDA tensors."""
+from typing import Optional
+
+import torch
+
+from . import _lib
+from .timer import FakeTimer
+
+
+def _f32(t, name):
+    return _lib.require_cuda(t, name, torch.float32)
+
+
+def interpolate(img, shape):
+    """utils/loss.py:20-21: bilinear, align_corners=True.  img (D,1,H,W) or (D,H,W) fp32."""
+    img = _f32(img, 'img')
+    lead = img.shape[:-2]
+    hin, win = img.shape[-2:]
+    hout, wout = int(shape[0]), int(shape[1])
+    out = torch.empty(lead + (hout, wout), dtype=torch.float32, device=img.device)
+    d = img.numel() // (hin * win)
+    if d:
+        with torch.cuda.device(img.device):
+            _lib.call('dvsof_resize_bilinear', _lib.ptr(img), d, hin, win, _lib.ptr(out), hout,
+                      wout, _lib.stream_ptr(img.device))
+    return out
+
+
+def charbonier_loss(delta, alpha: float = 0.45, epsilon: float = 1e-3,
+                    denominator: Optional[torch.Tensor] = None,
+                    device: Optional[torch.device] = torch.device('cpu')):
+    """utils/loss.py:24-35.  Kept for API compatibility (plain tensor ops, any device); the fused
+    kernels evaluate the same penalty inline."""
+    if delta.numel() == 0:
+        return torch.tensor(0, dtype=torch.float32, device=device)
+    delta = (delta.pow(2) + epsilon * epsilon).pow(alpha)
+    if denominator is None:
+        return delta.mean()
+    assert denominator.numel() == delta.numel()
+    return (delta / denominator).sum()
+
+
+def _scale_struct(flows, levels, grads=None):
+    sc = _lib.LossScales()
+    sc.n_scales = len(flows)
+    sc.n_pred = flows[0].shape[0]
+    for s, (f, im) in enumerate(zip(flows, levels)):
+        sc.H[s], sc.W[s] = f.shape[-2], f.shape[-1]
+        sc.flow[s] = f.data_ptr()
+        sc.images[s] = im.data_ptr()
+        sc.grad_flow[s] = grads[s].data_ptr() if grads is not None else None
+    return sc
+
+
+class _WarpLoss(torch.autograd.Function):
+    """terms[3*S] = [smoothness(s)..., photometric(s)..., outborder(s)...] of all scales in one
+    fused launch; backward is the analytic gradient w.r.t. every flow (images get none)."""
+
+    @staticmethod
+    def forward(ctx, match_idx, n_scales, *tensors):
+        levels, flows = tensors[:n_scales], tensors[n_scales:]
+        dev = flows[0].device
+        P = flows[0].shape[0]
+        with torch.cuda.device(dev):
+            sc = _scale_struct(flows, levels)
+            lib = _lib.load()
+            ws = torch.empty(lib.dvsof_loss_workspace_bytes(sc), dtype=torch.uint8, device=dev)
+            terms = torch.empty(3 * n_scales, dtype=torch.float32, device=dev)
+            n_bad = torch.empty(n_scales * P, dtype=torch.int32, device=dev)
+            _lib.call('dvsof_warp_loss_forward', sc, _lib.ptr(match_idx), _lib.ptr(terms),
+                      _lib.ptr(n_bad), _lib.ptr(ws), _lib.stream_ptr(dev))
+        ctx.n_scales = n_scales
+        ctx.save_for_backward(match_idx, n_bad, *levels, *flows)
+        return terms
+
+    @staticmethod
+    def backward(ctx, grad_terms):
+        S = ctx.n_scales
+        match_idx, n_bad = ctx.saved_tensors[:2]
+        levels, flows = ctx.saved_tensors[2:2 + S], ctx.saved_tensors[2 + S:]
+        dev = flows[0].device
+        grad_terms = grad_terms.contiguous()
+        grads = [torch.empty_like(f) for f in flows]
+        with torch.cuda.device(dev):
+            sc = _scale_struct(flows, levels, grads)
+            _lib.call('dvsof_warp_loss_backward', sc, _lib.ptr(match_idx), _lib.ptr(grad_terms),
+                      _lib.ptr(n_bad), _lib.stream_ptr(dev))
+        return (None, None) + (None,) * S + tuple(grads)
+
+
+def _check_shapes(owner, N, H, W):
+    # utils/loss.py:122-131 (same messages' meaning, AssertionError)
+    assert owner.N >= N, f'This object should be used for batch of at most {owner.N} samples, ' \
+                         f'but {N} samples are given'
+    assert owner.H == H, f'This object should be used for images of height {owner.H}, ' \
+                         f'but image of height {H} are given'
+    assert owner.W == W, f'This object should be used for images of width {owner.W}, ' \
+                         f'but image of width {W} are given'
+
+
+class Loss:
+    """One scale (utils/loss.py:38-171)."""
+
+    def __init__(self, pred_shape, batch_size, device, timers=FakeTimer()):
+        self.N = batch_size
+        self.H, self.W = pred_shape
+        self.device = device
+        self.timers = timers
+
+    def __call__(self, prev_images, next_images, flow):
+        N, C, H, W = prev_images.size()
+        _check_shapes(self, N, H, W)
+        assert tuple(next_images.size()) == (N, C, H, W)                   # loss.py:133-137
+        FN, FC, FH, FW = flow.size()
+        assert FN == N, f'Number of images and flows should be the same {N} vs {FN}'
+        assert FC == 2, 'Flow should contain 2 channels (dx and dy)'
+        assert FH == H, f'Height of images and flows should be the same {H} vs {FH}'
+        assert FW == W, f'Width of images and flows should be the same {W} vs {FW}'
+        assert C == 1, 'the fused kernel warps single-channel (grayscale) frames'
+        for name in ('grid_construction', 'smoothness_loss', 'outborder_loss'):
+            self.timers(name).start()
+            self.timers(name).stop()
+        self.timers('photometric_loss').start()
+        flow = _f32(flow, 'flow')
+        level = torch.cat((_f32(prev_images, 'prev_images').view(N, H, W),
+                           _f32(next_images, 'next_images').view(N, H, W)))
+        match_idx = torch.arange(2 * N, dtype=torch.int32, device=flow.device)
+        terms = _WarpLoss.apply(match_idx, 1, level, flow)
+        self.timers('photometric_loss').stop()
+        smoothness, photometric, outborder = terms.unbind(0)
+        return smoothness, photometric, outborder
+
+
+class Losses:
+    """All scales (utils/loss.py:174-214): image<->flow timestamp matching, the CHAINED bilinear
+    pyramid (line 210) and the per-scale terms, with no host synchronisation."""
+
+    def __init__(self, shapes, batch_size, device, timers=FakeTimer()):
+        self.losses = [Loss(shape, batch_size, device, timers) for shape in shapes]
+        self.timers = timers
+
+    def __call__(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+        S = len(flows)
+        assert S == len(self.losses) and 1 <= S <= _lib.MAX_SCALES
+        images = _f32(images, 'images')
+        dev = images.device
+        D, C, H, W = images.size()
+        assert C == 1, 'the fused kernel warps single-channel (grayscale) frames'
+        P = flow_sample_idx.shape[0]
+        flows = [_f32(f, 'flow') for f in flows]
+        for loss, f in zip(self.losses, flows):
+            assert f.dim() == 4 and f.shape[0] == P and f.shape[1] == 2
+            _check_shapes(loss, P, f.shape[-2], f.shape[-1])
+        with torch.no_grad(), torch.cuda.device(dev):
+            st = _lib.status_for(dev)
+            st.flush()
+            match_idx = torch.empty(2 * P, dtype=torch.int32, device=dev)
+            _lib.call('dvsof_match_timestamps',
+                      _lib.ptr(_f32(flow_ts, 'flow_ts')),
+                      _lib.ptr(_lib.require_cuda(flow_sample_idx, 'flow_sample_idx', torch.int64)),
+                      P, _lib.ptr(_f32(timestamps, 'timestamps')),
+                      _lib.ptr(_lib.require_cuda(sample_idx, 'sample_idx', torch.int64)), D,
+                      _lib.ptr(match_idx), _lib.ptr(st.word), _lib.stream_ptr(dev))
+            st.after_call()
+            levels = []
+            cur = images.view(D, H, W)
+            for f in flows:                                               # loss.py:207-210
+                cur = interpolate(cur, f.shape[-2:])
+                levels.append(cur)
+        terms = _WarpLoss.apply(match_idx, S, *levels, *flows)
+        flat = terms.unbind(0)
+        return tuple(flat[:S]), tuple(flat[S:2 * S]), tuple(flat[2 * S:])
+
+
+def init_losses(shape, batch_size, model, device, sequence_length, timers=FakeTimer()):
+    """utils/loss.py:217-240: one no-grad model call on EMPTY events to learn the output shapes."""
+    def empty(dtype):
+        return torch.tensor([], dtype=dtype, device=device)
+    events = {'x': empty(torch.long), 'y': empty(torch.long), 'timestamp': empty(torch.float32),
+              'polarity': empty(torch.long), 'element_index': empty(torch.long),
+              'sample_index': empty(torch.long)}
+    with torch.no_grad():
+        num_timestamps = sequence_length + 1
+        out = model(events,
+                    torch.tensor([0.04 * i for i in range(num_timestamps)], dtype=torch.float32,
+                                 device=device),
+                    torch.tensor([0] * num_timestamps, dtype=torch.long, device=device),
+                    shape, raw=True)
+    out_shapes = tuple(tuple(flow.shape[2:]) for flow in out[0])
+    return Losses(out_shapes, batch_size, device, timers=timers)

@@ -1,0 +1,149 @@
+/* dvsof.h -- C ABI of libdvsof.so: the B200 (sm_100a) CUDA hot path of
+ * e-sha/dvs_of_training_framework (event-image encoding, event transforms, multiscale
+ * warp loss forward/backward).
+ *
+ * Conventions
+ *  - every pointer marked [dev] is a device pointer owned by the caller; the library
+ *    allocates nothing and keeps no global state (re-entrant, stream-ordered);
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *  - return value: 0 = DVSOF_OK, negative = host-side argument / launch error, text
+ *    available from dvsof_last_error() (thread-local);
+ *  - data-dependent input validation happens ON DEVICE: kernels OR flag bits into the
+ *    caller's `status` word [dev, uint32, zero-initialised by the caller]; the host binding
+ *    reads it when it chooses (no forced sync) and raises the reference's error type.
+ *
+ * Each entry point cites the reference interface (relative to the reference repo) it
+ * replaces.  No torch types appear here; PyTorch/ctypes bindings live in
+ * dvs_of_training_framework_b200/_lib.py, reference-side stubs in INTEGRATION.md.
+ */
+#ifndef DVSOF_H_
+#define DVSOF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DVSOF_OK 0
+#define DVSOF_ERR_INVALID_ARGUMENT (-1)
+#define DVSOF_ERR_CUDA (-2)
+#define DVSOF_ERR_WORKSPACE (-3)
+
+/* status bits written by kernels */
+#define DVSOF_ST_BAD_POLARITY 0x1u     /* |p| != 1            (EV_FlowNet/net.py:124)      */
+#define DVSOF_ST_NOT_GROUPED 0x2u      /* sample_index not ascending (net.py:131-134)      */
+#define DVSOF_ST_BAD_SAMPLE 0x4u       /* sample_index outside [0, B)                      */
+#define DVSOF_ST_BAD_PIXEL 0x8u        /* x/y outside the image (reference: index error)   */
+#define DVSOF_ST_NO_MATCH 0x10u        /* image<->flow timestamp match != 1 (utils/loss.py:193) */
+#define DVSOF_ST_BAD_LUT 0x20u         /* map_events LUT entry outside [0, H*W)            */
+
+const char* dvsof_last_error(void);
+int dvsof_version(void);
+
+/* ---------------------------------------------------------------------------------------
+ * Event-image encoder.  Replaces EV_FlowNet/net.py:88-150 `compute_event_image` (called from
+ * Model.quantize, net.py:197-205) including the torch_scatter.scatter_sum / scatter_max calls
+ * at net.py:147-149.
+ *   out[b, c, y, x]   = #events with polarity c (c = (1-p)/2),
+ *   out[b, c+2, y, x] = max(0, max (t - start[b]) / dt[b]),  start[b] = timestamps[2b],
+ *   dt[b] = max(t[last event of sample b] - start[b], 1e-9).
+ * Events must be grouped by ascending sample_index.  `out` (B,4,H,W) fp32 is fully
+ * overwritten (zeroed inside the call).  workspace: dvsof_encode_workspace_bytes(B) bytes.
+ * ------------------------------------------------------------------------------------- */
+size_t dvsof_encode_workspace_bytes(int64_t n_samples);
+int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
+                             const int64_t* polarity, const int64_t* sample_index, /* [dev] N */
+                             int64_t n_events,
+                             const float* timestamps, /* [dev] 2*B */
+                             int64_t n_samples, int32_t H, int32_t W,
+                             float* out,        /* [dev] B*4*H*W */
+                             void* workspace,   /* [dev] */
+                             uint32_t* status,  /* [dev] */
+                             void* stream);
+
+/* Compact storage-form entry point: consumes the on-disk/encoded batch layout directly
+ * (utils/dataset.py:286-289 encode_batch: x,y int16, polarity bool, timestamp fp32) plus
+ * per-sample event counts instead of the int64 training form produced by decode_batch
+ * (utils/dataset.py:335-373).  Same output as dvsof_encode_event_image on the decoded batch.
+ * sample_begin: [dev] B+1 int64 exclusive prefix of events per sample. */
+int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,
+                                     const uint8_t* polarity01, /* 1 = positive */
+                                     const int64_t* sample_begin, int64_t n_events,
+                                     const float* timestamps, int64_t n_samples,
+                                     int32_t H, int32_t W, float* out, void* workspace,
+                                     uint32_t* status, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Event transforms.
+ * ------------------------------------------------------------------------------------- */
+/* utils/data.py:120-136 get_count_image: out[y, x] += 1 per event; out (H,W) uint64 is zeroed
+ * inside the call. */
+int dvsof_count_image(const int64_t* x, const int64_t* y, int64_t n_events, int32_t H, int32_t W,
+                      unsigned long long* out, uint32_t* status, void* stream);
+
+/* utils/data.py:24-42 EventCrop.__call__: keep rows with x in [x0,x0+w), y in [y0,y0+h), shift
+ * by (x0,y0), order preserved.  events / out are row-major (N, E) of `elem_size`-byte floats
+ * (4 = fp32, 8 = fp64); out must have room for N rows; *n_out [dev int64] receives N'. */
+size_t dvsof_compact_workspace_bytes(int64_t n_rows);
+int dvsof_event_crop(const void* events, int64_t n_events, int32_t n_cols, int32_t elem_size,
+                     double y0, double x0, double h, double w, void* out, int64_t* n_out,
+                     void* workspace, void* stream);
+
+/* utils/modules_to_build/transformations/src/transformation.cpp:35-85 `map_events`
+ * (python: utils.transformation.map, src/module.cpp:18-40), split in three stream-ordered
+ * steps because the output size is data dependent:
+ *   build: LUT (src[k] -> dst[k], k in LUT order) -> per-pixel CSR lists in `lut_ws`;
+ *   count: per-event fan-out + scan -> *n_out [dev int64];
+ *   write: rows in input order x LUT order; columns >= 2 copied verbatim. */
+size_t dvsof_map_lut_workspace_bytes(int32_t H, int32_t W, int64_t lut_size);
+int dvsof_map_events_build(const uint64_t* src, const uint64_t* dst, int64_t lut_size, int32_t H,
+                           int32_t W, void* lut_ws, uint32_t* status, void* stream);
+int dvsof_map_events_count(const float* events, int64_t n_events, int32_t n_cols, int32_t H,
+                           int32_t W, const void* lut_ws, void* ev_ws /* compact_workspace(N) */,
+                           int64_t* n_out, void* stream);
+int dvsof_map_events_write(const float* events, int64_t n_events, int32_t n_cols, int32_t H,
+                           int32_t W, const void* lut_ws, const void* ev_ws, float* out,
+                           void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Multiscale warp loss.  Replaces utils/loss.py:121-171 (Loss.__call__), :179-214
+ * (Losses.__call__) and autograd's backward of both.
+ * ------------------------------------------------------------------------------------- */
+/* utils/loss.py:182-206: for prediction p and k in {start, stop}: the unique d with
+ * timestamps[d] == flow_ts[p,k] (exact fp32) and sample_idx[d] == flow_sample_idx[p].
+ * match_idx: [dev] int32 2*P (first P = start indices, next P = stop indices). */
+int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_sample_idx, int64_t P,
+                           const float* timestamps, const int64_t* sample_idx, int64_t D,
+                           int32_t* match_idx, uint32_t* status, void* stream);
+
+/* utils/loss.py:20-21 interpolate (bilinear, align_corners=True), one level of the chained
+ * pyramid of utils/loss.py:207-210: src (D,Hin,Win) -> dst (D,Hout,Wout). */
+int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win, float* dst,
+                          int32_t Hout, int32_t Wout, void* stream);
+
+#define DVSOF_MAX_SCALES 8
+typedef struct {
+    int32_t n_scales;
+    int32_t n_pred;                          /* P */
+    int32_t H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
+    const float* flow[DVSOF_MAX_SCALES];     /* [dev] (P,2,H,W) contiguous */
+    const float* images[DVSOF_MAX_SCALES];   /* [dev] (D,H,W) pyramid level */
+    float* grad_flow[DVSOF_MAX_SCALES];      /* [dev] (P,2,H,W), backward only */
+} dvsof_loss_scales_t;
+
+/* forward: terms [dev] 3*n_scales fp32 laid out [smoothness[s]..., photometric[s]...,
+ * outborder[s]...]; n_bad [dev] int32 n_scales*P (out-of-border pixel count n_i per scale and
+ * prediction, kept for backward).  workspace: dvsof_loss_workspace_bytes(&scales). */
+size_t dvsof_loss_workspace_bytes(const dvsof_loss_scales_t* scales);
+int dvsof_warp_loss_forward(const dvsof_loss_scales_t* scales, const int32_t* match_idx,
+                            float* terms, int32_t* n_bad, void* workspace, void* stream);
+/* backward: grad_terms [dev] 3*n_scales fp32 (same layout as terms); writes grad_flow. */
+int dvsof_warp_loss_backward(const dvsof_loss_scales_t* scales, const int32_t* match_idx,
+                             const float* grad_terms, const int32_t* n_bad, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DVSOF_H_ */

@@ -1,0 +1,133 @@
+"""GPU parity: csrc/encode.cu through the C ABI vs the oracle / the reference's golden outputs.
+Bar: bit-exact (integer counts; fp32 timestamps are one IEEE sub + one IEEE div + max)."""
+import numpy as np
+import pytest
+import torch
+
+import dvs_of_training_framework_b200 as dv
+from oracle import encoder_oracle as eo
+from tests.helpers import np_events, synth_events
+
+pytestmark = pytest.mark.gpu
+
+
+def _cuda(ev):
+    return {k: torch.as_tensor(v).cuda() for k, v in ev.items()}
+
+
+@pytest.mark.parametrize('name', ['fixture', 'dense', 'ragged'])
+def test_matches_reference_golden(golden, name):
+    g = np.load(golden / f'encoder_{name}.npz')
+    ev = _cuda({k[3:]: g[k] for k in g.files if k.startswith('ev_')})
+    out = dv.compute_event_image(ev, torch.tensor(g['timestamps']).cuda(),
+                                 torch.tensor(g['sample_idx']).cuda(), (int(g['H']), int(g['W'])))
+    assert out.dtype == torch.float32 and out.is_cuda
+    assert np.array_equal(out.cpu().numpy(), g['out'])
+
+
+@pytest.mark.parametrize('B,H,W,n,contended', [
+    (1, 272, 352, 32768, False),      # cfg1 DAVIS 260x346 -> 272x352
+    (8, 256, 256, 131072, False),     # cfg2 MVSEC
+    (8, 256, 256, 131072, True),      # contended pixels
+    (3, 48, 80, 1001, False),         # n % 4 != 0 tail
+    (2, 480, 640, 200000, False),     # DSEC shape
+])
+def test_matches_oracle_synthetic(B, H, W, n, contended):
+    ev, ts, sidx = synth_events(7 + B, B, H, W, n, contended=contended)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_unaligned_views_take_scalar_path():
+    ev, ts, sidx = synth_events(3, 2, 64, 64, 5000)
+    want = eo.compute_event_image(np_events({k: v[1:] for k, v in ev.items()}), ts.numpy(),
+                                  sidx.numpy(), (64, 64))
+    cu = {k: v.cuda()[1:] for k, v in ev.items()}     # 8-byte / 4-byte offset views
+    got = dv.compute_event_image(cu, ts.cuda(), sidx.cuda(), (64, 64))
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_ragged_and_empty_samples():
+    ev, ts, sidx = synth_events(11, 6, 32, 48, 4000, ragged=True)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (32, 48))
+    got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 48))
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_empty_events_give_zeros():
+    # EV_FlowNet/net.py:115-116 (init_losses relies on it)
+    ev = {k: torch.zeros(0, dtype=torch.long).cuda() for k in ('x', 'y', 'polarity', 'sample_index')}
+    ev['timestamp'] = torch.zeros(0).cuda()
+    out = dv.compute_event_image(ev, torch.tensor([0., .04]).cuda(), torch.tensor([0, 0]).cuda(), (32, 32))
+    assert out.shape == (1, 4, 32, 32) and not out.any()
+
+
+def test_events_before_start_and_late_events():
+    # t < start -> negative t^ loses against 0; t > last -> t^ > 1 kept (dt uses the LAST event)
+    ev = {'x': [1, 1, 2, 2], 'y': [0, 0, 0, 0], 'polarity': [1, 1, -1, -1],
+          'sample_index': [0, 0, 0, 0], 'timestamp': np.array([0.5, 3.0, 0.2, 1.0], np.float32)}
+    ev = {k: np.asarray(v) for k, v in ev.items()}
+    ts = np.array([1.0, 2.0], np.float32)
+    want = eo.compute_event_image(ev, ts, np.array([0, 0]), (16, 16))
+    got = dv.compute_event_image(_cuda(ev), torch.tensor(ts).cuda(), torch.tensor([0, 0]).cuda(), (16, 16))
+    assert np.array_equal(got.cpu().numpy(), want)
+    assert want[0, 3, 0, 2] == 0 and want[0, 2, 0, 1] > 1
+
+
+def test_quantize_extends_to_multiple_of_16():
+    ev, ts, sidx = synth_events(5, 1, 260, 346, 2000)
+    out = dv.quantize(_cuda(ev), ts.cuda(), sidx.cuda(), (260, 346))
+    assert out.shape == (1, 4, 272, 352)
+    assert np.array_equal(out.cpu().numpy(),
+                          eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (272, 352)))
+
+
+@pytest.mark.parametrize('field,value', [('polarity', 0), ('sample_index', -1), ('x', 9999)])
+def test_invalid_input_raises_assertion(field, value):
+    ev, ts, sidx = synth_events(1, 2, 32, 32, 100)
+    ev[field][150] = value
+    with pytest.raises(AssertionError):
+        dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 32))
+
+
+def test_ungrouped_samples_raise():
+    ev, ts, sidx = synth_events(1, 2, 32, 32, 100)
+    ev['sample_index'] = ev['sample_index'].flip(0)
+    with pytest.raises(AssertionError):
+        dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 32))
+
+
+def test_compact_storage_form_equals_decoded_form():
+    B, H, W = 4, 64, 96
+    ev, ts, sidx = synth_events(21, B, H, W, 7001, ragged=True)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    eps = torch.bincount(ev['sample_index'], minlength=B)
+    got = dv.compute_event_image_compact(ev['x'].to(torch.int16).cuda(), ev['y'].to(torch.int16).cuda(),
+                                         ev['timestamp'].cuda(), (ev['polarity'] > 0).cuda(),
+                                         eps.cuda(), ts.cuda(), (H, W))
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_full_size_properties_cfg3_like():
+    """At sizes the oracle cannot finish quickly: size-independent checks (count conservation,
+    linearity over a split of the stream, max of maxima)."""
+    B, H, W, n = 4, 256, 256, 2_000_000
+    ev, ts, sidx = synth_events(33, B, H, W, n)
+    cu = _cuda(ev)
+    full = dv.compute_event_image(cu, ts.cuda(), sidx.cuda(), (H, W))
+    assert int(full[:, :2].sum()) == B * n
+    pos = int((ev['polarity'] > 0).sum())
+    assert int(full[:, 0].sum()) == pos
+    assert float(full[:, 2:].max()) <= 1.0 and float(full[:, 2:].min()) >= 0.0
+    # per-sample last event has t^ == 1 exactly (dt = t_last - start)
+    last = torch.cumsum(torch.bincount(ev['sample_index']), 0) - 1
+    for b in range(B):
+        i = int(last[b])
+        c = 2 + (0 if ev['polarity'][i] > 0 else 1)
+        assert float(full[b, c, int(ev['y'][i]), int(ev['x'][i])]) == 1.0
+    # counts are invariant under any permutation inside a sample
+    perm = torch.cat([torch.randperm(n) + b * n for b in range(B)])
+    sh = {k: v[perm].contiguous() for k, v in ev.items()}
+    cnt2 = dv.compute_event_image(_cuda(sh), ts.cuda(), sidx.cuda(), (H, W))[:, :2]
+    assert torch.equal(cnt2, full[:, :2])

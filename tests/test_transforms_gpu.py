@@ -1,0 +1,90 @@
+"""GPU parity (bit-exact) for count image, EventCrop, map_events / RandomRotation."""
+import numpy as np
+import pytest
+import torch
+
+import dvs_of_training_framework_b200 as dv
+from oracle import encoder_oracle as eo
+
+pytestmark = pytest.mark.gpu
+
+
+def test_golden_crop_count_rotation(golden):
+    g = np.load(golden / 'transforms.npz')
+    box = g['box'].tolist()
+    cropped = dv.EventCrop(box)(g['events'].copy())
+    assert cropped.dtype == np.float64 and np.array_equal(cropped, g['cropped'])
+    cnt = dv.get_count_image([cropped[:, 0], cropped[:, 1]], (box[2], box[3]))
+    assert cnt.dtype == np.uint64 and np.array_equal(cnt, g['count'])
+    e5 = np.hstack([g['events'], np.zeros((g['events'].shape[0], 1))])
+    rot = dv.RandomRotation(30, (260, 346))
+    for ang in ('0.0', '90.0', '17.5'):
+        rim, rev, a = rot(g['images'], e5.copy(), angle=float(ang))
+        assert a == float(ang)
+        assert np.array_equal(rim, g[f'rot_images_{ang}'])
+        assert rev.dtype == np.float32 and np.array_equal(rev, g[f'rot_events_{ang}'])
+
+
+def test_map_identity_exact():
+    # tests/dataset/test_dataset.py:42-73: angle 0 == identity, exact equality
+    H, W = 260, 346
+    rng = np.random.default_rng(1)
+    n = 20000
+    ev = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), np.sort(rng.random(n)),
+                   rng.choice([-1, 1], n), np.zeros(n)], 1).astype(np.float32)
+    idx = np.arange(H * W, dtype=np.uint64)
+    out = dv.transformation.map(ev, (H, W), idx, idx)
+    assert np.array_equal(out, ev)
+
+
+def test_map_fanout_order_and_drops():
+    H, W = 40, 50
+    rng = np.random.default_rng(2)
+    M = 6000
+    src = rng.integers(0, H * W // 2, M).astype(np.uint64)   # many duplicates, half unmapped
+    dst = rng.integers(0, H * W, M).astype(np.uint64)
+    n = 30000
+    ev = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), rng.random(n),
+                   rng.choice([-1, 1], n), rng.integers(0, 3, n)], 1).astype(np.float32)
+    want = eo.map_events(ev, (H, W), src, dst)
+    got = dv.transformation.map(ev, (H, W), src, dst)
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_map_argument_errors():
+    ev = np.zeros((4, 5), np.float32)
+    idx = np.arange(10, dtype=np.uint64)
+    with pytest.raises(ValueError):
+        dv.transformation.map(ev, (4, 4), idx, idx[:5])
+    with pytest.raises(TypeError):
+        dv.transformation.map(ev.astype(np.float64), (4, 4), idx, idx)
+    with pytest.raises(TypeError):
+        dv.transformation.map(ev, (4, 4), idx.astype(np.int64), idx)
+    assert dv.transformation.map(np.zeros((0, 5), np.float32), (4, 4), idx, idx).shape == (0, 5)
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.float64])
+def test_crop_random_boxes(dtype):
+    rng = np.random.default_rng(3)
+    n = 100003
+    ev = np.stack([rng.integers(0, 346, n), rng.integers(0, 260, n), np.sort(rng.random(n)),
+                   rng.choice([-1, 1], n)], 1).astype(dtype)
+    for box in ([0, 0, 260, 346], [2, 45, 256, 256], [100, 100, 1, 1], [0, 0, 0, 0]):
+        want = eo.event_crop(ev, box)
+        got = dv.EventCrop(box)(ev.copy())
+        assert got.dtype == dtype and np.array_equal(got, want)
+    assert dv.EventCrop([0, 0, 5, 5])(np.zeros((0, 4), dtype)).shape == (0, 4)
+
+
+def test_count_image_large_and_bad_pixel():
+    rng = np.random.default_rng(4)
+    n = 3_000_000
+    x, y = rng.integers(0, 640, n), rng.integers(0, 480, n)
+    want = eo.get_count_image([x, y], (480, 640))
+    got = dv.get_count_image([x, y], (480, 640))
+    assert np.array_equal(got, want) and int(got.sum()) == n
+    with pytest.raises(ValueError):
+        dv.get_count_image([np.array([640]), np.array([0])], (480, 640))
+    # CUDA tensors in -> CUDA tensor out
+    out = dv.get_count_image([torch.tensor(x).cuda(), torch.tensor(y).cuda()], (480, 640))
+    assert out.is_cuda and np.array_equal(out.cpu().numpy().astype(np.uint64), want)
