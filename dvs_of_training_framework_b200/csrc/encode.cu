@@ -267,26 +267,32 @@ extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_samples) {
     return round_up((size_t)(n_samples > 0 ? n_samples : 1) * sizeof(float2), 256);
 }
 
-extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
-                                        const int64_t* p, const int64_t* b, int64_t n,
-                                        const float* timestamps, int64_t B, int32_t H, int32_t W,
-                                        float* out, void* workspace, uint32_t* status,
-                                        void* stream_) {
-    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+extern "C" int dvsof_encode_prepare(const float* t, const int64_t* b, int64_t n,
+                                   const float* timestamps, int64_t B, int32_t H, int32_t W,
+                                   float* out, void* workspace, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, workspace)) return rc;
     cudaStream_t stream = (cudaStream_t)stream_;
     const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
     cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
     if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
     if (n == 0) return DVSOF_OK;                                    // net.py:115-116
-    if (!x || !y || !t || !p || !b || !timestamps)
-        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
-    float2* sd = reinterpret_cast<float2*>(workspace);
-    {
-        const int threads = 128;  // 4 samples per CTA
-        const int blocks = (int)((B * 32 + threads - 1) / threads);
-        sample_bounds_kernel<<<blocks, threads, 0, stream>>>(b, t, n, timestamps, (int)B, sd);
-        if (int rc = check_launch("sample_bounds_kernel")) return rc;
-    }
+    if (!t || !b || !timestamps) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    const int threads = 128;  // one warp per sample, 4 samples per CTA
+    const int blocks = (int)((B * 32 + threads - 1) / threads);
+    sample_bounds_kernel<<<blocks, threads, 0, stream>>>(b, t, n, timestamps, (int)B,
+                                                         reinterpret_cast<float2*>(workspace));
+    return check_launch("sample_bounds_kernel");
+}
+
+extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const float* t,
+                                   const int64_t* p, const int64_t* b, int64_t n, int64_t B,
+                                   int32_t H, int32_t W, float* out, const void* workspace,
+                                   uint32_t* status, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    if (n == 0) return DVSOF_OK;
+    if (!x || !y || !t || !p || !b) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const float2* sd = reinterpret_cast<const float2*>(workspace);
     const bool vec = aligned16(x) && aligned16(y) && aligned16(t) && aligned16(p) && aligned16(b);
     if (vec) {
         const int grid = encode_grid((n >> 2) + 1, 256, 8);
@@ -296,6 +302,16 @@ extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, cons
         encode_scalar_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
     }
     return check_launch("encode_kernel");
+}
+
+extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
+                                        const int64_t* p, const int64_t* b, int64_t n,
+                                        const float* timestamps, int64_t B, int32_t H, int32_t W,
+                                        float* out, void* workspace, uint32_t* status,
+                                        void* stream_) {
+    if (!status) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null status word");
+    if (int rc = dvsof_encode_prepare(t, b, n, timestamps, B, H, W, out, workspace, stream_)) return rc;
+    return dvsof_encode_scatter(x, y, t, p, b, n, B, H, W, out, workspace, status, stream_);
 }
 
 extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,

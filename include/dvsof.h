@@ -63,6 +63,17 @@ int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
                              uint32_t* status,  /* [dev] */
                              void* stream);
 
+/* The two stream-ordered phases of dvsof_encode_event_image, exported separately so a caller
+ * (bench.py) can put CUDA events around the scatter kernel alone:
+ *   prepare: zero `out`, per-sample (start, dt) into `workspace`;   scatter: the event stream. */
+int dvsof_encode_prepare(const float* t, const int64_t* sample_index, int64_t n_events,
+                         const float* timestamps, int64_t n_samples, int32_t H, int32_t W,
+                         float* out, void* workspace, void* stream);
+int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const float* t,
+                         const int64_t* polarity, const int64_t* sample_index, int64_t n_events,
+                         int64_t n_samples, int32_t H, int32_t W, float* out,
+                         const void* workspace, uint32_t* status, void* stream);
+
 /* Compact storage-form entry point: consumes the on-disk/encoded batch layout directly
  * (utils/dataset.py:286-289 encode_batch: x,y int16, polarity bool, timestamp fp32) plus
  * per-sample event counts instead of the int64 training form produced by decode_batch

@@ -134,3 +134,12 @@ def test_decode_events_matches_reference_layout():
     assert out['element_index'].tolist() == [0, 0, 0, 0, 0]
     assert out['sample_index'].tolist() == [0, 0, 1, 1, 1]
     assert out['x'].dtype == np.int64
+
+
+def test_torch_baseline_port_equals_numpy_oracle():
+    from oracle import encoder_oracle_torch as eot
+    from tests.helpers import np_events, synth_events
+    ev, ts, sidx = synth_events(17, 3, 40, 56, 5000, ragged=True)
+    a = eot.compute_event_image(ev, ts, sidx, (40, 56)).numpy()
+    b = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (40, 56))
+    assert np.array_equal(a, b)
