@@ -1,0 +1,405 @@
+#!/usr/bin/env python
+"""bench.py -- hot-path benchmark of dvs_of_training_framework_b200 on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    (N > 1: launched by torchrun, one rank per GPU)
+
+Headline metric (BASELINE.json): encoded ("voxelized") Mevents/s on configs[1] -- MVSEC-shaped
+256x256 events, batch 8, 131072 events/sample.  A step = one pass of the encoder
+over one synthetic batch, inputs resident in HBM, L2 flushed between steps.  The same JSON line
+also carries the warp-loss fwd+bwd samples/s (`warp_loss`), larger workloads (`workloads`), the
+end-to-end number through the public Python API from pinned host buffers (`e2e`), the roofline
+of the dominant kernel and the CPU baseline (oracle port, timed on this box's host cores).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+CFG = {
+    'cfg1': dict(B=1, H=260, W=346, n=32768, T=0.032),
+    'cfg2': dict(B=8, H=256, W=256, n=131072, T=0.032),
+    'cfg3': dict(B=32, H=256, W=256, n=5_000_000, T=0.032),
+    'cfg4': dict(B=16, H=480, W=640, n=1_048_576, T=0.1),
+}
+HEADLINE = 'cfg2'
+
+
+def peaks():
+    f = ROOT / 'MEASURED_PEAKS.json'
+    if f.exists():
+        return float(json.loads(f.read_text())['hbm_gbs']), 'measured (MEASURED_PEAKS.json hbm_gbs)'
+    return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
+
+
+def fast_events(seed, B, H, W, n, T, device):
+    """Synthetic events of SURVEY 8d generated on `device` (same distribution as
+    tests/helpers.synth_events; torch device RNG so cfg3's 160 M events take milliseconds)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    N = B * n
+    ev = {'x': torch.randint(0, W, (N,), generator=g, device=device),
+          'y': torch.randint(0, H, (N,), generator=g, device=device),
+          'polarity': (torch.rand(N, generator=g, device=device) < 0.7).long() * 2 - 1,
+          'sample_index': torch.arange(B, device=device).repeat_interleave(n)}
+    t = torch.rand(B, n, generator=g, device=device) * T
+    ev['timestamp'] = torch.sort(t, dim=1)[0].reshape(-1).float()
+    timestamps = torch.tensor([0, T] * B, dtype=torch.float32, device=device)
+    sample_idx = torch.arange(B, device=device).repeat_interleave(2)
+    return ev, timestamps, sample_idx
+
+
+def encoder_bytes(B, H, W, N):
+    return 36 * N + 8 * B + 16 * B * H * W
+
+
+def loss_bytes(B, H, W):
+    tot, prev = 0, H * W
+    for k in (3, 2, 1, 0):
+        p = (H // 2 ** k) * (W // 2 ** k)
+        tot += 40 * B * p + 8 * B * (prev + p)
+        prev = p
+    return tot
+
+
+class Clocks:
+    """nvidia-smi sampling during the timed region (B200_PROFILING.md clocks line)."""
+    Q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.proc, self.path = index, None, None
+
+    def __enter__(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix='.csv')
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', f'--id={self.index}', f'--query-gpu={self.Q}',
+                 '--format=csv,noheader,nounits', '-lms', '100'],
+                stdout=open(self.path, 'w'), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *a):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.proc.wait()
+
+    def summary(self):
+        out = {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': []}
+        try:
+            rows = [r.split(', ') for r in open(self.path).read().strip().splitlines() if r]
+            sm = sorted(int(r[0]) for r in rows)
+            out['sm_mhz'] = sm[len(sm) // 2]
+            out['sm_max_mhz'] = int(rows[0][1])
+            names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+            out['reasons'] = [n for i, n in enumerate(names) if any(r[2 + i].strip() == 'Active' for r in rows)]
+            out['samples'] = len(rows)
+        except Exception as e:  # nvidia-smi missing / no samples
+            out['error'] = str(e)[:80]
+        return out
+
+
+class L2Flusher:
+    def __init__(self, device):
+        self.buf = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+
+    def __call__(self):
+        self.buf.zero_()
+
+
+def time_steps(fn, K, W, flush, inner=None):
+    """W warm-ups, then K timed steps.  Each step has its own CUDA event pair on the launching
+    (current) stream, the L2 flush sits between pairs.  Returns per-step ms list (+ inner ms)."""
+    for _ in range(W):
+        flush()
+        fn()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for a, b in evs:
+        flush()
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) for a, b in evs]
+
+
+def bench_encoder(name, K, W, dev, seed_off=0):
+    import dvs_of_training_framework_b200 as dv
+    L = dv._lib
+    c = CFG[name]
+    B, H, Wd, n = c['B'], c['H'], c['W'], c['n']
+    He, We = dv.extend_size((H, Wd))
+    ev, ts, _ = fast_events(1234 + int(name[3:]) + seed_off, B, H, Wd, n, c['T'], dev)
+    N = B * n
+    out = torch.empty((B, 4, He, We), dtype=torch.float32, device=dev)
+    ws = torch.empty(L.load().dvsof_encode_workspace_bytes(B), dtype=torch.uint8, device=dev)
+    status = torch.zeros(1, dtype=torch.int32, device=dev)
+    sp = L.stream_ptr(dev)
+    flush = L2Flusher(dev)
+
+    def prepare():
+        L.call('dvsof_encode_prepare', L.ptr(ev['timestamp']), L.ptr(ev['sample_index']), N,
+               L.ptr(ts), B, He, We, L.ptr(out), L.ptr(ws), sp)
+
+    def scatter():
+        L.call('dvsof_encode_scatter', L.ptr(ev['x']), L.ptr(ev['y']), L.ptr(ev['timestamp']),
+               L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, B, He, We, L.ptr(out),
+               L.ptr(ws), L.ptr(status), sp)
+
+    for _ in range(W):
+        flush(); prepare(); scatter()
+    torch.cuda.synchronize()
+    E = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    marks = [(E(), E(), E()) for _ in range(K)]
+    for e0, k0, k1 in marks:
+        flush()
+        e0.record(); prepare(); k0.record(); scatter(); k1.record()
+    torch.cuda.synchronize()
+    assert int(status.item()) == 0, 'encoder flagged invalid input'
+    assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved'
+    step_ms = float(np.mean([e0.elapsed_time(k1) for e0, _, k1 in marks]))
+    kern_ms = float(np.mean([k0.elapsed_time(k1) for _, k0, k1 in marks]))
+    return dict(workload=name, events=N, step_ms=step_ms, kernel_ms=kern_ms,
+                bytes=encoder_bytes(B, He, We, N), launches_per_step=2)
+
+
+def bench_loss(name, K, W, dev):
+    import dvs_of_training_framework_b200 as dv
+    from tests.helpers import synth_loss_inputs
+    c = CFG[name]
+    B, H, Wd = c['B'], c['H'], c['W']
+    inp = synth_loss_inputs(1234 + int(name[3:]), B, H, Wd, 3.0, device=dev)
+    flows = [f.requires_grad_() for f in inp['flows']]
+    ev = dv.Losses(inp['shapes'], B, dev)
+    flush = L2Flusher(dev)
+    wts = (0.5, 1.0, 1.0)
+
+    def step():
+        for f in flows:
+            f.grad = None
+        terms = ev(flows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'],
+                   inp['sample_idx'])
+        loss = sum(w * sum(t) / len(t) for w, t in zip(wts, terms))   # utils/training.py:12-24
+        loss.backward()
+        return loss
+
+    ms = time_steps(step, K, W, flush)
+    step_ms = float(np.mean(ms))
+    return dict(workload=name, samples=B, step_ms=step_ms, bytes=loss_bytes(B, H, Wd),
+                launches_per_step=8)
+
+
+def bench_e2e(name, K, W, dev):
+    """Public API, host buffers: H2D of the event arrays from pinned memory, encode, D2H of the
+    event image into pinned memory -- all inside the timed region."""
+    import dvs_of_training_framework_b200 as dv
+    c = CFG[name]
+    B, H, Wd, n = c['B'], c['H'], c['W'], c['n']
+    ev, ts, sidx = fast_events(1234 + int(name[3:]), B, H, Wd, n, c['T'], dev)
+    host = {k: v.cpu().pin_memory() for k, v in ev.items()}
+    ts_h, sidx_h = ts.cpu().pin_memory(), sidx.cpu().pin_memory()
+    He, We = dv.extend_size((H, Wd))
+    out_h = torch.empty((B, 4, He, We), dtype=torch.float32).pin_memory()
+    h2d = sum(v.numel() * v.element_size() for v in host.values()) + ts_h.numel() * 4 + sidx_h.numel() * 8
+    d2h = out_h.numel() * 4
+
+    def step():
+        d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        img = dv.quantize(d, ts_h.to(dev, non_blocking=True), sidx_h.to(dev, non_blocking=True), (H, Wd))
+        out_h.copy_(img, non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(W):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        step()
+    dt = (time.perf_counter() - t0) / K
+    assert int(out_h[:, :2].sum(dtype=torch.float64)) == B * n
+    return dict(events=B * n, step_s=dt, h2d=h2d, d2h=d2h)
+
+
+def cpu_encoder_pass(name, threads=None):
+    """One pass of the oracle's torch-CPU port of the reference encoder on the workload."""
+    from oracle import encoder_oracle_torch as eot
+    import dvs_of_training_framework_b200 as dv
+    c = CFG[name]
+    if threads:
+        torch.set_num_threads(threads)
+    ev, ts, sidx = fast_events(1234 + int(name[3:]), c['B'], c['H'], c['W'], c['n'], c['T'], 'cpu')
+    size = dv.extend_size((c['H'], c['W']))
+    return (lambda: eot.compute_event_image(ev, ts, sidx, size)), c['B'] * c['n']
+
+
+def cpu_baseline(name, budget_s=12.0):
+    fn, N = cpu_encoder_pass(name)
+    fn()
+    t0 = time.perf_counter()
+    reps = 0
+    while time.perf_counter() - t0 < budget_s:
+        fn()
+        reps += 1
+    dt = (time.perf_counter() - t0) / reps
+    return {'value': N / dt / 1e6, 'unit': 'Mevents/s', 'cores': torch.get_num_threads(),
+            'kind': 'port', 'sample': f'{reps} full passes of {name} ({N} events) in {budget_s:.0f} s, '
+            'oracle/encoder_oracle_torch.py (the reference ATen op sequence, CPU)',
+            'host_cpus': len(os.sched_getaffinity(0))}
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    fn, N = cpu_encoder_pass(HEADLINE)
+    for _ in range(args.warmup):
+        fn()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        fn()
+    dt = (time.perf_counter() - t0) / args.steps
+    v = N / dt / 1e6
+    c = CFG[HEADLINE]
+    line = {'impl': 'reference', 'metric': 'encoded Mevents/s', 'value': v, 'unit': 'Mevents/s',
+            'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3,
+            'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+            'data': 'synthetic',
+            'config': {'workload': f'{HEADLINE}: MVSEC-shaped 256x256 events, batch {c["B"]}, '
+                                   f'{c["n"]} events/sample -> (B,4,256,256) event image'},
+            'cpu_baseline': {'value': v, 'unit': 'Mevents/s', 'cores': torch.get_num_threads(),
+                             'kind': 'port', 'sample': f'{args.steps} full passes of {HEADLINE}; the '
+                             'reference is Python+torch_scatter and cannot travel: oracle torch-CPU port'},
+            'e2e': {'value': v, 'unit': 'Mevents/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=50)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--quick', action='store_true', help='headline workload only (for ncu runs)')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'ours' and not args.quick else args.warmup
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    if args.impl == 'reference':
+        run_reference(args, rank)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py needs a CUDA device: the product path has no CPU fallback')
+    import dvs_of_training_framework_b200 as dv
+    dv._lib.load()
+    dv._lib.Status.mode = 'deferred'
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group('nccl', device_id=dev)
+    K, W = args.steps, args.warmup
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sync_all()
+    with Clocks(local) as clk:
+        head = bench_encoder(HEADLINE, K, W, dev, seed_off=rank)
+        sync_all()
+        loss = bench_loss(HEADLINE, K, W, dev)
+        sync_all()
+    clocks = clk.summary()
+    head_ms = max_over_ranks(head['step_ms'])
+    kern_ms = max_over_ranks(head['kernel_ms'])
+    loss_ms = max_over_ranks(loss['step_ms'])
+    e2e = bench_e2e(HEADLINE, max(3, K // 5), 3, dev)
+    e2e_s = max_over_ranks(e2e['step_s'])
+    sync_all()
+    extra = {}
+    if not args.quick:
+        for name in ('cfg3', 'cfg4'):
+            k2 = max(3, min(K, 10))
+            r = bench_encoder(name, k2, 3, dev, seed_off=rank)
+            r['step_ms'], r['kernel_ms'] = max_over_ranks(r['step_ms']), max_over_ranks(r['kernel_ms'])
+            extra[name] = r
+            torch.cuda.empty_cache()
+            ll = bench_loss(name, k2, 3, dev)
+            ll['step_ms'] = max_over_ranks(ll['step_ms'])
+            extra[name + '_loss'] = ll
+            torch.cuda.empty_cache()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak, peak_src = peaks()
+    c = CFG[HEADLINE]
+    achieved = head['bytes'] / (kern_ms * 1e-3) / 1e9
+    line = {
+        'metric': 'encoded Mevents/s', 'value': world * head['events'] / (head_ms * 1e-3) / 1e6,
+        'unit': 'Mevents/s', 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': head_ms,
+        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': f'{HEADLINE}: MVSEC-shaped 256x256 events, batch {c["B"]}/GPU, '
+                               f'{c["n"]} events/sample -> (B,4,256,256) event image; int64 SoA '
+                               'events (36 B/event) resident in HBM',
+                   'l2': '256 MiB memset between steps (outside the event pairs)',
+                   'validation': 'deferred (device status word, no host sync per call)',
+                   'parallelism': f'replicas x{world} (sharded by sample, no data-path collective)'},
+        'clocks': clocks,
+        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+                     'frac': achieved / peak, 'traffic': None, 'kernel': 'encode_vec4_kernel',
+                     'kernel_ms': kern_ms, 'algorithmic_bytes': head['bytes'], 'peak_source': peak_src},
+        'e2e': {'value': world * e2e['events'] / e2e_s / 1e6, 'unit': 'Mevents/s',
+                'h2d_bytes_per_step': e2e['h2d'], 'd2h_bytes_per_step': e2e['d2h'],
+                'api': 'dv.quantize(events, timestamps, sample_idx, imsize) from pinned host tensors'},
+        'gpu_launches': K * head['launches_per_step'],
+        'warp_loss': {'metric': 'warp-loss fwd+bwd samples/s', 'value': world * loss['samples'] / (loss_ms * 1e-3),
+                      'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
+                      'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
+                                   'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
+                                   'note': 'whole API step (8 kernels + autograd glue), not a single kernel'}},
+        'workloads': {},
+    }
+    for name, r in extra.items():
+        if name.endswith('_loss'):
+            line['workloads'][name] = {'samples_per_s': world * r['samples'] / (r['step_ms'] * 1e-3),
+                                       'ms_per_step': r['step_ms'],
+                                       'hbm_frac_step': r['bytes'] / (r['step_ms'] * 1e-3) / 1e9 / peak}
+        else:
+            line['workloads'][name] = {'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6,
+                                       'ms_per_step': r['step_ms'], 'kernel_ms': r['kernel_ms'],
+                                       'hbm_gbs_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9,
+                                       'hbm_frac_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9 / peak}
+    line['cpu_baseline'] = cpu_baseline(HEADLINE) if world == 1 and not args.quick else None
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()
