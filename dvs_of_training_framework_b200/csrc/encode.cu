@@ -8,6 +8,7 @@
 // RED.MAX.S32 on the bit pattern for the timestamps (signed-int order == float order for
 // t^ >= 0, and any negative t^ loses against the initial +0.0, which is exactly
 // scatter_max(..., out=zeros)).  Both are order independent => bit-exact vs the oracle.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace dvsof {
@@ -147,6 +148,107 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     if (flags) atomicOr(status, flags);
 }
 
+// ---------------------------------------------------------------------------------------
+// TMA-staged persistent variant: one elected thread streams whole event chunks
+// (x,y,p,b: CH*8 B each, t: CH*4 B) into a STAGES-deep shared-memory ring with bulk async copies
+// (cp.async.bulk -> UBLKCP, completion on an mbarrier, L2 evict-first policy); all warps consume
+// a landed chunk with conflict-free LDS and issue the two REDs per event.  The HBM stream is
+// decoupled from warp scheduling (no long-scoreboard stalls on the loads) and takes no LSU
+// tag-stage cycles away from the reductions, which are the SM-side bound of this kernel.
+// ---------------------------------------------------------------------------------------
+namespace tma {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar, uint64_t pol) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+}  // namespace tma
+
+template <int CH, int STAGES, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+encode_tma_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                  const float* __restrict__ t, const int64_t* __restrict__ p,
+                  const int64_t* __restrict__ b, int64_t n, int64_t n_chunks,
+                  const float2* __restrict__ sd, int n_samples, int H, int W,
+                  float* __restrict__ out, uint32_t* __restrict__ status) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int kStageBytes = CH * 36;
+    __shared__ uint64_t full[STAGES];
+    auto stage_ptr = [&](int s, int field) -> unsigned char* {   // field 0..3 = x,y,p,b ; 4 = t
+        return smem_raw + (size_t)s * kStageBytes + (size_t)field * CH * 8;
+    };
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) tma::mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    uint64_t pol = 0;
+    auto issue = [&](int s, int64_t chunk) {
+        const int64_t e0 = chunk * CH;
+        tma::mbar_expect_tx(&full[s], kStageBytes);
+        tma::bulk_g2s(stage_ptr(s, 0), x + e0, CH * 8, &full[s], pol);
+        tma::bulk_g2s(stage_ptr(s, 1), y + e0, CH * 8, &full[s], pol);
+        tma::bulk_g2s(stage_ptr(s, 2), p + e0, CH * 8, &full[s], pol);
+        tma::bulk_g2s(stage_ptr(s, 3), b + e0, CH * 8, &full[s], pol);
+        tma::bulk_g2s(stage_ptr(s, 4), t + e0, CH * 4, &full[s], pol);
+    };
+    if (threadIdx.x == 0) {
+        pol = tma::evict_first_policy();
+        for (int s = 0; s < STAGES; ++s) {
+            const int64_t c = (int64_t)blockIdx.x + (int64_t)s * gridDim.x;
+            if (c < n_chunks) issue(s, c);
+        }
+    }
+    unsigned flags = 0;
+    int s = 0;
+    unsigned parity = 0;
+    for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
+        tma::mbar_wait(&full[s], parity);
+        const int64_t* sx = reinterpret_cast<const int64_t*>(stage_ptr(s, 0));
+        const int64_t* sy = reinterpret_cast<const int64_t*>(stage_ptr(s, 1));
+        const int64_t* sp = reinterpret_cast<const int64_t*>(stage_ptr(s, 2));
+        const int64_t* sb = reinterpret_cast<const int64_t*>(stage_ptr(s, 3));
+        const float* st = reinterpret_cast<const float*>(stage_ptr(s, 4));
+#pragma unroll
+        for (int j = threadIdx.x; j < CH; j += THREADS) {
+            const int64_t bi = sb[j];
+            int64_t bn;
+            if (j + 1 < CH) bn = sb[j + 1];
+            else { const int64_t nxt = (c + 1) * CH; bn = nxt < n ? __ldg(b + nxt) : bi; }
+            if (bi > bn) flags |= DVSOF_ST_NOT_GROUPED;
+            flags |= scatter_event(sx[j], sy[j], st[j], sp[j], bi, sd, n_samples, H, W, out);
+        }
+        __syncthreads();   // every warp is done reading stage s
+        if (threadIdx.x == 0) {
+            const int64_t nc = c + (int64_t)STAGES * gridDim.x;
+            if (nc < n_chunks) issue(s, nc);
+        }
+        if (++s == STAGES) { s = 0; parity ^= 1; }
+    }
+    if (flags) atomicOr(status, flags);
+}
+
 // unaligned views (e.g. a DDP shard that starts at an odd event index): scalar loads
 __global__ void __launch_bounds__(256)
 encode_scalar_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
@@ -252,6 +354,37 @@ static int encode_grid(int64_t work_items, int threads, int ctas_per_sm) {
     return (int)blocks;
 }
 
+template <int CH, int STAGES, int THREADS, int CTAS_PER_SM>
+static int launch_tma_cfg(const int64_t* x, const int64_t* y, const float* t, const int64_t* p,
+                          const int64_t* b, int64_t n, const float2* sd, int B, int H, int W,
+                          float* out, uint32_t* status, cudaStream_t stream, int64_t* done) {
+    const int64_t n_chunks = n / CH;
+    *done = n_chunks * CH;
+    if (n_chunks == 0) return DVSOF_OK;
+    auto kern = encode_tma_kernel<CH, STAGES, THREADS>;
+    const int smem = CH * 36 * STAGES;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_tma smem attr: %s", cudaGetErrorString(e));
+        configured = true;
+    }
+    int64_t grid = (int64_t)kNumSMs * CTAS_PER_SM;
+    if (grid > n_chunks) grid = n_chunks;
+    kern<<<(unsigned)grid, THREADS, smem, stream>>>(x, y, t, p, b, n, n_chunks, sd, B, H, W, out, status);
+    return check_launch("encode_tma_kernel");
+}
+
+static int launch_tma(int variant, const int64_t* x, const int64_t* y, const float* t,
+                      const int64_t* p, const int64_t* b, int64_t n, const float2* sd, int B, int H,
+                      int W, float* out, uint32_t* status, cudaStream_t stream, int64_t* done) {
+    switch (variant) {
+        case 1: return launch_tma_cfg<1024, 3, 512, 2>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
+        case 2: return launch_tma_cfg<2048, 3, 1024, 1>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
+        default: return launch_tma_cfg<512, 4, 256, 3>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
+    }
+}
+
 static int check_encode_args(int64_t n, int64_t B, int H, int W, const void* out, const void* ws,
                              const void* status) {
     if (n < 0 || B <= 0 || H <= 0 || W <= 0)
@@ -294,7 +427,17 @@ extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const fl
     cudaStream_t stream = (cudaStream_t)stream_;
     const float2* sd = reinterpret_cast<const float2*>(workspace);
     const bool vec = aligned16(x) && aligned16(y) && aligned16(t) && aligned16(p) && aligned16(b);
-    if (vec) {
+    static const int variant = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : 0;
+    if (vec && variant >= 1 && variant <= 3) {
+        int64_t done = 0;
+        if (int rc = launch_tma(variant, x, y, t, p, b, n, sd, (int)B, H, W, out, status, stream, &done)) return rc;
+        if (done < n) {   // remainder (< one chunk): pointer offsets keep the 16 B alignment
+            const int64_t r = n - done;
+            const int grid = encode_grid((r >> 2) + 1, 256, 8);
+            encode_vec4_kernel<<<grid, 256, 0, stream>>>(x + done, y + done, t + done, p + done,
+                                                         b + done, r, sd, (int)B, H, W, out, status);
+        }
+    } else if (vec) {
         const int grid = encode_grid((n >> 2) + 1, 256, 8);
         encode_vec4_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
     } else {
