@@ -1,0 +1,216 @@
+"""GPU parity: csrc/loss.cu (fused multiscale warp loss, forward + analytic backward) through
+the C ABI vs (1) the reference's own outputs committed under tests/golden (values AND gradients
+of utils/loss.py run unmodified, see make_golden.py), (2) the reference's known-answer tests
+tests/loss/test_loss.py:20,41,63, (3) the torch-fp32 CPU oracle on seeded inputs.
+Bar (north_star): rtol 1e-5 / atol 1e-6 in fp32."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+import dvs_of_training_framework_b200 as dv
+from oracle import loss_oracle as lo
+from tests.helpers import synth_loss_inputs
+
+pytestmark = pytest.mark.gpu
+RTOL, ATOL = 1e-5, 1e-6
+WEIGHTS = (0.5, 1.0, 1.0)          # utils/options.py loss weights (smooth, photo, outborder)
+
+
+def _combined(terms):
+    return sum(w * sum(t) / len(t) for w, t in zip(WEIGHTS, terms))    # utils/training.py:12-24
+
+
+def _run_gpu(inp, flows_cpu, batch_size=None):
+    shapes = [tuple(f.shape[-2:]) for f in flows_cpu]
+    P = flows_cpu[0].shape[0]
+    flows = [f.detach().clone().cuda().requires_grad_() for f in flows_cpu]
+    ev = dv.Losses(shapes, batch_size or P, 'cuda')
+    terms = ev(flows, inp['flow_ts'].cuda(), inp['flow_sample_idx'].cuda(), inp['images'].cuda(),
+               inp['timestamps'].cuda(), inp['sample_idx'].cuda())
+    return flows, terms
+
+
+def _as_array(terms):
+    return np.array([[float(v.detach()) for v in t] for t in terms])
+
+
+@pytest.mark.parametrize('tag', ['a', 'b', 'c'])
+def test_matches_reference_golden_values_and_grads(golden, tag):
+    g = np.load(golden / f'loss_{tag}.npz')
+    inp = {k: torch.tensor(g[k]) for k in ('flow_ts', 'flow_sample_idx', 'timestamps', 'sample_idx')}
+    inp['images'] = torch.tensor(g['images']).float()
+    flows, terms = _run_gpu(inp, [torch.tensor(g[f'flow{k}']) for k in range(4)])
+    np.testing.assert_allclose(_as_array(terms), g['terms'], rtol=RTOL, atol=ATOL)
+    total = _combined(terms)
+    np.testing.assert_allclose(float(total), float(g['total']), rtol=RTOL, atol=ATOL)
+    total.backward()
+    for k, f in enumerate(flows):
+        np.testing.assert_allclose(f.grad.cpu().numpy(), g[f'grad{k}'], rtol=RTOL, atol=ATOL)
+
+
+def test_reference_kat_no_changes():
+    # tests/loss/test_loss.py:8-22: zero images, zero flow, 5x6 -> (0.002, 0.002, 0)
+    H, W = 5, 6
+    ts = torch.tensor([0, 0.4]).cuda()
+    ev = dv.Losses([(H, W)], 2, 'cuda')
+    out = ev([torch.zeros(1, 2, H, W).cuda()], ts.view(1, 2), torch.LongTensor([0]).cuda(),
+             torch.zeros(2, 1, H, W).cuda(), ts, torch.LongTensor([0, 0]).cuda())
+    for term, gt in zip(out, [0.002, 0.002, 0]):
+        assert len(term) == 1 and abs(float(term[0]) - gt) < 5e-6
+
+
+def test_reference_kat_fixture(golden):
+    # tests/loss/test_loss.py:25-65: goldens 0.622660; 0.002120 / 0.652659 / 0.007802 (+-5e-6)
+    H, W = 246, 340
+    f = np.load(golden / 'fixture_000001.npz')
+    images = torch.tensor(np.stack([f['image1'][:H, :W], f['image2'][:H, :W]])[:, None]).float().cuda()
+    ts = torch.tensor([0, float(f['stop']) - float(f['start'])], dtype=torch.float32).cuda()
+    sidx, fs = torch.LongTensor([0, 0]).cuda(), torch.LongTensor([0]).cuda()
+    ev = dv.Losses([(H, W)], 2, 'cuda')
+    out = ev([torch.zeros(1, 2, H, W).cuda()], ts.view(1, 2), fs, images, ts, sidx)
+    for term, gt in zip(out, [0.002, 0.622660, 0]):
+        assert abs(float(term[0]) - gt) < 5e-6
+    flow = torch.tensor(f['flow'][:H, :W]).permute(2, 0, 1)[None].contiguous().cuda()
+    out = ev([flow], ts.view(1, 2), fs, images, ts, sidx)
+    for term, gt in zip(out, [0.002120, 0.652659, 0.007802]):
+        assert abs(float(term[0]) - gt) < 5e-6
+    kat = np.load(golden / 'loss_kat.npz')
+    np.testing.assert_allclose([float(t[0]) for t in out], kat['pred'], rtol=RTOL, atol=ATOL)
+
+
+@pytest.mark.parametrize('B,H,W,sigma', [
+    (1, 260, 346, 3.0),       # cfg1 DAVIS
+    (8, 256, 256, 3.0),       # cfg2 MVSEC
+    (8, 256, 256, 64.0),      # stress: most pixels warp out of the image
+    (3, 72, 104, 3.0),        # ragged tiles (not multiples of 32), odd sizes at coarse scales
+    (2, 480, 640, 3.0),       # cfg4 DSEC shape, small batch so the CPU oracle stays quick
+])
+def test_matches_oracle_values_and_grads(B, H, W, sigma):
+    inp = synth_loss_inputs(100 + B + H, B, H, W, sigma)
+    flows, terms = _run_gpu(inp, inp['flows'])
+    oflows = [f.clone().requires_grad_() for f in inp['flows']]
+    oterms = lo.multiscale_loss(oflows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                inp['timestamps'], inp['sample_idx'])
+    np.testing.assert_allclose(_as_array(terms), _as_array(oterms), rtol=RTOL, atol=ATOL)
+    _combined(terms).backward()
+    lo.combined(oterms).backward()
+    for a, b in zip(flows, oflows):
+        np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.numpy(), rtol=RTOL, atol=ATOL)
+
+
+def test_per_term_gradients_with_unequal_weights():
+    """backward contracts with an arbitrary grad_terms vector (12 independent cotangents)."""
+    inp = synth_loss_inputs(7, 2, 64, 96, 6.0)
+    flows, terms = _run_gpu(inp, inp['flows'])
+    oflows = [f.clone().requires_grad_() for f in inp['flows']]
+    oterms = lo.multiscale_loss(oflows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                inp['timestamps'], inp['sample_idx'])
+    g = torch.Generator().manual_seed(3)
+    cot = torch.rand(3, 4, generator=g) + 0.1
+    sum(cot[k, s] * terms[k][s] for k in range(3) for s in range(4)).backward()
+    sum(cot[k, s] * oterms[k][s] for k in range(3) for s in range(4)).backward()
+    for a, b in zip(flows, oflows):
+        np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.numpy(), rtol=RTOL, atol=ATOL)
+
+
+def test_image_flow_matching_with_shuffled_images():
+    """utils/loss.py:182-206: predictions find their frames by (timestamp, sample) equality, in
+    any image order; distinct timestamps per sample."""
+    B, H, W = 4, 48, 64
+    inp = synth_loss_inputs(17, B, H, W, 2.0)
+    ts = inp['timestamps'].clone()
+    for b in range(B):
+        ts[2 * b:2 * b + 2] += 0.1 * b
+    inp['timestamps'], inp['flow_ts'] = ts, ts.view(-1, 2).clone()
+    perm = torch.tensor([5, 0, 3, 6, 1, 7, 2, 4])
+    shuf = dict(inp, images=inp['images'][perm], timestamps=ts[perm], sample_idx=inp['sample_idx'][perm])
+    _, t0 = _run_gpu(inp, inp['flows'])
+    _, t1 = _run_gpu(shuf, inp['flows'])
+    assert np.array_equal(_as_array(t0), _as_array(t1))
+    oterms = lo.multiscale_loss(inp['flows'], shuf['flow_ts'], shuf['flow_sample_idx'], shuf['images'],
+                                shuf['timestamps'], shuf['sample_idx'])
+    np.testing.assert_allclose(_as_array(t1), _as_array(oterms), rtol=RTOL, atol=ATOL)
+
+
+def test_missing_or_duplicate_frame_raises_assertion():
+    inp = synth_loss_inputs(1, 2, 32, 32, 1.0)
+    bad = dict(inp, flow_ts=inp['flow_ts'] + 1.0)                        # no frame has that time
+    with pytest.raises(AssertionError):
+        _run_gpu(bad, inp['flows'])
+    dup = dict(inp, sample_idx=torch.zeros_like(inp['sample_idx']))       # two frames match
+    with pytest.raises(AssertionError):
+        _run_gpu(dup, inp['flows'])
+
+
+def test_single_scale_loss_object_and_partial_batch():
+    # Loss(pred_shape, batch_size, device)(prev, next, flow), N <= batch_size (loss.py:122-124)
+    H, W, N = 40, 56, 3
+    g = torch.Generator().manual_seed(5)
+    prev = torch.randint(0, 256, (N, 1, H, W), generator=g).float()
+    nxt = torch.randint(0, 256, (N, 1, H, W), generator=g).float()
+    flow = (torch.randn(N, 2, H, W, generator=g) * 4).requires_grad_()
+    fl = flow.detach().clone().cuda().requires_grad_()
+    sm, ph, ob = dv.Loss((H, W), 8, 'cuda')(prev.cuda(), nxt.cuda(), fl)
+    osm, oph, oob = lo.scale_loss(prev, nxt, flow)
+    np.testing.assert_allclose([float(sm), float(ph), float(ob)],
+                               [float(osm), float(oph), float(oob)], rtol=RTOL, atol=ATOL)
+    (0.5 * sm + ph + ob).backward()
+    (0.5 * osm + oph + oob).backward()
+    np.testing.assert_allclose(fl.grad.cpu().numpy(), flow.grad.numpy(), rtol=RTOL, atol=ATOL)
+    with pytest.raises(AssertionError):
+        dv.Loss((H, W), 2, 'cuda')(prev.cuda(), nxt.cuda(), fl)           # N > batch_size
+    with pytest.raises(AssertionError):
+        dv.Loss((H + 1, W), 8, 'cuda')(prev.cuda(), nxt.cuda(), fl)       # wrong height
+
+
+@pytest.mark.parametrize('hin,win,hout,wout', [(260, 346, 32, 43), (32, 43, 65, 86), (7, 9, 7, 9),
+                                               (480, 640, 60, 80), (5, 6, 1, 1)])
+def test_interpolate_matches_aten(hin, win, hout, wout):
+    g = torch.Generator().manual_seed(hin)
+    img = torch.randint(0, 256, (3, 1, hin, win), generator=g).float()
+    want = F.interpolate(img, size=(hout, wout), mode='bilinear', align_corners=True)
+    got = dv.interpolate(img.cuda(), (hout, wout)).cpu()
+    np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=RTOL, atol=1e-4)
+
+
+def test_deterministic_bitwise():
+    inp = synth_loss_inputs(9, 4, 128, 160, 5.0)
+    f0, t0 = _run_gpu(inp, inp['flows'])
+    f1, t1 = _run_gpu(inp, inp['flows'])
+    assert np.array_equal(_as_array(t0), _as_array(t1))
+    _combined(t0).backward()
+    _combined(t1).backward()
+    for a, b in zip(f0, f1):
+        assert torch.equal(a.grad, b.grad)
+
+
+def test_full_size_properties_cfg4():
+    """BASELINE cfg4 size (480x640, batch 16) -- beyond a quick CPU oracle run: size-independent
+    properties.  (1) identical frames + constant flow: photometric == smoothness == eps^(2 alpha);
+    (2) permuting the batch permutes gradients and keeps every term (means over the batch);
+    (3) backward is linear in the cotangent."""
+    B, H, W = 16, 480, 640
+    inp = synth_loss_inputs(44, B, H, W, 3.0, device='cuda')
+    shapes = inp['shapes']
+    ev = dv.Losses(shapes, B, 'cuda')
+    args = (inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'], inp['sample_idx'])
+    c0 = (1e-3 ** 2) ** 0.45
+    same = inp['images'].clone()
+    same[1::2] = same[0::2]
+    zero = [torch.zeros(B, 2, h, w, device='cuda') for h, w in shapes]
+    sm, ph, ob = ev(zero, inp['flow_ts'], inp['flow_sample_idx'], same, inp['timestamps'], inp['sample_idx'])
+    np.testing.assert_allclose([float(v) for v in sm + ph], [c0] * 8, rtol=RTOL, atol=ATOL)
+    assert all(float(v) == 0 for v in ob)
+    flows = [f.requires_grad_() for f in inp['flows']]
+    terms = ev(flows, *args)
+    _combined(terms).backward()
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(1)).cuda()
+    pflows = [f.detach()[perm].contiguous().requires_grad_() for f in flows]
+    pterms = ev(pflows, inp['flow_ts'][perm], inp['flow_sample_idx'][perm], inp['images'],
+                inp['timestamps'], inp['sample_idx'])
+    np.testing.assert_allclose(_as_array(pterms), _as_array(terms), rtol=RTOL, atol=ATOL)
+    (3.0 * _combined(pterms)).backward()
+    for f, pf in zip(flows, pflows):
+        torch.testing.assert_close(pf.grad, 3.0 * f.grad[perm], rtol=RTOL, atol=ATOL)
+        assert torch.isfinite(f.grad).all()
