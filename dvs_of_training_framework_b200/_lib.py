@@ -26,6 +26,12 @@ class LossScales(C.Structure):
                 ('grad_flow', C.c_void_p * MAX_SCALES)]
 
 
+class LossFrames(C.Structure):
+    _fields_ = [('images', C.c_void_p), ('n_images', C.c_int32), ('H0', C.c_int32), ('W0', C.c_int32),
+                ('flow_ts', C.c_void_p), ('flow_sample_idx', C.c_void_p),
+                ('timestamps', C.c_void_p), ('sample_idx', C.c_void_p)]
+
+
 _SIGNATURES = {
     'dvsof_last_error': (C.c_char_p, []),
     'dvsof_version': (C.c_int, []),
@@ -58,6 +64,8 @@ _SIGNATURES = {
     'dvsof_loss_workspace_bytes': (C.c_size_t, [C.POINTER(LossScales)]),
     'dvsof_warp_loss_forward': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_void_p, C.c_void_p]),
+    'dvsof_multiscale_loss_forward': (C.c_int, [C.POINTER(LossScales), C.POINTER(LossFrames)]
+                                      + [C.c_void_p] * 6),
     'dvsof_warp_loss_backward': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]),
 }

@@ -22,6 +22,27 @@ inline int check_launch(const char* what) {
     return DVSOF_OK;
 }
 
+// Launch through cudaLaunchKernelEx; `pdl` = programmatic dependent launch: the kernel may start
+// while its predecessor on the stream still runs and must call griddepcontrol.wait before it
+// touches anything the predecessor writes.
+template <typename... KArgs, typename... Args>
+inline int launch_kernel(const char* what, void (*kern)(KArgs...), int grid, int block, size_t smem,
+                         cudaStream_t stream, bool pdl, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3((unsigned)block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "%s: %s", what, cudaGetErrorString(e));
+    return DVSOF_OK;
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -36,6 +57,14 @@ __device__ __forceinline__ int warp_sum(int v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
+
+// programmatic dependent launch (PDL): release the next kernel on the stream early / block until
+// every kernel this one depends on has completed and its writes are visible.  Both are no-ops
+// when the launch did not carry the PDL attribute (see launch_kernel above).
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // streaming (evict-first) loads for data touched exactly once
 template <typename T>

@@ -14,41 +14,65 @@
 namespace dvsof {
 
 // ---------------------------------------------------------------------------------------
-// per-sample (start, dt): one warp per sample, 32-ary upper-bound search in sample_index
+// prepare: zero the event image AND find per-sample (start, dt) in ONE launch.
+// CTA s (mod grid) runs a 256-ary upper-bound search in sample_index for sample s (3 dependent
+// DRAM round trips at 1 M events, 4 at 160 M -- the old warp-wide version needed 2 x 4..6), the
+// rest of the grid streams zeros with 16 B stores meanwhile.  Dependent kernels are released
+// right away (programmatic dependent launch) and block in griddepcontrol.wait before they touch
+// `out` / `sd`, so their own event loads overlap this kernel.
 // ---------------------------------------------------------------------------------------
-template <typename GetKey>
-__device__ __forceinline__ int64_t warp_upper_bound(GetKey key_at, int64_t n, int64_t s, int lane) {
-    // first index i in [0,n) with key(i) > s (n if none).  All 32 lanes cooperate.
+
+constexpr int kPrepThreads = 256;
+
+// first index i in [0,n) with b[i] > s (n if none); all kPrepThreads threads of the CTA cooperate
+__device__ __forceinline__ int64_t cta_upper_bound(const int64_t* __restrict__ b, int64_t n,
+                                                   int64_t s, int* warp_first) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     int64_t lo = 0, hi = n;
     while (lo < hi) {
-        const int64_t step = (hi - lo + 31) / 32;
-        const int64_t pos = lo + (int64_t)(lane + 1) * step - 1;
-        const bool gt = (pos < hi) ? (key_at(pos) > s) : true;
+        const int64_t step = (hi - lo + kPrepThreads - 1) / kPrepThreads;
+        const int64_t pos = lo + (int64_t)(tid + 1) * step - 1;
+        const bool gt = (pos < hi) ? (__ldg(b + pos) > s) : true;
         const unsigned m = __ballot_sync(0xffffffffu, gt);
-        if (m == 0) { lo = hi; break; }
-        const int first = __ffs(m) - 1;
-        const int64_t seg_end = lo + (int64_t)(first + 1) * step - 1;
+        if (lane == 0) warp_first[warp] = m ? warp * 32 + (__ffs(m) - 1) : kPrepThreads;
+        __syncthreads();
+        int first = kPrepThreads;
+#pragma unroll
+        for (int w = 0; w < kPrepThreads / 32; ++w) first = min(first, warp_first[w]);
+        __syncthreads();
+        const int64_t cand = lo + (int64_t)(first + 1) * step - 1;   // first probe that is > s
         lo = lo + (int64_t)first * step;
-        hi = seg_end < hi ? seg_end : hi;
+        hi = cand < hi ? cand : hi;
     }
     return lo;
 }
 
-__global__ void sample_bounds_kernel(const int64_t* __restrict__ b, const float* __restrict__ t,
-                                     int64_t n, const float* __restrict__ timestamps,
-                                     int n_samples, float2* __restrict__ sd) {
-    const int lane = threadIdx.x & 31;
-    const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (s >= n_samples) return;
-    auto key = [&](int64_t i) { return b[i]; };
-    const int64_t end = warp_upper_bound(key, n, (int64_t)s, lane);
-    const int64_t begin = (s == 0) ? 0 : warp_upper_bound(key, n, (int64_t)s - 1, lane);
-    if (lane == 0) {
-        const float start = timestamps[2 * s];
-        float dt = 0.f;
-        if (end > begin) dt = __fsub_rn(t[end - 1], start);   // net.py:136-137
-        dt = fmaxf(dt, 1e-9f);                               // net.py:138
-        sd[s] = make_float2(start, dt);
+__global__ void __launch_bounds__(kPrepThreads)
+encode_prepare_kernel(const int64_t* __restrict__ b, const float* __restrict__ t, int64_t n,
+                      const float* __restrict__ timestamps, int n_samples,
+                      float2* __restrict__ sd, float* __restrict__ out, size_t n_floats) {
+    __shared__ int warp_first[kPrepThreads / 32];
+    pdl_launch_dependents();
+    if (n > 0) {
+        for (int s = blockIdx.x; s < n_samples; s += gridDim.x) {
+            const int64_t end = cta_upper_bound(b, n, (int64_t)s, warp_first);
+            if (threadIdx.x == 0) {
+                const float start = timestamps[2 * s];
+                float dt = 0.f;
+                if (end > 0 && b[end - 1] == (int64_t)s) dt = __fsub_rn(t[end - 1], start);  // net.py:136-137
+                sd[s] = make_float2(start, fmaxf(dt, 1e-9f));                                  // net.py:138
+            }
+        }
+    }
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    if ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
+        float4* o4 = reinterpret_cast<float4*>(out);
+        const size_t n4 = n_floats >> 2;
+        for (size_t i = tid; i < n4; i += stride) o4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (size_t i = (n4 << 2) + tid; i < n_floats; i += stride) out[i] = 0.f;
+    } else {
+        for (size_t i = tid; i < n_floats; i += stride) out[i] = 0.f;
     }
 }
 
@@ -78,23 +102,26 @@ __device__ __forceinline__ unsigned scatter_event(int64_t xi, int64_t yi, float 
                                                   int64_t bi, const float2* __restrict__ sd,
                                                   int n_samples, int H, int W,
                                                   float* __restrict__ out) {
+    // validate in 64 bit, then continue in 32 bit (fewer live registers per event in flight)
     if (pi != 1 && pi != -1) return DVSOF_ST_BAD_POLARITY;
     if ((uint64_t)bi >= (uint64_t)n_samples) return DVSOF_ST_BAD_SAMPLE;
     if ((uint64_t)xi >= (uint64_t)W || (uint64_t)yi >= (uint64_t)H) return DVSOF_ST_BAD_PIXEL;
-    const float2 s = __ldg(sd + bi);
+    const unsigned x32 = (unsigned)xi, y32 = (unsigned)yi, b32 = (unsigned)bi;
+    const unsigned c = (unsigned)(1 - (int)pi) >> 1;                 // net.py:142
+    const float2 s = __ldg(sd + b32);
     const float tn = __fdiv_rn(__fsub_rn(ti, s.x), s.y);           // net.py:141
-    const int c = (int)((1 - pi) >> 1);                             // net.py:142
     const size_t plane = (size_t)H * W;
-    const size_t cell = ((size_t)bi * 4 + c) * plane + (size_t)yi * W + xi;  // net.py:144
-    atomicAdd(out + cell, 1.0f);                                    // scatter_sum, net.py:147
-    atomicMax(reinterpret_cast<int*>(out + cell + 2 * plane), __float_as_int(tn));  // net.py:149
+    float* cell = out + (size_t)(b32 * 4u + c) * plane + (y32 * (unsigned)W + x32);  // net.py:144
+    atomicAdd(cell, 1.0f);                                          // scatter_sum, net.py:147
+    atomicMax(reinterpret_cast<int*>(cell + 2 * plane), __float_as_int(tn));  // scatter_max, net.py:149
     return 0u;
 }
 
 // ---------------------------------------------------------------------------------------
 // int64 structure-of-arrays stream, 4 events per thread per iteration (16 B loads)
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
 encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
                    const float* __restrict__ t, const int64_t* __restrict__ p,
                    const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
@@ -104,6 +131,7 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     const int64_t nvec = n >> 2;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     unsigned flags = 0;
+    bool waited = false;
     // warp-uniform trip count so the shuffle below is always convergent
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < nvec;
          base += stride) {
@@ -126,6 +154,7 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
         }
         // grouping check (net.py:131-134): sample_index must be non-decreasing
         long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
+        if (!waited) { pdl_wait(); waited = true; }   // `out` zeroed + `sd` ready from here on
         if (valid) {
             const int64_t nxt = 4 * (i + 1);
             if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : bb.y;
@@ -137,6 +166,7 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             flags |= scatter_event(xb.y, yb.y, tt.w, pb.y, bb.y, sd, n_samples, H, W, out);
         }
     }
+    if (!waited) pdl_wait();
     // tail (n % 4 events): first threads of block 0
     if (blockIdx.x == 0) {
         const int64_t i = (nvec << 2) + threadIdx.x;
@@ -144,6 +174,51 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             if (i + 1 < n && b[i] > b[i + 1]) flags |= DVSOF_ST_NOT_GROUPED;
             flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
         }
+    }
+    if (flags) atomicOr(status, flags);
+}
+
+// 2 events per thread per iteration: half the live registers of the vec4 kernel -> twice the
+// resident warps to cover DRAM latency (the REDs are fire-and-forget, only the loads stall).
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
+encode_vec2_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                   const float* __restrict__ t, const int64_t* __restrict__ p,
+                   const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
+                   int n_samples, int H, int W, float* __restrict__ out,
+                   uint32_t* __restrict__ status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nvec = n >> 1;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned flags = 0;
+    bool waited = false;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < nvec;
+         base += stride) {
+        const int64_t i = base + lane;
+        const bool valid = i < nvec;
+        longlong2 xa, ya, pa, ba = make_longlong2(0, 0);
+        float2 tt;
+        if (valid) {
+            xa = __ldcs(reinterpret_cast<const longlong2*>(x) + i);
+            ya = __ldcs(reinterpret_cast<const longlong2*>(y) + i);
+            pa = __ldcs(reinterpret_cast<const longlong2*>(p) + i);
+            ba = __ldcs(reinterpret_cast<const longlong2*>(b) + i);
+            tt = __ldcs(reinterpret_cast<const float2*>(t) + i);
+        }
+        long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
+        if (!waited) { pdl_wait(); waited = true; }
+        if (valid) {
+            const int64_t nxt = 2 * (i + 1);
+            if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : ba.y;
+            if (ba.x > ba.y || ba.y > bnext) flags |= DVSOF_ST_NOT_GROUPED;
+            flags |= scatter_event(xa.x, ya.x, tt.x, pa.x, ba.x, sd, n_samples, H, W, out);
+            flags |= scatter_event(xa.y, ya.y, tt.y, pa.y, ba.y, sd, n_samples, H, W, out);
+        }
+    }
+    if (!waited) pdl_wait();
+    if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
+        const int64_t i = n - 1;
+        flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
     }
     if (flags) atomicOr(status, flags);
 }
@@ -223,6 +298,7 @@ encode_tma_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     unsigned flags = 0;
     int s = 0;
     unsigned parity = 0;
+    pdl_wait();   // the first STAGES chunks are already in flight
     for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
         tma::mbar_wait(&full[s], parity);
         const int64_t* sx = reinterpret_cast<const int64_t*>(stage_ptr(s, 0));
@@ -258,6 +334,7 @@ encode_scalar_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ 
                      uint32_t* __restrict__ status) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     unsigned flags = 0;
+    pdl_wait();
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const int64_t bi = __ldcs(b + i);
         if (i + 1 < n && bi > b[i + 1]) flags |= DVSOF_ST_NOT_GROUPED;
@@ -354,11 +431,21 @@ static int encode_grid(int64_t work_items, int threads, int ctas_per_sm) {
     return (int)blocks;
 }
 
+struct EncodeArgs {
+    const int64_t *x, *y; const float* t; const int64_t *p, *b; int64_t n;
+    const float2* sd; int B, H, W; float* out; uint32_t* status;
+};
+
+template <typename K>
+static int launch_stream(K kern, const char* name, int grid, int threads, size_t smem,
+                         cudaStream_t stream, bool pdl, const EncodeArgs& a) {
+    return launch_kernel(name, kern, grid, threads, smem, stream, pdl, a.x, a.y, a.t, a.p, a.b, a.n,
+                         a.sd, a.B, a.H, a.W, a.out, a.status);
+}
+
 template <int CH, int STAGES, int THREADS, int CTAS_PER_SM>
-static int launch_tma_cfg(const int64_t* x, const int64_t* y, const float* t, const int64_t* p,
-                          const int64_t* b, int64_t n, const float2* sd, int B, int H, int W,
-                          float* out, uint32_t* status, cudaStream_t stream, int64_t* done) {
-    const int64_t n_chunks = n / CH;
+static int launch_tma_cfg(const EncodeArgs& a, cudaStream_t stream, bool pdl, int64_t* done) {
+    const int64_t n_chunks = a.n / CH;
     *done = n_chunks * CH;
     if (n_chunks == 0) return DVSOF_OK;
     auto kern = encode_tma_kernel<CH, STAGES, THREADS>;
@@ -371,18 +458,8 @@ static int launch_tma_cfg(const int64_t* x, const int64_t* y, const float* t, co
     }
     int64_t grid = (int64_t)kNumSMs * CTAS_PER_SM;
     if (grid > n_chunks) grid = n_chunks;
-    kern<<<(unsigned)grid, THREADS, smem, stream>>>(x, y, t, p, b, n, n_chunks, sd, B, H, W, out, status);
-    return check_launch("encode_tma_kernel");
-}
-
-static int launch_tma(int variant, const int64_t* x, const int64_t* y, const float* t,
-                      const int64_t* p, const int64_t* b, int64_t n, const float2* sd, int B, int H,
-                      int W, float* out, uint32_t* status, cudaStream_t stream, int64_t* done) {
-    switch (variant) {
-        case 1: return launch_tma_cfg<1024, 3, 512, 2>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
-        case 2: return launch_tma_cfg<2048, 3, 1024, 1>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
-        default: return launch_tma_cfg<512, 4, 256, 3>(x, y, t, p, b, n, sd, B, H, W, out, status, stream, done);
-    }
+    return launch_kernel("encode_tma_kernel", kern, (int)grid, THREADS, smem, stream, pdl, a.x, a.y,
+                         a.t, a.p, a.b, a.n, n_chunks, a.sd, a.B, a.H, a.W, a.out, a.status);
 }
 
 static int check_encode_args(int64_t n, int64_t B, int H, int W, const void* out, const void* ws,
@@ -400,21 +477,64 @@ extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_samples) {
     return round_up((size_t)(n_samples > 0 ? n_samples : 1) * sizeof(float2), 256);
 }
 
+// variant of the streaming kernel: DVSOF_ENCODE_VARIANT (experiments, scripts/exp_encoder.py);
+// unset = the default chosen from the measurements recorded in DESIGN.md section 4
+static int encode_variant() {
+    static const int v = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : -1;
+    return v;
+}
+
 extern "C" int dvsof_encode_prepare(const float* t, const int64_t* b, int64_t n,
                                    const float* timestamps, int64_t B, int32_t H, int32_t W,
                                    float* out, void* workspace, void* stream_) {
     if (int rc = check_encode_args(n, B, H, W, out, workspace, workspace)) return rc;
-    cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
-    cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
-    if (n == 0) return DVSOF_OK;                                    // net.py:115-116
-    if (!t || !b || !timestamps) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
-    const int threads = 128;  // one warp per sample, 4 samples per CTA
-    const int blocks = (int)((B * 32 + threads - 1) / threads);
-    sample_bounds_kernel<<<blocks, threads, 0, stream>>>(b, t, n, timestamps, (int)B,
-                                                         reinterpret_cast<float2*>(workspace));
-    return check_launch("sample_bounds_kernel");
+    if (n > 0 && (!t || !b || !timestamps))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    const size_t n_floats = (size_t)B * 4 * H * W;
+    // enough CTAs to stream the zeros at full rate, at least one per sample for the search
+    int64_t grid = (int64_t)((n_floats / 4 + kPrepThreads * 8 - 1) / (kPrepThreads * 8));
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    if (grid < B) grid = B < kNumSMs * 8 ? B : kNumSMs * 8;
+    if (grid < 1) grid = 1;
+    return launch_kernel("encode_prepare_kernel", encode_prepare_kernel, (int)grid, kPrepThreads, 0,
+                         (cudaStream_t)stream_, false, b, t, n, timestamps, (int)B,
+                         reinterpret_cast<float2*>(workspace), out, n_floats);   // n == 0: net.py:115-116
+}
+
+static int encode_scatter_impl(const EncodeArgs& a, cudaStream_t stream, bool pdl) {
+    const bool vec = aligned16(a.x) && aligned16(a.y) && aligned16(a.t) && aligned16(a.p) && aligned16(a.b);
+    const int variant = encode_variant();
+    if (!vec)
+        return launch_stream(encode_scalar_kernel, "encode_scalar_kernel", encode_grid(a.n, 256, 8),
+                             256, 0, stream, pdl, a);
+    if (variant >= 1 && variant <= 3) {
+        int64_t done = 0;
+        int rc;
+        if (variant == 1) rc = launch_tma_cfg<1024, 3, 512, 2>(a, stream, pdl, &done);
+        else if (variant == 2) rc = launch_tma_cfg<2048, 3, 1024, 1>(a, stream, pdl, &done);
+        else rc = launch_tma_cfg<512, 4, 256, 3>(a, stream, pdl, &done);
+        if (rc) return rc;
+        if (done < a.n) {   // remainder (< one chunk): pointer offsets keep the 16 B alignment
+            EncodeArgs r = a;
+            r.x += done; r.y += done; r.t += done; r.p += done; r.b += done; r.n = a.n - done;
+            return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel",
+                                 encode_grid((r.n >> 2) + 1, 256, 8), 256, 0, stream,
+                                 pdl && done == 0, r);
+        }
+        return DVSOF_OK;
+    }
+    switch (variant) {
+        case 4: return launch_stream(encode_vec2_kernel<6>, "encode_vec2_kernel<6>",
+                                     encode_grid((a.n >> 1) + 1, 256, 6), 256, 0, stream, pdl, a);
+        case 5: return launch_stream(encode_vec2_kernel<8>, "encode_vec2_kernel<8>",
+                                     encode_grid((a.n >> 1) + 1, 256, 8), 256, 0, stream, pdl, a);
+        case 6: return launch_stream(encode_vec4_kernel<4>, "encode_vec4_kernel<4>",
+                                     encode_grid((a.n >> 2) + 1, 256, 4), 256, 0, stream, pdl, a);
+        case 7: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                                     encode_grid((a.n >> 2) + 1, 256, 16), 256, 0, stream, pdl, a);
+        default: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                                      encode_grid((a.n >> 2) + 1, 256, 8), 256, 0, stream, pdl, a);
+    }
 }
 
 extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const float* t,
@@ -424,27 +544,8 @@ extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const fl
     if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
     if (n == 0) return DVSOF_OK;
     if (!x || !y || !t || !p || !b) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
-    cudaStream_t stream = (cudaStream_t)stream_;
-    const float2* sd = reinterpret_cast<const float2*>(workspace);
-    const bool vec = aligned16(x) && aligned16(y) && aligned16(t) && aligned16(p) && aligned16(b);
-    static const int variant = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : 0;
-    if (vec && variant >= 1 && variant <= 3) {
-        int64_t done = 0;
-        if (int rc = launch_tma(variant, x, y, t, p, b, n, sd, (int)B, H, W, out, status, stream, &done)) return rc;
-        if (done < n) {   // remainder (< one chunk): pointer offsets keep the 16 B alignment
-            const int64_t r = n - done;
-            const int grid = encode_grid((r >> 2) + 1, 256, 8);
-            encode_vec4_kernel<<<grid, 256, 0, stream>>>(x + done, y + done, t + done, p + done,
-                                                         b + done, r, sd, (int)B, H, W, out, status);
-        }
-    } else if (vec) {
-        const int grid = encode_grid((n >> 2) + 1, 256, 8);
-        encode_vec4_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
-    } else {
-        const int grid = encode_grid(n, 256, 8);
-        encode_scalar_kernel<<<grid, 256, 0, stream>>>(x, y, t, p, b, n, sd, (int)B, H, W, out, status);
-    }
-    return check_launch("encode_kernel");
+    const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(workspace), (int)B, H, W, out, status};
+    return encode_scatter_impl(a, (cudaStream_t)stream_, false);
 }
 
 extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
@@ -453,8 +554,13 @@ extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, cons
                                         float* out, void* workspace, uint32_t* status,
                                         void* stream_) {
     if (!status) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null status word");
+    if (n > 0 && (!x || !y || !p)) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
     if (int rc = dvsof_encode_prepare(t, b, n, timestamps, B, H, W, out, workspace, stream_)) return rc;
-    return dvsof_encode_scatter(x, y, t, p, b, n, B, H, W, out, workspace, status, stream_);
+    if (n == 0) return DVSOF_OK;
+    const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(workspace), (int)B, H, W, out, status};
+    static const bool no_pdl = getenv("DVSOF_NO_PDL") != nullptr;
+    // scatter is released while prepare still runs; it blocks in griddepcontrol.wait
+    return encode_scatter_impl(a, (cudaStream_t)stream_, !no_pdl);
 }
 
 extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,

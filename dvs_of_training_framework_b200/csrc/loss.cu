@@ -98,8 +98,10 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
                                         const float* __restrict__ timestamps,
                                         const int64_t* __restrict__ sample_idx, int D,
                                         int32_t* __restrict__ match_idx,
-                                        uint32_t* __restrict__ status) {
+                                        uint32_t* __restrict__ status, unsigned* ticket) {
+    pdl_launch_dependents();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;   // i = k * P + p
+    if (i == 0 && ticket) *ticket = 0u;                    // arms the forward kernel's finalize
     if (i >= 2 * P) return;
     const int k = i / P, p = i - k * P;
     const float want = flow_ts[2 * p + k];
@@ -115,6 +117,8 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
 __global__ void __launch_bounds__(256)
 resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
                        int Hout, int Wout, int64_t total) {
+    pdl_launch_dependents();
+    pdl_wait();                                  // src may be the previous level of the chain
     const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
     const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -139,11 +143,19 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
 
 // ------------------------------ forward ------------------------------------------------
 // record: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
+__device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
+                               int32_t* n_bad, double (*wacc)[6]);
+
 __global__ void __launch_bounds__(kLossThreads)
 warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
-                     float* __restrict__ partials) {
+                     float* partials, unsigned* ticket, float* __restrict__ terms,
+                     int32_t* __restrict__ n_bad) {
     __shared__ float F[2][kTile + 1][kTile + 2];
     __shared__ float red[kLossThreads / 32][kRec];
+    __shared__ double wacc[kLossThreads / 32][6];
+    __shared__ bool is_last;
+    pdl_launch_dependents();
+    pdl_wait();                       // pyramid levels + match_idx come from the preceding kernels
     const TileCoord tc = decode_cta(tab);
     const int H = tab.H[tc.s], W = tab.W[tc.s], P = tab.n_pred;
     const size_t plane = (size_t)H * W;
@@ -192,51 +204,68 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     if (threadIdx.x < 7) {
         float t = 0.f;
         for (int w = 0; w < kLossThreads / 32; ++w) t += red[w][threadIdx.x];
-        partials[(size_t)blockIdx.x * kRec + threadIdx.x] = t;
+        __stcg(partials + (size_t)blockIdx.x * kRec + threadIdx.x, t);
     }
-}
-
-// one CTA per scale, one warp per prediction: fixed-order fp64 sums of the tile records
-__global__ void __launch_bounds__(1024)
-warp_loss_finalize_kernel(const __grid_constant__ ScaleTable tab, const float* __restrict__ partials,
-                          float* __restrict__ terms, int32_t* __restrict__ n_bad) {
-    __shared__ double wacc[32][6];
-    const int s = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int P = tab.n_pred, H = tab.H[s], W = tab.W[s];
-    const int per = tab.tiles_x[s] * tab.tiles_y[s];
-    double tot[6] = {0, 0, 0, 0, 0, 0};   // photo, h, v, d_a, d_b, outborder
-    for (int n = warp; n < P; n += 32) {
-        double a[7] = {0, 0, 0, 0, 0, 0, 0};
-        const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
-        for (int t = lane; t < per; t += 32)
-#pragma unroll
-            for (int k = 0; k < 7; ++k) a[k] += (double)rec[(size_t)t * kRec + k];
-#pragma unroll
-        for (int k = 0; k < 7; ++k)
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-        for (int k = 0; k < 5; ++k) tot[k] += a[k];
-        const double nb = a[6];
-        if (nb > 0) tot[5] += a[5] / (2.0 * nb * (double)P);               // loss.py:99-113
-        if (lane == 0) n_bad[s * P + n] = (int32_t)nb;
-    }
-    if (lane == 0)
-        for (int k = 0; k < 6; ++k) wacc[warp][k] = tot[k];
+    // the last CTA to arrive reduces all records in a FIXED order (deterministic, fp64)
+    __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) {
-        double t[6] = {0, 0, 0, 0, 0, 0};
-        for (int w = 0; w < 32; ++w)
-            for (int k = 0; k < 6; ++k) t[k] += wacc[w][k];
-        const double N2 = 2.0 * P;
-        const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
-        double sm = 0;
-        if (ch > 0) sm += t[1] / ch;
-        if (cv > 0) sm += t[2] / cv;
-        if (cd > 0) sm += (t[3] + t[4]) / cd;
-        const int S = tab.n_scales;
-        terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
-        terms[S + s] = (float)(t[0] / ((double)P * H * W));                  // loss.py:33
-        terms[2 * S + s] = (float)t[5];
+        const unsigned prev = atomicAdd(ticket, 1u);
+        is_last = (prev == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    finalize_terms(tab, partials, terms, n_bad, wacc);
+    if (threadIdx.x == 0) *ticket = 0u;   // self-resetting for the next call on this workspace
+}
+
+// run by ONE CTA (kLossThreads threads): warp w sums the records of (scale, prediction) pairs
+// w, w+8, ... in a fixed order in fp64; thread 0 then combines per scale.
+__device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
+                               int32_t* n_bad, double (*wacc)[6]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int P = tab.n_pred, S = tab.n_scales;
+    for (int s = 0; s < S; ++s) {
+        const int H = tab.H[s], W = tab.W[s];
+        const int per = tab.tiles_x[s] * tab.tiles_y[s];
+        double tot[6] = {0, 0, 0, 0, 0, 0};   // photo, h, v, d_a, d_b, outborder
+        for (int n = warp; n < P; n += kLossThreads / 32) {
+            double a[7] = {0, 0, 0, 0, 0, 0, 0};
+            const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
+            for (int t = lane; t < per; t += 32) {
+                const float4 r0 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
+                const float4 r1 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
+                a[0] += (double)r0.x; a[1] += (double)r0.y; a[2] += (double)r0.z; a[3] += (double)r0.w;
+                a[4] += (double)r1.x; a[5] += (double)r1.y; a[6] += (double)r1.z;
+            }
+#pragma unroll
+            for (int k = 0; k < 7; ++k)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
+            for (int k = 0; k < 5; ++k) tot[k] += a[k];
+            const double nb = a[6];
+            if (nb > 0) tot[5] += a[5] / (2.0 * nb * (double)P);               // loss.py:99-113
+            if (lane == 0) n_bad[s * P + n] = (int32_t)nb;
+        }
+        if (lane == 0)
+            for (int k = 0; k < 6; ++k) wacc[warp][k] = tot[k];
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t[6] = {0, 0, 0, 0, 0, 0};
+            for (int w = 0; w < kLossThreads / 32; ++w)
+                for (int k = 0; k < 6; ++k) t[k] += wacc[w][k];
+            const double N2 = 2.0 * P;
+            const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
+            double sm = 0;
+            if (ch > 0) sm += t[1] / ch;
+            if (cv > 0) sm += t[2] / cv;
+            if (cd > 0) sm += (t[3] + t[4]) / cd;
+            terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
+            terms[S + s] = (float)(t[0] / ((double)P * H * W));                  // loss.py:33
+            terms[2 * S + s] = (float)t[5];
+        }
+        __syncthreads();
     }
 }
 
@@ -342,10 +371,22 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
     return DVSOF_OK;
 }
 
+static size_t partial_bytes(const ScaleTable& tab) {
+    return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
+}
+
 extern "C" size_t dvsof_loss_workspace_bytes(const dvsof_loss_scales_t* sc) {
     ScaleTable tab;
     if (build_table(sc, &tab, false)) return 0;
-    return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
+    return partial_bytes(tab) + 256;   // tile records + the finalize ticket
+}
+
+static int launch_forward(const ScaleTable& tab, const int32_t* match_idx, float* terms,
+                          int32_t* n_bad, void* workspace, cudaStream_t stream, bool pdl) {
+    float* partials = reinterpret_cast<float*>(workspace);
+    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    return launch_kernel("warp_loss_fwd_kernel", warp_loss_fwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
+                         kLossThreads, 0, stream, pdl, tab, match_idx, partials, ticket, terms, n_bad);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -356,11 +397,9 @@ extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int3
     if (!match_idx || !terms || !n_bad || !workspace)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_forward: null buffer");
     cudaStream_t stream = (cudaStream_t)stream_;
-    float* partials = reinterpret_cast<float*>(workspace);
-    warp_loss_fwd_kernel<<<tab.cta_begin[DVSOF_MAX_SCALES], kLossThreads, 0, stream>>>(tab, match_idx, partials);
-    if (int rc = check_launch("warp_loss_fwd_kernel")) return rc;
-    warp_loss_finalize_kernel<<<tab.n_scales, 1024, 0, stream>>>(tab, partials, terms, n_bad);
-    return check_launch("warp_loss_finalize_kernel");
+    cudaError_t e = cudaMemsetAsync(static_cast<char*>(workspace) + partial_bytes(tab), 0, 4, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "loss ticket memset: %s", cudaGetErrorString(e));
+    return launch_forward(tab, match_idx, terms, n_bad, workspace, stream, false);
 }
 
 extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -370,31 +409,71 @@ extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!match_idx || !grad_terms || !n_bad)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_backward: null buffer");
-    warp_loss_bwd_kernel<<<tab.cta_begin[DVSOF_MAX_SCALES], kLossThreads, 0, (cudaStream_t)stream_>>>(
-        tab, match_idx, grad_terms, n_bad);
-    return check_launch("warp_loss_bwd_kernel");
+    return launch_kernel("warp_loss_bwd_kernel", warp_loss_bwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
+                         kLossThreads, 0, (cudaStream_t)stream_, false, tab, match_idx, grad_terms, n_bad);
+}
+
+static int launch_match(const float* flow_ts, const int64_t* flow_sample_idx, int64_t P,
+                        const float* timestamps, const int64_t* sample_idx, int64_t D,
+                        int32_t* match_idx, uint32_t* status, unsigned* ticket, cudaStream_t stream) {
+    if (P < 1 || D < 1 || P > (1 << 24) || D > (1 << 24) || !flow_ts || !flow_sample_idx ||
+        !timestamps || !sample_idx || !match_idx || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "match_timestamps: bad arguments");
+    const int threads = 128, blocks = (int)((2 * P + threads - 1) / threads);
+    return launch_kernel("match_timestamps_kernel", match_timestamps_kernel, blocks, threads, 0, stream,
+                         false, flow_ts, flow_sample_idx, (int)P, timestamps, sample_idx, (int)D,
+                         match_idx, status, ticket);
 }
 
 extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_sample_idx,
                                       int64_t P, const float* timestamps,
                                       const int64_t* sample_idx, int64_t D, int32_t* match_idx,
                                       uint32_t* status, void* stream_) {
-    if (P < 1 || D < 1 || P > (1 << 24) || D > (1 << 24) || !flow_ts || !flow_sample_idx ||
-        !timestamps || !sample_idx || !match_idx || !status)
-        return fail(DVSOF_ERR_INVALID_ARGUMENT, "match_timestamps: bad arguments");
-    const int threads = 128, blocks = (int)((2 * P + threads - 1) / threads);
-    match_timestamps_kernel<<<blocks, threads, 0, (cudaStream_t)stream_>>>(
-        flow_ts, flow_sample_idx, (int)P, timestamps, sample_idx, (int)D, match_idx, status);
-    return check_launch("match_timestamps_kernel");
+    return launch_match(flow_ts, flow_sample_idx, P, timestamps, sample_idx, D, match_idx, status,
+                        nullptr, (cudaStream_t)stream_);
 }
 
-extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
-                                     float* dst, int32_t Hout, int32_t Wout, void* stream_) {
+static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, float* dst,
+                         int32_t Hout, int32_t Wout, cudaStream_t stream, bool pdl) {
     if (D < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || !src || !dst)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: bad arguments");
     const int64_t total = D * Hout * Wout;
     int64_t blocks = (total + 255) / 256;
     if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-    resize_bilinear_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(src, Hin, Win, dst, Hout, Wout, total);
-    return check_launch("resize_bilinear_kernel");
+    return launch_kernel("resize_bilinear_kernel", resize_bilinear_kernel, (int)blocks, 256, 0, stream,
+                         pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, total);
+}
+
+extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
+                                     float* dst, int32_t Hout, int32_t Wout, void* stream_) {
+    return launch_resize(src, D, Hin, Win, dst, Hout, Wout, (cudaStream_t)stream_, false);
+}
+
+// Whole forward of utils/loss.py:179-214 in one call: timestamp matching, the chained pyramid
+// (each level resized from the previous one, line 210) into the caller's level buffers
+// scales->images[s], the fused per-scale terms.  Kernels are chained with programmatic dependent
+// launch, so there is no host work and no idle gap between them.
+extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
+                                             const dvsof_loss_frames_t* fr, int32_t* match_idx,
+                                             float* terms, int32_t* n_bad, void* workspace,
+                                             uint32_t* status, void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, false)) return rc;
+    if (!fr || !fr->images || fr->n_images < 1 || fr->H0 < 1 || fr->W0 < 1 || !match_idx || !terms ||
+        !n_bad || !workspace || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_forward: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
+                              fr->sample_idx, fr->n_images, match_idx, status, ticket, stream))
+        return rc;
+    const float* src = fr->images;
+    int Hin = fr->H0, Win = fr->W0;
+    for (int s = 0; s < sc->n_scales; ++s) {                               // loss.py:207-210
+        float* dst = const_cast<float*>(sc->images[s]);
+        if (int rc = launch_resize(src, fr->n_images, Hin, Win, dst, sc->H[s], sc->W[s], stream, true))
+            return rc;
+        src = dst; Hin = sc->H[s]; Win = sc->W[s];
+    }
+    return launch_forward(tab, match_idx, terms, n_bad, workspace, stream, true);
 }

@@ -1,0 +1,116 @@
+"""EV-FlowNet stand-in for the data-parallel train-step measurement (SURVEY.md section 8 row
+A16 / (e), BASELINE.json configs[1] and configs[4]).
+
+The network itself is OUT of the hot-path scope: its convolutions stay on cuDNN, as the
+north_star says.  What matters here is the call site the reference's `Model.forward` has
+(EV_FlowNet/net.py:207-264): `forward(events, timestamps, sample_idx, imsize, raw, intermediate)`
+starts with `quantize` -> the CUDA event-image encoder of this package, and returns
+`(flows coarse->fine, flow_ts (P,2), flow_sample_idx (P), [features])`, which is what
+`training.process_minibatch` and `loss.Losses` consume.  Same layer plan as the reference
+(4 stride-2 encoders 64..512, 2 residual blocks, 4 nearest-upsample decoders with a 1x1 flow
+head `tanh * 256` each; 14,136,680 parameters) so the step cost is representative; weights are
+random (there are no checkpoints offline).  A user of the reference keeps the reference's own
+`EV_FlowNet/net.py` and only swaps `compute_event_image`."""
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from .encoder import quantize
+
+_WIDTHS = (64, 128, 256, 512)
+
+
+class _ConvReluBN(nn.Module):
+    """conv -> relu -> batchnorm (the reference normalises AFTER the activation, net.py:36,54)."""
+
+    def __init__(self, cin, cout, stride=1, pad=0):
+        super().__init__()
+        self.conv = nn.Conv2d(cin, cout, 3, stride=stride, padding=pad)
+        self.bn = nn.BatchNorm2d(cout)
+        nn.init.kaiming_normal_(self.conv.weight, a=4.4, nonlinearity='relu')
+        nn.init.zeros_(self.conv.bias)
+        nn.init.constant_(self.bn.weight, 0.1)
+
+    def forward(self, x):
+        return self.bn(F.relu(self.conv(x)))
+
+
+class _Down(nn.Module):
+    """stride-2 3x3 conv, input padded on the right/bottom only (net.py:39-54)."""
+
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.block = _ConvReluBN(cin, cout, stride=2)
+
+    def forward(self, x):
+        return self.block(F.pad(x, (0, 2, 0, 2)))
+
+
+class _Residual(nn.Module):
+    def __init__(self, ch, depth=2):
+        super().__init__()
+        self.body = nn.Sequential(*[_ConvReluBN(ch, ch, pad=1) for _ in range(depth)])
+
+    def forward(self, x):
+        return x + self.body(x)
+
+
+class _Up(nn.Module):
+    """nearest x2, reflect pad 1, 3x3 conv (net.py:72-85)."""
+
+    def __init__(self, cin, cout):
+        super().__init__()
+        self.block = _ConvReluBN(cin, cout)
+
+    def forward(self, x):
+        return self.block(F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect'))
+
+
+class Model(nn.Module):
+    def __init__(self, device='cuda'):
+        super().__init__()
+        self.device = device
+        chans = (4,) + _WIDTHS
+        self.enc = nn.ModuleList(_Down(chans[i], chans[i + 1]) for i in range(4))
+        self.tr = nn.ModuleList(_Residual(_WIDTHS[-1]) for _ in range(2))
+        outs = (256, 128, 64, 32)
+        self.dec = nn.ModuleList()
+        self.flow = nn.ModuleList()
+        for i, cout in enumerate(outs):
+            cin = 2 * _WIDTHS[3 - i] + (2 if i else 0)     # features + skip (+ previous flow)
+            self.dec.append(_Up(cin, cout))
+            head = nn.Conv2d(cout, 2, 1)
+            nn.init.kaiming_normal_(head.weight, a=4.4, nonlinearity='relu')
+            nn.init.zeros_(head.bias)
+            self.flow.append(head)
+        self.to(device)
+
+    def quantize(self, events, timestamps, sample_idx, imsize):
+        return quantize(events, timestamps, sample_idx, imsize)           # net.py:197-205
+
+    def forward(self, events, timestamps, sample_idx, imsize, raw=True, intermediate=False):
+        outsize = [(imsize[0] // 2 ** k, imsize[1] // 2 ** k) for k in (3, 2, 1, 0)]
+        x = self.quantize(events, timestamps, sample_idx, imsize) if raw else events
+        feats = {'input': x} if intermediate else None
+        skips = []
+        h = x
+        for i, enc in enumerate(self.enc):
+            h = enc(h)
+            skips.append(h)
+            if intermediate:
+                feats[f'enc_{i}'] = h
+        for i, res in enumerate(self.tr):
+            h = res(h)
+            if intermediate:
+                feats[f'tr_{i}'] = h
+        flows = []
+        for i, (dec, head) in enumerate(zip(self.dec, self.flow)):
+            h = dec(torch.cat((h, skips[3 - i]), 1))
+            f = torch.tanh(head(h)) * 256.
+            flows.append(f)
+            h = torch.cat((h, f), 1)
+            if intermediate:
+                feats[f'dec_op_{i}'] = h
+        result = tuple(f[..., :s[0], :s[1]] for f, s in zip(flows, outsize))
+        extra = (feats,) if intermediate else ()
+        return (result, timestamps.reshape(-1, 2), sample_idx[0::2]) + extra

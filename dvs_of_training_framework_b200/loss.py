@@ -57,9 +57,35 @@ def _scale_struct(flows, levels, grads=None):
     return sc
 
 
+def _carve(buf, sizes):
+    """Split a flat fp32 buffer into 16-byte aligned pieces of `sizes` elements."""
+    out, off = [], 0
+    for n in sizes:
+        out.append(buf[off:off + n])
+        off += (n + 3) & ~3
+    return out
+
+
+def _flat_len(sizes):
+    return sum((n + 3) & ~3 for n in sizes)
+
+
+def _backward(match_idx, n_bad, levels, flows, grad_terms):
+    dev = flows[0].device
+    sizes = [f.numel() for f in flows]
+    gbuf = torch.empty(_flat_len(sizes), dtype=torch.float32, device=dev)
+    grads = [g.view(f.shape) for g, f in zip(_carve(gbuf, sizes), flows)]
+    with torch.cuda.device(dev):
+        sc = _scale_struct(flows, levels, grads)
+        _lib.call('dvsof_warp_loss_backward', sc, _lib.ptr(match_idx), _lib.ptr(grad_terms.contiguous()),
+                  _lib.ptr(n_bad), _lib.stream_ptr(dev))
+    return grads
+
+
 class _WarpLoss(torch.autograd.Function):
     """terms[3*S] = [smoothness(s)..., photometric(s)..., outborder(s)...] of all scales in one
-    fused launch; backward is the analytic gradient w.r.t. every flow (images get none)."""
+    fused launch, from ready-made pyramid levels; backward is the analytic gradient w.r.t. every
+    flow (images get none)."""
 
     @staticmethod
     def forward(ctx, match_idx, n_scales, *tensors):
@@ -83,14 +109,47 @@ class _WarpLoss(torch.autograd.Function):
         S = ctx.n_scales
         match_idx, n_bad = ctx.saved_tensors[:2]
         levels, flows = ctx.saved_tensors[2:2 + S], ctx.saved_tensors[2 + S:]
-        dev = flows[0].device
-        grad_terms = grad_terms.contiguous()
-        grads = [torch.empty_like(f) for f in flows]
+        return (None, None) + (None,) * S + tuple(_backward(match_idx, n_bad, levels, flows, grad_terms))
+
+
+class _MultiscaleLoss(torch.autograd.Function):
+    """utils/loss.py:179-214 forward in ONE library call (matching + chained pyramid + fused
+    terms, kernels chained on the stream with programmatic dependent launch)."""
+
+    @staticmethod
+    def forward(ctx, owner, images, flow_ts, flow_sample_idx, timestamps, sample_idx, *flows):
+        dev = images.device
+        D, _, H, W = images.shape
+        S, P = len(flows), flows[0].shape[0]
+        lvl_sizes = [D * f.shape[-2] * f.shape[-1] for f in flows]
         with torch.cuda.device(dev):
-            sc = _scale_struct(flows, levels, grads)
-            _lib.call('dvsof_warp_loss_backward', sc, _lib.ptr(match_idx), _lib.ptr(grad_terms),
-                      _lib.ptr(n_bad), _lib.stream_ptr(dev))
-        return (None, None) + (None,) * S + tuple(grads)
+            # one allocation per call: pyramid levels | match_idx | n_bad | terms (the first three
+            # are what backward needs, so they cannot live in a buffer shared between calls)
+            buf = torch.empty(_flat_len(lvl_sizes + [2 * P, S * P, 3 * S]), dtype=torch.float32, device=dev)
+            pieces = _carve(buf, lvl_sizes + [2 * P, S * P, 3 * S])
+            levels = [pc.view(D, f.shape[-2], f.shape[-1]) for pc, f in zip(pieces, flows)]
+            match_idx, n_bad, terms = pieces[S].view(torch.int32), pieces[S + 1].view(torch.int32), pieces[S + 2]
+            sc = _scale_struct(flows, levels)
+            fr = _lib.LossFrames()
+            fr.images, fr.n_images, fr.H0, fr.W0 = images.data_ptr(), D, H, W
+            fr.flow_ts, fr.flow_sample_idx = flow_ts.data_ptr(), flow_sample_idx.data_ptr()
+            fr.timestamps, fr.sample_idx = timestamps.data_ptr(), sample_idx.data_ptr()
+            ws = owner._workspace(sc, dev)
+            st = _lib.status_for(dev)
+            st.flush()
+            _lib.call('dvsof_multiscale_loss_forward', sc, fr, _lib.ptr(match_idx), _lib.ptr(terms),
+                      _lib.ptr(n_bad), _lib.ptr(ws), _lib.ptr(st.word), _lib.stream_ptr(dev))
+            st.after_call()                                              # loss.py:193 asserts
+        ctx.n_scales = S
+        ctx.save_for_backward(match_idx, n_bad, *levels, *flows)
+        return terms
+
+    @staticmethod
+    def backward(ctx, grad_terms):
+        S = ctx.n_scales
+        match_idx, n_bad = ctx.saved_tensors[:2]
+        levels, flows = ctx.saved_tensors[2:2 + S], ctx.saved_tensors[2 + S:]
+        return (None,) * 6 + tuple(_backward(match_idx, n_bad, levels, flows, grad_terms))
 
 
 def _check_shapes(owner, N, H, W):
@@ -138,42 +197,47 @@ class Loss:
 
 class Losses:
     """All scales (utils/loss.py:174-214): image<->flow timestamp matching, the CHAINED bilinear
-    pyramid (line 210) and the per-scale terms, with no host synchronisation."""
+    pyramid (line 210) and the per-scale terms, with no host synchronisation (Status.mode
+    'deferred') or exactly one (mode 'sync', to raise the reference's AssertionError in place)."""
 
     def __init__(self, shapes, batch_size, device, timers=FakeTimer()):
         self.losses = [Loss(shape, batch_size, device, timers) for shape in shapes]
         self.timers = timers
+        self._ws = {}
 
-    def __call__(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+    def _workspace(self, sc, dev):
+        key = (dev, sc.n_pred)
+        ws = self._ws.get(key)
+        if ws is None:   # tile records + ticket; only live inside one forward call
+            ws = self._ws[key] = torch.empty(_lib.load().dvsof_loss_workspace_bytes(sc),
+                                             dtype=torch.uint8, device=dev)
+        return ws
+
+    def terms(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+        """The 3*S terms as ONE autograd-connected tensor
+        [smoothness(s)..., photometric(s)..., outborder(s)...]; `__call__` returns views of it."""
         S = len(flows)
         assert S == len(self.losses) and 1 <= S <= _lib.MAX_SCALES
         images = _f32(images, 'images')
-        dev = images.device
-        D, C, H, W = images.size()
-        assert C == 1, 'the fused kernel warps single-channel (grayscale) frames'
+        assert images.dim() == 4 and images.shape[1] == 1, \
+            'the fused kernel warps single-channel (grayscale) frames'
+        D = images.shape[0]
         P = flow_sample_idx.shape[0]
         flows = [_f32(f, 'flow') for f in flows]
         for loss, f in zip(self.losses, flows):
             assert f.dim() == 4 and f.shape[0] == P and f.shape[1] == 2
             _check_shapes(loss, P, f.shape[-2], f.shape[-1])
-        with torch.no_grad(), torch.cuda.device(dev):
-            st = _lib.status_for(dev)
-            st.flush()
-            match_idx = torch.empty(2 * P, dtype=torch.int32, device=dev)
-            _lib.call('dvsof_match_timestamps',
-                      _lib.ptr(_f32(flow_ts, 'flow_ts')),
-                      _lib.ptr(_lib.require_cuda(flow_sample_idx, 'flow_sample_idx', torch.int64)),
-                      P, _lib.ptr(_f32(timestamps, 'timestamps')),
-                      _lib.ptr(_lib.require_cuda(sample_idx, 'sample_idx', torch.int64)), D,
-                      _lib.ptr(match_idx), _lib.ptr(st.word), _lib.stream_ptr(dev))
-            st.after_call()
-            levels = []
-            cur = images.view(D, H, W)
-            for f in flows:                                               # loss.py:207-210
-                cur = interpolate(cur, f.shape[-2:])
-                levels.append(cur)
-        terms = _WarpLoss.apply(match_idx, S, *levels, *flows)
-        flat = terms.unbind(0)
+        flow_ts = _f32(flow_ts, 'flow_ts')
+        timestamps = _f32(timestamps, 'timestamps')
+        assert flow_ts.numel() == 2 * P and timestamps.numel() == D and sample_idx.numel() == D
+        return _MultiscaleLoss.apply(self, images, flow_ts,
+                                     _lib.require_cuda(flow_sample_idx, 'flow_sample_idx', torch.int64),
+                                     timestamps, _lib.require_cuda(sample_idx, 'sample_idx', torch.int64),
+                                     *flows)
+
+    def __call__(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+        S = len(flows)
+        flat = self.terms(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx).unbind(0)
         return tuple(flat[:S]), tuple(flat[S:2 * S]), tuple(flat[2 * S:])
 
 

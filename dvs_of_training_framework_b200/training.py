@@ -1,0 +1,327 @@
+"""Training step -- drop-in for the reference's `utils/training.py` (`combined_loss` :12-24,
+`process_minibatch` :37-86, `train` :89-235, `validate` :244-271) with the data-parallel
+partition the reference lacks:
+
+  * the batch is sharded BY SAMPLE across ranks (`shard_batch`): events are grouped by
+    ascending `sample_index` (utils/dataset.py:974-985), so a shard is one contiguous event
+    range plus the matching `2b` ranges of images / timestamps / sample_idx -- no data-path
+    collective;
+  * the only exchange is the gradient allreduce of the optimizer step (`GradientAllreducer`):
+    flat fp32 buckets, NCCL over NVLink (gloo in the CPU tests), launched as each bucket's
+    gradients become ready so the wire time hides behind cuDNN's backward.
+
+One process per GPU (torchrun); world size 1 degenerates to the reference's loop.
+"""
+import torch
+import torch.distributed as dist
+
+from .timer import FakeTimer
+
+
+def mean(values):
+    """utils/common.py:22-23."""
+    return sum(values) / len(values)
+
+
+def _world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+_WEIGHTS = {}
+
+
+def _weight_vector(weights, S, device):
+    key = (weights, S, device)
+    w = _WEIGHTS.get(key)
+    if w is None:
+        w = _WEIGHTS[key] = torch.tensor([wk / S for wk in weights for _ in range(S)],
+                                         dtype=torch.float32, device=device)
+    return w
+
+
+def combined_loss(evaluator, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx,
+                  features, weights=[0.5, 1, 1]):
+    """utils/training.py:12-24: loss = sum_k w_k * mean_s(term[k][s]), k over (smoothness,
+    photometric, outborder).  With the fused evaluator the 3*S terms are one tensor, so the
+    weighted sum is a single dot product (one node in the autograd graph instead of ~30)."""
+    if hasattr(evaluator, 'terms'):
+        flat = evaluator.terms(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
+        S = flat.numel() // 3
+        loss = torch.dot(flat, _weight_vector(tuple(float(w) for w in weights), S, flat.device))
+        parts = flat.unbind(0)
+        return loss, (tuple(parts[:S]), tuple(parts[S:2 * S]), tuple(parts[2 * S:]))
+    terms = evaluator(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
+    loss = sum(map(lambda v, w: w * mean(v), terms, weights))
+    return loss, terms
+
+
+def predictions2tag(predictions):
+    """utils/training.py:33-34."""
+    return (f'{x.shape[-2]}x{x.shape[-1]}' for x in predictions)
+
+
+def shard_bounds(n_samples, rank, world):
+    """Samples [lo, hi) of rank `rank`: equal split, remainder to the first ranks."""
+    base, rem = divmod(n_samples, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_batch(batch, rank, world):
+    """Partition a collated batch (utils/dataset.py:961-1020 layout) by sample.  Returns a new
+    dict with this rank's contiguous sample range, `sample_index` / `sample_idx` rebased to
+    start at 0.  Frames per sample = len(timestamps) / size (2 for sequence length 1)."""
+    if world == 1:
+        return batch
+    B = int(batch['size'])
+    lo, hi = shard_bounds(B, rank, world)
+    out = dict(batch)
+    out['size'] = hi - lo
+    per = batch['timestamps'].numel() // B
+    for k in ('timestamps', 'sample_idx', 'images'):
+        out[k] = batch[k][lo * per:hi * per]
+    out['sample_idx'] = out['sample_idx'] - lo
+    if 'events' in batch:
+        ev = batch['events']
+        b = ev['sample_index']
+        # grouped + ascending -> the shard is one contiguous range (two binary searches)
+        edges = torch.searchsorted(b, torch.tensor([lo, hi], dtype=b.dtype, device=b.device))
+        e0, e1 = int(edges[0]), int(edges[1])
+        sh = {k: v[e0:e1] for k, v in ev.items() if isinstance(v, torch.Tensor) and v.dim() == 1
+              and v.numel() == b.numel()}
+        sh['sample_index'] = sh['sample_index'] - lo
+        for k, v in ev.items():
+            sh.setdefault(k, v)
+        out['events'] = sh
+    if 'data' in batch:   # pre-quantised event images (B,4,H,W)
+        out['data'] = batch['data'][lo:hi]
+    if isinstance(batch.get('augmentation_params'), dict):
+        out['augmentation_params'] = {k: v[lo:hi] for k, v in batch['augmentation_params'].items()}
+    return out
+
+
+class GradientAllreducer:
+    """Flat-bucket gradient averaging for the data-parallel step.
+
+    Every parameter's `.grad` is a view into one of a few flat fp32 buckets (filled in reverse
+    registration order = the order backward produces them), so a bucket is reduced in place with
+    one `all_reduce(SUM)` pre-scaled by 1/world, issued from a post-accumulate hook the moment
+    its last gradient lands -- asynchronously, on the process group's own stream, while cuDNN
+    continues with the earlier layers.  `wait()` before `optimizer.step()`."""
+
+    def __init__(self, params, bucket_mb=16.0, group=None):
+        self.group = group
+        self.rank, self.world = _world()
+        self.params = [p for p in params if p.requires_grad]
+        self.buckets, self.where, self.handles = [], {}, []
+        cap = int(bucket_mb * (1 << 20)) // 4
+        cur, cur_n = [], 0
+        for p in reversed(self.params):
+            if cur and cur_n + p.numel() > cap:
+                self._close(cur, cur_n)
+                cur, cur_n = [], 0
+            cur.append(p)
+            cur_n += p.numel()
+        if cur:
+            self._close(cur, cur_n)
+        self.hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+        self.enabled = True          # False on non-boundary micro-batches (accumulation)
+
+    def _close(self, plist, n):
+        flat = torch.zeros(n, dtype=plist[0].dtype, device=plist[0].device)
+        idx, off = len(self.buckets), 0
+        for p in plist:
+            p.grad = flat[off:off + p.numel()].view_as(p)
+            self.where[p] = idx
+            off += p.numel()
+        self.buckets.append({'flat': flat, 'params': plist, 'pending': len(plist)})
+
+    def _on_grad(self, p):
+        if not self.enabled or self.world == 1:
+            return
+        b = self.buckets[self.where[p]]
+        b['pending'] -= 1
+        if b['pending'] == 0:
+            b['flat'].div_(self.world)
+            self.handles.append(dist.all_reduce(b['flat'], op=dist.ReduceOp.SUM, group=self.group,
+                                                async_op=True))
+
+    def wait(self):
+        """Block the current stream on every outstanding bucket; reduce buckets whose hooks did
+        not all fire (parameters unused in this step keep their zero gradient)."""
+        if self.world > 1 and self.enabled:
+            for b in self.buckets:
+                if b['pending'] != 0:    # same on every rank: same graph, same unused parameters
+                    b['flat'].div_(self.world)
+                    self.handles.append(dist.all_reduce(b['flat'], op=dist.ReduceOp.SUM,
+                                                        group=self.group, async_op=True))
+            for h in self.handles:
+                h.wait()
+        self.handles = []
+        for b in self.buckets:
+            b['pending'] = len(b['params'])
+
+    def zero_grad(self):
+        """Keep the flat views (set_to_none would detach them): zero in place."""
+        for b in self.buckets:
+            b['flat'].zero_()
+
+    def broadcast_parameters(self, module):
+        """Rank 0's weights and buffers everywhere (BatchNorm statistics stay per replica
+        afterwards)."""
+        if self.world == 1:
+            return
+        for t in list(module.parameters()) + list(module.buffers()):
+            dist.broadcast(t.data, src=0, group=self.group)
+
+
+def process_minibatch(model, batch, timers, device, is_raw, evaluator, weights,
+                      return_prediction=False):
+    """utils/training.py:37-86, unchanged in meaning: H2D of the batch, model forward (whose
+    first act is `quantize` -> the CUDA encoder), fused multiscale loss."""
+    timers('batch2gpu').start()
+    timestamps, sample_idx, images = map(lambda x: x.to(device, non_blocking=True),
+                                         (batch['timestamps'], batch['sample_idx'], batch['images']))
+    if is_raw:
+        events = dict(batch['events'])
+        for k in set.difference(set(events.keys()), {'size'}):
+            events[k] = events[k].to(device, non_blocking=True)
+    else:
+        events = batch['data'].to(device, non_blocking=True)
+    timers('batch2gpu').stop()
+    shape = images.size()[-2:]
+    timers('forward').start()
+    prediction, flow_ts, flow_sample_idx, features = model(events, timestamps, sample_idx, shape,
+                                                           raw=is_raw, intermediate=True)
+    tags = predictions2tag(prediction)
+    timers('forward').stop()
+    timers('loss').start()
+    loss, terms = combined_loss(evaluator, prediction, flow_ts, flow_sample_idx, images,
+                                timestamps, sample_idx, features, weights=weights)
+    terms = ((y.item() for y in x) for x in terms)      # lazy, as the reference: no sync here
+    timers('loss').stop()
+    add_info = tuple()
+    if return_prediction:
+        add_info = ({'prediction': prediction, 'flow_ts': flow_ts,
+                     'flow_sample_idx': flow_sample_idx, 'features': features}, )
+    return (loss, terms, tags) + add_info
+
+
+def add_loss(loss_sum, loss_values):
+    """utils/training.py:238-241."""
+    if len(loss_sum) == 0:
+        return list(loss_values)
+    return [x + y for x, y in zip(loss_sum, loss_values)]
+
+
+def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, evaluator,
+          weights=[0.5, 1, 1], is_raw=True, accumulation_steps=1, timers=FakeTimer(), hooks={},
+          init_step=0, init_samples_passed=0, max_events_per_batch: int = 350000,
+          reducer: GradientAllreducer = None):
+    """utils/training.py:89-235 with the data-parallel partition: under an initialised process
+    group every rank receives the same global batch from `loader`, keeps its shard (by sample)
+    and averages gradients through `reducer` before the optimizer step.  Logging, hooks,
+    accumulation and the over-large-batch skip follow the reference; only rank 0 logs."""
+    rank, world = _world()
+    if world > 1 and reducer is None:
+        reducer = GradientAllreducer(model.parameters())
+        reducer.broadcast_parameters(model)
+    model.train()
+    samples_passed = init_samples_passed
+    loss_sum, smooth_sum, photo_sum, out_reg_sum = 0, [], [], []
+    if reducer is not None:
+        reducer.zero_grad()
+    else:
+        optimizer.zero_grad(set_to_none=True)
+    init_batch = init_step * accumulation_steps
+    global_step = init_batch
+    num_skipped = 0
+    timers('batch_construction').start()
+    for batch in loader:
+        if global_step == num_steps * accumulation_steps:
+            break
+        num_events = batch['events']['x'].numel() if is_raw else 0
+        if num_events > max_events_per_batch:                       # training.py:141-150
+            num_skipped += 1
+            num_processed = global_step - init_batch
+            if rank == 0:
+                print(f'Skipping batch with {num_events} events')
+                print(f'Processing rate is {num_processed / (num_processed + num_skipped):.2f}')
+            continue
+        global_step += 1
+        timers('batch_construction').stop()
+        samples_passed += batch['size']
+        is_step_boundary = global_step % accumulation_steps == 0
+        if reducer is not None:
+            reducer.enabled = is_step_boundary     # reduce once per optimizer step
+        local = shard_batch(batch, rank, world)
+        loss, (smoothness, photometric, out_reg), tags = process_minibatch(
+            model, local, timers, device, is_raw, evaluator, weights)
+        loss /= accumulation_steps
+        timers('backprop').start()
+        loss.backward()
+        timers('backprop').stop()
+        photo_sum = add_loss(photo_sum, photometric)
+        smooth_sum = add_loss(smooth_sum, smoothness)
+        out_reg_sum = add_loss(out_reg_sum, out_reg)
+        if is_step_boundary:
+            timers('optimizer_step').start()
+            if reducer is not None:
+                reducer.wait()
+            optimizer.step()
+            if reducer is not None:
+                reducer.zero_grad()
+            else:
+                optimizer.zero_grad(set_to_none=True)
+            timers('optimizer_step').stop()
+            scheduler.step()
+            timers('logging').start()
+            loss_sum += loss.item()
+            if rank == 0 and logger is not None:
+                for tag, s, p, o in zip(tags, smooth_sum, photo_sum, out_reg_sum):
+                    logger.add_scalar(f'Train/photometric loss/{tag}', p / accumulation_steps, samples_passed)
+                    logger.add_scalar(f'Train/smoothness loss/{tag}', s / accumulation_steps, samples_passed)
+                    logger.add_scalar(f'Train/out regularization/{tag}', o / accumulation_steps, samples_passed)
+                logger.add_scalar('General/Train loss', loss_sum, samples_passed)
+                for i, lr in enumerate([p['lr'] for p in optimizer.param_groups]):
+                    logger.add_scalar(f'General/learning rate/{i}', lr, samples_passed)
+            loss_sum, smooth_sum, photo_sum, out_reg_sum = 0, [], [], []
+            timers('logging').stop()
+            step = global_step // accumulation_steps
+            for k, hook in hooks.items():
+                timers(k).start()
+                hook(step, samples_passed)
+                timers(k).stop()
+            model.train()
+        else:
+            timers('logging').start()
+            loss_sum += loss.item()
+            timers('logging').stop()
+        timers('batch_construction').start()
+    timers('batch_construction').stop()
+    return global_step // accumulation_steps
+
+
+def validate(model, device, loader, samples_passed, logger, evaluator, weights=[0.5, 1, 1],
+             is_raw=True):
+    """utils/training.py:244-271."""
+    model.eval()
+    n = len(loader)
+    photo_sum, smooth_sum, out_reg_sum, loss_sum = [], [], [], 0
+    tags = ()
+    with torch.no_grad():
+        for batch in loader:
+            loss, (smoothness, photometric, out_reg), tags = process_minibatch(
+                model, batch, FakeTimer(), device, is_raw, evaluator, weights)
+            photo_sum = add_loss(photo_sum, photometric)
+            smooth_sum = add_loss(smooth_sum, smoothness)
+            out_reg_sum = add_loss(out_reg_sum, out_reg)
+            loss_sum += loss.item()
+    logger.add_scalar('General/Validation loss', loss_sum / n, samples_passed)
+    for tag, s, p, o in zip(tags, smooth_sum, photo_sum, out_reg_sum):
+        logger.add_scalar(f'Validation/smoothness loss/{tag}', s / n, samples_passed)
+        logger.add_scalar(f'Validation/photometric loss/{tag}', p / n, samples_passed)
+        logger.add_scalar(f'Validation/out regularization loss/{tag}', o / n, samples_passed)
+    return loss_sum / n

@@ -154,6 +154,24 @@ int dvsof_warp_loss_forward(const dvsof_loss_scales_t* scales, const int32_t* ma
 int dvsof_warp_loss_backward(const dvsof_loss_scales_t* scales, const int32_t* match_idx,
                              const float* grad_terms, const int32_t* n_bad, void* stream);
 
+/* utils/loss.py:179-214 `Losses.__call__` forward in ONE call: timestamp matching (:182-206),
+ * the chained pyramid (:207-210; level s is resized from level s-1, level 0 from `images`) written
+ * into the caller's level buffers scales->images[s] (D,H_s,W_s), and the per-scale terms.
+ * match_idx [dev int32 2P], terms, n_bad as in dvsof_warp_loss_forward (all outputs, kept by the
+ * caller for dvsof_warp_loss_backward). */
+typedef struct {
+    const float* images;            /* [dev] (D,H0,W0) full-resolution frames, fp32 */
+    int32_t n_images, H0, W0;       /* D */
+    const float* flow_ts;           /* [dev] (P,2) */
+    const int64_t* flow_sample_idx; /* [dev] (P) */
+    const float* timestamps;        /* [dev] (D) */
+    const int64_t* sample_idx;      /* [dev] (D) */
+} dvsof_loss_frames_t;
+int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* scales,
+                                  const dvsof_loss_frames_t* frames, int32_t* match_idx,
+                                  float* terms, int32_t* n_bad, void* workspace, uint32_t* status,
+                                  void* stream);
+
 #ifdef __cplusplus
 }
 #endif

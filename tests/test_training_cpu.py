@@ -1,0 +1,194 @@
+"""CPU (no GPU): host logic of the data-parallel step -- batch sharding
+by sample, flat-bucket gradient averaging over `gloo` at world size 2, and the `train` loop
+contract of utils/training.py:89-235.  The CUDA loss has no CPU path, so the loss used here is
+the torch oracle (test infrastructure) behind the same evaluator interface."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+from torch import nn
+
+from dvs_of_training_framework_b200 import training as tr
+from oracle import loss_oracle as lo
+from tests.helpers import synth_events, synth_loss_inputs
+
+
+def _batch(B=4, H=32, W=32, n=500, seed=3):
+    ev, ts, sidx = synth_events(seed, B, H, W, n, ragged=True)
+    inp = synth_loss_inputs(seed, B, H, W, 2.0)
+    return {'events': ev, 'timestamps': ts, 'sample_idx': sidx, 'images': inp['images'],
+            'augmentation_params': {'idx': torch.arange(B)}, 'size': B}
+
+
+def test_shard_bounds_cover_and_balance():
+    for B in (1, 5, 8, 256):
+        for world in (1, 2, 3, 8):
+            edges = [tr.shard_bounds(B, r, world) for r in range(world)]
+            assert edges[0][0] == 0 and edges[-1][1] == B
+            assert all(a[1] == b[0] for a, b in zip(edges, edges[1:]))
+            sizes = [hi - lo for lo, hi in edges]
+            assert max(sizes) - min(sizes) <= 1
+
+
+@pytest.mark.parametrize('world', [2, 3, 4])
+def test_shard_batch_partitions_by_sample(world):
+    batch = _batch()
+    shards = [tr.shard_batch(batch, r, world) for r in range(world)]
+    assert sum(s['size'] for s in shards) == batch['size']
+    for k in ('x', 'y', 'timestamp', 'polarity'):
+        assert torch.equal(torch.cat([s['events'][k] for s in shards]), batch['events'][k])
+    assert torch.equal(torch.cat([s['images'] for s in shards]), batch['images'])
+    lo_ = 0
+    for s in shards:
+        b = s['events']['sample_index']
+        if b.numel():
+            assert int(b.min()) >= 0 and int(b.max()) < s['size']       # rebased to the shard
+        assert torch.equal(s['sample_idx'], torch.arange(s['size']).repeat_interleave(2))
+        assert s['timestamps'].numel() == 2 * s['size']
+        assert torch.equal(s['augmentation_params']['idx'], torch.arange(lo_, lo_ + s['size']))
+        # the encoder's contract (net.py:101): (sample_idx[-1] + 1) * 2 == len(timestamps)
+        assert (int(s['sample_idx'][-1]) + 1) * 2 == s['timestamps'].numel()
+        lo_ += s['size']
+    assert tr.shard_batch(batch, 0, 1) is batch
+
+
+def test_combined_loss_generic_and_fused_paths_agree():
+    inp = synth_loss_inputs(5, 2, 32, 48, 2.0)
+
+    class Generic:
+        def __call__(self, flows, *a):
+            return lo.multiscale_loss(flows, *a)
+
+    class Fused(Generic):            # same numbers behind the single-tensor `terms` interface
+        def terms(self, flows, *a):
+            return torch.stack([t for group in lo.multiscale_loss(flows, *a) for t in group])
+
+    args = (inp['flows'], inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'],
+            inp['sample_idx'], None)
+    l0, t0 = tr.combined_loss(Generic(), *args, weights=[0.5, 1, 1])
+    l1, t1 = tr.combined_loss(Fused(), *args, weights=[0.5, 1, 1])
+    assert abs(float(l0) - float(l1)) < 1e-6 * max(1.0, abs(float(l0)))
+    assert len(t1) == 3 and all(len(g) == 4 for g in t1)
+    for a, b in zip(t0, t1):
+        for u, v in zip(a, b):
+            assert float(u) == float(v)
+    assert float(l0) == pytest.approx(float(lo.combined(t0)), rel=1e-6)
+
+
+class TinyFlowNet(nn.Module):
+    """4-scale flow predictor with the Model.forward contract (no BatchNorm: replicas == one
+    big batch exactly)."""
+
+    def __init__(self):
+        super().__init__()
+        self.heads = nn.ModuleList(nn.Conv2d(1, 2, 3, padding=1) for _ in range(4))
+        self.unused = nn.Parameter(torch.zeros(3))        # never gets a gradient
+
+    def forward(self, events, timestamps, sample_idx, imsize, raw=True, intermediate=False):
+        B = timestamps.numel() // 2
+        H, W = imsize
+        x = torch.zeros(B, 1, H, W)
+        if events['x'].numel():
+            x.view(B, -1).index_put_((events['sample_index'], events['y'] * W + events['x']),
+                                     torch.ones(events['x'].numel()), accumulate=True)
+        flows = tuple(h(nn.functional.interpolate(x, size=(H // 2 ** k, W // 2 ** k)))
+                      for h, k in zip(self.heads, (3, 2, 1, 0)))
+        return flows, timestamps.reshape(-1, 2), sample_idx[0::2], {}
+
+
+class OracleEvaluator:
+    def __call__(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+        return lo.multiscale_loss(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
+
+
+class Log:
+    def __init__(self):
+        self.rows = []
+
+    def add_scalar(self, tag, value, step):
+        self.rows.append((tag, float(value), step))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _reference_grads(batch, steps=1):
+    torch.manual_seed(0)
+    model = TinyFlowNet()
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    tr.train(model, 'cpu', [batch] * steps, opt, steps, torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0),
+             Log(), OracleEvaluator(), max_events_per_batch=10 ** 9)
+    return [p.detach().clone() for p in model.parameters()]
+
+
+def _worker(rank, world, port, batch, q):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        torch.manual_seed(rank)                              # different init: broadcast must fix it
+        model = TinyFlowNet()
+        red = tr.GradientAllreducer(model.parameters(), bucket_mb=1e-4)   # many small buckets
+        red.broadcast_parameters(model)
+        opt = torch.optim.SGD(model.parameters(), lr=0.1)
+        log = Log()
+        steps = tr.train(model, 'cpu', [batch, batch], opt, 2,
+                         torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0), log, OracleEvaluator(),
+                         max_events_per_batch=10 ** 9, reducer=red)
+        q.put((rank, steps, len(red.buckets), [p.detach().numpy().copy() for p in model.parameters()],
+               len(log.rows)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_data_parallel_train_equals_single_process_gloo():
+    """world 2 over gloo: after 2 optimizer steps both replicas hold the SAME weights, equal to
+    the single-process run on the whole batch (equal shards, no BatchNorm => mean of shard
+    gradients == full-batch gradient)."""
+    torch.manual_seed(0)
+    init = TinyFlowNet()
+    batch = _batch(B=4, n=300)
+    # equal-size shards are required for mean-of-means == global mean
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, batch, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda r: r[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][1] == res[1][1] == 2 and res[0][2] > 1
+    for a, b in zip(res[0][3], res[1][3]):
+        assert (a == b).all()                                 # replicas in lock-step
+    want = _reference_grads(batch, steps=2)
+    for a, w in zip(res[0][3], want):
+        torch.testing.assert_close(torch.from_numpy(a), w, rtol=2e-4, atol=1e-6)
+    assert res[0][4] > 0 and res[1][4] == 0                   # only rank 0 logs
+    del init
+
+
+def test_train_loop_contract_single_process():
+    """utils/training.py:89-235: skip of over-large batches, accumulation, hooks, logging tags."""
+    torch.manual_seed(0)
+    model = TinyFlowNet()
+    opt = torch.optim.SGD(model.parameters(), lr=0.01)
+    sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0)
+    log, calls = Log(), []
+    batch = _batch(B=2, n=200)
+    big = _batch(B=2, n=5000, seed=9)
+    steps = tr.train(model, 'cpu', [batch, big, batch, batch, batch], opt, 2, sched, log,
+                     OracleEvaluator(), accumulation_steps=2, hooks={'h': lambda s, n: calls.append((s, n))},
+                     max_events_per_batch=3000)
+    assert steps == 2 and calls == [(1, 4), (2, 8)]
+    tags = {t for t, _, _ in log.rows}
+    assert 'General/Train loss' in tags and 'Train/photometric loss/32x32' in tags
+    assert 'Train/smoothness loss/4x4' in tags and 'General/learning rate/0' in tags
+    v = tr.validate(model, 'cpu', [batch], 8, log, OracleEvaluator())
+    assert v > 0 and any(t == 'General/Validation loss' for t, _, _ in log.rows)
