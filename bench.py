@@ -33,6 +33,9 @@ CFG = {
     'cfg4': dict(B=16, H=480, W=640, n=1_048_576, T=0.1),
 }
 HEADLINE = 'cfg2'
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the scatter kernel, from the committed
+# `ncu --set full` capture (profiles/r01_ncu_full_v1_summary.csv)
+TRAFFIC = {'cfg2': 46.15e6}
 
 
 def peaks():
@@ -161,25 +164,43 @@ def bench_encoder(name, K, W, dev, seed_off=0):
                L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, B, He, We, L.ptr(out),
                L.ptr(ws), L.ptr(status), sp)
 
+    def whole():
+        L.call('dvsof_encode_event_image', L.ptr(ev['x']), L.ptr(ev['y']), L.ptr(ev['timestamp']),
+               L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, L.ptr(ts), B, He, We, L.ptr(out),
+               L.ptr(ws), L.ptr(status), sp)
+
+    E = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    # (1) the step: one library call = prepare (zero + per-sample dt) -> scatter, PDL-chained
+    for _ in range(W):
+        flush(); whole()
+    torch.cuda.synchronize()
+    marks = [(E(), E()) for _ in range(K)]
+    for e0, e1 in marks:
+        flush()
+        e0.record(); whole(); e1.record()
+    torch.cuda.synchronize()
+    step_ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in marks]))
+    # (2) the dominant kernel alone (events on the launching stream around the scatter launch)
     for _ in range(W):
         flush(); prepare(); scatter()
     torch.cuda.synchronize()
-    E = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    marks = [(E(), E(), E()) for _ in range(K)]
-    for e0, k0, k1 in marks:
-        flush()
-        e0.record(); prepare(); k0.record(); scatter(); k1.record()
+    marks = [(E(), E()) for _ in range(K)]
+    for k0, k1 in marks:
+        flush(); prepare()
+        k0.record(); scatter(); k1.record()
     torch.cuda.synchronize()
     assert int(status.item()) == 0, 'encoder flagged invalid input'
     assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved'
-    step_ms = float(np.mean([e0.elapsed_time(k1) for e0, _, k1 in marks]))
-    kern_ms = float(np.mean([k0.elapsed_time(k1) for _, k0, k1 in marks]))
+    kern_ms = float(np.mean([k0.elapsed_time(k1) for k0, k1 in marks]))
     return dict(workload=name, events=N, step_ms=step_ms, kernel_ms=kern_ms,
                 bytes=encoder_bytes(B, He, We, N), launches_per_step=2)
 
 
 def bench_loss(name, K, W, dev):
+    """fwd+bwd of the multiscale loss the way the train loop calls it
+    (training.combined_loss -> Losses.terms -> one library call; loss.backward() -> one call)."""
     import dvs_of_training_framework_b200 as dv
+    from dvs_of_training_framework_b200 import training as tr
     from tests.helpers import synth_loss_inputs
     c = CFG[name]
     B, H, Wd = c['B'], c['H'], c['W']
@@ -187,50 +208,149 @@ def bench_loss(name, K, W, dev):
     flows = [f.requires_grad_() for f in inp['flows']]
     ev = dv.Losses(inp['shapes'], B, dev)
     flush = L2Flusher(dev)
-    wts = (0.5, 1.0, 1.0)
 
     def step():
         for f in flows:
             f.grad = None
-        terms = ev(flows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'],
-                   inp['sample_idx'])
-        loss = sum(w * sum(t) / len(t) for w, t in zip(wts, terms))   # utils/training.py:12-24
+        loss, _ = tr.combined_loss(ev, flows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                   inp['timestamps'], inp['sample_idx'], None, weights=[0.5, 1, 1])
         loss.backward()
         return loss
 
     ms = time_steps(step, K, W, flush)
     step_ms = float(np.mean(ms))
+    # kernel level: the fused forward (all scales, ready-made pyramid) and backward launches alone
+    L = dv._lib
+    from dvs_of_training_framework_b200.loss import _scale_struct, interpolate
+    fl = [f.detach() for f in flows]
+    levels, cur = [], inp['images'].view(2 * B, H, Wd)
+    for f in fl:
+        cur = interpolate(cur, f.shape[-2:])
+        levels.append(cur)
+    grads = [torch.empty_like(f) for f in fl]
+    sc = _scale_struct(fl, levels, grads)
+    S = len(fl)
+    ws = torch.empty(L.load().dvsof_loss_workspace_bytes(sc), dtype=torch.uint8, device=dev)
+    terms = torch.empty(3 * S, device=dev)
+    n_bad = torch.empty(S * B, dtype=torch.int32, device=dev)
+    match = torch.cat((torch.arange(0, 2 * B, 2), torch.arange(1, 2 * B, 2))).to(torch.int32).to(dev)
+    gt = torch.tensor([0.5 / S] * S + [1.0 / S] * S + [1.0 / S] * S, device=dev)
+    sp = L.stream_ptr(dev)
+    fwd = lambda: L.call('dvsof_warp_loss_forward', sc, L.ptr(match), L.ptr(terms), L.ptr(n_bad), L.ptr(ws), sp)  # noqa: E731
+    bwd = lambda: L.call('dvsof_warp_loss_backward', sc, L.ptr(match), L.ptr(gt), L.ptr(n_bad), sp)  # noqa: E731
+    fwd_ms = float(np.mean(time_steps(fwd, K, W, flush)))
+    bwd_ms = float(np.mean(time_steps(bwd, K, W, flush)))
+    px = sum(B * f.shape[-2] * f.shape[-1] for f in fl)
     return dict(workload=name, samples=B, step_ms=step_ms, bytes=loss_bytes(B, H, Wd),
-                launches_per_step=8)
+                fwd_ms=fwd_ms, bwd_ms=bwd_ms, fwd_bytes=16 * px, bwd_bytes=24 * px, launches_per_step=7)
 
 
-def bench_e2e(name, K, W, dev):
-    """Public API, host buffers: H2D of the event arrays from pinned memory, encode, D2H of the
-    event image into pinned memory -- all inside the timed region."""
+def make_train_batch(B, H, W, n, T, seed):
+    """A collated batch (utils/dataset.py:961-1020 layout) in pinned host memory."""
+    ev, ts, sidx = fast_events(seed, B, H, W, n, T, 'cpu')
+    ev['element_index'] = torch.zeros_like(ev['x'])
+    g = torch.Generator().manual_seed(seed)
+    images = torch.randint(0, 256, (2 * B, 1, H, W), generator=g).float()
+    pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
+    return {'events': {k: pin(v) for k, v in ev.items()}, 'timestamps': pin(ts), 'sample_idx': pin(sidx),
+            'images': pin(images), 'augmentation_params': None, 'size': B}
+
+
+def bench_train_step(K, W, dev, world, per_gpu=32):
+    """EV-FlowNet data-parallel training step (BASELINE configs[4] shapes: 256x256, 131072
+    events/sample; `per_gpu` samples per GPU => global batch 256 at 8 GPUs): H2D of the shard,
+    encode, cuDNN forward, fused loss, backward with overlapped NCCL allreduce, AdamW step."""
+    import torch.distributed as dist
+    import dvs_of_training_framework_b200 as dv
+    from dvs_of_training_framework_b200 import training as tr
+    from dvs_of_training_framework_b200.evflownet import Model
+    c = CFG['cfg2']
+    rank = dist.get_rank() if world > 1 else 0
+    torch.manual_seed(0)
+    model = Model(dev).to(memory_format=torch.channels_last)
+    red = tr.GradientAllreducer(model.parameters())
+    red.broadcast_parameters(model)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)      # train_flownet.py:59-61
+    evaluator = dv.init_losses((c['H'], c['W']), per_gpu, model, dev, 1)
+    batch = make_train_batch(per_gpu, c['H'], c['W'], c['n'], c['T'], 1234 + 5 + rank)
+    timers = dv.timer.FakeTimer()
+    model.train()
+
+    def step():
+        loss, _, _ = tr.process_minibatch(model, batch, timers, dev, True, evaluator, [0.5, 1, 1])
+        loss.backward()
+        red.wait()
+        opt.step()
+        red.zero_grad()
+        return loss
+
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        loss = step()
+    e1.record()
+    torch.cuda.synchronize()
+    assert torch.isfinite(loss).item(), 'train step produced a non-finite loss'
+    return dict(samples=per_gpu, step_ms=e0.elapsed_time(e1) / K, params=sum(p.numel() for p in model.parameters()))
+
+
+def bench_e2e(name, K, W, dev, compact=False):
+    """Public API, host buffers.  Every step: H2D of that step's event arrays from pinned host
+    memory, `dv.quantize` (the reference-facing call), D2H of the event image into pinned memory
+    -- all inside the timed region.  Steps alternate between two CUDA streams (user-level double
+    buffering) so step k's D2H overlaps step k+1's H2D on the full-duplex link; a step's pinned
+    output is only reused after its own D2H has completed.
+    compact=True: the storage-form entry (utils/dataset.py:286-289 int16/bool/fp32, 9 B/event)."""
     import dvs_of_training_framework_b200 as dv
     c = CFG[name]
     B, H, Wd, n = c['B'], c['H'], c['W'], c['n']
     ev, ts, sidx = fast_events(1234 + int(name[3:]), B, H, Wd, n, c['T'], dev)
-    host = {k: v.cpu().pin_memory() for k, v in ev.items()}
+    if compact:
+        host = {'x': ev['x'].to(torch.int16), 'y': ev['y'].to(torch.int16), 'timestamp': ev['timestamp'],
+                'polarity': (ev['polarity'] > 0), 'eps': torch.full((B,), n, dtype=torch.int64, device=dev)}
+    else:
+        host = {k: v for k, v in ev.items()}
+    host = {k: v.cpu().pin_memory() for k, v in host.items()}
     ts_h, sidx_h = ts.cpu().pin_memory(), sidx.cpu().pin_memory()
     He, We = dv.extend_size((H, Wd))
-    out_h = torch.empty((B, 4, He, We), dtype=torch.float32).pin_memory()
+    outs = [torch.empty((B, 4, He, We), dtype=torch.float32).pin_memory() for _ in range(2)]
     h2d = sum(v.numel() * v.element_size() for v in host.values()) + ts_h.numel() * 4 + sidx_h.numel() * 8
-    d2h = out_h.numel() * 4
+    d2h = outs[0].numel() * 4
+    streams = [torch.cuda.Stream(dev) for _ in range(2)]
+    done = [None, None]
 
-    def step():
-        d = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-        img = dv.quantize(d, ts_h.to(dev, non_blocking=True), sidx_h.to(dev, non_blocking=True), (H, Wd))
-        out_h.copy_(img, non_blocking=True)
-        torch.cuda.synchronize()
+    def step(i):
+        k = i & 1
+        if done[k] is not None:
+            done[k].synchronize()          # the pinned output of step i-2 has landed
+        with torch.cuda.stream(streams[k]):
+            d = {kk: v.to(dev, non_blocking=True) for kk, v in host.items()}
+            t_d = ts_h.to(dev, non_blocking=True)
+            if compact:
+                img = dv.compute_event_image_compact(d['x'], d['y'], d['timestamp'], d['polarity'],
+                                                     d['eps'], t_d, (He, We))
+            else:
+                img = dv.quantize(d, t_d, sidx_h.to(dev, non_blocking=True), (H, Wd))
+            outs[k].copy_(img, non_blocking=True)
+            done[k] = torch.cuda.Event()
+            done[k].record()
 
-    for _ in range(W):
-        step()
+    for i in range(2 * ((W + 1) // 2)):
+        step(i)
+    torch.cuda.synchronize()
     t0 = time.perf_counter()
-    for _ in range(K):
-        step()
+    for i in range(K):
+        step(i)
+    torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / K
-    assert int(out_h[:, :2].sum(dtype=torch.float64)) == B * n
+    for o in outs[:min(K, 2)]:
+        assert int(o[:, :2].sum(dtype=torch.float64)) == B * n
     return dict(events=B * n, step_s=dt, h2d=h2d, d2h=d2h)
 
 
@@ -339,6 +459,14 @@ def main():
     loss_ms = max_over_ranks(loss['step_ms'])
     e2e = bench_e2e(HEADLINE, max(3, K // 5), 3, dev)
     e2e_s = max_over_ranks(e2e['step_s'])
+    e2e_c = bench_e2e(HEADLINE, max(3, K // 5), 3, dev, compact=True)
+    e2e_c_s = max_over_ranks(e2e_c['step_s'])
+    sync_all()
+    train = None
+    if not args.quick:
+        train = bench_train_step(max(3, min(K, 10)), 3, dev, world)
+        train['step_ms'] = max_over_ranks(train['step_ms'])
+        torch.cuda.empty_cache()
     sync_all()
     extra = {}
     if not args.quick:
@@ -372,24 +500,40 @@ def main():
                    'parallelism': f'replicas x{world} (sharded by sample, no data-path collective)'},
         'clocks': clocks,
         'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': None, 'kernel': 'encode_vec4_kernel',
+                     'frac': achieved / peak, 'traffic': TRAFFIC.get(HEADLINE), 'kernel': 'encode_vec4_kernel',
                      'kernel_ms': kern_ms, 'algorithmic_bytes': head['bytes'], 'peak_source': peak_src},
         'e2e': {'value': world * e2e['events'] / e2e_s / 1e6, 'unit': 'Mevents/s',
                 'h2d_bytes_per_step': e2e['h2d'], 'd2h_bytes_per_step': e2e['d2h'],
-                'api': 'dv.quantize(events, timestamps, sample_idx, imsize) from pinned host tensors'},
+                'api': 'dv.quantize(events, timestamps, sample_idx, imsize) from pinned host tensors; '
+                       'two streams, step k D2H overlaps step k+1 H2D',
+                'compact_storage_form': {'value': world * e2e_c['events'] / e2e_c_s / 1e6, 'unit': 'Mevents/s',
+                                         'h2d_bytes_per_step': e2e_c['h2d'], 'd2h_bytes_per_step': e2e_c['d2h'],
+                                         'api': 'dv.compute_event_image_compact (int16/bool/fp32 storage form, 9 B/event)'}},
         'gpu_launches': K * head['launches_per_step'],
         'warp_loss': {'metric': 'warp-loss fwd+bwd samples/s', 'value': world * loss['samples'] / (loss_ms * 1e-3),
                       'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
                       'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
                                    'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
-                                   'note': 'whole API step (8 kernels + autograd glue), not a single kernel'}},
+                                   'note': 'whole API step (combined_loss + backward: 7 launches + autograd glue)'},
+                      'kernels': {'fwd_ms': loss['fwd_ms'], 'bwd_ms': loss['bwd_ms'],
+                                  'fwd_hbm_frac': loss['fwd_bytes'] / (loss['fwd_ms'] * 1e-3) / 1e9 / peak,
+                                  'bwd_hbm_frac': loss['bwd_bytes'] / (loss['bwd_ms'] * 1e-3) / 1e9 / peak}},
         'workloads': {},
     }
+    if train is not None:
+        line['train_step'] = {'metric': 'train-step samples/s', 'value': world * train['samples'] / (train['step_ms'] * 1e-3),
+                              'unit': 'samples/s', 'ms_per_step': train['step_ms'],
+                              'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN), 256x256, 131072 events/sample, '
+                                          f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad), '
+                                          'H2D of the batch inside the step; flat-bucket NCCL allreduce overlapped with backward'}
     for name, r in extra.items():
         if name.endswith('_loss'):
             line['workloads'][name] = {'samples_per_s': world * r['samples'] / (r['step_ms'] * 1e-3),
                                        'ms_per_step': r['step_ms'],
-                                       'hbm_frac_step': r['bytes'] / (r['step_ms'] * 1e-3) / 1e9 / peak}
+                                       'hbm_frac_step': r['bytes'] / (r['step_ms'] * 1e-3) / 1e9 / peak,
+                                       'fwd_kernel_ms': r['fwd_ms'], 'bwd_kernel_ms': r['bwd_ms'],
+                                       'fwd_kernel_hbm_frac': r['fwd_bytes'] / (r['fwd_ms'] * 1e-3) / 1e9 / peak,
+                                       'bwd_kernel_hbm_frac': r['bwd_bytes'] / (r['bwd_ms'] * 1e-3) / 1e9 / peak}
         else:
             line['workloads'][name] = {'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6,
                                        'ms_per_step': r['step_ms'], 'kernel_ms': r['kernel_ms'],

@@ -86,7 +86,12 @@ __device__ __forceinline__ Warp warp_sample(const float* __restrict__ img, int H
             if (x1ok) se = __ldg(row + xi + 1);
         }
     }
-    r.val = nw * (ey * ex) + ne * (ey * wx) + sw * (wy * ex) + se * (wy * wx);
+    // same operation order as ATen's CPU grid_sampler (weights s*e, s*w, n*e, n*w; products
+    // summed left to right, no FMA contraction): where warped ~= prev the Charbonnier derivative
+    // amplifies a 1-ulp difference of `val` by ~1e3, so the interpolation is kept bit-compatible
+    r.val = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(nw, __fmul_rn(ey, ex)), __fmul_rn(ne, __fmul_rn(ey, wx))),
+                                __fmul_rn(sw, __fmul_rn(wy, ex))),
+                      __fmul_rn(se, __fmul_rn(wy, wx)));
     r.ddx = (ne - nw) * ey + (se - sw) * wy;
     r.ddy = (sw - nw) * ex + (se - ne) * wx;
     return r;
@@ -143,8 +148,9 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
 
 // ------------------------------ forward ------------------------------------------------
 // record: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
+constexpr int kMaxPairs = 256;     // (scale, prediction) pairs reduced per finalize pass
 __device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, double (*wacc)[6]);
+                               int32_t* n_bad, double (*pair_acc)[6]);
 
 __global__ void __launch_bounds__(kLossThreads)
 warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
@@ -152,7 +158,7 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
                      int32_t* __restrict__ n_bad) {
     __shared__ float F[2][kTile + 1][kTile + 2];
     __shared__ float red[kLossThreads / 32][kRec];
-    __shared__ double wacc[kLossThreads / 32][6];
+    __shared__ double wacc[kMaxPairs][6];
     __shared__ bool is_last;
     pdl_launch_dependents();
     pdl_wait();                       // pyramid levels + match_idx come from the preceding kernels
@@ -160,12 +166,14 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     const int H = tab.H[tc.s], W = tab.W[tc.s], P = tab.n_pred;
     const size_t plane = (size_t)H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-    for (int i = threadIdx.x; i < 2 * (kTile + 1) * (kTile + 1); i += kLossThreads) {
-        const int ch = i / ((kTile + 1) * (kTile + 1));
-        const int rem = i - ch * (kTile + 1) * (kTile + 1);
-        const int ly = rem / (kTile + 1), lx = rem - ly * (kTile + 1);
-        const int y = tc.y0 + ly, x = tc.x0 + lx;
-        F[ch][ly][lx] = (y < H && x < W) ? __ldg(flow + ch * plane + (size_t)y * W + x) : 0.f;
+    for (int r = threadIdx.x >> 5; r < 2 * (kTile + 1); r += kLossThreads / 32) {   // row per warp
+        const int ch = r / (kTile + 1), ly = r - ch * (kTile + 1);
+        const int y = tc.y0 + ly;
+        const float* row = flow + ch * plane + (size_t)y * W;
+        for (int lx = threadIdx.x & 31; lx < kTile + 1; lx += 32) {
+            const int x = tc.x0 + lx;
+            F[ch][ly][lx] = (y < H && x < W) ? __ldg(row + x) : 0.f;
+        }
     }
     __syncthreads();
     const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
@@ -220,17 +228,19 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     if (threadIdx.x == 0) *ticket = 0u;   // self-resetting for the next call on this workspace
 }
 
-// run by ONE CTA (kLossThreads threads): warp w sums the records of (scale, prediction) pairs
-// w, w+8, ... in a fixed order in fp64; thread 0 then combines per scale.
+// run by ONE CTA (kLossThreads threads): warp w sums the tile records of the (scale, prediction)
+// pairs w, w+8, ... (all scales in flight at once: one round of loads, one barrier) in a fixed
+// order in fp64; thread s then combines scale s.
 __device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, double (*wacc)[6]) {
+                               int32_t* n_bad, double (*pair_acc)[6]) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int P = tab.n_pred, S = tab.n_scales;
-    for (int s = 0; s < S; ++s) {
-        const int H = tab.H[s], W = tab.W[s];
-        const int per = tab.tiles_x[s] * tab.tiles_y[s];
-        double tot[6] = {0, 0, 0, 0, 0, 0};   // photo, h, v, d_a, d_b, outborder
-        for (int n = warp; n < P; n += kLossThreads / 32) {
+    double tot[6] = {0, 0, 0, 0, 0, 0};            // thread s < S: running totals of scale s
+    for (int p0 = 0; p0 < P; p0 += kMaxPairs / DVSOF_MAX_SCALES) {
+        const int pn = min(P - p0, kMaxPairs / DVSOF_MAX_SCALES);
+        for (int q = warp; q < S * pn; q += kLossThreads / 32) {
+            const int s = q / pn, n = p0 + (q - s * pn);
+            const int per = tab.tiles_x[s] * tab.tiles_y[s];
             double a[7] = {0, 0, 0, 0, 0, 0, 0};
             const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
             for (int t = lane; t < per; t += 32) {
@@ -243,55 +253,64 @@ __device__ void finalize_terms(const ScaleTable& tab, const float* partials, flo
             for (int k = 0; k < 7; ++k)
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-            for (int k = 0; k < 5; ++k) tot[k] += a[k];
-            const double nb = a[6];
-            if (nb > 0) tot[5] += a[5] / (2.0 * nb * (double)P);               // loss.py:99-113
-            if (lane == 0) n_bad[s * P + n] = (int32_t)nb;
-        }
-        if (lane == 0)
-            for (int k = 0; k < 6; ++k) wacc[warp][k] = tot[k];
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            double t[6] = {0, 0, 0, 0, 0, 0};
-            for (int w = 0; w < kLossThreads / 32; ++w)
-                for (int k = 0; k < 6; ++k) t[k] += wacc[w][k];
-            const double N2 = 2.0 * P;
-            const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
-            double sm = 0;
-            if (ch > 0) sm += t[1] / ch;
-            if (cv > 0) sm += t[2] / cv;
-            if (cd > 0) sm += (t[3] + t[4]) / cd;
-            terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
-            terms[S + s] = (float)(t[0] / ((double)P * H * W));                  // loss.py:33
-            terms[2 * S + s] = (float)t[5];
+            if (lane == 0) {
+                const double nb = a[6];
+                for (int k = 0; k < 5; ++k) pair_acc[q][k] = a[k];
+                pair_acc[q][5] = nb > 0 ? a[5] / (2.0 * nb * (double)P) : 0.0;   // loss.py:99-113
+                n_bad[s * P + n] = (int32_t)nb;
+            }
         }
         __syncthreads();
+        if ((int)threadIdx.x < S)
+            for (int j = 0; j < pn; ++j)
+                for (int k = 0; k < 6; ++k) tot[k] += pair_acc[threadIdx.x * pn + j][k];
+        __syncthreads();
+    }
+    if ((int)threadIdx.x < S) {
+        const int s = threadIdx.x, H = tab.H[s], W = tab.W[s];
+        const double N2 = 2.0 * P;
+        const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
+        double sm = 0;
+        if (ch > 0) sm += tot[1] / ch;
+        if (cv > 0) sm += tot[2] / cv;
+        if (cd > 0) sm += (tot[3] + tot[4]) / cd;
+        terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
+        terms[S + s] = (float)(tot[0] / ((double)P * H * W));                // loss.py:33
+        terms[2 * S + s] = (float)tot[5];
     }
 }
 
 // ------------------------------ backward -----------------------------------------------
 // d(terms)/d(flow), contracted with grad_terms.  Every pixel gathers its own gradient (no
-// atomics): photometric via the bilinear tap differences, out-of-border via c'(flow)/(2 n_i N),
-// smoothness from the 8 neighbour differences it takes part in.
+// atomics, one write): photometric via the bilinear tap differences, out-of-border via
+// c'(flow)/(2 n_i N), smoothness from the 8 neighbour pairs it belongs to.  Each neighbour pair
+// is owned by the top-left pixel ("cell") of its 2x2 block, its Charbonnier derivative is
+// evaluated ONCE (4 pairs x 2 channels per cell) into shared memory and read by both ends:
+// 9 instead of 17 lg2/ex2 pairs per pixel -- the kernel is SFU/issue bound, not HBM bound.
+constexpr int kCell = kTile + 1;   // cells (x0-1 .. x0+31) x (y0-1 .. y0+31)
+
 __global__ void __launch_bounds__(kLossThreads)
 warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
                      const float* __restrict__ grad_terms, const int32_t* __restrict__ n_bad) {
-    __shared__ float F[2][kTile + 2][kTile + 3];   // halo of 1 on every side; F[.][ly+1][lx+1]
+    __shared__ float F[2][kTile + 2][kTile + 3];   // flow, halo of 1: F[.][ly+1][lx+1]
+    __shared__ float G[2][4][kCell][kCell + 1];    // pair gradients [ch][h,v,da,db][cy+1][cx+1]
     const TileCoord tc = decode_cta(tab);
     const int S = tab.n_scales, P = tab.n_pred;
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const size_t plane = (size_t)H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     float* grad = tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane;
-    for (int i = threadIdx.x; i < 2 * (kTile + 2) * (kTile + 2); i += kLossThreads) {
-        const int ch = i / ((kTile + 2) * (kTile + 2));
-        const int rem = i - ch * (kTile + 2) * (kTile + 2);
-        const int ly = rem / (kTile + 2), lx = rem - ly * (kTile + 2);
-        const int y = tc.y0 + ly - 1, x = tc.x0 + lx - 1;
-        F[ch][ly][lx] = (y >= 0 && y < H && x >= 0 && x < W)
-                            ? __ldg(flow + ch * plane + (size_t)y * W + x) : 0.f;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    // flow tile + halo: one row per warp iteration, coalesced
+    for (int r = wrp; r < 2 * (kTile + 2); r += kLossThreads / 32) {
+        const int ch = r / (kTile + 2), ly = r - ch * (kTile + 2);
+        const int y = tc.y0 + ly - 1;
+        const float* row = flow + ch * plane + (size_t)y * W;
+        for (int lx = lane; lx < kTile + 2; lx += 32) {
+            const int x = tc.x0 + lx - 1;
+            F[ch][ly][lx] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(row + x) : 0.f;
+        }
     }
-    __syncthreads();
     const float g_sm = grad_terms[tc.s], g_ph = grad_terms[S + tc.s], g_ob = grad_terms[2 * S + tc.s];
     const float N2 = 2.f * (float)P;
     const float ch_n = N2 * (float)H * (float)(W - 1), cv_n = N2 * (float)(H - 1) * (float)W;
@@ -299,16 +318,34 @@ warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     const float k_h = ch_n > 0.f ? 0.25f * g_sm / ch_n : 0.f;
     const float k_v = cv_n > 0.f ? 0.25f * g_sm / cv_n : 0.f;
     const float k_d = cd_n > 0.f ? 0.25f * g_sm / cd_n : 0.f;
+    __syncthreads();
+    // pair gradients of the 33x33 cells: cell (cx,cy) = pixel (x0-1+cx, y0-1+cy)
+    for (int i = threadIdx.x; i < kCell * kCell; i += kLossThreads) {
+        const int cy = i / kCell, cx = i - cy * kCell;
+        const int x = tc.x0 - 1 + cx, y = tc.y0 - 1 + cy;
+        const bool in = x >= 0 && y >= 0 && x < W && y < H;
+        const bool R = in && x + 1 < W, Dn = in && y + 1 < H;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            const float f = F[ch][cy][cx], fr = F[ch][cy][cx + 1];
+            const float fd = F[ch][cy + 1][cx], fdr = F[ch][cy + 1][cx + 1];
+            G[ch][0][cy][cx] = R ? k_h * charb_grad(fr - f) : 0.f;
+            G[ch][1][cy][cx] = Dn ? k_v * charb_grad(fd - f) : 0.f;
+            G[ch][2][cy][cx] = (R && Dn) ? k_d * charb_grad(fdr - f) : 0.f;
+            G[ch][3][cy][cx] = (R && Dn) ? k_d * charb_grad(fr - fd) : 0.f;
+        }
+    }
     const float k_ph = g_ph / ((float)P * (float)H * (float)W);
     const int nb = n_bad[tc.s * P + tc.n];
     const float k_ob = nb > 0 ? g_ob / (2.f * (float)nb * (float)P) : 0.f;
     const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
     const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
-    const int lx = (threadIdx.x & 31) + 1, lyb = threadIdx.x >> 5;
-    const int x = tc.x0 + lx - 1;
+    __syncthreads();
+    const int lx = lane + 1;
+    const int x = tc.x0 + lane;
 #pragma unroll
     for (int r = 0; r < kTile / 8; ++r) {
-        const int ly = lyb + 8 * r + 1, y = tc.y0 + ly - 1;
+        const int ly = wrp + 8 * r + 1, y = tc.y0 + ly - 1;
         if (y >= H || x >= W) continue;
         const float u = F[0][ly][lx], v = F[1][ly][lx];
         const Warp wp = warp_sample(next, H, W, x, y, u, v);
@@ -318,19 +355,13 @@ warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
             g[0] += k_ob * charb_grad(u);
             g[1] += k_ob * charb_grad(v);
         }
-        const bool L = x > 0, R = x + 1 < W, U = y > 0, Dn = y + 1 < H;
+        // own cell = (lx, ly) in G coordinates; left = lx-1, up = ly-1
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
-            const float f = F[ch][ly][lx];
-            float a = 0.f;
-            if (L) a += k_h * charb_grad(f - F[ch][ly][lx - 1]);
-            if (R) a -= k_h * charb_grad(F[ch][ly][lx + 1] - f);
-            if (U) a += k_v * charb_grad(f - F[ch][ly - 1][lx]);
-            if (Dn) a -= k_v * charb_grad(F[ch][ly + 1][lx] - f);
-            if (U && L) a += k_d * charb_grad(f - F[ch][ly - 1][lx - 1]);
-            if (Dn && R) a -= k_d * charb_grad(F[ch][ly + 1][lx + 1] - f);
-            if (Dn && L) a += k_d * charb_grad(f - F[ch][ly + 1][lx - 1]);
-            if (U && R) a -= k_d * charb_grad(F[ch][ly - 1][lx + 1] - f);
+            float a = G[ch][0][ly][lx - 1] - G[ch][0][ly][lx];         // horizontal pairs
+            a += G[ch][1][ly - 1][lx] - G[ch][1][ly][lx];              // vertical
+            a += G[ch][2][ly - 1][lx - 1] - G[ch][2][ly][lx];          // diagonal "\"
+            a += G[ch][3][ly][lx - 1] - G[ch][3][ly - 1][lx];          // diagonal "/"
             g[ch] += a;
         }
         grad[(size_t)y * W + x] = g[0];

@@ -1,0 +1,32 @@
+"""Experiment harness (GPU box): time the fused warp-loss step and its forward / backward
+kernels on the named configs (default cfg2 cfg3 cfg4); used under ncu for the loss profiles."""
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import bench  # noqa: E402
+import dvs_of_training_framework_b200 as dv  # noqa: E402
+
+
+def main():
+    dev = torch.device('cuda', 0)
+    dv._lib.Status.mode = 'deferred'
+    peak, _ = bench.peaks()
+    res = {}
+    for name in sys.argv[1:] or ['cfg2', 'cfg3', 'cfg4']:
+        r = bench.bench_loss(name, 5, 3, dev)
+        res[name] = {'step_ms': round(r['step_ms'], 4), 'fwd_ms': round(r['fwd_ms'], 4),
+                     'bwd_ms': round(r['bwd_ms'], 4),
+                     'fwd_GBs': round(r['fwd_bytes'] / r['fwd_ms'] / 1e6, 1),
+                     'bwd_GBs': round(r['bwd_bytes'] / r['bwd_ms'] / 1e6, 1),
+                     'fwd_frac': round(r['fwd_bytes'] / r['fwd_ms'] / 1e6 / peak, 4),
+                     'bwd_frac': round(r['bwd_bytes'] / r['bwd_ms'] / 1e6 / peak, 4)}
+        torch.cuda.empty_cache()
+    print(json.dumps(res))
+
+
+if __name__ == '__main__':
+    main()
