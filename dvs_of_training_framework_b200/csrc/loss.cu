@@ -10,6 +10,7 @@
 // grid is g = (pix + flow) / ((S-1)/2) - 1 with IEEE division (utils/loss.py:150-156), then
 // ix = (g + 1) * ((S-1)/2) as ATen's CPU grid_sampler does for align_corners=True.
 #include "common.cuh"
+#include "exact_div.h"
 
 namespace dvsof {
 
@@ -21,13 +22,23 @@ constexpr int kRec = 8;            // floats per CTA partial record
 
 // Charbonnier c(d) = (d^2 + eps^2)^alpha and c'(d) = 2 alpha d (d^2+eps^2)^(alpha-1).
 // lg2/ex2 on the SFU: relative error ~3e-7, inside the 1e-5 budget of the path.
+__device__ __forceinline__ float ex2_approx(float x) {   // MUFU.EX2 (arguments here are > -20: no denormals)
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float lg2_approx(float x) {   // MUFU.LG2 (arguments here are >= 1e-6: normal)
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ float charb(float d) {
     const float s = fmaf(d, d, kEps2);
-    return exp2f(kAlpha * __log2f(s));
+    return ex2_approx(kAlpha * lg2_approx(s));
 }
 __device__ __forceinline__ float charb_grad(float d) {
     const float s = fmaf(d, d, kEps2);
-    return 2.f * kAlpha * d * exp2f((kAlpha - 1.f) * __log2f(s));
+    return (2.f * kAlpha) * d * ex2_approx((kAlpha - 1.f) * lg2_approx(s));
 }
 
 struct ScaleTable {
@@ -35,6 +46,7 @@ struct ScaleTable {
     int H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
     int tiles_x[DVSOF_MAX_SCALES], tiles_y[DVSOF_MAX_SCALES];
     int cta_begin[DVSOF_MAX_SCALES + 1];
+    float rx[DVSOF_MAX_SCALES], ry[DVSOF_MAX_SCALES];   // RN(1/((W-1)/2)), RN(1/((H-1)/2)); 0 = plain division
     const float* flow[DVSOF_MAX_SCALES];
     const float* images[DVSOF_MAX_SCALES];
     float* grad_flow[DVSOF_MAX_SCALES];
@@ -55,46 +67,67 @@ __device__ __forceinline__ TileCoord decode_cta(const ScaleTable& tab) {
 // pixel (x,y) displaced by (u,v); also returns the normalised grid (for the border mask) and the
 // spatial derivatives of the sample.
 struct Warp { float val, ddx, ddy, gx, gy; };
-__device__ __forceinline__ Warp warp_sample(const float* __restrict__ img, int H, int W, int x,
-                                            int y, float u, float v) {
-    const float hx = (float)(W - 1) / 2.f, hy = (float)(H - 1) / 2.f;
+struct GridNorm { float hx, hy, rx, ry; };   // half extents (S-1)/2 and their correctly rounded reciprocals
+
+__device__ __forceinline__ Warp warp_sample(const float* __restrict__ img, int H, int W,
+                                            const GridNorm& gn, int x, int y, float u, float v,
+                                            bool valid = true) {
     Warp r;
-    r.gx = __fsub_rn(__fdiv_rn(__fadd_rn((float)x, u), hx), 1.f);    // utils/loss.py:150-156
-    r.gy = __fsub_rn(__fdiv_rn(__fadd_rn((float)y, v), hy), 1.f);
-    const float ix = __fmul_rn(__fadd_rn(r.gx, 1.f), hx);            // ATen CPU unnormalize
-    const float iy = __fmul_rn(__fadd_rn(r.gy, 1.f), hy);
+    r.gx = __fsub_rn(dvsof_div_by_const(__fadd_rn((float)x, u), gn.hx, gn.rx), 1.f);   // utils/loss.py:150-156
+    r.gy = __fsub_rn(dvsof_div_by_const(__fadd_rn((float)y, v), gn.hy, gn.ry), 1.f);
+    const float ix = __fmul_rn(__fadd_rn(r.gx, 1.f), gn.hx);            // ATen CPU unnormalize
+    const float iy = __fmul_rn(__fadd_rn(r.gy, 1.f), gn.hy);
     const float xw = floorf(ix), yn = floorf(iy);
     const float wx = ix - xw, wy = iy - yn;                          // weight of east / south
     const float ex = 1.f - wx, ey = 1.f - wy;
-    // taps outside the image contribute zero (padding_mode='zeros'); range test in float so
-    // huge / non-finite coordinates never reach an int conversion
-    const bool x0ok = xw >= 0.f && xw <= (float)(W - 1);
-    const bool x1ok = xw >= -1.f && xw <= (float)(W - 2);
-    const bool y0ok = yn >= 0.f && yn <= (float)(H - 1);
-    const bool y1ok = yn >= -1.f && yn <= (float)(H - 2);
-    float nw = 0.f, ne = 0.f, sw = 0.f, se = 0.f;
-    if (x0ok || x1ok) {
-        const int xi = (int)xw, yi = (int)yn;
-        if (y0ok) {
-            const float* row = img + (size_t)yi * W;
-            if (x0ok) nw = __ldg(row + xi);
-            if (x1ok) ne = __ldg(row + xi + 1);
-        }
-        if (y1ok) {
-            const float* row = img + (size_t)(yi + 1) * W;
-            if (x0ok) sw = __ldg(row + xi);
-            if (x1ok) se = __ldg(row + xi + 1);
-        }
-    }
-    // same operation order as ATen's CPU grid_sampler (weights s*e, s*w, n*e, n*w; products
-    // summed left to right, no FMA contraction): where warped ~= prev the Charbonnier derivative
-    // amplifies a 1-ulp difference of `val` by ~1e3, so the interpolation is kept bit-compatible
-    r.val = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(nw, __fmul_rn(ey, ex)), __fmul_rn(ne, __fmul_rn(ey, wx))),
-                                __fmul_rn(sw, __fmul_rn(wy, ex))),
-                      __fmul_rn(se, __fmul_rn(wy, wx)));
+    // clamp in float (huge / non-finite coordinates never reach the int conversion), then the
+    // four zero-padded taps with unsigned range tests; 32-bit offsets inside one image plane
+    const int xi = (int)fminf(fmaxf(xw, -2.f), (float)W);
+    const int yi = (int)fminf(fmaxf(yn, -2.f), (float)H);
+    const bool x0ok = (unsigned)xi < (unsigned)W, x1ok = (unsigned)(xi + 1) < (unsigned)W;
+    const bool y0ok = valid && (unsigned)yi < (unsigned)H, y1ok = valid && (unsigned)(yi + 1) < (unsigned)H;
+    const int o = yi * W + xi;
+    const float nw = (x0ok && y0ok) ? __ldg(img + o) : 0.f;
+    const float ne = (x1ok && y0ok) ? __ldg(img + o + 1) : 0.f;
+    const float sw = (x0ok && y1ok) ? __ldg(img + o + W) : 0.f;
+    const float se = (x1ok && y1ok) ? __ldg(img + o + W + 1) : 0.f;
+    // same operations as ATen's vectorised CPU grid_sampler (weights s*e, s*w, n*e, n*w; the sum
+    // nw*w0 + ne*w1 + sw*w2 + se*w3 is compiled there to mul + 3 chained FMAs -- pinned by
+    // tests/test_oracle_golden.py::test_aten_bilinear_operation_order).  Where warped ~= prev the
+    // Charbonnier derivative amplifies a 1-ulp difference of `val` ~1e3 times, so the
+    // interpolation is kept bit-compatible with the reference's CPU path.
+    r.val = __fmaf_rn(se, __fmul_rn(wy, wx),
+                      __fmaf_rn(sw, __fmul_rn(wy, ex),
+                                __fmaf_rn(ne, __fmul_rn(ey, wx), __fmul_rn(nw, __fmul_rn(ey, ex)))));
     r.ddx = (ne - nw) * ey + (se - sw) * wy;
     r.ddy = (sw - nw) * ex + (se - ne) * wx;
     return r;
+}
+
+// sum K per-thread values over the warp with the halving butterfly: 4+2+1+1+1 = 9 shuffles for
+// K = 7 instead of 35.  Afterwards lane l (l & 3 == 0) holds the total of value index
+// ((l >> 4) & 1) * 4 + ((l >> 3) & 1) * 2 + ((l >> 2) & 1) in v[0].
+__device__ __forceinline__ void warp_sum8(float (&v)[8], int lane) {
+    const bool up16 = lane & 16, up8 = lane & 8, up4 = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const float send = up16 ? v[i] : v[i + 4];
+        const float keep = up16 ? v[i + 4] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const float send = up8 ? v[i] : v[i + 2];
+        const float keep = up8 ? v[i + 2] : v[i];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    {
+        const float send = up4 ? v[0] : v[1];
+        const float keep = up4 ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    }
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 2);
+    v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
 // ------------------------------ timestamp matching -------------------------------------
@@ -142,7 +175,40 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
         const float* im = src + (size_t)d * Hin * Win;
         const float a = __ldg(im + (size_t)y0 * Win + x0), b = __ldg(im + (size_t)y0 * Win + x1);
         const float c = __ldg(im + (size_t)y1 * Win + x0), e = __ldg(im + (size_t)y1 * Win + x1);
-        dst[i] = hy * (hx * a + lx * b) + ly * (hx * c + lx * e);
+        // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair, one
+        // for the rows): bit-identical to the reference's F.interpolate on the upsampling levels of
+        // the chain (pinned on CPU by tests/test_oracle_golden.py::test_aten_upsample_operation_order)
+        const float top = __fmaf_rn(hx, a, __fmul_rn(lx, b)), bot = __fmaf_rn(hx, c, __fmul_rn(lx, e));
+        dst[i] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+    }
+}
+
+// Stage the 2-channel flow tile (EDGE x EDGE pixels starting HALO before the tile origin, zero
+// outside the image) into shared memory [2][EDGE][PITCH].  All global loads of a thread are
+// issued before its first shared store (fixed trip count, fully unrolled): one DRAM round trip
+// per CTA instead of one per row -- ncu showed the previous row-per-warp loop (load -> store ->
+// next load) holding 60 % of all stall samples.
+template <int EDGE, int PITCH, int HALO>
+__device__ __forceinline__ void stage_flow_tile(float* __restrict__ Fs, const float* __restrict__ flow,
+                                                size_t plane, int H, int W, int y0, int x0) {
+    constexpr int kElems = 2 * EDGE * EDGE;
+    constexpr int kIters = (kElems + kLossThreads - 1) / kLossThreads;
+    float v[kIters];
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) {
+        const int i = threadIdx.x + k * kLossThreads;
+        const int ch = i / (EDGE * EDGE), rem = i - ch * (EDGE * EDGE);
+        const int ly = rem / EDGE, lx = rem - ly * EDGE;
+        const int y = y0 + ly - HALO, x = x0 + lx - HALO;
+        const bool ok = i < kElems && y >= 0 && y < H && x >= 0 && x < W;
+        v[k] = ok ? __ldg(flow + ch * plane + y * W + x) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < kIters; ++k) {
+        const int i = threadIdx.x + k * kLossThreads;
+        const int ch = i / (EDGE * EDGE), rem = i - ch * (EDGE * EDGE);
+        const int ly = rem / EDGE, lx = rem - ly * EDGE;
+        if (i < kElems) Fs[(ch * EDGE + ly) * PITCH + lx] = v[k];
     }
 }
 
@@ -166,48 +232,47 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     const int H = tab.H[tc.s], W = tab.W[tc.s], P = tab.n_pred;
     const size_t plane = (size_t)H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-    for (int r = threadIdx.x >> 5; r < 2 * (kTile + 1); r += kLossThreads / 32) {   // row per warp
-        const int ch = r / (kTile + 1), ly = r - ch * (kTile + 1);
-        const int y = tc.y0 + ly;
-        const float* row = flow + ch * plane + (size_t)y * W;
-        for (int lx = threadIdx.x & 31; lx < kTile + 1; lx += 32) {
-            const int x = tc.x0 + lx;
-            F[ch][ly][lx] = (y < H && x < W) ? __ldg(row + x) : 0.f;
-        }
-    }
+    stage_flow_tile<kTile + 1, kTile + 2, 0>(&F[0][0][0], flow, plane, H, W, tc.y0, tc.x0);
     __syncthreads();
     const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
     const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
+    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
     const int lx = threadIdx.x & 31, lyb = threadIdx.x >> 5;
     const int x = tc.x0 + lx;
+    const float m_r = (x + 1 < W) ? 1.f : 0.f;            // pixel has a right neighbour
+    const int xc = min(x, W - 1);
+    // acc: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
     float acc[kRec] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // branch-free over the tile (off-image lanes/rows contribute through 0/1 masks, F is 0
+    // there): the four rows' loads and MUFU chains interleave freely
 #pragma unroll
     for (int r = 0; r < kTile / 8; ++r) {
         const int ly = lyb + 8 * r, y = tc.y0 + ly;
-        if (y >= H || x >= W) continue;
+        const bool valid = (x < W) && (y < H);
+        const float m_v = valid ? 1.f : 0.f;
         const float u = F[0][ly][lx], v = F[1][ly][lx];
-        const Warp wp = warp_sample(next, H, W, x, y, u, v);
-        acc[0] += charb(wp.val - __ldg(prev + (size_t)y * W + x));         // loss.py:72-74
-        const bool right = x + 1 < W, down = y + 1 < H;
+        const Warp wp = warp_sample(next, H, W, gn, x, y, u, v, valid);
+        const float pv = __ldg(prev + min(y, H - 1) * W + xc);
+        acc[0] = fmaf(m_v, charb(wp.val - pv), acc[0]);                     // loss.py:72-74
+        const float m_d = (y + 1 < H) ? m_v : 0.f, m_rv = m_r * m_v, m_rd = m_r * m_d;
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {                                    // loss.py:76-90
-            const float f = F[ch][ly][lx];
-            if (right) acc[1] += charb(F[ch][ly][lx + 1] - f);
-            if (down) acc[2] += charb(F[ch][ly + 1][lx] - f);
-            if (right && down) {
-                acc[3] += charb(F[ch][ly + 1][lx + 1] - f);
-                acc[4] += charb(F[ch][ly][lx + 1] - F[ch][ly + 1][lx]);
-            }
+            const float f = F[ch][ly][lx], fr = F[ch][ly][lx + 1];
+            const float fd = F[ch][ly + 1][lx], fdr = F[ch][ly + 1][lx + 1];
+            acc[1] = fmaf(m_rv, charb(fr - f), acc[1]);
+            acc[2] = fmaf(m_d, charb(fd - f), acc[2]);
+            acc[3] = fmaf(m_rd, charb(fdr - f), acc[3]);
+            acc[4] = fmaf(m_rd, charb(fr - fd), acc[4]);
         }
-        if (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f) {   // loss.py:92-94
-            acc[5] += charb(u) + charb(v);
-            acc[6] += 1.f;
+        const bool bad = valid && (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f);   // loss.py:92-94
+        if (__any_sync(0xffffffffu, bad)) {                                 // warp-uniform, rare
+            const float m_b = bad ? 1.f : 0.f;
+            acc[5] = fmaf(m_b, charb(u) + charb(v), acc[5]);
+            acc[6] += m_b;
         }
     }
-#pragma unroll
-    for (int k = 0; k < 7; ++k) acc[k] = warp_sum(acc[k]);
-    if ((threadIdx.x & 31) == 0)
-        for (int k = 0; k < 7; ++k) red[threadIdx.x >> 5][k] = acc[k];
+    warp_sum8(acc, lx);
+    if ((lx & 3) == 0) red[lyb][((lx >> 4) & 1) * 4 + ((lx >> 3) & 1) * 2 + ((lx >> 2) & 1)] = acc[0];
     __syncthreads();
     if (threadIdx.x < 7) {
         float t = 0.f;
@@ -301,16 +366,7 @@ warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     float* grad = tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    // flow tile + halo: one row per warp iteration, coalesced
-    for (int r = wrp; r < 2 * (kTile + 2); r += kLossThreads / 32) {
-        const int ch = r / (kTile + 2), ly = r - ch * (kTile + 2);
-        const int y = tc.y0 + ly - 1;
-        const float* row = flow + ch * plane + (size_t)y * W;
-        for (int lx = lane; lx < kTile + 2; lx += 32) {
-            const int x = tc.x0 + lx - 1;
-            F[ch][ly][lx] = (y >= 0 && y < H && x >= 0 && x < W) ? __ldg(row + x) : 0.f;
-        }
-    }
+    stage_flow_tile<kTile + 2, kTile + 3, 1>(&F[0][0][0], flow, plane, H, W, tc.y0, tc.x0);
     const float g_sm = grad_terms[tc.s], g_ph = grad_terms[S + tc.s], g_ob = grad_terms[2 * S + tc.s];
     const float N2 = 2.f * (float)P;
     const float ch_n = N2 * (float)H * (float)(W - 1), cv_n = N2 * (float)(H - 1) * (float)W;
@@ -340,32 +396,38 @@ warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     const float k_ob = nb > 0 ? g_ob / (2.f * (float)nb * (float)P) : 0.f;
     const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
     const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
+    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
     __syncthreads();
     const int lx = lane + 1;
     const int x = tc.x0 + lane;
+    const int xc = min(x, W - 1);
 #pragma unroll
     for (int r = 0; r < kTile / 8; ++r) {
         const int ly = wrp + 8 * r + 1, y = tc.y0 + ly - 1;
-        if (y >= H || x >= W) continue;
+        const bool valid = (x < W) && (y < H);
         const float u = F[0][ly][lx], v = F[1][ly][lx];
-        const Warp wp = warp_sample(next, H, W, x, y, u, v);
-        const float cp = k_ph * charb_grad(wp.val - __ldg(prev + (size_t)y * W + x));
+        const Warp wp = warp_sample(next, H, W, gn, x, y, u, v, valid);
+        const float cp = k_ph * charb_grad(wp.val - __ldg(prev + min(y, H - 1) * W + xc));
         float g[2] = {cp * wp.ddx, cp * wp.ddy};
-        if (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f) {
-            g[0] += k_ob * charb_grad(u);
-            g[1] += k_ob * charb_grad(v);
+        const bool bad = valid && (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f);
+        if (__any_sync(0xffffffffu, bad)) {                                 // warp-uniform, rare
+            const float kb = bad ? k_ob : 0.f;
+            g[0] = fmaf(kb, charb_grad(u), g[0]);
+            g[1] = fmaf(kb, charb_grad(v), g[1]);
         }
         // own cell = (lx, ly) in G coordinates; left = lx-1, up = ly-1
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             float a = G[ch][0][ly][lx - 1] - G[ch][0][ly][lx];         // horizontal pairs
             a += G[ch][1][ly - 1][lx] - G[ch][1][ly][lx];              // vertical
-            a += G[ch][2][ly - 1][lx - 1] - G[ch][2][ly][lx];          // diagonal "\"
+            a += G[ch][2][ly - 1][lx - 1] - G[ch][2][ly][lx];          // diagonal "\\"
             a += G[ch][3][ly][lx - 1] - G[ch][3][ly - 1][lx];          // diagonal "/"
             g[ch] += a;
         }
-        grad[(size_t)y * W + x] = g[0];
-        grad[plane + (size_t)y * W + x] = g[1];
+        if (valid) {
+            grad[y * W + x] = g[0];
+            grad[plane + y * W + x] = g[1];
+        }
     }
 }
 
@@ -391,6 +453,10 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
         tab->W[s] = sc->W[s];
         tab->tiles_x[s] = (sc->W[s] + kTile - 1) / kTile;
         tab->tiles_y[s] = (sc->H[s] + kTile - 1) / kTile;
+        const float hx = (float)(sc->W[s] - 1) / 2.f, hy = (float)(sc->H[s] - 1) / 2.f;
+        // a 1-pixel side makes the reference divide by zero (NaN/inf grid); here: NaN grid as well
+        tab->rx[s] = dvsof_div_const_ok(hx) ? dvsof_recip_rn(hx) : NAN;
+        tab->ry[s] = dvsof_div_const_ok(hy) ? dvsof_recip_rn(hy) : NAN;
         tab->flow[s] = sc->flow[s];
         tab->images[s] = sc->images[s];
         tab->grad_flow[s] = sc->grad_flow[s];

@@ -25,4 +25,9 @@ ncu)
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'encode_v|encode_t' -c 3 -f -o $OUT/ncu_full_cfg3 \
       python scripts/exp_encoder.py cfg3 > $OUT/ncu_full_cfg3.log 2>&1
   ls -la $OUT;;
+loss)
+  timeout 600 python scripts/exp_loss.py cfg2 cfg3 cfg4 > $OUT/loss.json 2> $OUT/loss.err; cat $OUT/loss.json; tail -3 $OUT/loss.err;;
+lossncu)
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'warp_loss|resize|match' -c 14 -f -o $OUT/ncu_full_loss_cfg4 \
+      python scripts/exp_loss.py cfg4 > $OUT/ncu_full_loss_cfg4.log 2>&1; tail -2 $OUT/ncu_full_loss_cfg4.log;;
 esac; done

@@ -143,3 +143,69 @@ def test_torch_baseline_port_equals_numpy_oracle():
     a = eot.compute_event_image(ev, ts, sidx, (40, 56)).numpy()
     b = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (40, 56))
     assert np.array_equal(a, b)
+
+
+def test_aten_bilinear_operation_order():
+    """Pins the arithmetic the CUDA warp kernel copies (csrc/loss.cu warp_sample): ATen's CPU
+    grid_sample (the reference's F.grid_sample, utils/loss.py:70) evaluates
+    ix = (g + 1) * ((W-1)/2), weights (1-wy)(1-wx).., and the tap sum as mul + 3 chained FMAs.
+    Emulated in numpy (fp32 fma through float64) this must reproduce torch bit for bit."""
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    H, W = 64, 80
+    img = torch.randint(0, 256, (1, 1, H, W)).float()
+    flow = torch.randn(1, 2, H, W) * 3
+    grid = lo.normalised_grid(flow)
+    out = F.grid_sample(img, grid.permute(0, 2, 3, 1), mode='bilinear', padding_mode='zeros',
+                        align_corners=True)[0, 0].numpy()
+    f32 = np.float32
+    gx, gy = grid[0, 0].numpy(), grid[0, 1].numpy()
+    ix, iy = (gx + f32(1)) * f32((W - 1) / 2.), (gy + f32(1)) * f32((H - 1) / 2.)
+    xw, yn = np.floor(ix), np.floor(iy)
+    wx, wy = ix - xw, iy - yn
+    ex, ey = f32(1) - wx, f32(1) - wy
+    im = img[0, 0].numpy()
+
+    def tap(yy, xx):
+        ok = (yy >= 0) & (yy < H) & (xx >= 0) & (xx < W)
+        return np.where(ok, im[np.clip(yy, 0, H - 1).astype(int), np.clip(xx, 0, W - 1).astype(int)],
+                        f32(0)).astype(f32)
+
+    def fma(a, b, c):
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(f32)
+
+    nw, ne, sw, se = tap(yn, xw), tap(yn, xw + 1), tap(yn + 1, xw), tap(yn + 1, xw + 1)
+    val = fma(se, wy * wx, fma(sw, wy * ex, fma(ne, ey * wx, nw * (ey * ex))))
+    assert np.array_equal(val, out)
+
+
+def test_aten_upsample_operation_order():
+    """Pins the arithmetic csrc/loss.cu resize_bilinear_kernel copies for the UPSAMPLING levels of
+    the chained pyramid (utils/loss.py:210): src index = i * (in-1)/(out-1) in fp32, lambda =
+    index - floor, and out = fma(hy, fma(hx, a, lx*b), ly * fma(hx, c, lx*e)).  (The first,
+    downsampling level of the chain is not reproducible bit for bit from outside ATen; it agrees to
+    1 ulp, which the GPU gradient tests account for through the reference's own sensitivity.)"""
+    import torch.nn.functional as F
+    f32 = np.float32
+
+    def fma(a, b, c):
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(f32)
+
+    torch.manual_seed(1)
+    img = F.interpolate(torch.randint(0, 256, (1, 1, 260, 346)).float(), size=(32, 43), mode='bilinear',
+                        align_corners=True)
+    for ho, wo in ((65, 86), (130, 173), (260, 346)):
+        out = F.interpolate(img, size=(ho, wo), mode='bilinear', align_corners=True)
+        im = img[0, 0].numpy()
+        hi, wi = im.shape
+        ys = np.arange(ho, dtype=f32) * (f32(hi - 1) / f32(ho - 1))
+        xs = np.arange(wo, dtype=f32) * (f32(wi - 1) / f32(wo - 1))
+        y0, x0 = np.minimum(ys.astype(np.int64), hi - 1), np.minimum(xs.astype(np.int64), wi - 1)
+        y1, x1 = np.minimum(y0 + 1, hi - 1), np.minimum(x0 + 1, wi - 1)
+        ly, lx = (ys - y0.astype(f32))[:, None], (xs - x0.astype(f32))[None, :]
+        a, b, c, e = im[y0][:, x0], im[y0][:, x1], im[y1][:, x0], im[y1][:, x1]
+        hx, hy = (f32(1) - lx) + 0 * a, (f32(1) - ly) + 0 * a
+        lx, ly = lx + 0 * a, ly + 0 * a
+        val = fma(hy, fma(hx, a, lx * b), ly * fma(hx, c, lx * e))
+        assert np.array_equal(val, out[0, 0].numpy())
+        img = out
