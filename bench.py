@@ -404,10 +404,30 @@ def run_reference(args, rank):
                              'reference is Python+torch_scatter and cannot travel: oracle torch-CPU port'},
             'e2e': {'value': v, 'unit': 'Mevents/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
-    print(json.dumps(line))
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner, cuDNN warnings) write to fd 1; the driver wants exactly
+    ONE JSON line there.  Route fd 1 to stderr for the run and keep the real one for emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + '\n').encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=50)
@@ -540,7 +560,7 @@ def main():
                                        'hbm_gbs_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9,
                                        'hbm_frac_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9 / peak}
     line['cpu_baseline'] = cpu_baseline(HEADLINE) if world == 1 and not args.quick else None
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 

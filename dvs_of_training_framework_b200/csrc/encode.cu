@@ -532,8 +532,22 @@ static int encode_scatter_impl(const EncodeArgs& a, cudaStream_t stream, bool pd
                                      encode_grid((a.n >> 2) + 1, 256, 4), 256, 0, stream, pdl, a);
         case 7: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
                                      encode_grid((a.n >> 2) + 1, 256, 16), 256, 0, stream, pdl, a);
+        case 0: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                                     encode_grid((a.n >> 2) + 1, 256, 8), 256, 0, stream, pdl, a);
+        case 8: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                                     encode_grid((a.n >> 2) + 1, 256, 32), 256, 0, stream, pdl, a);
+        case 9: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                                     encode_grid((a.n >> 2) + 1, 256, 128), 256, 0, stream, pdl, a);
+        case 10: return launch_stream(encode_vec2_kernel<6>, "encode_vec2_kernel<6>",
+                                      encode_grid((a.n >> 1) + 1, 256, 48), 256, 0, stream, pdl, a);
+        case 11: return launch_stream(encode_vec4_kernel<4>, "encode_vec4_kernel<4>",
+                                      encode_grid((a.n >> 2) + 1, 256, 32), 256, 0, stream, pdl, a);
+        // default: up to 128 CTAs per SM in the grid (3 resident at a time), i.e. one pass of 4
+        // events per thread for anything below ~78 M events: fresh CTAs keep the load phase of one
+        // and the RED phase of another interleaved.  Measured (profiles/r01h_variants.jsonl):
+        // cfg4 54.6 -> 76.4 Gev/s and cfg3 78.0 -> 81.8 Gev/s over the 8-per-SM persistent grid.
         default: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                      encode_grid((a.n >> 2) + 1, 256, 8), 256, 0, stream, pdl, a);
+                                      encode_grid((a.n >> 2) + 1, 256, 128), 256, 0, stream, pdl, a);
     }
 }
 

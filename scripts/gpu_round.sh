@@ -11,7 +11,7 @@ tests)
 ubench)
   timeout 300 ./scripts/ubench_atomics > $OUT/ubench_atomics.json 2>&1; cat $OUT/ubench_atomics.json;;
 variants)
-  for v in 0 1 2 3 4 5 6 7; do
+  for v in ${VARIANTS:-0 7 8 9 10 11}; do
     DVSOF_ENCODE_VARIANT=$v timeout 600 python scripts/exp_encoder.py cfg2 cfg3 cfg4 >> $OUT/variants.jsonl 2>> $OUT/variants.err
   done; cat $OUT/variants.jsonl;;
 bench)
