@@ -150,7 +150,7 @@ def bench_encoder(name, K, W, dev, seed_off=0):
     ev, ts, _ = fast_events(1234 + int(name[3:]) + seed_off, B, H, Wd, n, c['T'], dev)
     N = B * n
     out = torch.empty((B, 4, He, We), dtype=torch.float32, device=dev)
-    ws = torch.empty(L.load().dvsof_encode_workspace_bytes(B), dtype=torch.uint8, device=dev)
+    ws = torch.empty(L.load().dvsof_encode_workspace_bytes(N, B, He, We), dtype=torch.uint8, device=dev)
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     sp = L.stream_ptr(dev)
     flush = L2Flusher(dev)
@@ -167,7 +167,7 @@ def bench_encoder(name, K, W, dev, seed_off=0):
     def whole():
         L.call('dvsof_encode_event_image', L.ptr(ev['x']), L.ptr(ev['y']), L.ptr(ev['timestamp']),
                L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, L.ptr(ts), B, He, We, L.ptr(out),
-               L.ptr(ws), L.ptr(status), sp)
+               L.ptr(ws), ws.numel(), L.ptr(status), sp)
 
     E = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     # (1) the step: one library call = prepare (zero + per-sample dt) -> scatter, PDL-chained

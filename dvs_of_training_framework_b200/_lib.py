@@ -35,9 +35,10 @@ class LossFrames(C.Structure):
 _SIGNATURES = {
     'dvsof_last_error': (C.c_char_p, []),
     'dvsof_version': (C.c_int, []),
-    'dvsof_encode_workspace_bytes': (C.c_size_t, [C.c_int64]),
+    'dvsof_encode_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32, C.c_int32]),
     'dvsof_encode_event_image': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p, C.c_int64,
-                                            C.c_int32, C.c_int32] + [C.c_void_p] * 4),
+                                            C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
+                                            C.c_void_p, C.c_void_p]),
     'dvsof_encode_prepare': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                        C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_encode_scatter': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_int32, C.c_int32]

@@ -10,6 +10,7 @@
 // scatter_max(..., out=zeros)).  Both are order independent => bit-exact vs the oracle.
 #include <stdlib.h>
 #include "common.cuh"
+#include "encode_binned.cuh"
 
 namespace dvsof {
 
@@ -50,7 +51,8 @@ __device__ __forceinline__ int64_t cta_upper_bound(const int64_t* __restrict__ b
 __global__ void __launch_bounds__(kPrepThreads)
 encode_prepare_kernel(const int64_t* __restrict__ b, const float* __restrict__ t, int64_t n,
                       const float* __restrict__ timestamps, int n_samples,
-                      float2* __restrict__ sd, float* __restrict__ out, size_t n_floats) {
+                      float2* __restrict__ sd, int64_t* __restrict__ ends,
+                      float* __restrict__ out, size_t n_floats) {
     __shared__ int warp_first[kPrepThreads / 32];
     pdl_launch_dependents();
     if (n > 0) {
@@ -61,6 +63,7 @@ encode_prepare_kernel(const int64_t* __restrict__ b, const float* __restrict__ t
                 float dt = 0.f;
                 if (end > 0 && b[end - 1] == (int64_t)s) dt = __fsub_rn(t[end - 1], start);  // net.py:136-137
                 sd[s] = make_float2(start, fmaxf(dt, 1e-9f));                                  // net.py:138
+                ends[s] = end;                      // exclusive end of sample s in the event stream
             }
         }
     }
@@ -473,15 +476,43 @@ static int check_encode_args(int64_t n, int64_t B, int H, int W, const void* out
     return DVSOF_OK;
 }
 
-extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_samples) {
-    return round_up((size_t)(n_samples > 0 ? n_samples : 1) * sizeof(float2), 256);
+// which path: DVSOF_ENCODE_PATH=direct|binned forces one (tests); default: binned for streams
+// large and dense enough to pay for the second pass (>= 4 M events, >= 8 events per output cell)
+static int encode_path_override() {   // read per call: tests switch it at run time
+    const char* e = getenv("DVSOF_ENCODE_PATH");
+    if (!e) return 0;
+    return e[0] == 'd' ? 1 : (e[0] == 'b' ? 2 : 0);
 }
 
-// variant of the streaming kernel: DVSOF_ENCODE_VARIANT (experiments, scripts/exp_encoder.py);
-// unset = the default chosen from the measurements recorded in DESIGN.md section 4
-static int encode_variant() {
-    static const int v = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : -1;
-    return v;
+static bool use_binned(const BinPlan& plan, int64_t n, int64_t B, int H, int W, size_t workspace_bytes) {
+    if (!plan.ok || workspace_bytes < plan.total) return false;
+    const int ov = encode_path_override();
+    if (ov == 1) return false;
+    if (ov == 2) return true;
+    // measured (profiles/r01l_binned_launches.csv, cfg3: 160 M events on 32 x 256^2): bin 1.36 ms +
+    // reduce 0.40 ms vs 1.96 ms direct.  Worth it only when the stream is dense -- at ~2 events per
+    // cell (cfg4) the direct path's REDs are cheaper than the extra 12 B/event of record traffic.
+    return n >= (4 << 20) && n >= 8 * B * (int64_t)H * W;
+}
+
+extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_events, int64_t n_samples, int32_t H, int32_t W) {
+    return make_bin_plan(n_events, n_samples, H, W).total;
+}
+
+static int launch_prepare(const float* t, const int64_t* b, int64_t n, const float* timestamps,
+                          int64_t B, int32_t H, int32_t W, float* out, void* workspace, bool zero,
+                          cudaStream_t stream) {
+    const BinPlan plan = make_bin_plan(0, B, H, W);      // sd | ends offsets only
+    const size_t n_floats = zero ? (size_t)B * 4 * H * W : 0;
+    // enough CTAs to stream the zeros at full rate, at least one per sample for the search
+    int64_t grid = (int64_t)((n_floats / 4 + kPrepThreads * 8 - 1) / (kPrepThreads * 8));
+    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+    if (grid < B) grid = B < kNumSMs * 8 ? B : kNumSMs * 8;
+    if (grid < 1) grid = 1;
+    return launch_kernel("encode_prepare_kernel", encode_prepare_kernel, (int)grid, kPrepThreads, 0,
+                         stream, false, b, t, n, timestamps, (int)B, reinterpret_cast<float2*>(workspace),
+                         reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + plan.off_ends),
+                         out, n_floats);                 // n == 0: zeros only, net.py:115-116
 }
 
 extern "C" int dvsof_encode_prepare(const float* t, const int64_t* b, int64_t n,
@@ -490,15 +521,14 @@ extern "C" int dvsof_encode_prepare(const float* t, const int64_t* b, int64_t n,
     if (int rc = check_encode_args(n, B, H, W, out, workspace, workspace)) return rc;
     if (n > 0 && (!t || !b || !timestamps))
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
-    const size_t n_floats = (size_t)B * 4 * H * W;
-    // enough CTAs to stream the zeros at full rate, at least one per sample for the search
-    int64_t grid = (int64_t)((n_floats / 4 + kPrepThreads * 8 - 1) / (kPrepThreads * 8));
-    if (grid > kNumSMs * 8) grid = kNumSMs * 8;
-    if (grid < B) grid = B < kNumSMs * 8 ? B : kNumSMs * 8;
-    if (grid < 1) grid = 1;
-    return launch_kernel("encode_prepare_kernel", encode_prepare_kernel, (int)grid, kPrepThreads, 0,
-                         (cudaStream_t)stream_, false, b, t, n, timestamps, (int)B,
-                         reinterpret_cast<float2*>(workspace), out, n_floats);   // n == 0: net.py:115-116
+    return launch_prepare(t, b, n, timestamps, B, H, W, out, workspace, true, (cudaStream_t)stream_);
+}
+
+// variant of the streaming kernel: DVSOF_ENCODE_VARIANT (experiments, scripts/exp_encoder.py);
+// unset = the default chosen from the measurements recorded in DESIGN.md section 4
+static int encode_variant() {
+    static const int v = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : -1;
+    return v;
 }
 
 static int encode_scatter_impl(const EncodeArgs& a, cudaStream_t stream, bool pdl) {
@@ -562,19 +592,54 @@ extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const fl
     return encode_scatter_impl(a, (cudaStream_t)stream_, false);
 }
 
+static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream);
+
 extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
                                         const int64_t* p, const int64_t* b, int64_t n,
                                         const float* timestamps, int64_t B, int32_t H, int32_t W,
-                                        float* out, void* workspace, uint32_t* status,
-                                        void* stream_) {
-    if (!status) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null status word");
-    if (n > 0 && (!x || !y || !p)) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
-    if (int rc = dvsof_encode_prepare(t, b, n, timestamps, B, H, W, out, workspace, stream_)) return rc;
+                                        float* out, void* workspace, size_t workspace_bytes,
+                                        uint32_t* status, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    if (n > 0 && (!x || !y || !p || !t || !b || !timestamps))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    if (workspace_bytes < make_bin_plan(0, B, H, W).total)
+        return fail(DVSOF_ERR_WORKSPACE, "encode: workspace of %zu bytes is too small", workspace_bytes);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const BinPlan plan = make_bin_plan(n, B, H, W);
+    const bool binned = n > 0 && use_binned(plan, n, B, H, W, workspace_bytes);
+    // binned: pass 2 writes every output cell, so the image is not zeroed first
+    if (int rc = launch_prepare(t, b, n, timestamps, B, H, W, out, workspace, !binned, stream)) return rc;
     if (n == 0) return DVSOF_OK;
     const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(workspace), (int)B, H, W, out, status};
+    if (binned) return encode_binned_impl(a, plan, workspace, stream);
     static const bool no_pdl = getenv("DVSOF_NO_PDL") != nullptr;
     // scatter is released while prepare still runs; it blocks in griddepcontrol.wait
-    return encode_scatter_impl(a, (cudaStream_t)stream_, !no_pdl);
+    return encode_scatter_impl(a, stream, !no_pdl);
+}
+
+static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream) {
+    char* ws = static_cast<char*>(workspace);
+    const int64_t* ends = reinterpret_cast<const int64_t*>(ws + plan.off_ends);
+    uint16_t* codes = reinterpret_cast<uint16_t*>(ws + plan.off_codes);
+    float* ts = reinterpret_cast<float*>(ws + plan.off_ts);
+    uint32_t* table = reinterpret_cast<uint32_t*>(ws + plan.off_table);
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(encode_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(encode_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytes);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_binned smem attr: %s", cudaGetErrorString(e));
+        configured = true;
+    }
+    if (plan.max_chunks > INT32_MAX || (int64_t)a.B * plan.T > INT32_MAX)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_binned: grid too large");
+    if (int rc = launch_kernel("encode_bin_kernel", encode_bin_kernel, (int)plan.max_chunks, kBinThreads,
+                               kBinStageBytes, stream, true, a.x, a.y, a.t, a.p, a.b, a.n, ends, a.B, a.H,
+                               a.W, plan.r_log2, plan.T, codes, ts, table, a.status))
+        return rc;
+    return launch_kernel("encode_reduce_kernel", encode_reduce_kernel, a.B * plan.T, kRedThreads,
+                         (size_t)plan.cells * 8, stream, true, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                         plan.r_log2, plan.T, a.out);
 }
 
 extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,

@@ -1,0 +1,287 @@
+// encode_binned.cuh -- two-pass, shared-memory-privatised event-image encoder for LARGE event
+// streams (included by encode.cu; same results as the direct RED kernel, bit for bit).
+//
+// Why: the direct kernel issues two L2 reductions per event.  On B200 that path saturates at
+// ~190 G scattered REDs/s (scripts/ubench_atomics.cu; ncu: lts__t_tag_requests 76 % at 164 G/s),
+// i.e. <= 95 Gevents/s = 52 % of the HBM roofline of the 36 B/event stream -- while shared-memory
+// atomics run 17x faster (3.2 T/s).  A whole sample's slab (H*W*2 cells * 8 B = 1 MB at 256^2)
+// does not fit in one SM and cluster-remote shared atomics are as slow as global REDs (82-184 G/s),
+// so the stream is first PARTITIONED by output row band:
+//
+//   pass 1 (bin):    a CTA takes a chunk of kBinChunk consecutive events of ONE sample, counting-
+//                    sorts them by tile (band of 2^r rows) in shared memory and writes them back
+//                    as 6-byte records {u16 cell-in-tile, f32 t} -- contiguous per (chunk, tile)
+//                    run -- plus the chunk's run table.  HBM: 36 B read + 6 B written per event.
+//   pass 2 (reduce): a CTA owns one (sample, tile): its slab of {u32 count, s32 max-key} lives in
+//                    shared memory; it streams its runs of every chunk of the sample (6 B/event),
+//                    applies ATOMS.ADD / ATOMS.MAX, then writes its 4 output plane bands ONCE with
+//                    coalesced stores (no memset of the image, no global atomics).
+//
+// Exactness: counts are integers; the timestamp plane is max_i f(t_i) with f(t) = (t - start) / dt
+// monotone non-decreasing (IEEE sub and div by dt > 0 are monotone), so it equals f(max_i t_i):
+// pass 2 keeps the max of the RAW t under an order-preserving integer key and normalises once per
+// cell at the flush.  max(0, .) against the zero-initialised plane = scatter_max(out=zeros).
+#pragma once
+#include "common.cuh"
+
+namespace dvsof {
+
+constexpr int kBinChunk = 8192;       // events per pass-1 chunk
+constexpr int kBinThreads = 512;      // pass-1 CTA: 16 events per thread
+constexpr int kRedBatch = 8;          // pass-2 loads in flight per lane
+constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
+constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
+constexpr int kRedThreads = 512;      // pass-2 CTA: 16 warps stream the runs of one slab, 3 CTAs per SM
+constexpr size_t kBinSlabBytes = 32 * 1024;
+constexpr int kBinStageBytes = kBinChunk * (sizeof(float) + sizeof(uint16_t));   // pass-1 staging
+
+struct BinPlan {
+    int ok;                 // geometry feasible
+    int r_log2, R, T;       // rows per tile (2^r_log2) and tiles per sample
+    int cells;              // R * W * 2 slab cells
+    int64_t max_chunks;     // upper bound of sum_s ceil(n_s / kBinChunk)
+    size_t off_ends, off_codes, off_ts, off_table, total;   // workspace layout (after the sd array)
+};
+
+inline BinPlan make_bin_plan(int64_t n, int64_t B, int H, int W) {
+    BinPlan p = {};
+    p.off_ends = round_up((size_t)(B > 0 ? B : 1) * sizeof(float2), 256);
+    p.total = p.off_ends + round_up((size_t)(B > 0 ? B : 1) * sizeof(int64_t), 256);
+    if (n <= 0 || B <= 0 || B > kBinMaxSamples) return p;
+    int r = 0;
+    while (((size_t)2 << r) * W * 16 <= kBinSlabBytes) ++r;        // largest 2^r rows within the slab
+    if ((size_t)(1 << r) * W * 16 > kBinSlabBytes) return p;          // one row does not fit
+    while (r > 0 && (1 << (r - 1)) >= H) --r;                          // no taller than the image
+    p.r_log2 = r; p.R = 1 << r;
+    p.T = (H + p.R - 1) >> r;
+    p.cells = p.R * W * 2;
+    if (p.T > kBinMaxTiles || p.cells > 65536) return p;
+    p.max_chunks = n / kBinChunk + B + 1;
+    p.off_codes = p.total;
+    p.off_ts = p.off_codes + round_up((size_t)p.max_chunks * kBinChunk * sizeof(uint16_t), 256);
+    p.off_table = p.off_ts + round_up((size_t)p.max_chunks * kBinChunk * sizeof(float), 256);
+    p.total = p.off_table + round_up((size_t)p.max_chunks * (p.T + 1) * sizeof(uint32_t), 256);
+    p.ok = 1;
+    return p;
+}
+
+// order-preserving map float -> signed int (all finite values and infinities); self-inverse
+__device__ __forceinline__ int ordered_key(float t) {
+    const int b = __float_as_int(t);
+    return b ^ ((b >> 31) & 0x7fffffff);
+}
+__device__ __forceinline__ float key_to_float(int k) { return __int_as_float(k ^ ((k >> 31) & 0x7fffffff)); }
+
+// Every CTA derives the chunk layout from the per-sample ends (B <= kBinMaxSamples):
+// prefix[s] = number of chunks of samples < s.  Returns through shared memory.
+template <int THREADS>
+__device__ __forceinline__ void chunk_prefix(const int64_t* __restrict__ ends, int n_samples,
+                                             int* prefix /* [kBinMaxSamples + 1] shared */) {
+    for (int s = threadIdx.x; s < n_samples; s += THREADS) {
+        const int64_t lo = s ? ends[s - 1] : 0, hi = ends[s];
+        const int64_t cnt = hi > lo ? hi - lo : 0;
+        prefix[s + 1] = (int)((cnt + kBinChunk - 1) / kBinChunk);
+    }
+    if (threadIdx.x == 0) prefix[0] = 0;
+    __syncthreads();
+    if (threadIdx.x < 32) {                      // one warp: serial over 32-wide blocks, scan inside
+        int carry = 0;
+        for (int base = 0; base < n_samples; base += 32) {
+            const int i = base + threadIdx.x;
+            int v = i < n_samples ? prefix[i + 1] : 0;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, v, o);
+                if ((int)threadIdx.x >= o) v += u;
+            }
+            if (i < n_samples) prefix[i + 1] = v + carry;
+            carry += __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+}
+
+}  // namespace dvsof
+
+namespace dvsof {
+
+// ---------------------------------------------------------------------------------------
+// pass 1: partition one chunk of one sample by tile (counting sort in shared memory)
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBinThreads, 2)
+encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                  const float* __restrict__ t, const int64_t* __restrict__ p,
+                  const int64_t* __restrict__ b, int64_t n, const int64_t* __restrict__ ends,
+                  int n_samples, int H, int W, int r_log2, int T,
+                  uint16_t* __restrict__ codes_g, float* __restrict__ ts_g,
+                  uint32_t* __restrict__ table, uint32_t* __restrict__ status) {
+    __shared__ int prefix[kBinMaxSamples + 1];
+    __shared__ unsigned hist[kBinMaxTiles + 1];      // counts, then exclusive bases (T + 1 entries)
+    __shared__ unsigned cursor[kBinMaxTiles];
+    extern __shared__ __align__(16) unsigned char stage_raw[];   // kBinStageBytes (dynamic: > 48 KB total)
+    float* ts_s = reinterpret_cast<float*>(stage_raw);
+    uint16_t* codes_s = reinterpret_cast<uint16_t*>(stage_raw + kBinChunk * sizeof(float));
+    __shared__ int s_sample;
+    pdl_launch_dependents();
+    pdl_wait();                                       // ends[] come from the prepare kernel
+    chunk_prefix<kBinThreads>(ends, n_samples, prefix);
+    const int chunk = blockIdx.x;
+    unsigned flags = 0;
+    if (chunk == 0 && threadIdx.x == 0) {             // the layout itself: monotone, covers [0, n)
+        int64_t prev = 0;
+        for (int s = 0; s < n_samples; ++s) { if (ends[s] < prev) flags |= DVSOF_ST_NOT_GROUPED; prev = ends[s]; }
+        if (prev != n) flags |= DVSOF_ST_BAD_SAMPLE;  // events with sample_index >= B (or < 0 at the front)
+    }
+    if (chunk >= prefix[n_samples]) { if (flags) atomicOr(status, flags); return; }
+    if (threadIdx.x < 32) {                           // which sample owns this chunk
+        for (int base = 0; base < n_samples; base += 32) {
+            const int s = base + threadIdx.x;
+            if (s < n_samples && prefix[s] <= chunk && chunk < prefix[s + 1]) s_sample = s;
+        }
+    }
+    for (int k = threadIdx.x; k <= T; k += kBinThreads) hist[k] = 0;
+    __syncthreads();
+    const int s = s_sample;
+    const int64_t s_begin = s ? ends[s - 1] : 0;
+    const int64_t e0 = s_begin + (int64_t)(chunk - prefix[s]) * kBinChunk;
+    const int64_t e1 = min(e0 + (int64_t)kBinChunk, ends[s]);
+    constexpr int kPer = kBinChunk / kBinThreads;     // 16 events per thread
+    unsigned packed[kPer];                            // tile << 16 | code, 0xffffffff = dropped
+    float tv[kPer];
+#pragma unroll
+    for (int k = 0; k < kPer; k += 2) {               // two events in flight per thread and step
+        int64_t xi[2], yi[2], pi[2], bi[2];
+        bool ok[2];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int64_t i = e0 + (int64_t)(k + j) * kBinThreads + threadIdx.x;
+            ok[j] = i < e1;
+            if (ok[j]) {
+                xi[j] = __ldcs(x + i); yi[j] = __ldcs(y + i); pi[j] = __ldcs(p + i); bi[j] = __ldcs(b + i);
+                tv[k + j] = __ldcs(t + i);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            packed[k + j] = 0xffffffffu;
+            if (!ok[j]) continue;
+            if (pi[j] != 1 && pi[j] != -1) { flags |= DVSOF_ST_BAD_POLARITY; continue; }
+            if (bi[j] != (int64_t)s) { flags |= DVSOF_ST_NOT_GROUPED; continue; }
+            if ((uint64_t)xi[j] >= (uint64_t)W || (uint64_t)yi[j] >= (uint64_t)H) { flags |= DVSOF_ST_BAD_PIXEL; continue; }
+            const unsigned yy = (unsigned)yi[j], tile = yy >> r_log2;
+            const unsigned c = (unsigned)(1 - (int)pi[j]) >> 1;                   // net.py:142
+            const unsigned code = (((yy & ((1u << r_log2) - 1u)) * (unsigned)W + (unsigned)xi[j]) << 1) | c;
+            packed[k + j] = (tile << 16) | code;
+            atomicAdd(&hist[tile], 1u);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {                            // exclusive scan of the T tile counts
+        unsigned carry = 0;
+        for (int base = 0; base <= T; base += 32) {
+            const int k = base + threadIdx.x;
+            const unsigned cnt = k < T ? hist[k] : 0u;
+            unsigned v = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned u = __shfl_up_sync(0xffffffffu, v, o);
+                if ((int)threadIdx.x >= o) v += u;
+            }
+            const unsigned excl = carry + v - cnt;
+            if (k <= T) {
+                hist[k] = excl;                                      // hist[T] = total kept events
+                if (k < T) cursor[k] = excl;
+                table[(size_t)chunk * (T + 1) + k] = excl;
+            }
+            carry += __shfl_sync(0xffffffffu, v, 31);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kPer; ++k) {
+        if (packed[k] == 0xffffffffu) continue;
+        const unsigned pos = atomicAdd(&cursor[packed[k] >> 16], 1u);
+        codes_s[pos] = (uint16_t)(packed[k] & 0xffffu);
+        ts_s[pos] = tv[k];
+    }
+    __syncthreads();
+    const unsigned total = hist[T];
+    uint32_t* cg = reinterpret_cast<uint32_t*>(codes_g + (size_t)chunk * kBinChunk);
+    const uint32_t* cs = reinterpret_cast<const uint32_t*>(codes_s);
+    float* tg = ts_g + (size_t)chunk * kBinChunk;
+    for (unsigned i = threadIdx.x; i < (total + 1) / 2; i += kBinThreads) cg[i] = cs[i];
+    for (unsigned i = threadIdx.x; i < total; i += kBinThreads) tg[i] = ts_s[i];
+    if (flags) atomicOr(status, flags);
+}
+
+// ---------------------------------------------------------------------------------------
+// pass 2: one CTA per (sample, tile): shared-memory slab, then one coalesced write of the bands
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kRedThreads, 3)
+encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restrict__ ts_g,
+                     const uint32_t* __restrict__ table, const int64_t* __restrict__ ends,
+                     const float2* __restrict__ sd, int n_samples, int H, int W, int r_log2, int T,
+                     float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned slab[];   // [cells] counts, then [cells] max keys
+    __shared__ int prefix[kBinMaxSamples + 1];
+    pdl_wait();                                         // records + tables come from pass 1
+    const int s = blockIdx.x / T, tile = blockIdx.x - s * T;
+    const int R = 1 << r_log2, cells = R * W * 2;
+    unsigned* cnt = slab;
+    int* key = reinterpret_cast<int*>(slab + cells);
+    for (int i = threadIdx.x; i < cells; i += kRedThreads) { cnt[i] = 0u; key[i] = INT_MIN; }
+    chunk_prefix<kRedThreads>(ends, n_samples, prefix);   // ends with __syncthreads()
+    const int cb = prefix[s], nc = prefix[s + 1] - prefix[s];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int c0 = warp * 32; c0 < nc; c0 += (kRedThreads / 32) * 32) {
+        unsigned lo = 0, hi = 0;                          // each lane: the run of one chunk
+        if (c0 + lane < nc) {
+            const uint32_t* row = table + (size_t)(cb + c0 + lane) * (T + 1) + tile;
+            lo = __ldg(row); hi = __ldg(row + 1);
+        }
+        const int m = min(32, nc - c0);
+        for (int j = 0; j < m; ++j) {
+            const unsigned l = __shfl_sync(0xffffffffu, lo, j), h = __shfl_sync(0xffffffffu, hi, j);
+            const size_t base = (size_t)(cb + c0 + j) * kBinChunk;
+            for (unsigned i0 = l; i0 < h; i0 += 32 * kRedBatch) {   // kRedBatch records per lane in flight
+                unsigned code[kRedBatch];
+                float tv[kRedBatch];
+#pragma unroll
+                for (int u = 0; u < kRedBatch; ++u) {
+                    const unsigned i = i0 + u * 32 + lane;
+                    code[u] = 0xffffffffu;
+                    if (i < h) { code[u] = __ldcs(codes_g + base + i); tv[u] = __ldcs(ts_g + base + i); }
+                }
+#pragma unroll
+                for (int u = 0; u < kRedBatch; ++u) {
+                    if (code[u] == 0xffffffffu) continue;
+                    atomicAdd(&cnt[code[u]], 1u);                // scatter_sum, net.py:147-148
+                    atomicMax(&key[code[u]], ordered_key(tv[u]));   // scatter_max of the raw t, net.py:149
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const float2 nd = sd[s];
+    const int y0 = tile << r_log2;
+    const size_t plane = (size_t)H * W;
+    float* o = out + (size_t)s * 4 * plane;
+    for (int i = threadIdx.x; i < R * W; i += kRedThreads) {
+        const int row = i / W, xx = i - row * W, yy = y0 + row;
+        if (yy >= H) break;
+        const size_t px = (size_t)yy * W + xx;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int k = key[2 * i + c];
+            float tn = 0.f;
+            if (k != INT_MIN) {
+                tn = __fdiv_rn(__fsub_rn(key_to_float(k), nd.x), nd.y);          // net.py:141
+                if (__float_as_int(tn) <= 0) tn = 0.f;                           // max against the zero plane
+            }
+            o[c * plane + px] = (float)cnt[2 * i + c];
+            o[(c + 2) * plane + px] = tn;
+        }
+    }
+}
+
+}  // namespace dvsof

@@ -50,11 +50,11 @@ def compute_event_image(events, timestamps, sample_idx, imsize, device='cuda',
     with torch.cuda.device(dev):
         st = _lib.status_for(dev)
         st.flush()
-        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(bs), dtype=torch.uint8, device=dev)
+        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(n, bs, H, W), dtype=torch.uint8, device=dev)
         _lib.call('dvsof_encode_event_image', _lib.ptr(ev['x']), _lib.ptr(ev['y']),
                   _lib.ptr(ev['timestamp']), _lib.ptr(ev['polarity']), _lib.ptr(ev['sample_index']),
-                  n, _lib.ptr(timestamps), bs, H, W, _lib.ptr(out), _lib.ptr(ws), _lib.ptr(st.word),
-                  _lib.stream_ptr(dev))
+                  n, _lib.ptr(timestamps), bs, H, W, _lib.ptr(out), _lib.ptr(ws), ws.numel(),
+                  _lib.ptr(st.word), _lib.stream_ptr(dev))
         if n:
             st.after_call()
     return out
@@ -84,7 +84,7 @@ def compute_event_image_compact(x, y, timestamp, polarity, events_per_sample, ti
     with torch.cuda.device(dev):
         st = _lib.status_for(dev)
         st.flush()
-        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(bs), dtype=torch.uint8, device=dev)
+        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(0, bs, H, W), dtype=torch.uint8, device=dev)
         _lib.call('dvsof_encode_event_image_compact', _lib.ptr(x), _lib.ptr(y), _lib.ptr(t),
                   _lib.ptr(p), _lib.ptr(begin), n, _lib.ptr(timestamps), bs, H, W, _lib.ptr(out),
                   _lib.ptr(ws), _lib.ptr(st.word), _lib.stream_ptr(dev))

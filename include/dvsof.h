@@ -50,9 +50,13 @@ int dvsof_version(void);
  *   out[b, c+2, y, x] = max(0, max (t - start[b]) / dt[b]),  start[b] = timestamps[2b],
  *   dt[b] = max(t[last event of sample b] - start[b], 1e-9).
  * Events must be grouped by ascending sample_index.  `out` (B,4,H,W) fp32 is fully
- * overwritten (zeroed inside the call).  workspace: dvsof_encode_workspace_bytes(B) bytes.
+ * overwritten.  workspace: dvsof_encode_workspace_bytes(N, B, H, W) bytes; pass its size as
+ * `workspace_bytes`.  Two device paths with identical results: the direct one (two L2 reductions
+ * per event) and, for large streams when the workspace has room for it, the two-pass one that
+ * bins the events by row band and reduces them in shared memory (csrc/encode_binned.cuh).
+ * A workspace of dvsof_encode_workspace_bytes(0, B, H, W) bytes selects the direct path.
  * ------------------------------------------------------------------------------------- */
-size_t dvsof_encode_workspace_bytes(int64_t n_samples);
+size_t dvsof_encode_workspace_bytes(int64_t n_events, int64_t n_samples, int32_t H, int32_t W);
 int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
                              const int64_t* polarity, const int64_t* sample_index, /* [dev] N */
                              int64_t n_events,
@@ -60,6 +64,7 @@ int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
                              int64_t n_samples, int32_t H, int32_t W,
                              float* out,        /* [dev] B*4*H*W */
                              void* workspace,   /* [dev] */
+                             size_t workspace_bytes,
                              uint32_t* status,  /* [dev] */
                              void* stream);
 

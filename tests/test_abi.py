@@ -47,11 +47,13 @@ def test_sass_is_sm100a_only(lib):
 def test_host_side_argument_errors(lib):
     assert lib.dvsof_version() >= 100
     rc = lib.dvsof_encode_event_image(None, None, None, None, None, -1, None, 1, 4, 4, None, None,
-                                      None, None)
+                                      0, None, None)
     assert rc == -1 and b'encode' in lib.dvsof_last_error()
     rc = lib.dvsof_event_crop(None, 0, 1, 4, 0., 0., 1., 1., None, None, None, None)
     assert rc == -1
-    assert lib.dvsof_encode_workspace_bytes(32) >= 32 * 8
+    assert lib.dvsof_encode_workspace_bytes(0, 32, 256, 256) >= 32 * 16
+    small, big = lib.dvsof_encode_workspace_bytes(1000, 8, 256, 256), lib.dvsof_encode_workspace_bytes(10 ** 7, 8, 256, 256)
+    assert big > small + 6 * 10 ** 7          # room for the 6 B/event records of the binned path
     assert lib.dvsof_compact_workspace_bytes(5000) >= 8 * 5
     assert lib.dvsof_map_lut_workspace_bytes(260, 346, 90000) > 260 * 346 * 12
 

@@ -15,8 +15,16 @@ def _cuda(ev):
     return {k: torch.as_tensor(v).cuda() for k, v in ev.items()}
 
 
+@pytest.fixture(params=['direct', 'binned'])
+def path(request, monkeypatch):
+    """Both device paths of the encoder (csrc/encode.cu direct REDs, csrc/encode_binned.cuh two-pass
+    shared-memory slabs); the library reads DVSOF_ENCODE_PATH at every call."""
+    monkeypatch.setenv('DVSOF_ENCODE_PATH', request.param)
+    return request.param
+
+
 @pytest.mark.parametrize('name', ['fixture', 'dense', 'ragged'])
-def test_matches_reference_golden(golden, name):
+def test_matches_reference_golden(golden, name, path):
     g = np.load(golden / f'encoder_{name}.npz')
     ev = _cuda({k[3:]: g[k] for k in g.files if k.startswith('ev_')})
     out = dv.compute_event_image(ev, torch.tensor(g['timestamps']).cuda(),
@@ -32,14 +40,14 @@ def test_matches_reference_golden(golden, name):
     (3, 48, 80, 1001, False),         # n % 4 != 0 tail
     (2, 480, 640, 200000, False),     # DSEC shape
 ])
-def test_matches_oracle_synthetic(B, H, W, n, contended):
+def test_matches_oracle_synthetic(B, H, W, n, contended, path):
     ev, ts, sidx = synth_events(7 + B, B, H, W, n, contended=contended)
     want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
     got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
     assert np.array_equal(got.cpu().numpy(), want)
 
 
-def test_unaligned_views_take_scalar_path():
+def test_unaligned_views_take_scalar_path(path):
     ev, ts, sidx = synth_events(3, 2, 64, 64, 5000)
     want = eo.compute_event_image(np_events({k: v[1:] for k, v in ev.items()}), ts.numpy(),
                                   sidx.numpy(), (64, 64))
@@ -48,7 +56,7 @@ def test_unaligned_views_take_scalar_path():
     assert np.array_equal(got.cpu().numpy(), want)
 
 
-def test_ragged_and_empty_samples():
+def test_ragged_and_empty_samples(path):
     ev, ts, sidx = synth_events(11, 6, 32, 48, 4000, ragged=True)
     want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (32, 48))
     got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 48))
@@ -63,7 +71,7 @@ def test_empty_events_give_zeros():
     assert out.shape == (1, 4, 32, 32) and not out.any()
 
 
-def test_events_before_start_and_late_events():
+def test_events_before_start_and_late_events(path):
     # t < start -> negative t^ loses against 0; t > last -> t^ > 1 kept (dt uses the LAST event)
     ev = {'x': [1, 1, 2, 2], 'y': [0, 0, 0, 0], 'polarity': [1, 1, -1, -1],
           'sample_index': [0, 0, 0, 0], 'timestamp': np.array([0.5, 3.0, 0.2, 1.0], np.float32)}
@@ -84,14 +92,14 @@ def test_quantize_extends_to_multiple_of_16():
 
 
 @pytest.mark.parametrize('field,value', [('polarity', 0), ('sample_index', -1), ('x', 9999)])
-def test_invalid_input_raises_assertion(field, value):
+def test_invalid_input_raises_assertion(field, value, path):
     ev, ts, sidx = synth_events(1, 2, 32, 32, 100)
     ev[field][150] = value
     with pytest.raises(AssertionError):
         dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 32))
 
 
-def test_ungrouped_samples_raise():
+def test_ungrouped_samples_raise(path):
     ev, ts, sidx = synth_events(1, 2, 32, 32, 100)
     ev['sample_index'] = ev['sample_index'].flip(0)
     with pytest.raises(AssertionError):
@@ -131,3 +139,30 @@ def test_full_size_properties_cfg3_like():
     sh = {k: v[perm].contiguous() for k, v in ev.items()}
     cnt2 = dv.compute_event_image(_cuda(sh), ts.cuda(), sidx.cuda(), (H, W))[:, :2]
     assert torch.equal(cnt2, full[:, :2])
+
+
+def test_binned_equals_direct_bitwise_dense(monkeypatch):
+    """The two device paths on a stream dense enough for real slab contention (40 events per
+    cell) and with negative / late timestamps: bit-identical images."""
+    B, H, W, n = 3, 80, 112, 700_000
+    ev, ts, sidx = synth_events(55, B, H, W, n, contended=True)
+    ev['timestamp'] = ev['timestamp'] - 0.004            # some events before `start` -> clamp at 0
+    ts = ts.clone()
+    ts[0::2] = 0.001
+    outs = {}
+    for p in ('direct', 'binned'):
+        monkeypatch.setenv('DVSOF_ENCODE_PATH', p)
+        outs[p] = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert torch.equal(outs['direct'], outs['binned'])
+    assert int(outs['binned'][:, :2].sum()) == B * n and float(outs['binned'][:, 2:].min()) == 0.0
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    assert np.array_equal(outs['binned'].cpu().numpy(), want)
+
+
+def test_default_path_selection_large_stream_is_exact():
+    """>= 4 M events and >= 8 events per cell -> the library picks the binned path by itself."""
+    B, H, W, n = 2, 64, 64, 2_200_000
+    ev, ts, sidx = synth_events(77, B, H, W, n)
+    got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    assert np.array_equal(got.cpu().numpy(), want)
