@@ -534,7 +534,7 @@ def main():
                       'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
                       'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
                                    'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
-                                   'note': 'whole API step (combined_loss + backward: 7 launches + autograd glue)'},
+                                   'note': 'whole API step: combined_loss (1 library call = match + 4 resize + fused forward, PDL-chained) + dot + backward (1 launch); host-bound'},
                       'kernels': {'fwd_ms': loss['fwd_ms'], 'bwd_ms': loss['bwd_ms'],
                                   'fwd_hbm_frac': loss['fwd_bytes'] / (loss['fwd_ms'] * 1e-3) / 1e9 / peak,
                                   'bwd_hbm_frac': loss['bwd_bytes'] / (loss['bwd_ms'] * 1e-3) / 1e9 / peak}},

@@ -3,7 +3,8 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
 
     encoder.compute_event_image / quantize / extend_size   <- EV_FlowNet/net.py:88-205
     loss.Loss / Losses / init_losses / charbonier_loss      <- utils/loss.py
-    data.get_count_image / EventCrop / RandomRotation       <- utils/data.py
+    data.get_count_image / EventCrop / RandomRotation /
+         frame_generator                                    <- utils/data.py
     transformation.map                                      <- utils/transformation (native ext)
 
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
@@ -11,9 +12,10 @@ CPU fallback."""
 from . import _lib  # noqa: F401
 from .encoder import compute_event_image, compute_event_image_compact, extend_size, quantize  # noqa: F401
 from .loss import Loss, Losses, charbonier_loss, init_losses, interpolate  # noqa: F401
-from .data import EventCrop, RandomRotation, get_count_image  # noqa: F401
+from .data import EventCrop, RandomRotation, frame_generator, frame_offsets, get_count_image  # noqa: F401
 from . import transformation  # noqa: F401
 
 __all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
-           'EventCrop', 'RandomRotation', 'get_count_image', 'transformation']
+           'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets',
+           'transformation']

@@ -58,6 +58,8 @@ _SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_map_events_write': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_window_offsets': (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64,
+                                       C.c_void_p, C.c_void_p]),
     'dvsof_match_timestamps': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p,
                                          C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_resize_bilinear': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
@@ -121,31 +123,52 @@ class Status:
 
     mode 'sync'     -- check right after the call (reference behaviour: AssertionError raised
                        by the call itself; one host sync per call);
-    mode 'deferred' -- the word is checked at the next call that uses this object or at
-                       `flush()`; no sync on the hot path.
+    mode 'deferred' -- the word is copied to pinned host memory asynchronously after each call and
+                       looked at when that copy has LANDED (event query at the next call, never a
+                       wait), or at `flush(wait=True)` / `synchronize()`: no sync on the hot path,
+                       errors surface one or two calls late.
     """
     mode = 'sync'
 
     def __init__(self, device):
         self.word = torch.zeros(1, dtype=torch.int32, device=device)
+        self.host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self.event = torch.cuda.Event()
         self.pending = False
+
+    def _raise(self, bits, exc):
+        raise exc('; '.join(t for b, t in _ST_TEXT.items() if bits & b))
 
     def check(self, exc=AssertionError):
         bits = int(self.word.item()) & 0xffffffff
         self.pending = False
         if bits:
             self.word.zero_()
-            raise exc('; '.join(t for b, t in _ST_TEXT.items() if bits & b))
+            self._raise(bits, exc)
 
     def after_call(self, exc=AssertionError):
         if Status.mode == 'sync':
             self.check(exc)
         else:
+            self.host.copy_(self.word, non_blocking=True)
+            self.event.record()
             self.pending = True
 
-    def flush(self, exc=AssertionError):
-        if self.pending:
-            self.check(exc)
+    def flush(self, exc=AssertionError, wait=False):
+        if not self.pending:
+            return
+        if wait:
+            self.event.synchronize()
+        elif not self.event.query():
+            return                                   # still in flight: look again at the next call
+        self.pending = False
+        bits = int(self.host[0]) & 0xffffffff
+        if bits:
+            self.word.zero_()
+            self._raise(bits, exc)
+
+    def synchronize(self, exc=AssertionError):
+        self.flush(exc, wait=True)
 
 
 _status = {}

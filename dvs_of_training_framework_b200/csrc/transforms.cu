@@ -329,3 +329,43 @@ extern "C" int dvsof_map_events_write(const float* events, int64_t n, int32_t n_
         count, write, n, reinterpret_cast<const int64_t*>(ev_ws));
     return check_launch("map_events_write");
 }
+
+
+// ---------------------------------------------------------------------------------------
+// utils/data.py:139-152 frame_generator: np.searchsorted(t, frames.ravel(), side='right') --
+// for every window boundary the number of events with t <= boundary (events sorted by t).
+// One thread per boundary, binary search; comparisons in fp64 as numpy promotes them.
+// ---------------------------------------------------------------------------------------
+namespace dvsof {
+template <typename T>
+__global__ void window_offsets_kernel(const T* __restrict__ t, int64_t n,
+                                      const double* __restrict__ bounds, int64_t n_bounds,
+                                      int64_t* __restrict__ out) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_bounds) return;
+    const double v = bounds[k];
+    int64_t lo = 0, hi = n;                        // first i with t[i] > v
+    while (lo < hi) {
+        const int64_t mid = lo + ((hi - lo) >> 1);
+        if ((double)__ldg(t + mid) <= v) lo = mid + 1; else hi = mid;
+    }
+    out[k] = lo;
+}
+}  // namespace dvsof
+
+extern "C" int dvsof_window_offsets(const void* t, int32_t elem_size, int64_t n_events,
+                                    const double* bounds, int64_t n_bounds, int64_t* out,
+                                    void* stream_) {
+    using namespace dvsof;
+    if (n_events < 0 || n_bounds < 0 || (elem_size != 4 && elem_size != 8) || (n_bounds && (!bounds || !out)) ||
+        (n_events && !t))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "window_offsets: bad arguments");
+    if (n_bounds == 0) return DVSOF_OK;
+    const int threads = 128, blocks = (int)((n_bounds + threads - 1) / threads);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (elem_size == 4)
+        return launch_kernel("window_offsets_kernel", window_offsets_kernel<float>, blocks, threads, 0, stream,
+                             false, static_cast<const float*>(t), n_events, bounds, n_bounds, out);
+    return launch_kernel("window_offsets_kernel", window_offsets_kernel<double>, blocks, threads, 0, stream,
+                         false, static_cast<const double*>(t), n_events, bounds, n_bounds, out);
+}

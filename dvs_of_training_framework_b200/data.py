@@ -1,5 +1,5 @@
 """Event transforms of the reference's `utils/data.py` on the GPU: `get_count_image` (:120-136),
-`EventCrop` (:24-42), `RandomRotation` (:155-220).  numpy in -> numpy out (copies inside);
+`EventCrop` (:24-42), `RandomRotation` (:155-220), `frame_generator` (:139-152).  numpy in -> numpy out (copies inside);
 CUDA tensors in -> CUDA tensors out."""
 import numpy as np
 import torch
@@ -108,3 +108,30 @@ def RandomRotation(interval, shape):
         return rimg, revents, angle
 
     return rotation
+
+
+def frame_offsets(t, frames):
+    """Per-window event ranges: `np.searchsorted(t, frames.ravel(), side='right').reshape(-1, 2)`
+    (utils/data.py:150) computed on the device.  t: sorted timestamps (numpy or CUDA tensor,
+    fp32/fp64); frames: [(start_ts, stop_ts), ...].  Returns an int64 CUDA tensor (F, 2)."""
+    tt = _to_cuda(t)
+    if tt.dtype not in (torch.float32, torch.float64):
+        tt = tt.to(torch.float64)
+    tt = tt.contiguous()
+    dev = tt.device
+    bounds = torch.as_tensor(np.asarray(frames, dtype=np.float64).ravel()).to(dev)
+    out = torch.empty(bounds.numel(), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('dvsof_window_offsets', _lib.ptr(tt), tt.element_size(), tt.numel(), _lib.ptr(bounds),
+                  bounds.numel(), _lib.ptr(out), _lib.stream_ptr(dev))
+    return out.view(-1, 2)
+
+
+def frame_generator(events, frames):
+    """utils/data.py:139-152: yields ([component[i_start:i_stop] for component in events], start,
+    stop) for every (start, stop) window; events = [x, y, t, p] sorted by t.  The window table is
+    built by one kernel launch; slices are views of the caller's arrays (numpy or CUDA)."""
+    frames = np.array(frames)
+    idx = frame_offsets(events[2], frames).cpu().numpy()
+    for (start, stop), (i_start, i_stop) in zip(frames, idx):
+        yield [p[i_start:i_stop] for p in events], start, stop

@@ -112,6 +112,51 @@ class _WarpLoss(torch.autograd.Function):
         return (None, None) + (None,) * S + tuple(_backward(match_idx, n_bad, levels, flows, grad_terms))
 
 
+class _Plan:
+    """Per (device, P, D, image size, scale shapes) constants of the fused call: the layout of the
+    one fp32 buffer a forward allocates (pyramid levels | match_idx | n_bad | terms), the gradient
+    buffer layout, and reusable ctypes argument blocks whose pointer fields are the only thing
+    that changes from call to call (no tensor views, no struct rebuilds on the hot path)."""
+
+    def __init__(self, dev, P, D, H, W, shapes):
+        self.S = S = len(shapes)
+        self.shapes = shapes
+        sizes = [D * h * w for h, w in shapes] + [2 * P, S * P, 3 * S]
+        self.offs, off = [], 0
+        for n in sizes:
+            self.offs.append(off)
+            off += (n + 3) & ~3                              # 16-byte aligned pieces
+        self.total = off
+        self.gsizes = [P * 2 * h * w for h, w in shapes]
+        self.goffs, off = [], 0
+        for n in self.gsizes:
+            self.goffs.append(off)
+            off += (n + 3) & ~3
+        self.gtotal = off
+        self.fwd, self.bwd, self.frames = _lib.LossScales(), _lib.LossScales(), _lib.LossFrames()
+        for sc in (self.fwd, self.bwd):
+            sc.n_scales, sc.n_pred = S, P
+            for s, (h, w) in enumerate(shapes):
+                sc.H[s], sc.W[s] = h, w
+        self.frames.n_images, self.frames.H0, self.frames.W0 = D, H, W
+        self.ws = torch.empty(_lib.load().dvsof_loss_workspace_bytes(self._sized(self.fwd)),
+                              dtype=torch.uint8, device=dev)  # tile records + ticket, forward only
+        self.ws_ptr = _lib.ptr(self.ws)
+
+    @staticmethod
+    def _sized(sc):
+        for s in range(sc.n_scales):                         # workspace_bytes validates non-null
+            sc.flow[s] = sc.images[s] = 1
+        return sc
+
+    def fill(self, sc, base, flows, grad_base=None):
+        for s in range(self.S):
+            sc.flow[s] = flows[s].data_ptr()
+            sc.images[s] = base + 4 * self.offs[s]
+            if grad_base is not None:
+                sc.grad_flow[s] = grad_base + 4 * self.goffs[s]
+
+
 class _MultiscaleLoss(torch.autograd.Function):
     """utils/loss.py:179-214 forward in ONE library call (matching + chained pyramid + fused
     terms, kernels chained on the stream with programmatic dependent launch)."""
@@ -120,36 +165,42 @@ class _MultiscaleLoss(torch.autograd.Function):
     def forward(ctx, owner, images, flow_ts, flow_sample_idx, timestamps, sample_idx, *flows):
         dev = images.device
         D, _, H, W = images.shape
-        S, P = len(flows), flows[0].shape[0]
-        lvl_sizes = [D * f.shape[-2] * f.shape[-1] for f in flows]
+        plan = owner._plan(dev, flows[0].shape[0], D, H, W, flows)
+        S = plan.S
         with torch.cuda.device(dev):
-            # one allocation per call: pyramid levels | match_idx | n_bad | terms (the first three
-            # are what backward needs, so they cannot live in a buffer shared between calls)
-            buf = torch.empty(_flat_len(lvl_sizes + [2 * P, S * P, 3 * S]), dtype=torch.float32, device=dev)
-            pieces = _carve(buf, lvl_sizes + [2 * P, S * P, 3 * S])
-            levels = [pc.view(D, f.shape[-2], f.shape[-1]) for pc, f in zip(pieces, flows)]
-            match_idx, n_bad, terms = pieces[S].view(torch.int32), pieces[S + 1].view(torch.int32), pieces[S + 2]
-            sc = _scale_struct(flows, levels)
-            fr = _lib.LossFrames()
-            fr.images, fr.n_images, fr.H0, fr.W0 = images.data_ptr(), D, H, W
+            # one allocation per call: what backward needs (levels, match_idx, n_bad) cannot live
+            # in a buffer shared between calls
+            buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
+            base = buf.data_ptr()
+            plan.fill(plan.fwd, base, flows)
+            fr = plan.frames
+            fr.images = images.data_ptr()
             fr.flow_ts, fr.flow_sample_idx = flow_ts.data_ptr(), flow_sample_idx.data_ptr()
             fr.timestamps, fr.sample_idx = timestamps.data_ptr(), sample_idx.data_ptr()
-            ws = owner._workspace(sc, dev)
             st = _lib.status_for(dev)
             st.flush()
-            _lib.call('dvsof_multiscale_loss_forward', sc, fr, _lib.ptr(match_idx), _lib.ptr(terms),
-                      _lib.ptr(n_bad), _lib.ptr(ws), _lib.ptr(st.word), _lib.stream_ptr(dev))
+            o = plan.offs
+            _lib.call('dvsof_multiscale_loss_forward', plan.fwd, fr, base + 4 * o[S], base + 4 * o[S + 2],
+                      base + 4 * o[S + 1], plan.ws_ptr, _lib.ptr(st.word), _lib.stream_ptr(dev))
             st.after_call()                                              # loss.py:193 asserts
-        ctx.n_scales = S
-        ctx.save_for_backward(match_idx, n_bad, *levels, *flows)
-        return terms
+        ctx.plan = plan
+        ctx.save_for_backward(buf, *flows)
+        return buf[o[S + 2]:o[S + 2] + 3 * S]
 
     @staticmethod
     def backward(ctx, grad_terms):
-        S = ctx.n_scales
-        match_idx, n_bad = ctx.saved_tensors[:2]
-        levels, flows = ctx.saved_tensors[2:2 + S], ctx.saved_tensors[2 + S:]
-        return (None,) * 6 + tuple(_backward(match_idx, n_bad, levels, flows, grad_terms))
+        plan = ctx.plan
+        buf, flows = ctx.saved_tensors[0], ctx.saved_tensors[1:]
+        dev, S, o = buf.device, plan.S, plan.offs
+        grad_terms = grad_terms.contiguous()
+        with torch.cuda.device(dev):
+            gbuf = torch.empty(plan.gtotal, dtype=torch.float32, device=dev)
+            base = buf.data_ptr()
+            plan.fill(plan.bwd, base, flows, gbuf.data_ptr())
+            _lib.call('dvsof_warp_loss_backward', plan.bwd, base + 4 * o[S], _lib.ptr(grad_terms),
+                      base + 4 * o[S + 1], _lib.stream_ptr(dev))
+        grads = tuple(gbuf[g:g + n].view(f.shape) for g, n, f in zip(plan.goffs, plan.gsizes, flows))
+        return (None,) * 6 + grads
 
 
 def _check_shapes(owner, N, H, W):
@@ -203,15 +254,15 @@ class Losses:
     def __init__(self, shapes, batch_size, device, timers=FakeTimer()):
         self.losses = [Loss(shape, batch_size, device, timers) for shape in shapes]
         self.timers = timers
-        self._ws = {}
+        self._plans = {}
 
-    def _workspace(self, sc, dev):
-        key = (dev, sc.n_pred)
-        ws = self._ws.get(key)
-        if ws is None:   # tile records + ticket; only live inside one forward call
-            ws = self._ws[key] = torch.empty(_lib.load().dvsof_loss_workspace_bytes(sc),
-                                             dtype=torch.uint8, device=dev)
-        return ws
+    def _plan(self, dev, P, D, H, W, flows):
+        shapes = tuple((f.shape[-2], f.shape[-1]) for f in flows)
+        key = (dev, P, D, H, W, shapes)
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = self._plans[key] = _Plan(dev, P, D, H, W, shapes)
+        return plan
 
     def terms(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
         """The 3*S terms as ONE autograd-connected tensor

@@ -123,6 +123,13 @@ int dvsof_map_events_write(const float* events, int64_t n_events, int32_t n_cols
                            int32_t W, const void* lut_ws, const void* ev_ws, float* out,
                            void* stream);
 
+/* utils/data.py:139-152 frame_generator: out[k] = np.searchsorted(t, bounds[k], side='right') for
+ * every window boundary (frames.ravel()); t sorted ascending, fp32 (elem_size 4) or fp64 (8),
+ * compared in fp64 as numpy does.  The (start, stop) offset pairs slice the event arrays per
+ * evaluation window (utils/testing.py:64) without leaving the device. */
+int dvsof_window_offsets(const void* t, int32_t elem_size, int64_t n_events, const double* bounds,
+                         int64_t n_bounds, int64_t* out, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Multiscale warp loss.  Replaces utils/loss.py:121-171 (Loss.__call__), :179-214
  * (Losses.__call__) and autograd's backward of both.

@@ -166,3 +166,23 @@ def test_default_path_selection_large_stream_is_exact():
     got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
     want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
     assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_deferred_validation_reports_without_blocking():
+    """Status.mode 'deferred': the call returns without a host sync; the error surfaces at
+    `synchronize()` (or at a later call once the async copy of the status word has landed)."""
+    from dvs_of_training_framework_b200 import _lib
+    ev, ts, sidx = synth_events(1, 2, 32, 32, 100)
+    ev['polarity'][7] = 0
+    st = _lib.status_for(torch.device('cuda', torch.cuda.current_device()))
+    old = _lib.Status.mode
+    _lib.Status.mode = 'deferred'
+    try:
+        dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (32, 32))     # no raise here
+        with pytest.raises(AssertionError, match='polarity'):
+            st.synchronize()
+        good, ts2, sidx2 = synth_events(2, 2, 32, 32, 100)
+        dv.compute_event_image(_cuda(good), ts2.cuda(), sidx2.cuda(), (32, 32))
+        st.synchronize()                                                         # clean again
+    finally:
+        _lib.Status.mode = old

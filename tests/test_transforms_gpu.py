@@ -88,3 +88,24 @@ def test_count_image_large_and_bad_pixel():
     # CUDA tensors in -> CUDA tensor out
     out = dv.get_count_image([torch.tensor(x).cuda(), torch.tensor(y).cuda()], (480, 640))
     assert out.is_cuda and np.array_equal(out.cpu().numpy().astype(np.uint64), want)
+
+
+@pytest.mark.parametrize('dtype', [np.float32, np.float64])
+def test_frame_generator_matches_reference_slicing(dtype):
+    """utils/data.py:139-152 (used by utils/testing.py:64): searchsorted(side='right') windows,
+    including duplicates of a boundary value, empty windows and windows past the last event."""
+    from dvs_of_training_framework_b200 import data as dd
+    rng = np.random.default_rng(4)
+    n = 5000
+    t = np.sort(rng.uniform(0, 1, n)).astype(dtype)
+    t[100:110] = t[100]                                    # ties on a boundary
+    ev = [rng.integers(0, 346, n), rng.integers(0, 260, n), t, rng.choice([-1, 1], n)]
+    frames = [(0.0, 0.1), (float(t[100]), 0.5), (0.5, 0.5), (0.9, 2.0), (-1.0, 0.0)]
+    want = np.searchsorted(t, np.array(frames).ravel(), side='right').reshape(-1, 2)
+    got = dd.frame_offsets(t, frames).cpu().numpy()
+    assert np.array_equal(got, want)
+    for (e, start, stop), (a, b), (fs, fe) in zip(dd.frame_generator(ev, frames), want, frames):
+        assert start == fs and stop == fe
+        for comp, ref in zip(e, ev):
+            assert np.array_equal(comp, ref[a:b])
+    assert dd.frame_offsets(t[:0], frames).sum() == 0
