@@ -241,8 +241,32 @@ def bench_loss(name, K, W, dev):
     fwd_ms = float(np.mean(time_steps(fwd, K, W, flush)))
     bwd_ms = float(np.mean(time_steps(bwd, K, W, flush)))
     px = sum(B * f.shape[-2] * f.shape[-1] for f in fl)
+    # the fused training sweep alone (terms + d(loss)/d(flow) in one pass: 16 B read + 8 B written
+    # per pixel), n_bad filled by one untimed call with the counting pre-pass
+    import ctypes
+    coef = (ctypes.c_float * (3 * S))(*([0.5 / S] * S + [1.0 / S] * S + [1.0 / S] * S))
+    loss1 = torch.empty(1, device=dev)
+    fus = lambda cp: L.call('dvsof_warp_loss_fused', sc, L.ptr(match), coef, L.ptr(terms), L.ptr(loss1),  # noqa: E731
+                            L.ptr(n_bad), L.ptr(ws), cp, sp)
+    fus(1)
+    fused_ms = float(np.mean(time_steps(lambda: fus(0), K, W, flush)))
+    fusedc_ms = float(np.mean(time_steps(lambda: fus(1), K, W, flush)))
     return dict(workload=name, samples=B, step_ms=step_ms, bytes=loss_bytes(B, H, Wd),
-                fwd_ms=fwd_ms, bwd_ms=bwd_ms, fwd_bytes=16 * px, bwd_bytes=24 * px, launches_per_step=7)
+                fwd_ms=fwd_ms, bwd_ms=bwd_ms, fwd_bytes=16 * px, bwd_bytes=24 * px,
+                fused_ms=fused_ms, fused_with_count_ms=fusedc_ms, fused_bytes=24 * px,
+                launches_per_step=9)
+
+
+def fused_kernels(r, peak):
+    """Kernel-level loss figures: the fused training sweep (24 B/pixel moved; SURVEY 8d counts the
+    same work as 16 + 24 = 40 B/pixel for separate forward and backward passes) and the generic
+    forward / backward kernels behind Losses.__call__."""
+    frac = lambda b, ms: b / (ms * 1e-3) / 1e9 / peak  # noqa: E731
+    return {'fused_ms': r['fused_ms'], 'fused_with_count_ms': r['fused_with_count_ms'],
+            'fused_hbm_frac_24B_per_px': frac(r['fused_bytes'], r['fused_ms']),
+            'fused_hbm_frac_survey_40B_per_px': frac(r['fwd_bytes'] + r['bwd_bytes'], r['fused_ms']),
+            'fwd_ms': r['fwd_ms'], 'bwd_ms': r['bwd_ms'],
+            'fwd_hbm_frac': frac(r['fwd_bytes'], r['fwd_ms']), 'bwd_hbm_frac': frac(r['bwd_bytes'], r['bwd_ms'])}
 
 
 def make_train_batch(B, H, W, n, T, seed):
@@ -534,10 +558,8 @@ def main():
                       'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
                       'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
                                    'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
-                                   'note': 'whole API step: combined_loss (1 library call = match + 4 resize + fused forward, PDL-chained) + dot + backward (1 launch); host-bound'},
-                      'kernels': {'fwd_ms': loss['fwd_ms'], 'bwd_ms': loss['bwd_ms'],
-                                  'fwd_hbm_frac': loss['fwd_bytes'] / (loss['fwd_ms'] * 1e-3) / 1e9 / peak,
-                                  'bwd_hbm_frac': loss['bwd_bytes'] / (loss['bwd_ms'] * 1e-3) / 1e9 / peak}},
+                                   'note': 'whole API step: combined_loss = 1 library call (memset + match + 4 resize + border count + fused terms-and-gradient sweep, PDL-chained); loss.backward() = 1 no-op rescale launch; host-bound at this size'},
+                      'kernels': fused_kernels(loss, peak)},
         'workloads': {},
     }
     if train is not None:
@@ -551,9 +573,7 @@ def main():
             line['workloads'][name] = {'samples_per_s': world * r['samples'] / (r['step_ms'] * 1e-3),
                                        'ms_per_step': r['step_ms'],
                                        'hbm_frac_step': r['bytes'] / (r['step_ms'] * 1e-3) / 1e9 / peak,
-                                       'fwd_kernel_ms': r['fwd_ms'], 'bwd_kernel_ms': r['bwd_ms'],
-                                       'fwd_kernel_hbm_frac': r['fwd_bytes'] / (r['fwd_ms'] * 1e-3) / 1e9 / peak,
-                                       'bwd_kernel_hbm_frac': r['bwd_bytes'] / (r['bwd_ms'] * 1e-3) / 1e9 / peak}
+                                       'kernels': fused_kernels(r, peak)}
         else:
             line['workloads'][name] = {'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6,
                                        'ms_per_step': r['step_ms'], 'kernel_ms': r['kernel_ms'],

@@ -71,6 +71,12 @@ _SIGNATURES = {
                                       + [C.c_void_p] * 6),
     'dvsof_warp_loss_backward': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_void_p]),
+    'dvsof_multiscale_loss_fused': (C.c_int, [C.POINTER(LossScales), C.POINTER(LossFrames),
+                                              C.POINTER(C.c_float)] + [C.c_void_p] * 7),
+    'dvsof_warp_loss_fused': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.POINTER(C.c_float),
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                        C.c_void_p]),
+    'dvsof_scale_gradients': (C.c_int, [C.POINTER(LossScales), C.c_void_p, C.c_void_p]),
 }
 
 

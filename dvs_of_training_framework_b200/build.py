@@ -22,7 +22,8 @@ def needs_build():
     if not LIB.exists():
         return True
     t = LIB.stat().st_mtime
-    deps = [CSRC / s for s in SOURCES] + [CSRC / 'common.cuh', PKG.parent / 'include' / 'dvsof.h']
+    deps = [CSRC / s for s in SOURCES] + sorted(CSRC.glob('*.cuh')) + sorted(CSRC.glob('*.h')) + \
+        [PKG.parent / 'include' / 'dvsof.h']
     return any(d.stat().st_mtime > t for d in deps)
 
 

@@ -49,6 +49,24 @@ DVSOF_HD float dvsof_div_by_const(float a, float h, float r) {
 #endif
 }
 
+// Branch-free variant for the sampling grid g = a / h - 1 of the warp-loss kernels (5 instructions,
+// no slow path): bit-identical to a / h for 1e-30 <= |a| < 1e30 and a == 0.  Outside that range
+// the callers do not need the last bit: for tinier |a| the quotient only has to vanish against the
+// "- 1" that follows (it does: |q| < 1e-29), for larger or non-finite |a| it only has to keep
+// sign, magnitude class (huge / inf / NaN) -- RN(a * r) does.
+DVSOF_HD float dvsof_div_by_const_grid(float a, float h, float r) {
+#ifdef __CUDA_ARCH__
+    const float q0 = __fmul_rn(a, r);
+    const float rem = __fmaf_rn(-q0, h, a);
+    const float q = __fmaf_rn(rem, r, q0);
+#else
+    const float q0 = a * r;
+    const float rem = fmaf(-q0, h, a);
+    const float q = fmaf(rem, r, q0);
+#endif
+    return fabsf(a) < DVSOF_EXACT_DIV_MAX ? q : q0;
+}
+
 // host: correctly rounded fp32 reciprocal of h (h > 0, normal), and whether the fast path may be
 // used for this divisor (significand not all ones, sane exponent)
 static inline float dvsof_recip_rn(float h) {

@@ -11,6 +11,7 @@
 // ix = (g + 1) * ((S-1)/2) as ATen's CPU grid_sampler does for align_corners=True.
 #include "common.cuh"
 #include "exact_div.h"
+#include <stdlib.h>
 
 namespace dvsof {
 
@@ -47,6 +48,7 @@ struct ScaleTable {
     int tiles_x[DVSOF_MAX_SCALES], tiles_y[DVSOF_MAX_SCALES];
     int cta_begin[DVSOF_MAX_SCALES + 1];
     float rx[DVSOF_MAX_SCALES], ry[DVSOF_MAX_SCALES];   // RN(1/((W-1)/2)), RN(1/((H-1)/2)); 0 = plain division
+    float coef[3 * DVSOF_MAX_SCALES];                   // fused pass: d(loss)/d(term[k][s]) at [k * MAX + s]
     const float* flow[DVSOF_MAX_SCALES];
     const float* images[DVSOF_MAX_SCALES];
     float* grad_flow[DVSOF_MAX_SCALES];
@@ -216,7 +218,7 @@ __device__ __forceinline__ void stage_flow_tile(float* __restrict__ Fs, const fl
 // record: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
 constexpr int kMaxPairs = 256;     // (scale, prediction) pairs reduced per finalize pass
 __device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, double (*pair_acc)[6]);
+                               int32_t* n_bad, float* loss_out, double (*pair_acc)[6]);
 
 __global__ void __launch_bounds__(kLossThreads)
 warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
@@ -289,21 +291,21 @@ warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     __syncthreads();
     if (!is_last) return;
     __threadfence();
-    finalize_terms(tab, partials, terms, n_bad, wacc);
+    finalize_terms(tab, partials, terms, n_bad, nullptr, wacc);
     if (threadIdx.x == 0) *ticket = 0u;   // self-resetting for the next call on this workspace
 }
 
-// run by ONE CTA (kLossThreads threads): warp w sums the tile records of the (scale, prediction)
+// run by ONE CTA (any whole number of warps): warp w sums the tile records of the (scale, prediction)
 // pairs w, w+8, ... (all scales in flight at once: one round of loads, one barrier) in a fixed
 // order in fp64; thread s then combines scale s.
 __device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, double (*pair_acc)[6]) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+                               int32_t* n_bad, float* loss_out, double (*pair_acc)[6]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const int P = tab.n_pred, S = tab.n_scales;
     double tot[6] = {0, 0, 0, 0, 0, 0};            // thread s < S: running totals of scale s
     for (int p0 = 0; p0 < P; p0 += kMaxPairs / DVSOF_MAX_SCALES) {
         const int pn = min(P - p0, kMaxPairs / DVSOF_MAX_SCALES);
-        for (int q = warp; q < S * pn; q += kLossThreads / 32) {
+        for (int q = warp; q < S * pn; q += n_warps) {
             const int s = q / pn, n = p0 + (q - s * pn);
             const int per = tab.tiles_x[s] * tab.tiles_y[s];
             double a[7] = {0, 0, 0, 0, 0, 0, 0};
@@ -322,7 +324,7 @@ __device__ void finalize_terms(const ScaleTable& tab, const float* partials, flo
                 const double nb = a[6];
                 for (int k = 0; k < 5; ++k) pair_acc[q][k] = a[k];
                 pair_acc[q][5] = nb > 0 ? a[5] / (2.0 * nb * (double)P) : 0.0;   // loss.py:99-113
-                n_bad[s * P + n] = (int32_t)nb;
+                if (n_bad) n_bad[s * P + n] = (int32_t)nb;
             }
         }
         __syncthreads();
@@ -342,6 +344,15 @@ __device__ void finalize_terms(const ScaleTable& tab, const float* partials, flo
         terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
         terms[S + s] = (float)(tot[0] / ((double)P * H * W));                // loss.py:33
         terms[2 * S + s] = (float)tot[5];
+    }
+    if (loss_out) {                       // fused pass: loss = sum_k sum_s coef[k][s] * term[k][s]
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float l = 0.f;
+            for (int k = 0; k < 3; ++k)
+                for (int s = 0; s < S; ++s) l = fmaf(tab.coef[k * DVSOF_MAX_SCALES + s], terms[k * S + s], l);
+            *loss_out = l;
+        }
     }
 }
 
@@ -431,12 +442,34 @@ warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __re
     }
 }
 
+// d(loss)/d(flow) *= factor, in place, for all scales in one launch; nothing is touched when the
+// factor is exactly 1 (loss.backward() of the unscaled training loss).
+__global__ void __launch_bounds__(256)
+scale_gradients_kernel(const __grid_constant__ ScaleTable tab, const float* __restrict__ factor) {
+    const float f = *factor;
+    if (f == 1.f) return;
+    for (int s = 0; s < tab.n_scales; ++s) {
+        float* g = tab.grad_flow[s];
+        const size_t n = (size_t)tab.n_pred * 2 * tab.H[s] * tab.W[s];
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+            g[i] *= f;
+    }
+}
+
 }  // namespace dvsof
+
+#include "loss_strip.cuh"
 
 // ---------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------
 using namespace dvsof;
+
+// DVSOF_LOSS_LEGACY=1 selects the first-generation tile kernels (kept for A/B measurements)
+static bool legacy_loss() {
+    static const bool v = [] { const char* e = getenv("DVSOF_LOSS_LEGACY"); return e && e[0] == '1'; }();
+    return v;
+}
 
 static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need_grad) {
     if (!sc) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: null scale table");
@@ -462,9 +495,14 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
         tab->grad_flow[s] = sc->grad_flow[s];
         tab->cta_begin[s] = (int)begin;
         begin += (int64_t)tab->tiles_x[s] * tab->tiles_y[s] * sc->n_pred;
-        if (begin > INT32_MAX) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: too many tiles");
+        // 2^23 tiles: the float tile decode of the strip kernels stays exact; 2*H*W < 2^31: 32-bit
+        // offsets inside one prediction's flow block
+        if (begin > (1 << 23)) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: too many tiles");
+        if ((int64_t)sc->H[s] * sc->W[s] >= (1 << 30))
+            return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: scale %d too large", s);
     }
     for (int s = sc->n_scales; s <= DVSOF_MAX_SCALES; ++s) tab->cta_begin[s] = (int)begin;
+    for (int i = 0; i < 3 * DVSOF_MAX_SCALES; ++i) tab->coef[i] = 0.f;
     return DVSOF_OK;
 }
 
@@ -482,8 +520,13 @@ static int launch_forward(const ScaleTable& tab, const int32_t* match_idx, float
                           int32_t* n_bad, void* workspace, cudaStream_t stream, bool pdl) {
     float* partials = reinterpret_cast<float*>(workspace);
     unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
-    return launch_kernel("warp_loss_fwd_kernel", warp_loss_fwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
-                         kLossThreads, 0, stream, pdl, tab, match_idx, partials, ticket, terms, n_bad);
+    if (legacy_loss())
+        return launch_kernel("warp_loss_fwd_kernel", warp_loss_fwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
+                             kLossThreads, 0, stream, pdl, tab, match_idx, partials, ticket, terms, n_bad);
+    return launch_kernel("warp_loss_strip_kernel<fwd>", warp_loss_strip_kernel<true, false>,
+                         tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, pdl, tab, match_idx,
+                         (const float*)nullptr, (const int32_t*)nullptr, partials, ticket, terms, n_bad,
+                         (float*)nullptr);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -506,8 +549,13 @@ extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!match_idx || !grad_terms || !n_bad)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_backward: null buffer");
-    return launch_kernel("warp_loss_bwd_kernel", warp_loss_bwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
-                         kLossThreads, 0, (cudaStream_t)stream_, false, tab, match_idx, grad_terms, n_bad);
+    if (legacy_loss())
+        return launch_kernel("warp_loss_bwd_kernel", warp_loss_bwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
+                             kLossThreads, 0, (cudaStream_t)stream_, false, tab, match_idx, grad_terms, n_bad);
+    return launch_kernel("warp_loss_strip_kernel<bwd>", warp_loss_strip_kernel<false, true>,
+                         tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, (cudaStream_t)stream_, false, tab,
+                         match_idx, grad_terms, n_bad, (float*)nullptr, (unsigned*)nullptr, (float*)nullptr,
+                         (int32_t*)nullptr, (float*)nullptr);
 }
 
 static int launch_match(const float* flow_ts, const int64_t* flow_sample_idx, int64_t P,
@@ -546,21 +594,10 @@ extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, i
     return launch_resize(src, D, Hin, Win, dst, Hout, Wout, (cudaStream_t)stream_, false);
 }
 
-// Whole forward of utils/loss.py:179-214 in one call: timestamp matching, the chained pyramid
-// (each level resized from the previous one, line 210) into the caller's level buffers
-// scales->images[s], the fused per-scale terms.  Kernels are chained with programmatic dependent
-// launch, so there is no host work and no idle gap between them.
-extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
-                                             const dvsof_loss_frames_t* fr, int32_t* match_idx,
-                                             float* terms, int32_t* n_bad, void* workspace,
-                                             uint32_t* status, void* stream_) {
-    ScaleTable tab;
-    if (int rc = build_table(sc, &tab, false)) return rc;
-    if (!fr || !fr->images || fr->n_images < 1 || fr->H0 < 1 || fr->W0 < 1 || !match_idx || !terms ||
-        !n_bad || !workspace || !status)
-        return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_forward: bad arguments");
-    cudaStream_t stream = (cudaStream_t)stream_;
-    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+// matching + chained pyramid (utils/loss.py:182-210), PDL-chained on the stream
+static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t* fr,
+                                    int32_t* match_idx, uint32_t* status, unsigned* ticket,
+                                    cudaStream_t stream) {
     if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
                               fr->sample_idx, fr->n_images, match_idx, status, ticket, stream))
         return rc;
@@ -572,5 +609,100 @@ extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
             return rc;
         src = dst; Hin = sc->H[s]; Win = sc->W[s];
     }
+    return DVSOF_OK;
+}
+
+static bool frames_ok(const dvsof_loss_frames_t* fr) {
+    return fr && fr->images && fr->n_images >= 1 && fr->H0 >= 1 && fr->W0 >= 1;
+}
+
+// Whole forward of utils/loss.py:179-214 in one call: timestamp matching, the chained pyramid
+// (each level resized from the previous one, line 210) into the caller's level buffers
+// scales->images[s], the fused per-scale terms.  Kernels are chained with programmatic dependent
+// launch, so there is no host work and no idle gap between them.
+extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
+                                             const dvsof_loss_frames_t* fr, int32_t* match_idx,
+                                             float* terms, int32_t* n_bad, void* workspace,
+                                             uint32_t* status, void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, false)) return rc;
+    if (!frames_ok(fr) || !match_idx || !terms || !n_bad || !workspace || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_forward: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ticket, stream)) return rc;
     return launch_forward(tab, match_idx, terms, n_bad, workspace, stream, true);
+}
+
+// The training pass: the same forward plus d(loss)/d(flow) of
+// loss = sum_k sum_s coef[k*n_scales + s] * term[k][s] (utils/training.py:12-24 gives
+// coef = w_k / n_scales) written to scales->grad_flow in the SAME sweep over the flow.
+extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
+                                           const dvsof_loss_frames_t* fr, const float* coef,
+                                           int32_t* match_idx, float* terms, float* loss,
+                                           int32_t* n_bad, void* workspace, uint32_t* status,
+                                           void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, true)) return rc;
+    if (!frames_ok(fr) || !coef || !match_idx || !terms || !loss || !n_bad || !workspace || !status)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_fused: bad arguments");
+    for (int k = 0; k < 3; ++k)
+        for (int s = 0; s < sc->n_scales; ++s) tab.coef[k * DVSOF_MAX_SCALES + s] = coef[k * sc->n_scales + s];
+    cudaStream_t stream = (cudaStream_t)stream_;
+    float* partials = reinterpret_cast<float*>(workspace);
+    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
+    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ticket, stream)) return rc;
+    const int grid = tab.cta_begin[DVSOF_MAX_SCALES];
+    if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel, grid, kSThreads, 0,
+                               stream, true, tab, n_bad))
+        return rc;
+    return launch_kernel("warp_loss_strip_kernel<fused>", warp_loss_strip_kernel<true, true>, grid,
+                         kSThreads, 0, stream, true, tab, (const int32_t*)match_idx,
+                         (const float*)nullptr, (const int32_t*)n_bad, partials, ticket, terms,
+                         (int32_t*)nullptr, loss);
+}
+
+// The fused sweep on ready-made pyramid levels (single-scale Loss objects, kernel-level timing):
+// count_pass != 0 runs the out-of-border counting pre-pass into n_bad first; 0 reuses n_bad.
+extern "C" int dvsof_warp_loss_fused(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
+                                     const float* coef, float* terms, float* loss, int32_t* n_bad,
+                                     void* workspace, int32_t count_pass, void* stream_) {
+    ScaleTable tab;
+    if (int rc = build_table(sc, &tab, true)) return rc;
+    if (!match_idx || !coef || !terms || !loss || !n_bad || !workspace)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_fused: null buffer");
+    for (int k = 0; k < 3; ++k)
+        for (int s = 0; s < sc->n_scales; ++s) tab.coef[k * DVSOF_MAX_SCALES + s] = coef[k * sc->n_scales + s];
+    cudaStream_t stream = (cudaStream_t)stream_;
+    float* partials = reinterpret_cast<float*>(workspace);
+    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    const int grid = tab.cta_begin[DVSOF_MAX_SCALES];
+    cudaError_t e = cudaMemsetAsync(ticket, 0, 4, stream);
+    if (e == cudaSuccess && count_pass)
+        e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "warp_loss_fused memset: %s", cudaGetErrorString(e));
+    if (count_pass)
+        if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel, grid, kSThreads, 0,
+                                   stream, false, tab, n_bad))
+            return rc;
+    return launch_kernel("warp_loss_strip_kernel<fused>", warp_loss_strip_kernel<true, true>, grid,
+                         kSThreads, 0, stream, false, tab, match_idx, (const float*)nullptr,
+                         (const int32_t*)n_bad, partials, ticket, terms, (int32_t*)nullptr, loss);
+}
+
+// grad_flow[s] *= *factor for all scales (backward of the fused pass when the incoming gradient
+// of the loss is not 1); a no-op launch when it is.
+extern "C" int dvsof_scale_gradients(const dvsof_loss_scales_t* sc, const float* factor, void* stream_) {
+    ScaleTable tab;
+    if (!sc || !factor) return fail(DVSOF_ERR_INVALID_ARGUMENT, "scale_gradients: null argument");
+    dvsof_loss_scales_t tmp = *sc;
+    for (int s = 0; s < tmp.n_scales && s < DVSOF_MAX_SCALES; ++s) {   // flow / images are not read here
+        if (!tmp.flow[s]) tmp.flow[s] = tmp.grad_flow[s];
+        if (!tmp.images[s]) tmp.images[s] = tmp.grad_flow[s];
+    }
+    if (int rc = build_table(&tmp, &tab, true)) return rc;
+    return launch_kernel("scale_gradients_kernel", scale_gradients_kernel, kNumSMs * 8, 256, 0,
+                         (cudaStream_t)stream_, false, tab, factor);
 }

@@ -121,7 +121,7 @@ class _Plan:
     def __init__(self, dev, P, D, H, W, shapes):
         self.S = S = len(shapes)
         self.shapes = shapes
-        sizes = [D * h * w for h, w in shapes] + [2 * P, S * P, 3 * S]
+        sizes = [D * h * w for h, w in shapes] + [2 * P, S * P, 3 * S, 1]   # .. | fused: the loss
         self.offs, off = [], 0
         for n in sizes:
             self.offs.append(off)
@@ -157,6 +157,62 @@ class _Plan:
                 sc.grad_flow[s] = grad_base + 4 * self.goffs[s]
 
 
+def _fill_frames(plan, images, flow_ts, flow_sample_idx, timestamps, sample_idx):
+    fr = plan.frames
+    fr.images = images.data_ptr()
+    fr.flow_ts, fr.flow_sample_idx = flow_ts.data_ptr(), flow_sample_idx.data_ptr()
+    fr.timestamps, fr.sample_idx = timestamps.data_ptr(), sample_idx.data_ptr()
+    return fr
+
+
+class _FusedTrainingLoss(torch.autograd.Function):
+    """utils/training.py:12-24 on top of utils/loss.py:179-214 as ONE sweep: the 3*S terms, the
+    weighted loss and d(loss)/d(flow) of every scale come out of the same kernel
+    (`dvsof_multiscale_loss_fused`); backward only rescales the stored gradient by the incoming
+    d/d(loss) -- on device, and not at all when that is exactly 1."""
+
+    @staticmethod
+    def forward(ctx, owner, coef, images, flow_ts, flow_sample_idx, timestamps, sample_idx, *flows):
+        dev = images.device
+        D, _, H, W = images.shape
+        plan = owner._plan(dev, flows[0].shape[0], D, H, W, flows)
+        S, o = plan.S, plan.offs
+        with torch.cuda.device(dev):
+            buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
+            gbuf = torch.empty(plan.gtotal, dtype=torch.float32, device=dev)
+            base = buf.data_ptr()
+            plan.fill(plan.bwd, base, flows, gbuf.data_ptr())
+            fr = _fill_frames(plan, images, flow_ts, flow_sample_idx, timestamps, sample_idx)
+            st = _lib.status_for(dev)
+            st.flush()
+            _lib.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S],
+                      base + 4 * o[S + 2], base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr,
+                      _lib.ptr(st.word), _lib.stream_ptr(dev))
+            st.after_call()                                              # loss.py:193 asserts
+        ctx.plan, ctx.gbuf, ctx.buf, ctx.shapes = plan, gbuf, buf, [f.shape for f in flows]
+        loss = buf[o[S + 3]:o[S + 3] + 1].view(())
+        terms = buf[o[S + 2]:o[S + 2] + 3 * S]
+        ctx.mark_non_differentiable(terms)
+        return loss, terms
+
+    @staticmethod
+    def backward(ctx, grad_loss, _grad_terms):
+        plan, gbuf = ctx.plan, ctx.gbuf
+        if gbuf is None:
+            raise RuntimeError('the fused training loss stores its gradient once: a second backward '
+                               '(retain_graph) needs Losses.__call__ / Losses.terms')
+        dev = gbuf.device
+        grad_loss = _f32(grad_loss, 'grad_loss')
+        with torch.cuda.device(dev):
+            sc = plan.bwd       # only the gradient pointers are read by the rescale
+            for s in range(plan.S):
+                sc.grad_flow[s] = gbuf.data_ptr() + 4 * plan.goffs[s]
+            _lib.call('dvsof_scale_gradients', sc, _lib.ptr(grad_loss), _lib.stream_ptr(dev))
+        grads = tuple(gbuf[g:g + n].view(shp) for g, n, shp in zip(plan.goffs, plan.gsizes, ctx.shapes))
+        ctx.gbuf = ctx.buf = None
+        return (None,) * 7 + grads
+
+
 class _MultiscaleLoss(torch.autograd.Function):
     """utils/loss.py:179-214 forward in ONE library call (matching + chained pyramid + fused
     terms, kernels chained on the stream with programmatic dependent launch)."""
@@ -173,10 +229,7 @@ class _MultiscaleLoss(torch.autograd.Function):
             buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
             base = buf.data_ptr()
             plan.fill(plan.fwd, base, flows)
-            fr = plan.frames
-            fr.images = images.data_ptr()
-            fr.flow_ts, fr.flow_sample_idx = flow_ts.data_ptr(), flow_sample_idx.data_ptr()
-            fr.timestamps, fr.sample_idx = timestamps.data_ptr(), sample_idx.data_ptr()
+            fr = _fill_frames(plan, images, flow_ts, flow_sample_idx, timestamps, sample_idx)
             st = _lib.status_for(dev)
             st.flush()
             o = plan.offs
@@ -255,6 +308,7 @@ class Losses:
         self.losses = [Loss(shape, batch_size, device, timers) for shape in shapes]
         self.timers = timers
         self._plans = {}
+        self._coefs = {}
 
     def _plan(self, dev, P, D, H, W, flows):
         shapes = tuple((f.shape[-2], f.shape[-1]) for f in flows)
@@ -264,9 +318,7 @@ class Losses:
             plan = self._plans[key] = _Plan(dev, P, D, H, W, shapes)
         return plan
 
-    def terms(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
-        """The 3*S terms as ONE autograd-connected tensor
-        [smoothness(s)..., photometric(s)..., outborder(s)...]; `__call__` returns views of it."""
+    def _checked(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
         S = len(flows)
         assert S == len(self.losses) and 1 <= S <= _lib.MAX_SCALES
         images = _f32(images, 'images')
@@ -281,10 +333,32 @@ class Losses:
         flow_ts = _f32(flow_ts, 'flow_ts')
         timestamps = _f32(timestamps, 'timestamps')
         assert flow_ts.numel() == 2 * P and timestamps.numel() == D and sample_idx.numel() == D
-        return _MultiscaleLoss.apply(self, images, flow_ts,
-                                     _lib.require_cuda(flow_sample_idx, 'flow_sample_idx', torch.int64),
-                                     timestamps, _lib.require_cuda(sample_idx, 'sample_idx', torch.int64),
-                                     *flows)
+        return (images, flow_ts, _lib.require_cuda(flow_sample_idx, 'flow_sample_idx', torch.int64),
+                timestamps, _lib.require_cuda(sample_idx, 'sample_idx', torch.int64), *flows)
+
+    def terms(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
+        """The 3*S terms as ONE autograd-connected tensor
+        [smoothness(s)..., photometric(s)..., outborder(s)...]; `__call__` returns views of it."""
+        return _MultiscaleLoss.apply(self, *self._checked(flows, flow_ts, flow_sample_idx, images,
+                                                          timestamps, sample_idx))
+
+    def combined(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx,
+                 weights=(0.5, 1, 1)):
+        """(loss, terms) with loss = sum_k weights[k] * mean_s(term[k][s]) (utils/training.py:12-24).
+        When a flow requires grad, the gradient is produced by the same kernel sweep as the terms
+        (`_FusedTrainingLoss`); `terms` is then a detached tensor (logging only)."""
+        args = self._checked(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
+        S = len(flows)
+        key = (S,) + tuple(float(w) for w in weights)
+        coef = self._coefs.get(key)
+        if coef is None:
+            vals = [w / S for w in key[1:] for _ in range(S)]
+            coef = self._coefs[key] = ((_lib.C.c_float * (3 * S))(*vals),
+                                       torch.tensor(vals, dtype=torch.float32, device=images.device))
+        if torch.is_grad_enabled() and any(f.requires_grad for f in args[5:]):
+            return _FusedTrainingLoss.apply(self, coef[0], *args)
+        flat = _MultiscaleLoss.apply(self, *args)
+        return torch.dot(flat, coef[1]), flat
 
     def __call__(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx):
         S = len(flows)

@@ -29,27 +29,16 @@ def _world():
     return 0, 1
 
 
-_WEIGHTS = {}
-
-
-def _weight_vector(weights, S, device):
-    key = (weights, S, device)
-    w = _WEIGHTS.get(key)
-    if w is None:
-        w = _WEIGHTS[key] = torch.tensor([wk / S for wk in weights for _ in range(S)],
-                                         dtype=torch.float32, device=device)
-    return w
-
-
 def combined_loss(evaluator, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx,
                   features, weights=[0.5, 1, 1]):
     """utils/training.py:12-24: loss = sum_k w_k * mean_s(term[k][s]), k over (smoothness,
-    photometric, outborder).  With the fused evaluator the 3*S terms are one tensor, so the
-    weighted sum is a single dot product (one node in the autograd graph instead of ~30)."""
-    if hasattr(evaluator, 'terms'):
-        flat = evaluator.terms(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
+    photometric, outborder).  The fused evaluator (`Losses.combined`) returns the weighted loss,
+    the 3*S terms and -- when a flow requires grad -- d(loss)/d(flow) from ONE kernel sweep (one
+    node in the autograd graph instead of ~30)."""
+    if hasattr(evaluator, 'combined'):
+        loss, flat = evaluator.combined(flows, flow_ts, flow_sample_idx, images, timestamps,
+                                        sample_idx, weights)
         S = flat.numel() // 3
-        loss = torch.dot(flat, _weight_vector(tuple(float(w) for w in weights), S, flat.device))
         parts = flat.unbind(0)
         return loss, (tuple(parts[:S]), tuple(parts[S:2 * S]), tuple(parts[2 * S:]))
     terms = evaluator(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)

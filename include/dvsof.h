@@ -184,6 +184,30 @@ int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* scales,
                                   float* terms, int32_t* n_bad, void* workspace, uint32_t* status,
                                   void* stream);
 
+/* The training pass of utils/training.py:12-24 + :186 (`combined_loss` then `loss.backward()`):
+ * everything dvsof_multiscale_loss_forward does PLUS, in the same sweep over the flow,
+ *   loss       = sum_k sum_s coef[k*n_scales + s] * term[k][s]      (coef [host] = w_k / n_scales)
+ *   grad_flow  = d(loss) / d(flow[s])                               (scales->grad_flow, all written)
+ * i.e. autograd's backward of utils/loss.py:121-171 for that fixed linear combination, without a
+ * second pass over flow and frames: 16 B/pixel read, 8 B/pixel written.  n_bad [dev int32
+ * n_scales*P] is filled by a counting pre-pass (the border term's gradient needs n_i).
+ * loss [dev] 1 float.  Deterministic. */
+int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* scales,
+                                const dvsof_loss_frames_t* frames, const float* coef,
+                                int32_t* match_idx, float* terms, float* loss, int32_t* n_bad,
+                                void* workspace, uint32_t* status, void* stream);
+
+/* The same fused sweep on ready-made pyramid levels scales->images[s] and a given match_idx
+ * (single-scale utils/loss.py:121-171 callers; kernel-level timing).  count_pass != 0: run the
+ * out-of-border counting pre-pass into n_bad first; 0: n_bad already holds the counts. */
+int dvsof_warp_loss_fused(const dvsof_loss_scales_t* scales, const int32_t* match_idx,
+                          const float* coef, float* terms, float* loss, int32_t* n_bad,
+                          void* workspace, int32_t count_pass, void* stream);
+
+/* grad_flow[s] *= *factor [dev, 1 float] for every scale, in place, one launch; returns without
+ * touching memory when *factor == 1 (backward of the fused pass: the incoming d/d(loss)). */
+int dvsof_scale_gradients(const dvsof_loss_scales_t* scales, const float* factor, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,19 @@ int main(int argc, char** argv) {
                 if (bad < 5) printf("mismatch S=%d a=%a want=%a got=%a\n", S, a, want, got);
                 ++bad;
             }
+            /* the branch-free grid variant: exact in [1e-30, 1e30), harmless outside (see header) */
+            const float gg = dvsof_div_by_const_grid(a, h, r), mag = fabsf(a);
+            int ok;
+            if (mag == 0.f || (mag >= DVSOF_EXACT_DIV_MIN && mag < DVSOF_EXACT_DIV_MAX))
+                ok = memcmp(&want, &gg, 4) == 0;
+            else if (mag < DVSOF_EXACT_DIV_MIN)
+                ok = (gg - 1.f) == (want - 1.f) && (gg + 1.f) == (want + 1.f);
+            else
+                ok = (gg != gg) == (want != want) && (gg != gg || ((gg < 0) == (want < 0) && fabsf(gg) > 1e20f));
+            if (!ok) {
+                if (bad < 5) printf("grid variant mismatch S=%d a=%a want=%a got=%a\n", S, a, want, gg);
+                ++bad;
+            }
         }
     }
     printf("checked=%ld mismatches=%ld skipped_divisors=%ld\n", total, bad, skipped);

@@ -247,3 +247,113 @@ def test_full_size_properties_cfg4():
     for f, pf in zip(flows, pflows):
         torch.testing.assert_close(pf.grad, 3.0 * f.grad[perm], rtol=RTOL, atol=ATOL)
         assert torch.isfinite(f.grad).all()
+
+
+# ------------------------------------------------------------------------------------------
+# fused training pass (dvsof_multiscale_loss_fused): loss, terms and gradients from ONE sweep
+# ------------------------------------------------------------------------------------------
+def _run_fused(inp, flows_cpu, weights=WEIGHTS, scale=None):
+    shapes = [tuple(f.shape[-2:]) for f in flows_cpu]
+    flows = [f.detach().clone().cuda().requires_grad_() for f in flows_cpu]
+    ev = dv.Losses(shapes, flows_cpu[0].shape[0], 'cuda')
+    loss, flat = ev.combined(flows, inp['flow_ts'].cuda(), inp['flow_sample_idx'].cuda(),
+                             inp['images'].cuda(), inp['timestamps'].cuda(), inp['sample_idx'].cuda(),
+                             weights)
+    (loss if scale is None else loss * scale).backward()
+    return flows, loss, flat
+
+
+@pytest.mark.parametrize('tag', ['a', 'b', 'c'])
+def test_fused_matches_reference_golden(golden, tag):
+    g = np.load(golden / f'loss_{tag}.npz')
+    inp = {k: torch.tensor(g[k]) for k in ('flow_ts', 'flow_sample_idx', 'timestamps', 'sample_idx')}
+    inp['images'] = torch.tensor(g['images']).float()
+    flows_cpu = [torch.tensor(g[f'flow{k}']) for k in range(4)]
+    flows, loss, flat = _run_fused(inp, flows_cpu)
+    np.testing.assert_allclose(flat.cpu().numpy().reshape(3, 4), g['terms'], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(float(loss), float(g['total']), rtol=RTOL, atol=ATOL)
+    assert not flat.requires_grad
+    assert_grads_close([f.grad for f in flows], [g[f'grad{k}'] for k in range(4)], inp, flows_cpu)
+
+
+@pytest.mark.parametrize('B,H,W,sigma,scale', [
+    (1, 260, 346, 3.0, None),     # cfg1 DAVIS: odd widths at every scale
+    (8, 256, 256, 3.0, 0.25),     # cfg2 MVSEC, loss / accumulation_steps
+    (8, 256, 256, 64.0, None),    # stress: most pixels warp out of the image
+    (3, 72, 104, 3.0, 3.0),       # ragged tiles
+    (2, 480, 640, 3.0, None),     # cfg4 DSEC shape
+    (2, 33, 65, 2.0, None),       # one pixel past a tile edge in both directions
+])
+def test_fused_matches_oracle_and_generic_path(B, H, W, sigma, scale):
+    inp = synth_loss_inputs(300 + B + H, B, H, W, sigma)
+    flows, loss, flat = _run_fused(inp, inp['flows'], scale=scale)
+    gflows, gterms = _run_gpu(inp, inp['flows'])
+    np.testing.assert_allclose(flat.cpu().numpy().reshape(3, 4), _as_array(gterms), rtol=1e-6, atol=1e-7)
+    oflows = [f.clone().requires_grad_() for f in inp['flows']]
+    oterms = lo.multiscale_loss(oflows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                inp['timestamps'], inp['sample_idx'])
+    np.testing.assert_allclose(flat.cpu().numpy().reshape(3, 4), _as_array(oterms), rtol=RTOL, atol=ATOL)
+    ototal = lo.combined(oterms)
+    np.testing.assert_allclose(float(loss), float(ototal), rtol=RTOL, atol=ATOL)
+    k = 1.0 if scale is None else scale
+    (ototal * k).backward()
+    cot = torch.tensor(WEIGHTS).view(3, 1).expand(3, 4) / 4 * k
+    assert_grads_close([f.grad for f in flows], [f.grad.numpy() for f in oflows], inp, inp['flows'], cot)
+
+
+def test_fused_unequal_weights_and_no_grad_path():
+    inp = synth_loss_inputs(11, 2, 64, 96, 6.0)
+    w = (0.3, 1.7, 0.9)
+    flows, loss, flat = _run_fused(inp, inp['flows'], weights=w)
+    oflows = [f.clone().requires_grad_() for f in inp['flows']]
+    oterms = lo.multiscale_loss(oflows, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                inp['timestamps'], inp['sample_idx'])
+    ototal = sum(wk * sum(t) / len(t) for wk, t in zip(w, oterms))
+    ototal.backward()
+    np.testing.assert_allclose(float(loss), float(ototal), rtol=RTOL, atol=ATOL)
+    cot = torch.tensor(w).view(3, 1).expand(3, 4) / 4
+    assert_grads_close([f.grad for f in flows], [f.grad.numpy() for f in oflows], inp, inp['flows'], cot)
+    # validation: no flow requires grad -> forward-only kernels, same numbers
+    ev = dv.Losses(inp['shapes'], 2, 'cuda')
+    with torch.no_grad():
+        l2, f2 = ev.combined([f.cuda() for f in inp['flows']], inp['flow_ts'].cuda(),
+                             inp['flow_sample_idx'].cuda(), inp['images'].cuda(),
+                             inp['timestamps'].cuda(), inp['sample_idx'].cuda(), w)
+    np.testing.assert_allclose(float(l2), float(loss), rtol=1e-6)
+    np.testing.assert_allclose(f2.cpu().numpy(), flat.cpu().numpy(), rtol=1e-6, atol=1e-7)
+
+
+def test_fused_deterministic_and_single_backward():
+    inp = synth_loss_inputs(9, 4, 128, 160, 5.0)
+    f0, l0, t0 = _run_fused(inp, inp['flows'])
+    f1, l1, t1 = _run_fused(inp, inp['flows'])
+    assert torch.equal(l0, l1) and torch.equal(t0, t1)
+    for a, b in zip(f0, f1):
+        assert torch.equal(a.grad, b.grad)
+    flows = [f.detach().clone().cuda().requires_grad_() for f in inp['flows']]
+    ev = dv.Losses(inp['shapes'], 4, 'cuda')
+    loss, _ = ev.combined(flows, inp['flow_ts'].cuda(), inp['flow_sample_idx'].cuda(),
+                          inp['images'].cuda(), inp['timestamps'].cuda(), inp['sample_idx'].cuda())
+    loss.backward(retain_graph=True)
+    with pytest.raises(RuntimeError):
+        loss.backward()
+
+
+def test_fused_full_size_cfg4_agrees_with_generic_path():
+    """BASELINE cfg4 size (480x640, batch 16): the fused sweep against the two-kernel path
+    (itself oracle-checked at smaller sizes): same terms, same gradients."""
+    B, H, W = 16, 480, 640
+    inp = synth_loss_inputs(44, B, H, W, 3.0, device='cuda')
+    ev = dv.Losses(inp['shapes'], B, 'cuda')
+    args = (inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'], inp['sample_idx'])
+    fa = [f.clone().requires_grad_() for f in inp['flows']]
+    fb = [f.clone().requires_grad_() for f in inp['flows']]
+    loss, flat = ev.combined(fa, *args)
+    loss.backward()
+    terms = ev(fb, *args)
+    total = _combined(terms)
+    total.backward()
+    np.testing.assert_allclose(flat.cpu().numpy().reshape(3, 4), _as_array(terms), rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(float(loss), float(total), rtol=1e-6)
+    for a, b in zip(fa, fb):
+        torch.testing.assert_close(a.grad, b.grad, rtol=RTOL, atol=ATOL)
