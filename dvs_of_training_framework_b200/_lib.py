@@ -1,11 +1,14 @@
 """ctypes binding of libdvsof.so (include/dvsof.h).  No CPU fallback: if the CUDA library is
 missing or a tensor is not on a CUDA device, the call fails loudly."""
 import ctypes as C
+import os
 from pathlib import Path
 
 import torch
 
-_LIB_PATH = Path(__file__).resolve().parent / 'libdvsof.so'
+# DVSOF_LIB selects another build of the same library (kernel tuning sweeps); default: in-tree
+_LIB_PATH = Path(os.environ['DVSOF_LIB']).resolve() if os.environ.get('DVSOF_LIB') else \
+    Path(__file__).resolve().parent / 'libdvsof.so'
 _lib = None
 
 MAX_SCALES = 8

@@ -5,7 +5,7 @@ from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / 'csrc'
-LIB = PKG / 'libdvsof.so'
+LIB = Path(os.environ['DVSOF_LIB']) if os.environ.get('DVSOF_LIB') else PKG / 'libdvsof.so'
 SOURCES = ['runtime.cu', 'encode.cu', 'transforms.cu', 'loss.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
@@ -38,7 +38,8 @@ def build_lib(force=False, verbose=False):
     procs = []
     for src in SOURCES:
         obj = objdir / (src[:-3] + '.o')
-        cmd = [nvcc, *NVCC_FLAGS, '-c', str(CSRC / src), '-o', str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, *os.environ.get('DVSOF_NVCC_EXTRA', '').split(), '-c', str(CSRC / src),
+               '-o', str(obj)]
         if verbose:
             print(' '.join(cmd))
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

@@ -18,8 +18,6 @@ namespace dvsof {
 constexpr float kAlpha = 0.45f;    // utils/loss.py:25
 constexpr float kEps2 = 1e-3f * 1e-3f;  // utils/loss.py:26,31
 constexpr int kTile = 32;          // tile edge (pixels)
-constexpr int kLossThreads = 256;  // 32 x 8 threads, 4 rows per thread
-constexpr int kRec = 8;            // floats per CTA partial record
 
 // Charbonnier c(d) = (d^2 + eps^2)^alpha and c'(d) = 2 alpha d (d^2+eps^2)^(alpha-1).
 // lg2/ex2 on the SFU: relative error ~3e-7, inside the 1e-5 budget of the path.
@@ -33,21 +31,16 @@ __device__ __forceinline__ float lg2_approx(float x) {   // MUFU.LG2 (arguments 
     asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ float charb(float d) {
-    const float s = fmaf(d, d, kEps2);
-    return ex2_approx(kAlpha * lg2_approx(s));
-}
-__device__ __forceinline__ float charb_grad(float d) {
-    const float s = fmaf(d, d, kEps2);
-    return (2.f * kAlpha) * d * ex2_approx((kAlpha - 1.f) * lg2_approx(s));
-}
-
 struct ScaleTable {
     int n_scales, n_pred;
     int H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
     int tiles_x[DVSOF_MAX_SCALES], tiles_y[DVSOF_MAX_SCALES];
     int cta_begin[DVSOF_MAX_SCALES + 1];
-    float rx[DVSOF_MAX_SCALES], ry[DVSOF_MAX_SCALES];   // RN(1/((W-1)/2)), RN(1/((H-1)/2)); 0 = plain division
+    float hx[DVSOF_MAX_SCALES], hy[DVSOF_MAX_SCALES];   // half extents (W-1)/2, (H-1)/2
+    float rx[DVSOF_MAX_SCALES], ry[DVSOF_MAX_SCALES];   // their correctly rounded reciprocals (NaN: degenerate side)
+    // gradient normalisers 2 alpha / count: [0..2] smoothness h / v / diagonal (incl. the 1/4),
+    // [3] photometric 1/(P H W), [4] border 1/(2 P) (divided by n_i in the kernel)
+    float norm[5][DVSOF_MAX_SCALES];
     float coef[3 * DVSOF_MAX_SCALES];                   // fused pass: d(loss)/d(term[k][s]) at [k * MAX + s]
     const float* flow[DVSOF_MAX_SCALES];
     const float* images[DVSOF_MAX_SCALES];
@@ -55,56 +48,18 @@ struct ScaleTable {
 };
 
 struct TileCoord { int s, n, y0, x0; };
-__device__ __forceinline__ TileCoord decode_cta(const ScaleTable& tab) {
-    int s = 0;
-    while (s + 1 < tab.n_scales && (int)blockIdx.x >= tab.cta_begin[s + 1]) ++s;
-    const int local = blockIdx.x - tab.cta_begin[s];
-    const int per = tab.tiles_x[s] * tab.tiles_y[s];
-    const int n = local / per, tile = local - n * per;
-    const int ty = tile / tab.tiles_x[s];
-    return TileCoord{s, n, ty * kTile, (tile - ty * tab.tiles_x[s]) * kTile};
-}
-
-// bilinear sample of `img` (H x W) at the position the reference's grid_sample visits for
-// pixel (x,y) displaced by (u,v); also returns the normalised grid (for the border mask) and the
-// spatial derivatives of the sample.
-struct Warp { float val, ddx, ddy, gx, gy; };
+// Bilinear sampling notes (the code is request_taps + phase 3 of the strip kernel, loss_strip.cuh):
+// the position is the one the reference's grid_sample visits for pixel (x,y) displaced by (u,v):
+//   g  = (pix + flow) / ((S-1)/2) - 1        IEEE division (utils/loss.py:150-156), exact_div.h
+//   ix = (g + 1) * ((S-1)/2)                 ATen CPU unnormalize for align_corners=True
+// coordinates are clamped in float (huge / non-finite values never reach the int conversion), the
+// four zero-padded taps use unsigned range tests and 32-bit offsets inside one image plane, and
+// the weighted sum is evaluated with the same operations as ATen's vectorised CPU grid_sampler
+// (weights s*e, s*w, n*e, n*w; nw*w0 + ne*w1 + sw*w2 + se*w3 is compiled there to mul + 3 chained
+// FMAs -- pinned by tests/test_oracle_golden.py::test_aten_bilinear_operation_order).  Where
+// warped ~= prev the Charbonnier derivative amplifies a 1-ulp difference of the sample ~1e3
+// times, so the interpolation is kept bit-compatible with the reference's CPU path.
 struct GridNorm { float hx, hy, rx, ry; };   // half extents (S-1)/2 and their correctly rounded reciprocals
-
-__device__ __forceinline__ Warp warp_sample(const float* __restrict__ img, int H, int W,
-                                            const GridNorm& gn, int x, int y, float u, float v,
-                                            bool valid = true) {
-    Warp r;
-    r.gx = __fsub_rn(dvsof_div_by_const(__fadd_rn((float)x, u), gn.hx, gn.rx), 1.f);   // utils/loss.py:150-156
-    r.gy = __fsub_rn(dvsof_div_by_const(__fadd_rn((float)y, v), gn.hy, gn.ry), 1.f);
-    const float ix = __fmul_rn(__fadd_rn(r.gx, 1.f), gn.hx);            // ATen CPU unnormalize
-    const float iy = __fmul_rn(__fadd_rn(r.gy, 1.f), gn.hy);
-    const float xw = floorf(ix), yn = floorf(iy);
-    const float wx = ix - xw, wy = iy - yn;                          // weight of east / south
-    const float ex = 1.f - wx, ey = 1.f - wy;
-    // clamp in float (huge / non-finite coordinates never reach the int conversion), then the
-    // four zero-padded taps with unsigned range tests; 32-bit offsets inside one image plane
-    const int xi = (int)fminf(fmaxf(xw, -2.f), (float)W);
-    const int yi = (int)fminf(fmaxf(yn, -2.f), (float)H);
-    const bool x0ok = (unsigned)xi < (unsigned)W, x1ok = (unsigned)(xi + 1) < (unsigned)W;
-    const bool y0ok = valid && (unsigned)yi < (unsigned)H, y1ok = valid && (unsigned)(yi + 1) < (unsigned)H;
-    const int o = yi * W + xi;
-    const float nw = (x0ok && y0ok) ? __ldg(img + o) : 0.f;
-    const float ne = (x1ok && y0ok) ? __ldg(img + o + 1) : 0.f;
-    const float sw = (x0ok && y1ok) ? __ldg(img + o + W) : 0.f;
-    const float se = (x1ok && y1ok) ? __ldg(img + o + W + 1) : 0.f;
-    // same operations as ATen's vectorised CPU grid_sampler (weights s*e, s*w, n*e, n*w; the sum
-    // nw*w0 + ne*w1 + sw*w2 + se*w3 is compiled there to mul + 3 chained FMAs -- pinned by
-    // tests/test_oracle_golden.py::test_aten_bilinear_operation_order).  Where warped ~= prev the
-    // Charbonnier derivative amplifies a 1-ulp difference of `val` ~1e3 times, so the
-    // interpolation is kept bit-compatible with the reference's CPU path.
-    r.val = __fmaf_rn(se, __fmul_rn(wy, wx),
-                      __fmaf_rn(sw, __fmul_rn(wy, ex),
-                                __fmaf_rn(ne, __fmul_rn(ey, wx), __fmul_rn(nw, __fmul_rn(ey, ex)))));
-    r.ddx = (ne - nw) * ey + (se - sw) * wy;
-    r.ddy = (sw - nw) * ex + (se - ne) * wx;
-    return r;
-}
 
 // sum K per-thread values over the warp with the halving butterfly: 4+2+1+1+1 = 9 shuffles for
 // K = 7 instead of 35.  Afterwards lane l (l & 3 == 0) holds the total of value index
@@ -138,10 +93,12 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
                                         const float* __restrict__ timestamps,
                                         const int64_t* __restrict__ sample_idx, int D,
                                         int32_t* __restrict__ match_idx,
-                                        uint32_t* __restrict__ status, unsigned* ticket) {
+                                        uint32_t* __restrict__ status, unsigned* tickets,
+                                        int n_tickets) {
     pdl_launch_dependents();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;   // i = k * P + p
-    if (i == 0 && ticket) *ticket = 0u;                    // arms the forward kernel's finalize
+    if (tickets)                                           // arms the reduction of the loss kernel
+        for (int k = i; k < n_tickets; k += gridDim.x * blockDim.x) tickets[k] = 0u;
     if (i >= 2 * P) return;
     const int k = i / P, p = i - k * P;
     const float want = flow_ts[2 * p + k];
@@ -185,261 +142,130 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
     }
 }
 
-// Stage the 2-channel flow tile (EDGE x EDGE pixels starting HALO before the tile origin, zero
-// outside the image) into shared memory [2][EDGE][PITCH].  All global loads of a thread are
-// issued before its first shared store (fixed trip count, fully unrolled): one DRAM round trip
-// per CTA instead of one per row -- ncu showed the previous row-per-warp loop (load -> store ->
-// next load) holding 60 % of all stall samples.
-template <int EDGE, int PITCH, int HALO>
-__device__ __forceinline__ void stage_flow_tile(float* __restrict__ Fs, const float* __restrict__ flow,
-                                                size_t plane, int H, int W, int y0, int x0) {
-    constexpr int kElems = 2 * EDGE * EDGE;
-    constexpr int kIters = (kElems + kLossThreads - 1) / kLossThreads;
-    float v[kIters];
+// ------------------------------ deterministic reduction of the tile records ------------
+// record of one tile (CTA): [photo, smooth_h, smooth_v, smooth_diag, -, outborder_sum, n_bad, -].
+// Two levels, each run by whichever CTA arrives LAST at a ticket (release/acquire at gpu scope,
+// issued by one thread; the data is read back with L2 loads):
+//   pair level  -- the last tile of a (scale, prediction) pair sums that pair's records in a
+//                  fixed order in fp64 and writes the pair record + n_i;
+//   final level -- the last pair sums the pair records per scale, again in a fixed order, and
+//                  writes the 3*S terms (+ the weighted loss of the fused pass).
+// Results do not depend on arrival order; tickets reset themselves for the next call.
+constexpr int kRec = 8;            // floats per tile record
+constexpr int kPairRec = 8;        // doubles per pair record: [photo, h, v, diag, outborder/(2 n_i P), -, -, -]
+
+__device__ __forceinline__ unsigned ticket_arrive(unsigned* t) {
+    unsigned before;
+    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(before) : "l"(t) : "memory");
+    return before;
+}
+__device__ __forceinline__ double warp_sum_f64(double v) {
 #pragma unroll
-    for (int k = 0; k < kIters; ++k) {
-        const int i = threadIdx.x + k * kLossThreads;
-        const int ch = i / (EDGE * EDGE), rem = i - ch * (EDGE * EDGE);
-        const int ly = rem / EDGE, lx = rem - ly * EDGE;
-        const int y = y0 + ly - HALO, x = x0 + lx - HALO;
-        const bool ok = i < kElems && y >= 0 && y < H && x >= 0 && x < W;
-        v[k] = ok ? __ldg(flow + ch * plane + y * W + x) : 0.f;
-    }
-#pragma unroll
-    for (int k = 0; k < kIters; ++k) {
-        const int i = threadIdx.x + k * kLossThreads;
-        const int ch = i / (EDGE * EDGE), rem = i - ch * (EDGE * EDGE);
-        const int ly = rem / EDGE, lx = rem - ly * EDGE;
-        if (i < kElems) Fs[(ch * EDGE + ly) * PITCH + lx] = v[k];
-    }
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
 }
 
-// ------------------------------ forward ------------------------------------------------
-// record: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
-constexpr int kMaxPairs = 256;     // (scale, prediction) pairs reduced per finalize pass
-__device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, float* loss_out, double (*pair_acc)[6]);
-
-__global__ void __launch_bounds__(kLossThreads)
-warp_loss_fwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
-                     float* partials, unsigned* ticket, float* __restrict__ terms,
-                     int32_t* __restrict__ n_bad) {
-    __shared__ float F[2][kTile + 1][kTile + 2];
-    __shared__ float red[kLossThreads / 32][kRec];
-    __shared__ double wacc[kMaxPairs][6];
-    __shared__ bool is_last;
-    pdl_launch_dependents();
-    pdl_wait();                       // pyramid levels + match_idx come from the preceding kernels
-    const TileCoord tc = decode_cta(tab);
-    const int H = tab.H[tc.s], W = tab.W[tc.s], P = tab.n_pred;
-    const size_t plane = (size_t)H * W;
-    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-    stage_flow_tile<kTile + 1, kTile + 2, 0>(&F[0][0][0], flow, plane, H, W, tc.y0, tc.x0);
-    __syncthreads();
-    const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
-    const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
-    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
-    const int lx = threadIdx.x & 31, lyb = threadIdx.x >> 5;
-    const int x = tc.x0 + lx;
-    const float m_r = (x + 1 < W) ? 1.f : 0.f;            // pixel has a right neighbour
-    const int xc = min(x, W - 1);
-    // acc: [photo, smooth_h, smooth_v, smooth_diag_a, smooth_diag_b, outborder_sum, n_bad, -]
-    float acc[kRec] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    // branch-free over the tile (off-image lanes/rows contribute through 0/1 masks, F is 0
-    // there): the four rows' loads and MUFU chains interleave freely
-#pragma unroll
-    for (int r = 0; r < kTile / 8; ++r) {
-        const int ly = lyb + 8 * r, y = tc.y0 + ly;
-        const bool valid = (x < W) && (y < H);
-        const float m_v = valid ? 1.f : 0.f;
-        const float u = F[0][ly][lx], v = F[1][ly][lx];
-        const Warp wp = warp_sample(next, H, W, gn, x, y, u, v, valid);
-        const float pv = __ldg(prev + min(y, H - 1) * W + xc);
-        acc[0] = fmaf(m_v, charb(wp.val - pv), acc[0]);                     // loss.py:72-74
-        const float m_d = (y + 1 < H) ? m_v : 0.f, m_rv = m_r * m_v, m_rd = m_r * m_d;
-#pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {                                    // loss.py:76-90
-            const float f = F[ch][ly][lx], fr = F[ch][ly][lx + 1];
-            const float fd = F[ch][ly + 1][lx], fdr = F[ch][ly + 1][lx + 1];
-            acc[1] = fmaf(m_rv, charb(fr - f), acc[1]);
-            acc[2] = fmaf(m_d, charb(fd - f), acc[2]);
-            acc[3] = fmaf(m_rd, charb(fdr - f), acc[3]);
-            acc[4] = fmaf(m_rd, charb(fr - fd), acc[4]);
-        }
-        const bool bad = valid && (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f);   // loss.py:92-94
-        if (__any_sync(0xffffffffu, bad)) {                                 // warp-uniform, rare
-            const float m_b = bad ? 1.f : 0.f;
-            acc[5] = fmaf(m_b, charb(u) + charb(v), acc[5]);
-            acc[6] += m_b;
-        }
+// all threads of the CTA (whole warps); `red` holds (blockDim/32) x 7 doubles
+__device__ void reduce_pair(const ScaleTable& tab, int s, int n, const float* partials,
+                            double* pair_rec, int32_t* n_bad, double (*red)[7]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const int P = tab.n_pred, per = tab.tiles_x[s] * tab.tiles_y[s];
+    const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
+    double a[7] = {0, 0, 0, 0, 0, 0, 0};
+    for (int t = threadIdx.x; t < per; t += blockDim.x) {
+        const float4 r0 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
+        const float4 r1 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
+        a[0] += (double)r0.x; a[1] += (double)r0.y; a[2] += (double)r0.z; a[3] += (double)r0.w;
+        a[4] += (double)r1.x; a[5] += (double)r1.y; a[6] += (double)r1.z;
     }
-    warp_sum8(acc, lx);
-    if ((lx & 3) == 0) red[lyb][((lx >> 4) & 1) * 4 + ((lx >> 3) & 1) * 2 + ((lx >> 2) & 1)] = acc[0];
-    __syncthreads();
-    if (threadIdx.x < 7) {
-        float t = 0.f;
-        for (int w = 0; w < kLossThreads / 32; ++w) t += red[w][threadIdx.x];
-        __stcg(partials + (size_t)blockIdx.x * kRec + threadIdx.x, t);
-    }
-    // the last CTA to arrive reduces all records in a FIXED order (deterministic, fp64)
-    __threadfence();
+#pragma unroll
+    for (int k = 0; k < 7; ++k) a[k] = warp_sum_f64(a[k]);
+    if (lane == 0)
+#pragma unroll
+        for (int k = 0; k < 7; ++k) red[warp][k] = a[k];
     __syncthreads();
     if (threadIdx.x == 0) {
-        const unsigned prev = atomicAdd(ticket, 1u);
-        is_last = (prev == gridDim.x - 1);
+        double t[7];
+        for (int k = 0; k < 7; ++k) {
+            t[k] = 0;
+            for (int w = 0; w < n_warps; ++w) t[k] += red[w][k];
+        }
+        double* out = pair_rec + (size_t)(s * P + n) * kPairRec;
+        const double nb = t[6];
+        __stcg(out + 0, t[0]); __stcg(out + 1, t[1]); __stcg(out + 2, t[2]); __stcg(out + 3, t[3] + t[4]);
+        __stcg(out + 4, nb > 0 ? t[5] / (2.0 * nb * (double)P) : 0.0);                 // loss.py:99-113
+        if (n_bad) n_bad[s * P + n] = (int32_t)nb;
     }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    finalize_terms(tab, partials, terms, n_bad, nullptr, wacc);
-    if (threadIdx.x == 0) *ticket = 0u;   // self-resetting for the next call on this workspace
 }
 
-// run by ONE CTA (any whole number of warps): warp w sums the tile records of the (scale, prediction)
-// pairs w, w+8, ... (all scales in flight at once: one round of loads, one barrier) in a fixed
-// order in fp64; thread s then combines scale s.
-__device__ void finalize_terms(const ScaleTable& tab, const float* partials, float* terms,
-                               int32_t* n_bad, float* loss_out, double (*pair_acc)[6]) {
+__device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, float* terms,
+                             float* loss_out) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const int P = tab.n_pred, S = tab.n_scales;
-    double tot[6] = {0, 0, 0, 0, 0, 0};            // thread s < S: running totals of scale s
-    for (int p0 = 0; p0 < P; p0 += kMaxPairs / DVSOF_MAX_SCALES) {
-        const int pn = min(P - p0, kMaxPairs / DVSOF_MAX_SCALES);
-        for (int q = warp; q < S * pn; q += n_warps) {
-            const int s = q / pn, n = p0 + (q - s * pn);
-            const int per = tab.tiles_x[s] * tab.tiles_y[s];
-            double a[7] = {0, 0, 0, 0, 0, 0, 0};
-            const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
-            for (int t = lane; t < per; t += 32) {
-                const float4 r0 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
-                const float4 r1 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
-                a[0] += (double)r0.x; a[1] += (double)r0.y; a[2] += (double)r0.z; a[3] += (double)r0.w;
-                a[4] += (double)r1.x; a[5] += (double)r1.y; a[6] += (double)r1.z;
-            }
+    for (int s = warp; s < S; s += n_warps) {
+        double a[5] = {0, 0, 0, 0, 0};
+        for (int n = lane; n < P; n += 32) {
+            const double* r = pair_rec + (size_t)(s * P + n) * kPairRec;
 #pragma unroll
-            for (int k = 0; k < 7; ++k)
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) a[k] += __shfl_xor_sync(0xffffffffu, a[k], o);
-            if (lane == 0) {
-                const double nb = a[6];
-                for (int k = 0; k < 5; ++k) pair_acc[q][k] = a[k];
-                pair_acc[q][5] = nb > 0 ? a[5] / (2.0 * nb * (double)P) : 0.0;   // loss.py:99-113
-                if (n_bad) n_bad[s * P + n] = (int32_t)nb;
-            }
+            for (int k = 0; k < 5; ++k) a[k] += __ldcg(r + k);
         }
-        __syncthreads();
-        if ((int)threadIdx.x < S)
-            for (int j = 0; j < pn; ++j)
-                for (int k = 0; k < 6; ++k) tot[k] += pair_acc[threadIdx.x * pn + j][k];
-        __syncthreads();
-    }
-    if ((int)threadIdx.x < S) {
-        const int s = threadIdx.x, H = tab.H[s], W = tab.W[s];
-        const double N2 = 2.0 * P;
-        const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
-        double sm = 0;
-        if (ch > 0) sm += tot[1] / ch;
-        if (cv > 0) sm += tot[2] / cv;
-        if (cd > 0) sm += (tot[3] + tot[4]) / cd;
-        terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
-        terms[S + s] = (float)(tot[0] / ((double)P * H * W));                // loss.py:33
-        terms[2 * S + s] = (float)tot[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) a[k] = warp_sum_f64(a[k]);
+        if (lane == 0) {
+            const int H = tab.H[s], W = tab.W[s];
+            const double N2 = 2.0 * P;
+            const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
+            double sm = 0;
+            if (ch > 0) sm += a[1] / ch;
+            if (cv > 0) sm += a[2] / cv;
+            if (cd > 0) sm += a[3] / cd;
+            terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
+            terms[S + s] = (float)(a[0] / ((double)P * H * W));                  // loss.py:33
+            terms[2 * S + s] = (float)a[4];
+        }
     }
     if (loss_out) {                       // fused pass: loss = sum_k sum_s coef[k][s] * term[k][s]
         __syncthreads();
         if (threadIdx.x == 0) {
             float l = 0.f;
             for (int k = 0; k < 3; ++k)
-                for (int s = 0; s < S; ++s) l = fmaf(tab.coef[k * DVSOF_MAX_SCALES + s], terms[k * S + s], l);
+                for (int s = 0; s < S; ++s)
+                    l = fmaf(tab.coef[k * DVSOF_MAX_SCALES + s], __ldcg(terms + k * S + s), l);
             *loss_out = l;
         }
     }
 }
 
-// ------------------------------ backward -----------------------------------------------
-// d(terms)/d(flow), contracted with grad_terms.  Every pixel gathers its own gradient (no
-// atomics, one write): photometric via the bilinear tap differences, out-of-border via
-// c'(flow)/(2 n_i N), smoothness from the 8 neighbour pairs it belongs to.  Each neighbour pair
-// is owned by the top-left pixel ("cell") of its 2x2 block, its Charbonnier derivative is
-// evaluated ONCE (4 pairs x 2 channels per cell) into shared memory and read by both ends:
-// 9 instead of 17 lg2/ex2 pairs per pixel -- the kernel is SFU/issue bound, not HBM bound.
-constexpr int kCell = kTile + 1;   // cells (x0-1 .. x0+31) x (y0-1 .. y0+31)
+// workspace carved by the host: tile records | pair records | tickets (1 + S*P words)
+struct LossWorkspace {
+    float* partials;
+    double* pair_rec;
+    unsigned* tickets;     // [0] = pairs finished; [1 + s*P + n] = tiles of the pair finished
+};
 
-__global__ void __launch_bounds__(kLossThreads)
-warp_loss_bwd_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
-                     const float* __restrict__ grad_terms, const int32_t* __restrict__ n_bad) {
-    __shared__ float F[2][kTile + 2][kTile + 3];   // flow, halo of 1: F[.][ly+1][lx+1]
-    __shared__ float G[2][4][kCell][kCell + 1];    // pair gradients [ch][h,v,da,db][cy+1][cx+1]
-    const TileCoord tc = decode_cta(tab);
-    const int S = tab.n_scales, P = tab.n_pred;
-    const int H = tab.H[tc.s], W = tab.W[tc.s];
-    const size_t plane = (size_t)H * W;
-    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-    float* grad = tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane;
-    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    stage_flow_tile<kTile + 2, kTile + 3, 1>(&F[0][0][0], flow, plane, H, W, tc.y0, tc.x0);
-    const float g_sm = grad_terms[tc.s], g_ph = grad_terms[S + tc.s], g_ob = grad_terms[2 * S + tc.s];
-    const float N2 = 2.f * (float)P;
-    const float ch_n = N2 * (float)H * (float)(W - 1), cv_n = N2 * (float)(H - 1) * (float)W;
-    const float cd_n = N2 * (float)(H - 1) * (float)(W - 1);
-    const float k_h = ch_n > 0.f ? 0.25f * g_sm / ch_n : 0.f;
-    const float k_v = cv_n > 0.f ? 0.25f * g_sm / cv_n : 0.f;
-    const float k_d = cd_n > 0.f ? 0.25f * g_sm / cd_n : 0.f;
+// Called by every CTA after its tile record is in `partials` (written by threads < 7, then a
+// __syncthreads by the caller is NOT needed: done here).
+__device__ __forceinline__ void finish_tile(const ScaleTable& tab, const TileCoord& tc,
+                                            const LossWorkspace& ws, float* terms, int32_t* n_bad,
+                                            float* loss_out, double (*red)[7], bool* flag) {
+    const int P = tab.n_pred, pair = tc.s * P + tc.n;
+    __syncthreads();                                       // record stores happen-before the arrive
+    if (threadIdx.x == 0)
+        *flag = ticket_arrive(ws.tickets + 1 + pair) == (unsigned)(tab.tiles_x[tc.s] * tab.tiles_y[tc.s]) - 1u;
     __syncthreads();
-    // pair gradients of the 33x33 cells: cell (cx,cy) = pixel (x0-1+cx, y0-1+cy)
-    for (int i = threadIdx.x; i < kCell * kCell; i += kLossThreads) {
-        const int cy = i / kCell, cx = i - cy * kCell;
-        const int x = tc.x0 - 1 + cx, y = tc.y0 - 1 + cy;
-        const bool in = x >= 0 && y >= 0 && x < W && y < H;
-        const bool R = in && x + 1 < W, Dn = in && y + 1 < H;
-#pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {
-            const float f = F[ch][cy][cx], fr = F[ch][cy][cx + 1];
-            const float fd = F[ch][cy + 1][cx], fdr = F[ch][cy + 1][cx + 1];
-            G[ch][0][cy][cx] = R ? k_h * charb_grad(fr - f) : 0.f;
-            G[ch][1][cy][cx] = Dn ? k_v * charb_grad(fd - f) : 0.f;
-            G[ch][2][cy][cx] = (R && Dn) ? k_d * charb_grad(fdr - f) : 0.f;
-            G[ch][3][cy][cx] = (R && Dn) ? k_d * charb_grad(fr - fd) : 0.f;
-        }
-    }
-    const float k_ph = g_ph / ((float)P * (float)H * (float)W);
-    const int nb = n_bad[tc.s * P + tc.n];
-    const float k_ob = nb > 0 ? g_ob / (2.f * (float)nb * (float)P) : 0.f;
-    const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
-    const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
-    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
+    if (!*flag) return;
+    __threadfence();                                       // acquire side (finishing CTAs only)
+    reduce_pair(tab, tc.s, tc.n, ws.partials, ws.pair_rec, n_bad, red);
     __syncthreads();
-    const int lx = lane + 1;
-    const int x = tc.x0 + lane;
-    const int xc = min(x, W - 1);
-#pragma unroll
-    for (int r = 0; r < kTile / 8; ++r) {
-        const int ly = wrp + 8 * r + 1, y = tc.y0 + ly - 1;
-        const bool valid = (x < W) && (y < H);
-        const float u = F[0][ly][lx], v = F[1][ly][lx];
-        const Warp wp = warp_sample(next, H, W, gn, x, y, u, v, valid);
-        const float cp = k_ph * charb_grad(wp.val - __ldg(prev + min(y, H - 1) * W + xc));
-        float g[2] = {cp * wp.ddx, cp * wp.ddy};
-        const bool bad = valid && (wp.gx < -1.f || wp.gx > 1.f || wp.gy < -1.f || wp.gy > 1.f);
-        if (__any_sync(0xffffffffu, bad)) {                                 // warp-uniform, rare
-            const float kb = bad ? k_ob : 0.f;
-            g[0] = fmaf(kb, charb_grad(u), g[0]);
-            g[1] = fmaf(kb, charb_grad(v), g[1]);
-        }
-        // own cell = (lx, ly) in G coordinates; left = lx-1, up = ly-1
-#pragma unroll
-        for (int ch = 0; ch < 2; ++ch) {
-            float a = G[ch][0][ly][lx - 1] - G[ch][0][ly][lx];         // horizontal pairs
-            a += G[ch][1][ly - 1][lx] - G[ch][1][ly][lx];              // vertical
-            a += G[ch][2][ly - 1][lx - 1] - G[ch][2][ly][lx];          // diagonal "\\"
-            a += G[ch][3][ly][lx - 1] - G[ch][3][ly - 1][lx];          // diagonal "/"
-            g[ch] += a;
-        }
-        if (valid) {
-            grad[y * W + x] = g[0];
-            grad[plane + y * W + x] = g[1];
-        }
+    if (threadIdx.x == 0) {
+        ws.tickets[1 + pair] = 0u;                         // self-resetting
+        *flag = ticket_arrive(ws.tickets) == (unsigned)(tab.n_scales * P) - 1u;
     }
+    __syncthreads();
+    if (!*flag) return;
+    __threadfence();
+    reduce_final(tab, ws.pair_rec, terms, loss_out);
+    if (threadIdx.x == 0) ws.tickets[0] = 0u;
 }
 
 // d(loss)/d(flow) *= factor, in place, for all scales in one launch; nothing is touched when the
@@ -465,12 +291,6 @@ scale_gradients_kernel(const __grid_constant__ ScaleTable tab, const float* __re
 // ---------------------------------------------------------------------------------------
 using namespace dvsof;
 
-// DVSOF_LOSS_LEGACY=1 selects the first-generation tile kernels (kept for A/B measurements)
-static bool legacy_loss() {
-    static const bool v = [] { const char* e = getenv("DVSOF_LOSS_LEGACY"); return e && e[0] == '1'; }();
-    return v;
-}
-
 static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need_grad) {
     if (!sc) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: null scale table");
     if (sc->n_scales < 1 || sc->n_scales > DVSOF_MAX_SCALES || sc->n_pred < 1)
@@ -488,8 +308,15 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
         tab->tiles_y[s] = (sc->H[s] + kTile - 1) / kTile;
         const float hx = (float)(sc->W[s] - 1) / 2.f, hy = (float)(sc->H[s] - 1) / 2.f;
         // a 1-pixel side makes the reference divide by zero (NaN/inf grid); here: NaN grid as well
+        tab->hx[s] = hx;
+        tab->hy[s] = hy;
         tab->rx[s] = dvsof_div_const_ok(hx) ? dvsof_recip_rn(hx) : NAN;
         tab->ry[s] = dvsof_div_const_ok(hy) ? dvsof_recip_rn(hy) : NAN;
+        const double a2 = 2.0 * (double)kAlpha, N2 = 2.0 * sc->n_pred, Hd = sc->H[s], Wd = sc->W[s];
+        const double cnt[3] = {N2 * Hd * (Wd - 1), N2 * (Hd - 1) * Wd, N2 * (Hd - 1) * (Wd - 1)};
+        for (int k = 0; k < 3; ++k) tab->norm[k][s] = cnt[k] > 0 ? (float)(a2 * 0.25 / cnt[k]) : 0.f;
+        tab->norm[3][s] = (float)(a2 / ((double)sc->n_pred * Hd * Wd));
+        tab->norm[4][s] = (float)(a2 / N2);
         tab->flow[s] = sc->flow[s];
         tab->images[s] = sc->images[s];
         tab->grad_flow[s] = sc->grad_flow[s];
@@ -506,27 +333,42 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
     return DVSOF_OK;
 }
 
+// workspace layout: tile records | pair records | tickets
 static size_t partial_bytes(const ScaleTable& tab) {
     return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
+}
+static size_t pair_bytes(const ScaleTable& tab) {
+    return round_up((size_t)tab.n_scales * tab.n_pred * kPairRec * sizeof(double), 256);
+}
+static int n_tickets(const ScaleTable& tab) { return 1 + tab.n_scales * tab.n_pred; }
+static LossWorkspace carve(const ScaleTable& tab, void* workspace) {
+    char* p = static_cast<char*>(workspace);
+    LossWorkspace ws;
+    ws.partials = reinterpret_cast<float*>(p);
+    ws.pair_rec = reinterpret_cast<double*>(p + partial_bytes(tab));
+    ws.tickets = reinterpret_cast<unsigned*>(p + partial_bytes(tab) + pair_bytes(tab));
+    return ws;
 }
 
 extern "C" size_t dvsof_loss_workspace_bytes(const dvsof_loss_scales_t* sc) {
     ScaleTable tab;
     if (build_table(sc, &tab, false)) return 0;
-    return partial_bytes(tab) + 256;   // tile records + the finalize ticket
+    return partial_bytes(tab) + pair_bytes(tab) + round_up((size_t)n_tickets(tab) * 4, 256);
 }
 
-static int launch_forward(const ScaleTable& tab, const int32_t* match_idx, float* terms,
-                          int32_t* n_bad, void* workspace, cudaStream_t stream, bool pdl) {
-    float* partials = reinterpret_cast<float*>(workspace);
-    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
-    if (legacy_loss())
-        return launch_kernel("warp_loss_fwd_kernel", warp_loss_fwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
-                             kLossThreads, 0, stream, pdl, tab, match_idx, partials, ticket, terms, n_bad);
-    return launch_kernel("warp_loss_strip_kernel<fwd>", warp_loss_strip_kernel<true, false>,
-                         tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, pdl, tab, match_idx,
-                         (const float*)nullptr, (const int32_t*)nullptr, partials, ticket, terms, n_bad,
-                         (float*)nullptr);
+static int zero_tickets(const ScaleTable& tab, const LossWorkspace& ws, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(ws.tickets, 0, (size_t)n_tickets(tab) * 4, stream);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "loss ticket memset: %s", cudaGetErrorString(e));
+    return DVSOF_OK;
+}
+
+template <bool kVal, bool kGrad>
+static int launch_strip(const char* what, const ScaleTable& tab, const int32_t* match_idx,
+                        const float* grad_terms, const int32_t* n_bad_in, const LossWorkspace& ws,
+                        float* terms, int32_t* n_bad_out, float* loss, cudaStream_t stream, bool pdl) {
+    return launch_kernel(what, warp_loss_strip_kernel<kVal, kGrad>, tab.cta_begin[DVSOF_MAX_SCALES],
+                         kSThreads, 0, stream, pdl, tab, match_idx, grad_terms, n_bad_in, ws, terms,
+                         n_bad_out, loss);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -537,9 +379,10 @@ extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int3
     if (!match_idx || !terms || !n_bad || !workspace)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_forward: null buffer");
     cudaStream_t stream = (cudaStream_t)stream_;
-    cudaError_t e = cudaMemsetAsync(static_cast<char*>(workspace) + partial_bytes(tab), 0, 4, stream);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "loss ticket memset: %s", cudaGetErrorString(e));
-    return launch_forward(tab, match_idx, terms, n_bad, workspace, stream, false);
+    const LossWorkspace ws = carve(tab, workspace);
+    if (int rc = zero_tickets(tab, ws, stream)) return rc;
+    return launch_strip<true, false>("warp_loss_strip_kernel<fwd>", tab, match_idx, nullptr, nullptr, ws,
+                                     terms, n_bad, nullptr, stream, false);
 }
 
 extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -549,25 +392,22 @@ extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!match_idx || !grad_terms || !n_bad)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_backward: null buffer");
-    if (legacy_loss())
-        return launch_kernel("warp_loss_bwd_kernel", warp_loss_bwd_kernel, tab.cta_begin[DVSOF_MAX_SCALES],
-                             kLossThreads, 0, (cudaStream_t)stream_, false, tab, match_idx, grad_terms, n_bad);
-    return launch_kernel("warp_loss_strip_kernel<bwd>", warp_loss_strip_kernel<false, true>,
-                         tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, (cudaStream_t)stream_, false, tab,
-                         match_idx, grad_terms, n_bad, (float*)nullptr, (unsigned*)nullptr, (float*)nullptr,
-                         (int32_t*)nullptr, (float*)nullptr);
+    return launch_strip<false, true>("warp_loss_strip_kernel<bwd>", tab, match_idx, grad_terms, n_bad,
+                                     LossWorkspace{nullptr, nullptr, nullptr}, nullptr, nullptr, nullptr,
+                                     (cudaStream_t)stream_, false);
 }
 
 static int launch_match(const float* flow_ts, const int64_t* flow_sample_idx, int64_t P,
                         const float* timestamps, const int64_t* sample_idx, int64_t D,
-                        int32_t* match_idx, uint32_t* status, unsigned* ticket, cudaStream_t stream) {
+                        int32_t* match_idx, uint32_t* status, unsigned* tickets, int n_tick,
+                        cudaStream_t stream) {
     if (P < 1 || D < 1 || P > (1 << 24) || D > (1 << 24) || !flow_ts || !flow_sample_idx ||
         !timestamps || !sample_idx || !match_idx || !status)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "match_timestamps: bad arguments");
     const int threads = 128, blocks = (int)((2 * P + threads - 1) / threads);
     return launch_kernel("match_timestamps_kernel", match_timestamps_kernel, blocks, threads, 0, stream,
                          false, flow_ts, flow_sample_idx, (int)P, timestamps, sample_idx, (int)D,
-                         match_idx, status, ticket);
+                         match_idx, status, tickets, n_tick);
 }
 
 extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_sample_idx,
@@ -575,7 +415,7 @@ extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_
                                       const int64_t* sample_idx, int64_t D, int32_t* match_idx,
                                       uint32_t* status, void* stream_) {
     return launch_match(flow_ts, flow_sample_idx, P, timestamps, sample_idx, D, match_idx, status,
-                        nullptr, (cudaStream_t)stream_);
+                        nullptr, 0, (cudaStream_t)stream_);
 }
 
 static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, float* dst,
@@ -596,10 +436,10 @@ extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, i
 
 // matching + chained pyramid (utils/loss.py:182-210), PDL-chained on the stream
 static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t* fr,
-                                    int32_t* match_idx, uint32_t* status, unsigned* ticket,
-                                    cudaStream_t stream) {
+                                    int32_t* match_idx, uint32_t* status, unsigned* tickets,
+                                    int n_tick, cudaStream_t stream) {
     if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
-                              fr->sample_idx, fr->n_images, match_idx, status, ticket, stream))
+                              fr->sample_idx, fr->n_images, match_idx, status, tickets, n_tick, stream))
         return rc;
     const float* src = fr->images;
     int Hin = fr->H0, Win = fr->W0;
@@ -629,9 +469,16 @@ extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
     if (!frames_ok(fr) || !match_idx || !terms || !n_bad || !workspace || !status)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_forward: bad arguments");
     cudaStream_t stream = (cudaStream_t)stream_;
-    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
-    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ticket, stream)) return rc;
-    return launch_forward(tab, match_idx, terms, n_bad, workspace, stream, true);
+    const LossWorkspace ws = carve(tab, workspace);
+    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream))
+        return rc;
+    return launch_strip<true, false>("warp_loss_strip_kernel<fwd>", tab, match_idx, nullptr, nullptr, ws,
+                                     terms, n_bad, nullptr, stream, true);
+}
+
+static void set_coef(ScaleTable* tab, const float* coef) {
+    for (int k = 0; k < 3; ++k)
+        for (int s = 0; s < tab->n_scales; ++s) tab->coef[k * DVSOF_MAX_SCALES + s] = coef[k * tab->n_scales + s];
 }
 
 // The training pass: the same forward plus d(loss)/d(flow) of
@@ -646,22 +493,18 @@ extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!frames_ok(fr) || !coef || !match_idx || !terms || !loss || !n_bad || !workspace || !status)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_fused: bad arguments");
-    for (int k = 0; k < 3; ++k)
-        for (int s = 0; s < sc->n_scales; ++s) tab.coef[k * DVSOF_MAX_SCALES + s] = coef[k * sc->n_scales + s];
+    set_coef(&tab, coef);
     cudaStream_t stream = (cudaStream_t)stream_;
-    float* partials = reinterpret_cast<float*>(workspace);
-    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
+    const LossWorkspace ws = carve(tab, workspace);
     cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
     if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
-    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ticket, stream)) return rc;
-    const int grid = tab.cta_begin[DVSOF_MAX_SCALES];
-    if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel, grid, kSThreads, 0,
-                               stream, true, tab, n_bad))
+    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream))
         return rc;
-    return launch_kernel("warp_loss_strip_kernel<fused>", warp_loss_strip_kernel<true, true>, grid,
-                         kSThreads, 0, stream, true, tab, (const int32_t*)match_idx,
-                         (const float*)nullptr, (const int32_t*)n_bad, partials, ticket, terms,
-                         (int32_t*)nullptr, loss);
+    if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel,
+                               tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, true, tab, n_bad))
+        return rc;
+    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, n_bad, ws,
+                                    terms, nullptr, loss, stream, true);
 }
 
 // The fused sweep on ready-made pyramid levels (single-scale Loss objects, kernel-level timing):
@@ -673,23 +516,19 @@ extern "C" int dvsof_warp_loss_fused(const dvsof_loss_scales_t* sc, const int32_
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!match_idx || !coef || !terms || !loss || !n_bad || !workspace)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_fused: null buffer");
-    for (int k = 0; k < 3; ++k)
-        for (int s = 0; s < sc->n_scales; ++s) tab.coef[k * DVSOF_MAX_SCALES + s] = coef[k * sc->n_scales + s];
+    set_coef(&tab, coef);
     cudaStream_t stream = (cudaStream_t)stream_;
-    float* partials = reinterpret_cast<float*>(workspace);
-    unsigned* ticket = reinterpret_cast<unsigned*>(static_cast<char*>(workspace) + partial_bytes(tab));
-    const int grid = tab.cta_begin[DVSOF_MAX_SCALES];
-    cudaError_t e = cudaMemsetAsync(ticket, 0, 4, stream);
-    if (e == cudaSuccess && count_pass)
-        e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "warp_loss_fused memset: %s", cudaGetErrorString(e));
-    if (count_pass)
-        if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel, grid, kSThreads, 0,
-                                   stream, false, tab, n_bad))
+    const LossWorkspace ws = carve(tab, workspace);
+    if (int rc = zero_tickets(tab, ws, stream)) return rc;
+    if (count_pass) {
+        cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
+        if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel,
+                                   tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, false, tab, n_bad))
             return rc;
-    return launch_kernel("warp_loss_strip_kernel<fused>", warp_loss_strip_kernel<true, true>, grid,
-                         kSThreads, 0, stream, false, tab, match_idx, (const float*)nullptr,
-                         (const int32_t*)n_bad, partials, ticket, terms, (int32_t*)nullptr, loss);
+    }
+    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, n_bad, ws,
+                                    terms, nullptr, loss, stream, false);
 }
 
 // grad_flow[s] *= *factor for all scales (backward of the fused pass when the incoming gradient

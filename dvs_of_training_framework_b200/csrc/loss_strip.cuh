@@ -27,8 +27,14 @@
 
 namespace dvsof {
 
+#ifndef DVSOF_LOSS_GROUP
+#define DVSOF_LOSS_GROUP 2                // tuning knobs (scripts/exp_loss_variants.sh builds the sweep)
+#endif
+#ifndef DVSOF_LOSS_MIN_CTAS
+#define DVSOF_LOSS_MIN_CTAS 7
+#endif
 constexpr int kSR = 8;                    // rows per warp strip
-constexpr int kGroup = 4;                 // rows whose taps are in flight together
+constexpr int kGroup = DVSOF_LOSS_GROUP;  // rows whose taps are in flight together
 constexpr int kSWarps = kTile / kSR;      // 4 warps per CTA
 constexpr int kSThreads = 32 * kSWarps;   // 128
 constexpr int kFH = kTile + 2;            // staged flow rows  y0-1 .. y0+32
@@ -90,8 +96,7 @@ __device__ __forceinline__ bool out_of_border(float gx, float gy) {             
 // float quotient with one correction step is exact.
 __device__ __forceinline__ TileCoord decode_cta_fast(const ScaleTable& tab) {
     int s = 0;
-#pragma unroll
-    for (int k = 1; k < DVSOF_MAX_SCALES; ++k) s += (k < tab.n_scales && (int)blockIdx.x >= tab.cta_begin[k]) ? 1 : 0;
+    for (int k = 1; k < tab.n_scales; ++k) s += (int)blockIdx.x >= tab.cta_begin[k] ? 1 : 0;
     const int local = blockIdx.x - tab.cta_begin[s];
     const int tx = tab.tiles_x[s], per = tx * tab.tiles_y[s];
     int n = (int)__fdividef((float)local + 0.5f, (float)per);
@@ -174,14 +179,14 @@ __device__ __forceinline__ Taps request_taps(const float* __restrict__ next, con
 }
 
 template <bool kVal, bool kGrad>
-__global__ void __launch_bounds__(kSThreads)
+__global__ void __launch_bounds__(kSThreads, DVSOF_LOSS_MIN_CTAS)
 warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
                        const float* __restrict__ grad_terms, const int32_t* __restrict__ n_bad_in,
-                       float* partials, unsigned* ticket, float* __restrict__ terms,
-                       int32_t* __restrict__ n_bad_out, float* __restrict__ loss_out) {
+                       const LossWorkspace ws, float* terms, int32_t* __restrict__ n_bad_out,
+                       float* __restrict__ loss_out) {
     __shared__ __align__(16) float2 F[kFH][kFP];
     __shared__ float red[kSWarps][kRec];
-    __shared__ double wacc[kVal ? kMaxPairs : 1][6];
+    __shared__ double dred[kVal ? kSWarps : 1][7];
     __shared__ bool is_last;
     pdl_launch_dependents();
     pdl_wait();                       // pyramid levels, match_idx, n_bad come from preceding kernels
@@ -205,22 +210,19 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
         const float g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
         const float g_ph = grad_terms ? grad_terms[S + tc.s] : tab.coef[DVSOF_MAX_SCALES + tc.s];
         const float g_ob = grad_terms ? grad_terms[2 * S + tc.s] : tab.coef[2 * DVSOF_MAX_SCALES + tc.s];
-        const float N2 = 2.f * (float)P;
-        const float ch_n = N2 * (float)H * (float)(W - 1), cv_n = N2 * (float)(H - 1) * (float)W;
-        const float cd_n = N2 * (float)(H - 1) * (float)(W - 1);
-        const float a2 = 2.f * kAlpha;
-        kh = ch_n > 0.f ? a2 * 0.25f * g_sm / ch_n : 0.f;
-        kv = cv_n > 0.f ? a2 * 0.25f * g_sm / cv_n : 0.f;
-        kd = cd_n > 0.f ? a2 * 0.25f * g_sm / cd_n : 0.f;
-        k_ph = a2 * g_ph / ((float)P * (float)H * (float)W);
+        // 2 alpha / (element count of the mean), per direction, precomputed on the host
+        kh = g_sm * tab.norm[0][tc.s];
+        kv = g_sm * tab.norm[1][tc.s];
+        kd = g_sm * tab.norm[2][tc.s];
+        k_ph = g_ph * tab.norm[3][tc.s];
         const int nb = n_bad_in[tc.s * P + tc.n];
-        k_ob = nb > 0 ? a2 * g_ob / (2.f * (float)nb * (float)P) : 0.f;
+        k_ob = nb > 0 ? __fdividef(g_ob * tab.norm[4][tc.s], (float)nb) : 0.f;   // loss.py:99-113
     }
     const float khx = x_r ? kh : 0.f, kvx = x_in ? kv : 0.f, kdx = x_r ? kd : 0.f;
     const float mhx = x_r ? 1.f : 0.f, mvx = x_in ? 1.f : 0.f;
     const float* prev = tab.images[tc.s] + (size_t)match_idx[tc.n] * plane;
     const float* next = tab.images[tc.s] + (size_t)match_idx[P + tc.n] * plane;
-    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
+    const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
     float* grad = kGrad ? tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane : nullptr;
     // finished base pointers in registers: every access below is base + 32-bit offset (IMAD.WIDE)
     asm volatile("" : "+l"(prev), "+l"(next), "+l"(grad));
@@ -348,20 +350,9 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < kSWarps; ++w) t += red[w][threadIdx.x];
-        __stcg(partials + (size_t)blockIdx.x * kRec + threadIdx.x, t);
+        __stcg(ws.partials + (size_t)blockIdx.x * kRec + threadIdx.x, t);
     }
-    // the last CTA to arrive reduces all records in a FIXED order (deterministic, fp64)
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const unsigned before = atomicAdd(ticket, 1u);
-        is_last = (before == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    finalize_terms(tab, partials, terms, n_bad_out, loss_out, wacc);
-    if (threadIdx.x == 0) *ticket = 0u;   // self-resetting for the next call on this workspace
+    finish_tile(tab, tc, ws, terms, n_bad_out, loss_out, dred, &is_last);
 }
 
 // Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
@@ -376,7 +367,7 @@ outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restri
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const int plane = H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-    const GridNorm gn{(float)(W - 1) / 2.f, (float)(H - 1) / 2.f, tab.rx[tc.s], tab.ry[tc.s]};
+    const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = tc.x0 + lane, ys = tc.y0 + warp * kSR;
     const float xf = (float)x;
