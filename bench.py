@@ -251,7 +251,29 @@ def bench_loss(name, K, W, dev):
     fus(1)
     fused_ms = float(np.mean(time_steps(lambda: fus(0), K, W, flush)))
     fusedc_ms = float(np.mean(time_steps(lambda: fus(1), K, W, flush)))
-    return dict(workload=name, samples=B, step_ms=step_ms, bytes=loss_bytes(B, H, Wd),
+    # the whole training pass through the C ABI alone (no Python autograd around it): one
+    # dvsof_multiscale_loss_fused call (memset, match, 4 resize, border count, fused sweep) + the
+    # backward's rescale launch -- what a compiled host (or a CUDA-graph replay) pays per step
+    plan = ev._plan(dev, B, 2 * B, H, Wd, fl)
+    o = plan.offs
+    buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
+    gbuf = torch.empty(plan.gtotal, dtype=torch.float32, device=dev)
+    from dvs_of_training_framework_b200.loss import _fill_frames
+    fr = _fill_frames(plan, inp['images'], inp['flow_ts'], inp['flow_sample_idx'], inp['timestamps'],
+                      inp['sample_idx'])
+    plan.fill(plan.bwd, buf.data_ptr(), fl, gbuf.data_ptr())
+    st = L.status_for(dev)
+    one = torch.ones(1, device=dev)
+    base = buf.data_ptr()
+
+    def abi_step():
+        L.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S], base + 4 * o[S + 2],
+               base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr, L.ptr(st.word), sp)
+        L.call('dvsof_scale_gradients', plan.bwd, L.ptr(one), sp)
+
+    abi_ms = float(np.mean(time_steps(abi_step, K, W, flush)))
+    st.check()
+    return dict(workload=name, samples=B, step_ms=step_ms, abi_ms=abi_ms, bytes=loss_bytes(B, H, Wd),
                 fwd_ms=fwd_ms, bwd_ms=bwd_ms, fwd_bytes=16 * px, bwd_bytes=24 * px,
                 fused_ms=fused_ms, fused_with_count_ms=fusedc_ms, fused_bytes=24 * px,
                 launches_per_step=9)
@@ -262,7 +284,9 @@ def fused_kernels(r, peak):
     same work as 16 + 24 = 40 B/pixel for separate forward and backward passes) and the generic
     forward / backward kernels behind Losses.__call__."""
     frac = lambda b, ms: b / (ms * 1e-3) / 1e9 / peak  # noqa: E731
-    return {'fused_ms': r['fused_ms'], 'fused_with_count_ms': r['fused_with_count_ms'],
+    return {'c_abi_step_ms': r['abi_ms'], 'c_abi_samples_per_s': r['samples'] / (r['abi_ms'] * 1e-3),
+            'c_abi_step_hbm_frac_survey_bytes': frac(r['bytes'], r['abi_ms']),
+            'fused_ms': r['fused_ms'], 'fused_with_count_ms': r['fused_with_count_ms'],
             'fused_hbm_frac_24B_per_px': frac(r['fused_bytes'], r['fused_ms']),
             'fused_hbm_frac_survey_40B_per_px': frac(r['fwd_bytes'] + r['bwd_bytes'], r['fused_ms']),
             'fwd_ms': r['fwd_ms'], 'bwd_ms': r['bwd_ms'],

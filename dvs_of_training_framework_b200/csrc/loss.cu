@@ -111,34 +111,57 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
 }
 
 // ------------------------------ bilinear resize (align_corners) ------------------------
-__global__ void __launch_bounds__(256)
+// A thread produces 4 consecutive pixels of one output row (16 taps in flight, one 16-byte store
+// when the row pitch allows); a CTA covers 128 columns x 8 rows of the (D*Hout) x Wout output.
+// 32-bit index arithmetic, one integer division per thread.
+constexpr int kRX = 4, kRRows = 8;
+__global__ void __launch_bounds__(32 * kRRows)
 resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
-                       int Hout, int Wout, int64_t total) {
+                       int Hout, int Wout, int rows /* D * Hout */) {
     pdl_launch_dependents();
     pdl_wait();                                  // src may be the previous level of the chain
+    const int row = blockIdx.x * kRRows + (threadIdx.x >> 5);
+    const int xb = (blockIdx.y * 32 + (threadIdx.x & 31)) * kRX;
+    if (row >= rows || xb >= Wout) return;
     const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
     const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-        const int x = (int)(i % Wout);
-        const int64_t r = i / Wout;
-        const int y = (int)(r % Hout);
-        const int64_t d = r / Hout;
-        const float fy = sy * (float)y, fx = sx * (float)x;
-        int y0 = (int)fy, x0 = (int)fx;
-        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+    const int d = row / Hout, y = row - d * Hout;
+    const float fy = sy * (float)y;
+    int y0 = (int)fy;
+    y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+    const int y1 = y0 + (y0 < Hin - 1);
+    const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
+    const float* r0 = src + ((size_t)d * Hin + y0) * Win;
+    const float* r1 = src + ((size_t)d * Hin + y1) * Win;
+    float a[kRX], b[kRX], c[kRX], e[kRX], lx[kRX];
+#pragma unroll
+    for (int k = 0; k < kRX; ++k) {
+        const int x = min(xb + k, Wout - 1);     // lanes past the row end recompute its last pixel
+        const float fx = sx * (float)x;
+        int x0 = (int)fx;
         x0 = x0 < Win - 1 ? x0 : Win - 1;
-        const int y1 = y0 + (y0 < Hin - 1), x1 = x0 + (x0 < Win - 1);
-        const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), lx = fminf(fmaxf(fx - (float)x0, 0.f), 1.f);
-        const float hy = 1.f - ly, hx = 1.f - lx;
-        const float* im = src + (size_t)d * Hin * Win;
-        const float a = __ldg(im + (size_t)y0 * Win + x0), b = __ldg(im + (size_t)y0 * Win + x1);
-        const float c = __ldg(im + (size_t)y1 * Win + x0), e = __ldg(im + (size_t)y1 * Win + x1);
+        const int x1 = x0 + (x0 < Win - 1);
+        lx[k] = fminf(fmaxf(fx - (float)x0, 0.f), 1.f);
+        a[k] = __ldg(r0 + x0); b[k] = __ldg(r0 + x1);
+        c[k] = __ldg(r1 + x0); e[k] = __ldg(r1 + x1);
+    }
+    float o[kRX];
+#pragma unroll
+    for (int k = 0; k < kRX; ++k) {
         // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair, one
         // for the rows): bit-identical to the reference's F.interpolate on the upsampling levels of
         // the chain (pinned on CPU by tests/test_oracle_golden.py::test_aten_upsample_operation_order)
-        const float top = __fmaf_rn(hx, a, __fmul_rn(lx, b)), bot = __fmaf_rn(hx, c, __fmul_rn(lx, e));
-        dst[i] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+        const float hx = 1.f - lx[k];
+        const float top = __fmaf_rn(hx, a[k], __fmul_rn(lx[k], b[k])), bot = __fmaf_rn(hx, c[k], __fmul_rn(lx[k], e[k]));
+        o[k] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+    }
+    float* out = dst + (size_t)row * Wout + xb;
+    if ((Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
+        *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < kRX; ++k)
+            if (xb + k < Wout) out[k] = o[k];
     }
 }
 
@@ -422,11 +445,22 @@ static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, 
                          int32_t Hout, int32_t Wout, cudaStream_t stream, bool pdl) {
     if (D < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || !src || !dst)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: bad arguments");
-    const int64_t total = D * Hout * Wout;
-    int64_t blocks = (total + 255) / 256;
-    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-    return launch_kernel("resize_bilinear_kernel", resize_bilinear_kernel, (int)blocks, 256, 0, stream,
-                         pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, total);
+    const int64_t rows = D * Hout;
+    if (rows > INT32_MAX / 2 || (int64_t)Hin * Win > INT32_MAX / 2)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: too large");
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((rows + kRRows - 1) / kRRows), (unsigned)((Wout + 32 * kRX - 1) / (32 * kRX)));
+    cfg.blockDim = dim3(32 * kRRows);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, resize_bilinear_kernel, src, (int)Hin, (int)Win, dst, (int)Hout,
+                                       (int)Wout, (int)rows);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "resize_bilinear_kernel: %s", cudaGetErrorString(e));
+    return DVSOF_OK;
 }
 
 extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,

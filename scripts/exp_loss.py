@@ -24,7 +24,7 @@ def main():
                      'bwd_GBs': round(r['bwd_bytes'] / r['bwd_ms'] / 1e6, 1),
                      'fwd_frac': round(r['fwd_bytes'] / r['fwd_ms'] / 1e6 / peak, 4),
                      'bwd_frac': round(r['bwd_bytes'] / r['bwd_ms'] / 1e6 / peak, 4),
-                     'fused_ms': round(r['fused_ms'], 4),
+                     'abi_ms': round(r['abi_ms'], 4), 'fused_ms': round(r['fused_ms'], 4),
                      'fused_with_count_ms': round(r['fused_with_count_ms'], 4),
                      'fused_GBs': round(r['fused_bytes'] / r['fused_ms'] / 1e6, 1),
                      'fused_frac': round(r['fused_bytes'] / r['fused_ms'] / 1e6 / peak, 4)}
