@@ -111,57 +111,68 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
 }
 
 // ------------------------------ bilinear resize (align_corners) ------------------------
-// A thread produces 4 consecutive pixels of one output row (16 taps in flight, one 16-byte store
-// when the row pitch allows); a CTA covers 128 columns x 8 rows of the (D*Hout) x Wout output.
-// 32-bit index arithmetic, one integer division per thread.
-constexpr int kRX = 4, kRRows = 8;
-__global__ void __launch_bounds__(32 * kRRows)
+// A thread produces 4 consecutive pixels of kRY consecutive output rows: the column taps and
+// weights are computed once per thread, a row costs two base pointers, 16 loads and one 16-byte
+// store (when the row pitch allows).  A CTA covers 128 columns x 32 rows of the (D*Hout) x Wout
+// output; 32-bit index arithmetic, one integer division per thread.
+constexpr int kRX = 4, kRY = 4, kRWarps = 8;
+__global__ void __launch_bounds__(32 * kRWarps)
 resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
                        int Hout, int Wout, int rows /* D * Hout */) {
     pdl_launch_dependents();
     pdl_wait();                                  // src may be the previous level of the chain
-    const int row = blockIdx.x * kRRows + (threadIdx.x >> 5);
+    const int row0 = (blockIdx.x * kRWarps + (threadIdx.x >> 5)) * kRY;
     const int xb = (blockIdx.y * 32 + (threadIdx.x & 31)) * kRX;
-    if (row >= rows || xb >= Wout) return;
+    if (row0 >= rows || xb >= Wout) return;
     const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
     const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
-    const int d = row / Hout, y = row - d * Hout;
-    const float fy = sy * (float)y;
-    int y0 = (int)fy;
-    y0 = y0 < Hin - 1 ? y0 : Hin - 1;
-    const int y1 = y0 + (y0 < Hin - 1);
-    const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
-    const float* r0 = src + ((size_t)d * Hin + y0) * Win;
-    const float* r1 = src + ((size_t)d * Hin + y1) * Win;
-    float a[kRX], b[kRX], c[kRX], e[kRX], lx[kRX];
+    int x0[kRX], x1[kRX];
+    float lx[kRX], hx[kRX];
 #pragma unroll
     for (int k = 0; k < kRX; ++k) {
         const int x = min(xb + k, Wout - 1);     // lanes past the row end recompute its last pixel
         const float fx = sx * (float)x;
-        int x0 = (int)fx;
-        x0 = x0 < Win - 1 ? x0 : Win - 1;
-        const int x1 = x0 + (x0 < Win - 1);
-        lx[k] = fminf(fmaxf(fx - (float)x0, 0.f), 1.f);
-        a[k] = __ldg(r0 + x0); b[k] = __ldg(r0 + x1);
-        c[k] = __ldg(r1 + x0); e[k] = __ldg(r1 + x1);
+        int xi = (int)fx;
+        xi = xi < Win - 1 ? xi : Win - 1;
+        x0[k] = xi;
+        x1[k] = xi + (xi < Win - 1);
+        lx[k] = fminf(fmaxf(fx - (float)xi, 0.f), 1.f);
+        hx[k] = 1.f - lx[k];
     }
-    float o[kRX];
+    const bool vec = (Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+    int d = row0 / Hout, y = row0 - d * Hout;
 #pragma unroll
-    for (int k = 0; k < kRX; ++k) {
-        // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair, one
-        // for the rows): bit-identical to the reference's F.interpolate on the upsampling levels of
-        // the chain (pinned on CPU by tests/test_oracle_golden.py::test_aten_upsample_operation_order)
-        const float hx = 1.f - lx[k];
-        const float top = __fmaf_rn(hx, a[k], __fmul_rn(lx[k], b[k])), bot = __fmaf_rn(hx, c[k], __fmul_rn(lx[k], e[k]));
-        o[k] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
-    }
-    float* out = dst + (size_t)row * Wout + xb;
-    if ((Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0) {
-        *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
-    } else {
+    for (int j = 0; j < kRY; ++j) {
+        const int row = row0 + j;
+        if (row >= rows) break;
+        const float fy = sy * (float)y;
+        int y0 = (int)fy;
+        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+        const int y1 = y0 + (y0 < Hin - 1);
+        const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
+        const float* r0 = src + (size_t)(d * Hin + y0) * Win;
+        const float* r1 = src + (size_t)(d * Hin + y1) * Win;
+        float o[kRX];
 #pragma unroll
-        for (int k = 0; k < kRX; ++k)
-            if (xb + k < Wout) out[k] = o[k];
+        for (int k = 0; k < kRX; ++k) {
+            const float a = __ldg(r0 + x0[k]), b = __ldg(r0 + x1[k]);
+            const float c = __ldg(r1 + x0[k]), e = __ldg(r1 + x1[k]);
+            // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair,
+            // one for the rows): bit-identical to the reference's F.interpolate on the upsampling
+            // levels of the chain (pinned on CPU by
+            // tests/test_oracle_golden.py::test_aten_upsample_operation_order)
+            const float top = __fmaf_rn(hx[k], a, __fmul_rn(lx[k], b)), bot = __fmaf_rn(hx[k], c, __fmul_rn(lx[k], e));
+            o[k] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+        }
+        float* out = dst + (size_t)row * Wout + xb;
+        if (vec) {
+            *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kRX; ++k)
+                if (xb + k < Wout) out[k] = o[k];
+        }
+        if (++y == Hout) { y = 0; ++d; }
     }
 }
 
@@ -449,8 +460,9 @@ static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, 
     if (rows > INT32_MAX / 2 || (int64_t)Hin * Win > INT32_MAX / 2)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: too large");
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((rows + kRRows - 1) / kRRows), (unsigned)((Wout + 32 * kRX - 1) / (32 * kRX)));
-    cfg.blockDim = dim3(32 * kRRows);
+    const int cta_rows = kRWarps * kRY;
+    cfg.gridDim = dim3((unsigned)((rows + cta_rows - 1) / cta_rows), (unsigned)((Wout + 32 * kRX - 1) / (32 * kRX)));
+    cfg.blockDim = dim3(32 * kRWarps);
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

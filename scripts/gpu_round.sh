@@ -20,7 +20,7 @@ bench)
 ncu)
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_bench_quick.csv \
       python bench.py --quick --steps 3 --warmup 1 > $OUT/ncu_launches.log 2>&1
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'encode_|warp_loss' -c 12 -f -o $OUT/ncu_full_cfg2 \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'encode_|strip' -c 12 -f -o $OUT/ncu_full_cfg2 \
       python bench.py --quick --steps 2 --warmup 1 > $OUT/ncu_full_cfg2.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:'encode_v|encode_t' -c 3 -f -o $OUT/ncu_full_cfg3 \
       python scripts/exp_encoder.py cfg3 > $OUT/ncu_full_cfg3.log 2>&1
@@ -28,6 +28,6 @@ ncu)
 loss)
   timeout 600 python scripts/exp_loss.py cfg2 cfg3 cfg4 > $OUT/loss.json 2> $OUT/loss.err; cat $OUT/loss.json; tail -3 $OUT/loss.err;;
 lossncu)
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'warp_loss|resize|match' -c 14 -f -o $OUT/ncu_full_loss_cfg4 \
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:'strip|resize|match|outborder|scale_grad' -c 24 -f -o $OUT/ncu_full_loss_cfg4 \
       python scripts/exp_loss.py cfg4 > $OUT/ncu_full_loss_cfg4.log 2>&1; tail -2 $OUT/ncu_full_loss_cfg4.log;;
 esac; done
