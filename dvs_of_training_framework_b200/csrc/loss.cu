@@ -35,6 +35,7 @@ struct ScaleTable {
     int n_scales, n_pred;
     int H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
     int tiles_x[DVSOF_MAX_SCALES], tiles_y[DVSOF_MAX_SCALES];
+    float inv_tx[DVSOF_MAX_SCALES], inv_per[DVSOF_MAX_SCALES];   // 1 / tiles_x, 1 / (tiles_x * tiles_y)
     int cta_begin[DVSOF_MAX_SCALES + 1];
     float hx[DVSOF_MAX_SCALES], hy[DVSOF_MAX_SCALES];   // half extents (W-1)/2, (H-1)/2
     float rx[DVSOF_MAX_SCALES], ry[DVSOF_MAX_SCALES];   // their correctly rounded reciprocals (NaN: degenerate side)
@@ -108,72 +109,6 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
         if (timestamps[d] == want && sample_idx[d] == smp) { ++hits; idx = d; }   // loss.py:187-191
     if (hits != 1) atomicOr(status, DVSOF_ST_NO_MATCH);                           // loss.py:193
     match_idx[i] = idx;
-}
-
-// ------------------------------ bilinear resize (align_corners) ------------------------
-// A thread produces 4 consecutive pixels of kRY consecutive output rows: the column taps and
-// weights are computed once per thread, a row costs two base pointers, 16 loads and one 16-byte
-// store (when the row pitch allows).  A CTA covers 128 columns x 32 rows of the (D*Hout) x Wout
-// output; 32-bit index arithmetic, one integer division per thread.
-constexpr int kRX = 4, kRY = 4, kRWarps = 8;
-__global__ void __launch_bounds__(32 * kRWarps)
-resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
-                       int Hout, int Wout, int rows /* D * Hout */) {
-    pdl_launch_dependents();
-    pdl_wait();                                  // src may be the previous level of the chain
-    const int row0 = (blockIdx.x * kRWarps + (threadIdx.x >> 5)) * kRY;
-    const int xb = (blockIdx.y * 32 + (threadIdx.x & 31)) * kRX;
-    if (row0 >= rows || xb >= Wout) return;
-    const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
-    const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
-    int x0[kRX], x1[kRX];
-    float lx[kRX], hx[kRX];
-#pragma unroll
-    for (int k = 0; k < kRX; ++k) {
-        const int x = min(xb + k, Wout - 1);     // lanes past the row end recompute its last pixel
-        const float fx = sx * (float)x;
-        int xi = (int)fx;
-        xi = xi < Win - 1 ? xi : Win - 1;
-        x0[k] = xi;
-        x1[k] = xi + (xi < Win - 1);
-        lx[k] = fminf(fmaxf(fx - (float)xi, 0.f), 1.f);
-        hx[k] = 1.f - lx[k];
-    }
-    const bool vec = (Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
-    int d = row0 / Hout, y = row0 - d * Hout;
-#pragma unroll
-    for (int j = 0; j < kRY; ++j) {
-        const int row = row0 + j;
-        if (row >= rows) break;
-        const float fy = sy * (float)y;
-        int y0 = (int)fy;
-        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
-        const int y1 = y0 + (y0 < Hin - 1);
-        const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
-        const float* r0 = src + (size_t)(d * Hin + y0) * Win;
-        const float* r1 = src + (size_t)(d * Hin + y1) * Win;
-        float o[kRX];
-#pragma unroll
-        for (int k = 0; k < kRX; ++k) {
-            const float a = __ldg(r0 + x0[k]), b = __ldg(r0 + x1[k]);
-            const float c = __ldg(r1 + x0[k]), e = __ldg(r1 + x1[k]);
-            // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair,
-            // one for the rows): bit-identical to the reference's F.interpolate on the upsampling
-            // levels of the chain (pinned on CPU by
-            // tests/test_oracle_golden.py::test_aten_upsample_operation_order)
-            const float top = __fmaf_rn(hx[k], a, __fmul_rn(lx[k], b)), bot = __fmaf_rn(hx[k], c, __fmul_rn(lx[k], e));
-            o[k] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
-        }
-        float* out = dst + (size_t)row * Wout + xb;
-        if (vec) {
-            *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
-        } else {
-#pragma unroll
-            for (int k = 0; k < kRX; ++k)
-                if (xb + k < Wout) out[k] = o[k];
-        }
-        if (++y == Hout) { y = 0; ++d; }
-    }
 }
 
 // ------------------------------ deterministic reduction of the tile records ------------
@@ -320,6 +255,93 @@ scale_gradients_kernel(const __grid_constant__ ScaleTable tab, const float* __re
 
 #include "loss_strip.cuh"
 
+namespace dvsof {
+// ------------------------------ bilinear resize (align_corners) ------------------------
+// A thread produces 4 consecutive pixels of kRY consecutive output rows: the column taps and
+// weights are computed once per thread, a row costs two base pointers, 16 loads and one 16-byte
+// store (when the row pitch allows).  A CTA covers 128 columns x 32 rows of the (D*Hout) x Wout
+// output; 32-bit index arithmetic, one integer division per thread.
+constexpr int kRX = 4, kRY = 4, kRWarps = 8;
+//
+// Side job (the fused training pass, last pyramid level only): the first `side_ctas` CTAs of the
+// launch count the out-of-border pixels of the flow instead (outborder_count_tile) -- work that
+// depends on nothing in the chain, so it runs before / while the resize CTAs wait for the
+// previous level, and the launch as a whole still completes only after that level has.
+template <bool kSide>
+__global__ void __launch_bounds__(32 * kRWarps)
+resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
+                       int Hout, int Wout, int rows /* D * Hout */, int col_ctas,
+                       const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad, int side_ctas) {
+    pdl_launch_dependents();
+    int cta = blockIdx.x;
+    if (kSide) {
+        __shared__ int cnt[kRWarps];
+        if (cta < side_ctas) {
+            outborder_count_tile<kRWarps>(tab, n_bad, cta, cnt);
+            return;
+        }
+        cta -= side_ctas;
+    }
+    pdl_wait();                                  // src may be the previous level of the chain
+    const int cta_y = cta / col_ctas, cta_x = cta - cta_y * col_ctas;
+    const int row0 = (cta_y * kRWarps + (threadIdx.x >> 5)) * kRY;
+    const int xb = (cta_x * 32 + (threadIdx.x & 31)) * kRX;
+    if (row0 >= rows || xb >= Wout) return;
+    const float sy = Hout > 1 ? (float)(Hin - 1) / (float)(Hout - 1) : 0.f;
+    const float sx = Wout > 1 ? (float)(Win - 1) / (float)(Wout - 1) : 0.f;
+    int x0[kRX], x1[kRX];
+    float lx[kRX], hx[kRX];
+#pragma unroll
+    for (int k = 0; k < kRX; ++k) {
+        const int x = min(xb + k, Wout - 1);     // lanes past the row end recompute its last pixel
+        const float fx = sx * (float)x;
+        int xi = (int)fx;
+        xi = xi < Win - 1 ? xi : Win - 1;
+        x0[k] = xi;
+        x1[k] = xi + (xi < Win - 1);
+        lx[k] = fminf(fmaxf(fx - (float)xi, 0.f), 1.f);
+        hx[k] = 1.f - lx[k];
+    }
+    const bool vec = (Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
+    int d = row0 / Hout, y = row0 - d * Hout;
+#pragma unroll
+    for (int j = 0; j < kRY; ++j) {
+        const int row = row0 + j;
+        if (row >= rows) break;
+        const float fy = sy * (float)y;
+        int y0 = (int)fy;
+        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+        const int y1 = y0 + (y0 < Hin - 1);
+        const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
+        const float* r0 = src + (size_t)(d * Hin + y0) * Win;
+        const float* r1 = src + (size_t)(d * Hin + y1) * Win;
+        float* out = dst + (size_t)row * Wout + xb;
+        asm volatile("" : "+l"(r0), "+l"(r1), "+l"(out));   // finished row pointers: tap = base + 32-bit column
+        float o[kRX];
+#pragma unroll
+        for (int k = 0; k < kRX; ++k) {
+            const float a = __ldg(r0 + x0[k]), b = __ldg(r0 + x1[k]);
+            const float c = __ldg(r1 + x0[k]), e = __ldg(r1 + x1[k]);
+            // operation order of ATen's CPU upsample_bilinear2d as compiled (two FMAs per row pair,
+            // one for the rows): bit-identical to the reference's F.interpolate on the upsampling
+            // levels of the chain (pinned on CPU by
+            // tests/test_oracle_golden.py::test_aten_upsample_operation_order)
+            const float top = __fmaf_rn(hx[k], a, __fmul_rn(lx[k], b)), bot = __fmaf_rn(hx[k], c, __fmul_rn(lx[k], e));
+            o[k] = __fmaf_rn(hy, top, __fmul_rn(ly, bot));
+        }
+        if (vec) {
+            *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kRX; ++k)
+                if (xb + k < Wout) out[k] = o[k];
+        }
+        if (++y == Hout) { y = 0; ++d; }
+    }
+}
+
+}  // namespace dvsof
+
 // ---------------------------------------------------------------------------------------
 // C ABI
 // ---------------------------------------------------------------------------------------
@@ -340,6 +362,8 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
         tab->W[s] = sc->W[s];
         tab->tiles_x[s] = (sc->W[s] + kTile - 1) / kTile;
         tab->tiles_y[s] = (sc->H[s] + kTile - 1) / kTile;
+        tab->inv_tx[s] = 1.f / (float)tab->tiles_x[s];
+        tab->inv_per[s] = 1.f / ((float)tab->tiles_x[s] * (float)tab->tiles_y[s]);
         const float hx = (float)(sc->W[s] - 1) / 2.f, hy = (float)(sc->H[s] - 1) / 2.f;
         // a 1-pixel side makes the reference divide by zero (NaN/inf grid); here: NaN grid as well
         tab->hx[s] = hx;
@@ -452,27 +476,29 @@ extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_
                         nullptr, 0, (cudaStream_t)stream_);
 }
 
+// side != nullptr: the launch also runs the out-of-border count of `side` (tiles first) into n_bad
 static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, float* dst,
-                         int32_t Hout, int32_t Wout, cudaStream_t stream, bool pdl) {
+                         int32_t Hout, int32_t Wout, cudaStream_t stream, bool pdl,
+                         const ScaleTable* side = nullptr, int32_t* n_bad = nullptr) {
     if (D < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || !src || !dst)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: bad arguments");
     const int64_t rows = D * Hout;
     if (rows > INT32_MAX / 2 || (int64_t)Hin * Win > INT32_MAX / 2)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: too large");
-    cudaLaunchConfig_t cfg = {};
     const int cta_rows = kRWarps * kRY;
-    cfg.gridDim = dim3((unsigned)((rows + cta_rows - 1) / cta_rows), (unsigned)((Wout + 32 * kRX - 1) / (32 * kRX)));
-    cfg.blockDim = dim3(32 * kRWarps);
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, resize_bilinear_kernel, src, (int)Hin, (int)Win, dst, (int)Hout,
-                                       (int)Wout, (int)rows);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "resize_bilinear_kernel: %s", cudaGetErrorString(e));
-    return DVSOF_OK;
+    const int64_t row_ctas = (rows + cta_rows - 1) / cta_rows, col_ctas = (Wout + 32 * kRX - 1) / (32 * kRX);
+    const int side_ctas = side ? side->cta_begin[DVSOF_MAX_SCALES] : 0;
+    if (row_ctas * col_ctas + side_ctas > INT32_MAX)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: too large");
+    static const ScaleTable none = {};
+    const int grid = (int)(row_ctas * col_ctas) + side_ctas;
+    if (side)
+        return launch_kernel("resize_bilinear_kernel<side>", resize_bilinear_kernel<true>, grid, 32 * kRWarps,
+                             0, stream, pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, (int)rows,
+                             (int)col_ctas, *side, n_bad, side_ctas);
+    return launch_kernel("resize_bilinear_kernel", resize_bilinear_kernel<false>, grid, 32 * kRWarps, 0,
+                         stream, pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, (int)rows,
+                         (int)col_ctas, none, (int32_t*)nullptr, 0);
 }
 
 extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
@@ -483,7 +509,8 @@ extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, i
 // matching + chained pyramid (utils/loss.py:182-210), PDL-chained on the stream
 static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t* fr,
                                     int32_t* match_idx, uint32_t* status, unsigned* tickets,
-                                    int n_tick, cudaStream_t stream) {
+                                    int n_tick, cudaStream_t stream,
+                                    const ScaleTable* side = nullptr, int32_t* n_bad = nullptr) {
     if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
                               fr->sample_idx, fr->n_images, match_idx, status, tickets, n_tick, stream))
         return rc;
@@ -491,7 +518,9 @@ static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_l
     int Hin = fr->H0, Win = fr->W0;
     for (int s = 0; s < sc->n_scales; ++s) {                               // loss.py:207-210
         float* dst = const_cast<float*>(sc->images[s]);
-        if (int rc = launch_resize(src, fr->n_images, Hin, Win, dst, sc->H[s], sc->W[s], stream, true))
+        const bool last = s + 1 == sc->n_scales;
+        if (int rc = launch_resize(src, fr->n_images, Hin, Win, dst, sc->H[s], sc->W[s], stream, true,
+                                   last ? side : nullptr, last ? n_bad : nullptr))
             return rc;
         src = dst; Hin = sc->H[s]; Win = sc->W[s];
     }
@@ -544,10 +573,8 @@ extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
     const LossWorkspace ws = carve(tab, workspace);
     cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
     if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
-    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream))
-        return rc;
-    if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel,
-                               tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, true, tab, n_bad))
+    if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream,
+                                          &tab, n_bad))
         return rc;
     return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, n_bad, ws,
                                     terms, nullptr, loss, stream, true);

@@ -92,18 +92,19 @@ __device__ __forceinline__ bool out_of_border(float gx, float gy) {             
     return gx < -1.f || gx > 1.f || gy < -1.f || gy > 1.f;
 }
 
-// (scale, prediction, tile) of this CTA without integer division: tiles per plane < 2^20, so a
-// float quotient with one correction step is exact.
-__device__ __forceinline__ TileCoord decode_cta_fast(const ScaleTable& tab) {
+// (scale, prediction, tile) of this CTA without integer division: at most 2^23 tiles (checked on
+// the host), so a float product with the host's reciprocal and one correction step is exact.
+__device__ __forceinline__ TileCoord decode_cta_fast(const ScaleTable& tab, int cta) {
     int s = 0;
-    for (int k = 1; k < tab.n_scales; ++k) s += (int)blockIdx.x >= tab.cta_begin[k] ? 1 : 0;
-    const int local = blockIdx.x - tab.cta_begin[s];
+#pragma unroll 1
+    for (int k = 1; k < tab.n_scales; ++k) s += cta >= tab.cta_begin[k] ? 1 : 0;
+    const int local = cta - tab.cta_begin[s];
     const int tx = tab.tiles_x[s], per = tx * tab.tiles_y[s];
-    int n = (int)__fdividef((float)local + 0.5f, (float)per);
+    int n = (int)(((float)local + 0.5f) * tab.inv_per[s]);
     n += (n + 1) * per <= local ? 1 : 0;
     n -= n * per > local ? 1 : 0;
     const int tile = local - n * per;
-    int ty = (int)__fdividef((float)tile + 0.5f, (float)tx);
+    int ty = (int)(((float)tile + 0.5f) * tab.inv_tx[s]);
     ty += (ty + 1) * tx <= tile ? 1 : 0;
     ty -= ty * tx > tile ? 1 : 0;
     return TileCoord{s, n, ty * kTile, (tile - ty * tx) * kTile};
@@ -116,6 +117,8 @@ __device__ __forceinline__ TileCoord decode_cta_fast(const ScaleTable& tab) {
 // 32-bit (one (prediction, channel-pair) block holds < 2^31 elements, checked on the host).
 __device__ __forceinline__ void stage_flow_strip_tile(float2 (*F)[kFP], const float* __restrict__ flow,
                                                       int plane, int H, int W, int y0, int x0) {
+    const float* flow1 = flow + plane;
+    asm volatile("" : "+l"(flow), "+l"(flow1));           // finished channel bases: address = base + 32-bit offset
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kPer = (kFH + kSWarps - 1) / kSWarps;   // 9 row slots per warp (34 rows)
     const int x = x0 + lane;
@@ -128,7 +131,7 @@ __device__ __forceinline__ void stage_flow_strip_tile(float2 (*F)[kFP], const fl
         const bool ok = xok && ty < kFH && y >= 0 && y < H;
         const int off = y * W + x;
         u[k] = ok ? __ldg(flow + off) : 0.f;
-        v[k] = ok ? __ldg(flow + plane + off) : 0.f;
+        v[k] = ok ? __ldg(flow1 + off) : 0.f;
     }
     float eu = 0.f, ev = 0.f;
     const int ety = threadIdx.x >> 1, eright = threadIdx.x & 1;          // threads 0..67: edge columns
@@ -137,7 +140,7 @@ __device__ __forceinline__ void stage_flow_strip_tile(float2 (*F)[kFP], const fl
         const bool ok = ety < kFH && y >= 0 && y < H && xe >= 0 && xe < W;
         const int off = y * W + xe;
         eu = ok ? __ldg(flow + off) : 0.f;
-        ev = ok ? __ldg(flow + plane + off) : 0.f;
+        ev = ok ? __ldg(flow1 + off) : 0.f;
     }
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
@@ -190,7 +193,7 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
     __shared__ bool is_last;
     pdl_launch_dependents();
     pdl_wait();                       // pyramid levels, match_idx, n_bad come from preceding kernels
-    const TileCoord tc = decode_cta_fast(tab);
+    const TileCoord tc = decode_cta_fast(tab, blockIdx.x);
     const int S = tab.n_scales, P = tab.n_pred;
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const int plane = H * W;
@@ -357,31 +360,32 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
 
 // Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
 // pass, which needs it for the gradient of the border term: same coordinates, same comparison.
-// Independent of the pyramid, so it does its work BEFORE griddepcontrol.wait and overlaps the
-// last resize kernel; the wait at the end keeps the completion chain transitive for its dependent.
-__global__ void __launch_bounds__(kSThreads)
-outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad) {
-    __shared__ int cnt[kSWarps];
-    pdl_launch_dependents();
-    const TileCoord tc = decode_cta_fast(tab);
+// One 32x32 tile per CTA of NW warps (tile index `cta`); n_bad must be zero beforehand.
+template <int NW>
+__device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int32_t* __restrict__ n_bad,
+                                                     int cta, int* cnt /* shared, NW ints */) {
+    constexpr int kRows = kTile / NW;
+    const TileCoord tc = decode_cta_fast(tab, cta);
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const int plane = H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    const float* flow1 = flow + plane;
+    asm volatile("" : "+l"(flow), "+l"(flow1));
     const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = tc.x0 + lane, ys = tc.y0 + warp * kSR;
+    const int x = tc.x0 + lane, ys = tc.y0 + warp * kRows;
     const float xf = (float)x;
     int n = 0;
-    float u[kSR], v[kSR];
+    float u[kRows], v[kRows];
 #pragma unroll
-    for (int r = 0; r < kSR; ++r) {
+    for (int r = 0; r < kRows; ++r) {
         const bool ok = x < W && ys + r < H;
         const int off = (ys + r) * W + x;
         u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
-        v[r] = ok ? __ldg(flow + plane + off) : 0.f;
+        v[r] = ok ? __ldg(flow1 + off) : 0.f;
     }
 #pragma unroll
-    for (int r = 0; r < kSR; ++r) {
+    for (int r = 0; r < kRows; ++r) {
         const bool ok = x < W && ys + r < H;
         const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
         n += (ok && out_of_border(gx, gy)) ? 1 : 0;
@@ -392,10 +396,17 @@ outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restri
     if (threadIdx.x == 0) {
         int t = 0;
 #pragma unroll
-        for (int w = 0; w < kSWarps; ++w) t += cnt[w];
+        for (int w = 0; w < NW; ++w) t += cnt[w];
         if (t) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, t);
     }
-    pdl_wait();
+}
+
+// stand-alone launch (dvsof_warp_loss_fused with count_pass; the multiscale call runs the same
+// tiles as a side job of the last pyramid level's resize launch, see resize_bilinear_kernel)
+__global__ void __launch_bounds__(kSThreads)
+outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad) {
+    __shared__ int cnt[kSWarps];
+    outborder_count_tile<kSWarps>(tab, n_bad, blockIdx.x, cnt);
 }
 
 }  // namespace dvsof
