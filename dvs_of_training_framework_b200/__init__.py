@@ -6,6 +6,7 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
     data.get_count_image / EventCrop / RandomRotation /
          frame_generator                                    <- utils/data.py
     transformation.map                                      <- utils/transformation (native ext)
+    eval.flow_error_dense                                   <- utils/eval.py:6-50
 
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
 CPU fallback."""
@@ -14,8 +15,9 @@ from .encoder import compute_event_image, compute_event_image_compact, extend_si
 from .loss import Loss, Losses, charbonier_loss, init_losses, interpolate  # noqa: F401
 from .data import EventCrop, RandomRotation, frame_generator, frame_offsets, get_count_image  # noqa: F401
 from . import transformation  # noqa: F401
+from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
 
 __all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
            'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets',
-           'transformation']
+           'transformation', 'flow_error_dense', 'flow_error_dense_device']

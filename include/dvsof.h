@@ -130,6 +130,19 @@ int dvsof_map_events_write(const float* events, int64_t n_events, int32_t n_cols
 int dvsof_window_offsets(const void* t, int32_t elem_size, int64_t n_events, const double* bounds,
                          int64_t n_bounds, int64_t* out, void* stream);
 
+/* utils/eval.py:6-50 flow_error_dense (per evaluation window, utils/testing.py:84-92): endpoint
+ * error of flow_pred against flow_gt over the first `rows` rows (all rows, or 190 with is_car) of
+ * (H, W, 2) row-major flows [dev; elem size 4 = fp32, 8 = fp64], restricted to pixels with
+ * count_image[y, x] > 0 (the uint64 image of dvsof_count_image; ignored when is_dense) whose GT is
+ * finite and non-zero.  out [dev] 3 doubles: sum of EE, number of points, number with EE < 3 --
+ * AEE = out[0] / out[1], percent_AEE = out[2] / (out[1] + 1e-5).  Deterministic.
+ * workspace: dvsof_flow_error_workspace_bytes(). */
+size_t dvsof_flow_error_workspace_bytes(void);
+int dvsof_flow_error_dense(const void* flow_gt, int32_t gt_elem_size, const void* flow_pred,
+                           int32_t pred_elem_size, const unsigned long long* count_image,
+                           int32_t rows, int32_t W, int32_t is_dense, double* out, void* workspace,
+                           void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Multiscale warp loss.  Replaces utils/loss.py:121-171 (Loss.__call__), :179-214
  * (Losses.__call__) and autograd's backward of both.
