@@ -13,11 +13,12 @@ CPU fallback."""
 from . import _lib  # noqa: F401
 from .encoder import compute_event_image, compute_event_image_compact, extend_size, quantize  # noqa: F401
 from .loss import Loss, Losses, charbonier_loss, init_losses, interpolate  # noqa: F401
-from .data import EventCrop, RandomRotation, frame_generator, frame_offsets, get_count_image  # noqa: F401
+from .data import (EventCrop, RandomRotation, augment_events, frame_generator, frame_offsets,  # noqa: F401
+                   get_count_image, rotation_lut)
 from . import transformation  # noqa: F401
 from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
 
 __all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
-           'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets',
+           'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets', 'augment_events', 'rotation_lut',
            'transformation', 'flow_error_dense', 'flow_error_dense_device']

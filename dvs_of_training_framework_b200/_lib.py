@@ -61,6 +61,12 @@ _SIGNATURES = {
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_map_events_write': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_augment_events_count': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                             C.c_int32, C.c_void_p, C.POINTER(C.c_double), C.c_void_p,
+                                             C.c_void_p, C.c_void_p]),
+    'dvsof_augment_events_write': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                             C.c_int32, C.c_void_p, C.POINTER(C.c_double), C.c_void_p,
+                                             C.c_void_p, C.c_void_p]),
     'dvsof_window_offsets': (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64,
                                        C.c_void_p, C.c_void_p]),
     'dvsof_flow_error_workspace_bytes': (C.c_size_t, []),

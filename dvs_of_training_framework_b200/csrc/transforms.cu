@@ -212,6 +212,60 @@ struct MapWrite {
     }
 };
 
+// ------------------------------ fused augmentation ------------------------------------
+// utils/dataset.py:753-769 applied to the (N, E) fp32 event rows in ONE count + scan + write:
+//   flip      x <- W - x - 1                       (dataset.py:757, fp32 like numpy: two roundings)
+//   rotation  (x, y) <- every LUT target of pixel (int(y), int(x)), in LUT order; unmapped pixels
+//             drop the event                       (data.py:213-216 -> transformation.cpp:35-85)
+//   crop      keep x in [x0, x0+w), y in [y0, y0+h), shift by (x0, y0)     (data.py:24-42)
+// Equal to running the three reference steps one after the other (order preserved), without the
+// two intermediate event arrays.
+struct AugParams {
+    const float* ev; int E; int W; int64_t HW;
+    int flip; float Wf;
+    const int32_t* cnt; const int32_t* off; const int32_t* lut_dst;   // cnt == nullptr: no rotation
+    int crop; double y0, x0, y1, x1;
+    __device__ __forceinline__ float flipped_x(const float* row) const {
+        return flip ? __fsub_rn(__fsub_rn(Wf, row[0]), 1.f) : row[0];
+    }
+    __device__ __forceinline__ bool inside(float x, float y) const {
+        return !crop || ((double)x >= x0 && (double)x < x1 && (double)y >= y0 && (double)y < y1);
+    }
+};
+struct AugCount {
+    AugParams p;
+    __device__ int64_t operator()(int64_t r) const {
+        const float* row = p.ev + r * p.E;
+        const float x = p.flipped_x(row), y = row[1];
+        if (!p.cnt) return p.inside(x, y) ? 1 : 0;
+        const int key = __float2int_rz(y) * p.W + __float2int_rz(x);
+        if (key < 0 || key >= p.HW) return 0;
+        const int32_t* d = p.lut_dst + p.off[key];
+        int64_t c = 0;
+        for (int j = 0, m = p.cnt[key]; j < m; ++j) c += p.inside((float)(d[j] % p.W), (float)(d[j] / p.W)) ? 1 : 0;
+        return c;
+    }
+};
+struct AugWrite {
+    AugParams p; float* out;
+    __device__ __forceinline__ void emit(float* dst, const float* row, float x, float y) const {
+        dst[0] = p.crop ? (float)((double)x - p.x0) : x;               // data.py:41
+        dst[1] = p.crop ? (float)((double)y - p.y0) : y;
+        for (int col = 2; col < p.E; ++col) dst[col] = row[col];
+    }
+    __device__ void operator()(int64_t r, int64_t pos, int64_t) const {
+        const float* row = p.ev + r * p.E;
+        const float x = p.flipped_x(row), y = row[1];
+        if (!p.cnt) { emit(out + pos * p.E, row, x, y); return; }
+        const int key = __float2int_rz(y) * p.W + __float2int_rz(x);
+        const int32_t* d = p.lut_dst + p.off[key];
+        for (int j = 0, m = p.cnt[key]; j < m; ++j) {
+            const float cx = (float)(d[j] % p.W), cy = (float)(d[j] / p.W);
+            if (p.inside(cx, cy)) { emit(out + pos * p.E, row, cx, cy); ++pos; }
+        }
+    }
+};
+
 template <class Count>
 static int run_scan(Count count, int64_t n, int64_t* chunks, int64_t* n_out, cudaStream_t stream) {
     const int64_t nb = (n + kChunk - 1) / kChunk;
@@ -330,6 +384,48 @@ extern "C" int dvsof_map_events_write(const float* events, int64_t n, int32_t n_
     return check_launch("map_events_write");
 }
 
+
+static int aug_params(AugParams* p, const float* events, int64_t n, int32_t n_cols, int32_t H, int32_t W,
+                      int32_t flip, const void* lut_ws, const double* box) {
+    if (n < 0 || n_cols < 2 || H <= 0 || W <= 0 || (n > 0 && !events))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "augment_events: bad arguments");
+    const int64_t HW = (int64_t)H * W;
+    p->ev = events; p->E = n_cols; p->W = W; p->HW = HW;
+    p->flip = flip != 0; p->Wf = (float)W;
+    p->cnt = p->off = p->lut_dst = nullptr;
+    if (lut_ws) {
+        LutView v = lut_view(const_cast<void*>(lut_ws), HW, 0);
+        p->cnt = v.cnt; p->off = v.off; p->lut_dst = v.lut_dst;
+    }
+    p->crop = box != nullptr;
+    if (box) { p->y0 = box[0]; p->x0 = box[1]; p->y1 = box[0] + box[2]; p->x1 = box[1] + box[3]; }
+    else p->y0 = p->x0 = p->y1 = p->x1 = 0;
+    return DVSOF_OK;
+}
+
+extern "C" int dvsof_augment_events_count(const float* events, int64_t n, int32_t n_cols, int32_t H,
+                                          int32_t W, int32_t flip, const void* lut_ws,
+                                          const double* box, void* ev_ws, int64_t* n_out,
+                                          void* stream_) {
+    AugParams p;
+    if (int rc = aug_params(&p, events, n, n_cols, H, W, flip, lut_ws, box)) return rc;
+    if (!ev_ws || !n_out) return fail(DVSOF_ERR_INVALID_ARGUMENT, "augment_events_count: null workspace");
+    return run_scan(AugCount{p}, n, reinterpret_cast<int64_t*>(ev_ws), n_out, (cudaStream_t)stream_);
+}
+
+extern "C" int dvsof_augment_events_write(const float* events, int64_t n, int32_t n_cols, int32_t H,
+                                          int32_t W, int32_t flip, const void* lut_ws,
+                                          const double* box, const void* ev_ws, float* out,
+                                          void* stream_) {
+    AugParams p;
+    if (int rc = aug_params(&p, events, n, n_cols, H, W, flip, lut_ws, box)) return rc;
+    if (!ev_ws) return fail(DVSOF_ERR_INVALID_ARGUMENT, "augment_events_write: null workspace");
+    if (n == 0) return DVSOF_OK;
+    const int64_t nb = (n + kChunk - 1) / kChunk;
+    compact_write_kernel<<<(unsigned)nb, kCompactThreads, 0, (cudaStream_t)stream_>>>(
+        AugCount{p}, AugWrite{p, out}, n, reinterpret_cast<const int64_t*>(ev_ws));
+    return check_launch("augment_events_write");
+}
 
 // ---------------------------------------------------------------------------------------
 // utils/data.py:139-152 frame_generator: np.searchsorted(t, frames.ravel(), side='right') --

@@ -110,6 +110,48 @@ def RandomRotation(interval, shape):
     return rotation
 
 
+def rotation_lut(shape, angle, device='cuda'):
+    """The nearest-neighbour LUT of utils/data.py:186-200 for `angle` degrees as a device-side
+    `RotationLUT` (reusable over many event arrays; feeds `augment_events`)."""
+    H, W = int(shape[0]), int(shape[1])
+    xs, ys = np.meshgrid(range(W), range(H))
+    xs, ys = xs.ravel(), ys.ravel()
+    rad = angle * np.pi / 180
+    mat = np.array([[np.cos(rad), -np.sin(rad)], [np.sin(rad), np.cos(rad)]])
+    r = mat.dot(np.vstack(((xs.astype(float) - W / 2)[None], (ys.astype(float) - H / 2)[None])))
+    x1 = np.rint(r[0] + W / 2).astype(int)
+    y1 = np.rint(r[1] + H / 2).astype(int)
+    m = (x1 >= 0) & (x1 < W) & (y1 >= 0) & (y1 < H)
+    return RotationLUT((H, W), torch.as_tensor(y1[m] * W + x1[m], dtype=torch.int64, device=device),
+                       torch.as_tensor((ys * W + xs)[m], dtype=torch.int64, device=device), device=device)
+
+
+def augment_events(events, shape, is_flip=False, lut=None, box=None):
+    """The event side of utils/dataset.py:753-769 in one device pass: horizontal flip
+    (`x = W - x - 1`), rotation remap through `lut` (a `RotationLUT`, e.g. `rotation_lut(shape,
+    angle)`; None = no rotation) and `EventCrop(box)` with box = [y0, x0, h, w] (None = no crop).
+    Same rows in the same order as the three reference steps applied one after the other.
+    events: (N, E>=2) float32, numpy or CUDA tensor; returns the same kind."""
+    is_np = isinstance(events, np.ndarray)
+    ev = _lib.require_cuda(_to_cuda(events), 'events', torch.float32)
+    n, E = ev.shape
+    H, W = int(shape[0]), int(shape[1])
+    dev = ev.device
+    cbox = (_lib.C.c_double * 4)(*[float(v) for v in box[:4]]) if box is not None else None
+    lut_ptr = _lib.ptr(lut.ws) if lut is not None else None
+    if lut is not None:
+        assert (lut.H, lut.W) == (H, W), 'LUT built for another frame size'
+    with torch.cuda.device(dev):
+        ws = torch.empty(_lib.load().dvsof_compact_workspace_bytes(n), dtype=torch.uint8, device=dev)
+        n_out = torch.empty(1, dtype=torch.int64, device=dev)
+        _lib.call('dvsof_augment_events_count', _lib.ptr(ev), n, E, H, W, int(bool(is_flip)), lut_ptr, cbox,
+                  _lib.ptr(ws), _lib.ptr(n_out), _lib.stream_ptr(dev))
+        out = torch.empty((int(n_out.item()), E), dtype=torch.float32, device=dev)   # data-dependent size
+        _lib.call('dvsof_augment_events_write', _lib.ptr(ev), n, E, H, W, int(bool(is_flip)), lut_ptr, cbox,
+                  _lib.ptr(ws), _lib.ptr(out), _lib.stream_ptr(dev))
+    return out.cpu().numpy() if is_np else out
+
+
 def frame_offsets(t, frames):
     """Per-window event ranges: `np.searchsorted(t, frames.ravel(), side='right').reshape(-1, 2)`
     (utils/data.py:150) computed on the device.  t: sorted timestamps (numpy or CUDA tensor,

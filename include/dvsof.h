@@ -123,6 +123,19 @@ int dvsof_map_events_write(const float* events, int64_t n_events, int32_t n_cols
                            int32_t W, const void* lut_ws, const void* ev_ws, float* out,
                            void* stream);
 
+/* The event side of the augmentation block of utils/dataset.py:753-769 in one count + scan +
+ * write over the (N, E) fp32 rows: optional horizontal flip x <- W - x - 1 (:757), optional
+ * rotation remap through a LUT built by dvsof_map_events_build (utils/data.py:213-216; lut_ws ==
+ * NULL: none), optional crop to box = [y0, x0, h, w] with shift (utils/data.py:24-42 EventCrop; box
+ * [host, 4 doubles] == NULL: none).  Same rows, same order as the three reference steps run in
+ * sequence.  ev_ws: dvsof_compact_workspace_bytes(N); *n_out [dev int64] = number of output rows. */
+int dvsof_augment_events_count(const float* events, int64_t n_events, int32_t n_cols, int32_t H,
+                               int32_t W, int32_t flip, const void* lut_ws, const double* box,
+                               void* ev_ws, int64_t* n_out, void* stream);
+int dvsof_augment_events_write(const float* events, int64_t n_events, int32_t n_cols, int32_t H,
+                               int32_t W, int32_t flip, const void* lut_ws, const double* box,
+                               const void* ev_ws, float* out, void* stream);
+
 /* utils/data.py:139-152 frame_generator: out[k] = np.searchsorted(t, bounds[k], side='right') for
  * every window boundary (frames.ravel()); t sorted ascending, fp32 (elem_size 4) or fp64 (8),
  * compared in fp64 as numpy does.  The (start, stop) offset pairs slice the event arrays per

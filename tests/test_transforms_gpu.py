@@ -109,3 +109,58 @@ def test_frame_generator_matches_reference_slicing(dtype):
         for comp, ref in zip(e, ev):
             assert np.array_equal(comp, ref[a:b])
     assert dd.frame_offsets(t[:0], frames).sum() == 0
+
+
+# ------------------------------------------------------------------------------------------
+# fused augmentation (flip + rotation LUT + crop in one pass), utils/dataset.py:753-769
+# ------------------------------------------------------------------------------------------
+def _reference_sequence(ev, shape, flip, angle, box):
+    """The three reference steps one after the other, on the oracle (numpy)."""
+    H, W = shape
+    ev = ev.copy()
+    if flip:
+        ev[:, 0] = W - ev[:, 0] - 1                                   # dataset.py:757
+    if angle is not None:
+        src, dst = eo.rotation_lut(shape, angle)
+        ev = eo.map_events(ev, shape, src, dst)
+    if box is not None:
+        ev = eo.event_crop(ev, box)
+    return ev
+
+
+@pytest.mark.parametrize('flip,angle,box', [
+    (False, None, None), (True, None, None), (False, 17.5, None), (False, None, [2, 45, 256, 256]),
+    (True, -23.0, [2, 45, 256, 256]), (True, 90.0, [0, 0, 260, 346]), (False, 5.0, [100, 100, 1, 1]),
+])
+def test_augment_events_equals_reference_sequence(flip, angle, box):
+    H, W = 260, 346
+    rng = np.random.default_rng(11)
+    n = 50001
+    ev = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), np.sort(rng.random(n)),
+                   rng.choice([-1, 1], n), rng.integers(0, 2, n)], 1).astype(np.float32)
+    want = _reference_sequence(ev, (H, W), flip, angle, box)
+    lut = dv.rotation_lut((H, W), angle) if angle is not None else None
+    got = dv.augment_events(ev, (H, W), is_flip=flip, lut=lut, box=box)
+    assert got.dtype == np.float32 and got.shape == want.shape and np.array_equal(got, want)
+    # and the same through the separate device ops (each pinned against the reference goldens)
+    seq = torch.tensor(ev).cuda()
+    if flip:
+        seq[:, 0] = W - seq[:, 0] - 1
+    if lut is not None:
+        seq = lut.apply(seq.contiguous())
+    if box is not None:
+        seq = dv.EventCrop(box)(seq)
+    assert np.array_equal(seq.cpu().numpy(), got)
+
+
+def test_augment_events_golden_rotation_then_crop(golden):
+    """Reference outputs (tests/golden/transforms.npz: RandomRotation of utils/data.py run
+    unmodified) followed by the reference's EventCrop semantics."""
+    g = np.load(golden / 'transforms.npz')
+    e5 = np.hstack([g['events'], np.zeros((g['events'].shape[0], 1))]).astype(np.float32)
+    box = g['box'].tolist()
+    for ang in ('0.0', '90.0', '17.5'):
+        want = eo.event_crop(g[f'rot_events_{ang}'], box)
+        got = dv.augment_events(e5, (260, 346), lut=dv.rotation_lut((260, 346), float(ang)), box=box)
+        assert np.array_equal(got, want)
+    assert dv.augment_events(np.zeros((0, 5), np.float32), (260, 346), is_flip=True, box=box).shape == (0, 5)
