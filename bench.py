@@ -117,11 +117,19 @@ class Clocks:
 
 
 class L2Flusher:
+    """Evicts the 126 MB L2 between timed steps: a 256 MiB buffer is written (memset).  With
+    DVSOF_FLUSH=write+read a second 256 MiB buffer is then READ, so that the lines left in L2 are
+    clean -- otherwise the timed kernel also pays the write-back of the flusher's dirty lines."""
+    MODE = os.environ.get('DVSOF_FLUSH', 'write')
+
     def __init__(self, device):
         self.buf = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
+        self.rd = torch.zeros(64 << 20, dtype=torch.int32, device=device) if self.MODE == 'write+read' else None
 
     def __call__(self):
         self.buf.zero_()
+        if self.rd is not None:
+            self.rd.sum()
 
 
 def time_steps(fn, K, W, flush, inner=None):

@@ -226,6 +226,65 @@ encode_vec2_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     if (flags) atomicOr(status, flags);
 }
 
+// Software-pipelined persistent variant: 2 events per thread per iteration, the loads of
+// iteration k+1 are issued BEFORE the reductions of iteration k, so that one thread always has a
+// DRAM request in flight while its REDs drain into L2 -- in the one-pass kernels above a short
+// stream (cfg2: 1 M events = 3.5 events per resident thread) runs as "everybody loads, then
+// everybody reduces".  Measured (profiles/r01ab_variants.jsonl): no gain -- cfg2 stays at 22.6 us
+// with 2 or 4 CTAs/SM of this kernel exactly as with every one-pass variant, cfg3/cfg4 lose 10-15 %
+// to the smaller grid.  Kept as experiment variants 12 / 14; the cfg2 time is not a scheduling
+// artefact of the one-pass kernels.
+struct EventPair { longlong2 x, y, p, b; float2 t; };
+__device__ __forceinline__ EventPair load_pair(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                                               const float* __restrict__ t, const int64_t* __restrict__ p,
+                                               const int64_t* __restrict__ b, int64_t i, bool valid) {
+    EventPair e;
+    e.b = make_longlong2(0, 0);
+    if (valid) {
+        e.x = __ldcs(reinterpret_cast<const longlong2*>(x) + i);
+        e.y = __ldcs(reinterpret_cast<const longlong2*>(y) + i);
+        e.p = __ldcs(reinterpret_cast<const longlong2*>(p) + i);
+        e.b = __ldcs(reinterpret_cast<const longlong2*>(b) + i);
+        e.t = __ldcs(reinterpret_cast<const float2*>(t) + i);
+    }
+    return e;
+}
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB)
+encode_pipe_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                   const float* __restrict__ t, const int64_t* __restrict__ p,
+                   const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
+                   int n_samples, int H, int W, float* __restrict__ out,
+                   uint32_t* __restrict__ status) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nvec = n >> 1;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned flags = 0;
+    int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);   // warp-uniform
+    EventPair cur = load_pair(x, y, t, p, b, base + lane, base + lane < nvec);
+    pdl_wait();                                   // `out` zeroed + `sd` ready from here on
+    while (base < nvec) {
+        const int64_t i = base + lane, nbase = base + stride;
+        const bool valid = i < nvec;
+        const EventPair nxt = load_pair(x, y, t, p, b, nbase + lane, nbase < nvec && nbase + lane < nvec);
+        long long bnext = __shfl_down_sync(0xffffffffu, cur.b.x, 1);
+        if (valid) {
+            const int64_t after = 2 * (i + 1);
+            if (lane == 31 || i + 1 >= nvec) bnext = (after < n) ? b[after] : cur.b.y;
+            if (cur.b.x > cur.b.y || cur.b.y > bnext) flags |= DVSOF_ST_NOT_GROUPED;
+            flags |= scatter_event(cur.x.x, cur.y.x, cur.t.x, cur.p.x, cur.b.x, sd, n_samples, H, W, out);
+            flags |= scatter_event(cur.x.y, cur.y.y, cur.t.y, cur.p.y, cur.b.y, sd, n_samples, H, W, out);
+        }
+        cur = nxt;
+        base = nbase;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
+        const int64_t i = n - 1;
+        flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
+    }
+    if (flags) atomicOr(status, flags);
+}
+
 // ---------------------------------------------------------------------------------------
 // TMA-staged persistent variant: one elected thread streams whole event chunks
 // (x,y,p,b: CH*8 B each, t: CH*4 B) into a STAGES-deep shared-memory ring with bulk async copies
@@ -572,6 +631,10 @@ static int encode_scatter_impl(const EncodeArgs& a, cudaStream_t stream, bool pd
                                       encode_grid((a.n >> 1) + 1, 256, 48), 256, 0, stream, pdl, a);
         case 11: return launch_stream(encode_vec4_kernel<4>, "encode_vec4_kernel<4>",
                                       encode_grid((a.n >> 2) + 1, 256, 32), 256, 0, stream, pdl, a);
+        case 12: return launch_stream(encode_pipe_kernel<4>, "encode_pipe_kernel<4>",
+                                      encode_grid((a.n >> 1) + 1, 256, 4), 256, 0, stream, pdl, a);
+        case 14: return launch_stream(encode_pipe_kernel<4>, "encode_pipe_kernel<4>",
+                                      encode_grid((a.n >> 1) + 1, 256, 2), 256, 0, stream, pdl, a);
         // default: up to 128 CTAs per SM in the grid (3 resident at a time), i.e. one pass of 4
         // events per thread for anything below ~78 M events: fresh CTAs keep the load phase of one
         // and the RED phase of another interleaved.  Measured (profiles/r01h_variants.jsonl):
