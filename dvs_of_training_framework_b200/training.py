@@ -166,6 +166,71 @@ class GradientAllreducer:
             dist.broadcast(t.data, src=0, group=self.group)
 
 
+def _upload(batch, device, is_raw):
+    """H2D of what process_minibatch needs (utils/training.py:46-56), non-blocking."""
+    out = dict(batch)
+    for k in ('timestamps', 'sample_idx', 'images'):
+        out[k] = batch[k].to(device, non_blocking=True)
+    if is_raw:
+        ev = dict(batch['events'])
+        for k in set.difference(set(ev.keys()), {'size'}):
+            ev[k] = ev[k].to(device, non_blocking=True)
+        out['events'] = ev
+    else:
+        out['data'] = batch['data'].to(device, non_blocking=True)
+    return out
+
+
+def _tensors(batch):
+    for v in batch.values():
+        if isinstance(v, torch.Tensor):
+            yield v
+        elif isinstance(v, dict):
+            yield from _tensors(v)
+
+
+class DevicePrefetcher:
+    """Wraps a loader of collated host batches: keeps this rank's shard (by sample) and uploads
+    batch k+1 on a copy stream while the caller computes on batch k, so the per-step H2D
+    (36 B/event in the int64 training form) hides behind cuDNN instead of preceding it -- with 8
+    ranks sharing one host the serial copy was 10 % of the step.  Yields device-resident batches
+    that `process_minibatch` takes as is (`.to(device)` of a device tensor is a no-op).  Pinned
+    host tensors make the copies asynchronous; pageable ones still work (synchronous copy)."""
+
+    def __init__(self, loader, device, is_raw=True, rank=0, world=1):
+        self.loader, self.device, self.is_raw = loader, torch.device(device), is_raw
+        self.rank, self.world = rank, world
+        self.stream = torch.cuda.Stream(self.device) if self.device.type == 'cuda' else None
+
+    def _stage(self, batch):
+        if batch is None:
+            return None
+        local = dict(shard_batch(batch, self.rank, self.world))
+        local['global_size'] = batch['size']                     # what the reference's counters see
+        local['global_events'] = batch['events']['x'].numel() if self.is_raw else 0
+        if self.stream is None:
+            return _upload(local, self.device, self.is_raw)
+        with torch.cuda.stream(self.stream):
+            return _upload(local, self.device, self.is_raw)
+
+    def __iter__(self):
+        it = iter(self.loader)
+        nxt = self._stage(next(it, None))
+        while nxt is not None:
+            cur = nxt
+            if self.stream is not None:
+                compute = torch.cuda.current_stream(self.device)
+                compute.wait_stream(self.stream)                 # batch k has landed
+                for t in _tensors(cur):
+                    if t.is_cuda:
+                        t.record_stream(compute)                 # allocated on the copy stream
+            nxt = self._stage(next(it, None))                    # upload k+1 starts now
+            yield cur
+
+    def __len__(self):
+        return len(self.loader)
+
+
 def process_minibatch(model, batch, timers, device, is_raw, evaluator, weights,
                       return_prediction=False):
     """utils/training.py:37-86, unchanged in meaning: H2D of the batch, model forward (whose
@@ -208,7 +273,7 @@ def add_loss(loss_sum, loss_values):
 def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, evaluator,
           weights=[0.5, 1, 1], is_raw=True, accumulation_steps=1, timers=FakeTimer(), hooks={},
           init_step=0, init_samples_passed=0, max_events_per_batch: int = 350000,
-          reducer: GradientAllreducer = None):
+          reducer: GradientAllreducer = None, prefetch: bool = False):
     """utils/training.py:89-235 with the data-parallel partition: under an initialised process
     group every rank receives the same global batch from `loader`, keeps its shard (by sample)
     and averages gradients through `reducer` before the optimizer step.  Logging, hooks,
@@ -227,11 +292,14 @@ def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, e
     init_batch = init_step * accumulation_steps
     global_step = init_batch
     num_skipped = 0
+    if prefetch:       # shard + upload one batch ahead on a copy stream (DevicePrefetcher)
+        loader = DevicePrefetcher(loader, device, is_raw, rank, world)
     timers('batch_construction').start()
     for batch in loader:
         if global_step == num_steps * accumulation_steps:
             break
-        num_events = batch['events']['x'].numel() if is_raw else 0
+        num_events = batch['global_events'] if 'global_events' in batch else \
+            (batch['events']['x'].numel() if is_raw else 0)
         if num_events > max_events_per_batch:                       # training.py:141-150
             num_skipped += 1
             num_processed = global_step - init_batch
@@ -241,11 +309,11 @@ def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, e
             continue
         global_step += 1
         timers('batch_construction').stop()
-        samples_passed += batch['size']
+        samples_passed += batch.get('global_size', batch['size'])
         is_step_boundary = global_step % accumulation_steps == 0
         if reducer is not None:
             reducer.enabled = is_step_boundary     # reduce once per optimizer step
-        local = shard_batch(batch, rank, world)
+        local = batch if prefetch else shard_batch(batch, rank, world)
         loss, (smoothness, photometric, out_reg), tags = process_minibatch(
             model, local, timers, device, is_raw, evaluator, weights)
         loss /= accumulation_steps

@@ -192,3 +192,32 @@ def test_train_loop_contract_single_process():
     assert 'Train/smoothness loss/4x4' in tags and 'General/learning rate/0' in tags
     v = tr.validate(model, 'cpu', [batch], 8, log, OracleEvaluator())
     assert v > 0 and any(t == 'General/Validation loss' for t, _, _ in log.rows)
+
+
+def test_prefetching_loader_is_transparent():
+    """train(..., prefetch=True) (DevicePrefetcher: shard + upload one batch ahead) takes the same
+    steps, hooks and weights as the plain loop, including the over-large-batch skip and the
+    sample counter, which must keep seeing the GLOBAL batch."""
+    def run(prefetch):
+        torch.manual_seed(0)
+        model = TinyFlowNet()
+        opt = torch.optim.SGD(model.parameters(), lr=0.01)
+        sched = torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0)
+        calls = []
+        batch, big = _batch(B=2, n=200), _batch(B=2, n=5000, seed=9)
+        steps = tr.train(model, 'cpu', [batch, big, batch, batch, batch], opt, 2, sched, Log(),
+                         OracleEvaluator(), accumulation_steps=2,
+                         hooks={'h': lambda s, n: calls.append((s, n))}, max_events_per_batch=3000,
+                         prefetch=prefetch)
+        return steps, calls, [p.detach().clone() for p in model.parameters()]
+    s0, c0, w0 = run(False)
+    s1, c1, w1 = run(True)
+    assert s0 == s1 == 2 and c0 == c1 == [(1, 4), (2, 8)]
+    for a, b in zip(w0, w1):
+        assert torch.equal(a, b)
+    # the wrapper alone: shards by sample, keeps order, reports the global size
+    batch = _batch(B=4, n=100)
+    got = list(tr.DevicePrefetcher([batch, batch], 'cpu', True, rank=1, world=2))
+    assert len(got) == 2 and got[0]['size'] == 2 and got[0]['global_size'] == 4
+    assert got[0]['global_events'] == batch['events']['x'].numel()
+    assert int(got[0]['events']['sample_index'].min()) == 0 and got[0]['images'].shape[0] == 4
