@@ -205,11 +205,12 @@ __device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, floa
     }
 }
 
-// workspace carved by the host: tile records | pair records | tickets (1 + S*P words)
+// workspace carved by the host: tile records | pair records | tickets (1 + S*P words) | tile counts
 struct LossWorkspace {
     float* partials;
     double* pair_rec;
     unsigned* tickets;     // [0] = pairs finished; [1 + s*P + n] = tiles of the pair finished
+    int32_t* tile_bad;     // out-of-border count of every tile (multiscale fused pass)
 };
 
 // Called by every CTA after its tile record is in `partials` (written by threads < 7, then a
@@ -271,13 +272,14 @@ template <bool kSide>
 __global__ void __launch_bounds__(32 * kRWarps)
 resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* __restrict__ dst,
                        int Hout, int Wout, int rows /* D * Hout */, int col_ctas,
-                       const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad, int side_ctas) {
+                       const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad, int side_ctas,
+                       int bad_per_tile) {
     pdl_launch_dependents();
     int cta = blockIdx.x;
     if (kSide) {
         __shared__ int cnt[kRWarps];
         if (cta < side_ctas) {
-            outborder_count_tile<kRWarps>(tab, n_bad, cta, cnt);
+            outborder_count_tile<kRWarps>(tab, n_bad, bad_per_tile != 0, cta, cnt);
             return;
         }
         cta -= side_ctas;
@@ -340,6 +342,217 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
     }
 }
 
+// ------------------------------ pyramid chain in one launch ----------------------------
+// utils/loss.py:207-210 resizes level s from level s-1, so the levels of ONE frame form a
+// dependency chain, but frames -- and row slabs of a frame -- are independent: `slabs` CTAs
+// (1024 threads each) share a frame.  CTA g owns rows [H*g/slabs, H*(g+1)/slabs) of every level;
+// walking the chain backwards gives the rows of each earlier level those depend on, which the CTA
+// computes for itself (a few halo rows are computed twice, never stored twice).  A level stays in
+// shared memory (two alternating buffers) for the next one to read -- the same per-pixel
+// arithmetic as resize_bilinear_kernel on the same values, hence the same bits -- while the owned
+// rows also go to global memory for the loss kernel.  One launch replaces the first `n_levels`
+// resize launches (normally all of them) AND the matching kernel: CTA 0 matches flows to frames
+// (utils/loss.py:182-206) and arms the tickets.  Side CTAs (last in the grid) run the border
+// count when this launch is the last of the pyramid.
+struct PyramidArgs {
+    const float* src; int D, H0, W0;
+    int n_levels;                                  // levels produced by this launch (>= 1)
+    int slabs;                                     // CTAs per frame
+    int H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
+    float sy[DVSOF_MAX_SCALES], sx[DVSOF_MAX_SCALES];   // source step per output row / column (host-computed)
+    float* dst[DVSOF_MAX_SCALES];
+    int buf_b_offset;                              // floats: buffer A = [0, off), buffer B = [off, ...)
+    const float* flow_ts; const int64_t* flow_sample_idx; int P;
+    const float* timestamps; const int64_t* sample_idx;
+    int32_t* match_idx; uint32_t* status; unsigned* tickets; int n_tickets;
+};
+constexpr int kPyrThreads = 1024;                   // at most; the host launches fewer warps for small slabs
+
+
+struct RowRange { int lo, hi; };                   // [lo, hi); empty when lo >= hi
+
+// source row of output row y (align_corners=True), exactly as the resize arithmetic picks it
+__host__ __device__ inline float pyr_step(int n_in, int n_out) {
+    return n_out > 1 ? (float)(n_in - 1) / (float)(n_out - 1) : 0.f;
+}
+__host__ __device__ inline int pyr_src_row(int Hin, float sy, int y) {
+    int y0 = (int)(sy * (float)y);
+    return y0 < Hin - 1 ? y0 : Hin - 1;
+}
+
+// rows of every level CTA `g` of a frame has to produce: need[l] (superset of its own rows)
+__host__ __device__ inline void pyr_plan_rows(const PyramidArgs& a, int g, RowRange* own, RowRange* need) {
+    for (int l = 0; l < a.n_levels; ++l) {
+        own[l].lo = (int)((unsigned)(a.H[l] * g) / (unsigned)a.slabs);          // H < 2^26, slabs <= 16
+        own[l].hi = (int)((unsigned)(a.H[l] * (g + 1)) / (unsigned)a.slabs);
+    }
+    need[a.n_levels - 1] = own[a.n_levels - 1];
+    for (int l = a.n_levels - 1; l > 0; --l) {
+        RowRange r = own[l - 1];
+        if (need[l].lo < need[l].hi) {
+            const int Hin = a.H[l - 1];
+            const int lo = pyr_src_row(Hin, a.sy[l], need[l].lo);
+            int hi = pyr_src_row(Hin, a.sy[l], need[l].hi - 1) + 2;      // y1 = y0 + 1, exclusive
+            hi = hi < Hin ? hi : Hin;
+            if (r.lo >= r.hi) { r.lo = lo; r.hi = hi; }
+            else { r.lo = lo < r.lo ? lo : r.lo; r.hi = hi > r.hi ? hi : r.hi; }
+        }
+        need[l - 1] = r;
+    }
+}
+
+// Rows [nd.lo, nd.hi) of one level for one frame, from `in` (row in_row0 of the source level is
+// its first row).  A warp task is kPyrRows rows x 128 columns: a lane owns 4 consecutive columns and
+// computes their taps and weights once per task.  The horizontal interpolation of a SOURCE row is
+// kept while consecutive output rows keep using it (when upsampling by 2, 8 output rows touch 5
+// source rows, not 16) -- it is the same expression on the same operands whichever output row
+// consumes it, so the bits do not change.  Owned rows go to `out` (global), all rows to `keep`
+// (shared, relative to nd.lo) when there is a next level.
+constexpr int kPyrRows = 8;
+__device__ __forceinline__ void pyr_hlerp(const float* row, const int* ox0, const int* ox1,
+                                          const float* lx, const float* hx, float* h) {
+    const char* base = reinterpret_cast<const char*>(row);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float p = *reinterpret_cast<const float*>(base + ox0[j]);
+        const float q = *reinterpret_cast<const float*>(base + ox1[j]);
+        h[j] = __fmaf_rn(hx[j], p, __fmul_rn(lx[j], q));
+    }
+}
+
+__device__ __forceinline__ void pyr_level_rows(const float* in, int Hin, int Win, int in_row0,
+                                               float* __restrict__ out, float* keep, int Wout,
+                                               float sy, float sx, RowRange nd, RowRange ow) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vec = (Wout & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    // rows per task (a power of two): up to kPyrRows, fewer when that would leave warps without a task
+    const int n_rows = nd.hi - nd.lo, n_warps = blockDim.x >> 5;
+    const int col_chunks = (Wout + 127) >> 7;
+    int rpt_log = 3;
+    while (rpt_log > 1 && (n_rows >> rpt_log) * col_chunks < n_warps) --rpt_log;
+    const int rpt = 1 << rpt_log;
+    const int n_tasks = ((n_rows + rpt - 1) >> rpt_log) * col_chunks;
+    const float inv_cc = 1.f / (float)col_chunks;
+    asm volatile("" : "+l"(out));
+    for (int task = warp; task < n_tasks; task += n_warps) {
+        // task = row task * col_chunks + column chunk; the float quotient is exact below 2^21 tasks
+        const int rt = n_tasks < (1 << 21) ? (int)(((float)task + 0.5f) * inv_cc) : task / col_chunks;
+        const int ybeg = nd.lo + (rt << rpt_log);
+        const int xq = ((task - rt * col_chunks) * 32 + lane) * 4;
+        if (xq >= Wout) continue;
+        int ox0[4], ox1[4];                                   // byte offsets of the taps in a source row
+        float lx[4], hx[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float fx = sx * (float)(xq + j);
+            int t = (int)fx;
+            t = t < Win - 1 ? t : Win - 1;
+            ox0[j] = t * 4;
+            ox1[j] = (t + (t < Win - 1)) * 4;
+            lx[j] = fminf(fmaxf(fx - (float)t, 0.f), 1.f);
+            hx[j] = 1.f - lx[j];
+        }
+        int cy0 = -1, cy1 = -1;                               // source rows whose interpolations h0 / h1 hold
+        float h0[4] = {0.f, 0.f, 0.f, 0.f}, h1[4] = {0.f, 0.f, 0.f, 0.f};
+        const int yend = min(ybeg + rpt, nd.hi);
+#pragma unroll 1                                      // compact code: the kernel starts with a cold i-cache
+        for (int y = ybeg; y < yend; ++y) {
+            const float fy = sy * (float)y;
+            int y0 = (int)fy;
+            y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+            const int y1 = y0 + (y0 < Hin - 1);
+            const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
+            float top[4], bot[4];
+            if (y0 == cy0) {                                  // all of these are warp-uniform
+#pragma unroll
+                for (int j = 0; j < 4; ++j) top[j] = h0[j];
+            } else if (y0 == cy1) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) top[j] = h1[j];
+            } else {
+                pyr_hlerp(in + (y0 - in_row0) * Win, ox0, ox1, lx, hx, top);
+            }
+            if (y1 == y0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bot[j] = top[j];
+            } else if (y1 == cy1) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bot[j] = h1[j];
+            } else {
+                pyr_hlerp(in + (y1 - in_row0) * Win, ox0, ox1, lx, hx, bot);
+            }
+            cy0 = y0; cy1 = y1;
+            float o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                o[j] = __fmaf_rn(hy, top[j], __fmul_rn(ly, bot[j]));           // ATen's operation order
+                h0[j] = top[j]; h1[j] = bot[j];
+            }
+            const bool mine = y >= ow.lo && y < ow.hi;
+            if (vec) {
+                const float4 v = make_float4(o[0], o[1], o[2], o[3]);
+                if (mine) *reinterpret_cast<float4*>(out + y * Wout + xq) = v;
+                if (keep) *reinterpret_cast<float4*>(keep + (y - nd.lo) * Wout + xq) = v;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (xq + j >= Wout) break;
+                    if (mine) out[y * Wout + xq + j] = o[j];
+                    if (keep) keep[(y - nd.lo) * Wout + xq + j] = o[j];
+                }
+            }
+        }
+    }
+}
+
+template <bool kSide>
+__global__ void __launch_bounds__(kPyrThreads)
+pyramid_chain_kernel(const __grid_constant__ PyramidArgs a, const __grid_constant__ ScaleTable tab,
+                     int32_t* __restrict__ n_bad, int side_ctas, int bad_per_tile) {
+    extern __shared__ __align__(16) float levels_smem[];
+    pdl_launch_dependents();
+    const int cta = blockIdx.x;
+    if (kSide) {                                   // after the pyramid CTAs (the critical path) in the grid
+        const int n_pyr = a.D * a.slabs;
+        if (cta >= n_pyr) {
+            outborder_count_warp_tile(tab, n_bad, bad_per_tile != 0,      // a tile per warp
+                                      (cta - n_pyr) * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5));
+            return;
+        }
+    }
+    if (cta == 0) {                                // utils/loss.py:182-206 (see match_timestamps_kernel)
+        for (int i = threadIdx.x; i < 2 * a.P; i += blockDim.x) {
+            const int k = i / a.P, p = i - k * a.P;
+            const float want = a.flow_ts[2 * p + k];
+            const int64_t smp = a.flow_sample_idx[p];
+            int hits = 0, idx = 0;
+#pragma unroll 2
+            for (int q = 0; q < a.D; ++q)
+                if (a.timestamps[q] == want && a.sample_idx[q] == smp) { ++hits; idx = q; }
+            if (hits != 1) atomicOr(a.status, DVSOF_ST_NO_MATCH);
+            a.match_idx[i] = idx;
+        }
+        for (int k = threadIdx.x; k < a.n_tickets; k += blockDim.x) a.tickets[k] = 0u;
+    }
+    const int d = cta / a.slabs, g = cta - d * a.slabs;
+    __shared__ RowRange own[DVSOF_MAX_SCALES], need[DVSOF_MAX_SCALES];
+    if (threadIdx.x == 0) pyr_plan_rows(a, g, own, need);      // once per CTA, not once per warp
+    __syncthreads();
+#pragma unroll 1
+    for (int l = 0; l < a.n_levels; ++l) {
+        const int Hout = a.H[l], Wout = a.W[l];
+        float* keep = (l + 1 < a.n_levels) ? levels_smem + ((l & 1) ? a.buf_b_offset : 0) : nullptr;
+        float* out = a.dst[l] + (size_t)d * Hout * Wout;
+        if (l == 0)                                // from the frame in global memory
+            pyr_level_rows(a.src + (size_t)d * a.H0 * a.W0, a.H0, a.W0, 0, out, keep, Wout, a.sy[0], a.sx[0],
+                           need[0], own[0]);
+        else                                       // from the previous level's rows in shared memory
+            pyr_level_rows(levels_smem + ((l & 1) ? 0 : a.buf_b_offset), a.H[l - 1], a.W[l - 1], need[l - 1].lo,
+                           out, keep, Wout, a.sy[l], a.sx[l], need[l], own[l]);
+        __syncthreads();
+    }
+}
+
 }  // namespace dvsof
 
 // ---------------------------------------------------------------------------------------
@@ -391,7 +604,7 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
     return DVSOF_OK;
 }
 
-// workspace layout: tile records | pair records | tickets
+// workspace layout: tile records | pair records | tickets | per-tile out-of-border counts
 static size_t partial_bytes(const ScaleTable& tab) {
     return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
 }
@@ -399,19 +612,22 @@ static size_t pair_bytes(const ScaleTable& tab) {
     return round_up((size_t)tab.n_scales * tab.n_pred * kPairRec * sizeof(double), 256);
 }
 static int n_tickets(const ScaleTable& tab) { return 1 + tab.n_scales * tab.n_pred; }
+static size_t ticket_bytes(const ScaleTable& tab) { return round_up((size_t)n_tickets(tab) * 4, 256); }
 static LossWorkspace carve(const ScaleTable& tab, void* workspace) {
     char* p = static_cast<char*>(workspace);
     LossWorkspace ws;
     ws.partials = reinterpret_cast<float*>(p);
     ws.pair_rec = reinterpret_cast<double*>(p + partial_bytes(tab));
     ws.tickets = reinterpret_cast<unsigned*>(p + partial_bytes(tab) + pair_bytes(tab));
+    ws.tile_bad = reinterpret_cast<int32_t*>(p + partial_bytes(tab) + pair_bytes(tab) + ticket_bytes(tab));
     return ws;
 }
 
 extern "C" size_t dvsof_loss_workspace_bytes(const dvsof_loss_scales_t* sc) {
     ScaleTable tab;
     if (build_table(sc, &tab, false)) return 0;
-    return partial_bytes(tab) + pair_bytes(tab) + round_up((size_t)n_tickets(tab) * 4, 256);
+    return partial_bytes(tab) + pair_bytes(tab) + ticket_bytes(tab) +
+           round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * sizeof(int32_t), 256);
 }
 
 static int zero_tickets(const ScaleTable& tab, const LossWorkspace& ws, cudaStream_t stream) {
@@ -423,10 +639,11 @@ static int zero_tickets(const ScaleTable& tab, const LossWorkspace& ws, cudaStre
 template <bool kVal, bool kGrad>
 static int launch_strip(const char* what, const ScaleTable& tab, const int32_t* match_idx,
                         const float* grad_terms, const int32_t* n_bad_in, const LossWorkspace& ws,
-                        float* terms, int32_t* n_bad_out, float* loss, cudaStream_t stream, bool pdl) {
+                        float* terms, int32_t* n_bad_out, float* loss, cudaStream_t stream, bool pdl,
+                        int bad_per_tile = 0) {
     return launch_kernel(what, warp_loss_strip_kernel<kVal, kGrad>, tab.cta_begin[DVSOF_MAX_SCALES],
-                         kSThreads, 0, stream, pdl, tab, match_idx, grad_terms, n_bad_in, ws, terms,
-                         n_bad_out, loss);
+                         kSThreads, 0, stream, pdl, tab, match_idx, grad_terms, n_bad_in, bad_per_tile, ws,
+                         terms, n_bad_out, loss);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -479,7 +696,7 @@ extern "C" int dvsof_match_timestamps(const float* flow_ts, const int64_t* flow_
 // side != nullptr: the launch also runs the out-of-border count of `side` (tiles first) into n_bad
 static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, float* dst,
                          int32_t Hout, int32_t Wout, cudaStream_t stream, bool pdl,
-                         const ScaleTable* side = nullptr, int32_t* n_bad = nullptr) {
+                         const ScaleTable* side = nullptr, int32_t* n_bad = nullptr, int bad_per_tile = 0) {
     if (D < 1 || Hin < 1 || Win < 1 || Hout < 1 || Wout < 1 || !src || !dst)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "resize_bilinear: bad arguments");
     const int64_t rows = D * Hout;
@@ -495,10 +712,10 @@ static int launch_resize(const float* src, int64_t D, int32_t Hin, int32_t Win, 
     if (side)
         return launch_kernel("resize_bilinear_kernel<side>", resize_bilinear_kernel<true>, grid, 32 * kRWarps,
                              0, stream, pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, (int)rows,
-                             (int)col_ctas, *side, n_bad, side_ctas);
+                             (int)col_ctas, *side, n_bad, side_ctas, bad_per_tile);
     return launch_kernel("resize_bilinear_kernel", resize_bilinear_kernel<false>, grid, 32 * kRWarps, 0,
                          stream, pdl, src, (int)Hin, (int)Win, dst, (int)Hout, (int)Wout, (int)rows,
-                         (int)col_ctas, none, (int32_t*)nullptr, 0);
+                         (int)col_ctas, none, (int32_t*)nullptr, 0, 0);
 }
 
 extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
@@ -506,21 +723,104 @@ extern "C" int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, i
     return launch_resize(src, D, Hin, Win, dst, Hout, Wout, (cudaStream_t)stream_, false);
 }
 
-// matching + chained pyramid (utils/loss.py:182-210), PDL-chained on the stream
+// Plan of one pyramid_chain_kernel launch: the number of leading levels it produces (level l+1 is
+// computed from the rows of level l held in shared memory, so the kept slabs of levels 0..k-2 must
+// fit), the CTAs per frame, and the shared-memory layout.
+constexpr size_t kPyrSmemMax = 200 * 1024;
+static bool plan_chain(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t* fr, PyramidArgs* a,
+                       size_t* smem_bytes, int* threads) {
+    const int last_rows = sc->H[sc->n_scales - 1];
+    int slabs = kNumSMs / (fr->n_images > 0 ? fr->n_images : 1);
+    slabs = slabs > 16 ? 16 : slabs;
+    slabs = slabs > last_rows / 4 ? last_rows / 4 : slabs;
+    a->slabs = slabs < 1 ? 1 : slabs;
+    // warps per CTA: about four 2-row x 128-column tasks of the last level each (every warp pays the
+    // per-level set-up, so idle warps are not free)
+    const int64_t tasks = (int64_t)((last_rows / a->slabs + 1) / 2 + 1) * ((sc->W[sc->n_scales - 1] + 127) / 128);
+    int warps = (int)((tasks + 3) / 4 < 4 ? 4 : ((tasks + 3) / 4 > kPyrThreads / 32 ? kPyrThreads / 32 : (tasks + 3) / 4));
+    *threads = warps * 32;
+    for (int l = 0; l < sc->n_scales; ++l) {
+        if (sc->H[l] >= (1 << 26)) return false;             // 32-bit slab arithmetic in the kernel
+        a->H[l] = sc->H[l]; a->W[l] = sc->W[l];
+        a->sy[l] = pyr_step(l ? sc->H[l - 1] : fr->H0, sc->H[l]);
+        a->sx[l] = pyr_step(l ? sc->W[l - 1] : fr->W0, sc->W[l]);
+    }
+    for (int k = sc->n_scales; k >= 1; --k) {
+        a->n_levels = k;
+        size_t buf[2] = {0, 0};
+        for (int g = 0; g < a->slabs; ++g) {
+            RowRange own[DVSOF_MAX_SCALES], need[DVSOF_MAX_SCALES];
+            pyr_plan_rows(*a, g, own, need);
+            for (int l = 0; l + 1 < k; ++l) {
+                const int rows = need[l].hi > need[l].lo ? need[l].hi - need[l].lo : 0;
+                const size_t n = (size_t)rows * sc->W[l];
+                if (n > buf[l & 1]) buf[l & 1] = n;
+            }
+        }
+        if ((buf[0] + 4 + buf[1]) * sizeof(float) <= kPyrSmemMax) {
+            buf[0] = (buf[0] + 3) & ~(size_t)3;                 // 16-byte aligned second buffer
+            a->buf_b_offset = (int)buf[0];
+            *smem_bytes = (buf[0] + buf[1]) * sizeof(float);
+            return true;
+        }
+    }
+    return false;
+}
+
+// matching + chained pyramid (utils/loss.py:182-210), PDL-chained on the stream.  side != nullptr:
+// the last launch of the pyramid also counts the out-of-border pixels into n_bad (per tile).
 static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t* fr,
                                     int32_t* match_idx, uint32_t* status, unsigned* tickets,
                                     int n_tick, cudaStream_t stream,
                                     const ScaleTable* side = nullptr, int32_t* n_bad = nullptr) {
-    if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
-                              fr->sample_idx, fr->n_images, match_idx, status, tickets, n_tick, stream))
-        return rc;
+    size_t smem = 0;
+    int threads = kPyrThreads;
+    PyramidArgs a = {};
+    const bool chain = sc->n_pred <= (1 << 20) && (int64_t)fr->H0 * fr->W0 < (1 << 30) &&
+                       fr->n_images <= (1 << 20) && plan_chain(sc, fr, &a, &smem, &threads);
+    const int k = a.n_levels;
+    int first = 0;
     const float* src = fr->images;
     int Hin = fr->H0, Win = fr->W0;
-    for (int s = 0; s < sc->n_scales; ++s) {                               // loss.py:207-210
+    if (chain) {
+        a.src = fr->images; a.D = fr->n_images; a.H0 = fr->H0; a.W0 = fr->W0;
+        for (int l = 0; l < k; ++l) a.dst[l] = const_cast<float*>(sc->images[l]);
+        a.flow_ts = fr->flow_ts; a.flow_sample_idx = fr->flow_sample_idx; a.P = sc->n_pred;
+        a.timestamps = fr->timestamps; a.sample_idx = fr->sample_idx;
+        a.match_idx = match_idx; a.status = status; a.tickets = tickets; a.n_tickets = n_tick;
+        if (!a.flow_ts || !a.flow_sample_idx || !a.timestamps || !a.sample_idx)
+            return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale loss: null matching input");
+        static unsigned long long attr_done = 0;             // per device; a race only repeats the call
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 64 || !((attr_done >> dev) & 1ull)) {
+            cudaFuncSetAttribute(pyramid_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPyrSmemMax);
+            cudaFuncSetAttribute(pyramid_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPyrSmemMax);
+            if (dev < 64) attr_done |= 1ull << dev;
+        }
+        const bool last = k == sc->n_scales;
+        static const ScaleTable none = {};
+        if (last && side) {
+            const int side_ctas = (side->cta_begin[DVSOF_MAX_SCALES] + threads / 32 - 1) / (threads / 32);
+            if (int rc = launch_kernel("pyramid_chain_kernel<side>", pyramid_chain_kernel<true>,
+                                       fr->n_images * a.slabs + side_ctas, threads, smem, stream, false, a, *side,
+                                       n_bad, side_ctas, 1))
+                return rc;
+        } else if (int rc = launch_kernel("pyramid_chain_kernel", pyramid_chain_kernel<false>, fr->n_images * a.slabs,
+                                          threads, smem, stream, false, a, none, (int32_t*)nullptr, 0, 0)) {
+            return rc;
+        }
+        first = k;
+        if (k > 0) { src = sc->images[k - 1]; Hin = sc->H[k - 1]; Win = sc->W[k - 1]; }
+    } else if (int rc = launch_match(fr->flow_ts, fr->flow_sample_idx, sc->n_pred, fr->timestamps,
+                                     fr->sample_idx, fr->n_images, match_idx, status, tickets, n_tick, stream)) {
+        return rc;
+    }
+    for (int s = first; s < sc->n_scales; ++s) {                           // loss.py:207-210
         float* dst = const_cast<float*>(sc->images[s]);
         const bool last = s + 1 == sc->n_scales;
         if (int rc = launch_resize(src, fr->n_images, Hin, Win, dst, sc->H[s], sc->W[s], stream, true,
-                                   last ? side : nullptr, last ? n_bad : nullptr))
+                                   last ? side : nullptr, last ? n_bad : nullptr, 1))
             return rc;
         src = dst; Hin = sc->H[s]; Win = sc->W[s];
     }
@@ -571,13 +871,13 @@ extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
     set_coef(&tab, coef);
     cudaStream_t stream = (cudaStream_t)stream_;
     const LossWorkspace ws = carve(tab, workspace);
-    cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
+    // the last pyramid launch leaves one out-of-border count per tile; the sweep sums its pair's
+    // counts itself and reports the pair totals in n_bad (no memset, no atomics)
     if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream,
-                                          &tab, n_bad))
+                                          &tab, ws.tile_bad))
         return rc;
-    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, n_bad, ws,
-                                    terms, nullptr, loss, stream, true);
+    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, ws.tile_bad, ws,
+                                    terms, n_bad, loss, stream, true, 1);
 }
 
 // The fused sweep on ready-made pyramid levels (single-scale Loss objects, kernel-level timing):

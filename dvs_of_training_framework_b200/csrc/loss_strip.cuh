@@ -185,7 +185,7 @@ template <bool kVal, bool kGrad>
 __global__ void __launch_bounds__(kSThreads, DVSOF_LOSS_MIN_CTAS)
 warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __restrict__ match_idx,
                        const float* __restrict__ grad_terms, const int32_t* __restrict__ n_bad_in,
-                       const LossWorkspace ws, float* terms, int32_t* __restrict__ n_bad_out,
+                       int bad_per_tile, const LossWorkspace ws, float* terms, int32_t* __restrict__ n_bad_out,
                        float* __restrict__ loss_out) {
     __shared__ __align__(16) float2 F[kFH][kFP];
     __shared__ float red[kSWarps][kRec];
@@ -218,7 +218,16 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
         kv = g_sm * tab.norm[1][tc.s];
         kd = g_sm * tab.norm[2][tc.s];
         k_ph = g_ph * tab.norm[3][tc.s];
-        const int nb = n_bad_in[tc.s * P + tc.n];
+        int nb;
+        if (bad_per_tile) {                       // per-tile counts of this (scale, prediction): sum them
+            const int per = tab.tiles_x[tc.s] * tab.tiles_y[tc.s];
+            const int32_t* tb = n_bad_in + tab.cta_begin[tc.s] + tc.n * per;
+            nb = 0;
+            for (int t = lane; t < per; t += 32) nb += __ldcg(tb + t);
+            nb = __reduce_add_sync(0xffffffffu, nb);
+        } else {
+            nb = n_bad_in[tc.s * P + tc.n];
+        }
         k_ob = nb > 0 ? __fdividef(g_ob * tab.norm[4][tc.s], (float)nb) : 0.f;   // loss.py:99-113
     }
     const float khx = x_r ? kh : 0.f, kvx = x_in ? kv : 0.f, kdx = x_r ? kd : 0.f;
@@ -360,11 +369,61 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
 
 // Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
 // pass, which needs it for the gradient of the border term: same coordinates, same comparison.
-// One 32x32 tile per CTA of NW warps (tile index `cta`); n_bad must be zero beforehand.
-template <int NW>
+// One 32x32 tile per CTA of NW warps (tile index `cta`).  per_tile: the tile's count is stored at
+// n_bad[cta] (no atomics, nothing to zero; the fused kernel sums a pair's tiles itself); otherwise
+// it is added to n_bad[s * P + n], which must be zero beforehand.
+template <int NW, int NT = 1>
 __device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int32_t* __restrict__ n_bad,
-                                                     int cta, int* cnt /* shared, NW ints */) {
+                                                     bool per_tile, int first_tile,
+                                                     int* cnt /* shared, NW * NT ints */) {
     constexpr int kRows = kTile / NW;
+    const int lane = threadIdx.x & 31, warp_all = threadIdx.x >> 5;
+    const int group = NT > 1 ? warp_all / NW : 0, warp = warp_all - group * NW;
+    const int cta = first_tile + group;
+    const bool active = NT == 1 || cta < tab.cta_begin[DVSOF_MAX_SCALES];
+    const TileCoord tc = decode_cta_fast(tab, active ? cta : 0);
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const int plane = H * W;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    const float* flow1 = flow + plane;
+    asm volatile("" : "+l"(flow), "+l"(flow1));
+    const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
+    const int x = tc.x0 + lane, ys = tc.y0 + warp * kRows;
+    const float xf = (float)x;
+    int n = 0;
+    float u[kRows], v[kRows];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const bool ok = active && x < W && ys + r < H;
+        const int off = (ys + r) * W + x;
+        u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
+        v[r] = ok ? __ldg(flow1 + off) : 0.f;
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const bool ok = active && x < W && ys + r < H;
+        const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
+        n += (ok && out_of_border(gx, gy)) ? 1 : 0;
+    }
+    n = warp_sum(n);
+    if (lane == 0) cnt[warp_all] = n;
+    __syncthreads();
+    if (warp == 0 && lane == 0 && active) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t += cnt[group * NW + w];
+        if (per_tile) n_bad[cta] = t;
+        else if (t) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, t);
+    }
+}
+
+// The same count with a whole 32x32 tile per WARP (8 rows in flight at a time): the tile decode
+// and pointer set-up are paid once per 32 rows and no cross-warp reduction is needed.  Used by the
+// 1024-thread pyramid kernel, where a CTA takes 32 tiles.
+__device__ __forceinline__ void outborder_count_warp_tile(const ScaleTable& tab, int32_t* __restrict__ n_bad,
+                                                          bool per_tile, int cta) {
+    constexpr int kRows = 8;
+    if (cta >= tab.cta_begin[DVSOF_MAX_SCALES]) return;          // warp-uniform
     const TileCoord tc = decode_cta_fast(tab, cta);
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const int plane = H * W;
@@ -372,32 +431,32 @@ __device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int3
     const float* flow1 = flow + plane;
     asm volatile("" : "+l"(flow), "+l"(flow1));
     const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = tc.x0 + lane, ys = tc.y0 + warp * kRows;
+    const int lane = threadIdx.x & 31;
+    const int x = tc.x0 + lane;
     const float xf = (float)x;
     int n = 0;
-    float u[kRows], v[kRows];
+    if (x < W) {
+#pragma unroll 1
+        for (int ys = tc.y0; ys < min(tc.y0 + kTile, H); ys += kRows) {
+            float u[kRows], v[kRows];
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-        const bool ok = x < W && ys + r < H;
-        const int off = (ys + r) * W + x;
-        u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
-        v[r] = ok ? __ldg(flow1 + off) : 0.f;
-    }
+            for (int r = 0; r < kRows; ++r) {
+                const bool ok = ys + r < H;
+                const int off = (ys + r) * W + x;
+                u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
+                v[r] = ok ? __ldg(flow1 + off) : 0.f;
+            }
 #pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-        const bool ok = x < W && ys + r < H;
-        const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
-        n += (ok && out_of_border(gx, gy)) ? 1 : 0;
+            for (int r = 0; r < kRows; ++r) {
+                const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
+                n += (ys + r < H && out_of_border(gx, gy)) ? 1 : 0;
+            }
+        }
     }
     n = warp_sum(n);
-    if (lane == 0) cnt[warp] = n;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int t = 0;
-#pragma unroll
-        for (int w = 0; w < NW; ++w) t += cnt[w];
-        if (t) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, t);
+    if (lane == 0) {
+        if (per_tile) n_bad[cta] = n;
+        else if (n) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, n);
     }
 }
 
@@ -406,7 +465,7 @@ __device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int3
 __global__ void __launch_bounds__(kSThreads)
 outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad) {
     __shared__ int cnt[kSWarps];
-    outborder_count_tile<kSWarps>(tab, n_bad, blockIdx.x, cnt);
+    outborder_count_tile<kSWarps>(tab, n_bad, false, blockIdx.x, cnt);
 }
 
 }  // namespace dvsof

@@ -1,6 +1,7 @@
 """Experiment harness (GPU box): time the fused warp-loss step and its forward / backward
 kernels on the named configs (default cfg2 cfg3 cfg4); used under ncu for the loss profiles."""
 import json
+import os
 import sys
 from pathlib import Path
 
@@ -17,7 +18,7 @@ def main():
     peak, _ = bench.peaks()
     res = {}
     for name in sys.argv[1:] or ['cfg2', 'cfg3', 'cfg4']:
-        r = bench.bench_loss(name, 5, 3, dev)
+        r = bench.bench_loss(name, int(os.environ.get('DVSOF_EXP_STEPS', 20)), 3, dev)
         res[name] = {'step_ms': round(r['step_ms'], 4), 'fwd_ms': round(r['fwd_ms'], 4),
                      'bwd_ms': round(r['bwd_ms'], 4),
                      'fwd_GBs': round(r['fwd_bytes'] / r['fwd_ms'] / 1e6, 1),
