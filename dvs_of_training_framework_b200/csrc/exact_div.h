@@ -67,6 +67,20 @@ DVSOF_HD float dvsof_div_by_const_grid(float a, float h, float r) {
     return fabsf(a) < DVSOF_EXACT_DIV_MAX ? q : q0;
 }
 
+// Out-of-border test of the grid coordinate g = RN(RN(a / h) - 1) without computing it:
+//   g >  1  <=>  RN(a / h) > 2       (floats above 1 that round back to 1 under "- 1" do not exist
+//                                     for a float q: q > 2 means q >= 2 + 2^-22, so q - 1 > 1)
+//           <=>  a > 2h              (2h is a float; the next float above it divides to more than
+//                                     the rounding midpoint 2 + 2^-23, 2h itself gives exactly 2)
+//   g < -1  <=>  RN(a / h) < -2^-24  (quotients in [-2^-24, 0) are absorbed by the "- 1")
+//           <=>  a < -h * 2^-24      (same argument one binade down; h * 2^-24 is exact)
+// A NaN or missing reciprocal (1-pixel side: the reference divides by zero) never tests outside,
+// like the comparisons on a NaN grid.  Enumerated against the division in
+// tests/csrc/exact_div_check.c.
+DVSOF_HD float dvsof_grid_outside_hi(float h, float r) { return r == r ? 2.f * h : INFINITY; }
+DVSOF_HD float dvsof_grid_outside_lo(float h, float r) { return r == r ? -h * 0x1p-24f : -INFINITY; }
+DVSOF_HD int dvsof_grid_outside(float a, float hi, float lo) { return a > hi || a < lo; }
+
 // host: correctly rounded fp32 reciprocal of h (h > 0, normal), and whether the fast path may be
 // used for this divisor (significand not all ones, sane exponent)
 static inline float dvsof_recip_rn(float h) {

@@ -452,55 +452,62 @@ __device__ __forceinline__ void pyr_level_rows(const float* in, int Hin, int Win
             lx[j] = fminf(fmaxf(fx - (float)t, 0.f), 1.f);
             hx[j] = 1.f - lx[j];
         }
-        int cy0 = -1, cy1 = -1;                               // source rows whose interpolations h0 / h1 hold
-        float h0[4] = {0.f, 0.f, 0.f, 0.f}, h1[4] = {0.f, 0.f, 0.f, 0.f};
         const int yend = min(ybeg + rpt, nd.hi);
+        // walk the SOURCE row pairs: all output rows between the same two source rows are emitted
+        // from one pair of horizontal interpolations, and the lower one becomes the next upper one
+        int y = ybeg, have = -1;
+        int off = y * Wout + xq;                              // element offset of (y, xq) in the level
+        float* keep_rel = keep ? keep - nd.lo * Wout : nullptr;   // keep_rel + off = the kept copy
+        const unsigned own_rows = (unsigned)(ow.hi > ow.lo ? ow.hi - ow.lo : 0);
+        float fy = sy * (float)y;
+        int y0 = (int)fy;
+        y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+        float top[4], bot[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1                                      // compact code: the kernel starts with a cold i-cache
-        for (int y = ybeg; y < yend; ++y) {
-            const float fy = sy * (float)y;
-            int y0 = (int)fy;
-            y0 = y0 < Hin - 1 ? y0 : Hin - 1;
+        while (y < yend) {                                    // warp-uniform control flow throughout
             const int y1 = y0 + (y0 < Hin - 1);
-            const float ly = fminf(fmaxf(fy - (float)y0, 0.f), 1.f), hy = 1.f - ly;
-            float top[4], bot[4];
-            if (y0 == cy0) {                                  // all of these are warp-uniform
+            if (y0 == have) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) top[j] = h0[j];
-            } else if (y0 == cy1) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) top[j] = h1[j];
+                for (int j = 0; j < 4; ++j) top[j] = bot[j];
             } else {
                 pyr_hlerp(in + (y0 - in_row0) * Win, ox0, ox1, lx, hx, top);
             }
             if (y1 == y0) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) bot[j] = top[j];
-            } else if (y1 == cy1) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) bot[j] = h1[j];
             } else {
                 pyr_hlerp(in + (y1 - in_row0) * Win, ox0, ox1, lx, hx, bot);
             }
-            cy0 = y0; cy1 = y1;
-            float o[4];
+            have = y1;
+            const float y0f = (float)y0;
+            int yn;
+#pragma unroll 1
+            do {
+                const float ly = fminf(fmaxf(fy - y0f, 0.f), 1.f), hy = 1.f - ly;
+                float o[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                o[j] = __fmaf_rn(hy, top[j], __fmul_rn(ly, bot[j]));           // ATen's operation order
-                h0[j] = top[j]; h1[j] = bot[j];
-            }
-            const bool mine = y >= ow.lo && y < ow.hi;
-            if (vec) {
-                const float4 v = make_float4(o[0], o[1], o[2], o[3]);
-                if (mine) *reinterpret_cast<float4*>(out + y * Wout + xq) = v;
-                if (keep) *reinterpret_cast<float4*>(keep + (y - nd.lo) * Wout + xq) = v;
-            } else {
+                for (int j = 0; j < 4; ++j)
+                    o[j] = __fmaf_rn(hy, top[j], __fmul_rn(ly, bot[j]));       // ATen's operation order
+                const bool mine = (unsigned)(y - ow.lo) < own_rows;
+                if (vec) {
+                    const float4 v = make_float4(o[0], o[1], o[2], o[3]);
+                    if (mine) *reinterpret_cast<float4*>(out + off) = v;
+                    if (keep) *reinterpret_cast<float4*>(keep_rel + off) = v;
+                } else {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (xq + j >= Wout) break;
-                    if (mine) out[y * Wout + xq + j] = o[j];
-                    if (keep) keep[(y - nd.lo) * Wout + xq + j] = o[j];
+                    for (int j = 0; j < 4; ++j) {
+                        if (xq + j >= Wout) break;
+                        if (mine) out[off + j] = o[j];
+                        if (keep) keep_rel[off + j] = o[j];
+                    }
                 }
-            }
+                ++y;
+                off += Wout;
+                fy = sy * (float)y;
+                yn = (int)fy;
+                yn = yn < Hin - 1 ? yn : Hin - 1;
+            } while (y < yend && yn == y0);
+            y0 = yn;
         }
     }
 }

@@ -91,6 +91,16 @@ __device__ __forceinline__ float grid_coord(float pix, float disp, float h, floa
 __device__ __forceinline__ bool out_of_border(float gx, float gy) {               // loss.py:92-94
     return gx < -1.f || gx > 1.f || gy < -1.f || gy > 1.f;
 }
+// The counting jobs only need the predicate, not the coordinates: pixel + flow against two
+// thresholds per axis decides it without the division (exact_div.h: dvsof_grid_outside).
+struct BorderTest { float hi_x, lo_x, hi_y, lo_y; };
+__device__ __forceinline__ BorderTest border_test(const ScaleTable& tab, int s) {
+    return BorderTest{dvsof_grid_outside_hi(tab.hx[s], tab.rx[s]), dvsof_grid_outside_lo(tab.hx[s], tab.rx[s]),
+                      dvsof_grid_outside_hi(tab.hy[s], tab.ry[s]), dvsof_grid_outside_lo(tab.hy[s], tab.ry[s])};
+}
+__device__ __forceinline__ bool outside_grid(float ax, float ay, const BorderTest& bt) {
+    return dvsof_grid_outside(ax, bt.hi_x, bt.lo_x) || dvsof_grid_outside(ay, bt.hi_y, bt.lo_y);
+}
 
 // (scale, prediction, tile) of this CTA without integer division: at most 2^23 tiles (checked on
 // the host), so a float product with the host's reciprocal and one correction step is exact.
@@ -387,7 +397,7 @@ __device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int3
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     const float* flow1 = flow + plane;
     asm volatile("" : "+l"(flow), "+l"(flow1));
-    const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
+    const BorderTest bt = border_test(tab, tc.s);
     const int x = tc.x0 + lane, ys = tc.y0 + warp * kRows;
     const float xf = (float)x;
     int n = 0;
@@ -402,8 +412,7 @@ __device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int3
 #pragma unroll
     for (int r = 0; r < kRows; ++r) {
         const bool ok = active && x < W && ys + r < H;
-        const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
-        n += (ok && out_of_border(gx, gy)) ? 1 : 0;
+        n += (ok && outside_grid(__fadd_rn(xf, u[r]), __fadd_rn((float)(ys + r), v[r]), bt)) ? 1 : 0;
     }
     n = warp_sum(n);
     if (lane == 0) cnt[warp_all] = n;
@@ -430,7 +439,7 @@ __device__ __forceinline__ void outborder_count_warp_tile(const ScaleTable& tab,
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     const float* flow1 = flow + plane;
     asm volatile("" : "+l"(flow), "+l"(flow1));
-    const GridNorm gn{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
+    const BorderTest bt = border_test(tab, tc.s);
     const int lane = threadIdx.x & 31;
     const int x = tc.x0 + lane;
     const float xf = (float)x;
@@ -448,8 +457,7 @@ __device__ __forceinline__ void outborder_count_warp_tile(const ScaleTable& tab,
             }
 #pragma unroll
             for (int r = 0; r < kRows; ++r) {
-                const float gx = grid_coord(xf, u[r], gn.hx, gn.rx), gy = grid_coord((float)(ys + r), v[r], gn.hy, gn.ry);
-                n += (ys + r < H && out_of_border(gx, gy)) ? 1 : 0;
+                n += (ys + r < H && outside_grid(__fadd_rn(xf, u[r]), __fadd_rn((float)(ys + r), v[r]), bt)) ? 1 : 0;
             }
         }
     }

@@ -4,6 +4,7 @@
  * numerators: pixel + flow, dense around the integers and half-integers where the bilinear cell
  * changes, plus random magnitudes.  Prints the number of mismatches (expected 0).
  * Build: gcc -O2 -ffp-contract=off -o exact_div_check exact_div_check.c -lm */
+#include <math.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -51,6 +52,50 @@ int main(int argc, char** argv) {
             }
         }
     }
-    printf("checked=%ld mismatches=%ld skipped_divisors=%ld\n", total, bad, skipped);
+    /* the division-free out-of-border test against g = a / h - 1 compared with +-1: every float
+     * within 256 ulps of both thresholds and of 0, plus random numerators */
+    long border = 0;
+    for (int S = 2; S <= 4096; ++S) {
+        const float h = (float)(S - 1) / 2.f;
+        if (!dvsof_div_const_ok(h)) continue;
+        const float r = dvsof_recip_rn(h);
+        const float hi = dvsof_grid_outside_hi(h, r), lo = dvsof_grid_outside_lo(h, r);
+        const float centres[4] = {hi, lo, 0.f, -0.f};
+        for (int c = 0; c < 4; ++c) {
+            float up = centres[c], dn = centres[c];
+            for (int k = 0; k <= 256; ++k) {
+                const float cand[2] = {up, dn};
+                for (int m = 0; m < 2; ++m) {
+                    const float a = cand[m], g = dvsof_div_by_const_grid(a, h, r) - 1.f, g2 = a / h - 1.f;
+                    const int want = g < -1.f || g > 1.f, want2 = g2 < -1.f || g2 > 1.f;
+                    const int got = dvsof_grid_outside(a, hi, lo);
+                    ++border;
+                    if (want != got || want2 != got) {
+                        if (bad < 5) printf("border mismatch S=%d a=%a want=%d/%d got=%d\n", S, a, want, want2, got);
+                        ++bad;
+                    }
+                }
+                up = nextafterf(up, INFINITY);
+                dn = nextafterf(dn, -INFINITY);
+            }
+        }
+        for (long i = 0; i < per / 4; ++i) {
+            float a;
+            switch (rnd() & 3) {
+                case 0: a = bits(rnd()); break;                                        /* any bit pattern */
+                case 1: a = ((float)rnd() / 4294967296.f - 0.25f) * 4.f * (float)S; break;
+                case 2: a = bits((rnd() & 0x807fffffu) | ((uint32_t)(90 + rnd() % 20) << 23)); break;   /* around -h 2^-24 */
+                default: a = 2.f * h + ((float)(rnd() & 0xffff) - 32768.f) * 0x1p-18f * h; break;
+            }
+            const float g = dvsof_div_by_const_grid(a, h, r) - 1.f;
+            const int want = g < -1.f || g > 1.f, got = dvsof_grid_outside(a, hi, lo);
+            ++border;
+            if (want != got) {
+                if (bad < 5) printf("border mismatch S=%d a=%a want=%d got=%d\n", S, a, want, got);
+                ++bad;
+            }
+        }
+    }
+    printf("checked=%ld border_checked=%ld mismatches=%ld skipped_divisors=%ld\n", total, border, bad, skipped);
     return bad != 0;
 }
