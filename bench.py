@@ -595,7 +595,7 @@ def main():
                       'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
                       'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
                                    'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
-                                   'note': 'whole training pass through the C ABI, device-resident inputs: dvsof_multiscale_loss_fused (memset + match + 4 resize + border count + fused terms-and-gradient sweep, PDL-chained) + dvsof_scale_gradients; bytes = SURVEY 8d figure (separate fwd + bwd + pyramid)'},
+                                   'note': 'whole training pass through the C ABI, device-resident inputs: dvsof_multiscale_loss_fused (one prelude launch: timestamp match + chained pyramid + border count; then the fused terms-and-gradient sweep, PDL-chained) + dvsof_scale_gradients; bytes = SURVEY 8d figure (separate fwd + bwd + pyramid)'},
                       'python_api': {'value': world * loss['samples'] / (loss_py_ms * 1e-3), 'unit': 'samples/s',
                                      'ms_per_step': loss_py_ms,
                                      'note': 'training.combined_loss(...) + loss.backward() through torch.autograd (same kernels; host-bound: Python + autograd engine per step)'},

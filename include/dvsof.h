@@ -215,9 +215,10 @@ int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* scales,
  *   loss       = sum_k sum_s coef[k*n_scales + s] * term[k][s]      (coef [host] = w_k / n_scales)
  *   grad_flow  = d(loss) / d(flow[s])                               (scales->grad_flow, all written)
  * i.e. autograd's backward of utils/loss.py:121-171 for that fixed linear combination, without a
- * second pass over flow and frames: 16 B/pixel read, 8 B/pixel written.  n_bad [dev int32
- * n_scales*P] is filled by a counting pre-pass (the border term's gradient needs n_i).
- * loss [dev] 1 float.  Deterministic. */
+ * second pass over flow and frames: 16 B/pixel read, 8 B/pixel written.  Two launches: the
+ * prelude (timestamp matching, all pyramid levels, and a count of the out-of-border pixels of
+ * every tile, which the border term's gradient needs as n_i) and the sweep.  n_bad [dev int32
+ * n_scales*P] receives the per-(scale, prediction) counts.  loss [dev] 1 float.  Deterministic. */
 int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* scales,
                                 const dvsof_loss_frames_t* frames, const float* coef,
                                 int32_t* match_idx, float* terms, float* loss, int32_t* n_bad,
