@@ -149,6 +149,43 @@ def time_steps(fn, K, W, flush, inner=None):
     return [a.elapsed_time(b) for a, b in evs]
 
 
+def bench_codec(name, K, W, dev):
+    """Batch codec through the C ABI on the events of `name`: dvsof_decode_events (storage form ->
+    int64 training form, 5 B read + 40 B written per event) and dvsof_encode_events (40 B read +
+    5 B written), L2 flushed between steps."""
+    import dvs_of_training_framework_b200 as dv
+    L = dv._lib
+    c = CFG[name]
+    B, n = c['B'], c['n']
+    N = B * n
+    g = torch.Generator(device=dev).manual_seed(77)
+    x = torch.randint(0, c['W'], (N,), generator=g, device=dev, dtype=torch.int16)
+    y = torch.randint(0, c['H'], (N,), generator=g, device=dev, dtype=torch.int16)
+    p = (torch.rand(N, generator=g, device=dev) < 0.7).view(torch.uint8)
+    eps = torch.full((B,), 2, dtype=torch.int64, device=dev)              # two elements per sample
+    epe = torch.full((2 * B,), n // 2, dtype=torch.int64, device=dev)
+    epe[1::2] = n - n // 2
+    out = [torch.empty(N, dtype=torch.int64, device=dev) for _ in range(5)]
+    ws = torch.empty(L.load().dvsof_codec_workspace_bytes(2 * B, B), dtype=torch.uint8, device=dev)
+    st = torch.zeros(1, dtype=torch.int32, device=dev)
+    sp = L.stream_ptr(dev)
+    x2, y2, p2 = torch.empty_like(x), torch.empty_like(y), torch.empty_like(p)
+    epe2 = torch.empty_like(epe)
+
+    def dec():
+        L.call('dvsof_decode_events', L.ptr(x), L.ptr(y), L.ptr(p), N, L.ptr(epe), 2 * B, L.ptr(eps), B,
+               *[L.ptr(o) for o in out], L.ptr(ws), L.ptr(st), sp)
+
+    def enc():
+        L.call('dvsof_encode_events', *[L.ptr(o) for o in out], N, L.ptr(eps), B, 2 * B, L.ptr(x2), L.ptr(y2),
+               L.ptr(p2), L.ptr(epe2), L.ptr(ws), L.ptr(st), sp)
+    flush = L2Flusher(dev)
+    dec_ms = float(np.mean(time_steps(dec, K, W, flush)))
+    enc_ms = float(np.mean(time_steps(enc, K, W, flush)))
+    assert int(st.item()) == 0 and torch.equal(x, x2) and torch.equal(p, p2) and torch.equal(epe, epe2)
+    return {'events': N, 'decode_ms': dec_ms, 'encode_ms': enc_ms, 'bytes': 45 * N}
+
+
 def bench_encoder(name, K, W, dev, seed_off=0):
     import dvs_of_training_framework_b200 as dv
     L = dv._lib
@@ -561,6 +598,8 @@ def main():
             ll['step_ms'] = max_over_ranks(ll['step_ms'])
             extra[name + '_loss'] = ll
             torch.cuda.empty_cache()
+    codec = bench_codec(HEADLINE, max(3, min(K, 10)), 3, dev) if (rank == 0 and not args.quick) else None
+    torch.cuda.empty_cache()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -620,6 +659,13 @@ def main():
                                        'ms_per_step': r['step_ms'], 'kernel_ms': r['kernel_ms'],
                                        'hbm_gbs_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9,
                                        'hbm_frac_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9 / peak}
+    if codec is not None:
+        line['workloads']['codec_' + HEADLINE] = {
+            'decode_mevents_per_s': codec['events'] / (codec['decode_ms'] * 1e-3) / 1e6, 'decode_ms': codec['decode_ms'],
+            'decode_hbm_frac': codec['bytes'] / (codec['decode_ms'] * 1e-3) / 1e9 / peak,
+            'encode_mevents_per_s': codec['events'] / (codec['encode_ms'] * 1e-3) / 1e6, 'encode_ms': codec['encode_ms'],
+            'encode_hbm_frac': codec['bytes'] / (codec['encode_ms'] * 1e-3) / 1e9 / peak,
+            'note': 'dvsof_decode_events / dvsof_encode_events (utils/dataset.py decode_batch / encode_batch, event part), 45 B/event, one GPU (rank 0)'}
     line['cpu_baseline'] = cpu_baseline(HEADLINE) if world == 1 and not args.quick else None
     emit(line)
     if world > 1:

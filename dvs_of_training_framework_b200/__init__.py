@@ -7,6 +7,7 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
          frame_generator                                    <- utils/data.py
     transformation.map                                      <- utils/transformation (native ext)
     eval.flow_error_dense                                   <- utils/eval.py:6-50
+    dataset.encode_batch / decode_batch (+ _info)          <- utils/dataset.py:201-373
 
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
 CPU fallback."""
@@ -17,8 +18,10 @@ from .data import (EventCrop, RandomRotation, augment_events, frame_generator, f
                    get_count_image, rotation_lut)
 from . import transformation  # noqa: F401
 from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
+from .dataset import decode_batch, decode_batch_info, decode_events, encode_batch, encode_batch_info  # noqa: F401
 
 __all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
            'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets', 'augment_events', 'rotation_lut',
-           'transformation', 'flow_error_dense', 'flow_error_dense_device']
+           'transformation', 'flow_error_dense', 'flow_error_dense_device',
+           'encode_batch', 'decode_batch', 'encode_batch_info', 'decode_batch_info', 'decode_events']

@@ -12,14 +12,15 @@ _LIB_PATH = Path(os.environ['DVSOF_LIB']).resolve() if os.environ.get('DVSOF_LIB
 _lib = None
 
 MAX_SCALES = 8
-ST_BAD_POLARITY, ST_NOT_GROUPED, ST_BAD_SAMPLE, ST_BAD_PIXEL, ST_NO_MATCH, ST_BAD_LUT = \
-    0x1, 0x2, 0x4, 0x8, 0x10, 0x20
+ST_BAD_POLARITY, ST_NOT_GROUPED, ST_BAD_SAMPLE, ST_BAD_PIXEL, ST_NO_MATCH, ST_BAD_LUT, ST_BAD_COUNTS = \
+    0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
 _ST_TEXT = {ST_BAD_POLARITY: 'polarity must be +1/-1 (EV_FlowNet/net.py:124)',
             ST_NOT_GROUPED: 'events must be grouped by ascending sample_index (net.py:131-134)',
             ST_BAD_SAMPLE: 'sample_index outside [0, batch)',
             ST_BAD_PIXEL: 'event coordinate outside the image',
             ST_NO_MATCH: 'each prediction needs exactly one image per timestamp (utils/loss.py:193)',
-            ST_BAD_LUT: 'map: src/dst index outside the image'}
+            ST_BAD_LUT: 'map: src/dst index outside the image',
+            ST_BAD_COUNTS: 'batch codec: run lengths do not cover the events, or an element index outside the batch'}
 
 
 class LossScales(C.Structure):
@@ -67,6 +68,13 @@ _SIGNATURES = {
     'dvsof_augment_events_write': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                              C.c_int32, C.c_void_p, C.POINTER(C.c_double), C.c_void_p,
                                              C.c_void_p, C.c_void_p]),
+    'dvsof_codec_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64]),
+    'dvsof_decode_events': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                      C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'dvsof_encode_events': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_window_offsets': (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64,
                                        C.c_void_p, C.c_void_p]),
     'dvsof_flow_error_workspace_bytes': (C.c_size_t, []),

@@ -465,3 +465,294 @@ extern "C" int dvsof_window_offsets(const void* t, int32_t elem_size, int64_t n_
     return launch_kernel("window_offsets_kernel", window_offsets_kernel<double>, blocks, threads, 0, stream,
                          false, static_cast<const double*>(t), n_events, bounds, n_bounds, out);
 }
+
+// ---------------------------------------------------------------------------------------
+// Batch codec on device: the event part of utils/dataset.py:240-305
+// `encode_batch` (training form -> 9 B/event storage form + run lengths) and :335-373
+// `decode_batch` (storage form -> int64 training form: widening plus the run-length expansion of
+// events_per_element / elements_per_sample into element_index / sample_index).
+// Both are one streaming pass: decode reads 5 B and writes 40 B per event, encode reads 40 B and
+// writes 5 B; the timestamps are shared between the two forms and never copied.
+// ---------------------------------------------------------------------------------------
+namespace dvsof {
+
+constexpr int kCodecPer = 4;                              // consecutive events per thread
+constexpr int kCodecChunk = kCompactThreads * kCodecPer;
+
+// workspace: elem_begin[E+1] | sample_shift[B+1] (int64) | elem_sample[E] | elem_local[E] (int32)
+struct CodecView {
+    int64_t* elem_begin; int64_t* sample_shift; int32_t* elem_sample; int32_t* elem_local;
+};
+__host__ __device__ inline CodecView codec_view(void* ws, int64_t E, int64_t B) {
+    CodecView v;
+    char* p = reinterpret_cast<char*>(ws);
+    auto take = [&](size_t bytes) { char* q = p; p += (bytes + 255) / 256 * 256; return q; };
+    v.elem_begin = reinterpret_cast<int64_t*>(take((E + 1) * 8));
+    v.sample_shift = reinterpret_cast<int64_t*>(take((B + 1) * 8));
+    v.elem_sample = reinterpret_cast<int32_t*>(take((E > 0 ? E : 1) * 4));
+    v.elem_local = reinterpret_cast<int32_t*>(take((E > 0 ? E : 1) * 4));
+    return v;
+}
+
+// exclusive prefix of src[0..n) into dst[0..n], dst[n] = total; one CTA
+__device__ void cta_prefix(const int64_t* __restrict__ src, int64_t n, int64_t* __restrict__ dst) {
+    int64_t carry = 0;
+    for (int64_t base = 0; base < n; base += kCompactThreads) {
+        const int64_t i = base + threadIdx.x;
+        const int64_t v = (i < n) ? src[i] : 0;
+        int64_t total;
+        const int64_t ex = block_exclusive_scan(v, &total);
+        if (i < n) dst[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) dst[n] = carry;
+}
+
+// last index k in [0, n] with a[k] <= v (a ascending, a[0] = 0 <= v)
+__device__ __forceinline__ int64_t upper_slot(const int64_t* __restrict__ a, int64_t n, int64_t v) {
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi + 1) >> 1;
+        if (a[mid] <= v) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// Plan of a decode: which sample an element belongs to and its index inside the sample
+// (utils/dataset.py:357-368: events_per_element is sliced by the prefix of elements_per_sample;
+// elements past the end of a truncated events_per_element simply do not exist).
+__global__ void __launch_bounds__(kCompactThreads)
+codec_plan_kernel(const int64_t* __restrict__ events_per_element, int64_t E,
+                  const int64_t* __restrict__ elements_per_sample, int64_t B, int64_t n_events,
+                  CodecView v, uint32_t* status) {
+    pdl_launch_dependents();                       // the per-event kernel may start its prologue
+    cta_prefix(elements_per_sample, B, v.sample_shift);
+    if (events_per_element) cta_prefix(events_per_element, E, v.elem_begin);
+    __syncthreads();
+    if (events_per_element) {
+        for (int64_t j = threadIdx.x; j < E; j += kCompactThreads) {
+            const int64_t s = upper_slot(v.sample_shift, B, j);      // empty samples are skipped
+            v.elem_sample[j] = (int32_t)(s < B ? s : B - 1);
+            v.elem_local[j] = (int32_t)(j - v.sample_shift[s < B ? s : B - 1]);
+            if (events_per_element[j] < 0) atomicOr(status, DVSOF_ST_BAD_COUNTS);
+        }
+        if (threadIdx.x == 0 && (v.elem_begin[E] != n_events || v.sample_shift[B] < E))
+            atomicOr(status, DVSOF_ST_BAD_COUNTS);
+    }
+}
+
+template <bool kVec>
+__global__ void __launch_bounds__(kCompactThreads)
+decode_events_kernel(const int16_t* __restrict__ x, const int16_t* __restrict__ y,
+                     const uint8_t* __restrict__ pol, int64_t n, CodecView v, int64_t E,
+                     int64_t* __restrict__ ox, int64_t* __restrict__ oy, int64_t* __restrict__ op,
+                     int64_t* __restrict__ oe, int64_t* __restrict__ os) {
+    const int64_t i0 = (int64_t)blockIdx.x * kCodecChunk + (int64_t)threadIdx.x * kCodecPer;
+    if (i0 >= n) return;
+    const int cnt = (int)(n - i0 < kCodecPer ? n - i0 : kCodecPer);
+    int64_t xs[kCodecPer], ys[kCodecPer], ps[kCodecPer], es[kCodecPer], ss[kCodecPer];
+    // the event arrays are inputs of the call; only the plan (read below) comes from codec_plan_kernel
+    if (kVec && cnt == kCodecPer) {
+        const short4 xv = *reinterpret_cast<const short4*>(x + i0), yv = *reinterpret_cast<const short4*>(y + i0);
+        const uchar4 pv = *reinterpret_cast<const uchar4*>(pol + i0);
+        xs[0] = xv.x; xs[1] = xv.y; xs[2] = xv.z; xs[3] = xv.w;
+        ys[0] = yv.x; ys[1] = yv.y; ys[2] = yv.z; ys[3] = yv.w;
+        ps[0] = pv.x; ps[1] = pv.y; ps[2] = pv.z; ps[3] = pv.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < kCodecPer; ++k) {
+            xs[k] = k < cnt ? x[i0 + k] : 0; ys[k] = k < cnt ? y[i0 + k] : 0; ps[k] = k < cnt ? pol[i0 + k] : 0;
+        }
+    }
+    pdl_wait();
+    // element of the first event by search, of the following ones by walking (empty elements skipped)
+    int64_t e = E > 0 ? upper_slot(v.elem_begin, E, i0) : 0;
+    if (e >= E) e = E > 0 ? E - 1 : 0;                       // counts do not cover the events: flagged by the plan
+    int64_t next = E > 0 ? v.elem_begin[e + 1] : n;
+#pragma unroll
+    for (int k = 0; k < kCodecPer; ++k) {
+        while (i0 + k >= next && e + 1 < E) { ++e; next = v.elem_begin[e + 1]; }
+        es[k] = E > 0 ? v.elem_local[e] : 0;
+        ss[k] = E > 0 ? v.elem_sample[e] : 0;
+        ps[k] = (ps[k] != 0 ? 1 : 0) * 2 - 1;               // dataset.py:351: bool -> long * 2 - 1
+    }
+    if (kVec && cnt == kCodecPer) {
+        int64_t* const outs[5] = {ox, oy, op, oe, os};
+        const int64_t* const vals[5] = {xs, ys, ps, es, ss};
+#pragma unroll
+        for (int a = 0; a < 5; ++a) {
+            longlong2* d = reinterpret_cast<longlong2*>(outs[a] + i0);
+            __stcs(d, make_longlong2(vals[a][0], vals[a][1]));
+            __stcs(d + 1, make_longlong2(vals[a][2], vals[a][3]));
+        }
+    } else {
+        for (int k = 0; k < cnt; ++k) {
+            ox[i0 + k] = xs[k]; oy[i0 + k] = ys[k]; op[i0 + k] = ps[k]; oe[i0 + k] = es[k]; os[i0 + k] = ss[k];
+        }
+    }
+}
+
+// encode: narrowing casts exactly as torch's (`.to(torch.short)` wraps, dataset.py:286-291) and the
+// histogram of dataset.py:293-302 (`np.add.at(events_per_element, e + element_shift[s], 1)`).
+// Events arrive grouped by (sample, element), so a warp usually holds one or two distinct
+// elements: one atomic per distinct element per warp.
+template <bool kVec>
+__global__ void __launch_bounds__(kCompactThreads)
+encode_events_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
+                     const int64_t* __restrict__ pol, const int64_t* __restrict__ elem,
+                     const int64_t* __restrict__ smp, int64_t n, CodecView v, int64_t B, int64_t E,
+                     int16_t* __restrict__ ox, int16_t* __restrict__ oy, uint8_t* __restrict__ op,
+                     unsigned long long* __restrict__ events_per_element, uint32_t* status) {
+    const int64_t i0 = (int64_t)blockIdx.x * kCodecChunk + (int64_t)threadIdx.x * kCodecPer;
+    const int cnt = i0 >= n ? 0 : (int)(n - i0 < kCodecPer ? n - i0 : kCodecPer);
+    int64_t xs[kCodecPer], ys[kCodecPer], ps[kCodecPer], es[kCodecPer], ss[kCodecPer], key[kCodecPer];
+    uint32_t flags = 0;
+    if (kVec && cnt == kCodecPer) {                       // 16-byte streaming loads
+        const int64_t* const ins[5] = {x, y, pol, elem, smp};
+        int64_t* const regs[5] = {xs, ys, ps, es, ss};
+#pragma unroll
+        for (int a = 0; a < 5; ++a) {
+            const longlong2* q = reinterpret_cast<const longlong2*>(ins[a] + i0);
+            const longlong2 lo = __ldcs(q), hi = __ldcs(q + 1);
+            regs[a][0] = lo.x; regs[a][1] = lo.y; regs[a][2] = hi.x; regs[a][3] = hi.y;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < kCodecPer; ++k) {
+            const bool on = k < cnt;
+            xs[k] = on ? __ldcs(x + i0 + k) : 0;
+            ys[k] = on ? __ldcs(y + i0 + k) : 0;
+            ps[k] = on ? __ldcs(pol + i0 + k) : 0;
+            es[k] = on ? __ldcs(elem + i0 + k) : 0;
+            ss[k] = on ? __ldcs(smp + i0 + k) : 0;
+        }
+    }
+    pdl_wait();                                    // sample_shift comes from codec_plan_kernel
+#pragma unroll
+    for (int k = 0; k < kCodecPer; ++k) {
+        const bool on = k < cnt;
+        key[k] = -1;
+        if (on) {
+            const int64_t s = (int16_t)ss[k];                         // dataset.py:291 `.to(torch.short)`
+            const int64_t e = es[k];
+            if (s < 0 || s >= B) flags |= DVSOF_ST_BAD_SAMPLE;
+            else {
+                const int64_t g = e + v.sample_shift[s];               // dataset.py:297
+                if (g < 0 || g >= E) flags |= DVSOF_ST_BAD_COUNTS;     // the reference: IndexError
+                else key[k] = g;
+            }
+        }
+    }
+    if (cnt > 0) {
+        if (kVec && cnt == kCodecPer) {
+            *reinterpret_cast<short4*>(ox + i0) = make_short4((short)xs[0], (short)xs[1], (short)xs[2], (short)xs[3]);
+            *reinterpret_cast<short4*>(oy + i0) = make_short4((short)ys[0], (short)ys[1], (short)ys[2], (short)ys[3]);
+            // ((p + 1) / 2).to(bool): true unless p == -1 (dataset.py:289)
+            *reinterpret_cast<uchar4*>(op + i0) = make_uchar4(ps[0] != -1, ps[1] != -1, ps[2] != -1, ps[3] != -1);
+        } else {
+            for (int k = 0; k < cnt; ++k) {
+                ox[i0 + k] = (int16_t)xs[k]; oy[i0 + k] = (int16_t)ys[k]; op[i0 + k] = ps[k] != -1;
+            }
+        }
+    }
+    // histogram: one atomic per distinct element per warp and slot.  When every thread's events
+    // share one element (the usual case: elements hold thousands of events) a single slot carries
+    // the whole chunk.
+    // Counts of the CTA's first element are gathered in shared memory and leave with one atomic.
+    __shared__ int64_t cta_key;
+    __shared__ unsigned cta_count;
+    if (threadIdx.x == 0) { cta_key = key[0]; cta_count = 0u; }
+    __syncthreads();
+    const int64_t k0 = cta_key;
+    const int lane = threadIdx.x & 31;
+    const bool same = key[0] == key[1] && key[1] == key[2] && key[2] == key[3] && (cnt == kCodecPer || cnt == 0);
+    const bool merged = __all_sync(0xffffffffu, same);
+#pragma unroll
+    for (int k = 0; k < kCodecPer; ++k) {
+        const int64_t fk = merged ? (k == 0 ? key[0] : -1) : key[k];
+        if (__all_sync(0xffffffffu, fk < 0)) continue;                   // warp-uniform
+        const unsigned peers = __match_any_sync(0xffffffffu, fk);
+        const unsigned total = __popc(peers) * (merged ? (unsigned)kCodecPer : 1u);
+        if (fk >= 0 && lane == __ffs(peers) - 1) {
+            if (fk == k0) atomicAdd(&cta_count, total);
+            else atomicAdd(events_per_element + fk, (unsigned long long)total);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && k0 >= 0 && cta_count) atomicAdd(events_per_element + k0, (unsigned long long)cta_count);
+    if (flags) atomicOr(status, flags);
+}
+
+}  // namespace dvsof
+
+extern "C" size_t dvsof_codec_workspace_bytes(int64_t n_elements, int64_t n_samples) {
+    if (n_elements < 0 || n_samples < 0) return 0;
+    using dvsof::round_up;
+    const size_t e = (size_t)(n_elements > 0 ? n_elements : 1);
+    return round_up((size_t)(n_elements + 1) * 8, 256) + round_up((size_t)(n_samples + 1) * 8, 256) +
+           2 * round_up(e * 4, 256);
+}
+
+static bool codec_vec_ok(const void* a, const void* b, const void* c) {
+    return dvsof::aligned16(a) && dvsof::aligned16(b) && dvsof::aligned16(c);
+}
+
+extern "C" int dvsof_decode_events(const int16_t* x, const int16_t* y, const uint8_t* polarity01,
+                                   int64_t n_events, const int64_t* events_per_element,
+                                   int64_t n_elements, const int64_t* elements_per_sample,
+                                   int64_t n_samples, int64_t* out_x, int64_t* out_y,
+                                   int64_t* out_polarity, int64_t* out_element_index,
+                                   int64_t* out_sample_index, void* workspace, uint32_t* status,
+                                   void* stream_) {
+    using namespace dvsof;
+    if (n_events < 0 || n_elements < 0 || n_samples < 1 || !elements_per_sample || !workspace || !status ||
+        (n_elements > 0 && !events_per_element) || n_elements > INT32_MAX ||
+        (n_events > 0 && (!x || !y || !polarity01 || !out_x || !out_y || !out_polarity ||
+                          !out_element_index || !out_sample_index)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "decode_events: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const CodecView v = codec_view(workspace, n_elements, n_samples);
+    codec_plan_kernel<<<1, kCompactThreads, 0, stream>>>(events_per_element ? events_per_element : elements_per_sample,
+                                                         n_elements, elements_per_sample, n_samples, n_events, v, status);
+    if (int rc = check_launch("codec_plan_kernel")) return rc;
+    if (n_events == 0) return DVSOF_OK;
+    const int64_t grid = (n_events + kCodecChunk - 1) / kCodecChunk;
+    if (grid > INT32_MAX) return fail(DVSOF_ERR_INVALID_ARGUMENT, "decode_events: too many events");
+    const bool vec = codec_vec_ok(x, y, out_x) && codec_vec_ok(out_y, out_polarity, out_element_index) &&
+                     aligned16(out_sample_index) && (reinterpret_cast<uintptr_t>(polarity01) & 3u) == 0;
+    return launch_kernel("decode_events_kernel", vec ? decode_events_kernel<true> : decode_events_kernel<false>,
+                         (int)grid, kCompactThreads, 0, stream, true, x, y, polarity01, n_events, v, n_elements,
+                         out_x, out_y, out_polarity, out_element_index, out_sample_index);
+}
+
+extern "C" int dvsof_encode_events(const int64_t* x, const int64_t* y, const int64_t* polarity,
+                                   const int64_t* element_index, const int64_t* sample_index,
+                                   int64_t n_events, const int64_t* elements_per_sample,
+                                   int64_t n_samples, int64_t n_elements, int16_t* out_x,
+                                   int16_t* out_y, uint8_t* out_polarity01, int64_t* events_per_element,
+                                   void* workspace, uint32_t* status, void* stream_) {
+    using namespace dvsof;
+    if (n_events < 0 || n_elements < 0 || n_samples < 1 || !elements_per_sample || !workspace || !status ||
+        (n_elements > 0 && !events_per_element) ||
+        (n_events > 0 && (!x || !y || !polarity || !element_index || !sample_index || !out_x || !out_y ||
+                          !out_polarity01)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_events: bad arguments");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const CodecView v = codec_view(workspace, n_elements, n_samples);
+    if (n_elements > 0) {
+        cudaError_t e = cudaMemsetAsync(events_per_element, 0, sizeof(int64_t) * n_elements, stream);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_events memset: %s", cudaGetErrorString(e));
+    }
+    codec_plan_kernel<<<1, kCompactThreads, 0, stream>>>(nullptr, 0, elements_per_sample, n_samples, 0, v, status);
+    if (int rc = check_launch("codec_plan_kernel")) return rc;
+    if (n_events == 0) return DVSOF_OK;
+    const int64_t grid = (n_events + kCodecChunk - 1) / kCodecChunk;
+    if (grid > INT32_MAX) return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_events: too many events");
+    const bool vec = (reinterpret_cast<uintptr_t>(out_x) & 7u) == 0 && (reinterpret_cast<uintptr_t>(out_y) & 7u) == 0 &&
+                     (reinterpret_cast<uintptr_t>(out_polarity01) & 3u) == 0 && codec_vec_ok(x, y, polarity) &&
+                     aligned16(element_index) && aligned16(sample_index);
+    auto* epe = reinterpret_cast<unsigned long long*>(events_per_element);
+    return launch_kernel("encode_events_kernel", vec ? encode_events_kernel<true> : encode_events_kernel<false>,
+                         (int)grid, kCompactThreads, 0, stream, true, x, y, polarity, element_index, sample_index,
+                         n_events, v, n_samples, n_elements, out_x, out_y, out_polarity01, epe, status);
+}

@@ -1,0 +1,117 @@
+"""Batch codec of the reference's data pipeline on device: utils/dataset.py
+`encode_batch_info` (:201-237), `encode_batch` (:240-305), `decode_batch_info` (:308-332) and
+`decode_batch` (:335-373) with the same names, arguments and result dictionaries -- the tensors are
+CUDA tensors and the per-event work (narrowing / widening, polarity mapping, the histogram and the
+run-length expansion the reference does with numpy and Python loops) runs in libdvsof.
+
+The 9 B/event storage form can also be fed to the encoder directly
+(`encoder.compute_event_image_compact`), which skips the int64 form altogether."""
+import torch
+
+from . import _lib
+
+
+def _cumsum_with_prefix(v):
+    out = torch.zeros(v.numel() + 1, dtype=torch.int64, device=v.device)
+    torch.cumsum(v.to(torch.int64), 0, out=out[1:])
+    return out
+
+
+def encode_batch_info(timestamps, sample_idx, images, augmentation_params, size):
+    """utils/dataset.py:201-237: elements_per_sample = (images of the sample) - 1 as uint8, images
+    as uint8."""
+    sample_idx = _lib.require_cuda(sample_idx, 'sample_idx')
+    counts = torch.bincount(sample_idx.to(torch.int64), minlength=int(size))
+    elements_per_sample = (counts.to(torch.int16) - 1).to(torch.uint8)          # :231-233
+    return {'timestamps': timestamps,
+            'elements_per_sample': elements_per_sample,
+            'images': images.to(torch.uint8),
+            'augmentation_params': augmentation_params}
+
+
+def encode_batch(events, timestamps, sample_idx, images, augmentation_params, size):
+    """utils/dataset.py:240-305.  events: dict of CUDA tensors {x, y, timestamp, polarity,
+    element_index, sample_index} (the training form).  Like the reference, the number of elements
+    is read from the LAST event (`int(new_e[-1]) + 1`, :298): one two-value D2H read."""
+    result = encode_batch_info(timestamps, sample_idx, images, augmentation_params, size)
+    x = _lib.require_cuda(events['x'], 'x', torch.int64)
+    dev = x.device
+    y = _lib.require_cuda(events['y'], 'y', torch.int64)
+    p = _lib.require_cuda(events['polarity'], 'polarity', torch.int64)
+    e = _lib.require_cuda(events['element_index'], 'element_index', torch.int64)
+    s = _lib.require_cuda(events['sample_index'], 'sample_index', torch.int64)
+    n = x.numel()
+    assert y.numel() == n and p.numel() == n and e.numel() == n and s.numel() == n
+    eps = result['elements_per_sample'].to(torch.int64)
+    bs = eps.numel()
+    assert n > 0, 'encode_batch: the reference indexes the last event (IndexError on an empty batch)'
+    last = torch.stack([e[-1], s[-1]]).tolist()                                   # :298
+    shift = _cumsum_with_prefix(eps)
+    last_s = ((last[1] + 2 ** 15) % 2 ** 16) - 2 ** 15                            # .to(torch.short), :291
+    total_elements = int(last[0] + shift[last_s].item()) + 1
+    ox = torch.empty(n, dtype=torch.int16, device=dev)
+    oy = torch.empty(n, dtype=torch.int16, device=dev)
+    op = torch.empty(n, dtype=torch.bool, device=dev)
+    epe = torch.empty(max(total_elements, 0), dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        st = _lib.status_for(dev)
+        st.flush(IndexError)
+        lib = _lib.load()
+        ws = torch.empty(lib.dvsof_codec_workspace_bytes(epe.numel(), bs), dtype=torch.uint8, device=dev)
+        _lib.call('dvsof_encode_events', _lib.ptr(x), _lib.ptr(y), _lib.ptr(p), _lib.ptr(e), _lib.ptr(s), n,
+                  _lib.ptr(eps), bs, epe.numel(), _lib.ptr(ox), _lib.ptr(oy), _lib.ptr(op.view(torch.uint8)),
+                  _lib.ptr(epe), _lib.ptr(ws), _lib.ptr(st.word), _lib.stream_ptr(dev))
+        st.after_call(IndexError)
+    result['events'] = {'x': ox, 'y': oy, 'timestamp': events['timestamp'], 'polarity': op,
+                        'events_per_element': epe}
+    return result
+
+
+def decode_batch_info(encoded_batch_info):
+    """utils/dataset.py:308-332."""
+    timestamps = encoded_batch_info['timestamps']
+    eps = encoded_batch_info['elements_per_sample']
+    batch_size = eps.numel()
+    sample_idx = torch.repeat_interleave(torch.arange(batch_size, dtype=torch.int64, device=eps.device),
+                                         eps.to(torch.int64) + 1)                 # :322-324
+    return {'timestamps': timestamps.to(torch.float32),
+            'sample_idx': sample_idx,
+            'images': encoded_batch_info['images'].to(torch.float32),
+            'augmentation_params': encoded_batch_info['augmentation_params'],
+            'size': batch_size}
+
+
+def decode_events(events, elements_per_sample):
+    """The event part of decode_batch (utils/dataset.py:349-372) in one device pass."""
+    x = _lib.require_cuda(events['x'], 'x', torch.int16)
+    dev = x.device
+    y = _lib.require_cuda(events['y'], 'y', torch.int16)
+    p = _lib.require_cuda(events['polarity'], 'polarity')
+    if p.dtype == torch.bool:
+        p = p.view(torch.uint8)
+    assert p.dtype == torch.uint8
+    epe = _lib.require_cuda(events['events_per_element'], 'events_per_element').to(torch.int64)
+    eps = _lib.require_cuda(elements_per_sample, 'elements_per_sample').to(torch.int64)
+    n = x.numel()
+    assert y.numel() == n and p.numel() == n
+    out = {k: torch.empty(n, dtype=torch.int64, device=dev)
+           for k in ('x', 'y', 'polarity', 'element_index', 'sample_index')}
+    with torch.cuda.device(dev):
+        st = _lib.status_for(dev)
+        st.flush()
+        lib = _lib.load()
+        ws = torch.empty(lib.dvsof_codec_workspace_bytes(epe.numel(), eps.numel()), dtype=torch.uint8, device=dev)
+        _lib.call('dvsof_decode_events', _lib.ptr(x), _lib.ptr(y), _lib.ptr(p), n, _lib.ptr(epe), epe.numel(),
+                  _lib.ptr(eps), eps.numel(), _lib.ptr(out['x']), _lib.ptr(out['y']), _lib.ptr(out['polarity']),
+                  _lib.ptr(out['element_index']), _lib.ptr(out['sample_index']), _lib.ptr(ws),
+                  _lib.ptr(st.word), _lib.stream_ptr(dev))
+        st.after_call()
+    return {'x': out['x'], 'y': out['y'], 'timestamp': events['timestamp'], 'polarity': out['polarity'],
+            'element_index': out['element_index'], 'sample_index': out['sample_index']}
+
+
+def decode_batch(encoded_batch):
+    """utils/dataset.py:335-373: the batch in the training form (the input format of encode_batch)."""
+    result = decode_batch_info(encoded_batch)
+    result['events'] = decode_events(encoded_batch['events'], encoded_batch['elements_per_sample'])
+    return result

@@ -38,6 +38,7 @@ extern "C" {
 #define DVSOF_ST_BAD_PIXEL 0x8u        /* x/y outside the image (reference: index error)   */
 #define DVSOF_ST_NO_MATCH 0x10u        /* image<->flow timestamp match != 1 (utils/loss.py:193) */
 #define DVSOF_ST_BAD_LUT 0x20u         /* map_events LUT entry outside [0, H*W)            */
+#define DVSOF_ST_BAD_COUNTS 0x40u      /* batch codec: run lengths do not cover the events / element outside the batch */
 
 const char* dvsof_last_error(void);
 int dvsof_version(void);
@@ -135,6 +136,29 @@ int dvsof_augment_events_count(const float* events, int64_t n_events, int32_t n_
 int dvsof_augment_events_write(const float* events, int64_t n_events, int32_t n_cols, int32_t H,
                                int32_t W, int32_t flip, const void* lut_ws, const double* box,
                                const void* ev_ws, float* out, void* stream);
+
+/* Batch codec, event part.  Storage form = utils/dataset.py:286-302: x, y
+ * int16, polarity bool (1 = positive), events_per_element [int64, E] (events of every element, the
+ * elements of all samples concatenated), elements_per_sample [int64, B]; the fp32 timestamps are
+ * the same array in both forms.  Training form = the int64 arrays of utils/dataset.py:362-372.
+ *   decode (dataset.py:335-373 `decode_batch`): widening, polarity*2-1 and the run-length expansion
+ *     into element_index / sample_index in one pass (5 B read, 40 B written per event).  Sets
+ *     DVSOF_ST_BAD_COUNTS when the run lengths do not add up to n_events.
+ *   encode (dataset.py:283-304 `encode_batch`): narrowing with torch's wrap-around, polarity
+ *     ((p+1)/2).to(bool), events_per_element[E] = histogram of element_index + shift[sample_index]
+ *     (zeroed inside).  n_elements is the caller's `int(new_e[-1]) + 1` (dataset.py:298).
+ * workspace: dvsof_codec_workspace_bytes(n_elements, n_samples). */
+size_t dvsof_codec_workspace_bytes(int64_t n_elements, int64_t n_samples);
+int dvsof_decode_events(const int16_t* x, const int16_t* y, const uint8_t* polarity01,
+                        int64_t n_events, const int64_t* events_per_element, int64_t n_elements,
+                        const int64_t* elements_per_sample, int64_t n_samples, int64_t* out_x,
+                        int64_t* out_y, int64_t* out_polarity, int64_t* out_element_index,
+                        int64_t* out_sample_index, void* workspace, uint32_t* status, void* stream);
+int dvsof_encode_events(const int64_t* x, const int64_t* y, const int64_t* polarity,
+                        const int64_t* element_index, const int64_t* sample_index, int64_t n_events,
+                        const int64_t* elements_per_sample, int64_t n_samples, int64_t n_elements,
+                        int16_t* out_x, int16_t* out_y, uint8_t* out_polarity01,
+                        int64_t* events_per_element, void* workspace, uint32_t* status, void* stream);
 
 /* utils/data.py:139-152 frame_generator: out[k] = np.searchsorted(t, bounds[k], side='right') for
  * every window boundary (frames.ravel()); t sorted ascending, fp32 (elem_size 4) or fp64 (8),

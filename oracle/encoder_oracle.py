@@ -164,11 +164,35 @@ def decode_events(x16, y16, pbool, t, events_per_element, elements_per_sample):
     """utils/dataset.py:335-373 (decode_batch, event part): storage form -> training form."""
     epe = np.asarray(events_per_element, dtype=np.int64)
     eps = np.asarray(elements_per_sample, dtype=np.int64)
-    sample_of_element = np.repeat(np.arange(eps.size), eps)
-    elem_in_sample = np.arange(epe.size) - np.repeat(np.cumsum(eps) - eps, eps)
+    # :357-359 slices events_per_element by the prefix of elements_per_sample: elements past the
+    # end of a shorter events_per_element (trailing empty ones, dropped by encode_batch :298) do
+    # not exist
+    sample_of_element = np.repeat(np.arange(eps.size), eps)[:epe.size]
+    elem_in_sample = np.arange(epe.size) - np.repeat(np.cumsum(eps) - eps, eps)[:epe.size]
     return {'x': np.asarray(x16).astype(np.int64),
             'y': np.asarray(y16).astype(np.int64),
             'timestamp': np.asarray(t, dtype=F32),
             'polarity': np.asarray(pbool).astype(np.int64) * 2 - 1,
             'element_index': np.repeat(elem_in_sample, epe),
             'sample_index': np.repeat(sample_of_element, epe)}
+
+
+def encode_events(x, y, polarity, element_index, sample_index, elements_per_sample):
+    """utils/dataset.py:286-302 (encode_batch, event part): training form -> storage form.  The
+    number of elements is taken from the LAST event (:298), so trailing empty elements vanish."""
+    s = np.asarray(sample_index).astype(np.int16)                                 # :291
+    shift = np.cumsum(np.concatenate([[0], np.asarray(elements_per_sample, dtype=np.int64)]))   # :294-296
+    new_e = np.asarray(element_index, dtype=np.int64) + shift[s]                  # :297
+    total = int(new_e[-1]) + 1                                                    # :298
+    epe = np.zeros(total, dtype=np.int64)
+    np.add.at(epe, new_e, 1)                                                      # :300-301
+    return {'x': np.asarray(x).astype(np.int16), 'y': np.asarray(y).astype(np.int16),
+            'polarity': ((np.asarray(polarity) + 1) / 2).astype(bool),            # :289
+            'events_per_element': epe}
+
+
+def elements_per_sample(sample_idx, size):
+    """utils/dataset.py:231-233 (encode_batch_info): images per sample minus one, as uint8."""
+    eps = np.zeros(size, dtype=np.int16) - 1
+    np.add.at(eps, np.asarray(sample_idx, dtype=np.int64), 1)
+    return eps.astype(np.uint8)

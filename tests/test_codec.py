@@ -1,0 +1,167 @@
+"""Batch codec: utils/dataset.py encode_batch / decode_batch.
+
+CPU: the numpy oracle against vectors produced by the reference's own functions
+(tests/golden/codec.npz, made by tests/golden/make_golden_codec.py; `fixture` is the batch of
+tests/dataset/test_encoding.py:21-80).  GPU: the device codec against the same vectors and against
+the oracle on larger seeded batches, bit for bit."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import encoder_oracle as eo
+
+G = np.load(Path(__file__).parent / 'golden' / 'codec.npz')
+CASES = ['fixture', 'ragged', 'droptail', 'single', 'bulk']
+DEC_KEYS = ['x', 'y', 'polarity', 'element_index', 'sample_index']
+
+
+def _case(name):
+    dec = {k: G[f'{name}/dec/{k}'] for k in DEC_KEYS + ['timestamp']}
+    enc = {k: G[f'{name}/enc/{k}'] for k in ['x', 'y', 'timestamp', 'polarity', 'events_per_element']}
+    back = {k: G[f'{name}/back/{k}'] for k in DEC_KEYS + ['timestamp']}
+    return dec, enc, G[f'{name}/enc/elements_per_sample'], back, G[f'{name}/sample_idx'], int(G[f'{name}/size'])
+
+
+def test_fixture_is_the_reference_test_vector():
+    # tests/dataset/test_encoding.py:57-67
+    _, enc, eps, _, _, _ = _case('fixture')
+    assert enc['events_per_element'].tolist() == [1, 2, 1, 1, 0, 1, 1]
+    assert eps.tolist() == [2, 1, 4] and eps.dtype == np.uint8
+    assert enc['polarity'].tolist() == [False, True, False, True, True, True, False]
+    assert enc['x'].dtype == np.int16
+
+
+@pytest.mark.parametrize('name', CASES)
+def test_oracle_matches_reference(name):
+    dec, enc, eps, back, sample_idx, size = _case(name)
+    assert np.array_equal(eo.elements_per_sample(sample_idx, size), eps)
+    got = eo.encode_events(dec['x'], dec['y'], dec['polarity'], dec['element_index'], dec['sample_index'], eps)
+    for k in ('x', 'y', 'polarity', 'events_per_element'):
+        assert got[k].dtype == enc[k].dtype and np.array_equal(got[k], enc[k]), k
+    out = eo.decode_events(enc['x'], enc['y'], enc['polarity'], enc['timestamp'], enc['events_per_element'], eps)
+    for k in DEC_KEYS:
+        assert out[k].dtype == np.int64 and np.array_equal(out[k], back[k]), k
+    for k in DEC_KEYS:                        # the round trip is the identity on these batches
+        assert np.array_equal(back[k], dec[k]), k
+
+
+def _cuda(d):
+    return {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in d.items()}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', CASES)
+def test_device_codec_matches_reference(name):
+    import dvs_of_training_framework_b200 as dv
+    dec, enc, eps, back, sample_idx, size = _case(name)
+    n_img = sample_idx.size
+    e = dv.encode_batch(_cuda(dec), torch.zeros(n_img).cuda(), torch.from_numpy(sample_idx).cuda(),
+                        torch.zeros(n_img, 1, 2, 2).cuda(), {}, size)
+    assert e['elements_per_sample'].dtype == torch.uint8
+    assert e['elements_per_sample'].cpu().numpy().tolist() == eps.tolist()
+    assert e['images'].dtype == torch.uint8
+    for k in ('x', 'y', 'polarity', 'events_per_element'):
+        got = e['events'][k].cpu().numpy()
+        assert got.dtype == enc[k].dtype and np.array_equal(got, enc[k]), k
+    assert e['events']['timestamp'].data_ptr() == e['events']['timestamp'].data_ptr()
+    d = dv.decode_batch(e)
+    assert d['size'] == size and np.array_equal(d['sample_idx'].cpu().numpy(), G[f'{name}/back/sample_idx'])
+    assert d['images'].dtype == torch.float32 and d['timestamps'].dtype == torch.float32
+    for k in DEC_KEYS:
+        got = d['events'][k].cpu().numpy()
+        assert got.dtype == np.int64 and np.array_equal(got, back[k]), k
+    assert np.array_equal(d['events']['timestamp'].cpu().numpy(), dec['timestamp'])
+
+
+def _big(seed, n_samples, n_events):
+    g = np.random.default_rng(seed)
+    eps = g.integers(1, 6, n_samples)
+    E = int(eps.sum())
+    epe = g.multinomial(n_events, g.dirichlet(np.ones(E) * 0.3))
+    epe[g.random(E) < 0.2] = 0
+    epe[-1] = max(epe[-1], 1)
+    n = int(epe.sum())
+    enc = {'x': g.integers(-5, 700, n).astype(np.int16), 'y': g.integers(0, 500, n).astype(np.int16),
+           'timestamp': g.random(n).astype(np.float32), 'polarity': g.random(n) < 0.7,
+           'events_per_element': epe.astype(np.int64)}
+    return enc, eps.astype(np.uint8)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('seed,n_samples,n_events', [(1, 8, 100_003), (2, 3, 4099), (3, 32, 1_000_001)])
+def test_device_decode_encode_against_oracle(seed, n_samples, n_events):
+    import dvs_of_training_framework_b200 as dv
+    enc, eps = _big(seed, n_samples, n_events)
+    want = eo.decode_events(enc['x'], enc['y'], enc['polarity'], enc['timestamp'], enc['events_per_element'], eps)
+    got = dv.decode_events(_cuda(enc), torch.from_numpy(eps).cuda())
+    for k in DEC_KEYS:
+        assert np.array_equal(got[k].cpu().numpy(), want[k]), k
+    # and back: the device encoder on the decoded form reproduces the storage form
+    sample_idx = np.repeat(np.arange(n_samples), eps.astype(np.int64) + 1)
+    e = dv.encode_batch(got, torch.zeros(sample_idx.size).cuda(), torch.from_numpy(sample_idx).cuda(),
+                        torch.zeros(sample_idx.size, 1, 1, 1).cuda(), {}, n_samples)
+    ref = eo.encode_events(want['x'], want['y'], want['polarity'], want['element_index'], want['sample_index'], eps)
+    for k in ('x', 'y', 'polarity', 'events_per_element'):
+        assert np.array_equal(e['events'][k].cpu().numpy(), ref[k]), k
+
+
+@pytest.mark.gpu
+def test_device_codec_unaligned_views_and_unsorted_histogram():
+    import dvs_of_training_framework_b200 as dv
+    enc, eps = _big(7, 4, 5003)
+    n = enc['x'].size
+    pad = {k: torch.from_numpy(np.concatenate([v[:1], v])).cuda()[1:] for k, v in enc.items() if k != 'events_per_element'}
+    pad['events_per_element'] = torch.from_numpy(enc['events_per_element']).cuda()
+    assert pad['x'].data_ptr() % 16 != 0
+    want = eo.decode_events(enc['x'], enc['y'], enc['polarity'], enc['timestamp'], enc['events_per_element'], eps)
+    got = dv.decode_events(pad, torch.from_numpy(eps).cuda())
+    for k in DEC_KEYS:
+        assert np.array_equal(got[k].cpu().numpy(), want[k]), k
+    # np.add.at semantics: the histogram does not need grouped events
+    perm = np.random.default_rng(0).permutation(n)
+    perm[-1], perm[np.argmax(perm == n - 1)] = n - 1, perm[-1]          # keep the last event last (:298)
+    shuf = {k: torch.from_numpy(want[k][perm]).cuda() for k in DEC_KEYS}
+    shuf['timestamp'] = torch.from_numpy(enc['timestamp'][perm]).cuda()
+    sample_idx = np.repeat(np.arange(4), eps.astype(np.int64) + 1)
+    e = dv.encode_batch(shuf, torch.zeros(sample_idx.size).cuda(), torch.from_numpy(sample_idx).cuda(),
+                        torch.zeros(sample_idx.size, 1, 1, 1).cuda(), {}, 4)
+    ref = eo.encode_events(want['x'][perm], want['y'][perm], want['polarity'][perm], want['element_index'][perm],
+                           want['sample_index'][perm], eps)
+    for k in ('x', 'y', 'polarity', 'events_per_element'):
+        assert np.array_equal(e['events'][k].cpu().numpy(), ref[k]), k
+
+
+@pytest.mark.gpu
+def test_device_codec_flags_inconsistent_counts():
+    import dvs_of_training_framework_b200 as dv
+    enc, eps = _big(9, 2, 1000)
+    enc['events_per_element'] = enc['events_per_element'].copy()
+    enc['events_per_element'][0] += 1
+    with pytest.raises(AssertionError):
+        dv.decode_events(_cuda(enc), torch.from_numpy(eps).cuda())
+    with pytest.raises(RuntimeError):
+        dv.decode_events({k: torch.from_numpy(v) for k, v in enc.items()}, torch.from_numpy(eps))
+
+
+@pytest.mark.gpu
+def test_compact_encoder_equals_decode_then_encode_image():
+    """The fused path (storage form straight into the event image) equals decode_batch followed
+    by the int64 encoder."""
+    import dvs_of_training_framework_b200 as dv
+    g = np.random.default_rng(5)
+    B, H, W = 4, 64, 96
+    eps = np.ones(B, dtype=np.uint8)
+    epe = g.integers(1000, 3000, B).astype(np.int64)
+    n = int(epe.sum())
+    t = np.concatenate([np.sort(g.random(k)).astype(np.float32) for k in epe])
+    enc = {'x': g.integers(0, W, n).astype(np.int16), 'y': g.integers(0, H, n).astype(np.int16),
+           'timestamp': t, 'polarity': g.random(n) < 0.7, 'events_per_element': epe}
+    ts = torch.tensor([0., 1.] * B).cuda()
+    sidx = torch.arange(B).repeat_interleave(2).cuda()
+    dec = dv.decode_events(_cuda(enc), torch.from_numpy(eps).cuda())
+    a = dv.compute_event_image(dec, ts, sidx, (H, W))
+    c = _cuda(enc)
+    b = dv.compute_event_image_compact(c['x'], c['y'], c['timestamp'], c['polarity'], c['events_per_element'], ts, (H, W))
+    assert torch.equal(a, b)
