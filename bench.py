@@ -360,7 +360,7 @@ def bench_train_step(K, W, dev, world, per_gpu=32):
     c = CFG['cfg2']
     rank = dist.get_rank() if world > 1 else 0
     torch.manual_seed(0)
-    model = Model(dev).to(memory_format=torch.channels_last)
+    model = Model(dev)          # NCHW: 34 ms/step against 39 ms in channels_last (scripts/exp_train_variants.py)
     red = tr.GradientAllreducer(model.parameters())
     red.broadcast_parameters(model)
     opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)      # train_flownet.py:59-61
@@ -644,7 +644,7 @@ def main():
     if train is not None:
         line['train_step'] = {'metric': 'train-step samples/s', 'value': world * train['samples'] / (train['step_ms'] * 1e-3),
                               'unit': 'samples/s', 'ms_per_step': train['step_ms'],
-                              'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN), 256x256, 131072 events/sample, '
+                              'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN convolutions; upsample+reflect-pad and ReLU+BatchNorm through libdvsof), 256x256, 131072 events/sample, '
                                           f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad), '
                                           'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward'}
     for name, r in extra.items():

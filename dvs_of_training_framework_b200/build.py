@@ -6,7 +6,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / 'csrc'
 LIB = Path(os.environ['DVSOF_LIB']) if os.environ.get('DVSOF_LIB') else PKG / 'libdvsof.so'
-SOURCES = ['runtime.cu', 'encode.cu', 'transforms.cu', 'loss.cu', 'eval.cu']
+SOURCES = ['runtime.cu', 'encode.cu', 'transforms.cu', 'loss.cu', 'eval.cu', 'glue.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 

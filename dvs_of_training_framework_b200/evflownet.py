@@ -15,9 +15,60 @@ import torch
 import torch.nn.functional as F
 from torch import nn
 
+from . import _lib
 from .encoder import quantize
 
 _WIDTHS = (64, 128, 256, 512)
+
+
+class _ReluBN(torch.autograd.Function):
+    """`bn(relu(z))` in training mode (net.py:36,54) through csrc/glue.cu: batch statistics and the
+    running-statistics update like torch.nn.BatchNorm2d, the ReLU folded into every pass."""
+
+    @staticmethod
+    def forward(ctx, z, weight, bias, running_mean, running_var, momentum, eps):
+        z = z.contiguous()
+        N, C = z.shape[0], z.shape[1]
+        HW = z.numel() // max(N * C, 1)
+        dev = z.device
+        y = torch.empty_like(z)
+        stats = torch.empty((2, C), dtype=torch.float32, device=dev)
+        lib = _lib.load()
+        ws = torch.empty(lib.dvsof_relu_bn_workspace_bytes(N, C), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('dvsof_relu_bn_forward', _lib.ptr(z), N, C, HW, _lib.ptr(weight), _lib.ptr(bias),
+                      _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps), _lib.ptr(y),
+                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(ws), _lib.stream_ptr(dev))
+        ctx.save_for_backward(z, weight, stats)
+        ctx.ws = ws
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        z, weight, stats = ctx.saved_tensors
+        gy = gy.contiguous()
+        N, C = z.shape[0], z.shape[1]
+        HW = z.numel() // max(N * C, 1)
+        dev = z.device
+        gz = torch.empty_like(z)
+        gwb = torch.empty((2, C), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.call('dvsof_relu_bn_backward', _lib.ptr(z), _lib.ptr(gy), N, C, HW, _lib.ptr(weight),
+                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(gz), _lib.ptr(gwb[0]), _lib.ptr(gwb[1]),
+                      _lib.ptr(ctx.ws), _lib.stream_ptr(dev))
+        return gz, gwb[0], gwb[1], None, None, None, None
+
+
+def relu_batchnorm(z, bn):
+    """bn(relu(z)).  Training on CUDA fp32 takes the fused kernels; evaluation mode and CPU tensors
+    (the world-size-2 tests of the host logic) the ATen ops."""
+    if (bn.training and z.is_cuda and z.dtype == torch.float32 and bn.track_running_stats
+            and bn.affine and bn.momentum is not None and z.numel() > 0):
+        if z.numel() // z.shape[1] <= 1:       # torch.nn.functional.batch_norm's own check
+            raise ValueError(f'Expected more than 1 value per channel when training, got input size {z.size()}')
+        bn.num_batches_tracked.add_(1)
+        return _ReluBN.apply(z, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps)
+    return bn(F.relu(z))
 
 
 class _ConvReluBN(nn.Module):
@@ -32,7 +83,7 @@ class _ConvReluBN(nn.Module):
         nn.init.constant_(self.bn.weight, 0.1)
 
     def forward(self, x):
-        return self.bn(F.relu(self.conv(x)))
+        return relu_batchnorm(self.conv(x), self.bn)
 
 
 class _Down(nn.Module):
@@ -55,6 +106,40 @@ class _Residual(nn.Module):
         return x + self.body(x)
 
 
+class _UpsamplePad(torch.autograd.Function):
+    """`F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect')` as one gather per
+    direction (csrc/glue.cu): the 4x upsampled intermediate is never written."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous()
+        N, C, H, W = x.shape
+        y = torch.empty((N, C, 2 * H + 2, 2 * W + 2), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.call('dvsof_upsample2x_reflect_pad_forward', _lib.ptr(x), N * C, H, W, _lib.ptr(y),
+                      _lib.stream_ptr(x.device))
+        ctx.shape = (N, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        gy = gy.contiguous()
+        N, C, H, W = ctx.shape
+        gx = torch.empty(ctx.shape, dtype=torch.float32, device=gy.device)
+        with torch.cuda.device(gy.device):
+            _lib.call('dvsof_upsample2x_reflect_pad_backward', _lib.ptr(gy), N * C, H, W, _lib.ptr(gx),
+                      _lib.stream_ptr(gy.device))
+        return gx
+
+
+def upsample2x_reflect_pad(x):
+    """Head of a decoder block (net.py:72-85).  CUDA fp32 tensors take the fused kernel; anything
+    else (the CPU world-size-2 tests of the host logic) the two ATen ops."""
+    if x.is_cuda and x.dtype == torch.float32:
+        return _UpsamplePad.apply(x)
+    return F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect')
+
+
 class _Up(nn.Module):
     """nearest x2, reflect pad 1, 3x3 conv (net.py:72-85)."""
 
@@ -63,7 +148,7 @@ class _Up(nn.Module):
         self.block = _ConvReluBN(cin, cout)
 
     def forward(self, x):
-        return self.block(F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect'))
+        return self.block(upsample2x_reflect_pad(x))
 
 
 class Model(nn.Module):

@@ -1,0 +1,89 @@
+"""Train-step glue kernels against the ATen ops they replace (EV_FlowNet/net.py:72-85)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+
+def _ref(x):
+    return F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect')
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('shape', [(2, 3, 1, 1), (1, 2, 1, 5), (2, 5, 4, 1), (3, 7, 16, 20), (2, 130, 33, 47),
+                                   (1, 1, 128, 128)])
+def test_upsample_reflect_pad_matches_aten(shape):
+    from dvs_of_training_framework_b200.evflownet import upsample2x_reflect_pad
+    g = torch.Generator(device='cuda').manual_seed(sum(shape))
+    x = torch.randn(shape, generator=g, device='cuda', requires_grad=True)
+    y = upsample2x_reflect_pad(x)
+    xr = x.detach().clone().requires_grad_()
+    yr = _ref(xr)
+    assert y.shape == yr.shape and torch.equal(y, yr)                 # a gather: exact
+    gy = torch.randn(y.shape, generator=g, device='cuda')
+    y.backward(gy)
+    yr.backward(gy)
+    # the adjoint sums up to 16 values per element; the order differs from ATen's two kernels
+    torch.testing.assert_close(x.grad, xr.grad, rtol=1e-5, atol=1e-5)
+    # and it is the exact adjoint: <y(x), gy> == <x, grad>
+    lhs = (y.detach().double() * gy.double()).sum()
+    rhs = (x.detach().double() * x.grad.double()).sum()
+    torch.testing.assert_close(lhs, rhs, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.gpu
+def test_upsample_reflect_pad_non_contiguous_input_and_determinism():
+    from dvs_of_training_framework_b200.evflownet import upsample2x_reflect_pad
+    x = torch.randn(2, 6, 9, 11, device='cuda')[:, ::2]
+    assert torch.equal(upsample2x_reflect_pad(x), _ref(x))
+    xs = torch.randn(4, 8, 32, 32, device='cuda', requires_grad=True)
+    gy = torch.randn(4, 8, 66, 66, device='cuda')
+    grads = []
+    for _ in range(2):
+        xs.grad = None
+        upsample2x_reflect_pad(xs).backward(gy)
+        grads.append(xs.grad.clone())
+    assert torch.equal(grads[0], grads[1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('shape', [(4, 3, 5, 7), (32, 32, 64, 64), (2, 512, 16, 16), (1, 8, 1, 2), (3, 5, 8, 8),
+                                   (8, 130, 20, 12)])
+def test_relu_batchnorm_matches_aten(shape):
+    from torch import nn
+    from dvs_of_training_framework_b200.evflownet import relu_batchnorm
+    g = torch.Generator(device='cuda').manual_seed(sum(shape))
+    C = shape[1]
+    bn = nn.BatchNorm2d(C).cuda()
+    ref = nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.copy_(torch.rand(C, generator=g, device='cuda') + 0.5)
+        bn.bias.copy_(torch.randn(C, generator=g, device='cuda'))
+        bn.running_mean.copy_(torch.randn(C, generator=g, device='cuda'))
+        bn.running_var.copy_(torch.rand(C, generator=g, device='cuda') + 0.5)
+    ref.load_state_dict(bn.state_dict())
+    z = torch.randn(shape, generator=g, device='cuda', requires_grad=True)
+    zr = z.detach().clone().requires_grad_()
+    y = relu_batchnorm(z, bn)
+    yr = ref(torch.relu(zr))
+    torch.testing.assert_close(y, yr, rtol=2e-5, atol=2e-5)
+    torch.testing.assert_close(bn.running_mean, ref.running_mean, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-5, atol=1e-6)
+    assert int(bn.num_batches_tracked) == int(ref.num_batches_tracked) == 1
+    gy = torch.randn(shape, generator=g, device='cuda')
+    y.backward(gy)
+    yr.backward(gy)
+    torch.testing.assert_close(z.grad, zr.grad, rtol=2e-4, atol=2e-5)
+    torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=2e-4, atol=2e-4)
+    torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=2e-5, atol=2e-4)
+    # evaluation mode goes through ATen (running statistics)
+    bn.eval()
+    assert torch.equal(relu_batchnorm(z.detach(), bn), bn(torch.relu(z.detach())))
+    assert int(bn.num_batches_tracked) == 1
+
+
+@pytest.mark.gpu
+def test_relu_batchnorm_single_value_per_channel_raises_like_torch():
+    from torch import nn
+    from dvs_of_training_framework_b200.evflownet import relu_batchnorm
+    with pytest.raises(ValueError):
+        relu_batchnorm(torch.randn(1, 8, 1, 1, device='cuda'), nn.BatchNorm2d(8).cuda())
