@@ -360,7 +360,10 @@ def bench_train_step(K, W, dev, world, per_gpu=32):
     c = CFG['cfg2']
     rank = dist.get_rank() if world > 1 else 0
     torch.manual_seed(0)
-    model = Model(dev)          # NCHW: 34 ms/step against 39 ms in channels_last (scripts/exp_train_variants.py)
+    # channels_last end to end: the glue kernels have (N, H, W, C) variants and the decoder inputs are
+    # filled up to a multiple of 8 channels, so cuDNN runs without layout or padding copies
+    # (15.9 ms/step against 21.1 ms in NCHW, scripts/exp_train_variants.py)
+    model = Model(dev).to(memory_format=torch.channels_last)
     red = tr.GradientAllreducer(model.parameters())
     red.broadcast_parameters(model)
     opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)      # train_flownet.py:59-61

@@ -70,6 +70,74 @@ upsample2x_reflect_pad_bwd_kernel(const float* __restrict__ gy, float* __restric
     }
 }
 
+// channels_last variants: a row of the tensor is W x C floats, a pixel is C contiguous floats.
+// Work item = V consecutive channels of one pixel (V = 4, 2 or 1 by divisibility of C); a CTA walks
+// output rows, its threads the flattened (pixel, channel) index of the row.  o / C through a float
+// reciprocal: exact below 2^21 items per row (checked on the host).
+template <int V> struct VecT;
+template <> struct VecT<4> { using T = float4; };
+template <> struct VecT<2> { using T = float2; };
+template <> struct VecT<1> { using T = float; };
+__device__ __forceinline__ float4 vadd(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
+__device__ __forceinline__ float2 vadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float vadd(float a, float b) { return a + b; }
+
+template <int V>
+__global__ void __launch_bounds__(256)
+upsample2x_reflect_pad_fwd_nhwc_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t N, int C,
+                                       int H, int W) {
+    using T = typename VecT<V>::T;
+    const int Ho = 2 * H + 2, Wo = 2 * W + 2, CV = C / V;
+    const float inv_cv = 1.f / (float)CV;
+    const int row_items = Wo * CV;
+    for (int64_t row = blockIdx.x; row < N * Ho; row += gridDim.x) {
+        const int64_t n = row / Ho;
+        const int i = (int)(row - n * Ho);
+        const int a = reflect_idx(i - 1, 2 * H) >> 1;
+        const T* src = reinterpret_cast<const T*>(x + (n * H + a) * (int64_t)W * C);
+        T* dst = reinterpret_cast<T*>(y + row * (int64_t)Wo * C);
+        for (int o = threadIdx.x; o < row_items; o += 256) {
+            const int j = (int)(((float)o + 0.5f) * inv_cv), cv = o - j * CV;
+            const int b = reflect_idx(j - 1, 2 * W) >> 1;
+            dst[o] = __ldg(src + b * CV + cv);
+        }
+    }
+}
+
+template <int V>
+__global__ void __launch_bounds__(256)
+upsample2x_reflect_pad_bwd_nhwc_kernel(const float* __restrict__ gy, float* __restrict__ gx, int64_t N, int C,
+                                       int H, int W) {
+    using T = typename VecT<V>::T;
+    const int Ho = 2 * H + 2, Wo = 2 * W + 2, CV = C / V;
+    const float inv_cv = 1.f / (float)CV;
+    const int row_items = W * CV;
+    for (int64_t row = blockIdx.x; row < N * H; row += gridDim.x) {
+        const int64_t n = row / H;
+        const int h = (int)(row - n * H);
+        int ri[4], nr = 0;
+        if (h == 0) ri[nr++] = 0;
+        ri[nr++] = 2 * h + 1;
+        ri[nr++] = 2 * h + 2;
+        if (h == H - 1) ri[nr++] = 2 * H + 1;
+        const T* base = reinterpret_cast<const T*>(gy + n * (int64_t)Ho * Wo * C);
+        T* dst = reinterpret_cast<T*>(gx + row * (int64_t)W * C);
+        for (int o = threadIdx.x; o < row_items; o += 256) {
+            const int w = (int)(((float)o + 0.5f) * inv_cv), cv = o - w * CV;
+            T acc = T();
+            for (int k = 0; k < nr; ++k) {
+                const T* r = base + (int64_t)ri[k] * Wo * CV + cv;
+                T s = w == 0 ? __ldg(r) : T();
+                s = vadd(s, __ldg(r + (2 * w + 1) * CV));
+                s = vadd(s, __ldg(r + (2 * w + 2) * CV));
+                if (w == W - 1) s = vadd(s, __ldg(r + (2 * W + 1) * CV));
+                acc = vadd(acc, s);
+            }
+            dst[o] = acc;
+        }
+    }
+}
+
 static int glue_grid(int64_t rows) {
     int64_t g = (rows + kGlueWarps - 1) / kGlueWarps;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -140,17 +208,32 @@ relu_bn_stats_kernel(const float* __restrict__ z, BnShape d, double* __restrict_
     }
 }
 
+// one WARP per channel: lanes stride over the slices, fixed-order combination
+__device__ __forceinline__ double2 bn_channel_sum(const double* __restrict__ partial, int c, int cs, int ks,
+                                                   int slices) {
+    const int lane = threadIdx.x & 31;
+    double s = 0, q = 0;
+    for (int k = lane; k < slices; k += 32) {               // partial[c * cs + k * ks]: layout of the stats kernel
+        s += partial[((size_t)c * cs + (size_t)k * ks) * 2];
+        q += partial[((size_t)c * cs + (size_t)k * ks) * 2 + 1];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+    return make_double2(s, q);
+}
+
 __global__ void __launch_bounds__(128)
-relu_bn_finalize_kernel(BnShape d, const double* __restrict__ partial, float momentum, float eps,
+relu_bn_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ partial, float momentum, float eps,
                         float* running_mean, float* running_var, float* __restrict__ save_mean,
                         float* __restrict__ save_invstd) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (c >= d.C) return;
-    double s = 0, q = 0;
-    for (int k = 0; k < d.slices; ++k) {
-        s += partial[((size_t)c * d.slices + k) * 2];
-        q += partial[((size_t)c * d.slices + k) * 2 + 1];
-    }
+    const double2 t = bn_channel_sum(partial, c, cs, ks, d.slices);
+    if ((threadIdx.x & 31) != 0) return;
+    const double s = t.x, q = t.y;
     const double M = (double)d.N * (double)d.HW;
     const double mean = s / M;
     double var = q / M - mean * mean;
@@ -205,20 +288,17 @@ relu_bn_bwd_stats_kernel(const float* __restrict__ z, const float* __restrict__ 
 }
 
 __global__ void __launch_bounds__(128)
-relu_bn_bwd_finalize_kernel(BnShape d, const double* __restrict__ partial, float* __restrict__ grad_weight,
+relu_bn_bwd_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ partial, float* __restrict__ grad_weight,
                             float* __restrict__ grad_bias, float* __restrict__ coef /* [C][2]: mean(gy), mean(gy xhat) */) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (c >= d.C) return;
-    double s1 = 0, s2 = 0;
-    for (int k = 0; k < d.slices; ++k) {
-        s1 += partial[((size_t)c * d.slices + k) * 2];
-        s2 += partial[((size_t)c * d.slices + k) * 2 + 1];
-    }
+    const double2 t = bn_channel_sum(partial, c, cs, ks, d.slices);
+    if ((threadIdx.x & 31) != 0) return;
     const double M = (double)d.N * (double)d.HW;
-    if (grad_bias) grad_bias[c] = (float)s1;
-    if (grad_weight) grad_weight[c] = (float)s2;
-    coef[2 * c] = (float)(s1 / M);
-    coef[2 * c + 1] = (float)(s2 / M);
+    if (grad_bias) grad_bias[c] = (float)t.x;
+    if (grad_weight) grad_weight[c] = (float)t.y;
+    coef[2 * c] = (float)(t.x / M);
+    coef[2 * c + 1] = (float)(t.y / M);
 }
 
 __global__ void __launch_bounds__(kBnThreads)
@@ -243,6 +323,129 @@ relu_bn_bwd_apply_kernel(const float* __restrict__ z, const float* __restrict__ 
         [&](int64_t i) { gz[i] = one(z[i], gy[i]); });
 }
 
+// channels_last: the tensor is (M = N*HW rows) x C.  A thread owns 4 consecutive channels (C % 4 == 0)
+// and walks rows; 256 / (C/4) rows are in flight per CTA iteration (C <= 1024), a CTA takes a
+// contiguous chunk of rows; the threads that share a channel quad are combined through shared
+// memory.  Partials: [slices][C][2] fp64, slices = number of CTAs.
+struct BnRows { int64_t M; int C; int slices; int64_t rows_per_cta; };
+
+template <class Body>
+__device__ __forceinline__ void bn_rows_for_each(const BnRows& d, Body body) {
+    const int CV = d.C >> 2, rpi = 256 / CV;                 // rows per iteration
+    const int r0 = threadIdx.x / CV, cv = threadIdx.x - r0 * CV;
+    if (r0 >= rpi) return;
+    const int64_t beg = (int64_t)blockIdx.x * d.rows_per_cta;
+    const int64_t end = beg + d.rows_per_cta < d.M ? beg + d.rows_per_cta : d.M;
+    for (int64_t r = beg + r0; r < end; r += rpi) body((r * d.C >> 2) + cv);     // float4 index
+}
+
+// combine (a, b) float4 pairs of the threads sharing a channel quad; result valid where r0 == 0
+__device__ __forceinline__ void bn_rows_combine(const BnRows& d, float4& a, float4& b) {
+    __shared__ float4 sa[256], sb[256];
+    const int CV = d.C >> 2, rpi = 256 / CV;
+    const int r0 = threadIdx.x / CV, cv = threadIdx.x - r0 * CV;
+    sa[threadIdx.x] = a; sb[threadIdx.x] = b;
+    __syncthreads();
+    if (r0 == 0) {
+        for (int k = 1; k < rpi; ++k) {
+            const float4 u = sa[k * CV + cv], v = sb[k * CV + cv];
+            a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
+            b.x += v.x; b.y += v.y; b.z += v.z; b.w += v.w;
+        }
+    }
+}
+
+__device__ __forceinline__ void bn_rows_store(const BnRows& d, double* partial, const float4& a, const float4& b) {
+    const int CV = d.C >> 2;
+    if ((int)threadIdx.x >= CV) return;                      // r0 == 0 threads: cv = threadIdx.x
+    const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const size_t c = (size_t)threadIdx.x * 4 + k;
+        partial[((size_t)blockIdx.x * d.C + c) * 2] = av[k];         // [slice][channel]: coalesced finalize
+        partial[((size_t)blockIdx.x * d.C + c) * 2 + 1] = bv[k];
+    }
+}
+
+__device__ __forceinline__ float4 relu4(float4 v) {
+    return make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+}
+
+__global__ void __launch_bounds__(256)
+relu_bn_stats_nhwc_kernel(const float4* __restrict__ z, BnRows d, double* __restrict__ partial) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+    bn_rows_for_each(d, [&](int64_t i) {
+        const float4 v = relu4(z[i]);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        q.x += v.x * v.x; q.y += v.y * v.y; q.z += v.z * v.z; q.w += v.w * v.w;
+    });
+    bn_rows_combine(d, s, q);
+    bn_rows_store(d, partial, s, q);
+}
+
+__global__ void __launch_bounds__(256)
+relu_bn_apply_nhwc_kernel(const float4* __restrict__ z, BnRows d, const float* __restrict__ weight,
+                          const float* __restrict__ bias, const float* __restrict__ save_mean,
+                          const float* __restrict__ save_invstd, float4* __restrict__ y) {
+    const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    float mean[4], a[4], b[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int c = cv * 4 + k;
+        mean[k] = save_mean[c];
+        a[k] = save_invstd[c] * (weight ? weight[c] : 1.f);
+        b[k] = bias ? bias[c] : 0.f;
+    }
+    bn_rows_for_each(d, [&](int64_t i) {
+        const float4 v = relu4(__ldcs(z + i));
+        y[i] = make_float4((v.x - mean[0]) * a[0] + b[0], (v.y - mean[1]) * a[1] + b[1],
+                           (v.z - mean[2]) * a[2] + b[2], (v.w - mean[3]) * a[3] + b[3]);
+    });
+}
+
+__global__ void __launch_bounds__(256)
+relu_bn_bwd_stats_nhwc_kernel(const float4* __restrict__ z, const float4* __restrict__ gy, BnRows d,
+                              const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                              double* __restrict__ partial) {
+    const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    float mean[4], inv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { mean[k] = save_mean[cv * 4 + k]; inv[k] = save_invstd[cv * 4 + k]; }
+    float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
+    bn_rows_for_each(d, [&](int64_t i) {
+        const float4 v = relu4(z[i]), g = gy[i];
+        s1.x += g.x; s1.y += g.y; s1.z += g.z; s1.w += g.w;
+        s2.x += g.x * ((v.x - mean[0]) * inv[0]); s2.y += g.y * ((v.y - mean[1]) * inv[1]);
+        s2.z += g.z * ((v.z - mean[2]) * inv[2]); s2.w += g.w * ((v.w - mean[3]) * inv[3]);
+    });
+    bn_rows_combine(d, s1, s2);
+    bn_rows_store(d, partial, s1, s2);
+}
+
+__global__ void __launch_bounds__(256)
+relu_bn_bwd_apply_nhwc_kernel(const float4* __restrict__ z, const float4* __restrict__ gy, BnRows d,
+                              const float* __restrict__ weight, const float* __restrict__ save_mean,
+                              const float* __restrict__ save_invstd, const float* __restrict__ coef,
+                              float4* __restrict__ gz) {
+    const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    float mean[4], inv[4], k4[4], m1[4], m2[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int c = cv * 4 + k;
+        mean[k] = save_mean[c]; inv[k] = save_invstd[c];
+        k4[k] = inv[k] * (weight ? weight[c] : 1.f);
+        m1[k] = coef[2 * c]; m2[k] = coef[2 * c + 1];
+    }
+    auto one = [&](float zv, float g, int k) {
+        const float xhat = (fmaxf(zv, 0.f) - mean[k]) * inv[k];
+        return zv > 0.f ? k4[k] * (g - m1[k] - xhat * m2[k]) : 0.f;
+    };
+    bn_rows_for_each(d, [&](int64_t i) {
+        const float4 v = __ldcs(z + i), g = __ldcs(gy + i);
+        gz[i] = make_float4(one(v.x, g.x, 0), one(v.y, g.y, 1), one(v.z, g.z, 2), one(v.w, g.w, 3));
+    });
+}
+
 static int bn_slices(int64_t N, int C) {
     int64_t s = (8 * (int64_t)kNumSMs + C - 1) / C;
     s = s < 1 ? 1 : s;
@@ -253,30 +456,78 @@ static int bn_slices(int64_t N, int C) {
 
 using namespace dvsof;
 
-extern "C" int dvsof_upsample2x_reflect_pad_forward(const float* x, int64_t planes, int32_t H, int32_t W,
-                                                    float* y, void* stream) {
-    if (planes < 0 || H < 1 || W < 1 || (planes > 0 && (!x || !y)) || H > (1 << 28) || W > (1 << 28))
+static int nhwc_vec(int C, const void* a, const void* b) {
+    const bool al = aligned16(a) && aligned16(b);
+    return (C % 4 == 0 && al) ? 4 : ((C % 2 == 0 && al) ? 2 : 1);
+}
+static int row_grid(int64_t rows) {
+    const int64_t cap = (int64_t)kNumSMs * 16;
+    return (int)(rows < 1 ? 1 : (rows > cap ? cap : rows));
+}
+
+extern "C" int dvsof_upsample2x_reflect_pad_forward(const float* x, int64_t N, int32_t C, int32_t H, int32_t W,
+                                                    float* y, int32_t channels_last, void* stream_) {
+    if (N < 0 || C < 1 || H < 1 || W < 1 || (N > 0 && (!x || !y)) || H > (1 << 20) || W > (1 << 20) ||
+        (channels_last && (2 * (int64_t)W + 2) * C >= (1 << 21)))
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "upsample2x_reflect_pad_forward: bad arguments");
-    if (planes == 0) return DVSOF_OK;
-    upsample2x_reflect_pad_fwd_kernel<<<glue_grid(planes * (2 * (int64_t)H + 2)), kGlueWarps * 32, 0,
-                                        (cudaStream_t)stream>>>(x, y, planes, H, W);
-    return check_launch("upsample2x_reflect_pad_fwd_kernel");
+    if (N == 0) return DVSOF_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!channels_last) {
+        const int64_t planes = N * C;
+        upsample2x_reflect_pad_fwd_kernel<<<glue_grid(planes * (2 * (int64_t)H + 2)), kGlueWarps * 32, 0, stream>>>(
+            x, y, planes, H, W);
+    } else {
+        const int grid = row_grid(N * (2 * (int64_t)H + 2));
+        switch (nhwc_vec(C, x, y)) {
+            case 4: upsample2x_reflect_pad_fwd_nhwc_kernel<4><<<grid, 256, 0, stream>>>(x, y, N, C, H, W); break;
+            case 2: upsample2x_reflect_pad_fwd_nhwc_kernel<2><<<grid, 256, 0, stream>>>(x, y, N, C, H, W); break;
+            default: upsample2x_reflect_pad_fwd_nhwc_kernel<1><<<grid, 256, 0, stream>>>(x, y, N, C, H, W);
+        }
+    }
+    return check_launch("upsample2x_reflect_pad_fwd");
 }
 
-extern "C" int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t planes, int32_t H,
-                                                     int32_t W, float* grad_x, void* stream) {
-    if (planes < 0 || H < 1 || W < 1 || (planes > 0 && (!grad_y || !grad_x)) || H > (1 << 28) || W > (1 << 28))
+extern "C" int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t N, int32_t C, int32_t H,
+                                                     int32_t W, float* grad_x, int32_t channels_last,
+                                                     void* stream_) {
+    if (N < 0 || C < 1 || H < 1 || W < 1 || (N > 0 && (!grad_y || !grad_x)) || H > (1 << 20) || W > (1 << 20) ||
+        (channels_last && (2 * (int64_t)W + 2) * C >= (1 << 21)))
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "upsample2x_reflect_pad_backward: bad arguments");
-    if (planes == 0) return DVSOF_OK;
-    upsample2x_reflect_pad_bwd_kernel<<<glue_grid(planes * (int64_t)H), kGlueWarps * 32, 0,
-                                        (cudaStream_t)stream>>>(grad_y, grad_x, planes, H, W);
-    return check_launch("upsample2x_reflect_pad_bwd_kernel");
+    if (N == 0) return DVSOF_OK;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (!channels_last) {
+        const int64_t planes = N * C;
+        upsample2x_reflect_pad_bwd_kernel<<<glue_grid(planes * (int64_t)H), kGlueWarps * 32, 0, stream>>>(
+            grad_y, grad_x, planes, H, W);
+    } else {
+        const int grid = row_grid(N * (int64_t)H);
+        switch (nhwc_vec(C, grad_y, grad_x)) {
+            case 4: upsample2x_reflect_pad_bwd_nhwc_kernel<4><<<grid, 256, 0, stream>>>(grad_y, grad_x, N, C, H, W); break;
+            case 2: upsample2x_reflect_pad_bwd_nhwc_kernel<2><<<grid, 256, 0, stream>>>(grad_y, grad_x, N, C, H, W); break;
+            default: upsample2x_reflect_pad_bwd_nhwc_kernel<1><<<grid, 256, 0, stream>>>(grad_y, grad_x, N, C, H, W);
+        }
+    }
+    return check_launch("upsample2x_reflect_pad_bwd");
 }
 
-// workspace: partial sums [C][slices][2] fp64 | coefficients [C][2] fp32
-extern "C" size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C) {
-    if (N < 1 || C < 1) return 0;
-    return round_up((size_t)C * bn_slices(N, C) * 2 * sizeof(double), 256) + round_up((size_t)C * 2 * sizeof(float), 256);
+// workspace: partial sums [C x slices][2] fp64 | coefficients [C][2] fp32
+static BnRows bn_rows(int64_t N, int C, int64_t HW) {
+    BnRows d;
+    d.M = N * HW; d.C = C;
+    const int rpi = 256 / (C / 4);
+    int64_t s = (d.M + (int64_t)rpi * 8 - 1) / ((int64_t)rpi * 8);       // >= 8 iterations per CTA
+    s = s < 1 ? 1 : (s > 8 * kNumSMs ? 8 * kNumSMs : s);
+    d.rows_per_cta = (d.M + s - 1) / s;
+    d.rows_per_cta = (d.rows_per_cta + rpi - 1) / rpi * rpi;
+    d.slices = (int)((d.M + d.rows_per_cta - 1) / d.rows_per_cta);
+    return d;
+}
+static bool bn_nhwc_ok(int C) { return C % 4 == 0 && C >= 4 && C <= 1024; }
+
+extern "C" size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C, int64_t HW, int32_t channels_last) {
+    if (N < 1 || C < 1 || HW < 1 || (channels_last && !bn_nhwc_ok(C))) return 0;
+    const size_t slices = channels_last ? (size_t)bn_rows(N, C, HW).slices : (size_t)bn_slices(N, C);
+    return round_up((size_t)C * slices * 2 * sizeof(double), 256) + round_up((size_t)C * 2 * sizeof(float), 256);
 }
 
 static bool bn_args_ok(int64_t N, int32_t C, int64_t HW, const void* a, const void* b) {
@@ -287,16 +538,28 @@ static bool bn_args_ok(int64_t N, int32_t C, int64_t HW, const void* a, const vo
 extern "C" int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64_t HW, const float* weight,
                                      const float* bias, float* running_mean, float* running_var,
                                      float momentum, float eps, float* y, float* save_mean,
-                                     float* save_invstd, void* workspace, void* stream_) {
-    if (!bn_args_ok(N, C, HW, z, y) || !save_mean || !save_invstd || !workspace)
-        return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_forward: bad arguments (fp32 NCHW, 16-byte aligned)");
+                                     float* save_invstd, void* workspace, int32_t channels_last,
+                                     void* stream_) {
+    if (!bn_args_ok(N, C, HW, z, y) || !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_forward: bad arguments (fp32, 16-byte aligned; "
+                                                "channels_last needs C % 4 == 0, C <= 1024)");
     cudaStream_t stream = (cudaStream_t)stream_;
-    const BnShape d{N, C, HW, bn_slices(N, C)};
     double* partial = static_cast<double*>(workspace);
+    if (channels_last) {
+        const BnRows r = bn_rows(N, C, HW);
+        const BnShape d{N, C, HW, r.slices};
+        relu_bn_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(reinterpret_cast<const float4*>(z), r, partial);
+        relu_bn_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, 1, C, partial, momentum, eps, running_mean,
+                                                                   running_var, save_mean, save_invstd);
+        relu_bn_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(reinterpret_cast<const float4*>(z), r, weight, bias,
+                                                                save_mean, save_invstd, reinterpret_cast<float4*>(y));
+        return check_launch("relu_bn_forward(nhwc)");
+    }
+    const BnShape d{N, C, HW, bn_slices(N, C)};
     const dim3 grid((unsigned)d.slices, (unsigned)C);
     relu_bn_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, d, partial);
-    relu_bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(d, partial, momentum, eps, running_mean, running_var,
-                                                               save_mean, save_invstd);
+    relu_bn_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, d.slices, 1, partial, momentum, eps, running_mean,
+                                                               running_var, save_mean, save_invstd);
     relu_bn_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, d, weight, bias, save_mean, save_invstd, y);
     return check_launch("relu_bn_forward");
 }
@@ -304,18 +567,32 @@ extern "C" int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64
 extern "C" int dvsof_relu_bn_backward(const float* z, const float* grad_y, int64_t N, int32_t C, int64_t HW,
                                       const float* weight, const float* save_mean, const float* save_invstd,
                                       float* grad_z, float* grad_weight, float* grad_bias, void* workspace,
-                                      void* stream_) {
+                                      int32_t channels_last, void* stream_) {
     if (!bn_args_ok(N, C, HW, z, grad_y) || !grad_z || (reinterpret_cast<uintptr_t>(grad_z) & 15) != 0 ||
-        !save_mean || !save_invstd || !workspace)
-        return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_backward: bad arguments (fp32 NCHW, 16-byte aligned)");
+        !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_backward: bad arguments (fp32, 16-byte aligned; "
+                                                "channels_last needs C % 4 == 0, C <= 1024)");
     cudaStream_t stream = (cudaStream_t)stream_;
-    const BnShape d{N, C, HW, bn_slices(N, C)};
     double* partial = static_cast<double*>(workspace);
+    if (channels_last) {
+        const BnRows r = bn_rows(N, C, HW);
+        const BnShape d{N, C, HW, r.slices};
+        float* coef = reinterpret_cast<float*>(static_cast<char*>(workspace) +
+                                               round_up((size_t)C * r.slices * 2 * sizeof(double), 256));
+        const float4* z4 = reinterpret_cast<const float4*>(z);
+        const float4* g4 = reinterpret_cast<const float4*>(grad_y);
+        relu_bn_bwd_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, g4, r, save_mean, save_invstd, partial);
+        relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, 1, C, partial, grad_weight, grad_bias, coef);
+        relu_bn_bwd_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, g4, r, weight, save_mean, save_invstd, coef,
+                                                                    reinterpret_cast<float4*>(grad_z));
+        return check_launch("relu_bn_backward(nhwc)");
+    }
+    const BnShape d{N, C, HW, bn_slices(N, C)};
     float* coef = reinterpret_cast<float*>(static_cast<char*>(workspace) +
                                            round_up((size_t)C * d.slices * 2 * sizeof(double), 256));
     const dim3 grid((unsigned)d.slices, (unsigned)C);
     relu_bn_bwd_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, grad_y, d, save_mean, save_invstd, partial);
-    relu_bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(d, partial, grad_weight, grad_bias, coef);
+    relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, d.slices, 1, partial, grad_weight, grad_bias, coef);
     relu_bn_bwd_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, grad_y, d, weight, save_mean, save_invstd, coef, grad_z);
     return check_launch("relu_bn_backward");
 }

@@ -27,26 +27,28 @@ class _ReluBN(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, z, weight, bias, running_mean, running_var, momentum, eps):
-        z = z.contiguous()
+        z, cl = _layout(z)
         N, C = z.shape[0], z.shape[1]
+        if cl and (C % 4 or C > 1024):
+            z, cl = z.contiguous(), 0
         HW = z.numel() // max(N * C, 1)
         dev = z.device
         y = torch.empty_like(z)
         stats = torch.empty((2, C), dtype=torch.float32, device=dev)
-        lib = _lib.load()
-        ws = torch.empty(lib.dvsof_relu_bn_workspace_bytes(N, C), dtype=torch.uint8, device=dev)
+        ws = torch.empty(_lib.load().dvsof_relu_bn_workspace_bytes(N, C, HW, cl), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
             _lib.call('dvsof_relu_bn_forward', _lib.ptr(z), N, C, HW, _lib.ptr(weight), _lib.ptr(bias),
                       _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps), _lib.ptr(y),
-                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(ws), _lib.stream_ptr(dev))
+                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(ws), cl, _lib.stream_ptr(dev))
         ctx.save_for_backward(z, weight, stats)
-        ctx.ws = ws
+        ctx.ws, ctx.cl = ws, cl
         return y
 
     @staticmethod
     def backward(ctx, gy):
         z, weight, stats = ctx.saved_tensors
-        gy = gy.contiguous()
+        cl = ctx.cl
+        gy = gy.contiguous(memory_format=torch.channels_last) if cl else gy.contiguous()
         N, C = z.shape[0], z.shape[1]
         HW = z.numel() // max(N * C, 1)
         dev = z.device
@@ -55,7 +57,7 @@ class _ReluBN(torch.autograd.Function):
         with torch.cuda.device(dev):
             _lib.call('dvsof_relu_bn_backward', _lib.ptr(z), _lib.ptr(gy), N, C, HW, _lib.ptr(weight),
                       _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(gz), _lib.ptr(gwb[0]), _lib.ptr(gwb[1]),
-                      _lib.ptr(ctx.ws), _lib.stream_ptr(dev))
+                      _lib.ptr(ctx.ws), cl, _lib.stream_ptr(dev))
         return gz, gwb[0], gwb[1], None, None, None, None
 
 
@@ -82,8 +84,13 @@ class _ConvReluBN(nn.Module):
         nn.init.zeros_(self.conv.bias)
         nn.init.constant_(self.bn.weight, 0.1)
 
-    def forward(self, x):
-        return relu_batchnorm(self.conv(x), self.bn)
+    def forward(self, x, pad_in=0):
+        if pad_in:          # zero input channels appended by the caller: matching zero weight slices
+            w = F.pad(self.conv.weight, (0, 0, 0, 0, 0, pad_in)).contiguous(memory_format=torch.channels_last)
+            z = F.conv2d(x, w, self.conv.bias, self.conv.stride, self.conv.padding)
+        else:
+            z = self.conv(x)
+        return relu_batchnorm(z, self.bn)
 
 
 class _Down(nn.Module):
@@ -106,28 +113,43 @@ class _Residual(nn.Module):
         return x + self.body(x)
 
 
+def _layout(x):
+    """(tensor in a layout the kernels take, channels_last flag): a channels_last tensor stays as it
+    is (the kernels have (N, H, W, C) variants), anything else is made NCHW-contiguous."""
+    if x.dim() == 4 and x.shape[1] > 1 and x.is_contiguous(memory_format=torch.channels_last) \
+            and not x.is_contiguous():
+        return x, 1
+    return x.contiguous(), 0
+
+
+def _empty(shape, cl, dev):
+    return torch.empty(shape, dtype=torch.float32, device=dev,
+                       memory_format=torch.channels_last if cl else torch.contiguous_format)
+
+
 class _UpsamplePad(torch.autograd.Function):
     """`F.pad(F.interpolate(x, scale_factor=2), (1, 1, 1, 1), mode='reflect')` as one gather per
     direction (csrc/glue.cu): the 4x upsampled intermediate is never written."""
 
     @staticmethod
     def forward(ctx, x):
-        x = x.contiguous()
+        x, cl = _layout(x)
         N, C, H, W = x.shape
-        y = torch.empty((N, C, 2 * H + 2, 2 * W + 2), dtype=torch.float32, device=x.device)
+        y = _empty((N, C, 2 * H + 2, 2 * W + 2), cl, x.device)
         with torch.cuda.device(x.device):
-            _lib.call('dvsof_upsample2x_reflect_pad_forward', _lib.ptr(x), N * C, H, W, _lib.ptr(y),
+            _lib.call('dvsof_upsample2x_reflect_pad_forward', _lib.ptr(x), N, C, H, W, _lib.ptr(y), cl,
                       _lib.stream_ptr(x.device))
-        ctx.shape = (N, C, H, W)
+        ctx.shape, ctx.cl = (N, C, H, W), cl
         return y
 
     @staticmethod
     def backward(ctx, gy):
-        gy = gy.contiguous()
+        cl = ctx.cl
+        gy = gy.contiguous(memory_format=torch.channels_last) if cl else gy.contiguous()
         N, C, H, W = ctx.shape
-        gx = torch.empty(ctx.shape, dtype=torch.float32, device=gy.device)
+        gx = _empty(ctx.shape, cl, gy.device)
         with torch.cuda.device(gy.device):
-            _lib.call('dvsof_upsample2x_reflect_pad_backward', _lib.ptr(gy), N * C, H, W, _lib.ptr(gx),
+            _lib.call('dvsof_upsample2x_reflect_pad_backward', _lib.ptr(gy), N, C, H, W, _lib.ptr(gx), cl,
                       _lib.stream_ptr(gy.device))
         return gx
 
@@ -147,8 +169,19 @@ class _Up(nn.Module):
         super().__init__()
         self.block = _ConvReluBN(cin, cout)
 
-    def forward(self, x):
-        return self.block(upsample2x_reflect_pad(x))
+    def forward(self, parts):
+        """parts: the tensors whose channel concatenation is the block's input (net.py:246-262).  In
+        channels_last the concatenation is filled up with zero channels to a multiple of 8 (and the
+        weight with zero slices): 130 / 258 / 514 input channels otherwise make cuDNN copy every
+        operand into a padded buffer around each of its three kernels (3.8 ms per step)."""
+        first = parts[0]
+        cl = first.is_contiguous(memory_format=torch.channels_last) and not first.is_contiguous()
+        pad_in = (-sum(p.shape[1] for p in parts)) % 8 if cl else 0
+        if pad_in:
+            N, _, H, W = first.shape
+            parts = tuple(parts) + (torch.empty((N, pad_in, H, W), dtype=first.dtype, device=first.device,
+                                                memory_format=torch.channels_last).zero_(),)
+        return self.block(upsample2x_reflect_pad(torch.cat(parts, 1)), pad_in)
 
 
 class Model(nn.Module):
@@ -190,7 +223,7 @@ class Model(nn.Module):
                 feats[f'tr_{i}'] = h
         flows = []
         for i, (dec, head) in enumerate(zip(self.dec, self.flow)):
-            h = dec(torch.cat((h, skips[3 - i]), 1))
+            h = dec((h, skips[3 - i]))
             f = torch.tanh(head(h)) * 256.
             flows.append(f)
             h = torch.cat((h, f), 1)

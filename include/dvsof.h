@@ -263,29 +263,33 @@ int dvsof_scale_gradients(const dvsof_loss_scales_t* scales, const float* factor
  * Train-step glue (the network's convolutions stay on cuDNN).
  * ------------------------------------------------------------------------------------- */
 /* EV_FlowNet/net.py:72-85, the head of every decoder block: nearest x2 upsampling followed by
- * ReflectionPad2d(1), as one gather.  x [dev] (planes, H, W) fp32 contiguous (planes = N*C),
- * y [dev] (planes, 2H+2, 2W+2).  backward: grad_x = the adjoint, fixed summation order. */
-int dvsof_upsample2x_reflect_pad_forward(const float* x, int64_t planes, int32_t H, int32_t W,
-                                         float* y, void* stream);
-int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t planes, int32_t H, int32_t W,
-                                          float* grad_x, void* stream);
+ * ReflectionPad2d(1), as one gather.  x [dev] fp32: (N, C, H, W) contiguous, or (N, H, W, C) when
+ * channels_last != 0; y likewise with 2H+2, 2W+2.  backward: grad_x = the adjoint, fixed
+ * summation order. */
+int dvsof_upsample2x_reflect_pad_forward(const float* x, int64_t N, int32_t C, int32_t H, int32_t W,
+                                         float* y, int32_t channels_last, void* stream);
+int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t N, int32_t C, int32_t H,
+                                          int32_t W, float* grad_x, int32_t channels_last,
+                                          void* stream);
 
 /* EV_FlowNet/net.py:36,54, the tail of every conv block: ReLU followed by BatchNorm2d in training
  * mode (batch statistics over (N, H, W) of relu(z), biased variance; running statistics updated
  * with `momentum`, unbiased variance, either may be NULL), as stats + apply passes that spread a
- * channel over many CTAs.  z, y, grad_* [dev] (N, C, HW) fp32 contiguous, 16-byte aligned;
- * weight / bias [dev] C floats or NULL; save_mean / save_invstd [dev] C floats (kept for backward).
- * backward: grad_z = d/dz, grad_weight / grad_bias [dev] C floats (or NULL).  Deterministic.
- * workspace: dvsof_relu_bn_workspace_bytes(N, C). */
-size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C);
+ * channel over many CTAs.  z, y, grad_* [dev] fp32, 16-byte aligned: (N, C, HW) contiguous, or
+ * (N, HW, C) when channels_last != 0; weight / bias [dev] C floats or NULL; save_mean /
+ * save_invstd [dev] C floats (kept for backward).  backward: grad_z = d/dz, grad_weight /
+ * grad_bias [dev] C floats (or NULL).  Deterministic.
+ * workspace: dvsof_relu_bn_workspace_bytes(N, C, HW, channels_last)  (channels_last: C % 4 == 0,
+ * C <= 1024, else 0). */
+size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C, int64_t HW, int32_t channels_last);
 int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64_t HW, const float* weight,
                           const float* bias, float* running_mean, float* running_var, float momentum,
                           float eps, float* y, float* save_mean, float* save_invstd, void* workspace,
-                          void* stream);
+                          int32_t channels_last, void* stream);
 int dvsof_relu_bn_backward(const float* z, const float* grad_y, int64_t N, int32_t C, int64_t HW,
                            const float* weight, const float* save_mean, const float* save_invstd,
                            float* grad_z, float* grad_weight, float* grad_bias, void* workspace,
-                           void* stream);
+                           int32_t channels_last, void* stream);
 
 #ifdef __cplusplus
 }

@@ -47,7 +47,7 @@ def main():
     torch.cuda.synchronize()
     print('step_ms', e0.elapsed_time(e1) / 5)
     from torch.profiler import ProfilerActivity, profile
-    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+    with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA], record_shapes=True) as prof:
         for _ in range(3):
             step()
         torch.cuda.synchronize()
@@ -55,6 +55,11 @@ def main():
     tot = sum(k.device_time_total for k in ka if k.device_type == torch.autograd.DeviceType.CUDA)
     print('cuda kernel time per step (ms):', tot / 3 / 1000)
     print(ka.table(sort_by='device_time_total', row_limit=45, max_name_column_width=70))
+    by_shape = prof.key_averages(group_by_input_shape=True)
+    rows = [k for k in by_shape if k.key in ('aten::copy_', 'aten::contiguous', 'aten::clone', 'aten::constant_pad_nd', 'aten::cat')]
+    rows.sort(key=lambda k: -k.device_time_total)
+    for k in rows[:25]:
+        print('SHAPE', k.key, round(k.device_time_total / 3000, 3), 'ms/step', k.count // 3, 'calls/step', k.input_shapes)
 
 
 if __name__ == '__main__':

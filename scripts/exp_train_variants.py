@@ -55,7 +55,7 @@ def main():
     import dvs_of_training_framework_b200 as dv
     dv._lib.Status.mode = 'deferred'
     res = {}
-    for fmt in ('nchw', 'nhwc'):
+    for fmt in ('nchw', 'nhwc', 'nhwc_in'):
         for bm in (False,):
             ms, loss = run(fmt, bm)
             res[f'{fmt}{"+benchmark" if bm else ""}'] = {'step_ms': round(ms, 2), 'loss': loss}

@@ -11,11 +11,17 @@ def _ref(x):
 @pytest.mark.gpu
 @pytest.mark.parametrize('shape', [(2, 3, 1, 1), (1, 2, 1, 5), (2, 5, 4, 1), (3, 7, 16, 20), (2, 130, 33, 47),
                                    (1, 1, 128, 128)])
-def test_upsample_reflect_pad_matches_aten(shape):
+@pytest.mark.parametrize('channels_last', [False, True])
+def test_upsample_reflect_pad_matches_aten(shape, channels_last):
     from dvs_of_training_framework_b200.evflownet import upsample2x_reflect_pad
     g = torch.Generator(device='cuda').manual_seed(sum(shape))
-    x = torch.randn(shape, generator=g, device='cuda', requires_grad=True)
+    x = torch.randn(shape, generator=g, device='cuda')
+    if channels_last:
+        x = x.contiguous(memory_format=torch.channels_last)
+    x.requires_grad_()
     y = upsample2x_reflect_pad(x)
+    if channels_last and not x.is_contiguous():          # 1x1 planes are both layouts at once
+        assert y.is_contiguous(memory_format=torch.channels_last)
     xr = x.detach().clone().requires_grad_()
     yr = _ref(xr)
     assert y.shape == yr.shape and torch.equal(y, yr)                 # a gather: exact
@@ -46,9 +52,10 @@ def test_upsample_reflect_pad_non_contiguous_input_and_determinism():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize('shape', [(4, 3, 5, 7), (32, 32, 64, 64), (2, 512, 16, 16), (1, 8, 1, 2), (3, 5, 8, 8),
+@pytest.mark.parametrize('shape', [(4, 3, 5, 7), (32, 32, 64, 64), (2, 512, 16, 16), (1, 8, 1, 2), (3, 5, 8, 8), (5, 96, 9, 7),
                                    (8, 130, 20, 12)])
-def test_relu_batchnorm_matches_aten(shape):
+@pytest.mark.parametrize('channels_last', [False, True])
+def test_relu_batchnorm_matches_aten(shape, channels_last):
     from torch import nn
     from dvs_of_training_framework_b200.evflownet import relu_batchnorm
     g = torch.Generator(device='cuda').manual_seed(sum(shape))
@@ -61,7 +68,10 @@ def test_relu_batchnorm_matches_aten(shape):
         bn.running_mean.copy_(torch.randn(C, generator=g, device='cuda'))
         bn.running_var.copy_(torch.rand(C, generator=g, device='cuda') + 0.5)
     ref.load_state_dict(bn.state_dict())
-    z = torch.randn(shape, generator=g, device='cuda', requires_grad=True)
+    z = torch.randn(shape, generator=g, device='cuda')
+    if channels_last:
+        z = z.contiguous(memory_format=torch.channels_last)
+    z.requires_grad_()
     zr = z.detach().clone().requires_grad_()
     y = relu_batchnorm(z, bn)
     yr = ref(torch.relu(zr))
