@@ -349,7 +349,23 @@ def make_train_batch(B, H, W, n, T, seed):
             'images': pin(images), 'augmentation_params': None, 'size': B}
 
 
-def bench_train_step(K, W, dev, world, per_gpu=32):
+def encode_host_batch(batch):
+    """The storage form of a collated host batch (utils/dataset.py:240-305 `encode_batch`, what
+    scripts/prepare_batches.py writes and PreprocessedDataloader reads), in pinned memory."""
+    ev = batch['events']
+    B = int(batch['size'])
+    per = batch['timestamps'].numel() // B
+    pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
+    counts = torch.bincount(ev['sample_index'], minlength=B)           # one element per sample here
+    return {'events': {'x': pin(ev['x'].to(torch.int16)), 'y': pin(ev['y'].to(torch.int16)),
+                       'timestamp': pin(ev['timestamp']), 'polarity': pin(ev['polarity'] > 0),
+                       'events_per_element': pin(counts)},
+            'elements_per_sample': pin(torch.full((B,), per - 1, dtype=torch.uint8)),
+            'timestamps': pin(batch['timestamps']), 'images': pin(batch['images'].to(torch.uint8)),
+            'augmentation_params': None}
+
+
+def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
     """EV-FlowNet data-parallel training step (BASELINE configs[4] shapes: 256x256, 131072
     events/sample; `per_gpu` samples per GPU => global batch 256 at 8 GPUs): H2D of the shard,
     encode, cuDNN forward, fused loss, backward with overlapped NCCL allreduce, AdamW step."""
@@ -369,6 +385,8 @@ def bench_train_step(K, W, dev, world, per_gpu=32):
     opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)      # train_flownet.py:59-61
     evaluator = dv.init_losses((c['H'], c['W']), per_gpu, model, dev, 1)
     batch = make_train_batch(per_gpu, c['H'], c['W'], c['n'], c['T'], 1234 + 5 + rank)
+    if encoded:             # 9 B/event + uint8 images cross PCIe, dataset.decode_batch expands on device
+        batch = encode_host_batch(batch)
     timers = dv.timer.FakeTimer()
     model.train()
     # every step uploads its batch from pinned host memory; the upload of step k+1 runs on a copy
@@ -588,6 +606,10 @@ def main():
         train = bench_train_step(max(3, min(K, 10)), 3, dev, world)
         train['step_ms'] = max_over_ranks(train['step_ms'])
         torch.cuda.empty_cache()
+        sync_all()
+        train_enc = bench_train_step(max(3, min(K, 10)), 3, dev, world, encoded=True)
+        train['encoded_step_ms'] = max_over_ranks(train_enc['step_ms'])
+        torch.cuda.empty_cache()
     sync_all()
     extra = {}
     if not args.quick:
@@ -649,7 +671,10 @@ def main():
                               'unit': 'samples/s', 'ms_per_step': train['step_ms'],
                               'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN convolutions; upsample+reflect-pad and ReLU+BatchNorm through libdvsof), 256x256, 131072 events/sample, '
                                           f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad), '
-                                          'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward'}
+                                          'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward',
+                              'storage_form_feed': {'value': world * train['samples'] / (train['encoded_step_ms'] * 1e-3), 'unit': 'samples/s',
+                                                    'ms_per_step': train['encoded_step_ms'],
+                                                    'note': 'the same step fed with batches in the storage form of utils/dataset.py encode_batch (9 B/event, uint8 images) and dataset.decode_batch on the device: a quarter of the upload'}}
     for name, r in extra.items():
         if name.endswith('_loss'):
             line['workloads'][name] = {'samples_per_s': world * r['samples'] / (r['abi_ms'] * 1e-3),

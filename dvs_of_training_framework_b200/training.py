@@ -91,6 +91,37 @@ def shard_batch(batch, rank, world):
     return out
 
 
+def shard_encoded_batch(batch, rank, world):
+    """The same partition for a batch in the storage form of utils/dataset.py:240-305 (what
+    `PreprocessedDataloader` reads from disk): this rank's samples, found from the run lengths
+    (cf. select_encoded_ranges, utils/dataset.py:67-115).  Host tensors; a few tiny prefix sums."""
+    if world == 1:
+        return batch
+    eps = batch['elements_per_sample'].to(torch.int64)
+    B = eps.numel()
+    lo, hi = shard_bounds(B, rank, world)
+    elem = torch.zeros(B + 1, dtype=torch.int64)
+    torch.cumsum(eps, 0, out=elem[1:])
+    ev = batch['events']
+    epe = ev['events_per_element'].to(torch.int64)
+    E = epe.numel()                                   # trailing empty elements may be missing (:298)
+    el0, el1 = min(int(elem[lo]), E), min(int(elem[hi]), E)
+    evb = torch.zeros(E + 1, dtype=torch.int64)
+    torch.cumsum(epe, 0, out=evb[1:])
+    e0, e1 = int(evb[el0]), int(evb[el1])
+    img0, img1 = int(elem[lo]) + lo, int(elem[hi]) + hi      # a sample has elements + 1 images
+    out = dict(batch)
+    out['elements_per_sample'] = batch['elements_per_sample'][lo:hi]
+    out['timestamps'] = batch['timestamps'][img0:img1]
+    out['images'] = batch['images'][img0:img1]
+    sh = {k: ev[k][e0:e1] for k in ('x', 'y', 'timestamp', 'polarity')}
+    sh['events_per_element'] = ev['events_per_element'][el0:el1]
+    out['events'] = sh
+    if isinstance(batch.get('augmentation_params'), dict):
+        out['augmentation_params'] = {k: v[lo:hi] for k, v in batch['augmentation_params'].items()}
+    return out
+
+
 class GradientAllreducer:
     """Flat-bucket gradient averaging for the data-parallel step.
 
@@ -202,9 +233,28 @@ class DevicePrefetcher:
         self.rank, self.world = rank, world
         self.stream = torch.cuda.Stream(self.device) if self.device.type == 'cuda' else None
 
+    def _stage_encoded(self, batch):
+        """A batch in the storage form (utils/dataset.py:240-305; 9 B/event, uint8 images): upload
+        that and expand it on the device (`dataset.decode_batch`) -- a quarter of the bytes of the
+        int64 training form cross PCIe.  Device only (libdvsof has no CPU path)."""
+        from . import dataset
+        local = shard_encoded_batch(batch, self.rank, self.world)
+
+        def up(v):
+            return v.to(self.device, non_blocking=True) if isinstance(v, torch.Tensor) else v
+        with torch.cuda.stream(self.stream):
+            dev = {k: ({kk: up(vv) for kk, vv in v.items()} if isinstance(v, dict) else up(v))
+                   for k, v in local.items()}
+            out = dataset.decode_batch(dev)
+        out['global_size'] = batch['elements_per_sample'].numel()
+        out['global_events'] = batch['events']['x'].numel()
+        return out
+
     def _stage(self, batch):
         if batch is None:
             return None
+        if 'elements_per_sample' in batch:
+            return self._stage_encoded(batch)
         local = dict(shard_batch(batch, self.rank, self.world))
         local['global_size'] = batch['size']                     # what the reference's counters see
         local['global_events'] = batch['events']['x'].numel() if self.is_raw else 0

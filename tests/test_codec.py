@@ -165,3 +165,67 @@ def test_compact_encoder_equals_decode_then_encode_image():
     c = _cuda(enc)
     b = dv.compute_event_image_compact(c['x'], c['y'], c['timestamp'], c['polarity'], c['events_per_element'], ts, (H, W))
     assert torch.equal(a, b)
+
+
+def _encoded_host_batch(seed, n_samples, n_events):
+    enc, eps = _big(seed, n_samples, n_events)
+    n_img = int(eps.astype(np.int64).sum()) + n_samples
+    g = np.random.default_rng(seed)
+    return {'events': {k: torch.from_numpy(v) for k, v in enc.items()},
+            'elements_per_sample': torch.from_numpy(eps),
+            'timestamps': torch.from_numpy(g.random(n_img).astype(np.float32)),
+            'images': torch.from_numpy(g.integers(0, 256, (n_img, 1, 4, 6)).astype(np.uint8)),
+            'augmentation_params': None}
+
+
+@pytest.mark.parametrize('world', [2, 3])
+def test_shard_encoded_batch_equals_shard_of_decoded(world):
+    """Host logic of the storage-form feed: sharding the encoded batch and decoding the shard gives
+    what sharding the decoded batch gives (training.shard_batch)."""
+    from dvs_of_training_framework_b200 import training as tr
+    batch = _encoded_host_batch(11, 5, 3000)
+    eps = batch['elements_per_sample'].numpy()
+    e = {k: v.numpy() for k, v in batch['events'].items()}
+    full = eo.decode_events(e['x'], e['y'], e['polarity'], e['timestamp'], e['events_per_element'], eps)
+    decoded = {'events': {k: torch.from_numpy(v) for k, v in full.items()},
+               'timestamps': batch['timestamps'], 'images': batch['images'], 'size': 5,
+               'sample_idx': torch.from_numpy(np.repeat(np.arange(5), eps.astype(np.int64) + 1)),
+               'augmentation_params': None}
+    total = 0
+    for rank in range(world):
+        lo, hi = tr.shard_bounds(5, rank, world)
+        sh = tr.shard_encoded_batch(batch, rank, world)
+        se = {k: v.numpy() for k, v in sh['events'].items()}
+        got = eo.decode_events(se['x'], se['y'], se['polarity'], se['timestamp'], se['events_per_element'],
+                               sh['elements_per_sample'].numpy())
+        sel = (full['sample_index'] >= lo) & (full['sample_index'] < hi)
+        for k in DEC_KEYS:
+            want = full[k][sel] - (lo if k == 'sample_index' else 0)
+            assert np.array_equal(got[k], want), (rank, k)
+        img = (decoded['sample_idx'] >= lo) & (decoded['sample_idx'] < hi)
+        assert torch.equal(sh['images'], batch['images'][img]) and torch.equal(sh['timestamps'], batch['timestamps'][img])
+        total += got['x'].size
+    assert total == full['x'].size
+
+
+@pytest.mark.gpu
+def test_prefetcher_accepts_encoded_batches():
+    """DevicePrefetcher on storage-form host batches yields the decoded training form on device."""
+    from dvs_of_training_framework_b200 import training as tr
+    batch = _encoded_host_batch(12, 4, 5000)
+    eps = batch['elements_per_sample'].numpy()
+    e = {k: v.numpy() for k, v in batch['events'].items()}
+    full = eo.decode_events(e['x'], e['y'], e['polarity'], e['timestamp'], e['events_per_element'], eps)
+    got = list(tr.DevicePrefetcher([batch, batch], 'cuda', True))
+    assert len(got) == 2
+    for b in got:
+        assert b['size'] == 4 and b['global_size'] == 4 and b['global_events'] == full['x'].size
+        assert b['images'].dtype == torch.float32 and b['images'].is_cuda
+        assert torch.equal(b['images'].cpu(), batch['images'].float())
+        assert b['sample_idx'].cpu().tolist() == np.repeat(np.arange(4), eps.astype(np.int64) + 1).tolist()
+        for k in DEC_KEYS:
+            assert np.array_equal(b['events'][k].cpu().numpy(), full[k]), k
+    sh = list(tr.DevicePrefetcher([batch], 'cuda', True, rank=1, world=2))[0]
+    sel = full['sample_index'] >= 2
+    assert sh['size'] == 2 and np.array_equal(sh['events']['x'].cpu().numpy(), full['x'][sel])
+    assert np.array_equal(sh['events']['sample_index'].cpu().numpy(), full['sample_index'][sel] - 2)
