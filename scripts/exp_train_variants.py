@@ -10,7 +10,7 @@ sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import bench  # noqa: E402
 
 
-def run(fmt, benchmark, per_gpu=32, steps=8):
+def run(fmt, benchmark, per_gpu=32, steps=8, fused_opt=False):
     import dvs_of_training_framework_b200 as dv
     from dvs_of_training_framework_b200 import training as tr
     from dvs_of_training_framework_b200.evflownet import Model
@@ -25,7 +25,7 @@ def run(fmt, benchmark, per_gpu=32, steps=8):
         q = model.quantize
         model.quantize = lambda *a: q(*a).contiguous(memory_format=torch.channels_last)
     red = tr.GradientAllreducer(model.parameters())
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True, fused=fused_opt)
     evaluator = dv.init_losses((c['H'], c['W']), per_gpu, model, dev, 1)
     batch = bench.make_train_batch(per_gpu, c['H'], c['W'], c['n'], c['T'], 1239)
     timers = dv.timer.FakeTimer()
@@ -55,11 +55,10 @@ def main():
     import dvs_of_training_framework_b200 as dv
     dv._lib.Status.mode = 'deferred'
     res = {}
-    for fmt in ('nchw', 'nhwc', 'nhwc_in'):
-        for bm in (False,):
-            ms, loss = run(fmt, bm)
-            res[f'{fmt}{"+benchmark" if bm else ""}'] = {'step_ms': round(ms, 2), 'loss': loss}
-            torch.cuda.empty_cache()
+    for fmt, bm, fo in (('nhwc', False, False), ('nhwc', True, False)):
+        ms, loss = run(fmt, bm, fused_opt=fo)
+        res[f'{fmt}{"+benchmark" if bm else ""}{"+fused_adamw" if fo else ""}'] = {'step_ms': round(ms, 2), 'loss': loss}
+        torch.cuda.empty_cache()
     print(json.dumps(res))
 
 
