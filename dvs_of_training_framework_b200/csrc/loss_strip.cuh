@@ -33,7 +33,10 @@ namespace dvsof {
 #ifndef DVSOF_LOSS_MIN_CTAS
 #define DVSOF_LOSS_MIN_CTAS 7
 #endif
-constexpr int kSR = 8;                    // rows per warp strip
+#ifndef DVSOF_LOSS_STRIP_ROWS
+#define DVSOF_LOSS_STRIP_ROWS 8
+#endif
+constexpr int kSR = DVSOF_LOSS_STRIP_ROWS;  // rows per warp strip
 constexpr int kGroup = DVSOF_LOSS_GROUP;  // rows whose taps are in flight together
 constexpr int kSWarps = kTile / kSR;      // 4 warps per CTA
 constexpr int kSThreads = 32 * kSWarps;   // 128
