@@ -205,13 +205,15 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
     __shared__ double dred[kVal ? kSWarps : 1][7];
     __shared__ bool is_last;
     pdl_launch_dependents();
-    pdl_wait();                       // pyramid levels, match_idx, n_bad come from preceding kernels
     const TileCoord tc = decode_cta_fast(tab, blockIdx.x);
     const int S = tab.n_scales, P = tab.n_pred;
     const int H = tab.H[tc.s], W = tab.W[tc.s];
     const int plane = H * W;
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    // the flow is an input of the call: its tile is staged while the prelude (pyramid levels,
+    // match_idx, tile counts, tickets) may still be running
     stage_flow_strip_tile(F, flow, plane, H, W, tc.y0, tc.x0);
+    pdl_wait();
 
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform
