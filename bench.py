@@ -382,7 +382,9 @@ def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
     model = Model(dev).to(memory_format=torch.channels_last)
     red = tr.GradientAllreducer(model.parameters())
     red.broadcast_parameters(model)
-    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True)      # train_flownet.py:59-61
+    # train_flownet.py:59-61; torch's single-kernel implementation of the same optimizer (the
+    # gradient views carry the parameters' strides, training.GradientAllreducer)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True, fused=True)
     evaluator = dv.init_losses((c['H'], c['W']), per_gpu, model, dev, 1)
     batch = make_train_batch(per_gpu, c['H'], c['W'], c['n'], c['T'], 1234 + 5 + rank)
     if encoded:             # 9 B/event + uint8 images cross PCIe, dataset.decode_batch expands on device
@@ -670,7 +672,7 @@ def main():
         line['train_step'] = {'metric': 'train-step samples/s', 'value': world * train['samples'] / (train['step_ms'] * 1e-3),
                               'unit': 'samples/s', 'ms_per_step': train['step_ms'],
                               'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN convolutions; upsample+reflect-pad and ReLU+BatchNorm through libdvsof), 256x256, 131072 events/sample, '
-                                          f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad), '
+                                          f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad, fused), '
                                           'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward',
                               'storage_form_feed': {'value': world * train['samples'] / (train['encoded_step_ms'] * 1e-3), 'unit': 'samples/s',
                                                     'ms_per_step': train['encoded_step_ms'],

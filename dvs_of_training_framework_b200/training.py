@@ -153,7 +153,12 @@ class GradientAllreducer:
         flat = torch.zeros(n, dtype=plist[0].dtype, device=plist[0].device)
         idx, off = len(self.buckets), 0
         for p in plist:
-            p.grad = flat[off:off + p.numel()].view_as(p)
+            piece = flat[off:off + p.numel()]
+            # the view has the parameter's own strides (channels_last weights stay channels_last):
+            # autograd's gradient layout contract holds, nothing is re-laid out when the gradient
+            # is accumulated, and fused optimizers accept the pair
+            dense = p.is_contiguous() or (p.dim() == 4 and p.is_contiguous(memory_format=torch.channels_last))
+            p.grad = piece.as_strided(p.size(), p.stride()) if dense else piece.view_as(p)
             self.where[p] = idx
             off += p.numel()
         self.buckets.append({'flat': flat, 'params': plist, 'pending': len(plist)})
