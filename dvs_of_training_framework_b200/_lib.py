@@ -80,12 +80,12 @@ _SIGNATURES = {
     'dvsof_upsample2x_reflect_pad_backward': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                                         C.c_void_p, C.c_int32, C.c_void_p]),
     'dvsof_relu_bn_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int32, C.c_int64, C.c_int32]),
-    'dvsof_relu_bn_forward': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p,
-                                        C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p, C.c_void_p,
-                                        C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
-    'dvsof_relu_bn_backward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
+    'dvsof_relu_bn_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    'dvsof_relu_bn_backward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                         C.c_int32, C.c_void_p]),
+                                         C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
     'dvsof_window_offsets': (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_int64,
                                        C.c_void_p, C.c_void_p]),
     'dvsof_flow_error_workspace_bytes': (C.c_size_t, []),

@@ -158,24 +158,31 @@ static int glue_grid(int64_t rows) {
 //   gz = [z > 0] * gamma * invstd * (gy - mean(gy) - xhat * mean(gy * xhat))
 // ---------------------------------------------------------------------------------------
 constexpr int kBnThreads = 256;
+constexpr int kFwdSums = 2;       // sum x, sum x^2                       (x = relu(z + conv_bias))
+constexpr int kBwdSums = 5;       // sum gy, sum gy*xhat; over x > 0: sum gy, count, sum xhat
 
 struct BnShape { int64_t N; int C; int64_t HW; int slices; };
 
-__device__ __forceinline__ double2 bn_block_sum(float a, float b) {
-    __shared__ double sa[kBnThreads / 32], sb[kBnThreads / 32];
-    double da = a, db = b;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        da += __shfl_xor_sync(0xffffffffu, da, o);
-        db += __shfl_xor_sync(0xffffffffu, db, o);
-    }
+// CTA-wide sums of K per-thread values, fp64 from the warp level up; result valid in thread 0
+template <int K>
+__device__ __forceinline__ void bn_block_sum(const float (&v)[K], double (&out)[K]) {
+    __shared__ double sm[K][kBnThreads / 32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (lane == 0) { sa[warp] = da; sb[warp] = db; }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        double d = v[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        if (lane == 0) sm[k][warp] = d;
+    }
     __syncthreads();
-    double ta = 0, tb = 0;
     if (threadIdx.x == 0)
-        for (int w = 0; w < kBnThreads / 32; ++w) { ta += sa[w]; tb += sb[w]; }
-    return make_double2(ta, tb);                           // valid in thread 0
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            double t = 0;
+            for (int w = 0; w < kBnThreads / 32; ++w) t += sm[k][w];
+            out[k] = t;
+        }
 }
 
 // visit the planes (n, c), n = slice, slice + slices, ... ; f(value index in the tensor, count 1 or 4)
@@ -189,40 +196,43 @@ __device__ __forceinline__ void bn_for_each(const BnShape& d, int c, int slice, 
     }
 }
 
+__device__ __forceinline__ float relu_b(float z, float cb) { return fmaxf(z + cb, 0.f); }
+
 __global__ void __launch_bounds__(kBnThreads)
-relu_bn_stats_kernel(const float* __restrict__ z, BnShape d, double* __restrict__ partial) {
+relu_bn_stats_kernel(const float* __restrict__ z, const float* __restrict__ conv_bias, BnShape d,
+                     double* __restrict__ partial) {
     const int c = blockIdx.y, slice = blockIdx.x;
-    float s = 0.f, q = 0.f;
+    const float cb = conv_bias ? conv_bias[c] : 0.f;
+    float v[kFwdSums] = {0.f, 0.f};
     bn_for_each(d, c, slice,
         [&](int64_t i) {
-            const float4 v = *reinterpret_cast<const float4*>(z + i);
-            const float a = fmaxf(v.x, 0.f), b = fmaxf(v.y, 0.f), e = fmaxf(v.z, 0.f), f = fmaxf(v.w, 0.f);
-            s += (a + b) + (e + f);
-            q += (a * a + b * b) + (e * e + f * f);
+            const float4 q = *reinterpret_cast<const float4*>(z + i);
+            const float a = relu_b(q.x, cb), b = relu_b(q.y, cb), e = relu_b(q.z, cb), f = relu_b(q.w, cb);
+            v[0] += (a + b) + (e + f);
+            v[1] += (a * a + b * b) + (e * e + f * f);
         },
-        [&](int64_t i) { const float a = fmaxf(z[i], 0.f); s += a; q += a * a; });
-    const double2 t = bn_block_sum(s, q);
-    if (threadIdx.x == 0) {
-        partial[((size_t)c * d.slices + slice) * 2] = t.x;
-        partial[((size_t)c * d.slices + slice) * 2 + 1] = t.y;
-    }
+        [&](int64_t i) { const float a = relu_b(z[i], cb); v[0] += a; v[1] += a * a; });
+    double t[kFwdSums];
+    bn_block_sum(v, t);
+    if (threadIdx.x == 0)
+        for (int k = 0; k < kFwdSums; ++k) partial[((size_t)c * d.slices + slice) * kFwdSums + k] = t[k];
 }
 
-// one WARP per channel: lanes stride over the slices, fixed-order combination
-__device__ __forceinline__ double2 bn_channel_sum(const double* __restrict__ partial, int c, int cs, int ks,
-                                                   int slices) {
+// one WARP per channel: lanes stride over the slices, fixed-order combination.
+// partial[(c * cs + k * ks) * K + j]: cs, ks = layout of the stats kernel
+template <int K>
+__device__ __forceinline__ void bn_channel_sum(const double* __restrict__ partial, int c, int cs, int ks,
+                                               int slices, double (&out)[K]) {
     const int lane = threadIdx.x & 31;
-    double s = 0, q = 0;
-    for (int k = lane; k < slices; k += 32) {               // partial[c * cs + k * ks]: layout of the stats kernel
-        s += partial[((size_t)c * cs + (size_t)k * ks) * 2];
-        q += partial[((size_t)c * cs + (size_t)k * ks) * 2 + 1];
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s += __shfl_xor_sync(0xffffffffu, s, o);
-        q += __shfl_xor_sync(0xffffffffu, q, o);
-    }
-    return make_double2(s, q);
+    for (int j = 0; j < K; ++j) out[j] = 0;
+    for (int k = lane; k < slices; k += 32)
+#pragma unroll
+        for (int j = 0; j < K; ++j) out[j] += partial[((size_t)c * cs + (size_t)k * ks) * K + j];
+#pragma unroll
+    for (int j = 0; j < K; ++j)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) out[j] += __shfl_xor_sync(0xffffffffu, out[j], o);
 }
 
 __global__ void __launch_bounds__(128)
@@ -231,12 +241,12 @@ relu_bn_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ pa
                         float* __restrict__ save_invstd) {
     const int c = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (c >= d.C) return;
-    const double2 t = bn_channel_sum(partial, c, cs, ks, d.slices);
+    double t[kFwdSums];
+    bn_channel_sum(partial, c, cs, ks, d.slices, t);
     if ((threadIdx.x & 31) != 0) return;
-    const double s = t.x, q = t.y;
     const double M = (double)d.N * (double)d.HW;
-    const double mean = s / M;
-    double var = q / M - mean * mean;
+    const double mean = t[0] / M;
+    double var = t[1] / M - mean * mean;
     var = var > 0 ? var : 0;
     save_mean[c] = (float)mean;
     save_invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
@@ -248,70 +258,93 @@ relu_bn_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ pa
 }
 
 __global__ void __launch_bounds__(kBnThreads)
-relu_bn_apply_kernel(const float* __restrict__ z, BnShape d, const float* __restrict__ weight,
-                     const float* __restrict__ bias, const float* __restrict__ save_mean,
-                     const float* __restrict__ save_invstd, float* __restrict__ y) {
+relu_bn_apply_kernel(const float* __restrict__ z, const float* __restrict__ conv_bias, BnShape d,
+                     const float* __restrict__ weight, const float* __restrict__ bias,
+                     const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                     float* __restrict__ y) {
     const int c = blockIdx.y, slice = blockIdx.x;
+    const float cb = conv_bias ? conv_bias[c] : 0.f;
     const float mean = save_mean[c];
     const float a = save_invstd[c] * (weight ? weight[c] : 1.f), b = bias ? bias[c] : 0.f;
     bn_for_each(d, c, slice,
         [&](int64_t i) {
             const float4 v = __ldcs(reinterpret_cast<const float4*>(z + i));
             float4 o;
-            o.x = (fmaxf(v.x, 0.f) - mean) * a + b; o.y = (fmaxf(v.y, 0.f) - mean) * a + b;
-            o.z = (fmaxf(v.z, 0.f) - mean) * a + b; o.w = (fmaxf(v.w, 0.f) - mean) * a + b;
+            o.x = (relu_b(v.x, cb) - mean) * a + b; o.y = (relu_b(v.y, cb) - mean) * a + b;
+            o.z = (relu_b(v.z, cb) - mean) * a + b; o.w = (relu_b(v.w, cb) - mean) * a + b;
             *reinterpret_cast<float4*>(y + i) = o;
         },
-        [&](int64_t i) { y[i] = (fmaxf(z[i], 0.f) - mean) * a + b; });
+        [&](int64_t i) { y[i] = (relu_b(z[i], cb) - mean) * a + b; });
+}
+
+// the five backward sums of one element
+__device__ __forceinline__ void bwd_acc(float (&v)[kBwdSums], float zv, float g, float cb, float mean, float invstd) {
+    const float zb = zv + cb;
+    const float xhat = (fmaxf(zb, 0.f) - mean) * invstd;
+    v[0] += g;
+    v[1] += g * xhat;
+    if (zb > 0.f) { v[2] += g; v[3] += 1.f; v[4] += xhat; }
 }
 
 __global__ void __launch_bounds__(kBnThreads)
-relu_bn_bwd_stats_kernel(const float* __restrict__ z, const float* __restrict__ gy, BnShape d,
-                         const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
-                         double* __restrict__ partial) {
+relu_bn_bwd_stats_kernel(const float* __restrict__ z, const float* __restrict__ conv_bias,
+                         const float* __restrict__ gy, BnShape d, const float* __restrict__ save_mean,
+                         const float* __restrict__ save_invstd, double* __restrict__ partial) {
     const int c = blockIdx.y, slice = blockIdx.x;
+    const float cb = conv_bias ? conv_bias[c] : 0.f;
     const float mean = save_mean[c], invstd = save_invstd[c];
-    float s1 = 0.f, s2 = 0.f;
+    float v[kBwdSums] = {0.f, 0.f, 0.f, 0.f, 0.f};
     bn_for_each(d, c, slice,
         [&](int64_t i) {
-            const float4 v = *reinterpret_cast<const float4*>(z + i), g = *reinterpret_cast<const float4*>(gy + i);
-            s1 += (g.x + g.y) + (g.z + g.w);
-            s2 += (g.x * ((fmaxf(v.x, 0.f) - mean) * invstd) + g.y * ((fmaxf(v.y, 0.f) - mean) * invstd)) +
-                  (g.z * ((fmaxf(v.z, 0.f) - mean) * invstd) + g.w * ((fmaxf(v.w, 0.f) - mean) * invstd));
+            const float4 q = *reinterpret_cast<const float4*>(z + i), g = *reinterpret_cast<const float4*>(gy + i);
+            bwd_acc(v, q.x, g.x, cb, mean, invstd); bwd_acc(v, q.y, g.y, cb, mean, invstd);
+            bwd_acc(v, q.z, g.z, cb, mean, invstd); bwd_acc(v, q.w, g.w, cb, mean, invstd);
         },
-        [&](int64_t i) { s1 += gy[i]; s2 += gy[i] * ((fmaxf(z[i], 0.f) - mean) * invstd); });
-    const double2 t = bn_block_sum(s1, s2);
-    if (threadIdx.x == 0) {
-        partial[((size_t)c * d.slices + slice) * 2] = t.x;
-        partial[((size_t)c * d.slices + slice) * 2 + 1] = t.y;
-    }
+        [&](int64_t i) { bwd_acc(v, z[i], gy[i], cb, mean, invstd); });
+    double t[kBwdSums];
+    bn_block_sum(v, t);
+    if (threadIdx.x == 0)
+        for (int k = 0; k < kBwdSums; ++k) partial[((size_t)c * d.slices + slice) * kBwdSums + k] = t[k];
 }
 
+// grad_weight = sum gy*xhat, grad_bias = sum gy, and the gradient of the folded convolution bias:
+// sum over the channel of gz = gamma*invstd * (A - mean(gy)*count - mean(gy*xhat)*X) over x > 0
 __global__ void __launch_bounds__(128)
-relu_bn_bwd_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ partial, float* __restrict__ grad_weight,
-                            float* __restrict__ grad_bias, float* __restrict__ coef /* [C][2]: mean(gy), mean(gy xhat) */) {
+relu_bn_bwd_finalize_kernel(BnShape d, int cs, int ks, const double* __restrict__ partial,
+                            const float* __restrict__ weight, const float* __restrict__ save_invstd,
+                            float* __restrict__ grad_weight, float* __restrict__ grad_bias,
+                            float* __restrict__ grad_conv_bias,
+                            float* __restrict__ coef /* [C][2]: mean(gy), mean(gy xhat) */) {
     const int c = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (c >= d.C) return;
-    const double2 t = bn_channel_sum(partial, c, cs, ks, d.slices);
+    double t[kBwdSums];
+    bn_channel_sum(partial, c, cs, ks, d.slices, t);
     if ((threadIdx.x & 31) != 0) return;
     const double M = (double)d.N * (double)d.HW;
-    if (grad_bias) grad_bias[c] = (float)t.x;
-    if (grad_weight) grad_weight[c] = (float)t.y;
-    coef[2 * c] = (float)(t.x / M);
-    coef[2 * c + 1] = (float)(t.y / M);
+    const double m1 = t[0] / M, m2 = t[1] / M;
+    if (grad_bias) grad_bias[c] = (float)t[0];
+    if (grad_weight) grad_weight[c] = (float)t[1];
+    if (grad_conv_bias) {
+        const double k = (double)save_invstd[c] * (weight ? (double)weight[c] : 1.0);
+        grad_conv_bias[c] = (float)(k * (t[2] - m1 * t[3] - m2 * t[4]));
+    }
+    coef[2 * c] = (float)m1;
+    coef[2 * c + 1] = (float)m2;
 }
 
 __global__ void __launch_bounds__(kBnThreads)
-relu_bn_bwd_apply_kernel(const float* __restrict__ z, const float* __restrict__ gy, BnShape d,
-                         const float* __restrict__ weight, const float* __restrict__ save_mean,
-                         const float* __restrict__ save_invstd, const float* __restrict__ coef,
-                         float* __restrict__ gz) {
+relu_bn_bwd_apply_kernel(const float* __restrict__ z, const float* __restrict__ conv_bias,
+                         const float* __restrict__ gy, BnShape d, const float* __restrict__ weight,
+                         const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                         const float* __restrict__ coef, float* __restrict__ gz) {
     const int c = blockIdx.y, slice = blockIdx.x;
+    const float cb = conv_bias ? conv_bias[c] : 0.f;
     const float mean = save_mean[c], invstd = save_invstd[c];
     const float k = invstd * (weight ? weight[c] : 1.f), m1 = coef[2 * c], m2 = coef[2 * c + 1];
     auto one = [&](float zv, float g) {
-        const float xhat = (fmaxf(zv, 0.f) - mean) * invstd;
-        return zv > 0.f ? k * (g - m1 - xhat * m2) : 0.f;
+        const float zb = zv + cb;
+        const float xhat = (fmaxf(zb, 0.f) - mean) * invstd;
+        return zb > 0.f ? k * (g - m1 - xhat * m2) : 0.f;
     };
     bn_for_each(d, c, slice,
         [&](int64_t i) {
@@ -326,7 +359,7 @@ relu_bn_bwd_apply_kernel(const float* __restrict__ z, const float* __restrict__ 
 // channels_last: the tensor is (M = N*HW rows) x C.  A thread owns 4 consecutive channels (C % 4 == 0)
 // and walks rows; 256 / (C/4) rows are in flight per CTA iteration (C <= 1024), a CTA takes a
 // contiguous chunk of rows; the threads that share a channel quad are combined through shared
-// memory.  Partials: [slices][C][2] fp64, slices = number of CTAs.
+// memory.  Partials: [slices][C][K] fp64, slices = number of CTAs.
 struct BnRows { int64_t M; int C; int slices; int64_t rows_per_cta; };
 
 template <class Body>
@@ -339,55 +372,56 @@ __device__ __forceinline__ void bn_rows_for_each(const BnRows& d, Body body) {
     for (int64_t r = beg + r0; r < end; r += rpi) body((r * d.C >> 2) + cv);     // float4 index
 }
 
-// combine (a, b) float4 pairs of the threads sharing a channel quad; result valid where r0 == 0
-__device__ __forceinline__ void bn_rows_combine(const BnRows& d, float4& a, float4& b) {
-    __shared__ float4 sa[256], sb[256];
+// combine the K float4 sums of the threads sharing a channel quad and store them:
+// partial[(slice * C + c) * K + j]
+template <int K>
+__device__ __forceinline__ void bn_rows_combine_store(const BnRows& d, const float4 (&v)[K], double* partial) {
+    __shared__ float4 sm[K][256];
     const int CV = d.C >> 2, rpi = 256 / CV;
-    const int r0 = threadIdx.x / CV, cv = threadIdx.x - r0 * CV;
-    sa[threadIdx.x] = a; sb[threadIdx.x] = b;
-    __syncthreads();
-    if (r0 == 0) {
-        for (int k = 1; k < rpi; ++k) {
-            const float4 u = sa[k * CV + cv], v = sb[k * CV + cv];
-            a.x += u.x; a.y += u.y; a.z += u.z; a.w += u.w;
-            b.x += v.x; b.y += v.y; b.z += v.z; b.w += v.w;
-        }
-    }
-}
-
-__device__ __forceinline__ void bn_rows_store(const BnRows& d, double* partial, const float4& a, const float4& b) {
-    const int CV = d.C >> 2;
-    if ((int)threadIdx.x >= CV) return;                      // r0 == 0 threads: cv = threadIdx.x
-    const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const size_t c = (size_t)threadIdx.x * 4 + k;
-        partial[((size_t)blockIdx.x * d.C + c) * 2] = av[k];         // [slice][channel]: coalesced finalize
-        partial[((size_t)blockIdx.x * d.C + c) * 2 + 1] = bv[k];
+    for (int j = 0; j < K; ++j) sm[j][threadIdx.x] = v[j];
+    __syncthreads();
+    if ((int)threadIdx.x >= CV) return;                      // r0 == 0 threads: cv = threadIdx.x
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+        double a[4] = {v[j].x, v[j].y, v[j].z, v[j].w};
+        for (int k = 1; k < rpi; ++k) {
+            const float4 u = sm[j][k * CV + threadIdx.x];
+            a[0] += u.x; a[1] += u.y; a[2] += u.z; a[3] += u.w;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            partial[((size_t)blockIdx.x * d.C + (size_t)threadIdx.x * 4 + q) * K + j] = a[q];
     }
 }
 
-__device__ __forceinline__ float4 relu4(float4 v) {
-    return make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+__device__ __forceinline__ float4 load_cb(const float* conv_bias, int cv) {
+    return conv_bias ? *reinterpret_cast<const float4*>(conv_bias + cv * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+}
+__device__ __forceinline__ float4 relu4(float4 v, float4 cb) {
+    return make_float4(relu_b(v.x, cb.x), relu_b(v.y, cb.y), relu_b(v.z, cb.z), relu_b(v.w, cb.w));
 }
 
 __global__ void __launch_bounds__(256)
-relu_bn_stats_nhwc_kernel(const float4* __restrict__ z, BnRows d, double* __restrict__ partial) {
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+relu_bn_stats_nhwc_kernel(const float4* __restrict__ z, const float* __restrict__ conv_bias, BnRows d,
+                          double* __restrict__ partial) {
+    const float4 cb = load_cb(conv_bias, threadIdx.x % (d.C >> 2));
+    float4 v[kFwdSums] = {make_float4(0.f, 0.f, 0.f, 0.f), make_float4(0.f, 0.f, 0.f, 0.f)};
     bn_rows_for_each(d, [&](int64_t i) {
-        const float4 v = relu4(z[i]);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-        q.x += v.x * v.x; q.y += v.y * v.y; q.z += v.z * v.z; q.w += v.w * v.w;
+        const float4 x = relu4(z[i], cb);
+        v[0].x += x.x; v[0].y += x.y; v[0].z += x.z; v[0].w += x.w;
+        v[1].x += x.x * x.x; v[1].y += x.y * x.y; v[1].z += x.z * x.z; v[1].w += x.w * x.w;
     });
-    bn_rows_combine(d, s, q);
-    bn_rows_store(d, partial, s, q);
+    bn_rows_combine_store(d, v, partial);
 }
 
 __global__ void __launch_bounds__(256)
-relu_bn_apply_nhwc_kernel(const float4* __restrict__ z, BnRows d, const float* __restrict__ weight,
-                          const float* __restrict__ bias, const float* __restrict__ save_mean,
-                          const float* __restrict__ save_invstd, float4* __restrict__ y) {
+relu_bn_apply_nhwc_kernel(const float4* __restrict__ z, const float* __restrict__ conv_bias, BnRows d,
+                          const float* __restrict__ weight, const float* __restrict__ bias,
+                          const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                          float4* __restrict__ y) {
     const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    const float4 cb = load_cb(conv_bias, cv);
     float mean[4], a[4], b[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -397,37 +431,45 @@ relu_bn_apply_nhwc_kernel(const float4* __restrict__ z, BnRows d, const float* _
         b[k] = bias ? bias[c] : 0.f;
     }
     bn_rows_for_each(d, [&](int64_t i) {
-        const float4 v = relu4(__ldcs(z + i));
+        const float4 v = relu4(__ldcs(z + i), cb);
         y[i] = make_float4((v.x - mean[0]) * a[0] + b[0], (v.y - mean[1]) * a[1] + b[1],
                            (v.z - mean[2]) * a[2] + b[2], (v.w - mean[3]) * a[3] + b[3]);
     });
 }
 
 __global__ void __launch_bounds__(256)
-relu_bn_bwd_stats_nhwc_kernel(const float4* __restrict__ z, const float4* __restrict__ gy, BnRows d,
-                              const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
-                              double* __restrict__ partial) {
+relu_bn_bwd_stats_nhwc_kernel(const float4* __restrict__ z, const float* __restrict__ conv_bias,
+                              const float4* __restrict__ gy, BnRows d, const float* __restrict__ save_mean,
+                              const float* __restrict__ save_invstd, double* __restrict__ partial) {
     const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    const float4 cb = load_cb(conv_bias, cv);
     float mean[4], inv[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) { mean[k] = save_mean[cv * 4 + k]; inv[k] = save_invstd[cv * 4 + k]; }
-    float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
+    float s[4][kBwdSums];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int j = 0; j < kBwdSums; ++j) s[q][j] = 0.f;
     bn_rows_for_each(d, [&](int64_t i) {
-        const float4 v = relu4(z[i]), g = gy[i];
-        s1.x += g.x; s1.y += g.y; s1.z += g.z; s1.w += g.w;
-        s2.x += g.x * ((v.x - mean[0]) * inv[0]); s2.y += g.y * ((v.y - mean[1]) * inv[1]);
-        s2.z += g.z * ((v.z - mean[2]) * inv[2]); s2.w += g.w * ((v.w - mean[3]) * inv[3]);
+        const float4 q = z[i], g = gy[i];
+        bwd_acc(s[0], q.x, g.x, cb.x, mean[0], inv[0]); bwd_acc(s[1], q.y, g.y, cb.y, mean[1], inv[1]);
+        bwd_acc(s[2], q.z, g.z, cb.z, mean[2], inv[2]); bwd_acc(s[3], q.w, g.w, cb.w, mean[3], inv[3]);
     });
-    bn_rows_combine(d, s1, s2);
-    bn_rows_store(d, partial, s1, s2);
+    float4 v[kBwdSums];
+#pragma unroll
+    for (int j = 0; j < kBwdSums; ++j) v[j] = make_float4(s[0][j], s[1][j], s[2][j], s[3][j]);
+    bn_rows_combine_store(d, v, partial);
 }
 
 __global__ void __launch_bounds__(256)
-relu_bn_bwd_apply_nhwc_kernel(const float4* __restrict__ z, const float4* __restrict__ gy, BnRows d,
-                              const float* __restrict__ weight, const float* __restrict__ save_mean,
-                              const float* __restrict__ save_invstd, const float* __restrict__ coef,
-                              float4* __restrict__ gz) {
+relu_bn_bwd_apply_nhwc_kernel(const float4* __restrict__ z, const float* __restrict__ conv_bias,
+                              const float4* __restrict__ gy, BnRows d, const float* __restrict__ weight,
+                              const float* __restrict__ save_mean, const float* __restrict__ save_invstd,
+                              const float* __restrict__ coef, float4* __restrict__ gz) {
     const int CV = d.C >> 2, cv = threadIdx.x % CV;
+    const float4 cb4 = load_cb(conv_bias, cv);
+    const float cb[4] = {cb4.x, cb4.y, cb4.z, cb4.w};
     float mean[4], inv[4], k4[4], m1[4], m2[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -437,8 +479,9 @@ relu_bn_bwd_apply_nhwc_kernel(const float4* __restrict__ z, const float4* __rest
         m1[k] = coef[2 * c]; m2[k] = coef[2 * c + 1];
     }
     auto one = [&](float zv, float g, int k) {
-        const float xhat = (fmaxf(zv, 0.f) - mean[k]) * inv[k];
-        return zv > 0.f ? k4[k] * (g - m1[k] - xhat * m2[k]) : 0.f;
+        const float zb = zv + cb[k];
+        const float xhat = (fmaxf(zb, 0.f) - mean[k]) * inv[k];
+        return zb > 0.f ? k4[k] * (g - m1[k] - xhat * m2[k]) : 0.f;
     };
     bn_rows_for_each(d, [&](int64_t i) {
         const float4 v = __ldcs(z + i), g = __ldcs(gy + i);
@@ -527,20 +570,25 @@ static bool bn_nhwc_ok(int C) { return C % 4 == 0 && C >= 4 && C <= 1024; }
 extern "C" size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C, int64_t HW, int32_t channels_last) {
     if (N < 1 || C < 1 || HW < 1 || (channels_last && !bn_nhwc_ok(C))) return 0;
     const size_t slices = channels_last ? (size_t)bn_rows(N, C, HW).slices : (size_t)bn_slices(N, C);
-    return round_up((size_t)C * slices * 2 * sizeof(double), 256) + round_up((size_t)C * 2 * sizeof(float), 256);
+    return round_up((size_t)C * slices * kBwdSums * sizeof(double), 256) + round_up((size_t)C * 2 * sizeof(float), 256);
 }
 
 static bool bn_args_ok(int64_t N, int32_t C, int64_t HW, const void* a, const void* b) {
     return N >= 1 && C >= 1 && C <= 65535 && HW >= 1 && a && b && (reinterpret_cast<uintptr_t>(a) & 15) == 0 &&
            (reinterpret_cast<uintptr_t>(b) & 15) == 0;
 }
+static float* bn_coef(void* workspace, int C, int slices) {
+    return reinterpret_cast<float*>(static_cast<char*>(workspace) +
+                                    round_up((size_t)C * slices * kBwdSums * sizeof(double), 256));
+}
 
-extern "C" int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64_t HW, const float* weight,
-                                     const float* bias, float* running_mean, float* running_var,
-                                     float momentum, float eps, float* y, float* save_mean,
-                                     float* save_invstd, void* workspace, int32_t channels_last,
-                                     void* stream_) {
-    if (!bn_args_ok(N, C, HW, z, y) || !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)))
+extern "C" int dvsof_relu_bn_forward(const float* z, const float* conv_bias, int64_t N, int32_t C, int64_t HW,
+                                     const float* weight, const float* bias, float* running_mean,
+                                     float* running_var, float momentum, float eps, float* y,
+                                     float* save_mean, float* save_invstd, void* workspace,
+                                     int32_t channels_last, void* stream_) {
+    if (!bn_args_ok(N, C, HW, z, y) || !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)) ||
+        (channels_last && conv_bias && (reinterpret_cast<uintptr_t>(conv_bias) & 15) != 0))
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_forward: bad arguments (fp32, 16-byte aligned; "
                                                 "channels_last needs C % 4 == 0, C <= 1024)");
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -548,28 +596,31 @@ extern "C" int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64
     if (channels_last) {
         const BnRows r = bn_rows(N, C, HW);
         const BnShape d{N, C, HW, r.slices};
-        relu_bn_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(reinterpret_cast<const float4*>(z), r, partial);
+        const float4* z4 = reinterpret_cast<const float4*>(z);
+        relu_bn_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, conv_bias, r, partial);
         relu_bn_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, 1, C, partial, momentum, eps, running_mean,
-                                                                   running_var, save_mean, save_invstd);
-        relu_bn_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(reinterpret_cast<const float4*>(z), r, weight, bias,
-                                                                save_mean, save_invstd, reinterpret_cast<float4*>(y));
+                                                               running_var, save_mean, save_invstd);
+        relu_bn_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, conv_bias, r, weight, bias, save_mean, save_invstd,
+                                                                reinterpret_cast<float4*>(y));
         return check_launch("relu_bn_forward(nhwc)");
     }
     const BnShape d{N, C, HW, bn_slices(N, C)};
     const dim3 grid((unsigned)d.slices, (unsigned)C);
-    relu_bn_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, d, partial);
+    relu_bn_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, conv_bias, d, partial);
     relu_bn_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, d.slices, 1, partial, momentum, eps, running_mean,
-                                                               running_var, save_mean, save_invstd);
-    relu_bn_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, d, weight, bias, save_mean, save_invstd, y);
+                                                           running_var, save_mean, save_invstd);
+    relu_bn_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, conv_bias, d, weight, bias, save_mean, save_invstd, y);
     return check_launch("relu_bn_forward");
 }
 
-extern "C" int dvsof_relu_bn_backward(const float* z, const float* grad_y, int64_t N, int32_t C, int64_t HW,
-                                      const float* weight, const float* save_mean, const float* save_invstd,
-                                      float* grad_z, float* grad_weight, float* grad_bias, void* workspace,
+extern "C" int dvsof_relu_bn_backward(const float* z, const float* conv_bias, const float* grad_y, int64_t N,
+                                      int32_t C, int64_t HW, const float* weight, const float* save_mean,
+                                      const float* save_invstd, float* grad_z, float* grad_weight,
+                                      float* grad_bias, float* grad_conv_bias, void* workspace,
                                       int32_t channels_last, void* stream_) {
     if (!bn_args_ok(N, C, HW, z, grad_y) || !grad_z || (reinterpret_cast<uintptr_t>(grad_z) & 15) != 0 ||
-        !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)))
+        !save_mean || !save_invstd || !workspace || (channels_last && !bn_nhwc_ok(C)) ||
+        (channels_last && conv_bias && (reinterpret_cast<uintptr_t>(conv_bias) & 15) != 0))
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "relu_bn_backward: bad arguments (fp32, 16-byte aligned; "
                                                 "channels_last needs C % 4 == 0, C <= 1024)");
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -577,22 +628,23 @@ extern "C" int dvsof_relu_bn_backward(const float* z, const float* grad_y, int64
     if (channels_last) {
         const BnRows r = bn_rows(N, C, HW);
         const BnShape d{N, C, HW, r.slices};
-        float* coef = reinterpret_cast<float*>(static_cast<char*>(workspace) +
-                                               round_up((size_t)C * r.slices * 2 * sizeof(double), 256));
+        float* coef = bn_coef(workspace, C, r.slices);
         const float4* z4 = reinterpret_cast<const float4*>(z);
         const float4* g4 = reinterpret_cast<const float4*>(grad_y);
-        relu_bn_bwd_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, g4, r, save_mean, save_invstd, partial);
-        relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, 1, C, partial, grad_weight, grad_bias, coef);
-        relu_bn_bwd_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, g4, r, weight, save_mean, save_invstd, coef,
-                                                                    reinterpret_cast<float4*>(grad_z));
+        relu_bn_bwd_stats_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, conv_bias, g4, r, save_mean, save_invstd, partial);
+        relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, 1, C, partial, weight, save_invstd, grad_weight,
+                                                                   grad_bias, grad_conv_bias, coef);
+        relu_bn_bwd_apply_nhwc_kernel<<<r.slices, 256, 0, stream>>>(z4, conv_bias, g4, r, weight, save_mean, save_invstd,
+                                                                    coef, reinterpret_cast<float4*>(grad_z));
         return check_launch("relu_bn_backward(nhwc)");
     }
     const BnShape d{N, C, HW, bn_slices(N, C)};
-    float* coef = reinterpret_cast<float*>(static_cast<char*>(workspace) +
-                                           round_up((size_t)C * d.slices * 2 * sizeof(double), 256));
+    float* coef = bn_coef(workspace, C, d.slices);
     const dim3 grid((unsigned)d.slices, (unsigned)C);
-    relu_bn_bwd_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, grad_y, d, save_mean, save_invstd, partial);
-    relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, d.slices, 1, partial, grad_weight, grad_bias, coef);
-    relu_bn_bwd_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, grad_y, d, weight, save_mean, save_invstd, coef, grad_z);
+    relu_bn_bwd_stats_kernel<<<grid, kBnThreads, 0, stream>>>(z, conv_bias, grad_y, d, save_mean, save_invstd, partial);
+    relu_bn_bwd_finalize_kernel<<<(C + 3) / 4, 128, 0, stream>>>(d, d.slices, 1, partial, weight, save_invstd,
+                                                               grad_weight, grad_bias, grad_conv_bias, coef);
+    relu_bn_bwd_apply_kernel<<<grid, kBnThreads, 0, stream>>>(z, conv_bias, grad_y, d, weight, save_mean, save_invstd,
+                                                             coef, grad_z);
     return check_launch("relu_bn_backward");
 }

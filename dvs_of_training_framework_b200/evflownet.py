@@ -22,11 +22,13 @@ _WIDTHS = (64, 128, 256, 512)
 
 
 class _ReluBN(torch.autograd.Function):
-    """`bn(relu(z))` in training mode (net.py:36,54) through csrc/glue.cu: batch statistics and the
-    running-statistics update like torch.nn.BatchNorm2d, the ReLU folded into every pass."""
+    """`bn(relu(z + conv_bias))` in training mode (net.py:36,54) through csrc/glue.cu: batch
+    statistics and the running-statistics update like torch.nn.BatchNorm2d, the bias add and the
+    ReLU folded into every pass (the convolution itself then runs without a bias: no separate add,
+    no separate reduction for its gradient)."""
 
     @staticmethod
-    def forward(ctx, z, weight, bias, running_mean, running_var, momentum, eps):
+    def forward(ctx, z, conv_bias, weight, bias, running_mean, running_var, momentum, eps):
         z, cl = _layout(z)
         N, C = z.shape[0], z.shape[1]
         if cl and (C % 4 or C > 1024):
@@ -37,39 +39,46 @@ class _ReluBN(torch.autograd.Function):
         stats = torch.empty((2, C), dtype=torch.float32, device=dev)
         ws = torch.empty(_lib.load().dvsof_relu_bn_workspace_bytes(N, C, HW, cl), dtype=torch.uint8, device=dev)
         with torch.cuda.device(dev):
-            _lib.call('dvsof_relu_bn_forward', _lib.ptr(z), N, C, HW, _lib.ptr(weight), _lib.ptr(bias),
-                      _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps), _lib.ptr(y),
-                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(ws), cl, _lib.stream_ptr(dev))
-        ctx.save_for_backward(z, weight, stats)
+            _lib.call('dvsof_relu_bn_forward', _lib.ptr(z), _lib.ptr(conv_bias), N, C, HW, _lib.ptr(weight),
+                      _lib.ptr(bias), _lib.ptr(running_mean), _lib.ptr(running_var), float(momentum), float(eps),
+                      _lib.ptr(y), _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(ws), cl, _lib.stream_ptr(dev))
+        ctx.save_for_backward(z, conv_bias, weight, stats)
         ctx.ws, ctx.cl = ws, cl
         return y
 
     @staticmethod
     def backward(ctx, gy):
-        z, weight, stats = ctx.saved_tensors
+        z, conv_bias, weight, stats = ctx.saved_tensors
         cl = ctx.cl
         gy = gy.contiguous(memory_format=torch.channels_last) if cl else gy.contiguous()
         N, C = z.shape[0], z.shape[1]
         HW = z.numel() // max(N * C, 1)
         dev = z.device
         gz = torch.empty_like(z)
-        gwb = torch.empty((2, C), dtype=torch.float32, device=dev)
+        g3 = torch.empty((3, C), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
-            _lib.call('dvsof_relu_bn_backward', _lib.ptr(z), _lib.ptr(gy), N, C, HW, _lib.ptr(weight),
-                      _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(gz), _lib.ptr(gwb[0]), _lib.ptr(gwb[1]),
-                      _lib.ptr(ctx.ws), cl, _lib.stream_ptr(dev))
-        return gz, gwb[0], gwb[1], None, None, None, None
+            _lib.call('dvsof_relu_bn_backward', _lib.ptr(z), _lib.ptr(conv_bias), _lib.ptr(gy), N, C, HW,
+                      _lib.ptr(weight), _lib.ptr(stats[0]), _lib.ptr(stats[1]), _lib.ptr(gz), _lib.ptr(g3[0]),
+                      _lib.ptr(g3[1]), _lib.ptr(g3[2]) if conv_bias is not None else None, _lib.ptr(ctx.ws), cl,
+                      _lib.stream_ptr(dev))
+        return gz, (g3[2] if conv_bias is not None else None), g3[0], g3[1], None, None, None, None
 
 
-def relu_batchnorm(z, bn):
-    """bn(relu(z)).  Training on CUDA fp32 takes the fused kernels; evaluation mode and CPU tensors
-    (the world-size-2 tests of the host logic) the ATen ops."""
-    if (bn.training and z.is_cuda and z.dtype == torch.float32 and bn.track_running_stats
-            and bn.affine and bn.momentum is not None and z.numel() > 0):
+def _fused_bn_ok(z, bn):
+    return (bn.training and z.is_cuda and z.dtype == torch.float32 and bn.track_running_stats
+            and bn.affine and bn.momentum is not None and z.numel() > 0)
+
+
+def relu_batchnorm(z, bn, conv_bias=None):
+    """bn(relu(z + conv_bias)).  Training on CUDA fp32 takes the fused kernels; evaluation mode and
+    CPU tensors (the world-size-2 tests of the host logic) the ATen ops."""
+    if _fused_bn_ok(z, bn):
         if z.numel() // z.shape[1] <= 1:       # torch.nn.functional.batch_norm's own check
             raise ValueError(f'Expected more than 1 value per channel when training, got input size {z.size()}')
         bn.num_batches_tracked.add_(1)
-        return _ReluBN.apply(z, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps)
+        return _ReluBN.apply(z, conv_bias, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.momentum, bn.eps)
+    if conv_bias is not None:
+        z = z + conv_bias.view(1, -1, 1, 1)
     return bn(F.relu(z))
 
 
@@ -85,12 +94,13 @@ class _ConvReluBN(nn.Module):
         nn.init.constant_(self.bn.weight, 0.1)
 
     def forward(self, x, pad_in=0):
+        w = self.conv.weight
         if pad_in:          # zero input channels appended by the caller: matching zero weight slices
-            w = F.pad(self.conv.weight, (0, 0, 0, 0, 0, pad_in)).contiguous(memory_format=torch.channels_last)
-            z = F.conv2d(x, w, self.conv.bias, self.conv.stride, self.conv.padding)
-        else:
-            z = self.conv(x)
-        return relu_batchnorm(z, self.bn)
+            w = F.pad(w, (0, 0, 0, 0, 0, pad_in)).contiguous(memory_format=torch.channels_last)
+        if _fused_bn_ok(x, self.bn):     # the bias is added inside the ReLU+BatchNorm kernels
+            z = F.conv2d(x, w, None, self.conv.stride, self.conv.padding)
+            return relu_batchnorm(z, self.bn, self.conv.bias)
+        return relu_batchnorm(F.conv2d(x, w, self.conv.bias, self.conv.stride, self.conv.padding), self.bn)
 
 
 class _Down(nn.Module):

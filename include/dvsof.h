@@ -272,23 +272,26 @@ int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t N, int32_
                                           int32_t W, float* grad_x, int32_t channels_last,
                                           void* stream);
 
-/* EV_FlowNet/net.py:36,54, the tail of every conv block: ReLU followed by BatchNorm2d in training
- * mode (batch statistics over (N, H, W) of relu(z), biased variance; running statistics updated
- * with `momentum`, unbiased variance, either may be NULL), as stats + apply passes that spread a
- * channel over many CTAs.  z, y, grad_* [dev] fp32, 16-byte aligned: (N, C, HW) contiguous, or
- * (N, HW, C) when channels_last != 0; weight / bias [dev] C floats or NULL; save_mean /
- * save_invstd [dev] C floats (kept for backward).  backward: grad_z = d/dz, grad_weight /
- * grad_bias [dev] C floats (or NULL).  Deterministic.
+/* EV_FlowNet/net.py:36,54, the tail of every conv block: (convolution bias,) ReLU and
+ * BatchNorm2d in training mode: y = BN(relu(z + conv_bias)), batch statistics over (N, H, W),
+ * biased variance; running statistics updated with `momentum`, unbiased variance, either may be
+ * NULL.  Stats + apply passes that spread a channel over many CTAs.  z, y, grad_* [dev] fp32,
+ * 16-byte aligned: (N, C, HW) contiguous, or (N, HW, C) when channels_last != 0; conv_bias [dev] C
+ * floats or NULL (z is then the output of a bias-free convolution: the bias add and its gradient
+ * reduction are folded in here); weight / bias [dev] C floats or NULL; save_mean / save_invstd
+ * [dev] C floats (kept for backward).  backward: grad_z = d/dz, grad_weight / grad_bias /
+ * grad_conv_bias [dev] C floats (or NULL).  Deterministic.
  * workspace: dvsof_relu_bn_workspace_bytes(N, C, HW, channels_last)  (channels_last: C % 4 == 0,
  * C <= 1024, else 0). */
 size_t dvsof_relu_bn_workspace_bytes(int64_t N, int32_t C, int64_t HW, int32_t channels_last);
-int dvsof_relu_bn_forward(const float* z, int64_t N, int32_t C, int64_t HW, const float* weight,
-                          const float* bias, float* running_mean, float* running_var, float momentum,
-                          float eps, float* y, float* save_mean, float* save_invstd, void* workspace,
-                          int32_t channels_last, void* stream);
-int dvsof_relu_bn_backward(const float* z, const float* grad_y, int64_t N, int32_t C, int64_t HW,
-                           const float* weight, const float* save_mean, const float* save_invstd,
-                           float* grad_z, float* grad_weight, float* grad_bias, void* workspace,
+int dvsof_relu_bn_forward(const float* z, const float* conv_bias, int64_t N, int32_t C, int64_t HW,
+                          const float* weight, const float* bias, float* running_mean,
+                          float* running_var, float momentum, float eps, float* y, float* save_mean,
+                          float* save_invstd, void* workspace, int32_t channels_last, void* stream);
+int dvsof_relu_bn_backward(const float* z, const float* conv_bias, const float* grad_y, int64_t N,
+                           int32_t C, int64_t HW, const float* weight, const float* save_mean,
+                           const float* save_invstd, float* grad_z, float* grad_weight,
+                           float* grad_bias, float* grad_conv_bias, void* workspace,
                            int32_t channels_last, void* stream);
 
 #ifdef __cplusplus

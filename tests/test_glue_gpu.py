@@ -73,8 +73,12 @@ def test_relu_batchnorm_matches_aten(shape, channels_last):
         z = z.contiguous(memory_format=torch.channels_last)
     z.requires_grad_()
     zr = z.detach().clone().requires_grad_()
-    y = relu_batchnorm(z, bn)
-    yr = ref(torch.relu(zr))
+    cb = cbr = None
+    if sum(shape) % 2 == 0:                   # half of the cases: a convolution bias folded in
+        cb = torch.randn(C, generator=g, device='cuda').requires_grad_()
+        cbr = cb.detach().clone().requires_grad_()
+    y = relu_batchnorm(z, bn, cb)
+    yr = ref(torch.relu(zr if cbr is None else zr + cbr.view(1, -1, 1, 1)))
     torch.testing.assert_close(y, yr, rtol=2e-5, atol=2e-5)
     torch.testing.assert_close(bn.running_mean, ref.running_mean, rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-5, atol=1e-6)
@@ -85,6 +89,8 @@ def test_relu_batchnorm_matches_aten(shape, channels_last):
     torch.testing.assert_close(z.grad, zr.grad, rtol=2e-4, atol=2e-5)
     torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=2e-4, atol=2e-4)
     torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=2e-5, atol=2e-4)
+    if cb is not None:
+        torch.testing.assert_close(cb.grad, cbr.grad, rtol=2e-4, atol=2e-4)
     # evaluation mode goes through ATen (running statistics)
     bn.eval()
     assert torch.equal(relu_batchnorm(z.detach(), bn), bn(torch.relu(z.detach())))
