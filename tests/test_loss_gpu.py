@@ -357,3 +357,58 @@ def test_fused_full_size_cfg4_agrees_with_generic_path():
     np.testing.assert_allclose(float(loss), float(total), rtol=1e-6)
     for a, b in zip(fa, fb):
         torch.testing.assert_close(a.grad, b.grad, rtol=RTOL, atol=ATOL)
+
+
+def _run_fused_abi(inp):
+    import ctypes
+    import dvs_of_training_framework_b200 as dv
+    from dvs_of_training_framework_b200.loss import _fill_frames
+    L = dv._lib
+    dev = torch.device('cuda', 0)
+    fl = [f.cuda().contiguous() for f in inp['flows']]
+    images = inp['images'].cuda()
+    B, S = fl[0].shape[0], len(fl)
+    D, _, H, W = images.shape
+    ev = dv.Losses(inp['shapes'], B, 'cuda')
+    plan = ev._plan(dev, B, D, H, W, fl)
+    o = plan.offs
+    buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
+    gbuf = torch.zeros(plan.gtotal, dtype=torch.float32, device=dev)
+    dev_in = {k: inp[k].cuda() for k in ('flow_ts', 'flow_sample_idx', 'timestamps', 'sample_idx')}
+    fr = _fill_frames(plan, images, dev_in['flow_ts'], dev_in['flow_sample_idx'], dev_in['timestamps'],
+                      dev_in['sample_idx'])
+    plan.fill(plan.bwd, buf.data_ptr(), fl, gbuf.data_ptr())
+    coef = (ctypes.c_float * (3 * S))(*([0.5 / S] * S + [1.0 / S] * S + [1.0 / S] * S))
+    st = L.status_for(dev)
+    base = buf.data_ptr()
+    L.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S], base + 4 * o[S + 2],
+           base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr, L.ptr(st.word), L.stream_ptr(dev))
+    st.check()
+    levels = [buf[o[s]:o[s] + D * h * w].view(D, 1, h, w).clone() for s, (h, w) in enumerate(inp['shapes'])]
+    n_bad = buf[o[S + 1]:o[S + 1] + S * B].view(torch.int32).view(S, B).clone()
+    return levels, n_bad, images, fl
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('B,H,W,n_scales', [(1, 260, 346, 4), (3, 97, 131, 4), (2, 64, 48, 3), (1, 33, 70, 1),
+                                            (40, 64, 64, 4), (1, 1024, 1536, 4), (1, 2048, 2304, 4)])
+def test_pyramid_chain_and_tile_counts_through_the_abi(B, H, W, n_scales):
+    """The one-launch prelude (pyramid_chain_kernel: row slabs, levels in shared memory, per-tile
+    border counts) against the level-by-level resize kernel and a direct count, for odd widths
+    (scalar stores), a single scale, many frames (one slab per frame) and a frame whose later
+    levels do not fit in shared memory (falls back to the resize kernel for them)."""
+    import dvs_of_training_framework_b200 as dv
+    inp = synth_loss_inputs(31 + B + H, B, H, W, sigma=6.0, n_scales=n_scales)
+    levels, n_bad, images, fl = _run_fused_abi(inp)
+    img = images
+    for s, (h, w) in enumerate(inp['shapes']):
+        img = dv.interpolate(img, (h, w))                       # utils/loss.py:207-210, chained
+        assert torch.equal(levels[s], img), f'level {s}'
+        # out-of-border count of utils/loss.py:92-113 per (scale, prediction)
+        f = fl[s]
+        xs = torch.arange(w, device='cuda', dtype=torch.float32).view(1, 1, w)
+        ys = torch.arange(h, device='cuda', dtype=torch.float32).view(1, h, 1)
+        gx = (xs + f[:, 0]) / ((w - 1) / 2) - 1 if w > 1 else torch.full_like(f[:, 0], float('nan'))
+        gy = (ys + f[:, 1]) / ((h - 1) / 2) - 1 if h > 1 else torch.full_like(f[:, 1], float('nan'))
+        bad = ((gx < -1) | (gx > 1) | (gy < -1) | (gy > 1)).flatten(1).sum(1).int()
+        assert torch.equal(n_bad[s], bad), f'border count, scale {s}'
