@@ -79,6 +79,12 @@ _SIGNATURES = {
                                                        C.c_void_p, C.c_int32, C.c_void_p]),
     'dvsof_upsample2x_reflect_pad_backward': (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                                         C.c_void_p, C.c_int32, C.c_void_p]),
+    'dvsof_upsample2x_reflect_pad_cat_forward': (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_int32), C.c_int32,
+                                                           C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                                           C.c_void_p]),
+    'dvsof_upsample2x_reflect_pad_cat_backward': (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int32),
+                                                            C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int32,
+                                                            C.c_void_p]),
     'dvsof_relu_bn_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int32, C.c_int64, C.c_int32]),
     'dvsof_relu_bn_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_void_p,
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p,

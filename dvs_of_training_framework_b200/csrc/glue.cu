@@ -138,6 +138,88 @@ upsample2x_reflect_pad_bwd_nhwc_kernel(const float* __restrict__ gy, float* __re
     }
 }
 
+// The same gather with the channel concatenation of the decoder input folded in (net.py:246-262:
+// `cat((h, skip), 1)` feeds the upsampling): up to kMaxParts channels_last sources, optional zero
+// channels at the end; the backward writes one contiguous gradient per source, so neither the
+// concatenated tensor nor the strided views of its gradient ever exist.
+constexpr int kMaxParts = 4;
+struct CatParts {
+    float* p[kMaxParts];          // sources (forward) / gradient destinations (backward; may be null)
+    int c_begin[kMaxParts + 1];   // channel offsets; c_begin[n_parts] = channels that come from sources
+    int n_parts;
+};
+__device__ __forceinline__ int cat_part(const CatParts& cp, int c) {
+    int k = 0;
+#pragma unroll
+    for (int i = 1; i <= kMaxParts; ++i) k += (i <= cp.n_parts && c >= cp.c_begin[i]) ? 1 : 0;
+    return k;                                                // == n_parts: the zero channels
+}
+
+template <int V>
+__global__ void __launch_bounds__(256)
+upsample2x_reflect_pad_cat_fwd_kernel(const __grid_constant__ CatParts cp, float* __restrict__ y, int64_t N,
+                                      int C, int H, int W) {
+    using T = typename VecT<V>::T;
+    const int Ho = 2 * H + 2, Wo = 2 * W + 2, CV = C / V;
+    const float inv_cv = 1.f / (float)CV;
+    const int row_items = Wo * CV;
+    for (int64_t row = blockIdx.x; row < N * Ho; row += gridDim.x) {
+        const int64_t n = row / Ho;
+        const int i = (int)(row - n * Ho);
+        const int a = reflect_idx(i - 1, 2 * H) >> 1;
+        const int64_t src_row = (n * H + a) * (int64_t)W;
+        T* dst = reinterpret_cast<T*>(y + row * (int64_t)Wo * C);
+        for (int o = threadIdx.x; o < row_items; o += 256) {
+            const int j = (int)(((float)o + 0.5f) * inv_cv), c = (o - j * CV) * V;
+            const int b = reflect_idx(j - 1, 2 * W) >> 1;
+            const int k = cat_part(cp, c);
+            T v = T();
+            if (k < cp.n_parts) {
+                const int ck = cp.c_begin[k + 1] - cp.c_begin[k];
+                v = __ldg(reinterpret_cast<const T*>(cp.p[k] + (src_row + b) * ck + (c - cp.c_begin[k])));
+            }
+            dst[o] = v;
+        }
+    }
+}
+
+template <int V>
+__global__ void __launch_bounds__(256)
+upsample2x_reflect_pad_cat_bwd_kernel(const float* __restrict__ gy, const __grid_constant__ CatParts cp,
+                                      int64_t N, int C, int H, int W) {
+    using T = typename VecT<V>::T;
+    const int Ho = 2 * H + 2, Wo = 2 * W + 2, CV = C / V;
+    const int CS = cp.c_begin[cp.n_parts] / V;               // channel vectors that have a destination
+    const float inv_cs = 1.f / (float)CS;
+    const int row_items = W * CS;
+    for (int64_t row = blockIdx.x; row < N * H; row += gridDim.x) {
+        const int64_t n = row / H;
+        const int h = (int)(row - n * H);
+        int ri[4], nr = 0;
+        if (h == 0) ri[nr++] = 0;
+        ri[nr++] = 2 * h + 1;
+        ri[nr++] = 2 * h + 2;
+        if (h == H - 1) ri[nr++] = 2 * H + 1;
+        const T* base = reinterpret_cast<const T*>(gy + n * (int64_t)Ho * Wo * C);
+        for (int o = threadIdx.x; o < row_items; o += 256) {
+            const int w = (int)(((float)o + 0.5f) * inv_cs), cv = o - w * CS, c = cv * V;
+            const int k = cat_part(cp, c);
+            if (!cp.p[k]) continue;
+            T acc = T();
+            for (int q = 0; q < nr; ++q) {
+                const T* r = base + (int64_t)ri[q] * Wo * CV + cv;
+                T s = w == 0 ? __ldg(r) : T();
+                s = vadd(s, __ldg(r + (2 * w + 1) * CV));
+                s = vadd(s, __ldg(r + (2 * w + 2) * CV));
+                if (w == W - 1) s = vadd(s, __ldg(r + (2 * W + 1) * CV));
+                acc = vadd(acc, s);
+            }
+            const int ck = cp.c_begin[k + 1] - cp.c_begin[k];
+            *reinterpret_cast<T*>(cp.p[k] + (row * W + w) * ck + (c - cp.c_begin[k])) = acc;
+        }
+    }
+}
+
 static int glue_grid(int64_t rows) {
     int64_t g = (rows + kGlueWarps - 1) / kGlueWarps;
     const int64_t cap = (int64_t)kNumSMs * 32;
@@ -551,6 +633,69 @@ extern "C" int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_
         }
     }
     return check_launch("upsample2x_reflect_pad_bwd");
+}
+
+static int cat_setup(float* const* parts, const int32_t* part_channels, int32_t n_parts, int32_t pad_channels,
+                     bool null_ok, CatParts* cp, int* C, int* V) {
+    if (n_parts < 1 || n_parts > kMaxParts || !parts || !part_channels || pad_channels < 0) return -1;
+    int c = 0, v = 4;
+    cp->n_parts = n_parts;
+    for (int k = 0; k < kMaxParts; ++k) { cp->p[k] = nullptr; cp->c_begin[k + 1] = 0; }
+    cp->c_begin[0] = 0;
+    for (int k = 0; k < n_parts; ++k) {
+        if (part_channels[k] < 1 || (!parts[k] && !null_ok)) return -1;
+        cp->p[k] = parts[k];
+        c += part_channels[k];
+        cp->c_begin[k + 1] = c;
+        while (v > 1 && (part_channels[k] % v || (reinterpret_cast<uintptr_t>(parts[k]) & (4 * v - 1)))) v >>= 1;
+    }
+    for (int k = n_parts + 1; k <= kMaxParts; ++k) cp->c_begin[k] = c;
+    while (v > 1 && pad_channels % v) v >>= 1;
+    *C = c + pad_channels;
+    *V = v;
+    return 0;
+}
+
+extern "C" int dvsof_upsample2x_reflect_pad_cat_forward(const float* const* parts, const int32_t* part_channels,
+                                                        int32_t n_parts, int32_t pad_channels, int64_t N,
+                                                        int32_t H, int32_t W, float* y, void* stream_) {
+    CatParts cp;
+    int C = 0, V = 1;
+    if (cat_setup(const_cast<float* const*>(reinterpret_cast<const float* const*>(parts)), part_channels, n_parts,
+                  pad_channels, false, &cp, &C, &V) || N < 0 || H < 1 || W < 1 || (N > 0 && !y) || H > (1 << 20) ||
+        W > (1 << 20) || (2 * (int64_t)W + 2) * C >= (1 << 21))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "upsample2x_reflect_pad_cat_forward: bad arguments");
+    if (N == 0) return DVSOF_OK;
+    while (V > 1 && (reinterpret_cast<uintptr_t>(y) & (4 * V - 1))) V >>= 1;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int grid = row_grid(N * (2 * (int64_t)H + 2));
+    switch (V) {
+        case 4: upsample2x_reflect_pad_cat_fwd_kernel<4><<<grid, 256, 0, stream>>>(cp, y, N, C, H, W); break;
+        case 2: upsample2x_reflect_pad_cat_fwd_kernel<2><<<grid, 256, 0, stream>>>(cp, y, N, C, H, W); break;
+        default: upsample2x_reflect_pad_cat_fwd_kernel<1><<<grid, 256, 0, stream>>>(cp, y, N, C, H, W);
+    }
+    return check_launch("upsample2x_reflect_pad_cat_fwd");
+}
+
+extern "C" int dvsof_upsample2x_reflect_pad_cat_backward(const float* grad_y, float* const* grad_parts,
+                                                         const int32_t* part_channels, int32_t n_parts,
+                                                         int32_t pad_channels, int64_t N, int32_t H, int32_t W,
+                                                         void* stream_) {
+    CatParts cp;
+    int C = 0, V = 1;
+    if (cat_setup(grad_parts, part_channels, n_parts, pad_channels, true, &cp, &C, &V) || N < 0 || H < 1 || W < 1 ||
+        (N > 0 && !grad_y) || H > (1 << 20) || W > (1 << 20) || (2 * (int64_t)W + 2) * C >= (1 << 21))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "upsample2x_reflect_pad_cat_backward: bad arguments");
+    if (N == 0) return DVSOF_OK;
+    while (V > 1 && (reinterpret_cast<uintptr_t>(grad_y) & (4 * V - 1))) V >>= 1;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int grid = row_grid(N * (int64_t)H);
+    switch (V) {
+        case 4: upsample2x_reflect_pad_cat_bwd_kernel<4><<<grid, 256, 0, stream>>>(grad_y, cp, N, C, H, W); break;
+        case 2: upsample2x_reflect_pad_cat_bwd_kernel<2><<<grid, 256, 0, stream>>>(grad_y, cp, N, C, H, W); break;
+        default: upsample2x_reflect_pad_cat_bwd_kernel<1><<<grid, 256, 0, stream>>>(grad_y, cp, N, C, H, W);
+    }
+    return check_launch("upsample2x_reflect_pad_cat_bwd");
 }
 
 // workspace: partial sums [C x slices][2] fp64 | coefficients [C][2] fp32

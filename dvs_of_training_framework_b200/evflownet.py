@@ -93,10 +93,10 @@ class _ConvReluBN(nn.Module):
         nn.init.zeros_(self.conv.bias)
         nn.init.constant_(self.bn.weight, 0.1)
 
-    def forward(self, x, pad_in=0):
-        w = self.conv.weight
-        if pad_in:          # zero input channels appended by the caller: matching zero weight slices
-            w = F.pad(w, (0, 0, 0, 0, 0, pad_in)).contiguous(memory_format=torch.channels_last)
+    def forward(self, x, w=None):
+        """w: the weight rearranged by the caller to the channel order of x (see _Up.forward)."""
+        if w is None:
+            w = self.conv.weight
         if _fused_bn_ok(x, self.bn):     # the bias is added inside the ReLU+BatchNorm kernels
             z = F.conv2d(x, w, None, self.conv.stride, self.conv.padding)
             return relu_batchnorm(z, self.bn, self.conv.bias)
@@ -164,6 +164,57 @@ class _UpsamplePad(torch.autograd.Function):
         return gx
 
 
+class _UpsamplePadCat(torch.autograd.Function):
+    """upsample2x_reflect_pad(cat(parts + zero channels, 1)) for channels_last parts in one gather;
+    backward writes one contiguous gradient per part (csrc/glue.cu)."""
+
+    @staticmethod
+    def forward(ctx, pad_in, *parts):
+        import ctypes
+        N, _, H, W = parts[0].shape
+        chans = [p.shape[1] for p in parts]
+        dev = parts[0].device
+        y = _empty((N, sum(chans) + pad_in, 2 * H + 2, 2 * W + 2), 1, dev)
+        ptrs = (ctypes.c_void_p * len(parts))(*[p.data_ptr() for p in parts])
+        cc = (ctypes.c_int32 * len(parts))(*chans)
+        with torch.cuda.device(dev):
+            _lib.call('dvsof_upsample2x_reflect_pad_cat_forward', ptrs, cc, len(parts), pad_in, N, H, W,
+                      _lib.ptr(y), _lib.stream_ptr(dev))
+        ctx.meta = (N, H, W, chans, pad_in)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        import ctypes
+        N, H, W, chans, pad_in = ctx.meta
+        gy = gy.contiguous(memory_format=torch.channels_last)
+        need = ctx.needs_input_grad[1:]
+        grads = [_empty((N, c, H, W), 1, gy.device) if nd else None for c, nd in zip(chans, need)]
+        ptrs = (ctypes.c_void_p * len(chans))(*[g.data_ptr() if g is not None else None for g in grads])
+        cc = (ctypes.c_int32 * len(chans))(*chans)
+        with torch.cuda.device(gy.device):
+            _lib.call('dvsof_upsample2x_reflect_pad_cat_backward', _lib.ptr(gy), ptrs, cc, len(chans), pad_in,
+                      N, H, W, _lib.stream_ptr(gy.device))
+        return (None,) + tuple(grads)
+
+
+def _is_cl(t):
+    return t.is_cuda and t.dtype == torch.float32 and t.dim() == 4 and \
+        t.is_contiguous(memory_format=torch.channels_last) and (not t.is_contiguous() or t.shape[1] == 1)
+
+
+def upsample2x_reflect_pad_cat(parts, pad_in=0):
+    """upsample2x_reflect_pad of the channel concatenation of `parts` (+ pad_in zero channels)."""
+    if len(parts) <= 4 and all(_is_cl(p) for p in parts) and parts[0].shape[2] * parts[0].shape[3] > 1:
+        return _UpsamplePadCat.apply(pad_in, *parts)
+    parts = tuple(parts)
+    if pad_in:
+        N, _, H, W = parts[0].shape
+        parts += (torch.empty((N, pad_in, H, W), dtype=parts[0].dtype, device=parts[0].device,
+                              memory_format=torch.channels_last).zero_(),)
+    return upsample2x_reflect_pad(torch.cat(parts, 1))
+
+
 def upsample2x_reflect_pad(x):
     """Head of a decoder block (net.py:72-85).  CUDA fp32 tensors take the fused kernel; anything
     else (the CPU world-size-2 tests of the host logic) the two ATen ops."""
@@ -179,19 +230,36 @@ class _Up(nn.Module):
         super().__init__()
         self.block = _ConvReluBN(cin, cout)
 
-    def forward(self, parts):
-        """parts: the tensors whose channel concatenation is the block's input (net.py:246-262).  In
-        channels_last the concatenation is filled up with zero channels to a multiple of 8 (and the
-        weight with zero slices): 130 / 258 / 514 input channels otherwise make cuDNN copy every
-        operand into a padded buffer around each of its three kernels (3.8 ms per step)."""
-        first = parts[0]
-        cl = first.is_contiguous(memory_format=torch.channels_last) and not first.is_contiguous()
-        pad_in = (-sum(p.shape[1] for p in parts)) % 8 if cl else 0
-        if pad_in:
-            N, _, H, W = first.shape
-            parts = tuple(parts) + (torch.empty((N, pad_in, H, W), dtype=first.dtype, device=first.device,
-                                                memory_format=torch.channels_last).zero_(),)
-        return self.block(upsample2x_reflect_pad(torch.cat(parts, 1)), pad_in)
+    def forward(self, h, f, skip):
+        """The block's input is cat((h, f, skip), 1) (net.py:246-262; f = the previous flow, None
+        for the first block).  In channels_last the parts go straight into the gather, in the order
+        (h, skip, f + zero channels) with the total filled up to a multiple of 8 channels -- 130 / 258
+        / 514 input channels otherwise make cuDNN copy every operand into a padded buffer around each
+        of its three kernels (3.8 ms per step), and a 2-channel part in the middle would break the
+        16-byte vectors of the gather.  The weight is rearranged to that order on the fly (input
+        channels are permuted and zero slices appended: the parameters stay as they are)."""
+        if _is_cl(h) and _is_cl(skip) and (f is None or f.is_cuda):
+            w = self.block.conv.weight
+            ch, cs = h.shape[1], skip.shape[1]
+            if f is None:
+                pad_in = (-(ch + cs)) % 8
+                parts = (h, skip)
+                if pad_in:
+                    w = F.pad(w, (0, 0, 0, 0, 0, pad_in))
+            else:
+                cf = f.shape[1]
+                pad_in = (-(ch + cs + cf)) % 8
+                N, _, H, W = f.shape
+                tail = torch.zeros((N, cf + pad_in, H, W), dtype=f.dtype, device=f.device).contiguous(
+                    memory_format=torch.channels_last)
+                tail[:, :cf] = f
+                parts = (h, skip, tail)
+                w = torch.cat((w[:, :ch], w[:, ch + cf:], w[:, ch:ch + cf],
+                               w.new_zeros((w.shape[0], pad_in) + tuple(w.shape[2:]))), 1)
+            w = w.contiguous(memory_format=torch.channels_last)
+            return self.block(upsample2x_reflect_pad_cat(parts, 0), w)
+        x = torch.cat((h, skip) if f is None else (h, f, skip), 1)
+        return self.block(upsample2x_reflect_pad(x))
 
 
 class Model(nn.Module):
@@ -233,12 +301,11 @@ class Model(nn.Module):
                 feats[f'tr_{i}'] = h
         flows = []
         for i, (dec, head) in enumerate(zip(self.dec, self.flow)):
-            h = dec((h, skips[3 - i]))
+            h = dec(h, flows[-1] if flows else None, skips[3 - i])
             f = torch.tanh(head(h)) * 256.
             flows.append(f)
-            h = torch.cat((h, f), 1)
             if intermediate:
-                feats[f'dec_op_{i}'] = h
+                feats[f'dec_op_{i}'] = torch.cat((h, f), 1)
         result = tuple(f[..., :s[0], :s[1]] for f, s in zip(flows, outsize))
         extra = (feats,) if intermediate else ()
         return (result, timestamps.reshape(-1, 2), sample_idx[0::2]) + extra

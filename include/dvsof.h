@@ -272,6 +272,19 @@ int dvsof_upsample2x_reflect_pad_backward(const float* grad_y, int64_t N, int32_
                                           int32_t W, float* grad_x, int32_t channels_last,
                                           void* stream);
 
+/* The same with the channel concatenation that builds the decoder input folded in
+ * (EV_FlowNet/net.py:246-262 `cat((h, skip), 1)`): parts [host array of n_parts <= 4 device
+ * pointers], each (N, H, W, part_channels[k]) channels_last fp32; pad_channels zero channels are
+ * appended (channel count of y = sum + pad).  backward writes one contiguous gradient per part
+ * (grad_parts[k] may be NULL: not needed).  channels_last only. */
+int dvsof_upsample2x_reflect_pad_cat_forward(const float* const* parts, const int32_t* part_channels,
+                                             int32_t n_parts, int32_t pad_channels, int64_t N, int32_t H,
+                                             int32_t W, float* y, void* stream);
+int dvsof_upsample2x_reflect_pad_cat_backward(const float* grad_y, float* const* grad_parts,
+                                              const int32_t* part_channels, int32_t n_parts,
+                                              int32_t pad_channels, int64_t N, int32_t H, int32_t W,
+                                              void* stream);
+
 /* EV_FlowNet/net.py:36,54, the tail of every conv block: (convolution bias,) ReLU and
  * BatchNorm2d in training mode: y = BN(relu(z + conv_bias)), batch statistics over (N, H, W),
  * biased variance; running statistics updated with `momentum`, unbiased variance, either may be
