@@ -115,3 +115,78 @@ def decode_batch(encoded_batch):
     result = decode_batch_info(encoded_batch)
     result['events'] = decode_events(encoded_batch['events'], encoded_batch['elements_per_sample'])
     return result
+
+
+def quantize_batch(batch, imsize=None):
+    """The loop body of scripts/quantize_preprocessed.py:77-92: the batch with
+    its events replaced by the event image `data` = quantize(events, ...) (EV_FlowNet/net.py:197-205).
+    Accepts the training form (events with int64 x, y, ...) and the storage form (`encode_batch`
+    output: the 9 B/event arrays go straight into the encoder, no int64 detour)."""
+    from . import encoder
+    if 'elements_per_sample' in batch:                      # storage form
+        info = decode_batch_info(batch)
+        ev = batch['events']
+        eps = batch['elements_per_sample'].to(torch.int64)
+        epe = ev['events_per_element'].to(torch.int64)
+        # events per sample from the run lengths (elements may be truncated at the end, :298)
+        elem_sample = torch.repeat_interleave(torch.arange(eps.numel(), device=eps.device), eps)[:epe.numel()]
+        per_sample = torch.zeros(eps.numel(), dtype=torch.int64, device=eps.device).index_add_(0, elem_sample, epe)
+        imsize = imsize if imsize is not None else batch['images'].shape[-2:]
+        # EV_FlowNet/net.py:101-103: two image time stamps per sample (one element per sample)
+        ts = info['timestamps']
+        assert ts.numel() == 2 * eps.numel()
+        data = encoder.compute_event_image_compact(ev['x'], ev['y'], ev['timestamp'], ev['polarity'], per_sample,
+                                                   ts.contiguous(), encoder.extend_size(imsize))
+        out = dict(info)
+    else:
+        imsize = imsize if imsize is not None else batch['images'].shape[-2:]
+        with torch.no_grad():
+            data = encoder.quantize(batch['events'], batch['timestamps'], batch['sample_idx'], imsize)
+        out = {k: v for k, v in batch.items() if k != 'events'}
+    out['data'] = data
+    return out
+
+
+def encode_quantized_batch(batch):
+    """utils/dataset.py:429-479: everything to the CPU (one synchronisation for all tensors, through
+    pinned buffers), `data` (B, C, H, W) -> (B*C, H, W), channels_per_sample = C as uint8, plus
+    encode_batch_info."""
+    B, C, H, W = batch['data'].size()
+    info = encode_batch_info(batch['timestamps'], batch['sample_idx'], batch['images'],
+                             batch['augmentation_params'], batch['size']) if batch['sample_idx'].is_cuda else None
+    if info is None:                                        # already on the CPU: the reference's own arithmetic
+        sidx = batch['sample_idx'].to(torch.int64)
+        eps = (torch.bincount(sidx, minlength=int(batch['size'])).to(torch.int16) - 1).to(torch.uint8)
+        info = {'timestamps': batch['timestamps'], 'elements_per_sample': eps,
+                'images': batch['images'].to(torch.uint8), 'augmentation_params': batch['augmentation_params']}
+    result = {'data': batch['data'].reshape(B * C, H, W),
+              'channels_per_sample': torch.full((B,), C, dtype=torch.uint8)}
+    result.update(info)
+
+    pending = []
+
+    def to_cpu(v):
+        if isinstance(v, dict):
+            return {k: to_cpu(x) for k, x in v.items()}
+        if isinstance(v, torch.Tensor) and v.is_cuda:
+            host = torch.empty(v.shape, dtype=v.dtype, pin_memory=True)
+            host.copy_(v, non_blocking=True)
+            pending.append(v.device)
+            return host
+        return v
+    result = to_cpu(result)
+    for dev in set(pending):
+        torch.cuda.current_stream(dev).synchronize()
+    return result
+
+
+def decode_quantized_batch(batch):
+    """utils/dataset.py:482-502."""
+    result = decode_batch_info(batch)
+    cps = batch['channels_per_sample']
+    assert cps.numel() > 0
+    assert bool((cps == cps[0]).all())
+    B, C = result['size'], int(cps[0])
+    _, H, W = batch['data'].size()
+    result['data'] = batch['data'].view(B, C, H, W)
+    return result

@@ -116,6 +116,20 @@ def main():
         for k, v in back['events'].items():
             out[f'{name}/back/{k}'] = v.numpy()
         out[f'{name}/back/sample_idx'] = back['sample_idx'].numpy()
+    # utils/dataset.py:429-502 encode_quantized_batch / decode_quantized_batch on a small quantized batch
+    g = torch.Generator().manual_seed(5)
+    qb = {'data': torch.rand(3, 4, 6, 8, generator=g), 'timestamps': cases['fixture']['timestamps'],
+          'sample_idx': cases['fixture']['sample_idx'], 'images': torch.randint(0, 256, (10, 1, 6, 8), generator=g).float(),
+          'augmentation_params': {}, 'size': 3}
+    qe = ds.encode_quantized_batch({k: (v.clone() if isinstance(v, torch.Tensor) else v) for k, v in qb.items()})
+    qd = ds.decode_quantized_batch(qe)
+    for k in ('data', 'timestamps', 'sample_idx', 'images'):
+        out[f'quant/in/{k}'] = qb[k].numpy()
+    for k in ('data', 'channels_per_sample', 'elements_per_sample', 'timestamps', 'images'):
+        out[f'quant/enc/{k}'] = qe[k].numpy()
+    for k in ('data', 'timestamps', 'sample_idx', 'images'):
+        out[f'quant/dec/{k}'] = qd[k].numpy()
+    out['quant/dec/size'] = np.int64(qd['size'])
     np.savez_compressed(OUT / 'codec.npz', **out)
     print('wrote', OUT / 'codec.npz', {k: out[f'{k}/dec/x'].size for k in cases})
 

@@ -229,3 +229,54 @@ def test_prefetcher_accepts_encoded_batches():
     sel = full['sample_index'] >= 2
     assert sh['size'] == 2 and np.array_equal(sh['events']['x'].cpu().numpy(), full['x'][sel])
     assert np.array_equal(sh['events']['sample_index'].cpu().numpy(), full['sample_index'][sel] - 2)
+
+
+def _quant_case():
+    inp = {k.split('/')[-1]: torch.from_numpy(G[k]) for k in G.files if k.startswith('quant/in/')}
+    enc = {k.split('/')[-1]: G[k] for k in G.files if k.startswith('quant/enc/')}
+    dec = {k.split('/')[-1]: G[k] for k in G.files if k.startswith('quant/dec/')}
+    return inp, enc, dec
+
+
+def test_quantized_batch_codec_matches_reference_on_cpu():
+    """utils/dataset.py:429-502 on host tensors (pure data plumbing: runs without the library)."""
+    from dvs_of_training_framework_b200 import dataset as ds
+    inp, enc, dec = _quant_case()
+    got = ds.encode_quantized_batch(dict(inp, augmentation_params={}, size=3))
+    for k, v in enc.items():
+        assert got[k].dtype == torch.from_numpy(v).dtype and np.array_equal(got[k].numpy(), v), k
+    back = ds.decode_quantized_batch(got)
+    for k in ('data', 'timestamps', 'sample_idx', 'images'):
+        assert back[k].dtype == torch.from_numpy(dec[k]).dtype and np.array_equal(back[k].numpy(), dec[k]), k
+    assert back['size'] == int(dec['size'])
+
+
+@pytest.mark.gpu
+def test_quantized_batch_codec_from_device_and_quantize_batch():
+    """encode_quantized_batch on a device batch (scripts/quantize_preprocessed.py:77-93) lands on the
+    CPU with the reference's values; quantize_batch gives the same event image from the training form
+    and from the storage form."""
+    import dvs_of_training_framework_b200 as dv
+    inp, enc, dec = _quant_case()
+    got = dv.encode_quantized_batch({**{k: v.cuda() for k, v in inp.items()}, 'augmentation_params': {}, 'size': 3})
+    for k, v in enc.items():
+        assert not got[k].is_cuda and np.array_equal(got[k].numpy(), v), k
+    g = np.random.default_rng(8)
+    B, H, W, n = 3, 40, 56, 2000
+    ev = {'x': torch.from_numpy(g.integers(0, W, B * n)), 'y': torch.from_numpy(g.integers(0, H, B * n)),
+          'timestamp': torch.from_numpy(np.concatenate([np.sort(g.random(n)) for _ in range(B)]).astype(np.float32)),
+          'polarity': torch.from_numpy(g.integers(0, 2, B * n) * 2 - 1),
+          'element_index': torch.zeros(B * n, dtype=torch.int64),
+          'sample_index': torch.arange(B).repeat_interleave(n)}
+    batch = {'events': {k: v.cuda() for k, v in ev.items()}, 'timestamps': torch.tensor([0., 1.] * B).cuda(),
+             'sample_idx': torch.arange(B).repeat_interleave(2).cuda(),
+             'images': torch.zeros(2 * B, 1, H, W).cuda(), 'augmentation_params': {}, 'size': B}
+    q = dv.quantize_batch(batch)
+    want = eo.compute_event_image({k: v.numpy() for k, v in ev.items()}, batch['timestamps'].cpu().numpy(),
+                                  batch['sample_idx'].cpu().numpy(), dv.extend_size((H, W)))
+    assert 'events' not in q and np.array_equal(q['data'].cpu().numpy(), want)
+    stored = dv.encode_batch(batch['events'], batch['timestamps'], batch['sample_idx'], batch['images'], {}, B)
+    q2 = dv.quantize_batch(stored)
+    assert torch.equal(q2['data'], q['data']) and q2['size'] == B
+    host = dv.encode_quantized_batch(q2)
+    assert host['data'].shape == (B * 4,) + tuple(dv.extend_size((H, W))) and host['data'].is_pinned()
