@@ -65,6 +65,22 @@ __device__ __forceinline__ void pdl_launch_dependents() {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// A pointer to data the PREDECESSOR writes must be passed through here after the wait: loads
+// through `const T* __restrict__` are invariant loads for the compiler, which moves them above the
+// wait's asm statement (seen in SASS: the match_idx loads of the forward loss sweep sat 260
+// instructions before ACQBULK and read the previous contents of the buffer).  The empty asm makes
+// the pointer's value unknown until the wait has executed, so nothing can be loaded through it
+// earlier.
+template <typename P>                               // P: a (possibly __restrict__) pointer type
+__device__ __forceinline__ void pdl_acquire(P& p) {
+    static_assert(sizeof(P) == 8, "pointers only");
+    asm volatile("" : "+l"(p) : : "memory");
+}
+template <typename... Ps>
+__device__ __forceinline__ void pdl_wait_for(Ps&... ptrs) {
+    pdl_wait();
+    (pdl_acquire(ptrs), ...);
+}
 
 // streaming (evict-first) loads for data touched exactly once
 template <typename T>

@@ -157,7 +157,7 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
         }
         // grouping check (net.py:131-134): sample_index must be non-decreasing
         long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
-        if (!waited) { pdl_wait(); waited = true; }   // `out` zeroed + `sd` ready from here on
+        if (!waited) { pdl_wait_for(sd); waited = true; }   // `out` zeroed + `sd` ready from here on
         if (valid) {
             const int64_t nxt = 4 * (i + 1);
             if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : bb.y;
@@ -169,7 +169,7 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             flags |= scatter_event(xb.y, yb.y, tt.w, pb.y, bb.y, sd, n_samples, H, W, out);
         }
     }
-    if (!waited) pdl_wait();
+    if (!waited) pdl_wait_for(sd);
     // tail (n % 4 events): first threads of block 0
     if (blockIdx.x == 0) {
         const int64_t i = (nvec << 2) + threadIdx.x;
@@ -209,7 +209,7 @@ encode_vec2_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             tt = __ldcs(reinterpret_cast<const float2*>(t) + i);
         }
         long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
-        if (!waited) { pdl_wait(); waited = true; }
+        if (!waited) { pdl_wait_for(sd); waited = true; }
         if (valid) {
             const int64_t nxt = 2 * (i + 1);
             if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : ba.y;
@@ -218,7 +218,7 @@ encode_vec2_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             flags |= scatter_event(xa.y, ya.y, tt.y, pa.y, ba.y, sd, n_samples, H, W, out);
         }
     }
-    if (!waited) pdl_wait();
+    if (!waited) pdl_wait_for(sd);
     if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
         const int64_t i = n - 1;
         flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
@@ -262,7 +262,7 @@ encode_pipe_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     unsigned flags = 0;
     int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);   // warp-uniform
     EventPair cur = load_pair(x, y, t, p, b, base + lane, base + lane < nvec);
-    pdl_wait();                                   // `out` zeroed + `sd` ready from here on
+    pdl_wait_for(sd);                        // `out` zeroed + `sd` ready from here on
     while (base < nvec) {
         const int64_t i = base + lane, nbase = base + stride;
         const bool valid = i < nvec;
@@ -360,7 +360,7 @@ encode_tma_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     unsigned flags = 0;
     int s = 0;
     unsigned parity = 0;
-    pdl_wait();   // the first STAGES chunks are already in flight
+    pdl_wait_for(sd);   // the first STAGES chunks are already in flight
     for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
         tma::mbar_wait(&full[s], parity);
         const int64_t* sx = reinterpret_cast<const int64_t*>(stage_ptr(s, 0));
@@ -396,7 +396,7 @@ encode_scalar_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ 
                      uint32_t* __restrict__ status) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     unsigned flags = 0;
-    pdl_wait();
+    pdl_wait_for(sd);
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         const int64_t bi = __ldcs(b + i);
         if (i + 1 < n && bi > b[i + 1]) flags |= DVSOF_ST_NOT_GROUPED;

@@ -123,7 +123,7 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     uint16_t* codes_s = reinterpret_cast<uint16_t*>(stage_raw + kBinChunk * sizeof(float));
     __shared__ int s_sample;
     pdl_launch_dependents();
-    pdl_wait();                                       // ends[] come from the prepare kernel
+    pdl_wait_for(ends);                                     // ends[] come from the prepare kernel
     chunk_prefix<kBinThreads>(ends, n_samples, prefix);
     const int chunk = blockIdx.x;
     unsigned flags = 0;
@@ -224,7 +224,7 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
                      float* __restrict__ out) {
     extern __shared__ __align__(16) unsigned slab[];   // [cells] counts, then [cells] max keys
     __shared__ int prefix[kBinMaxSamples + 1];
-    pdl_wait();                                         // records + tables come from pass 1
+    pdl_wait_for(codes_g, ts_g, table, ends, sd);                                       // records + tables come from pass 1
     const int s = blockIdx.x / T, tile = blockIdx.x - s * T;
     const int R = 1 << r_log2, cells = R * W * 2;
     unsigned* cnt = slab;

@@ -284,7 +284,7 @@ resize_bilinear_kernel(const float* __restrict__ src, int Hin, int Win, float* _
         }
         cta -= side_ctas;
     }
-    pdl_wait();                                  // src may be the previous level of the chain
+    pdl_wait_for(src);                           // src may be the previous level of the chain
     const int cta_y = cta / col_ctas, cta_x = cta - cta_y * col_ctas;
     const int row0 = (cta_y * kRWarps + (threadIdx.x >> 5)) * kRY;
     const int xb = (cta_x * 32 + (threadIdx.x & 31)) * kRX;

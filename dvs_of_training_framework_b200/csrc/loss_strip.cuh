@@ -213,7 +213,7 @@ warp_loss_strip_kernel(const __grid_constant__ ScaleTable tab, const int32_t* __
     // the flow is an input of the call: its tile is staged while the prelude (pyramid levels,
     // match_idx, tile counts, tickets) may still be running
     stage_flow_strip_tile(F, flow, plane, H, W, tc.y0, tc.x0);
-    pdl_wait();
+    pdl_wait_for(match_idx, n_bad_in);             // both come from the prelude (see pdl_acquire)
 
     const int lane = threadIdx.x & 31;
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform

@@ -564,7 +564,7 @@ decode_events_kernel(const int16_t* __restrict__ x, const int16_t* __restrict__ 
             xs[k] = k < cnt ? x[i0 + k] : 0; ys[k] = k < cnt ? y[i0 + k] : 0; ps[k] = k < cnt ? pol[i0 + k] : 0;
         }
     }
-    pdl_wait();
+    pdl_wait_for(v.elem_begin, v.elem_local, v.elem_sample);
     // element of the first event by search, of the following ones by walking (empty elements skipped)
     int64_t e = E > 0 ? upper_slot(v.elem_begin, E, i0) : 0;
     if (e >= E) e = E > 0 ? E - 1 : 0;                       // counts do not cover the events: flagged by the plan
@@ -627,7 +627,7 @@ encode_events_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ 
             ss[k] = on ? __ldcs(smp + i0 + k) : 0;
         }
     }
-    pdl_wait();                                    // sample_shift comes from codec_plan_kernel
+    pdl_wait_for(v.sample_shift);                                  // sample_shift comes from codec_plan_kernel
 #pragma unroll
     for (int k = 0; k < kCodecPer; ++k) {
         const bool on = k < cnt;

@@ -412,3 +412,62 @@ def test_pyramid_chain_and_tile_counts_through_the_abi(B, H, W, n_scales):
         gy = (ys + f[:, 1]) / ((h - 1) / 2) - 1 if h > 1 else torch.full_like(f[:, 1], float('nan'))
         bad = ((gx < -1) | (gx > 1) | (gy < -1) | (gy > 1)).flatten(1).sum(1).int()
         assert torch.equal(n_bad[s], bad), f'border count, scale {s}'
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('fused', [False, True])
+def test_sweep_reads_match_idx_only_after_the_prelude(fused):
+    """The sweep starts under the prelude (programmatic dependent launch) and may touch what the
+    prelude writes only after griddepcontrol.wait.  The compiler once hoisted the `match_idx`
+    loads of the forward sweep above the wait (invariant loads through a const __restrict__
+    pointer): at cfg4 size, where the prelude leaves SMs free for early sweep CTAs, the sweep then
+    warped whatever frames the buffer's previous contents named (or faulted on garbage).  Here the
+    buffer is poisoned before every call with an index that is valid (no fault) but wrong, and the
+    frames are shuffled so that a wrong index changes the photometric term.  Expected values: the
+    single-scale kernels (no dependent launch) on explicitly gathered frames."""
+    import ctypes
+    import dvs_of_training_framework_b200 as dv
+    from dvs_of_training_framework_b200.loss import _fill_frames
+    L = dv._lib
+    dev = torch.device('cuda', 0)
+    B, H, W = 16, 480, 640
+    inp = synth_loss_inputs(77, B, H, W, 3.0, device='cuda')
+    ts = inp['timestamps'].clone()
+    for b in range(B):
+        ts[2 * b:2 * b + 2] += 0.1 * b
+    perm = torch.randperm(2 * B, generator=torch.Generator().manual_seed(5)).cuda()
+    inv = torch.argsort(perm)
+    images = inp['images'][perm].contiguous()
+    fl = [f.contiguous() for f in inp['flows']]
+    S, D = len(fl), 2 * B
+    want = np.zeros((3, S), dtype=np.float32)
+    level = inp['images']
+    for s, (h, w) in enumerate(inp['shapes']):
+        level = dv.interpolate(level, (h, w))                   # utils/loss.py:207-210, chained
+        terms_s = dv.Loss((h, w), B, 'cuda')(level[0::2].contiguous(), level[1::2].contiguous(), fl[s])
+        want[:, s] = [float(v) for v in terms_s]
+    ev = dv.Losses(inp['shapes'], B, 'cuda')
+    plan = ev._plan(dev, B, D, H, W, fl)
+    o = plan.offs
+    buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
+    gbuf = torch.zeros(plan.gtotal, dtype=torch.float32, device=dev)
+    flow_ts, tsp, sidx = ts.view(-1, 2).contiguous(), ts[perm].contiguous(), inp['sample_idx'][perm].contiguous()
+    fr = _fill_frames(plan, images, flow_ts, inp['flow_sample_idx'], tsp, sidx)
+    plan.fill(plan.bwd, buf.data_ptr(), fl, gbuf.data_ptr())
+    coef = (ctypes.c_float * (3 * S))(*([0.5 / S] * S + [1.0 / S] * S + [1.0 / S] * S))
+    st = L.status_for(dev)
+    base = buf.data_ptr()
+    match = buf[o[S]:o[S] + 2 * B].view(torch.int32)
+    terms = buf[o[S + 2]:o[S + 2] + 3 * S]
+    for it in range(40):
+        match.fill_(it % D)                                   # stale contents: valid, wrong
+        if fused:
+            L.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S], base + 4 * o[S + 2],
+                   base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr, L.ptr(st.word), L.stream_ptr(dev))
+        else:
+            L.call('dvsof_multiscale_loss_forward', plan.bwd, fr, base + 4 * o[S], base + 4 * o[S + 2],
+                   base + 4 * o[S + 1], plan.ws_ptr, L.ptr(st.word), L.stream_ptr(dev))
+        st.check()
+        assert torch.equal(match.view(2, B), torch.stack((inv[0::2], inv[1::2])).int()), f'call {it}'
+        np.testing.assert_allclose(terms.cpu().numpy().reshape(3, S), want, rtol=RTOL, atol=ATOL,
+                                   err_msg=f'call {it}')
