@@ -26,9 +26,21 @@
 
 namespace dvsof {
 
-constexpr int kBinChunk = 8192;       // events per pass-1 chunk
-constexpr int kBinThreads = 512;      // pass-1 CTA: 16 events per thread
-constexpr int kRedBatch = 8;          // pass-2 loads in flight per lane
+#ifndef DVSOF_BIN_CHUNK
+#define DVSOF_BIN_CHUNK 4096
+#endif
+#ifndef DVSOF_BIN_THREADS
+#define DVSOF_BIN_THREADS 256
+#endif
+#ifndef DVSOF_BIN_MIN_CTAS
+#define DVSOF_BIN_MIN_CTAS 4
+#endif
+constexpr int kBinChunk = DVSOF_BIN_CHUNK;       // events per pass-1 chunk
+constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread
+#ifndef DVSOF_RED_BATCH
+#define DVSOF_RED_BATCH 4
+#endif
+constexpr int kRedBatch = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
 constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
 constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
 constexpr int kRedThreads = 512;      // pass-2 CTA: 16 warps stream the runs of one slab, 3 CTAs per SM
@@ -108,7 +120,7 @@ namespace dvsof {
 // ---------------------------------------------------------------------------------------
 // pass 1: partition one chunk of one sample by tile (counting sort in shared memory)
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kBinThreads, 2)
+__global__ void __launch_bounds__(kBinThreads, DVSOF_BIN_MIN_CTAS)
 encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
                   const float* __restrict__ t, const int64_t* __restrict__ p,
                   const int64_t* __restrict__ b, int64_t n, const int64_t* __restrict__ ends,
@@ -217,7 +229,10 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
 // ---------------------------------------------------------------------------------------
 // pass 2: one CTA per (sample, tile): shared-memory slab, then one coalesced write of the bands
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kRedThreads, 3)
+#ifndef DVSOF_RED_MIN_CTAS
+#define DVSOF_RED_MIN_CTAS 3
+#endif
+__global__ void __launch_bounds__(kRedThreads, DVSOF_RED_MIN_CTAS)
 encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restrict__ ts_g,
                      const uint32_t* __restrict__ table, const int64_t* __restrict__ ends,
                      const float2* __restrict__ sd, int n_samples, int H, int W, int r_log2, int T,
@@ -233,31 +248,51 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
     chunk_prefix<kRedThreads>(ends, n_samples, prefix);   // ends with __syncthreads()
     const int cb = prefix[s], nc = prefix[s + 1] - prefix[s];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int c0 = warp * 32; c0 < nc; c0 += (kRedThreads / 32) * 32) {
-        unsigned lo = 0, hi = 0;                          // each lane: the run of one chunk
-        if (c0 + lane < nc) {
-            const uint32_t* row = table + (size_t)(cb + c0 + lane) * (T + 1) + tile;
+    // Runs are short (kBinChunk / T records, one batch of 32 x kRedBatch), so a warp's time is the
+    // latency of one dependent trip to DRAM per run unless the next run is already in flight:
+    // chunks are dealt to the warps round-robin (k-th chunk of warp w = k * kWarps + w: every warp
+    // works even when a sample has few chunks), a lane holds the bounds of one of the warp's next
+    // 32 chunks, and the batch after the current one is requested before the current one is
+    // applied.  Everything that steers the loop is warp-uniform.
+    constexpr int kWarps = kRedThreads / 32;
+    constexpr unsigned kStep = 32 * kRedBatch;
+    const int my_n = nc > warp ? (nc - warp + kWarps - 1) / kWarps : 0;
+    for (int k0 = 0; k0 < my_n; k0 += 32) {
+        unsigned lo = 0, hi = 0;
+        if (k0 + lane < my_n) {
+            const uint32_t* row = table + (size_t)(cb + (k0 + lane) * kWarps + warp) * (T + 1) + tile;
             lo = __ldg(row); hi = __ldg(row + 1);
         }
-        const int m = min(32, nc - c0);
-        for (int j = 0; j < m; ++j) {
-            const unsigned l = __shfl_sync(0xffffffffu, lo, j), h = __shfl_sync(0xffffffffu, hi, j);
-            const size_t base = (size_t)(cb + c0 + j) * kBinChunk;
-            for (unsigned i0 = l; i0 < h; i0 += 32 * kRedBatch) {   // kRedBatch records per lane in flight
-                unsigned code[kRedBatch];
-                float tv[kRedBatch];
+        const int m = min(32, my_n - k0);
+        int j = -1;
+        unsigned i0 = 0, h = 0;
+        auto advance = [&]() {                            // next batch: same run, or the next non-empty one
+            i0 += kStep;
+            while (i0 >= h && ++j < m) { i0 = __shfl_sync(0xffffffffu, lo, j); h = __shfl_sync(0xffffffffu, hi, j); }
+        };
+        auto load = [&](unsigned* code, float* tv) {
+            const size_t base = (size_t)(cb + (k0 + j) * kWarps + warp) * kBinChunk;
 #pragma unroll
-                for (int u = 0; u < kRedBatch; ++u) {
-                    const unsigned i = i0 + u * 32 + lane;
-                    code[u] = 0xffffffffu;
-                    if (i < h) { code[u] = __ldcs(codes_g + base + i); tv[u] = __ldcs(ts_g + base + i); }
-                }
+            for (int u = 0; u < kRedBatch; ++u) {
+                const unsigned i = i0 + u * 32 + lane;
+                code[u] = 0xffffffffu;
+                if (i < h) { code[u] = __ldcs(codes_g + base + i); tv[u] = __ldcs(ts_g + base + i); }
+            }
+        };
+        unsigned code[kRedBatch], ncode[kRedBatch];
+        float tv[kRedBatch], ntv[kRedBatch];
+        advance();
+        if (j < m) load(code, tv);
+        while (j < m) {
+            advance();
+            if (j < m) load(ncode, ntv);
 #pragma unroll
-                for (int u = 0; u < kRedBatch; ++u) {
-                    if (code[u] == 0xffffffffu) continue;
+            for (int u = 0; u < kRedBatch; ++u) {
+                if (code[u] != 0xffffffffu) {
                     atomicAdd(&cnt[code[u]], 1u);                // scatter_sum, net.py:147-148
                     atomicMax(&key[code[u]], ordered_key(tv[u]));   // scatter_max of the raw t, net.py:149
                 }
+                code[u] = ncode[u]; tv[u] = ntv[u];
             }
         }
     }
