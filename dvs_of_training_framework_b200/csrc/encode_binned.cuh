@@ -9,7 +9,8 @@
 // so the stream is first PARTITIONED by output row band:
 //
 //   pass 1 (bin):    a CTA takes a chunk of kBinChunk consecutive events of ONE sample, counting-
-//                    sorts them by tile (band of 2^r rows) in shared memory and writes them back
+//                    sorts them by tile (band of 2^r rows) in shared memory (one shared atomic per
+//                    event: histogram and rank inside the tile's run at once) and writes them back
 //                    as 6-byte records {u16 cell-in-tile, f32 t} -- contiguous per (chunk, tile)
 //                    run -- plus the chunk's run table.  HBM: 36 B read + 6 B written per event.
 //   pass 2 (reduce): a CTA owns one (sample, tile): its slab of {u32 count, s32 max-key} lives in
@@ -43,8 +44,12 @@ constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per th
 constexpr int kRedBatch = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
 constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
 constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
-constexpr int kRedThreads = 512;      // pass-2 CTA: 16 warps stream the runs of one slab, 3 CTAs per SM
+#ifndef DVSOF_RED_THREADS
+#define DVSOF_RED_THREADS 512
+#endif
+constexpr int kRedThreads = DVSOF_RED_THREADS;      // pass-2 CTA: 16 warps stream the runs of one slab, 3 CTAs per SM
 constexpr size_t kBinSlabBytes = 32 * 1024;
+static_assert(kBinChunk <= 4096 && kBinMaxTiles <= 128 && kBinSlabBytes / 8 <= 4096, "packed record of pass 1");
 constexpr int kBinStageBytes = kBinChunk * (sizeof(float) + sizeof(uint16_t));   // pass-1 staging
 
 struct BinPlan {
@@ -67,7 +72,7 @@ inline BinPlan make_bin_plan(int64_t n, int64_t B, int H, int W) {
     p.r_log2 = r; p.R = 1 << r;
     p.T = (H + p.R - 1) >> r;
     p.cells = p.R * W * 2;
-    if (p.T > kBinMaxTiles || p.cells > 65536) return p;
+    if (p.T > kBinMaxTiles || p.cells > 4096) return p;          // code: 12 bits, tile: 7, rank in a chunk: 12
     p.max_chunks = n / kBinChunk + B + 1;
     p.off_codes = p.total;
     p.off_ts = p.off_codes + round_up((size_t)p.max_chunks * kBinChunk * sizeof(uint16_t), 256);
@@ -158,7 +163,7 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     const int64_t e0 = s_begin + (int64_t)(chunk - prefix[s]) * kBinChunk;
     const int64_t e1 = min(e0 + (int64_t)kBinChunk, ends[s]);
     constexpr int kPer = kBinChunk / kBinThreads;     // 16 events per thread
-    unsigned packed[kPer];                            // tile << 16 | code, 0xffffffff = dropped
+    unsigned packed[kPer];                            // rank | tile | code, 0xffffffff = dropped
     float tv[kPer];
 #pragma unroll
     for (int k = 0; k < kPer; k += 2) {               // two events in flight per thread and step
@@ -183,8 +188,10 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             const unsigned yy = (unsigned)yi[j], tile = yy >> r_log2;
             const unsigned c = (unsigned)(1 - (int)pi[j]) >> 1;                   // net.py:142
             const unsigned code = (((yy & ((1u << r_log2) - 1u)) * (unsigned)W + (unsigned)xi[j]) << 1) | c;
-            packed[k + j] = (tile << 16) | code;
-            atomicAdd(&hist[tile], 1u);
+            // ONE contended shared atomic per event: its return value is the event's rank inside
+            // the tile's run (the order inside a run is free: sum and max commute)
+            const unsigned rank = atomicAdd(&hist[tile], 1u);
+            packed[k + j] = (rank << 19) | (tile << 12) | code;    // 12 + 7 + 12 bits (make_bin_plan)
         }
     }
     __syncthreads();
@@ -212,8 +219,8 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
         if (packed[k] == 0xffffffffu) continue;
-        const unsigned pos = atomicAdd(&cursor[packed[k] >> 16], 1u);
-        codes_s[pos] = (uint16_t)(packed[k] & 0xffffu);
+        const unsigned pos = cursor[(packed[k] >> 12) & 127u] + (packed[k] >> 19);
+        codes_s[pos] = (uint16_t)(packed[k] & 0xfffu);
         ts_s[pos] = tv[k];
     }
     __syncthreads();
