@@ -33,8 +33,11 @@ namespace dvsof {
 #ifndef DVSOF_BIN_THREADS
 #define DVSOF_BIN_THREADS 256
 #endif
+#ifndef DVSOF_BIN_INFLIGHT
+#define DVSOF_BIN_INFLIGHT 4
+#endif
 #ifndef DVSOF_BIN_MIN_CTAS
-#define DVSOF_BIN_MIN_CTAS 4
+#define DVSOF_BIN_MIN_CTAS 3
 #endif
 constexpr int kBinChunk = DVSOF_BIN_CHUNK;       // events per pass-1 chunk
 constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread
@@ -163,14 +166,16 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     const int64_t e0 = s_begin + (int64_t)(chunk - prefix[s]) * kBinChunk;
     const int64_t e1 = min(e0 + (int64_t)kBinChunk, ends[s]);
     constexpr int kPer = kBinChunk / kBinThreads;     // 16 events per thread
+    constexpr int kFly = DVSOF_BIN_INFLIGHT;
+    static_assert(kPer % kFly == 0, "whole load steps");
     unsigned packed[kPer];                            // rank | tile | code, 0xffffffff = dropped
     float tv[kPer];
 #pragma unroll
-    for (int k = 0; k < kPer; k += 2) {               // two events in flight per thread and step
-        int64_t xi[2], yi[2], pi[2], bi[2];
-        bool ok[2];
+    for (int k = 0; k < kPer; k += kFly) {            // kFly events in flight per thread and step
+        int64_t xi[kFly], yi[kFly], pi[kFly], bi[kFly];
+        bool ok[kFly];
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int j = 0; j < kFly; ++j) {
             const int64_t i = e0 + (int64_t)(k + j) * kBinThreads + threadIdx.x;
             ok[j] = i < e1;
             if (ok[j]) {
@@ -179,7 +184,7 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             }
         }
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int j = 0; j < kFly; ++j) {
             packed[k + j] = 0xffffffffu;
             if (!ok[j]) continue;
             if (pi[j] != 1 && pi[j] != -1) { flags |= DVSOF_ST_BAD_POLARITY; continue; }
