@@ -548,7 +548,7 @@ static bool use_binned(const BinPlan& plan, int64_t n, int64_t B, int H, int W, 
     const int ov = encode_path_override();
     if (ov == 1) return false;
     if (ov == 2) return true;
-    // measured (profiles/r01bm_binned_launches_cfg3.csv, cfg3: 160 M events on 32 x 256^2): bin 1.25 ms +
+    // measured (profiles/r01bz_binned_launches_cfg3.csv, cfg3: 160 M events on 32 x 256^2): bin 1.02 ms +
     // reduce 0.31 ms vs 1.96 ms direct.  Worth it only when the stream is dense -- at ~2 events per
     // cell (cfg4) the direct path's REDs are cheaper than the extra 12 B/event of record traffic.
     return n >= (4 << 20) && n >= 8 * B * (int64_t)H * W;

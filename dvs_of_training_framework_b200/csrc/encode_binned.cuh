@@ -40,7 +40,7 @@ namespace dvsof {
 #define DVSOF_BIN_MIN_CTAS 3
 #endif
 constexpr int kBinChunk = DVSOF_BIN_CHUNK;       // events per pass-1 chunk
-constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread
+constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread, DVSOF_BIN_INFLIGHT at a time
 #ifndef DVSOF_RED_BATCH
 #define DVSOF_RED_BATCH 4
 #endif
