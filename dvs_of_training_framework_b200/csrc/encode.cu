@@ -549,9 +549,14 @@ static bool use_binned(const BinPlan& plan, int64_t n, int64_t B, int H, int W, 
     if (ov == 1) return false;
     if (ov == 2) return true;
     // measured (profiles/r01bz_binned_launches_cfg3.csv, cfg3: 160 M events on 32 x 256^2): bin 1.02 ms +
-    // reduce 0.31 ms vs 1.96 ms direct.  Worth it only when the stream is dense -- at ~2 events per
-    // cell (cfg4) the direct path's REDs are cheaper than the extra 12 B/event of record traffic.
-    return n >= (4 << 20) && n >= 8 * B * (int64_t)H * W;
+    // reduce 0.31 ms vs 1.96 ms direct.  The records cost 12 B/event of extra traffic and pass 2 runs
+    // B * T CTAs, so it pays for dense streams: from ~11 events per pixel with 8 samples of 256^2
+    // (256 pass-2 CTAs; profiles/r01by_encoder_size_sweep_direct_vs_binned.jsonl), and already at 3.4
+    // events per pixel on cfg4 (16 x 480 x 640: 1920 pass-2 CTAs, 217 us vs 234 us direct;
+    // profiles/r01cb_binned_launches_cfg4.csv).
+    const int64_t pixels = B * (int64_t)H * W;
+    const bool many_ctas = B * (int64_t)plan.T >= 2 * 3 * kNumSMs;     // two full waves of pass 2
+    return n >= (4 << 20) && n >= (many_ctas ? 3 : 8) * pixels;
 }
 
 extern "C" size_t dvsof_encode_workspace_bytes(int64_t n_events, int64_t n_samples, int32_t H, int32_t W) {
@@ -690,7 +695,9 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(encode_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(encode_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytes);
+            e = cudaFuncSetAttribute(encode_reduce_kernel<kRedBatchLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(encode_reduce_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_binned smem attr: %s", cudaGetErrorString(e));
         configured = true;
     }
@@ -700,7 +707,12 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
                                kBinStageBytes, stream, true, a.x, a.y, a.t, a.p, a.b, a.n, ends, a.B, a.H,
                                a.W, plan.r_log2, plan.T, codes, ts, table, a.status))
         return rc;
-    return launch_kernel("encode_reduce_kernel", encode_reduce_kernel, a.B * plan.T, kRedThreads,
+    // runs hold ~kBinChunk / T records: one record per lane and batch when that is at most two warps' worth
+    if (kBinChunk / plan.T <= 64)
+        return launch_kernel("encode_reduce_kernel<1>", encode_reduce_kernel<1>, a.B * plan.T, kRedThreads,
+                             (size_t)plan.cells * 8, stream, true, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                             plan.r_log2, plan.T, a.out);
+    return launch_kernel("encode_reduce_kernel", encode_reduce_kernel<kRedBatchLong>, a.B * plan.T, kRedThreads,
                          (size_t)plan.cells * 8, stream, true, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                          plan.r_log2, plan.T, a.out);
 }

@@ -44,15 +44,16 @@ constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per th
 #ifndef DVSOF_RED_BATCH
 #define DVSOF_RED_BATCH 4
 #endif
-constexpr int kRedBatch = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
+constexpr int kRedBatchLong = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
 constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
 constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
 #ifndef DVSOF_RED_THREADS
 #define DVSOF_RED_THREADS 512
 #endif
 constexpr int kRedThreads = DVSOF_RED_THREADS;      // pass-2 CTA: 16 warps stream the runs of one slab, 3 CTAs per SM
-constexpr size_t kBinSlabBytes = 32 * 1024;
-static_assert(kBinChunk <= 4096 && kBinMaxTiles <= 128 && kBinSlabBytes / 8 <= 4096, "packed record of pass 1");
+constexpr size_t kBinSlabBytes = 32 * 1024;      // preferred slab (3 CTAs/SM and 32 row bands at 256^2)
+constexpr size_t kBinSlabBytesMax = 64 * 1024;   // wide images
+static_assert(kBinChunk <= 4096 && kBinMaxTiles <= 128 && kBinSlabBytesMax / 8 <= 8192, "packed record of pass 1");
 constexpr int kBinStageBytes = kBinChunk * (sizeof(float) + sizeof(uint16_t));   // pass-1 staging
 
 struct BinPlan {
@@ -69,13 +70,16 @@ inline BinPlan make_bin_plan(int64_t n, int64_t B, int H, int W) {
     p.total = p.off_ends + round_up((size_t)(B > 0 ? B : 1) * sizeof(int64_t), 256);
     if (n <= 0 || B <= 0 || B > kBinMaxSamples) return p;
     int r = 0;
-    while (((size_t)2 << r) * W * 16 <= kBinSlabBytes) ++r;        // largest 2^r rows within the slab
-    if ((size_t)(1 << r) * W * 16 > kBinSlabBytes) return p;          // one row does not fit
+    while (((size_t)2 << r) * W * 16 <= kBinSlabBytes) ++r;        // largest 2^r rows within the preferred slab
+    if ((size_t)(1 << r) * W * 16 > kBinSlabBytesMax) return p;       // one row does not fit
     while (r > 0 && (1 << (r - 1)) >= H) --r;                          // no taller than the image
+    // wide images: more rows per slab (up to kBinSlabBytesMax) until the tile index fits its 7 bits
+    while (((H + (1 << r) - 1) >> r) > kBinMaxTiles - 1 && ((size_t)2 << r) * W * 16 <= kBinSlabBytesMax) ++r;
     p.r_log2 = r; p.R = 1 << r;
     p.T = (H + p.R - 1) >> r;
     p.cells = p.R * W * 2;
-    if (p.T > kBinMaxTiles || p.cells > 4096) return p;          // code: 12 bits, tile: 7, rank in a chunk: 12
+    // packed pass-1 record: code 13 bits, tile 7 (127 = the dropped marker's), rank in a chunk 12
+    if (p.T > kBinMaxTiles - 1 || p.cells > 8192 || (size_t)p.cells * 8 > kBinSlabBytesMax) return p;
     p.max_chunks = n / kBinChunk + B + 1;
     p.off_codes = p.total;
     p.off_ts = p.off_codes + round_up((size_t)p.max_chunks * kBinChunk * sizeof(uint16_t), 256);
@@ -196,7 +200,7 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             // ONE contended shared atomic per event: its return value is the event's rank inside
             // the tile's run (the order inside a run is free: sum and max commute)
             const unsigned rank = atomicAdd(&hist[tile], 1u);
-            packed[k + j] = (rank << 19) | (tile << 12) | code;    // 12 + 7 + 12 bits (make_bin_plan)
+            packed[k + j] = (rank << 20) | (tile << 13) | code;    // 12 + 7 + 13 bits (make_bin_plan)
         }
     }
     __syncthreads();
@@ -224,8 +228,8 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
 #pragma unroll
     for (int k = 0; k < kPer; ++k) {
         if (packed[k] == 0xffffffffu) continue;
-        const unsigned pos = cursor[(packed[k] >> 12) & 127u] + (packed[k] >> 19);
-        codes_s[pos] = (uint16_t)(packed[k] & 0xfffu);
+        const unsigned pos = cursor[(packed[k] >> 13) & 127u] + (packed[k] >> 20);
+        codes_s[pos] = (uint16_t)(packed[k] & 0x1fffu);
         ts_s[pos] = tv[k];
     }
     __syncthreads();
@@ -244,6 +248,7 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
 #ifndef DVSOF_RED_MIN_CTAS
 #define DVSOF_RED_MIN_CTAS 3
 #endif
+template <int kRedBatch>                       // records per lane and batch: 4 for runs of ~128, 1 for short runs (wide images)
 __global__ void __launch_bounds__(kRedThreads, DVSOF_RED_MIN_CTAS)
 encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restrict__ ts_g,
                      const uint32_t* __restrict__ table, const int64_t* __restrict__ ends,

@@ -159,6 +159,23 @@ def test_binned_equals_direct_bitwise_dense(monkeypatch):
     assert np.array_equal(outs['binned'].cpu().numpy(), want)
 
 
+@pytest.mark.parametrize('H,W', [(272, 640), (256, 1024), (480, 640)])
+def test_binned_wide_images_bitwise(monkeypatch, H, W):
+    """Wide images: more than 127 two-row bands -> the plan takes 4 rows per slab (40-64 KB of
+    shared memory, 13-bit cell codes) and pass 2 its short-run variant (one record per lane and
+    batch); (256, 1024) fills the 64 KB / 8192-cell limit exactly."""
+    B, n = 2, 150_000
+    ev, ts, sidx = synth_events(91 + W, B, H, W, n, contended=True)
+    outs = {}
+    for p in ('direct', 'binned'):
+        monkeypatch.setenv('DVSOF_ENCODE_PATH', p)
+        outs[p] = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert torch.equal(outs['direct'], outs['binned'])
+    assert int(outs['binned'][:, :2].sum()) == B * n
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    assert np.array_equal(outs['binned'].cpu().numpy(), want)
+
+
 def test_default_path_selection_large_stream_is_exact():
     """>= 4 M events and >= 8 events per cell -> the library picks the binned path by itself."""
     B, H, W, n = 2, 64, 64, 2_200_000
