@@ -479,8 +479,9 @@ def cpu_encoder_pass(name, threads=None):
     from oracle import encoder_oracle_torch as eot
     import dvs_of_training_framework_b200 as dv
     c = CFG[name]
-    if threads:
-        torch.set_num_threads(threads)
+    # all the host threads this process may use -- torchrun exports OMP_NUM_THREADS=1, which would
+    # time the reference on one core
+    torch.set_num_threads(threads or len(os.sched_getaffinity(0)))
     ev, ts, sidx = fast_events(1234 + int(name[3:]), c['B'], c['H'], c['W'], c['n'], c['T'], 'cpu')
     size = dv.extend_size((c['H'], c['W']))
     return (lambda: eot.compute_event_image(ev, ts, sidx, size)), c['B'] * c['n']
