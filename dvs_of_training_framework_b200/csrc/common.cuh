@@ -43,6 +43,19 @@ inline int launch_kernel(const char* what, void (*kern)(KArgs...), int grid, int
     return DVSOF_OK;
 }
 
+// Function attributes (dynamic shared memory opt-in) are per DEVICE: `mask` holds one bit per device
+// ordinal on which the caller has configured its kernels.  Returns true when the current device
+// still needs it (a race between threads only repeats the cheap call); devices >= 64 always do.
+inline bool needs_device_setup(const unsigned long long& mask, int* dev_out) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    *dev_out = dev;
+    return dev >= 64 || !((__atomic_load_n(&mask, __ATOMIC_RELAXED) >> dev) & 1ull);
+}
+inline void device_setup_done(unsigned long long& mask, int dev) {
+    if (dev < 64) __atomic_fetch_or(&mask, 1ull << dev, __ATOMIC_RELAXED);
+}
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 

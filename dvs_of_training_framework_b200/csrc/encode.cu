@@ -181,212 +181,6 @@ encode_vec4_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
     if (flags) atomicOr(status, flags);
 }
 
-// 2 events per thread per iteration: half the live registers of the vec4 kernel -> twice the
-// resident warps to cover DRAM latency (the REDs are fire-and-forget, only the loads stall).
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB)
-encode_vec2_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
-                   const float* __restrict__ t, const int64_t* __restrict__ p,
-                   const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
-                   int n_samples, int H, int W, float* __restrict__ out,
-                   uint32_t* __restrict__ status) {
-    const int lane = threadIdx.x & 31;
-    const int64_t nvec = n >> 1;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    unsigned flags = 0;
-    bool waited = false;
-    for (int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < nvec;
-         base += stride) {
-        const int64_t i = base + lane;
-        const bool valid = i < nvec;
-        longlong2 xa, ya, pa, ba = make_longlong2(0, 0);
-        float2 tt;
-        if (valid) {
-            xa = __ldcs(reinterpret_cast<const longlong2*>(x) + i);
-            ya = __ldcs(reinterpret_cast<const longlong2*>(y) + i);
-            pa = __ldcs(reinterpret_cast<const longlong2*>(p) + i);
-            ba = __ldcs(reinterpret_cast<const longlong2*>(b) + i);
-            tt = __ldcs(reinterpret_cast<const float2*>(t) + i);
-        }
-        long long bnext = __shfl_down_sync(0xffffffffu, ba.x, 1);
-        if (!waited) { pdl_wait_for(sd); waited = true; }
-        if (valid) {
-            const int64_t nxt = 2 * (i + 1);
-            if (lane == 31 || i + 1 >= nvec) bnext = (nxt < n) ? b[nxt] : ba.y;
-            if (ba.x > ba.y || ba.y > bnext) flags |= DVSOF_ST_NOT_GROUPED;
-            flags |= scatter_event(xa.x, ya.x, tt.x, pa.x, ba.x, sd, n_samples, H, W, out);
-            flags |= scatter_event(xa.y, ya.y, tt.y, pa.y, ba.y, sd, n_samples, H, W, out);
-        }
-    }
-    if (!waited) pdl_wait_for(sd);
-    if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
-        const int64_t i = n - 1;
-        flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
-    }
-    if (flags) atomicOr(status, flags);
-}
-
-// Software-pipelined persistent variant: 2 events per thread per iteration, the loads of
-// iteration k+1 are issued BEFORE the reductions of iteration k, so that one thread always has a
-// DRAM request in flight while its REDs drain into L2 -- in the one-pass kernels above a short
-// stream (cfg2: 1 M events = 3.5 events per resident thread) runs as "everybody loads, then
-// everybody reduces".  Measured (profiles/r01ab_variants.jsonl): no gain -- cfg2 stays at 22.6 us
-// with 2 or 4 CTAs/SM of this kernel exactly as with every one-pass variant, cfg3/cfg4 lose 10-15 %
-// to the smaller grid.  Kept as experiment variants 12 / 14; the cfg2 time is not a scheduling
-// artefact of the one-pass kernels.
-struct EventPair { longlong2 x, y, p, b; float2 t; };
-__device__ __forceinline__ EventPair load_pair(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
-                                               const float* __restrict__ t, const int64_t* __restrict__ p,
-                                               const int64_t* __restrict__ b, int64_t i, bool valid) {
-    EventPair e;
-    e.b = make_longlong2(0, 0);
-    if (valid) {
-        e.x = __ldcs(reinterpret_cast<const longlong2*>(x) + i);
-        e.y = __ldcs(reinterpret_cast<const longlong2*>(y) + i);
-        e.p = __ldcs(reinterpret_cast<const longlong2*>(p) + i);
-        e.b = __ldcs(reinterpret_cast<const longlong2*>(b) + i);
-        e.t = __ldcs(reinterpret_cast<const float2*>(t) + i);
-    }
-    return e;
-}
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB)
-encode_pipe_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
-                   const float* __restrict__ t, const int64_t* __restrict__ p,
-                   const int64_t* __restrict__ b, int64_t n, const float2* __restrict__ sd,
-                   int n_samples, int H, int W, float* __restrict__ out,
-                   uint32_t* __restrict__ status) {
-    const int lane = threadIdx.x & 31;
-    const int64_t nvec = n >> 1;
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    unsigned flags = 0;
-    int64_t base = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31);   // warp-uniform
-    EventPair cur = load_pair(x, y, t, p, b, base + lane, base + lane < nvec);
-    pdl_wait_for(sd);                        // `out` zeroed + `sd` ready from here on
-    while (base < nvec) {
-        const int64_t i = base + lane, nbase = base + stride;
-        const bool valid = i < nvec;
-        const EventPair nxt = load_pair(x, y, t, p, b, nbase + lane, nbase < nvec && nbase + lane < nvec);
-        long long bnext = __shfl_down_sync(0xffffffffu, cur.b.x, 1);
-        if (valid) {
-            const int64_t after = 2 * (i + 1);
-            if (lane == 31 || i + 1 >= nvec) bnext = (after < n) ? b[after] : cur.b.y;
-            if (cur.b.x > cur.b.y || cur.b.y > bnext) flags |= DVSOF_ST_NOT_GROUPED;
-            flags |= scatter_event(cur.x.x, cur.y.x, cur.t.x, cur.p.x, cur.b.x, sd, n_samples, H, W, out);
-            flags |= scatter_event(cur.x.y, cur.y.y, cur.t.y, cur.p.y, cur.b.y, sd, n_samples, H, W, out);
-        }
-        cur = nxt;
-        base = nbase;
-    }
-    if (blockIdx.x == 0 && threadIdx.x == 0 && (n & 1)) {
-        const int64_t i = n - 1;
-        flags |= scatter_event(x[i], y[i], t[i], p[i], b[i], sd, n_samples, H, W, out);
-    }
-    if (flags) atomicOr(status, flags);
-}
-
-// ---------------------------------------------------------------------------------------
-// TMA-staged persistent variant: one elected thread streams whole event chunks
-// (x,y,p,b: CH*8 B each, t: CH*4 B) into a STAGES-deep shared-memory ring with bulk async copies
-// (cp.async.bulk -> UBLKCP, completion on an mbarrier, L2 evict-first policy); all warps consume
-// a landed chunk with conflict-free LDS and issue the two REDs per event.  The HBM stream is
-// decoupled from warp scheduling (no long-scoreboard stalls on the loads) and takes no LSU
-// tag-stage cycles away from the reductions, which are the SM-side bound of this kernel.
-// ---------------------------------------------------------------------------------------
-namespace tma {
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ uint64_t evict_first_policy() {
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar, uint64_t pol) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-        ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
-}
-}  // namespace tma
-
-template <int CH, int STAGES, int THREADS>
-__global__ void __launch_bounds__(THREADS)
-encode_tma_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
-                  const float* __restrict__ t, const int64_t* __restrict__ p,
-                  const int64_t* __restrict__ b, int64_t n, int64_t n_chunks,
-                  const float2* __restrict__ sd, int n_samples, int H, int W,
-                  float* __restrict__ out, uint32_t* __restrict__ status) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr int kStageBytes = CH * 36;
-    __shared__ uint64_t full[STAGES];
-    auto stage_ptr = [&](int s, int field) -> unsigned char* {   // field 0..3 = x,y,p,b ; 4 = t
-        return smem_raw + (size_t)s * kStageBytes + (size_t)field * CH * 8;
-    };
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < STAGES; ++s) tma::mbar_init(&full[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-    uint64_t pol = 0;
-    auto issue = [&](int s, int64_t chunk) {
-        const int64_t e0 = chunk * CH;
-        tma::mbar_expect_tx(&full[s], kStageBytes);
-        tma::bulk_g2s(stage_ptr(s, 0), x + e0, CH * 8, &full[s], pol);
-        tma::bulk_g2s(stage_ptr(s, 1), y + e0, CH * 8, &full[s], pol);
-        tma::bulk_g2s(stage_ptr(s, 2), p + e0, CH * 8, &full[s], pol);
-        tma::bulk_g2s(stage_ptr(s, 3), b + e0, CH * 8, &full[s], pol);
-        tma::bulk_g2s(stage_ptr(s, 4), t + e0, CH * 4, &full[s], pol);
-    };
-    if (threadIdx.x == 0) {
-        pol = tma::evict_first_policy();
-        for (int s = 0; s < STAGES; ++s) {
-            const int64_t c = (int64_t)blockIdx.x + (int64_t)s * gridDim.x;
-            if (c < n_chunks) issue(s, c);
-        }
-    }
-    unsigned flags = 0;
-    int s = 0;
-    unsigned parity = 0;
-    pdl_wait_for(sd);   // the first STAGES chunks are already in flight
-    for (int64_t c = blockIdx.x; c < n_chunks; c += gridDim.x) {
-        tma::mbar_wait(&full[s], parity);
-        const int64_t* sx = reinterpret_cast<const int64_t*>(stage_ptr(s, 0));
-        const int64_t* sy = reinterpret_cast<const int64_t*>(stage_ptr(s, 1));
-        const int64_t* sp = reinterpret_cast<const int64_t*>(stage_ptr(s, 2));
-        const int64_t* sb = reinterpret_cast<const int64_t*>(stage_ptr(s, 3));
-        const float* st = reinterpret_cast<const float*>(stage_ptr(s, 4));
-#pragma unroll
-        for (int j = threadIdx.x; j < CH; j += THREADS) {
-            const int64_t bi = sb[j];
-            int64_t bn;
-            if (j + 1 < CH) bn = sb[j + 1];
-            else { const int64_t nxt = (c + 1) * CH; bn = nxt < n ? __ldg(b + nxt) : bi; }
-            if (bi > bn) flags |= DVSOF_ST_NOT_GROUPED;
-            flags |= scatter_event(sx[j], sy[j], st[j], sp[j], bi, sd, n_samples, H, W, out);
-        }
-        __syncthreads();   // every warp is done reading stage s
-        if (threadIdx.x == 0) {
-            const int64_t nc = c + (int64_t)STAGES * gridDim.x;
-            if (nc < n_chunks) issue(s, nc);
-        }
-        if (++s == STAGES) { s = 0; parity ^= 1; }
-    }
-    if (flags) atomicOr(status, flags);
-}
-
 // unaligned views (e.g. a DDP shard that starts at an odd event index): scalar loads
 __global__ void __launch_bounds__(256)
 encode_scalar_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
@@ -505,25 +299,6 @@ static int launch_stream(K kern, const char* name, int grid, int threads, size_t
                          a.sd, a.B, a.H, a.W, a.out, a.status);
 }
 
-template <int CH, int STAGES, int THREADS, int CTAS_PER_SM>
-static int launch_tma_cfg(const EncodeArgs& a, cudaStream_t stream, bool pdl, int64_t* done) {
-    const int64_t n_chunks = a.n / CH;
-    *done = n_chunks * CH;
-    if (n_chunks == 0) return DVSOF_OK;
-    auto kern = encode_tma_kernel<CH, STAGES, THREADS>;
-    const int smem = CH * 36 * STAGES;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_tma smem attr: %s", cudaGetErrorString(e));
-        configured = true;
-    }
-    int64_t grid = (int64_t)kNumSMs * CTAS_PER_SM;
-    if (grid > n_chunks) grid = n_chunks;
-    return launch_kernel("encode_tma_kernel", kern, (int)grid, THREADS, smem, stream, pdl, a.x, a.y,
-                         a.t, a.p, a.b, a.n, n_chunks, a.sd, a.B, a.H, a.W, a.out, a.status);
-}
-
 static int check_encode_args(int64_t n, int64_t B, int H, int W, const void* out, const void* ws,
                              const void* status) {
     if (n < 0 || B <= 0 || H <= 0 || W <= 0)
@@ -588,65 +363,20 @@ extern "C" int dvsof_encode_prepare(const float* t, const int64_t* b, int64_t n,
     return launch_prepare(t, b, n, timestamps, B, H, W, out, workspace, true, (cudaStream_t)stream_);
 }
 
-// variant of the streaming kernel: DVSOF_ENCODE_VARIANT (experiments, scripts/exp_encoder.py);
-// unset = the default chosen from the measurements recorded in DESIGN.md section 4
-static int encode_variant() {
-    static const int v = getenv("DVSOF_ENCODE_VARIANT") ? atoi(getenv("DVSOF_ENCODE_VARIANT")) : -1;
-    return v;
-}
-
 static int encode_scatter_impl(const EncodeArgs& a, cudaStream_t stream, bool pdl) {
     const bool vec = aligned16(a.x) && aligned16(a.y) && aligned16(a.t) && aligned16(a.p) && aligned16(a.b);
-    const int variant = encode_variant();
     if (!vec)
         return launch_stream(encode_scalar_kernel, "encode_scalar_kernel", encode_grid(a.n, 256, 8),
                              256, 0, stream, pdl, a);
-    if (variant >= 1 && variant <= 3) {
-        int64_t done = 0;
-        int rc;
-        if (variant == 1) rc = launch_tma_cfg<1024, 3, 512, 2>(a, stream, pdl, &done);
-        else if (variant == 2) rc = launch_tma_cfg<2048, 3, 1024, 1>(a, stream, pdl, &done);
-        else rc = launch_tma_cfg<512, 4, 256, 3>(a, stream, pdl, &done);
-        if (rc) return rc;
-        if (done < a.n) {   // remainder (< one chunk): pointer offsets keep the 16 B alignment
-            EncodeArgs r = a;
-            r.x += done; r.y += done; r.t += done; r.p += done; r.b += done; r.n = a.n - done;
-            return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel",
-                                 encode_grid((r.n >> 2) + 1, 256, 8), 256, 0, stream,
-                                 pdl && done == 0, r);
-        }
-        return DVSOF_OK;
-    }
-    switch (variant) {
-        case 4: return launch_stream(encode_vec2_kernel<6>, "encode_vec2_kernel<6>",
-                                     encode_grid((a.n >> 1) + 1, 256, 6), 256, 0, stream, pdl, a);
-        case 5: return launch_stream(encode_vec2_kernel<8>, "encode_vec2_kernel<8>",
-                                     encode_grid((a.n >> 1) + 1, 256, 8), 256, 0, stream, pdl, a);
-        case 6: return launch_stream(encode_vec4_kernel<4>, "encode_vec4_kernel<4>",
-                                     encode_grid((a.n >> 2) + 1, 256, 4), 256, 0, stream, pdl, a);
-        case 7: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                     encode_grid((a.n >> 2) + 1, 256, 16), 256, 0, stream, pdl, a);
-        case 0: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                     encode_grid((a.n >> 2) + 1, 256, 8), 256, 0, stream, pdl, a);
-        case 8: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                     encode_grid((a.n >> 2) + 1, 256, 32), 256, 0, stream, pdl, a);
-        case 9: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                     encode_grid((a.n >> 2) + 1, 256, 128), 256, 0, stream, pdl, a);
-        case 10: return launch_stream(encode_vec2_kernel<6>, "encode_vec2_kernel<6>",
-                                      encode_grid((a.n >> 1) + 1, 256, 48), 256, 0, stream, pdl, a);
-        case 11: return launch_stream(encode_vec4_kernel<4>, "encode_vec4_kernel<4>",
-                                      encode_grid((a.n >> 2) + 1, 256, 32), 256, 0, stream, pdl, a);
-        case 12: return launch_stream(encode_pipe_kernel<4>, "encode_pipe_kernel<4>",
-                                      encode_grid((a.n >> 1) + 1, 256, 4), 256, 0, stream, pdl, a);
-        case 14: return launch_stream(encode_pipe_kernel<4>, "encode_pipe_kernel<4>",
-                                      encode_grid((a.n >> 1) + 1, 256, 2), 256, 0, stream, pdl, a);
-        // default: up to 128 CTAs per SM in the grid (3 resident at a time), i.e. one pass of 4
-        // events per thread for anything below ~78 M events: fresh CTAs keep the load phase of one
-        // and the RED phase of another interleaved.  Measured (profiles/r01h_variants.jsonl):
-        // cfg4 54.6 -> 76.4 Gev/s and cfg3 78.0 -> 81.8 Gev/s over the 8-per-SM persistent grid.
-        default: return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
-                                      encode_grid((a.n >> 2) + 1, 256, 128), 256, 0, stream, pdl, a);
-    }
+    // up to 128 CTAs per SM in the grid (3 resident at a time), i.e. one pass of 4 events per thread
+    // for anything below ~78 M events: fresh CTAs keep the load phase of one and the RED phase of
+    // another interleaved.  Measured (profiles/r01h_variants.jsonl): cfg4 54.6 -> 76.4 Gev/s and
+    // cfg3 78.0 -> 81.8 Gev/s over an 8-per-SM persistent grid.  The other schedules tried in round 1
+    // (2 events per thread, a register software pipeline, cp.async.bulk chunk rings: same RED-bound
+    // throughput, profiles/r01b_variants.jsonl) left the product library with commit "r02: experiment
+    // kernels out of libdvsof"; they are in the history of this file.
+    return launch_stream(encode_vec4_kernel<3>, "encode_vec4_kernel<3>",
+                         encode_grid((a.n >> 2) + 1, 256, 128), 256, 0, stream, pdl, a);
 }
 
 extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const float* t,
@@ -691,15 +421,16 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     uint16_t* codes = reinterpret_cast<uint16_t*>(ws + plan.off_codes);
     float* ts = reinterpret_cast<float*>(ws + plan.off_ts);
     uint32_t* table = reinterpret_cast<uint32_t*>(ws + plan.off_table);
-    static bool configured = false;
-    if (!configured) {
+    static unsigned long long configured = 0;            // one bit per device (attributes are per device)
+    int dev = 0;
+    if (needs_device_setup(configured, &dev)) {
         cudaError_t e = cudaFuncSetAttribute(encode_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(encode_reduce_kernel<kRedBatchLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(encode_reduce_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_binned smem attr: %s", cudaGetErrorString(e));
-        configured = true;
+        device_setup_done(configured, dev);
     }
     if (plan.max_chunks > INT32_MAX || (int64_t)a.B * plan.T > INT32_MAX)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_binned: grid too large");

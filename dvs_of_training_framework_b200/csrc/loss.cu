@@ -799,11 +799,10 @@ static int launch_match_and_pyramid(const dvsof_loss_scales_t* sc, const dvsof_l
             return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale loss: null matching input");
         static unsigned long long attr_done = 0;             // per device; a race only repeats the call
         int dev = 0;
-        cudaGetDevice(&dev);
-        if (dev >= 64 || !((attr_done >> dev) & 1ull)) {
+        if (needs_device_setup(attr_done, &dev)) {
             cudaFuncSetAttribute(pyramid_chain_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPyrSmemMax);
             cudaFuncSetAttribute(pyramid_chain_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kPyrSmemMax);
-            if (dev < 64) attr_done |= 1ull << dev;
+            device_setup_done(attr_done, dev);
         }
         const bool last = k == sc->n_scales;
         static const ScaleTable none = {};

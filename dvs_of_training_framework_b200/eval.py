@@ -47,9 +47,10 @@ def flow_error_dense_device(flow_gt, flow_pred, event_img, is_car=False, is_dens
         cnt = cnt.contiguous()
     out = torch.empty(3, dtype=torch.float64, device=dev)
     with torch.cuda.device(dev):
-        ws = _ws.get(dev)
+        key = (dev, torch.cuda.current_stream(dev).cuda_stream)     # the ticket word is per stream
+        ws = _ws.get(key)
         if ws is None:
-            ws = _ws[dev] = torch.zeros(_lib.load().dvsof_flow_error_workspace_bytes(), dtype=torch.uint8,
+            ws = _ws[key] = torch.zeros(_lib.load().dvsof_flow_error_workspace_bytes(), dtype=torch.uint8,
                                         device=dev)
         _lib.call('dvsof_flow_error_dense', _lib.ptr(gt), gt.element_size(), _lib.ptr(pred),
                   pred.element_size(), _lib.ptr(cnt) if cnt is not None else None, rows, W,

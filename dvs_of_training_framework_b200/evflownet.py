@@ -279,7 +279,42 @@ class Model(nn.Module):
             nn.init.kaiming_normal_(head.weight, a=4.4, nonlinearity='relu')
             nn.init.zeros_(head.bias)
             self.flow.append(head)
+        self._register_load_state_dict_pre_hook(self._accept_reference_keys)
         self.to(device)
+
+    # parameter names of the reference's EV_FlowNet/net.py (GConv2d `conv`/`bn` directly under
+    # enc.N, ResNetBlock.conv.M, UpsampleBlock.conv) <-> the names of this module tree
+    _KEY_MAP = ((r'^enc\.(\d+)\.(conv|bn)\.', r'enc.\1.block.\2.'),
+                (r'^tr\.(\d+)\.conv\.(\d+)\.', r'tr.\1.body.\2.'),
+                (r'^dec\.(\d+)\.conv\.(conv|bn)\.', r'dec.\1.block.\2.'))
+
+    @classmethod
+    def _accept_reference_keys(cls, state_dict, prefix, *_):
+        """`load_state_dict` also takes a checkpoint written by the reference's Model
+        (utils/serializer.py `step_N.pt`['model']): its keys are renamed in place."""
+        import re
+        for key in list(state_dict.keys()):
+            local = key[len(prefix):]
+            for pat, rep in cls._KEY_MAP:
+                new = re.sub(pat, rep, local)
+                if new != local:
+                    state_dict[prefix + new] = state_dict.pop(key)
+                    break
+
+    def reference_state_dict(self):
+        """state_dict() under the reference's parameter names (loadable by EV_FlowNet/net.py Model)."""
+        import re
+        inv = ((r'^enc\.(\d+)\.block\.', r'enc.\1.'), (r'^tr\.(\d+)\.body\.(\d+)\.', r'tr.\1.conv.\2.'),
+               (r'^dec\.(\d+)\.block\.', r'dec.\1.conv.'))
+        out = {}
+        for k, v in self.state_dict().items():
+            for pat, rep in inv:
+                k2 = re.sub(pat, rep, k)
+                if k2 != k:
+                    k = k2
+                    break
+            out[k] = v
+        return out
 
     def quantize(self, events, timestamps, sample_idx, imsize):
         return quantize(events, timestamps, sample_idx, imsize)           # net.py:197-205
@@ -302,10 +337,12 @@ class Model(nn.Module):
         flows = []
         for i, (dec, head) in enumerate(zip(self.dec, self.flow)):
             h = dec(h, flows[-1] if flows else None, skips[3 - i])
-            f = torch.tanh(head(h)) * 256.
+            arth = head(h)
+            f = torch.tanh(arth) * 256.
             flows.append(f)
-            if intermediate:
-                feats[f'dec_op_{i}'] = torch.cat((h, f), 1)
+            if intermediate:             # net.py:246-258 (`dec_cat_i` is never materialised here: the
+                feats[f'dec_op_{i}'] = h  # concatenation happens inside the decoder's gather kernel)
+                feats[f'dec_flow_arth_{i}'] = arth
         result = tuple(f[..., :s[0], :s[1]] for f, s in zip(flows, outsize))
         extra = (feats,) if intermediate else ()
         return (result, timestamps.reshape(-1, 2), sample_idx[0::2]) + extra

@@ -312,7 +312,9 @@ class Losses:
 
     def _plan(self, dev, P, D, H, W, flows):
         shapes = tuple((f.shape[-2], f.shape[-1]) for f in flows)
-        key = (dev, P, D, H, W, shapes)
+        # the plan owns the reduction workspace (tile records, tickets, per-tile counts): one per
+        # stream, or two calls with equal shapes on different streams would share the tickets
+        key = (dev, torch.cuda.current_stream(dev).cuda_stream, P, D, H, W, shapes)
         plan = self._plans.get(key)
         if plan is None:
             plan = self._plans[key] = _Plan(dev, P, D, H, W, shapes)
@@ -349,10 +351,10 @@ class Losses:
         (`_FusedTrainingLoss`); `terms` is then a detached tensor (logging only)."""
         args = self._checked(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
         S = len(flows)
-        key = (S,) + tuple(float(w) for w in weights)
+        key = (images.device, S) + tuple(float(w) for w in weights)
         coef = self._coefs.get(key)
         if coef is None:
-            vals = [w / S for w in key[1:] for _ in range(S)]
+            vals = [w / S for w in key[2:] for _ in range(S)]
             coef = self._coefs[key] = ((_lib.C.c_float * (3 * S))(*vals),
                                        torch.tensor(vals, dtype=torch.float32, device=images.device))
         if torch.is_grad_enabled() and any(f.requires_grad for f in args[5:]):

@@ -360,6 +360,7 @@ def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, e
             num_processed = global_step - init_batch
             if rank == 0:
                 print(f'Skipping batch with {num_events} events')
+                print(f'Augmentation parameters {batch.get("augmentation_params")}')
                 print(f'Processing rate is {num_processed / (num_processed + num_skipped):.2f}')
             continue
         global_step += 1
@@ -371,7 +372,9 @@ def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, e
         local = batch if prefetch else shard_batch(batch, rank, world)
         loss, (smoothness, photometric, out_reg), tags = process_minibatch(
             model, local, timers, device, is_raw, evaluator, weights)
-        loss /= accumulation_steps
+        # not `loss /= ...` as training.py:155 has it: the fused evaluator's loss is a view of the
+        # buffer its autograd node owns, which torch refuses to modify in place
+        loss = loss / accumulation_steps
         timers('backprop').start()
         loss.backward()
         timers('backprop').stop()
@@ -408,9 +411,18 @@ def train(model, device, loader, optimizer, num_steps: int, scheduler, logger, e
                 timers(k).stop()
             model.train()
         else:
+            timers('optimizer_step').start()                        # training.py:206-211: every
+            timers('optimizer_step').stop()                         # phase exists in every row
+            for k in hooks:
+                timers(k).start()
+                timers(k).stop()
             timers('logging').start()
             loss_sum += loss.item()
             timers('logging').stop()
+        # training.py:222-233 (the timer group prints on rank 0 only and resets everywhere)
+        timers.log(names=['batch_construction', 'batch2gpu', 'forward', 'loss', 'grid_construction',
+                          'photometric_loss', 'smoothness_loss', 'outborder_loss', 'backprop',
+                          'optimizer_step', 'free', 'logging'] + list(hooks))
         timers('batch_construction').start()
     timers('batch_construction').stop()
     return global_step // accumulation_steps

@@ -34,3 +34,15 @@ def lib():
     from dvs_of_training_framework_b200 import build, _lib
     build.build_lib()
     return _lib.load()
+
+
+def pytest_terminal_summary(terminalreporter):
+    """Report the one relaxation of the gradient tolerance next to the result:
+    per test, how many gradient elements needed the ill-conditioning allowance of
+    tests/test_loss_gpu.py::assert_grads_close."""
+    mod = sys.modules.get('tests.test_loss_gpu')
+    widened = getattr(mod, 'WIDENED', None)
+    if widened:
+        terminalreporter.write_sep('-', 'gradient elements outside rtol 1e-5 / atol 1e-6 (allowed: reference 1-ulp sensitivity x4)')
+        for test, (w, n) in sorted(widened.items()):
+            terminalreporter.write_line(f'{w:6d} of {n:9d}  {test}')

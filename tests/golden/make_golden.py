@@ -10,9 +10,10 @@ What is run unmodified from /root/reference:
   EV_FlowNet/net.py       compute_event_image -- with a `torch_scatter` stand-in providing
                           scatter_sum / scatter_max through Tensor.scatter_add_ /
                           Tensor.scatter_reduce_('amax', include_self=True)
-  utils/data.py           EventCrop, get_count_image, RandomRotation -- with a pure-python
-                          stand-in for the native `transformation.map`, restating
-                          transformation.cpp:35-85 with a dict of lists (hash map in LUT order)
+  utils/data.py           EventCrop, get_count_image, RandomRotation -- the native
+                          `transformation.map` it imports is the reference's own
+                          src/transformation.cpp compiled by oracle/Makefile (Eigen container
+                          stand-in: oracle/ref_shim/transformation.h)
 """
 import importlib.util
 import sys
@@ -56,23 +57,19 @@ def load_reference():
     pkg.__path__ = [str(REF / 'utils')]
     sys.modules['utils'] = pkg
 
-    # python stand-in for the native transformation.map (transformation.cpp:35-85)
+    # the native `transformation.map`: the reference's own src/transformation.cpp (:35-85),
+    # compiled where it lies by oracle/Makefile against a container stand-in for the absent Eigen
+    # headers (oracle/ref_shim/transformation.h) -- not a restatement
     tr = types.ModuleType('utils.transformation')
+    sys.path.insert(0, str(OUT.parent.parent))
+    from oracle import map_events_native as native
+    native.build()
+    assert native.available('ref'), 'oracle/_ref/libmap_events_ref.so was not built'
 
     def map_events(events, shape, src, dst):
-        H, W = shape
-        table = {}
-        for s, d in zip(src.tolist(), dst.tolist()):
-            table.setdefault(int(s), []).append(int(d))
-        rows = []
-        for ev in events:
-            for d in table.get(int(ev[1]) * W + int(ev[0]), []):
-                r = ev.copy()
-                r[0], r[1] = d % W, d // W
-                rows.append(r)
-        if not rows:
-            return np.zeros((0, events.shape[1]), np.float32)
-        return np.stack(rows).astype(np.float32)
+        assert events.dtype == np.float32 and events.flags.c_contiguous      # module.cpp: Eigen::Ref, no cast
+        assert src.dtype == np.uint64 and dst.dtype == np.uint64
+        return native.ref_map(events, shape, src, dst)
     tr.map = map_events
     sys.modules['utils.transformation'] = tr
 

@@ -185,6 +185,41 @@ def test_default_path_selection_large_stream_is_exact():
     assert np.array_equal(got.cpu().numpy(), want)
 
 
+def test_cfg3_full_shape_default_path_binned_equals_direct_and_oracle(monkeypatch):
+    """BASELINE configs[2] at full size: batch 32, 256x256, 5 M events per sample (160 M events,
+    ~39 k pass-1 chunks, 32 x 32 pass-2 slabs).  The library picks the binned path by itself here;
+    it must be bit-identical to the direct path, conserve the event count per sample and polarity,
+    and equal the oracle on a 1-in-32 subset of the samples (each sample's image depends on its
+    own events only, so one sample can be checked alone)."""
+    B, H, W, n = 32, 256, 256, 5_000_000
+    dev = torch.device('cuda')
+    g = torch.Generator(device=dev).manual_seed(1234 + 3)
+    N = B * n
+    ev = {'x': torch.randint(0, W, (N,), generator=g, device=dev),
+          'y': torch.randint(0, H, (N,), generator=g, device=dev),
+          'polarity': (torch.rand(N, generator=g, device=dev) < 0.7).long() * 2 - 1,
+          'sample_index': torch.arange(B, device=dev).repeat_interleave(n)}
+    ev['timestamp'] = torch.sort(torch.rand(B, n, generator=g, device=dev) * 0.032, dim=1)[0].reshape(-1).float()
+    ts = torch.tensor([0, 0.032] * B, dtype=torch.float32, device=dev)
+    sidx = torch.arange(B, device=dev).repeat_interleave(2)
+    monkeypatch.delenv('DVSOF_ENCODE_PATH', raising=False)
+    default = dv.compute_event_image(ev, ts, sidx, (H, W))
+    monkeypatch.setenv('DVSOF_ENCODE_PATH', 'binned')
+    binned = dv.compute_event_image(ev, ts, sidx, (H, W))
+    monkeypatch.setenv('DVSOF_ENCODE_PATH', 'direct')
+    direct = dv.compute_event_image(ev, ts, sidx, (H, W))
+    assert torch.equal(direct, binned) and torch.equal(default, binned)
+    per_sample = default[:, :2].sum(dim=(2, 3), dtype=torch.float64)
+    pos = (ev['polarity'] > 0).view(B, n).sum(1).double()
+    assert torch.equal(per_sample[:, 0], pos) and torch.equal(per_sample[:, 1], n - pos)
+    assert float(default[:, 2:].max()) == 1.0 and float(default[:, 2:].min()) >= 0.0
+    for b in (7,):                                    # 1 in 32: the oracle on that sample alone
+        one = {k: v[b * n:(b + 1) * n].cpu().numpy() for k, v in ev.items()}
+        one['sample_index'] = one['sample_index'] - b
+        want = eo.compute_event_image(one, ts[2 * b:2 * b + 2].cpu().numpy(), np.zeros(2, np.int64), (H, W))
+        assert np.array_equal(default[b].cpu().numpy(), want[0])
+
+
 def test_deferred_validation_reports_without_blocking():
     """Status.mode 'deferred': the call returns without a host sync; the error surfaces at
     `synchronize()` (or at a later call once the async copy of the status word has landed)."""

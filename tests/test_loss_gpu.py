@@ -40,6 +40,9 @@ def _oracle_grads(inp, flows_cpu, scale=1.0, cot=None):
     return terms, [f.grad.numpy() for f in fl]
 
 
+WIDENED = {}        # test id -> the largest count of gradient elements that needed the allowance
+
+
 def assert_grads_close(got, want, inp, flows_cpu, cot=None):
     """rtol 1e-5 / atol 1e-6 (north_star) on every gradient element, widened ONLY where the
     reference itself is ill-conditioned: where the warped frame nearly equals the previous one the
@@ -47,9 +50,13 @@ def assert_grads_close(got, want, inp, flows_cpu, cot=None):
     interpolated grey value moves the reference's own gradient by more than the tolerance.  The
     allowance is that measured sensitivity: |grad_ref(images) - grad_ref(images * (1 +- 2^-22))|
     (a 1-2 ulp relative perturbation of the frames), times 4.  It is exactly zero for
-    well-conditioned pixels, and it must stay rare."""
+    well-conditioned pixels, and it must stay rare.  Returns (elements that needed the allowance,
+    elements compared); the per-test maximum is printed in the test log (`-rA` / the summary
+    line written by the session hook below) so the relaxation is reported next to the claim."""
+    import os
     _, up = _oracle_grads(inp, flows_cpu, 1.0 + 2.0 ** -22, cot)
     _, dn = _oracle_grads(inp, flows_cpu, 1.0 - 2.0 ** -22, cot)
+    total_w, total_n = 0, 0
     for g, w, a, b in zip(got, want, up, dn):
         g = g.cpu().numpy() if hasattr(g, 'cpu') else g
         sens = 4.0 * np.maximum(np.abs(a - w), np.abs(b - w))
@@ -60,6 +67,14 @@ def assert_grads_close(got, want, inp, flows_cpu, cot=None):
         bad = err > base + sens
         assert not bad.any(), (f'{int(bad.sum())} / {g.size} gradient elements off; worst abs '
                                f'{float(err[bad].max()):.3e}')
+        total_w += widened
+        total_n += g.size
+    test = os.environ.get('PYTEST_CURRENT_TEST', '?').split(' ')[0]
+    prev = WIDENED.get(test, (0, 0))
+    WIDENED[test] = (max(prev[0], total_w), max(prev[1], total_n))
+    print(f'[grad tolerance] {test}: {total_w} of {total_n} gradient elements outside rtol 1e-5 / atol 1e-6 '
+          f'(inside 4x the reference\'s own 1-ulp sensitivity)')
+    return total_w, total_n
 
 
 def _as_array(terms):
@@ -357,6 +372,24 @@ def test_fused_full_size_cfg4_agrees_with_generic_path():
     np.testing.assert_allclose(float(loss), float(total), rtol=1e-6)
     for a, b in zip(fa, fb):
         torch.testing.assert_close(a.grad, b.grad, rtol=RTOL, atol=ATOL)
+
+
+def test_cfg3_shape_batch32_matches_oracle():
+    """BASELINE configs[2] loss shape (256x256, batch 32 -- 2048 + 512 + 128 + 32 tiles, 64 frames in
+    the one-launch prelude): terms, loss and every gradient against the CPU oracle, through both
+    the two-kernel path and the fused training pass."""
+    B, H, W = 32, 256, 256
+    inp = synth_loss_inputs(1234 + 3, B, H, W, 3.0)
+    oterms, ograds = _oracle_grads(inp, inp['flows'])
+    want = _as_array(oterms)
+    flows, terms = _run_gpu(inp, inp['flows'])
+    np.testing.assert_allclose(_as_array(terms), want, rtol=RTOL, atol=ATOL)
+    _combined(terms).backward()
+    assert_grads_close([f.grad for f in flows], ograds, inp, inp['flows'])
+    f2, loss, flat = _run_fused(inp, inp['flows'])
+    np.testing.assert_allclose(flat.cpu().numpy().reshape(3, 4), want, rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(float(loss), float(lo.combined(oterms)), rtol=RTOL, atol=ATOL)
+    assert_grads_close([f.grad for f in f2], ograds, inp, inp['flows'])
 
 
 def _run_fused_abi(inp):

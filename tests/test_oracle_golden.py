@@ -209,3 +209,58 @@ def test_aten_upsample_operation_order():
         val = fma(hy, fma(hx, a, lx * b), ly * fma(hx, c, lx * e))
         assert np.array_equal(val, out[0, 0].numpy())
         img = out
+
+
+def test_loss_oracle_matches_reference_dummynet_cfg1(golden):
+    """BASELINE configs[0]: the reference's DummyNet (zero flow, 4 scales) through its own
+    init_losses + process_minibatch at 260x346, batch 1 (tests/golden/make_golden_dummynet.py)."""
+    g = np.load(golden / 'dummynet_cfg1.npz')
+    flows = [torch.zeros(1, 2, int(h), int(w)) for h, w in g['shapes']]
+    terms = lo.multiscale_loss(flows, torch.tensor(g['flow_ts']), torch.tensor(g['flow_sample_idx']),
+                               torch.tensor(g['images']).float(), torch.tensor(g['timestamps']),
+                               torch.tensor(g['sample_idx']))
+    got = np.array([[float(v) for v in t] for t in terms])
+    np.testing.assert_allclose(got, g['terms'], rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(float(lo.combined(terms)), float(g['loss']), rtol=1e-6, atol=1e-7)
+
+
+def _random_map_case(seed, H, W, n, M, E=5, frac=False):
+    rng = np.random.default_rng(seed)
+    cols = [rng.integers(0, W, n), rng.integers(0, H, n), np.sort(rng.random(n)), rng.choice([-1, 1], n)]
+    cols += [rng.integers(0, 4, n) for _ in range(E - 4)]
+    ev = np.stack(cols[:E], 1).astype(np.float32)
+    if frac:                                       # float -> int truncation (transformation.cpp:62,74)
+        ev[:, :2] += rng.random((n, 2)).astype(np.float32) * 0.999
+    src = rng.integers(0, max(1, H * W // 2), M).astype(np.uint64)   # fan-out > 1, half the pixels dropped
+    dst = rng.integers(0, H * W, M).astype(np.uint64)
+    return ev, src, dst
+
+
+@pytest.mark.parametrize('kind', ['port', 'ref'])
+def test_map_events_numpy_oracle_equals_native(kind):
+    """A6: numpy oracle == plain-C++ restatement (oracle/map_events_ref.cpp) == the reference's own
+    transformation.cpp:35-85 compiled from /root/reference (oracle/_ref, prebuilt where the tree
+    exists), on LUTs with fan-out > 1, dropped pixels, fractional coordinates, E = 4/5/6."""
+    from oracle import map_events_native as mn
+    if kind == 'port':
+        mn.build()
+    elif not mn.available('ref'):
+        pytest.skip('oracle/_ref/libmap_events_ref.so not built (needs /root/reference once)')
+    fn = mn.port_map if kind == 'port' else mn.ref_map
+    for seed, (H, W, n, M, E, frac) in enumerate([(20, 30, 500, 700, 5, False), (260, 346, 20000, 90000, 5, False),
+                                                  (16, 16, 300, 100, 4, True), (33, 47, 4000, 3000, 6, True),
+                                                  (8, 8, 0, 10, 5, False), (8, 8, 50, 0, 5, False)]):
+        ev, src, dst = _random_map_case(seed, H, W, n, M, E, frac)
+        want = eo.map_events(ev, (H, W), src, dst)
+        got = fn(ev, (H, W), src, dst)
+        assert got.dtype == np.float32 and got.shape == want.shape and np.array_equal(got, want), seed
+    # identity (tests/dataset/test_dataset.py:42-73) and the 90-degree LUT of RandomRotation (:122-170)
+    H, W = 260, 346
+    ev, _, _ = _random_map_case(9, H, W, 5000, 1)
+    idx = np.arange(H * W, dtype=np.uint64)
+    assert np.array_equal(fn(ev, (H, W), idx, idx), ev)
+    src, dst = eo.rotation_lut((H, W), 90.0)
+    assert np.array_equal(fn(ev, (H, W), src.astype(np.uint64), dst.astype(np.uint64)),
+                          eo.map_events(ev, (H, W), src, dst))
+    with pytest.raises(ValueError):
+        fn(ev, (H, W), idx, idx[:5])

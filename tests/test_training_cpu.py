@@ -55,16 +55,40 @@ def test_shard_batch_partitions_by_sample(world):
     assert tr.shard_batch(batch, 0, 1) is batch
 
 
+class _ViewLoss(torch.autograd.Function):
+    """Like loss._FusedTrainingLoss: the loss is a VIEW of a buffer the node owns (an in-place
+    `loss /= k` on it is what torch refuses), the terms are non-differentiable."""
+    @staticmethod
+    def forward(ctx, weights, args, *flows):
+        with torch.enable_grad():
+            fl = [f.detach().requires_grad_() for f in flows]
+            terms = lo.multiscale_loss(fl, *args)
+            loss = lo.combined(terms, weights)
+            ctx.grads = torch.autograd.grad(loss, fl)
+        buf = torch.cat([loss.detach().reshape(1), torch.stack([t.detach() for g in terms for t in g])])
+        flat = buf[1:]
+        ctx.mark_non_differentiable(flat)
+        return buf[0:1].view(()), flat
+
+    @staticmethod
+    def backward(ctx, g, _):
+        return (None, None) + tuple(g * x for x in ctx.grads)
+
+class Fused:                     # the (loss, flat_terms) interface of Losses.combined
+    def __call__(self, flows, *a):
+        return lo.multiscale_loss(flows, *a)
+
+    def combined(self, flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx, weights):
+        return _ViewLoss.apply(tuple(weights), (flow_ts, flow_sample_idx, images, timestamps, sample_idx),
+                               *flows)
+
+
 def test_combined_loss_generic_and_fused_paths_agree():
     inp = synth_loss_inputs(5, 2, 32, 48, 2.0)
 
     class Generic:
         def __call__(self, flows, *a):
             return lo.multiscale_loss(flows, *a)
-
-    class Fused(Generic):            # same numbers behind the single-tensor `terms` interface
-        def terms(self, flows, *a):
-            return torch.stack([t for group in lo.multiscale_loss(flows, *a) for t in group])
 
     args = (inp['flows'], inp['flow_ts'], inp['flow_sample_idx'], inp['images'], inp['timestamps'],
             inp['sample_idx'], None)
@@ -76,6 +100,19 @@ def test_combined_loss_generic_and_fused_paths_agree():
         for u, v in zip(a, b):
             assert float(u) == float(v)
     assert float(l0) == pytest.approx(float(lo.combined(t0)), rel=1e-6)
+    # the fused branch returns (loss, 3*S terms) and its loss survives the accumulation division
+    # and backward the way `train` applies them (utils/training.py:155-158)
+    fl = [f.clone().requires_grad_() for f in inp['flows']]
+    l2, t2 = tr.combined_loss(Fused(), fl, *args[1:], weights=[0.5, 1, 1])
+    assert l2.dim() == 0 and l2._is_view()
+    with pytest.raises(RuntimeError):
+        l2 /= 2
+    (l2 / 2).backward()
+    fr = [f.clone().requires_grad_() for f in inp['flows']]
+    l3, _ = tr.combined_loss(Generic(), fr, *args[1:], weights=[0.5, 1, 1])
+    (l3 / 2).backward()
+    for a, b in zip(fl, fr):
+        torch.testing.assert_close(a.grad, b.grad, rtol=1e-6, atol=1e-8)
 
 
 class TinyFlowNet(nn.Module):
@@ -221,3 +258,48 @@ def test_prefetching_loader_is_transparent():
     assert len(got) == 2 and got[0]['size'] == 2 and got[0]['global_size'] == 4
     assert got[0]['global_events'] == batch['events']['x'].numel()
     assert int(got[0]['events']['sample_index'].min()) == 0 and got[0]['images'].shape[0] == 4
+
+
+@pytest.mark.parametrize('accum', [1, 2])
+def test_train_with_fused_evaluator_and_wall_clock_timers(accum, capsys):
+    """`train` end to end with an evaluator of the `Losses.combined` kind (loss = view of a buffer
+    its autograd node owns) and the `--timers` group: same weights as with the generic evaluator,
+    one timer line per micro-batch with the phases of utils/training.py:222-233."""
+    from dvs_of_training_framework_b200.timer import SynchronizedWallClockTimer
+    batch = _batch(B=2, n=200)
+    out = []
+    for ev in (OracleEvaluator(), Fused()):
+        torch.manual_seed(0)
+        model = TinyFlowNet()
+        opt = torch.optim.SGD(model.parameters(), lr=0.05)
+        steps = tr.train(model, 'cpu', [batch] * (2 * accum), opt, 2,
+                         torch.optim.lr_scheduler.LambdaLR(opt, lambda s: 1.0), Log(), ev,
+                         accumulation_steps=accum, timers=SynchronizedWallClockTimer(),
+                         max_events_per_batch=10 ** 9)
+        assert steps == 2
+        out.append([p.detach().clone() for p in model.parameters()])
+    for a, b in zip(*out):
+        torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-7)
+    lines = [ln for ln in capsys.readouterr().out.splitlines() if ln.startswith('rank=0 time (ms)')]
+    assert len(lines) == 2 * 2 * accum
+    for name in ('batch_construction', 'batch2gpu', 'forward', 'loss', 'backprop', 'optimizer_step', 'logging'):
+        assert f'{name}: ' in lines[0]
+
+
+def test_evflownet_checkpoint_keys_follow_the_reference():
+    """A `step_N.pt`['model'] written by the reference's EV_FlowNet/net.py Model loads into the
+    stand-in network and vice versa (names: enc.N.{conv,bn}, tr.N.conv.M.{conv,bn},
+    dec.N.conv.{conv,bn}, flow.N -- net.py:20-86,153-190)."""
+    from dvs_of_training_framework_b200.evflownet import Model
+    torch.manual_seed(1)
+    a, b = Model('cpu'), Model('cpu')
+    ref = a.reference_state_dict()
+    assert len(ref) == 92
+    for k in ('enc.0.conv.weight', 'enc.3.bn.running_mean', 'tr.1.conv.1.bn.running_var',
+              'tr.0.conv.0.conv.bias', 'dec.3.conv.conv.bias', 'dec.0.conv.bn.weight', 'flow.2.weight'):
+        assert k in ref, k
+    assert not any('.block.' in k or '.body.' in k for k in ref)
+    res = b.load_state_dict({k: v.clone() for k, v in ref.items()})      # reference names -> strict load
+    assert not res.missing_keys and not res.unexpected_keys
+    for (ka, va), (kb, vb) in zip(a.state_dict().items(), b.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)

@@ -164,3 +164,36 @@ def test_augment_events_golden_rotation_then_crop(golden):
         got = dv.augment_events(e5, (260, 346), lut=dv.rotation_lut((260, 346), float(ang)), box=box)
         assert np.array_equal(got, want)
     assert dv.augment_events(np.zeros((0, 5), np.float32), (260, 346), is_flip=True, box=box).shape == (0, 5)
+
+
+@pytest.mark.parametrize('kind', ['ref', 'port'])
+def test_map_equals_native_reference_source(kind):
+    """A6 against the native component itself: the CUDA remap == the reference's own
+    transformation.cpp:35-85 compiled from the reference tree (oracle/_ref/libmap_events_ref.so,
+    built by oracle/Makefile where /root/reference exists and shipped prebuilt) and == the plain
+    C++ restatement, on random LUTs with fan-out > 1, dropped pixels, fractional coordinates and
+    the RandomRotation LUT at DAVIS size."""
+    from oracle import map_events_native as mn
+    if kind == 'port':
+        mn.build()
+    elif not mn.available('ref'):
+        pytest.skip('oracle/_ref/libmap_events_ref.so not present')
+    fn = mn.ref_map if kind == 'ref' else mn.port_map
+    rng = np.random.default_rng(11)
+    for H, W, n, M, E, frac in [(40, 50, 30000, 6000, 5, False), (260, 346, 100000, 90000, 5, False),
+                                (33, 47, 4000, 3000, 6, True), (16, 16, 300, 100, 4, True)]:
+        cols = [rng.integers(0, W, n), rng.integers(0, H, n), np.sort(rng.random(n)), rng.choice([-1, 1], n)]
+        cols += [rng.integers(0, 4, n) for _ in range(E - 4)]
+        ev = np.stack(cols[:E], 1).astype(np.float32)
+        if frac:
+            ev[:, :2] += rng.random((n, 2)).astype(np.float32) * 0.999
+        src = rng.integers(0, H * W // 2, M).astype(np.uint64)
+        dst = rng.integers(0, H * W, M).astype(np.uint64)
+        want = fn(ev, (H, W), src, dst)
+        got = dv.transformation.map(ev, (H, W), src, dst)
+        assert got.shape == want.shape and np.array_equal(got, want)
+    H, W = 260, 346
+    src, dst = eo.rotation_lut((H, W), 23.0)
+    ev = np.stack([rng.integers(0, W, 50000), rng.integers(0, H, 50000), np.sort(rng.random(50000)),
+                   rng.choice([-1, 1], 50000), np.zeros(50000)], 1).astype(np.float32)
+    assert np.array_equal(dv.transformation.map(ev, (H, W), src, dst), fn(ev, (H, W), src, dst))
