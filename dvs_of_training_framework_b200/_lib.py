@@ -24,7 +24,7 @@ _ST_TEXT = {ST_BAD_POLARITY: 'polarity must be +1/-1 (EV_FlowNet/net.py:124)',
 
 
 class LossScales(C.Structure):
-    _fields_ = [('n_scales', C.c_int32), ('n_pred', C.c_int32),
+    _fields_ = [('n_scales', C.c_int32), ('n_pred', C.c_int32), ('n_images', C.c_int32), ('reserved_', C.c_int32),
                 ('H', C.c_int32 * MAX_SCALES), ('W', C.c_int32 * MAX_SCALES),
                 ('flow', C.c_void_p * MAX_SCALES), ('images', C.c_void_p * MAX_SCALES),
                 ('grad_flow', C.c_void_p * MAX_SCALES)]

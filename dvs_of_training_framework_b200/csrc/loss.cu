@@ -46,6 +46,12 @@ struct ScaleTable {
     const float* flow[DVSOF_MAX_SCALES];
     const float* images[DVSOF_MAX_SCALES];
     float* grad_flow[DVSOF_MAX_SCALES];
+    // the sweep's work units: segments of 32 columns x seg_rows[s] rows, one warp (= CTA) each;
+    // seg_per[s] segments per (scale, prediction), seg_begin[s] = first block of scale s
+    int seg_rows[DVSOF_MAX_SCALES], seg_per[DVSOF_MAX_SCALES];
+    float inv_seg_per[DVSOF_MAX_SCALES];
+    int seg_begin[DVSOF_MAX_SCALES + 1];
+    int use_tma[DVSOF_MAX_SCALES];                      // flow / level of scale s have tensor maps
 };
 
 struct TileCoord { int s, n, y0, x0; };
@@ -138,8 +144,8 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
 __device__ void reduce_pair(const ScaleTable& tab, int s, int n, const float* partials,
                             double* pair_rec, int32_t* n_bad, double (*red)[7]) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
-    const int P = tab.n_pred, per = tab.tiles_x[s] * tab.tiles_y[s];
-    const float* rec = partials + ((size_t)tab.cta_begin[s] + (size_t)n * per) * kRec;
+    const int P = tab.n_pred, per = tab.seg_per[s];
+    const float* rec = partials + ((size_t)tab.seg_begin[s] + (size_t)n * per) * kRec;
     double a[7] = {0, 0, 0, 0, 0, 0, 0};
     for (int t = threadIdx.x; t < per; t += blockDim.x) {
         const float4 r0 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
@@ -221,7 +227,7 @@ __device__ __forceinline__ void finish_tile(const ScaleTable& tab, const TileCoo
     const int P = tab.n_pred, pair = tc.s * P + tc.n;
     __syncthreads();                                       // record stores happen-before the arrive
     if (threadIdx.x == 0)
-        *flag = ticket_arrive(ws.tickets + 1 + pair) == (unsigned)(tab.tiles_x[tc.s] * tab.tiles_y[tc.s]) - 1u;
+        *flag = ticket_arrive(ws.tickets + 1 + pair) == (unsigned)tab.seg_per[tc.s] - 1u;
     __syncthreads();
     if (!*flag) return;
     __threadfence();                                       // acquire side (finishing CTAs only)
@@ -254,7 +260,7 @@ scale_gradients_kernel(const __grid_constant__ ScaleTable tab, const float* __re
 
 }  // namespace dvsof
 
-#include "loss_strip.cuh"
+#include "loss_ring.cuh"
 
 namespace dvsof {
 // ------------------------------ bilinear resize (align_corners) ------------------------
@@ -567,6 +573,72 @@ pyramid_chain_kernel(const __grid_constant__ PyramidArgs a, const __grid_constan
 // ---------------------------------------------------------------------------------------
 using namespace dvsof;
 
+// Rows per sweep segment (one warp walks 32 columns x R rows): the taller the segment, the better
+// its fixed costs (decode, pointer set-up, halo pairs, record + ticket) are amortised; the shorter,
+// the more warps there are to fill 148 SMs x kSweepWarpsPerSM resident warps.  R = the largest of
+// 32 / 16 / 8 that still leaves two full waves of warps.  DVSOF_LOSS_SEG_ROWS overrides (tuning).
+constexpr int kSweepWarpsPerSM = DVSOF_LOSS_MIN_CTAS;
+static void plan_segments(const dvsof_loss_scales_t* sc, ScaleTable* tab) {
+    int64_t warp_rows = 0;
+    for (int s = 0; s < sc->n_scales; ++s) warp_rows += (int64_t)sc->n_pred * tab->tiles_x[s] * sc->H[s];
+    int R = 8;
+    for (int r = 32; r > 8; r >>= 1)
+        if (warp_rows / r >= 2LL * kNumSMs * kSweepWarpsPerSM) { R = r; break; }
+    if (const char* e = getenv("DVSOF_LOSS_SEG_ROWS")) {
+        const int v = atoi(e);
+        if (v >= 8 && v <= 4096 && v % 8 == 0) R = v;
+    }
+    int64_t begin = 0;
+    for (int s = 0; s < sc->n_scales; ++s) {
+        tab->seg_rows[s] = R;
+        tab->seg_per[s] = tab->tiles_x[s] * ((sc->H[s] + R - 1) / R);
+        tab->inv_seg_per[s] = 1.f / (float)tab->seg_per[s];
+        tab->seg_begin[s] = (int)begin;
+        begin += (int64_t)tab->seg_per[s] * sc->n_pred;
+        // a tensor map needs 16-byte aligned bases and row pitches
+        tab->use_tma[s] = sc->W[s] % 4 == 0 && aligned16(sc->flow[s]) && aligned16(sc->images[s]) &&
+                          sc->n_images > 0;
+    }
+    for (int s = sc->n_scales; s <= DVSOF_MAX_SCALES; ++s) tab->seg_begin[s] = (int)begin;
+    for (int s = sc->n_scales; s < DVSOF_MAX_SCALES; ++s) tab->use_tma[s] = 0;
+}
+
+// ---- tensor maps (cuTensorMapEncodeTiled through the runtime's driver entry point: no libcuda link) ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+// fp32 tensor (W, H, N) row-major with a (bw, bh, bn) box, zero fill outside
+static bool encode_map3(CUtensorMap* m, const float* base, int W, int H, int64_t N, int bw, int bh, int bn) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+    const cuuint64_t strides[2] = {(cuuint64_t)W * 4, (cuuint64_t)W * H * 4};
+    const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+    const cuuint32_t elem[3] = {1, 1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, elem,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+static void build_maps(const dvsof_loss_scales_t* sc, ScaleTable* tab, LossMaps* maps) {
+    for (int s = 0; s < sc->n_scales; ++s) {
+        if (!tab->use_tma[s]) continue;
+        if (!encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH, 2) ||
+            !encode_map3(&maps->prev[s], sc->images[s], sc->W[s], sc->H[s], sc->n_images, 32, kStageRows, 1))
+            tab->use_tma[s] = 0;             // no driver entry point / unencodable: plain loads
+    }
+}
+
 static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need_grad) {
     if (!sc) return fail(DVSOF_ERR_INVALID_ARGUMENT, "loss: null scale table");
     if (sc->n_scales < 1 || sc->n_scales > DVSOF_MAX_SCALES || sc->n_pred < 1)
@@ -608,12 +680,15 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
     }
     for (int s = sc->n_scales; s <= DVSOF_MAX_SCALES; ++s) tab->cta_begin[s] = (int)begin;
     for (int i = 0; i < 3 * DVSOF_MAX_SCALES; ++i) tab->coef[i] = 0.f;
+    plan_segments(sc, tab);
     return DVSOF_OK;
 }
 
 // workspace layout: tile records | pair records | tickets | per-tile out-of-border counts
 static size_t partial_bytes(const ScaleTable& tab) {
-    return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * kRec * sizeof(float), 256);
+    // one record per segment; sized for the shortest segments (8 rows = 4 per 32x32 tile) so that a
+    // workspace stays valid whatever DVSOF_LOSS_SEG_ROWS says at launch time
+    return round_up((size_t)tab.cta_begin[DVSOF_MAX_SCALES] * 4 * kRec * sizeof(float), 256);
 }
 static size_t pair_bytes(const ScaleTable& tab) {
     return round_up((size_t)tab.n_scales * tab.n_pred * kPairRec * sizeof(double), 256);
@@ -644,13 +719,17 @@ static int zero_tickets(const ScaleTable& tab, const LossWorkspace& ws, cudaStre
 }
 
 template <bool kVal, bool kGrad>
-static int launch_strip(const char* what, const ScaleTable& tab, const int32_t* match_idx,
+static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTable& tab, const int32_t* match_idx,
                         const float* grad_terms, const int32_t* n_bad_in, const LossWorkspace& ws,
                         float* terms, int32_t* n_bad_out, float* loss, cudaStream_t stream, bool pdl,
                         int bad_per_tile = 0) {
-    return launch_kernel(what, warp_loss_strip_kernel<kVal, kGrad>, tab.cta_begin[DVSOF_MAX_SCALES],
-                         kSThreads, 0, stream, pdl, tab, match_idx, grad_terms, n_bad_in, bad_per_tile, ws,
-                         terms, n_bad_out, loss);
+    LossMaps maps;
+    if (getenv("DVSOF_LOSS_NO_TMA"))                 // tests: force the plain-load staging
+        for (int s = 0; s < DVSOF_MAX_SCALES; ++s) tab.use_tma[s] = 0;
+    build_maps(sc, &tab, &maps);
+    return launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
+                         stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws, terms,
+                         n_bad_out, loss);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
@@ -663,7 +742,7 @@ extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int3
     cudaStream_t stream = (cudaStream_t)stream_;
     const LossWorkspace ws = carve(tab, workspace);
     if (int rc = zero_tickets(tab, ws, stream)) return rc;
-    return launch_strip<true, false>("warp_loss_strip_kernel<fwd>", tab, match_idx, nullptr, nullptr, ws,
+    return launch_sweep<true, false>("warp_loss_ring_kernel<fwd>", sc, tab, match_idx, nullptr, nullptr, ws,
                                      terms, n_bad, nullptr, stream, false);
 }
 
@@ -674,7 +753,7 @@ extern "C" int dvsof_warp_loss_backward(const dvsof_loss_scales_t* sc, const int
     if (int rc = build_table(sc, &tab, true)) return rc;
     if (!match_idx || !grad_terms || !n_bad)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "warp_loss_backward: null buffer");
-    return launch_strip<false, true>("warp_loss_strip_kernel<bwd>", tab, match_idx, grad_terms, n_bad,
+    return launch_sweep<false, true>("warp_loss_ring_kernel<bwd>", sc, tab, match_idx, grad_terms, n_bad,
                                      LossWorkspace{nullptr, nullptr, nullptr}, nullptr, nullptr, nullptr,
                                      (cudaStream_t)stream_, false);
 }
@@ -846,14 +925,17 @@ extern "C" int dvsof_multiscale_loss_forward(const dvsof_loss_scales_t* sc,
                                              float* terms, int32_t* n_bad, void* workspace,
                                              uint32_t* status, void* stream_) {
     ScaleTable tab;
-    if (int rc = build_table(sc, &tab, false)) return rc;
-    if (!frames_ok(fr) || !match_idx || !terms || !n_bad || !workspace || !status)
+    if (!sc || !frames_ok(fr) || !match_idx || !terms || !n_bad || !workspace || !status)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_forward: bad arguments");
+    dvsof_loss_scales_t with_frames = *sc;
+    with_frames.n_images = fr->n_images;
+    sc = &with_frames;
+    if (int rc = build_table(sc, &tab, false)) return rc;
     cudaStream_t stream = (cudaStream_t)stream_;
     const LossWorkspace ws = carve(tab, workspace);
     if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream))
         return rc;
-    return launch_strip<true, false>("warp_loss_strip_kernel<fwd>", tab, match_idx, nullptr, nullptr, ws,
+    return launch_sweep<true, false>("warp_loss_ring_kernel<fwd>", sc, tab, match_idx, nullptr, nullptr, ws,
                                      terms, n_bad, nullptr, stream, true);
 }
 
@@ -871,9 +953,12 @@ extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
                                            int32_t* n_bad, void* workspace, uint32_t* status,
                                            void* stream_) {
     ScaleTable tab;
-    if (int rc = build_table(sc, &tab, true)) return rc;
-    if (!frames_ok(fr) || !coef || !match_idx || !terms || !loss || !n_bad || !workspace || !status)
+    if (!sc || !frames_ok(fr) || !coef || !match_idx || !terms || !loss || !n_bad || !workspace || !status)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "multiscale_loss_fused: bad arguments");
+    dvsof_loss_scales_t with_frames = *sc;
+    with_frames.n_images = fr->n_images;
+    sc = &with_frames;
+    if (int rc = build_table(sc, &tab, true)) return rc;
     set_coef(&tab, coef);
     cudaStream_t stream = (cudaStream_t)stream_;
     const LossWorkspace ws = carve(tab, workspace);
@@ -882,7 +967,7 @@ extern "C" int dvsof_multiscale_loss_fused(const dvsof_loss_scales_t* sc,
     if (int rc = launch_match_and_pyramid(sc, fr, match_idx, status, ws.tickets, n_tickets(tab), stream,
                                           &tab, ws.tile_bad))
         return rc;
-    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, ws.tile_bad, ws,
+    return launch_sweep<true, true>("warp_loss_ring_kernel<fused>", sc, tab, match_idx, nullptr, ws.tile_bad, ws,
                                     terms, n_bad, loss, stream, true, 1);
 }
 
@@ -903,10 +988,10 @@ extern "C" int dvsof_warp_loss_fused(const dvsof_loss_scales_t* sc, const int32_
         cudaError_t e = cudaMemsetAsync(n_bad, 0, sizeof(int32_t) * sc->n_scales * sc->n_pred, stream);
         if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "n_bad memset: %s", cudaGetErrorString(e));
         if (int rc = launch_kernel("outborder_count_kernel", outborder_count_kernel,
-                                   tab.cta_begin[DVSOF_MAX_SCALES], kSThreads, 0, stream, false, tab, n_bad))
+                                   tab.cta_begin[DVSOF_MAX_SCALES], 32 * kCountWarps, 0, stream, false, tab, n_bad))
             return rc;
     }
-    return launch_strip<true, true>("warp_loss_strip_kernel<fused>", tab, match_idx, nullptr, n_bad, ws,
+    return launch_sweep<true, true>("warp_loss_ring_kernel<fused>", sc, tab, match_idx, nullptr, n_bad, ws,
                                     terms, nullptr, loss, stream, false);
 }
 

@@ -1,0 +1,599 @@
+// loss_ring.cuh -- the warp-loss sweep (included by loss.cu): utils/loss.py:121-171 for all scales
+// and predictions in one launch, forward terms and analytic backward.
+//
+// Work unit = one WARP = one CTA: a SEGMENT of 32 pixel columns x R rows (R = 8, 16 or 32, chosen
+// per launch) of one (scale, prediction).  The warp walks its segment top to bottom in stages of
+// 8 rows, one pixel column per lane.  Each stage's inputs arrive through TMA
+// (cp.async.bulk.tensor.3d, completion on an mbarrier) into a two-stage ring in shared memory:
+//     flow box   2 channels x 10 rows (y-1 .. y+8) x 36 columns (x0-1 .. x0+34), zero outside the image
+//     prev box   8 rows x 32 columns of the matched `prev` pyramid level
+// while the previous stage is being processed, so staging costs one elected lane a handful of
+// instructions per 8 rows instead of ~25 per row, and there is no CTA-wide barrier anywhere.
+// (W % 4 != 0 or unaligned bases cannot be described by a tensor map: those scales fill the same
+// ring with plain loads.)  The bilinear taps of `next` are a data-dependent gather and go through
+// L1 (LDG); everything else is as in round 1's strip kernel:
+//   * every neighbour pair of the smoothness term (utils/loss.py:76-90) is owned by the top-left
+//     pixel of its 2x2 block; value AND derivative come from one lg2 + one ex2:
+//         s = d^2 + eps^2,  t = s^(alpha-1),  c(d) = t * s,  c'(d) = 2 alpha d t;
+//   * the two flow channels travel as one packed fp32x2 value (FADD2 / FMUL2 / FFMA2);
+//   * derivatives never leave registers: a pixel's gradient is
+//         g(x,y) = L(x-1,y) - Gh(x,y) + Gv(x,y-1) - Gv(x,y) - Gda(x,y) - Gdb(x,y-1)
+//         L(x,y) = Gh(x,y) + Gda(x,y-1) + Gdb(x,y)          (everything the right neighbour needs)
+//     the row above is carried, the left neighbour arrives with one shuffle per channel; lane 0
+//     takes the left halo's L (evaluated for the 8 rows of a stage at once, spread over the lanes)
+//     with a predicated shared-memory load;
+//   * rows are processed in groups of 2: sampling positions and all taps of the group are
+//     requested first, the load-free pair phase runs while they are in flight.
+// Stages whose 8 rows and the row below lie inside the image (all but the last of a column) take
+// a path without per-row masks.
+//
+// Modes (template):  <kVal, !kGrad> forward terms;  <!kVal, kGrad> backward for arbitrary
+// d(loss)/d(terms);  <kVal, kGrad> the fused training pass: terms and d(sum_k coef_k term_k)/d(flow)
+// in a single sweep -- 16 B/pixel read, 8 B/pixel written.
+#pragma once
+#include <cuda.h>
+
+namespace dvsof {
+
+#ifndef DVSOF_LOSS_GROUP
+#define DVSOF_LOSS_GROUP 2                // rows whose taps are in flight together
+#endif
+#ifndef DVSOF_LOSS_MIN_CTAS
+#define DVSOF_LOSS_MIN_CTAS 20            // 1-warp CTAs per SM the register budget is held to
+#endif
+constexpr int kGroup = DVSOF_LOSS_GROUP;
+constexpr int kStageRows = 8;                               // rows per ring stage
+constexpr int kRingStages = 2;
+constexpr int kBoxW = 36, kBoxH = kStageRows + 2;           // flow box (floats per row, rows)
+constexpr int kPlane = kBoxW * kBoxH;                       // one channel of the flow box
+constexpr int kPrevOff = 736;                               // floats: 2944 B, 128-byte aligned
+constexpr int kStageFloats = 1024;
+constexpr unsigned kFlowBoxBytes = 2u * kPlane * 4u, kPrevBoxBytes = kStageRows * 32u * 4u;
+static_assert(kStageRows % kGroup == 0, "a stage is a whole number of groups");
+static_assert(2 * kPlane <= kPrevOff && kPrevOff + kStageRows * 32 <= kStageFloats, "stage layout");
+
+struct LossMaps {                         // tensor maps of the launch (kernel parameter space)
+    CUtensorMap flow[DVSOF_MAX_SCALES];   // (W, H, 2P) fp32, box (36, 10, 2)
+    CUtensorMap prev[DVSOF_MAX_SCALES];   // (W, H, D) fp32, box (32, 8, 1)
+};
+
+// ---- packed fp32x2 helpers (both flow channels in one FMA-pipe instruction) ----
+__device__ __forceinline__ float2 f2(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 f2add(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 f2sub(float2 a, float2 b) { return __ffma2_rn(b, f2(-1.f), a); }
+__device__ __forceinline__ float2 f2mul(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+
+struct Charb2 { float2 val, der; };       // c(d) and c'(d) / (2 alpha), both channels
+template <bool kVal, bool kGrad>
+__device__ __forceinline__ Charb2 charb2(float2 p, float2 q) {     // d = p - q
+    const float2 d = f2sub(p, q);
+    const float2 s = f2fma(d, d, f2(kEps2));
+    const float2 l = make_float2(lg2_approx(s.x), lg2_approx(s.y));
+    Charb2 r;
+    if (kGrad) {
+        const float2 e = f2mul(l, f2(kAlpha - 1.f));
+        const float2 t = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+        r.der = f2mul(d, t);
+        r.val = f2mul(t, s);
+    } else {
+        const float2 e = f2mul(l, f2(kAlpha));
+        r.der = f2(0.f);
+        r.val = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+    }
+    return r;
+}
+struct Charb1 { float val, der; };
+template <bool kVal, bool kGrad>
+__device__ __forceinline__ Charb1 charb1(float d) {
+    const float s = fmaf(d, d, kEps2);
+    const float l = lg2_approx(s);
+    Charb1 r;
+    if (kGrad) {
+        const float t = ex2_approx((kAlpha - 1.f) * l);
+        r.der = d * t;
+        r.val = t * s;
+    } else {
+        r.der = 0.f;
+        r.val = ex2_approx(kAlpha * l);
+    }
+    return r;
+}
+
+// normalised sampling coordinate of utils/loss.py:150-156 (IEEE division by the half extent)
+__device__ __forceinline__ float grid_coord(float pix, float disp, float h, float r) {
+    return __fsub_rn(dvsof_div_by_const_grid(__fadd_rn(pix, disp), h, r), 1.f);
+}
+__device__ __forceinline__ bool out_of_border(float gx, float gy) {               // loss.py:92-94
+    return gx < -1.f || gx > 1.f || gy < -1.f || gy > 1.f;
+}
+// The counting jobs only need the predicate, not the coordinates: pixel + flow against two
+// thresholds per axis decides it without the division (exact_div.h: dvsof_grid_outside).
+struct BorderTest { float hi_x, lo_x, hi_y, lo_y; };
+__device__ __forceinline__ BorderTest border_test(const ScaleTable& tab, int s) {
+    return BorderTest{dvsof_grid_outside_hi(tab.hx[s], tab.rx[s]), dvsof_grid_outside_lo(tab.hx[s], tab.rx[s]),
+                      dvsof_grid_outside_hi(tab.hy[s], tab.ry[s]), dvsof_grid_outside_lo(tab.hy[s], tab.ry[s])};
+}
+__device__ __forceinline__ bool outside_grid(float ax, float ay, const BorderTest& bt) {
+    return dvsof_grid_outside(ax, bt.hi_x, bt.lo_x) || dvsof_grid_outside(ay, bt.hi_y, bt.lo_y);
+}
+
+// q = a / b for 0 <= a < 2^23 and the host's float reciprocal of b, exact after one correction
+__device__ __forceinline__ int div_small(int a, int b, float inv_b) {
+    int q = (int)(((float)a + 0.5f) * inv_b);
+    q += (q + 1) * b <= a ? 1 : 0;
+    q -= q * b > a ? 1 : 0;
+    return q;
+}
+
+// (scale, prediction, 32x32 count tile) of border-count job `cta` (tiles_x / tiles_y / cta_begin)
+__device__ __forceinline__ TileCoord decode_cta_fast(const ScaleTable& tab, int cta) {
+    int s = 0;
+#pragma unroll 1
+    for (int k = 1; k < tab.n_scales; ++k) s += cta >= tab.cta_begin[k] ? 1 : 0;
+    const int local = cta - tab.cta_begin[s];
+    const int tx = tab.tiles_x[s], per = tx * tab.tiles_y[s];
+    const int n = div_small(local, per, tab.inv_per[s]);
+    const int tile = local - n * per;
+    const int ty = div_small(tile, tx, tab.inv_tx[s]);
+    return TileCoord{s, n, ty * kTile, (tile - ty * tx) * kTile};
+}
+
+// (scale, prediction, first row, first column) of sweep segment `blk` (seg_* tables)
+__device__ __forceinline__ TileCoord decode_segment(const ScaleTable& tab, int blk) {
+    int s = 0;
+#pragma unroll 1
+    for (int k = 1; k < tab.n_scales; ++k) s += blk >= tab.seg_begin[k] ? 1 : 0;
+    const int local = blk - tab.seg_begin[s];
+    const int tx = tab.tiles_x[s], per = tab.seg_per[s];
+    const int n = div_small(local, per, tab.inv_seg_per[s]);
+    const int seg = local - n * per;
+    const int cy = div_small(seg, tx, tab.inv_tx[s]);
+    return TileCoord{s, n, cy * tab.seg_rows[s], (seg - cy * tx) * kTile};
+}
+
+// ---- mbarrier / TMA (one elected lane issues, the whole warp waits) ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+// the executing CTA's shared window is part of its (1-CTA) cluster window: same 32-bit address
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+// One row's bilinear taps in flight: requested in phase 1, consumed in phase 3.
+struct Taps { float nw, ne, sw, se, wx, wy; bool bad; };
+
+// phase 1 of a row: sampling position exactly as the reference computes it (operation-order notes
+// at the top of loss.cu), then the four zero-padded taps of `next` are requested.  The position is
+// clamped to [-2, S] in float before the conversion (values out there have no tap inside the image:
+// the sample and its derivative are 0 whatever the weights), so one F2I.FLOOR replaces floor + F2I.
+__device__ __forceinline__ Taps request_taps(const float* __restrict__ next, int H, int W, float Hf, float Wf,
+                                             const GridNorm& gn, float xf, float yf, float2 uv, bool valid) {
+    Taps t;
+    const float gx = grid_coord(xf, uv.x, gn.hx, gn.rx), gy = grid_coord(yf, uv.y, gn.hy, gn.ry);
+    t.bad = valid && out_of_border(gx, gy);
+    const float ix = __fmul_rn(__fadd_rn(gx, 1.f), gn.hx);            // ATen CPU unnormalize
+    const float iy = __fmul_rn(__fadd_rn(gy, 1.f), gn.hy);
+    const float cx = fminf(fmaxf(ix, -2.f), Wf), cy = fminf(fmaxf(iy, -2.f), Hf);
+    const int xi = __float2int_rd(cx), yi = __float2int_rd(cy);
+    t.wx = cx - (float)xi;                                            // weight of east / south
+    t.wy = cy - (float)yi;
+    const bool x0ok = (unsigned)xi < (unsigned)W, x1ok = (unsigned)(xi + 1) < (unsigned)W;
+    const bool y0ok = (unsigned)yi < (unsigned)H, y1ok = (unsigned)(yi + 1) < (unsigned)H;
+    const int idx = yi * W + xi;
+    const float* p0 = next + idx;
+    const float* p1 = next + (idx + W);
+    t.nw = (x0ok && y0ok) ? __ldg(p0) : 0.f;
+    t.ne = (x1ok && y0ok) ? __ldg(p0 + 1) : 0.f;
+    t.sw = (x0ok && y1ok) ? __ldg(p1) : 0.f;
+    t.se = (x1ok && y1ok) ? __ldg(p1 + 1) : 0.f;
+    return t;
+}
+
+// Everything a warp carries from row to row and stage to stage.
+struct SweepState {
+    float2 a, b;                          // flow at (x, y), (x+1, y) of the current row
+    float2 gv_p, gda_p, gdb_p;            // pair gradients of the row above
+    float2 acc_h, acc_v, acc_d;           // smoothness sums (both channels)
+    float acc_p, acc_o, acc_n;            // photometric, border sum, border count
+};
+struct SweepConst {
+    int H, W;
+    float Hf, Wf, xf;
+    bool x_in, x_r;
+    float kh, kv, kd, k_ph, k_ob;         // gradient scales of this scale's terms
+    GridNorm gn;
+    const float* next;
+    float* grad0;                         // this lane's column of the gradient, channel 0 / 1:
+    float* grad1;                         // pixel (x, y) at [y * W]
+};
+
+// 8 rows y0 .. y0+7 from stage buffer F (flow box rows y0-1 .. y0+8, prev box rows y0 .. y0+7).
+// kEdge = false: all 8 rows and row y0+8 lie inside the image (no per-row masks).
+template <bool kVal, bool kGrad, bool kEdge>
+__device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const SweepConst& c, SweepState& st,
+                                            int y0, bool has_left, int lane) {
+    const int lx = lane + 1;
+    const float khx = c.x_r ? c.kh : 0.f, kvx = c.x_in ? c.kv : 0.f, kdx = c.x_r ? c.kd : 0.f;
+    const float mhx = c.x_r ? 1.f : 0.f, mvx = c.x_in ? 1.f : 0.f;
+    // ---- L of the cell left of the segment for the 8 rows: lane j evaluates row y0 + j ----
+    if (kGrad && has_left) {              // warp-uniform
+        const int j = lane & 7, y = y0 + j;
+        const float* fu = F + (j + 1) * kBoxW;
+        const float* fv = fu + kPlane;
+        const float2 p = make_float2(fu[0], fv[0]), q = make_float2(fu[1], fv[1]);
+        const float2 up = make_float2(fu[-kBoxW], fv[-kBoxW]), dn = make_float2(fu[kBoxW], fv[kBoxW]);
+        const float k_h = (!kEdge || y < c.H) ? c.kh : 0.f;
+        const float k_a = (y >= 1 && (!kEdge || y < c.H)) ? c.kd : 0.f;
+        const float k_b = (!kEdge || y + 1 < c.H) ? c.kd : 0.f;
+        float2 lh = f2mul(f2(k_h), charb2<false, true>(q, p).der);
+        lh = f2fma(f2(k_a), charb2<false, true>(q, up).der, lh);
+        lh = f2fma(f2(k_b), charb2<false, true>(q, dn).der, lh);
+        __syncwarp();                     // the previous stage's reads of lh_sm are done
+        if (lane < kStageRows) lh_sm[lane] = lh;
+        __syncwarp();
+    }
+    const unsigned lh_addr = smem_u32(lh_sm);
+    int goff = y0 * c.W;                  // warp-uniform element offset of row y in this lane's column
+    const float yf0 = (float)y0;
+#pragma unroll
+    for (int g0 = 0; g0 < kStageRows; g0 += kGroup) {
+        // the group's next-row neighbours (box row of image row y0+k is k+1)
+        float2 cc[kGroup], dd[kGroup];
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k) {
+            const float* fu = F + (g0 + k + 2) * kBoxW + lx;
+            cc[k] = make_float2(fu[0], fu[kPlane]);
+            dd[k] = make_float2(fu[1], fu[kPlane + 1]);
+        }
+        // ---- phase 1: sampling positions of the group's rows, all taps requested ----
+        Taps tp[kGroup];
+        float2 uv[kGroup];
+        float pv[kGroup];
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k) {
+            const int y = y0 + g0 + k;
+            uv[k] = k == 0 ? st.a : cc[k - 1];
+            const bool valid = c.x_in && (!kEdge || y < c.H);
+            tp[k] = request_taps(c.next, c.H, c.W, c.Hf, c.Wf, c.gn, c.xf, yf0 + (float)(g0 + k), uv[k], valid);
+            pv[k] = F[kPrevOff + (g0 + k) * 32 + lane];
+        }
+        // ---- phase 2: neighbour pairs of the group's rows (no global loads) ----
+        float2 gs[kGroup];
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k) {
+            const int r = g0 + k, y = y0 + r;
+            const bool row_in = !kEdge || y < c.H, row_d = !kEdge || y + 1 < c.H;    // warp-uniform
+            const float2 cn = cc[k], dn = dd[k];
+            const Charb2 ph = charb2<kVal, kGrad>(st.b, st.a);                 // loss.py:76-90
+            const Charb2 pvv = charb2<kVal, kGrad>(cn, st.a);
+            const Charb2 pa = charb2<kVal, kGrad>(dn, st.a);
+            const Charb2 pb = charb2<kVal, kGrad>(st.b, cn);
+            if (kVal) {
+                const float mh_r = row_in ? mhx : 0.f, mv_r = row_d ? mvx : 0.f, md_r = row_d ? mhx : 0.f;
+                st.acc_h = f2fma(f2(mh_r), ph.val, st.acc_h);
+                st.acc_v = f2fma(f2(mv_r), pvv.val, st.acc_v);
+                st.acc_d = f2fma(f2(md_r), f2add(pa.val, pb.val), st.acc_d);
+            }
+            gs[k] = f2(0.f);
+            if (kGrad) {
+                const float kh_r = row_in ? khx : 0.f, kv_r = row_d ? kvx : 0.f, kd_r = row_d ? kdx : 0.f;
+                const float2 gh = f2mul(f2(kh_r), ph.der), gv = f2mul(f2(kv_r), pvv.der);
+                const float2 gda = f2mul(f2(kd_r), pa.der), gdb = f2mul(f2(kd_r), pb.der);
+                const float2 L = f2add(f2add(gh, st.gda_p), gdb);
+                float2 Ll = make_float2(__shfl_up_sync(0xffffffffu, L.x, 1), __shfl_up_sync(0xffffffffu, L.y, 1));
+                // lane 0: the left halo's L of this row (0 in the first column block)
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %2, 0;\n\t"
+                             "@p ld.shared.v2.f32 {%0, %1}, [%3];\n\t}"
+                             : "+f"(Ll.x), "+f"(Ll.y) : "r"(lane), "r"(lh_addr + 8u * r) : "memory");
+                gs[k] = f2sub(f2add(f2sub(Ll, gh), f2sub(st.gv_p, gv)), f2add(gda, st.gdb_p));
+                st.gv_p = gv; st.gda_p = gda; st.gdb_p = gdb;
+            }
+            st.a = cn; st.b = dn;
+        }
+        // ---- phase 3: consume the taps: photometric term, border term, gradient ----
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k) {
+            const int y = y0 + g0 + k;
+            const bool valid = c.x_in && (!kEdge || y < c.H);
+            const Taps& t = tp[k];
+            const float ex = 1.f - t.wx, ey = 1.f - t.wy;
+            // operation order of ATen's CPU grid_sampler (see the notes in loss.cu)
+            const float val = __fmaf_rn(t.se, __fmul_rn(t.wy, t.wx),
+                                        __fmaf_rn(t.sw, __fmul_rn(t.wy, ex),
+                                                  __fmaf_rn(t.ne, __fmul_rn(ey, t.wx),
+                                                            __fmul_rn(t.nw, __fmul_rn(ey, ex)))));
+            const Charb1 pp = charb1<kVal, kGrad>(val - pv[k]);             // loss.py:72-74
+            if (kVal) st.acc_p = fmaf(valid ? 1.f : 0.f, pp.val, st.acc_p);
+            float2 gout = gs[k];
+            if (kGrad) {
+                const float ddx = (t.ne - t.nw) * ey + (t.se - t.sw) * t.wy;
+                const float ddy = (t.sw - t.nw) * ex + (t.se - t.ne) * t.wx;
+                gout = f2fma(f2(c.k_ph * pp.der), make_float2(ddx, ddy), gout);
+            }
+            if (__any_sync(0xffffffffu, t.bad)) {                          // warp-uniform, rare
+                const Charb2 bo = charb2<kVal, kGrad>(uv[k], f2(0.f));
+                const float m_b = t.bad ? 1.f : 0.f;
+                if (kVal) {
+                    st.acc_o = fmaf(m_b, bo.val.x + bo.val.y, st.acc_o);
+                    st.acc_n += m_b;
+                }
+                if (kGrad) gout = f2fma(f2(t.bad ? c.k_ob : 0.f), bo.der, gout);
+            }
+            if (kGrad && valid) {
+                c.grad0[goff] = gout.x;
+                c.grad1[goff] = gout.y;
+            }
+            goff += c.W;
+        }
+    }
+}
+
+// A stage filled with plain loads (scales a tensor map cannot describe): the same box layout,
+// zero outside the image.  All lanes; the caller separates it from the readers with __syncwarp.
+__device__ __forceinline__ void stage_manual(float* F, const float* __restrict__ flow, const float* __restrict__ prev,
+                                             int H, int W, int y0, int x0, int lane) {
+    const int plane = H * W;
+#pragma unroll 1
+    for (int r = 0; r < kBoxH; ++r) {
+        const int y = y0 - 1 + r;
+        const bool yok = y >= 0 && y < H;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int cidx = lane + 32 * h, x = x0 - 1 + cidx;
+            if (cidx < kBoxW) {
+                const bool ok = yok && x >= 0 && x < W;
+                F[r * kBoxW + cidx] = ok ? __ldg(flow + y * W + x) : 0.f;
+                F[kPlane + r * kBoxW + cidx] = ok ? __ldg(flow + plane + y * W + x) : 0.f;
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < kStageRows; ++r) {
+        const int y = y0 + r, x = x0 + lane;
+        F[kPrevOff + r * 32 + lane] = (y < H && x < W) ? __ldg(prev + y * W + x) : 0.f;
+    }
+}
+
+template <bool kVal, bool kGrad>
+__global__ void __launch_bounds__(32, DVSOF_LOSS_MIN_CTAS)
+warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_constant__ LossMaps maps,
+                      const int32_t* __restrict__ match_idx, const float* __restrict__ grad_terms,
+                      const int32_t* __restrict__ n_bad_in, int bad_per_tile, const LossWorkspace ws, float* terms,
+                      int32_t* __restrict__ n_bad_out, float* __restrict__ loss_out) {
+    __shared__ __align__(128) float ring[kRingStages][kStageFloats];
+    __shared__ __align__(8) uint64_t bars[kRingStages];
+    __shared__ __align__(8) float2 lh_sm[kStageRows];
+    __shared__ double dred[1][7];
+    __shared__ bool is_last;
+    pdl_launch_dependents();
+    const int lane = threadIdx.x;
+    const TileCoord tc = decode_segment(tab, blockIdx.x);
+    const int S = tab.n_scales, P = tab.n_pred;
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const int plane = H * W;
+    const int rows = min(tab.seg_rows[tc.s], H - tc.y0);
+    const int n_stages = (rows + kStageRows - 1) / kStageRows;
+    const bool tma = tab.use_tma[tc.s] != 0;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    const unsigned bar0 = smem_u32(&bars[0]), ring0 = smem_u32(&ring[0][0]);
+    if (lane < kStageRows) lh_sm[lane] = make_float2(0.f, 0.f);
+    if (tma && lane == 0) {
+        mbar_init(bar0, 1);
+        mbar_init(bar0 + 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // the flow is an input of the call: stage 0's box is requested while the prelude (pyramid
+        // levels, match_idx, tile counts, tickets) may still be running
+        mbar_expect_tx(bar0, kFlowBoxBytes + kPrevBoxBytes);
+        tma_load_3d(ring0, &maps.flow[tc.s], bar0, tc.x0 - 1, tc.y0 - 1, 2 * tc.n);
+    }
+    pdl_wait_for(match_idx, n_bad_in);             // both come from the prelude (see pdl_acquire)
+    const int i_prev = match_idx[tc.n], i_next = match_idx[P + tc.n];
+    if (tma && lane == 0)
+        tma_load_3d(ring0 + 4u * kPrevOff, &maps.prev[tc.s], bar0, tc.x0, tc.y0, i_prev);
+    __syncwarp();
+
+    SweepConst c;
+    c.H = H; c.W = W;
+    c.Hf = (float)H; c.Wf = (float)W;
+    const int x = tc.x0 + lane;
+    c.xf = (float)x;
+    c.x_in = x < W; c.x_r = x + 1 < W;
+    c.kh = c.kv = c.kd = c.k_ph = c.k_ob = 0.f;
+    if (kGrad) {
+        // d(loss)/d(term) of this scale: device vector (generic backward) or host coefficients (fused)
+        const float g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
+        const float g_ph = grad_terms ? grad_terms[S + tc.s] : tab.coef[DVSOF_MAX_SCALES + tc.s];
+        const float g_ob = grad_terms ? grad_terms[2 * S + tc.s] : tab.coef[2 * DVSOF_MAX_SCALES + tc.s];
+        // 2 alpha / (element count of the mean), per direction, precomputed on the host
+        c.kh = g_sm * tab.norm[0][tc.s];
+        c.kv = g_sm * tab.norm[1][tc.s];
+        c.kd = g_sm * tab.norm[2][tc.s];
+        c.k_ph = g_ph * tab.norm[3][tc.s];
+        int nb;
+        if (bad_per_tile) {                       // per-tile counts of this (scale, prediction): sum them
+            const int per = tab.tiles_x[tc.s] * tab.tiles_y[tc.s];
+            const int32_t* tb = n_bad_in + tab.cta_begin[tc.s] + tc.n * per;
+            nb = 0;
+            for (int t = lane; t < per; t += 32) nb += __ldcg(tb + t);
+            nb = __reduce_add_sync(0xffffffffu, nb);
+        } else {
+            nb = n_bad_in[tc.s * P + tc.n];
+        }
+        c.k_ob = nb > 0 ? __fdividef(g_ob * tab.norm[4][tc.s], (float)nb) : 0.f;   // loss.py:99-113
+    }
+    c.gn = GridNorm{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
+    const float* prev = tab.images[tc.s] + (size_t)i_prev * plane;
+    c.next = tab.images[tc.s] + (size_t)i_next * plane;
+    c.grad0 = kGrad ? tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane + x : nullptr;
+    c.grad1 = kGrad ? c.grad0 + plane : nullptr;
+    asm volatile("" : "+l"(c.next), "+l"(c.grad0), "+l"(c.grad1));  // finished bases: access = base + 32-bit offset
+
+    SweepState st;
+    st.a = st.b = f2(0.f);
+    st.acc_h = st.acc_v = st.acc_d = f2(0.f);
+    st.acc_p = st.acc_o = st.acc_n = 0.f;
+    st.gv_p = st.gda_p = st.gdb_p = f2(0.f);
+    const bool has_left = tc.x0 > 0;
+#pragma unroll 1
+    for (int j = 0; j < n_stages; ++j) {
+        const int y0 = tc.y0 + j * kStageRows;
+        float* F = ring[j & 1];
+        if (tma) {
+            if (j + 1 < n_stages) {               // request the next stage, then wait for this one
+                __syncwarp();                     // every lane is done with the buffer being refilled
+                if (lane == 0) {
+                    const unsigned bar = bar0 + 8u * ((j + 1) & 1), dst = ring0 + 4u * kStageFloats * ((j + 1) & 1);
+                    mbar_expect_tx(bar, kFlowBoxBytes + kPrevBoxBytes);
+                    tma_load_3d(dst, &maps.flow[tc.s], bar, tc.x0 - 1, y0 + kStageRows - 1, 2 * tc.n);
+                    tma_load_3d(dst + 4u * kPrevOff, &maps.prev[tc.s], bar, tc.x0, y0 + kStageRows, i_prev);
+                }
+            }
+            mbar_wait(bar0 + 8u * (j & 1), (unsigned)(j >> 1) & 1u);
+        } else {
+            __syncwarp();
+            stage_manual(F, flow, prev, H, W, y0, tc.x0, lane);
+            __syncwarp();
+        }
+        if (j == 0) {                             // first row of the segment and the cell row above it
+            const float* fu = F + kBoxW + lane + 1;
+            st.a = make_float2(fu[0], fu[kPlane]);
+            st.b = make_float2(fu[1], fu[kPlane + 1]);
+            if (kGrad && tc.y0 > 0) {             // the pairs reaching into row y0 from above
+                const float2 ua = make_float2(fu[-kBoxW], fu[kPlane - kBoxW]);
+                const float2 ub = make_float2(fu[1 - kBoxW], fu[kPlane + 1 - kBoxW]);
+                const float kvx = c.x_in ? c.kv : 0.f, kdx = c.x_r ? c.kd : 0.f;
+                st.gv_p = f2mul(f2(kvx), charb2<false, true>(st.a, ua).der);
+                st.gda_p = f2mul(f2(kdx), charb2<false, true>(st.b, ua).der);
+                st.gdb_p = f2mul(f2(kdx), charb2<false, true>(ub, st.a).der);
+            }
+        }
+        if (y0 + kStageRows < H) sweep_stage<kVal, kGrad, false>(F, lh_sm, c, st, y0, has_left, lane);
+        else sweep_stage<kVal, kGrad, true>(F, lh_sm, c, st, y0, has_left, lane);
+    }
+    if (!kVal) return;
+    // record: [photo, smooth_h, smooth_v, smooth_diag (both), -, outborder_sum, n_bad, -]
+    float acc[kRec] = {st.acc_p, st.acc_h.x + st.acc_h.y, st.acc_v.x + st.acc_v.y, st.acc_d.x + st.acc_d.y,
+                       0.f, st.acc_o, st.acc_n, 0.f};
+    warp_sum8(acc, lane);
+    if ((lane & 3) == 0)
+        __stcg(ws.partials + (size_t)blockIdx.x * kRec + (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)), acc[0]);
+    finish_tile(tab, tc, ws, terms, n_bad_out, loss_out, dred, &is_last);
+}
+
+// Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
+// pass, which needs it for the gradient of the border term: same coordinates, same comparison.
+// One 32x32 tile per CTA of NW warps (tile index `cta`).  per_tile: the tile's count is stored at
+// n_bad[cta] (no atomics, nothing to zero; the fused kernel sums a pair's tiles itself); otherwise
+// it is added to n_bad[s * P + n], which must be zero beforehand.
+template <int NW, int NT = 1>
+__device__ __forceinline__ void outborder_count_tile(const ScaleTable& tab, int32_t* __restrict__ n_bad,
+                                                     bool per_tile, int first_tile,
+                                                     int* cnt /* shared, NW * NT ints */) {
+    constexpr int kRows = kTile / NW;
+    const int lane = threadIdx.x & 31, warp_all = threadIdx.x >> 5;
+    const int group = NT > 1 ? warp_all / NW : 0, warp = warp_all - group * NW;
+    const int cta = first_tile + group;
+    const bool active = NT == 1 || cta < tab.cta_begin[DVSOF_MAX_SCALES];
+    const TileCoord tc = decode_cta_fast(tab, active ? cta : 0);
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const int plane = H * W;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    const float* flow1 = flow + plane;
+    asm volatile("" : "+l"(flow), "+l"(flow1));
+    const BorderTest bt = border_test(tab, tc.s);
+    const int x = tc.x0 + lane, ys = tc.y0 + warp * kRows;
+    const float xf = (float)x;
+    int n = 0;
+    float u[kRows], v[kRows];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const bool ok = active && x < W && ys + r < H;
+        const int off = (ys + r) * W + x;
+        u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
+        v[r] = ok ? __ldg(flow1 + off) : 0.f;
+    }
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+        const bool ok = active && x < W && ys + r < H;
+        n += (ok && outside_grid(__fadd_rn(xf, u[r]), __fadd_rn((float)(ys + r), v[r]), bt)) ? 1 : 0;
+    }
+    n = warp_sum(n);
+    if (lane == 0) cnt[warp_all] = n;
+    __syncthreads();
+    if (warp == 0 && lane == 0 && active) {
+        int t = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t += cnt[group * NW + w];
+        if (per_tile) n_bad[cta] = t;
+        else if (t) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, t);
+    }
+}
+
+// The same count with a whole 32x32 tile per WARP (8 rows in flight at a time): the tile decode
+// and pointer set-up are paid once per 32 rows and no cross-warp reduction is needed.  Used by the
+// 1024-thread pyramid kernel, where a CTA takes 32 tiles.
+__device__ __forceinline__ void outborder_count_warp_tile(const ScaleTable& tab, int32_t* __restrict__ n_bad,
+                                                          bool per_tile, int cta) {
+    constexpr int kRows = 8;
+    if (cta >= tab.cta_begin[DVSOF_MAX_SCALES]) return;          // warp-uniform
+    const TileCoord tc = decode_cta_fast(tab, cta);
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const int plane = H * W;
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
+    const float* flow1 = flow + plane;
+    asm volatile("" : "+l"(flow), "+l"(flow1));
+    const BorderTest bt = border_test(tab, tc.s);
+    const int lane = threadIdx.x & 31;
+    const int x = tc.x0 + lane;
+    const float xf = (float)x;
+    int n = 0;
+    if (x < W) {
+#pragma unroll 1
+        for (int ys = tc.y0; ys < min(tc.y0 + kTile, H); ys += kRows) {
+            float u[kRows], v[kRows];
+#pragma unroll
+            for (int r = 0; r < kRows; ++r) {
+                const bool ok = ys + r < H;
+                const int off = (ys + r) * W + x;
+                u[r] = ok ? __ldg(flow + off) : 0.f;             // 0 flow is never out of border
+                v[r] = ok ? __ldg(flow1 + off) : 0.f;
+            }
+#pragma unroll
+            for (int r = 0; r < kRows; ++r) {
+                n += (ys + r < H && outside_grid(__fadd_rn(xf, u[r]), __fadd_rn((float)(ys + r), v[r]), bt)) ? 1 : 0;
+            }
+        }
+    }
+    n = warp_sum(n);
+    if (lane == 0) {
+        if (per_tile) n_bad[cta] = n;
+        else if (n) atomicAdd(n_bad + tc.s * tab.n_pred + tc.n, n);
+    }
+}
+
+// stand-alone launch (dvsof_warp_loss_fused with count_pass; the multiscale call runs the same
+// tiles as a side job of the pyramid launch)
+constexpr int kCountWarps = 4;
+__global__ void __launch_bounds__(32 * kCountWarps)
+outborder_count_kernel(const __grid_constant__ ScaleTable tab, int32_t* __restrict__ n_bad) {
+    __shared__ int cnt[kCountWarps];
+    outborder_count_tile<kCountWarps>(tab, n_bad, false, blockIdx.x, cnt);
+}
+
+}  // namespace dvsof

@@ -49,6 +49,7 @@ def _scale_struct(flows, levels, grads=None):
     sc = _lib.LossScales()
     sc.n_scales = len(flows)
     sc.n_pred = flows[0].shape[0]
+    sc.n_images = levels[0].shape[0]
     for s, (f, im) in enumerate(zip(flows, levels)):
         sc.H[s], sc.W[s] = f.shape[-2], f.shape[-1]
         sc.flow[s] = f.data_ptr()
@@ -135,7 +136,7 @@ class _Plan:
         self.gtotal = off
         self.fwd, self.bwd, self.frames = _lib.LossScales(), _lib.LossScales(), _lib.LossFrames()
         for sc in (self.fwd, self.bwd):
-            sc.n_scales, sc.n_pred = S, P
+            sc.n_scales, sc.n_pred, sc.n_images = S, P, D
             for s, (h, w) in enumerate(shapes):
                 sc.H[s], sc.W[s] = h, w
         self.frames.n_images, self.frames.H0, self.frames.W0 = D, H, W

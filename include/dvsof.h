@@ -200,6 +200,10 @@ int dvsof_resize_bilinear(const float* src, int64_t D, int32_t Hin, int32_t Win,
 typedef struct {
     int32_t n_scales;
     int32_t n_pred;                          /* P */
+    int32_t n_images;                        /* D: frames in every images[s]; 0 = unknown (the level tiles
+                                              * are then staged with plain loads instead of TMA; the
+                                              * multiscale calls take it from `frames`) */
+    int32_t reserved_;
     int32_t H[DVSOF_MAX_SCALES], W[DVSOF_MAX_SCALES];
     const float* flow[DVSOF_MAX_SCALES];     /* [dev] (P,2,H,W) contiguous */
     const float* images[DVSOF_MAX_SCALES];   /* [dev] (D,H,W) pyramid level */
