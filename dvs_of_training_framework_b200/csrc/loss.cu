@@ -596,8 +596,10 @@ static void plan_segments(const dvsof_loss_scales_t* sc, ScaleTable* tab) {
         tab->seg_begin[s] = (int)begin;
         begin += (int64_t)tab->seg_per[s] * sc->n_pred;
         // a tensor map needs 16-byte aligned bases and row pitches
-        tab->use_tma[s] = sc->W[s] % 4 == 0 && aligned16(sc->flow[s]) && aligned16(sc->images[s]) &&
-                          sc->n_images > 0;
+        // bit 0: the flow box, bit 1: the prev-level box
+        tab->use_tma[s] = sc->W[s] % 4 == 0 ? (aligned16(sc->flow[s]) ? 1 : 0) |
+                                                  (aligned16(sc->images[s]) && sc->n_images > 0 ? 2 : 0)
+                                            : 0;
     }
     for (int s = sc->n_scales; s <= DVSOF_MAX_SCALES; ++s) tab->seg_begin[s] = (int)begin;
     for (int s = sc->n_scales; s < DVSOF_MAX_SCALES; ++s) tab->use_tma[s] = 0;
@@ -632,10 +634,13 @@ static bool encode_map3(CUtensorMap* m, const float* base, int W, int H, int64_t
 }
 static void build_maps(const dvsof_loss_scales_t* sc, ScaleTable* tab, LossMaps* maps) {
     for (int s = 0; s < sc->n_scales; ++s) {
-        if (!tab->use_tma[s]) continue;
-        if (!encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH, 2) ||
+        // no driver entry point / unencodable: plain loads for that part
+        if ((tab->use_tma[s] & 1) &&
+            !encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH, 2))
+            tab->use_tma[s] &= ~1;
+        if ((tab->use_tma[s] & 2) &&
             !encode_map3(&maps->prev[s], sc->images[s], sc->W[s], sc->H[s], sc->n_images, 32, kStageRows, 1))
-            tab->use_tma[s] = 0;             // no driver entry point / unencodable: plain loads
+            tab->use_tma[s] &= ~2;
     }
 }
 
@@ -726,6 +731,11 @@ static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTa
     LossMaps maps;
     if (getenv("DVSOF_LOSS_NO_TMA"))                 // tests: force the plain-load staging
         for (int s = 0; s < DVSOF_MAX_SCALES; ++s) tab.use_tma[s] = 0;
+    if (const char* e = getenv("DVSOF_LOSS_TMA_MASK"))   // debugging: 1 = flow boxes only, 2 = prev boxes only
+        for (int s = 0; s < DVSOF_MAX_SCALES; ++s) tab.use_tma[s] &= atoi(e);
+    if (const char* e = getenv("DVSOF_LOSS_TMA_MINW"))   // debugging: tensor maps only for scales at least this wide
+        for (int s = 0; s < sc->n_scales; ++s)
+            if (sc->W[s] < atoi(e) || sc->H[s] < atoi(e)) tab.use_tma[s] = 0;
     build_maps(sc, &tab, &maps);
     return launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
                          stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws, terms,

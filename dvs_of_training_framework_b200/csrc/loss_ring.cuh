@@ -346,8 +346,8 @@ __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const
 
 // A stage filled with plain loads (scales a tensor map cannot describe): the same box layout,
 // zero outside the image.  All lanes; the caller separates it from the readers with __syncwarp.
-__device__ __forceinline__ void stage_manual(float* F, const float* __restrict__ flow, const float* __restrict__ prev,
-                                             int H, int W, int y0, int x0, int lane) {
+__device__ __forceinline__ void stage_manual_flow(float* F, const float* __restrict__ flow, int H, int W, int y0,
+                                                  int x0, int lane) {
     const int plane = H * W;
 #pragma unroll 1
     for (int r = 0; r < kBoxH; ++r) {
@@ -363,6 +363,9 @@ __device__ __forceinline__ void stage_manual(float* F, const float* __restrict__
             }
         }
     }
+}
+__device__ __forceinline__ void stage_manual_prev(float* F, const float* __restrict__ prev, int H, int W, int y0,
+                                                  int x0, int lane) {
 #pragma unroll
     for (int r = 0; r < kStageRows; ++r) {
         const int y = y0 + r, x = x0 + lane;
@@ -389,7 +392,9 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
     const int plane = H * W;
     const int rows = min(tab.seg_rows[tc.s], H - tc.y0);
     const int n_stages = (rows + kStageRows - 1) / kStageRows;
-    const bool tma = tab.use_tma[tc.s] != 0;
+    const bool tma_flow = (tab.use_tma[tc.s] & 1) != 0, tma_prev = (tab.use_tma[tc.s] & 2) != 0;
+    const bool tma = tma_flow || tma_prev;
+    const unsigned stage_bytes = (tma_flow ? kFlowBoxBytes : 0u) + (tma_prev ? kPrevBoxBytes : 0u);
     const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     const unsigned bar0 = smem_u32(&bars[0]), ring0 = smem_u32(&ring[0][0]);
     if (lane < kStageRows) lh_sm[lane] = make_float2(0.f, 0.f);
@@ -399,12 +404,12 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         // the flow is an input of the call: stage 0's box is requested while the prelude (pyramid
         // levels, match_idx, tile counts, tickets) may still be running
-        mbar_expect_tx(bar0, kFlowBoxBytes + kPrevBoxBytes);
-        tma_load_3d(ring0, &maps.flow[tc.s], bar0, tc.x0 - 1, tc.y0 - 1, 2 * tc.n);
+        mbar_expect_tx(bar0, stage_bytes);
+        if (tma_flow) tma_load_3d(ring0, &maps.flow[tc.s], bar0, tc.x0 - 1, tc.y0 - 1, 2 * tc.n);
     }
     pdl_wait_for(match_idx, n_bad_in);             // both come from the prelude (see pdl_acquire)
     const int i_prev = match_idx[tc.n], i_next = match_idx[P + tc.n];
-    if (tma && lane == 0)
+    if (tma_prev && lane == 0)
         tma_load_3d(ring0 + 4u * kPrevOff, &maps.prev[tc.s], bar0, tc.x0, tc.y0, i_prev);
     __syncwarp();
 
@@ -459,17 +464,19 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
                 __syncwarp();                     // every lane is done with the buffer being refilled
                 if (lane == 0) {
                     const unsigned bar = bar0 + 8u * ((j + 1) & 1), dst = ring0 + 4u * kStageFloats * ((j + 1) & 1);
-                    mbar_expect_tx(bar, kFlowBoxBytes + kPrevBoxBytes);
-                    tma_load_3d(dst, &maps.flow[tc.s], bar, tc.x0 - 1, y0 + kStageRows - 1, 2 * tc.n);
-                    tma_load_3d(dst + 4u * kPrevOff, &maps.prev[tc.s], bar, tc.x0, y0 + kStageRows, i_prev);
+                    mbar_expect_tx(bar, stage_bytes);
+                    if (tma_flow) tma_load_3d(dst, &maps.flow[tc.s], bar, tc.x0 - 1, y0 + kStageRows - 1, 2 * tc.n);
+                    if (tma_prev) tma_load_3d(dst + 4u * kPrevOff, &maps.prev[tc.s], bar, tc.x0, y0 + kStageRows, i_prev);
                 }
             }
-            mbar_wait(bar0 + 8u * (j & 1), (unsigned)(j >> 1) & 1u);
-        } else {
+        }
+        if (!tma_flow || !tma_prev) {             // the parts no tensor map describes: plain loads
             __syncwarp();
-            stage_manual(F, flow, prev, H, W, y0, tc.x0, lane);
+            if (!tma_flow) stage_manual_flow(F, flow, H, W, y0, tc.x0, lane);
+            if (!tma_prev) stage_manual_prev(F, prev, H, W, y0, tc.x0, lane);
             __syncwarp();
         }
+        if (tma) mbar_wait(bar0 + 8u * (j & 1), (unsigned)(j >> 1) & 1u);
         if (j == 0) {                             // first row of the segment and the cell row above it
             const float* fu = F + kBoxW + lane + 1;
             st.a = make_float2(fu[0], fu[kPlane]);
