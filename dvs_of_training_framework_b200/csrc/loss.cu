@@ -636,7 +636,8 @@ static void build_maps(const dvsof_loss_scales_t* sc, ScaleTable* tab, LossMaps*
     for (int s = 0; s < sc->n_scales; ++s) {
         // no driver entry point / unencodable: plain loads for that part
         if ((tab->use_tma[s] & 1) &&
-            !encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH, 2))
+            !encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH,
+                         DVSOF_LOSS_FLOW_SPLIT ? 1 : 2))
             tab->use_tma[s] &= ~1;
         if ((tab->use_tma[s] & 2) &&
             !encode_map3(&maps->prev[s], sc->images[s], sc->W[s], sc->H[s], sc->n_images, 32, kStageRows, 1))

@@ -44,16 +44,23 @@ namespace dvsof {
 constexpr int kGroup = DVSOF_LOSS_GROUP;
 constexpr int kStageRows = 8;                               // rows per ring stage
 constexpr int kRingStages = 2;
-constexpr int kBoxW = 36, kBoxH = kStageRows + 2;           // flow box (floats per row, rows)
+#ifndef DVSOF_LOSS_BOX_LEFT
+#define DVSOF_LOSS_BOX_LEFT 4             // columns staged left of the segment (1 needed)
+#endif
+#ifndef DVSOF_LOSS_FLOW_SPLIT
+#define DVSOF_LOSS_FLOW_SPLIT 0           // 1: one TMA per flow channel
+#endif
+constexpr int kBoxLeft = DVSOF_LOSS_BOX_LEFT;
+constexpr int kBoxW = kBoxLeft == 1 ? 36 : 40, kBoxH = kStageRows + 2;   // flow box (floats per row, rows)
 constexpr int kPlane = kBoxW * kBoxH;                       // one channel of the flow box
-constexpr int kPrevOff = 736;                               // floats: 2944 B, 128-byte aligned
-constexpr int kStageFloats = 1024;
+constexpr int kPrevOff = (2 * kPlane + 31) / 32 * 32;       // floats; 128-byte aligned
+constexpr int kStageFloats = (kPrevOff + kStageRows * 32 + 31) / 32 * 32;
 constexpr unsigned kFlowBoxBytes = 2u * kPlane * 4u, kPrevBoxBytes = kStageRows * 32u * 4u;
 static_assert(kStageRows % kGroup == 0, "a stage is a whole number of groups");
 static_assert(2 * kPlane <= kPrevOff && kPrevOff + kStageRows * 32 <= kStageFloats, "stage layout");
 
 struct LossMaps {                         // tensor maps of the launch (kernel parameter space)
-    CUtensorMap flow[DVSOF_MAX_SCALES];   // (W, H, 2P) fp32, box (36, 10, 2)
+    CUtensorMap flow[DVSOF_MAX_SCALES];   // (W, H, 2P) fp32, box (kBoxW, 10, 2)
     CUtensorMap prev[DVSOF_MAX_SCALES];   // (W, H, D) fp32, box (32, 8, 1)
 };
 
@@ -170,9 +177,22 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
         "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
 // the executing CTA's shared window is part of its (1-CTA) cluster window: same 32-bit address
-__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
+__device__ __forceinline__ void tma_load_3d_raw(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
+    tma_load_3d_raw(dst, map, bar, c0, c1, c2);
+}
+// the flow box of a stage: columns x0 - kBoxLeft .., rows y0 - 1 .., both channels of prediction n
+__device__ __forceinline__ void tma_load_flow(unsigned dst, const CUtensorMap* map, unsigned bar, int x0, int y0, int n) {
+    if (DVSOF_LOSS_FLOW_SPLIT) {
+        tma_load_3d_raw(dst, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n);
+        tma_load_3d_raw(dst + 4u * kPlane, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n + 1);
+    } else {
+        tma_load_3d_raw(dst, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n);
+    }
 }
 
 // One row's bilinear taps in flight: requested in phase 1, consumed in phase 3.
@@ -228,13 +248,13 @@ struct SweepConst {
 template <bool kVal, bool kGrad, bool kEdge>
 __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const SweepConst& c, SweepState& st,
                                             int y0, bool has_left, int lane) {
-    const int lx = lane + 1;
+    const int lx = lane + kBoxLeft;
     const float khx = c.x_r ? c.kh : 0.f, kvx = c.x_in ? c.kv : 0.f, kdx = c.x_r ? c.kd : 0.f;
     const float mhx = c.x_r ? 1.f : 0.f, mvx = c.x_in ? 1.f : 0.f;
     // ---- L of the cell left of the segment for the 8 rows: lane j evaluates row y0 + j ----
     if (kGrad && has_left) {              // warp-uniform
         const int j = lane & 7, y = y0 + j;
-        const float* fu = F + (j + 1) * kBoxW;
+        const float* fu = F + (j + 1) * kBoxW + (kBoxLeft - 1);
         const float* fv = fu + kPlane;
         const float2 p = make_float2(fu[0], fv[0]), q = make_float2(fu[1], fv[1]);
         const float2 up = make_float2(fu[-kBoxW], fv[-kBoxW]), dn = make_float2(fu[kBoxW], fv[kBoxW]);
@@ -355,7 +375,7 @@ __device__ __forceinline__ void stage_manual_flow(float* F, const float* __restr
         const bool yok = y >= 0 && y < H;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
-            const int cidx = lane + 32 * h, x = x0 - 1 + cidx;
+            const int cidx = lane + 32 * h, x = x0 - kBoxLeft + cidx;
             if (cidx < kBoxW) {
                 const bool ok = yok && x >= 0 && x < W;
                 F[r * kBoxW + cidx] = ok ? __ldg(flow + y * W + x) : 0.f;
@@ -405,7 +425,7 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
         // the flow is an input of the call: stage 0's box is requested while the prelude (pyramid
         // levels, match_idx, tile counts, tickets) may still be running
         mbar_expect_tx(bar0, stage_bytes);
-        if (tma_flow) tma_load_3d(ring0, &maps.flow[tc.s], bar0, tc.x0 - 1, tc.y0 - 1, 2 * tc.n);
+        if (tma_flow) tma_load_flow(ring0, &maps.flow[tc.s], bar0, tc.x0, tc.y0, tc.n);
     }
     pdl_wait_for(match_idx, n_bad_in);             // both come from the prelude (see pdl_acquire)
     const int i_prev = match_idx[tc.n], i_next = match_idx[P + tc.n];
@@ -465,7 +485,7 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
                 if (lane == 0) {
                     const unsigned bar = bar0 + 8u * ((j + 1) & 1), dst = ring0 + 4u * kStageFloats * ((j + 1) & 1);
                     mbar_expect_tx(bar, stage_bytes);
-                    if (tma_flow) tma_load_3d(dst, &maps.flow[tc.s], bar, tc.x0 - 1, y0 + kStageRows - 1, 2 * tc.n);
+                    if (tma_flow) tma_load_flow(dst, &maps.flow[tc.s], bar, tc.x0, y0 + kStageRows, tc.n);
                     if (tma_prev) tma_load_3d(dst + 4u * kPrevOff, &maps.prev[tc.s], bar, tc.x0, y0 + kStageRows, i_prev);
                 }
             }
@@ -478,7 +498,7 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
         }
         if (tma) mbar_wait(bar0 + 8u * (j & 1), (unsigned)(j >> 1) & 1u);
         if (j == 0) {                             // first row of the segment and the cell row above it
-            const float* fu = F + kBoxW + lane + 1;
+            const float* fu = F + kBoxW + lane + kBoxLeft;
             st.a = make_float2(fu[0], fu[kPlane]);
             st.b = make_float2(fu[1], fu[kPlane + 1]);
             if (kGrad && tc.y0 > 0) {             // the pairs reaching into row y0 from above
