@@ -117,15 +117,15 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
     match_idx[i] = idx;
 }
 
-// ------------------------------ deterministic reduction of the tile records ------------
-// record of one tile (CTA): [photo, smooth_h, smooth_v, smooth_diag, -, outborder_sum, n_bad, -].
-// Two levels, each run by whichever CTA arrives LAST at a ticket (release/acquire at gpu scope,
-// issued by one thread; the data is read back with L2 loads):
-//   pair level  -- the last tile of a (scale, prediction) pair sums that pair's records in a
-//                  fixed order in fp64 and writes the pair record + n_i;
-//   final level -- the last pair sums the pair records per scale, again in a fixed order, and
-//                  writes the 3*S terms (+ the weighted loss of the fused pass).
-// Results do not depend on arrival order; tickets reset themselves for the next call.
+// ------------------------------ deterministic reduction of the segment records ---------
+// record of one sweep segment (warp): [photo, smooth_h, smooth_v, smooth_diag, -, outborder_sum, n_bad, -].
+// Two levels, both in loss_reduce_kernel (launched behind the sweep):
+//   pair level  -- one CTA per (scale, prediction) pair sums that pair's records in a fixed order
+//                  in fp64 and writes the pair record + n_i;
+//   final level -- the CTA that arrives LAST at the ticket (release/acquire at gpu scope, issued
+//                  by one thread; the data is read back with L2 loads) sums the pair records per
+//                  scale, again in a fixed order, and writes the 3*S terms (+ the weighted loss).
+// Results do not depend on arrival order; the ticket resets itself for the next call.
 constexpr int kRec = 8;            // floats per tile record
 constexpr int kPairRec = 8;        // doubles per pair record: [photo, h, v, diag, outborder/(2 n_i P), -, -, -]
 
@@ -211,37 +211,38 @@ __device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, floa
     }
 }
 
-// workspace carved by the host: tile records | pair records | tickets (1 + S*P words) | tile counts
+// workspace carved by the host: segment records | pair records | ticket | per-tile border counts
 struct LossWorkspace {
     float* partials;
     double* pair_rec;
-    unsigned* tickets;     // [0] = pairs finished; [1 + s*P + n] = tiles of the pair finished
+    unsigned* tickets;     // [0] = pairs finished (loss_reduce_kernel)
     int32_t* tile_bad;     // out-of-border count of every tile (multiscale fused pass)
 };
 
-// Called by every CTA after its tile record is in `partials` (written by threads < 7, then a
-// __syncthreads by the caller is NOT needed: done here).
-__device__ __forceinline__ void finish_tile(const ScaleTable& tab, const TileCoord& tc,
-                                            const LossWorkspace& ws, float* terms, int32_t* n_bad,
-                                            float* loss_out, double (*red)[7], bool* flag) {
-    const int P = tab.n_pred, pair = tc.s * P + tc.n;
-    __syncthreads();                                       // record stores happen-before the arrive
-    if (threadIdx.x == 0)
-        *flag = ticket_arrive(ws.tickets + 1 + pair) == (unsigned)tab.seg_per[tc.s] - 1u;
+// The reduction runs as its own small kernel behind the sweep (programmatic dependent launch: it is
+// resident and waiting when the sweep's last warp retires).  A ticket per sweep warp -- a gpu-scope
+// release fence + atomic at the end of every 1-warp CTA -- was measured at 13-25 us of a 30-100 us
+// sweep (gpurun_out/r02h: every warp holds its SM slot while its gradient stores drain); a kernel
+// boundary orders the records for free.  One CTA per (scale, prediction) pair sums that pair's
+// segment records; the last of these S*P CTAs (one ticket each) writes the terms and the loss.
+constexpr int kReduceThreads = 128;
+__global__ void __launch_bounds__(kReduceThreads)
+loss_reduce_kernel(const __grid_constant__ ScaleTable tab, const LossWorkspace ws, float* terms,
+                   int32_t* __restrict__ n_bad, float* __restrict__ loss_out) {
+    __shared__ double red[kReduceThreads / 32][7];
+    __shared__ bool is_last;
+    pdl_launch_dependents();
+    pdl_wait();                                            // the sweep's records are complete and visible
+    const int P = tab.n_pred, pair = blockIdx.x;
+    const int s = pair / P, n = pair - s * P;
+    reduce_pair(tab, s, n, ws.partials, ws.pair_rec, n_bad, red);
     __syncthreads();
-    if (!*flag) return;
-    __threadfence();                                       // acquire side (finishing CTAs only)
-    reduce_pair(tab, tc.s, tc.n, ws.partials, ws.pair_rec, n_bad, red);
+    if (threadIdx.x == 0) is_last = ticket_arrive(ws.tickets) == (unsigned)(tab.n_scales * P) - 1u;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        ws.tickets[1 + pair] = 0u;                         // self-resetting
-        *flag = ticket_arrive(ws.tickets) == (unsigned)(tab.n_scales * P) - 1u;
-    }
-    __syncthreads();
-    if (!*flag) return;
-    __threadfence();
+    if (!is_last) return;
+    __threadfence();                                       // acquire side (the finishing CTA only)
     reduce_final(tab, ws.pair_rec, terms, loss_out);
-    if (threadIdx.x == 0) ws.tickets[0] = 0u;
+    if (threadIdx.x == 0) ws.tickets[0] = 0u;              // self-resetting
 }
 
 // d(loss)/d(flow) *= factor, in place, for all scales in one launch; nothing is touched when the
@@ -699,7 +700,7 @@ static size_t partial_bytes(const ScaleTable& tab) {
 static size_t pair_bytes(const ScaleTable& tab) {
     return round_up((size_t)tab.n_scales * tab.n_pred * kPairRec * sizeof(double), 256);
 }
-static int n_tickets(const ScaleTable& tab) { return 1 + tab.n_scales * tab.n_pred; }
+static int n_tickets(const ScaleTable&) { return 1; }      // the reduce kernel's "pairs finished" counter
 static size_t ticket_bytes(const ScaleTable& tab) { return round_up((size_t)n_tickets(tab) * 4, 256); }
 static LossWorkspace carve(const ScaleTable& tab, void* workspace) {
     char* p = static_cast<char*>(workspace);
@@ -738,9 +739,12 @@ static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTa
         for (int s = 0; s < sc->n_scales; ++s)
             if (sc->W[s] < atoi(e) || sc->H[s] < atoi(e)) tab.use_tma[s] = 0;
     build_maps(sc, &tab, &maps);
-    return launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
-                         stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws, terms,
-                         n_bad_out, loss);
+    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
+                               stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws))
+        return rc;
+    if (!kVal) return DVSOF_OK;
+    return launch_kernel("loss_reduce_kernel", loss_reduce_kernel, tab.n_scales * tab.n_pred, kReduceThreads, 0,
+                         stream, true, tab, ws, terms, n_bad_out, loss);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,

@@ -397,13 +397,10 @@ template <bool kVal, bool kGrad>
 __global__ void __launch_bounds__(32, DVSOF_LOSS_MIN_CTAS)
 warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_constant__ LossMaps maps,
                       const int32_t* __restrict__ match_idx, const float* __restrict__ grad_terms,
-                      const int32_t* __restrict__ n_bad_in, int bad_per_tile, const LossWorkspace ws, float* terms,
-                      int32_t* __restrict__ n_bad_out, float* __restrict__ loss_out) {
+                      const int32_t* __restrict__ n_bad_in, int bad_per_tile, const LossWorkspace ws) {
     __shared__ __align__(128) float ring[kRingStages][kStageFloats];
     __shared__ __align__(8) uint64_t bars[kRingStages];
     __shared__ __align__(8) float2 lh_sm[kStageRows];
-    __shared__ double dred[1][7];
-    __shared__ bool is_last;
     pdl_launch_dependents();
     const int lane = threadIdx.x;
     const TileCoord tc = decode_segment(tab, blockIdx.x);
@@ -514,13 +511,13 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
         else sweep_stage<kVal, kGrad, true>(F, lh_sm, c, st, y0, has_left, lane);
     }
     if (!kVal) return;
-    // record: [photo, smooth_h, smooth_v, smooth_diag (both), -, outborder_sum, n_bad, -]
+    // record: [photo, smooth_h, smooth_v, smooth_diag (both), -, outborder_sum, n_bad, -]; summed by
+    // loss_reduce_kernel (loss.cu) after this launch -- no ticket, no fence here
     float acc[kRec] = {st.acc_p, st.acc_h.x + st.acc_h.y, st.acc_v.x + st.acc_v.y, st.acc_d.x + st.acc_d.y,
                        0.f, st.acc_o, st.acc_n, 0.f};
     warp_sum8(acc, lane);
     if ((lane & 3) == 0)
         __stcg(ws.partials + (size_t)blockIdx.x * kRec + (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)), acc[0]);
-    finish_tile(tab, tc, ws, terms, n_bad_out, loss_out, dred, &is_last);
 }
 
 // Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
