@@ -42,6 +42,7 @@ struct ScaleTable {
     // gradient normalisers 2 alpha / count: [0..2] smoothness h / v / diagonal (incl. the 1/4),
     // [3] photometric 1/(P H W), [4] border 1/(2 P) (divided by n_i in the kernel)
     float norm[5][DVSOF_MAX_SCALES];
+    float lk[3][DVSOF_MAX_SCALES];                      // log2(norm[0..2]); -inf for a direction without pairs
     float coef[3 * DVSOF_MAX_SCALES];                   // fused pass: d(loss)/d(term[k][s]) at [k * MAX + s]
     const float* flow[DVSOF_MAX_SCALES];
     const float* images[DVSOF_MAX_SCALES];
@@ -147,11 +148,25 @@ __device__ void reduce_pair(const ScaleTable& tab, int s, int n, const float* pa
     const int P = tab.n_pred, per = tab.seg_per[s];
     const float* rec = partials + ((size_t)tab.seg_begin[s] + (size_t)n * per) * kRec;
     double a[7] = {0, 0, 0, 0, 0, 0, 0};
-    for (int t = threadIdx.x; t < per; t += blockDim.x) {
-        const float4 r0 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
-        const float4 r1 = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
-        a[0] += (double)r0.x; a[1] += (double)r0.y; a[2] += (double)r0.z; a[3] += (double)r0.w;
-        a[4] += (double)r1.x; a[5] += (double)r1.y; a[6] += (double)r1.z;
+    // four records per thread in flight (the loop is latency bound: every record is an L2 round trip)
+    constexpr int kInFlight = 4;
+    for (int t0 = threadIdx.x; t0 < per; t0 += kInFlight * blockDim.x) {
+        float4 r0[kInFlight], r1[kInFlight];
+#pragma unroll
+        for (int j = 0; j < kInFlight; ++j) {
+            const int t = t0 + j * blockDim.x;
+            if (t < per) {
+                r0[j] = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
+                r1[j] = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
+            } else {
+                r0[j] = r1[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kInFlight; ++j) {               // fixed order: t0, t0 + blockDim, ...
+            a[0] += (double)r0[j].x; a[1] += (double)r0[j].y; a[2] += (double)r0[j].z; a[3] += (double)r0[j].w;
+            a[4] += (double)r1[j].x; a[5] += (double)r1[j].y; a[6] += (double)r1[j].z;
+        }
     }
 #pragma unroll
     for (int k = 0; k < 7; ++k) a[k] = warp_sum_f64(a[k]);
@@ -188,13 +203,8 @@ __device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, floa
         for (int k = 0; k < 5; ++k) a[k] = warp_sum_f64(a[k]);
         if (lane == 0) {
             const int H = tab.H[s], W = tab.W[s];
-            const double N2 = 2.0 * P;
-            const double ch = N2 * H * (W - 1), cv = N2 * (H - 1) * W, cd = N2 * (H - 1) * (W - 1);
-            double sm = 0;
-            if (ch > 0) sm += a[1] / ch;
-            if (cv > 0) sm += a[2] / cv;
-            if (cd > 0) sm += a[3] / cd;
-            terms[s] = (float)(sm / 4.0);                                        // loss.py:87-90
+            // the sweep accumulates k c(d) with k = 2 alpha / (4 x count) per direction (loss.py:87-90)
+            terms[s] = (float)(a[1] / (2.0 * (double)kAlpha));
             terms[S + s] = (float)(a[0] / ((double)P * H * W));                  // loss.py:33
             terms[2 * S + s] = (float)a[4];
         }
@@ -225,7 +235,7 @@ struct LossWorkspace {
 // sweep (gpurun_out/r02h: every warp holds its SM slot while its gradient stores drain); a kernel
 // boundary orders the records for free.  One CTA per (scale, prediction) pair sums that pair's
 // segment records; the last of these S*P CTAs (one ticket each) writes the terms and the loss.
-constexpr int kReduceThreads = 128;
+constexpr int kReduceThreads = 256;
 __global__ void __launch_bounds__(kReduceThreads)
 loss_reduce_kernel(const __grid_constant__ ScaleTable tab, const LossWorkspace ws, float* terms,
                    int32_t* __restrict__ n_bad, float* __restrict__ loss_out) {
@@ -671,7 +681,10 @@ static int build_table(const dvsof_loss_scales_t* sc, ScaleTable* tab, bool need
         tab->ry[s] = dvsof_div_const_ok(hy) ? dvsof_recip_rn(hy) : NAN;
         const double a2 = 2.0 * (double)kAlpha, N2 = 2.0 * sc->n_pred, Hd = sc->H[s], Wd = sc->W[s];
         const double cnt[3] = {N2 * Hd * (Wd - 1), N2 * (Hd - 1) * Wd, N2 * (Hd - 1) * (Wd - 1)};
-        for (int k = 0; k < 3; ++k) tab->norm[k][s] = cnt[k] > 0 ? (float)(a2 * 0.25 / cnt[k]) : 0.f;
+        for (int k = 0; k < 3; ++k) {
+            tab->norm[k][s] = cnt[k] > 0 ? (float)(a2 * 0.25 / cnt[k]) : 0.f;
+            tab->lk[k][s] = cnt[k] > 0 ? (float)log2(a2 * 0.25 / cnt[k]) : -INFINITY;
+        }
         tab->norm[3][s] = (float)(a2 / ((double)sc->n_pred * Hd * Wd));
         tab->norm[4][s] = (float)(a2 / N2);
         tab->flow[s] = sc->flow[s];

@@ -195,62 +195,64 @@ __device__ __forceinline__ void tma_load_flow(unsigned dst, const CUtensorMap* m
     }
 }
 
-// One row's bilinear taps in flight: requested in phase 1, consumed in phase 3.
-struct Taps { float nw, ne, sw, se, wx, wy; bool bad; };
-
-// phase 1 of a row: sampling position exactly as the reference computes it (operation-order notes
-// at the top of loss.cu), then the four zero-padded taps of `next` are requested.  The position is
-// clamped to [-2, S] in float before the conversion (values out there have no tap inside the image:
-// the sample and its derivative are 0 whatever the weights), so one F2I.FLOOR replaces floor + F2I.
-__device__ __forceinline__ Taps request_taps(const float* __restrict__ next, int H, int W, float Hf, float Wf,
-                                             const GridNorm& gn, float xf, float yf, float2 uv, bool valid) {
-    Taps t;
-    const float gx = grid_coord(xf, uv.x, gn.hx, gn.rx), gy = grid_coord(yf, uv.y, gn.hy, gn.ry);
-    t.bad = valid && out_of_border(gx, gy);
-    const float ix = __fmul_rn(__fadd_rn(gx, 1.f), gn.hx);            // ATen CPU unnormalize
-    const float iy = __fmul_rn(__fadd_rn(gy, 1.f), gn.hy);
-    const float cx = fminf(fmaxf(ix, -2.f), Wf), cy = fminf(fmaxf(iy, -2.f), Hf);
-    const int xi = __float2int_rd(cx), yi = __float2int_rd(cy);
-    t.wx = cx - (float)xi;                                            // weight of east / south
-    t.wy = cy - (float)yi;
-    const bool x0ok = (unsigned)xi < (unsigned)W, x1ok = (unsigned)(xi + 1) < (unsigned)W;
-    const bool y0ok = (unsigned)yi < (unsigned)H, y1ok = (unsigned)(yi + 1) < (unsigned)H;
-    const int idx = yi * W + xi;
-    const float* p0 = next + idx;
-    const float* p1 = next + (idx + W);
-    t.nw = (x0ok && y0ok) ? __ldg(p0) : 0.f;
-    t.ne = (x1ok && y0ok) ? __ldg(p0 + 1) : 0.f;
-    t.sw = (x0ok && y1ok) ? __ldg(p1) : 0.f;
-    t.se = (x1ok && y1ok) ? __ldg(p1 + 1) : 0.f;
-    return t;
+// Charbonnier pair with the term's normaliser folded into the exponent: with lk = log2(k),
+//     t' = 2^((alpha-1) lg2(s) + lk) = k s^(alpha-1),   der' = d t' = k c'(d) / (2 alpha),   val' = t' s = k c(d)
+// so neither the gradient nor the value needs a multiply by k afterwards, and a pair that does not
+// exist (image border) is switched off with lk = -inf (ex2(-inf) = +0: der' = val' = 0).
+template <bool kVal, bool kGrad>
+__device__ __forceinline__ Charb2 charb2k(float2 p, float2 q, float lk) {
+    const float2 d = f2sub(p, q);
+    const float2 s = f2fma(d, d, f2(kEps2));
+    const float2 l = make_float2(lg2_approx(s.x), lg2_approx(s.y));
+    Charb2 r;
+    if (kGrad) {
+        const float2 e = f2fma(l, f2(kAlpha - 1.f), f2(lk));
+        const float2 t = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+        r.der = f2mul(d, t);
+        r.val = f2mul(t, s);
+    } else {
+        const float2 e = f2fma(l, f2(kAlpha), f2(lk));
+        r.der = f2(0.f);
+        r.val = make_float2(ex2_approx(e.x), ex2_approx(e.y));
+    }
+    return r;
 }
 
 // Everything a warp carries from row to row and stage to stage.
 struct SweepState {
     float2 a, b;                          // flow at (x, y), (x+1, y) of the current row
-    float2 gv_p, gda_p, gdb_p;            // pair gradients of the row above
-    float2 acc_h, acc_v, acc_d;           // smoothness sums (both channels)
-    float acc_p, acc_o, acc_n;            // photometric, border sum, border count
+    float2 gv_p, gda_p, gdb_p;            // normalised pair derivatives of the row above
+    float2 acc_s;                         // smoothness: sum of k c(d) over all four directions (both channels)
+    float2 acc_p;                         // photometric sum (even / odd rows of the row pairs)
+    float acc_o, acc_n;                   // border sum, border count
 };
 struct SweepConst {
     int H, W;
     float Hf, Wf, xf;
-    bool x_in, x_r;
-    float kh, kv, kd, k_ph, k_ob;         // gradient scales of this scale's terms
+    bool x_in;
+    float lkh, lkv, lkd;                  // log2 of the smoothness normalisers, -inf where this lane has no such pair
+    float lk_h0, lk_d0;                   // the same for the halo column left of the segment (unmasked)
+    float g_sm, k_ph, k_ob;               // d(loss)/d(term) x normaliser of the remaining terms
     GridNorm gn;
     const float* next;
     float* grad0;                         // this lane's column of the gradient, channel 0 / 1:
     float* grad1;                         // pixel (x, y) at [y * W]
 };
 
+__device__ __forceinline__ float2 f2pair(float lo, float hi) { return make_float2(lo, hi); }
+
 // 8 rows y0 .. y0+7 from stage buffer F (flow box rows y0-1 .. y0+8, prev box rows y0 .. y0+7).
 // kEdge = false: all 8 rows and row y0+8 lie inside the image (no per-row masks).
+//
+// The smoothness pairs are evaluated per pixel with the two flow CHANNELS packed (u, v); the
+// photometric path (sampling position, weights, bilinear sum, Charbonnier, d/dx d/dy) is evaluated
+// for the two ROWS of a group packed (row k, row k+1): the same FADD2 / FMUL2 / FFMA2 do two pixels.
 template <bool kVal, bool kGrad, bool kEdge>
 __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const SweepConst& c, SweepState& st,
                                             int y0, bool has_left, int lane) {
+    static_assert(kGroup == 2, "the photometric path packs the two rows of a group");
     const int lx = lane + kBoxLeft;
-    const float khx = c.x_r ? c.kh : 0.f, kvx = c.x_in ? c.kv : 0.f, kdx = c.x_r ? c.kd : 0.f;
-    const float mhx = c.x_r ? 1.f : 0.f, mvx = c.x_in ? 1.f : 0.f;
+    const float ninf = -INFINITY;
     // ---- L of the cell left of the segment for the 8 rows: lane j evaluates row y0 + j ----
     if (kGrad && has_left) {              // warp-uniform
         const int j = lane & 7, y = y0 + j;
@@ -258,12 +260,13 @@ __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const
         const float* fv = fu + kPlane;
         const float2 p = make_float2(fu[0], fv[0]), q = make_float2(fu[1], fv[1]);
         const float2 up = make_float2(fu[-kBoxW], fv[-kBoxW]), dn = make_float2(fu[kBoxW], fv[kBoxW]);
-        const float k_h = (!kEdge || y < c.H) ? c.kh : 0.f;
-        const float k_a = (y >= 1 && (!kEdge || y < c.H)) ? c.kd : 0.f;
-        const float k_b = (!kEdge || y + 1 < c.H) ? c.kd : 0.f;
-        float2 lh = f2mul(f2(k_h), charb2<false, true>(q, p).der);
-        lh = f2fma(f2(k_a), charb2<false, true>(q, up).der, lh);
-        lh = f2fma(f2(k_b), charb2<false, true>(q, dn).der, lh);
+        // the halo cell's pairs all end in column x0 >= 1: they exist in x; rows decide
+        const float l_h = (!kEdge || y < c.H) ? c.lk_h0 : ninf;
+        const float l_a = (y >= 1 && (!kEdge || y < c.H)) ? c.lk_d0 : ninf;
+        const float l_b = (!kEdge || y + 1 < c.H) ? c.lk_d0 : ninf;
+        float2 lh = charb2k<false, true>(q, p, l_h).der;
+        lh = f2add(lh, charb2k<false, true>(q, up, l_a).der);
+        lh = f2add(lh, charb2k<false, true>(q, dn, l_b).der);
         __syncwarp();                     // the previous stage's reads of lh_sm are done
         if (lane < kStageRows) lh_sm[lane] = lh;
         __syncwarp();
@@ -271,96 +274,128 @@ __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const
     const unsigned lh_addr = smem_u32(lh_sm);
     int goff = y0 * c.W;                  // warp-uniform element offset of row y in this lane's column
     const float yf0 = (float)y0;
+    const float2 hx2 = f2(c.gn.hx), hy2 = f2(c.gn.hy), rx2 = f2(c.gn.rx), ry2 = f2(c.gn.ry);
 #pragma unroll
-    for (int g0 = 0; g0 < kStageRows; g0 += kGroup) {
-        // the group's next-row neighbours (box row of image row y0+k is k+1)
-        float2 cc[kGroup], dd[kGroup];
-#pragma unroll
-        for (int k = 0; k < kGroup; ++k) {
-            const float* fu = F + (g0 + k + 2) * kBoxW + lx;
-            cc[k] = make_float2(fu[0], fu[kPlane]);
-            dd[k] = make_float2(fu[1], fu[kPlane + 1]);
+    for (int g0 = 0; g0 < kStageRows; g0 += 2) {
+        const float* fr0 = F + (g0 + 1) * kBoxW + lx;      // box row of image row y0 + g0, this lane's column
+        const bool v0 = c.x_in && (!kEdge || y0 + g0 < c.H), v1 = c.x_in && (!kEdge || y0 + g0 + 1 < c.H);
+        // ---- phase 1 (rows packed): sampling positions of both rows, all eight taps requested ----
+        // utils/loss.py:150-156 + ATen's CPU unnormalize, operation for operation (notes in loss.cu);
+        // the position is clamped to [-2, S] in float before the conversion (out there no tap lies
+        // inside the image: sample and derivative are 0 whatever the weights), so one F2I.FLOOR
+        // replaces floor + F2I
+        const float2 U = f2pair(fr0[0], fr0[kBoxW]), V = f2pair(fr0[kPlane], fr0[kPlane + kBoxW]);
+        const float2 ax = f2add(f2(c.xf), U), ay = f2add(f2pair(yf0 + (float)g0, yf0 + (float)(g0 + 1)), V);
+        const float2 qx0 = f2mul(ax, rx2), qy0 = f2mul(ay, ry2);
+        const float2 qx = f2fma(f2fma(qx0, f2pair(-c.gn.hx, -c.gn.hx), ax), rx2, qx0);   // exact_div.h: a / h
+        const float2 qy = f2fma(f2fma(qy0, f2pair(-c.gn.hy, -c.gn.hy), ay), ry2, qy0);
+        const float2 gx = f2add(qx, f2(-1.f)), gy = f2add(qy, f2(-1.f));
+        const bool bad0 = v0 && fmaxf(fabsf(gx.x), fabsf(gy.x)) > 1.f;                  // loss.py:92-94
+        const bool bad1 = v1 && fmaxf(fabsf(gx.y), fabsf(gy.y)) > 1.f;
+        const float2 ix = f2mul(f2add(gx, f2(1.f)), hx2), iy = f2mul(f2add(gy, f2(1.f)), hy2);
+        const float cx0 = fminf(fmaxf(ix.x, -2.f), c.Wf), cx1 = fminf(fmaxf(ix.y, -2.f), c.Wf);
+        const float cy0 = fminf(fmaxf(iy.x, -2.f), c.Hf), cy1 = fminf(fmaxf(iy.y, -2.f), c.Hf);
+        const int xi0 = __float2int_rd(cx0), xi1 = __float2int_rd(cx1);
+        const int yi0 = __float2int_rd(cy0), yi1 = __float2int_rd(cy1);
+        const float2 wx = f2sub(f2pair(cx0, cx1), f2pair((float)xi0, (float)xi1));       // weight of east
+        const float2 wy = f2sub(f2pair(cy0, cy1), f2pair((float)yi0, (float)yi1));       // weight of south
+        float2 nw, ne, sw, se;
+        {
+            const bool xa = (unsigned)xi0 < (unsigned)c.W, xb = (unsigned)(xi0 + 1) < (unsigned)c.W;
+            const bool ya = (unsigned)yi0 < (unsigned)c.H, yb = (unsigned)(yi0 + 1) < (unsigned)c.H;
+            const int idx = yi0 * c.W + xi0;
+            const float* p0 = c.next + idx;
+            const float* p1 = c.next + (idx + c.W);
+            nw.x = (xa && ya) ? __ldg(p0) : 0.f;
+            ne.x = (xb && ya) ? __ldg(p0 + 1) : 0.f;
+            sw.x = (xa && yb) ? __ldg(p1) : 0.f;
+            se.x = (xb && yb) ? __ldg(p1 + 1) : 0.f;
         }
-        // ---- phase 1: sampling positions of the group's rows, all taps requested ----
-        Taps tp[kGroup];
-        float2 uv[kGroup];
-        float pv[kGroup];
-#pragma unroll
-        for (int k = 0; k < kGroup; ++k) {
-            const int y = y0 + g0 + k;
-            uv[k] = k == 0 ? st.a : cc[k - 1];
-            const bool valid = c.x_in && (!kEdge || y < c.H);
-            tp[k] = request_taps(c.next, c.H, c.W, c.Hf, c.Wf, c.gn, c.xf, yf0 + (float)(g0 + k), uv[k], valid);
-            pv[k] = F[kPrevOff + (g0 + k) * 32 + lane];
+        {
+            const bool xa = (unsigned)xi1 < (unsigned)c.W, xb = (unsigned)(xi1 + 1) < (unsigned)c.W;
+            const bool ya = (unsigned)yi1 < (unsigned)c.H, yb = (unsigned)(yi1 + 1) < (unsigned)c.H;
+            const int idx = yi1 * c.W + xi1;
+            const float* p0 = c.next + idx;
+            const float* p1 = c.next + (idx + c.W);
+            nw.y = (xa && ya) ? __ldg(p0) : 0.f;
+            ne.y = (xb && ya) ? __ldg(p0 + 1) : 0.f;
+            sw.y = (xa && yb) ? __ldg(p1) : 0.f;
+            se.y = (xb && yb) ? __ldg(p1 + 1) : 0.f;
         }
-        // ---- phase 2: neighbour pairs of the group's rows (no global loads) ----
-        float2 gs[kGroup];
+        // ---- phase 2 (channels packed): neighbour pairs of both rows (no global loads) ----
+        float2 gs[2];
 #pragma unroll
-        for (int k = 0; k < kGroup; ++k) {
+        for (int k = 0; k < 2; ++k) {
             const int r = g0 + k, y = y0 + r;
             const bool row_in = !kEdge || y < c.H, row_d = !kEdge || y + 1 < c.H;    // warp-uniform
-            const float2 cn = cc[k], dn = dd[k];
-            const Charb2 ph = charb2<kVal, kGrad>(st.b, st.a);                 // loss.py:76-90
-            const Charb2 pvv = charb2<kVal, kGrad>(cn, st.a);
-            const Charb2 pa = charb2<kVal, kGrad>(dn, st.a);
-            const Charb2 pb = charb2<kVal, kGrad>(st.b, cn);
-            if (kVal) {
-                const float mh_r = row_in ? mhx : 0.f, mv_r = row_d ? mvx : 0.f, md_r = row_d ? mhx : 0.f;
-                st.acc_h = f2fma(f2(mh_r), ph.val, st.acc_h);
-                st.acc_v = f2fma(f2(mv_r), pvv.val, st.acc_v);
-                st.acc_d = f2fma(f2(md_r), f2add(pa.val, pb.val), st.acc_d);
-            }
+            const float* fn = fr0 + (k + 1) * kBoxW;                                  // the row below
+            const float2 cn = make_float2(fn[0], fn[kPlane]), dn = make_float2(fn[1], fn[kPlane + 1]);
+            const float l_h = row_in ? c.lkh : ninf, l_v = row_d ? c.lkv : ninf, l_d = row_d ? c.lkd : ninf;
+            const Charb2 ph = charb2k<kVal, kGrad>(st.b, st.a, l_h);                 // loss.py:76-90
+            const Charb2 pvv = charb2k<kVal, kGrad>(cn, st.a, l_v);
+            const Charb2 pa = charb2k<kVal, kGrad>(dn, st.a, l_d);
+            const Charb2 pb = charb2k<kVal, kGrad>(st.b, cn, l_d);
+            if (kVal) st.acc_s = f2add(st.acc_s, f2add(f2add(ph.val, pvv.val), f2add(pa.val, pb.val)));
             gs[k] = f2(0.f);
             if (kGrad) {
-                const float kh_r = row_in ? khx : 0.f, kv_r = row_d ? kvx : 0.f, kd_r = row_d ? kdx : 0.f;
-                const float2 gh = f2mul(f2(kh_r), ph.der), gv = f2mul(f2(kv_r), pvv.der);
-                const float2 gda = f2mul(f2(kd_r), pa.der), gdb = f2mul(f2(kd_r), pb.der);
-                const float2 L = f2add(f2add(gh, st.gda_p), gdb);
+                const float2 L = f2add(f2add(ph.der, st.gda_p), pb.der);
                 float2 Ll = make_float2(__shfl_up_sync(0xffffffffu, L.x, 1), __shfl_up_sync(0xffffffffu, L.y, 1));
                 // lane 0: the left halo's L of this row (0 in the first column block)
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.eq.u32 p, %2, 0;\n\t"
                              "@p ld.shared.v2.f32 {%0, %1}, [%3];\n\t}"
                              : "+f"(Ll.x), "+f"(Ll.y) : "r"(lane), "r"(lh_addr + 8u * r) : "memory");
-                gs[k] = f2sub(f2add(f2sub(Ll, gh), f2sub(st.gv_p, gv)), f2add(gda, st.gdb_p));
-                st.gv_p = gv; st.gda_p = gda; st.gdb_p = gdb;
+                gs[k] = f2sub(f2add(f2sub(Ll, ph.der), f2sub(st.gv_p, pvv.der)), f2add(pa.der, st.gdb_p));
+                st.gv_p = pvv.der; st.gda_p = pa.der; st.gdb_p = pb.der;
             }
             st.a = cn; st.b = dn;
         }
-        // ---- phase 3: consume the taps: photometric term, border term, gradient ----
-#pragma unroll
-        for (int k = 0; k < kGroup; ++k) {
-            const int y = y0 + g0 + k;
-            const bool valid = c.x_in && (!kEdge || y < c.H);
-            const Taps& t = tp[k];
-            const float ex = 1.f - t.wx, ey = 1.f - t.wy;
-            // operation order of ATen's CPU grid_sampler (see the notes in loss.cu)
-            const float val = __fmaf_rn(t.se, __fmul_rn(t.wy, t.wx),
-                                        __fmaf_rn(t.sw, __fmul_rn(t.wy, ex),
-                                                  __fmaf_rn(t.ne, __fmul_rn(ey, t.wx),
-                                                            __fmul_rn(t.nw, __fmul_rn(ey, ex)))));
-            const Charb1 pp = charb1<kVal, kGrad>(val - pv[k]);             // loss.py:72-74
-            if (kVal) st.acc_p = fmaf(valid ? 1.f : 0.f, pp.val, st.acc_p);
-            float2 gout = gs[k];
-            if (kGrad) {
-                const float ddx = (t.ne - t.nw) * ey + (t.se - t.sw) * t.wy;
-                const float ddy = (t.sw - t.nw) * ex + (t.se - t.ne) * t.wx;
-                gout = f2fma(f2(c.k_ph * pp.der), make_float2(ddx, ddy), gout);
-            }
-            if (__any_sync(0xffffffffu, t.bad)) {                          // warp-uniform, rare
-                const Charb2 bo = charb2<kVal, kGrad>(uv[k], f2(0.f));
-                const float m_b = t.bad ? 1.f : 0.f;
-                if (kVal) {
-                    st.acc_o = fmaf(m_b, bo.val.x + bo.val.y, st.acc_o);
-                    st.acc_n += m_b;
-                }
-                if (kGrad) gout = f2fma(f2(t.bad ? c.k_ob : 0.f), bo.der, gout);
-            }
-            if (kGrad && valid) {
-                c.grad0[goff] = gout.x;
-                c.grad1[goff] = gout.y;
-            }
-            goff += c.W;
+        // ---- phase 3 (rows packed): consume the taps: photometric term and its gradient ----
+        const float2 pv = f2pair(F[kPrevOff + g0 * 32 + lane], F[kPrevOff + (g0 + 1) * 32 + lane]);
+        const float2 ex = f2sub(f2(1.f), wx), ey = f2sub(f2(1.f), wy);
+        // operation order of ATen's CPU grid_sampler: nw*(ey*ex) then fma ne*(ey*wx), sw*(wy*ex), se*(wy*wx)
+        const float2 val = f2fma(se, f2mul(wy, wx), f2fma(sw, f2mul(wy, ex), f2fma(ne, f2mul(ey, wx), f2mul(nw, f2mul(ey, ex)))));
+        const float2 d = f2sub(val, pv);                                             // loss.py:72-74
+        const float2 s2 = f2fma(d, d, f2(kEps2));
+        const float2 l2 = make_float2(lg2_approx(s2.x), lg2_approx(s2.y));
+        float2 pder = f2(0.f);
+        if (kGrad) {
+            const float2 t = make_float2(ex2_approx((kAlpha - 1.f) * l2.x), ex2_approx((kAlpha - 1.f) * l2.y));
+            pder = f2mul(d, t);
+            if (kVal) st.acc_p = f2fma(f2pair(v0 ? 1.f : 0.f, v1 ? 1.f : 0.f), f2mul(t, s2), st.acc_p);
+        } else {
+            const float2 cval = make_float2(ex2_approx(kAlpha * l2.x), ex2_approx(kAlpha * l2.y));
+            st.acc_p = f2fma(f2pair(v0 ? 1.f : 0.f, v1 ? 1.f : 0.f), cval, st.acc_p);
         }
+        float ox0 = 0.f, oy0 = 0.f, ox1 = 0.f, oy1 = 0.f;
+        if (kGrad) {
+            const float2 ddx = f2fma(f2sub(se, sw), wy, f2mul(f2sub(ne, nw), ey));
+            const float2 ddy = f2fma(f2sub(se, ne), wx, f2mul(f2sub(sw, nw), ex));
+            const float2 kder = f2mul(f2(c.k_ph), pder);
+            const float2 px = f2mul(kder, ddx), py = f2mul(kder, ddy);
+            ox0 = fmaf(c.g_sm, gs[0].x, px.x); oy0 = fmaf(c.g_sm, gs[0].y, py.x);
+            ox1 = fmaf(c.g_sm, gs[1].x, px.y); oy1 = fmaf(c.g_sm, gs[1].y, py.y);
+        }
+        if (__any_sync(0xffffffffu, bad0 || bad1)) {                                 // warp-uniform, rare
+            // border term (loss.py:96-119): Charbonnier of the flow itself on out-of-border pixels
+            const Charb2 b0 = charb2<kVal, kGrad>(make_float2(U.x, V.x), f2(0.f));
+            const Charb2 b1 = charb2<kVal, kGrad>(make_float2(U.y, V.y), f2(0.f));
+            const float m0 = bad0 ? 1.f : 0.f, m1 = bad1 ? 1.f : 0.f;
+            if (kVal) {
+                st.acc_o = fmaf(m0, b0.val.x + b0.val.y, st.acc_o);
+                st.acc_o = fmaf(m1, b1.val.x + b1.val.y, st.acc_o);
+                st.acc_n += m0 + m1;
+            }
+            if (kGrad) {
+                const float k0 = bad0 ? c.k_ob : 0.f, k1 = bad1 ? c.k_ob : 0.f;
+                ox0 = fmaf(k0, b0.der.x, ox0); oy0 = fmaf(k0, b0.der.y, oy0);
+                ox1 = fmaf(k1, b1.der.x, ox1); oy1 = fmaf(k1, b1.der.y, oy1);
+            }
+        }
+        if (kGrad) {
+            if (v0) { c.grad0[goff] = ox0; c.grad1[goff] = oy0; }
+            if (v1) { c.grad0[goff + c.W] = ox1; c.grad1[goff + c.W] = oy1; }
+        }
+        goff += 2 * c.W;
     }
 }
 
@@ -435,17 +470,20 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
     c.Hf = (float)H; c.Wf = (float)W;
     const int x = tc.x0 + lane;
     c.xf = (float)x;
-    c.x_in = x < W; c.x_r = x + 1 < W;
-    c.kh = c.kv = c.kd = c.k_ph = c.k_ob = 0.f;
+    c.x_in = x < W;
+    const bool x_r = x + 1 < W;
+    // log2 of 2 alpha / (4 x element count of the mean) per direction, precomputed on the host
+    // (-inf for a direction without pairs); lanes whose pixel has no such pair: -inf
+    c.lk_h0 = tab.lk[0][tc.s]; c.lk_d0 = tab.lk[2][tc.s];
+    c.lkh = x_r ? c.lk_h0 : -INFINITY;
+    c.lkv = c.x_in ? tab.lk[1][tc.s] : -INFINITY;
+    c.lkd = x_r ? c.lk_d0 : -INFINITY;
+    c.g_sm = c.k_ph = c.k_ob = 0.f;
     if (kGrad) {
         // d(loss)/d(term) of this scale: device vector (generic backward) or host coefficients (fused)
-        const float g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
+        c.g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
         const float g_ph = grad_terms ? grad_terms[S + tc.s] : tab.coef[DVSOF_MAX_SCALES + tc.s];
         const float g_ob = grad_terms ? grad_terms[2 * S + tc.s] : tab.coef[2 * DVSOF_MAX_SCALES + tc.s];
-        // 2 alpha / (element count of the mean), per direction, precomputed on the host
-        c.kh = g_sm * tab.norm[0][tc.s];
-        c.kv = g_sm * tab.norm[1][tc.s];
-        c.kd = g_sm * tab.norm[2][tc.s];
         c.k_ph = g_ph * tab.norm[3][tc.s];
         int nb;
         if (bad_per_tile) {                       // per-tile counts of this (scale, prediction): sum them
@@ -468,8 +506,8 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
 
     SweepState st;
     st.a = st.b = f2(0.f);
-    st.acc_h = st.acc_v = st.acc_d = f2(0.f);
-    st.acc_p = st.acc_o = st.acc_n = 0.f;
+    st.acc_s = st.acc_p = f2(0.f);
+    st.acc_o = st.acc_n = 0.f;
     st.gv_p = st.gda_p = st.gdb_p = f2(0.f);
     const bool has_left = tc.x0 > 0;
 #pragma unroll 1
@@ -501,20 +539,18 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
             if (kGrad && tc.y0 > 0) {             // the pairs reaching into row y0 from above
                 const float2 ua = make_float2(fu[-kBoxW], fu[kPlane - kBoxW]);
                 const float2 ub = make_float2(fu[1 - kBoxW], fu[kPlane + 1 - kBoxW]);
-                const float kvx = c.x_in ? c.kv : 0.f, kdx = c.x_r ? c.kd : 0.f;
-                st.gv_p = f2mul(f2(kvx), charb2<false, true>(st.a, ua).der);
-                st.gda_p = f2mul(f2(kdx), charb2<false, true>(st.b, ua).der);
-                st.gdb_p = f2mul(f2(kdx), charb2<false, true>(ub, st.a).der);
+                st.gv_p = charb2k<false, true>(st.a, ua, c.lkv).der;
+                st.gda_p = charb2k<false, true>(st.b, ua, c.lkd).der;
+                st.gdb_p = charb2k<false, true>(ub, st.a, c.lkd).der;
             }
         }
         if (y0 + kStageRows < H) sweep_stage<kVal, kGrad, false>(F, lh_sm, c, st, y0, has_left, lane);
         else sweep_stage<kVal, kGrad, true>(F, lh_sm, c, st, y0, has_left, lane);
     }
     if (!kVal) return;
-    // record: [photo, smooth_h, smooth_v, smooth_diag (both), -, outborder_sum, n_bad, -]; summed by
-    // loss_reduce_kernel (loss.cu) after this launch -- no ticket, no fence here
-    float acc[kRec] = {st.acc_p, st.acc_h.x + st.acc_h.y, st.acc_v.x + st.acc_v.y, st.acc_d.x + st.acc_d.y,
-                       0.f, st.acc_o, st.acc_n, 0.f};
+    // record: [photo, smoothness (normalised, all directions), -, -, -, outborder_sum, n_bad, -]; summed
+    // by loss_reduce_kernel (loss.cu) after this launch -- no ticket, no fence here
+    float acc[kRec] = {st.acc_p.x + st.acc_p.y, st.acc_s.x + st.acc_s.y, 0.f, 0.f, 0.f, st.acc_o, st.acc_n, 0.f};
     warp_sum8(acc, lane);
     if ((lane & 3) == 0)
         __stcg(ws.partials + (size_t)blockIdx.x * kRec + (((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)), acc[0]);
