@@ -119,16 +119,16 @@ __global__ void match_timestamps_kernel(const float* __restrict__ flow_ts,
 }
 
 // ------------------------------ deterministic reduction of the segment records ---------
-// record of one sweep segment (warp): [photo, smooth_h, smooth_v, smooth_diag, -, outborder_sum, n_bad, -].
+// record of one sweep segment (warp): [photo, smoothness, outborder_sum, n_bad].
 // Two levels, both in loss_reduce_kernel (launched behind the sweep):
-//   pair level  -- one CTA per (scale, prediction) pair sums that pair's records in a fixed order
+//   pair level  -- one warp per (scale, prediction) pair sums that pair's records in a fixed order
 //                  in fp64 and writes the pair record + n_i;
 //   final level -- the CTA that arrives LAST at the ticket (release/acquire at gpu scope, issued
 //                  by one thread; the data is read back with L2 loads) sums the pair records per
 //                  scale, again in a fixed order, and writes the 3*S terms (+ the weighted loss).
 // Results do not depend on arrival order; the ticket resets itself for the next call.
-constexpr int kRec = 8;            // floats per tile record
-constexpr int kPairRec = 8;        // doubles per pair record: [photo, h, v, diag, outborder/(2 n_i P), -, -, -]
+constexpr int kRec = 4;            // floats per segment record
+constexpr int kPairRec = 4;        // doubles per pair record: [photo, smoothness, outborder/(2 n_i P), -]
 
 __device__ __forceinline__ unsigned ticket_arrive(unsigned* t) {
     unsigned before;
@@ -141,72 +141,58 @@ __device__ __forceinline__ double warp_sum_f64(double v) {
     return v;
 }
 
-// all threads of the CTA (whole warps); `red` holds (blockDim/32) x 7 doubles
+// one warp: the records of pair (s, n) in a fixed order (lane l takes records l, l + 32, ...; eight
+// of them in flight: every record is an L2 round trip), fp64, then a butterfly over the lanes
 __device__ void reduce_pair(const ScaleTable& tab, int s, int n, const float* partials,
-                            double* pair_rec, int32_t* n_bad, double (*red)[7]) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+                            double* pair_rec, int32_t* n_bad) {
+    const int lane = threadIdx.x & 31;
     const int P = tab.n_pred, per = tab.seg_per[s];
     const float* rec = partials + ((size_t)tab.seg_begin[s] + (size_t)n * per) * kRec;
-    double a[7] = {0, 0, 0, 0, 0, 0, 0};
-    // four records per thread in flight (the loop is latency bound: every record is an L2 round trip)
-    constexpr int kInFlight = 4;
-    for (int t0 = threadIdx.x; t0 < per; t0 += kInFlight * blockDim.x) {
-        float4 r0[kInFlight], r1[kInFlight];
+    double a0 = 0, a1 = 0, a5 = 0, a6 = 0;         // photo, smoothness, border sum, border count
+    constexpr int kInFlight = 8;
+    for (int t0 = lane; t0 < per; t0 += kInFlight * 32) {
+        float4 r[kInFlight];
 #pragma unroll
         for (int j = 0; j < kInFlight; ++j) {
-            const int t = t0 + j * blockDim.x;
-            if (t < per) {
-                r0[j] = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec));
-                r1[j] = __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec) + 1);
-            } else {
-                r0[j] = r1[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+            const int t = t0 + j * 32;
+            r[j] = t < per ? __ldcg(reinterpret_cast<const float4*>(rec + (size_t)t * kRec)) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
-        for (int j = 0; j < kInFlight; ++j) {               // fixed order: t0, t0 + blockDim, ...
-            a[0] += (double)r0[j].x; a[1] += (double)r0[j].y; a[2] += (double)r0[j].z; a[3] += (double)r0[j].w;
-            a[4] += (double)r1[j].x; a[5] += (double)r1[j].y; a[6] += (double)r1[j].z;
+        for (int j = 0; j < kInFlight; ++j) {
+            a0 += (double)r[j].x; a1 += (double)r[j].y; a5 += (double)r[j].z; a6 += (double)r[j].w;
         }
     }
-#pragma unroll
-    for (int k = 0; k < 7; ++k) a[k] = warp_sum_f64(a[k]);
-    if (lane == 0)
-#pragma unroll
-        for (int k = 0; k < 7; ++k) red[warp][k] = a[k];
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double t[7];
-        for (int k = 0; k < 7; ++k) {
-            t[k] = 0;
-            for (int w = 0; w < n_warps; ++w) t[k] += red[w][k];
-        }
+    a0 = warp_sum_f64(a0); a1 = warp_sum_f64(a1); a5 = warp_sum_f64(a5); a6 = warp_sum_f64(a6);
+    if (lane == 0) {
         double* out = pair_rec + (size_t)(s * P + n) * kPairRec;
-        const double nb = t[6];
-        __stcg(out + 0, t[0]); __stcg(out + 1, t[1]); __stcg(out + 2, t[2]); __stcg(out + 3, t[3] + t[4]);
-        __stcg(out + 4, nb > 0 ? t[5] / (2.0 * nb * (double)P) : 0.0);                 // loss.py:99-113
-        if (n_bad) n_bad[s * P + n] = (int32_t)nb;
+        __stcg(out + 0, a0); __stcg(out + 1, a1);
+        __stcg(out + 2, a6 > 0 ? a5 / (2.0 * a6 * (double)P) : 0.0);                 // loss.py:99-113
+        if (n_bad) n_bad[s * P + n] = (int32_t)a6;
     }
 }
 
+// one CTA (whole warps): per scale the pair records in a fixed order -> the 3*S terms (+ the loss)
 __device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, float* terms,
-                             float* loss_out) {
+                             float* loss_out, float* term_sm /* shared, 3 * DVSOF_MAX_SCALES */) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
     const int P = tab.n_pred, S = tab.n_scales;
     for (int s = warp; s < S; s += n_warps) {
-        double a[5] = {0, 0, 0, 0, 0};
+        double a[3] = {0, 0, 0};
         for (int n = lane; n < P; n += 32) {
             const double* r = pair_rec + (size_t)(s * P + n) * kPairRec;
 #pragma unroll
-            for (int k = 0; k < 5; ++k) a[k] += __ldcg(r + k);
+            for (int k = 0; k < 3; ++k) a[k] += __ldcg(r + k);
         }
 #pragma unroll
-        for (int k = 0; k < 5; ++k) a[k] = warp_sum_f64(a[k]);
+        for (int k = 0; k < 3; ++k) a[k] = warp_sum_f64(a[k]);
         if (lane == 0) {
             const int H = tab.H[s], W = tab.W[s];
             // the sweep accumulates k c(d) with k = 2 alpha / (4 x count) per direction (loss.py:87-90)
-            terms[s] = (float)(a[1] / (2.0 * (double)kAlpha));
-            terms[S + s] = (float)(a[0] / ((double)P * H * W));                  // loss.py:33
-            terms[2 * S + s] = (float)a[4];
+            const float sm = (float)(a[1] / (2.0 * (double)kAlpha));
+            const float ph = (float)(a[0] / ((double)P * H * W));                  // loss.py:33
+            const float ob = (float)a[2];
+            terms[s] = sm; terms[S + s] = ph; terms[2 * S + s] = ob;
+            term_sm[s] = sm; term_sm[DVSOF_MAX_SCALES + s] = ph; term_sm[2 * DVSOF_MAX_SCALES + s] = ob;
         }
     }
     if (loss_out) {                       // fused pass: loss = sum_k sum_s coef[k][s] * term[k][s]
@@ -215,7 +201,7 @@ __device__ void reduce_final(const ScaleTable& tab, const double* pair_rec, floa
             float l = 0.f;
             for (int k = 0; k < 3; ++k)
                 for (int s = 0; s < S; ++s)
-                    l = fmaf(tab.coef[k * DVSOF_MAX_SCALES + s], __ldcg(terms + k * S + s), l);
+                    l = fmaf(tab.coef[k * DVSOF_MAX_SCALES + s], term_sm[k * DVSOF_MAX_SCALES + s], l);
             *loss_out = l;
         }
     }
@@ -235,23 +221,26 @@ struct LossWorkspace {
 // sweep (gpurun_out/r02h: every warp holds its SM slot while its gradient stores drain); a kernel
 // boundary orders the records for free.  One CTA per (scale, prediction) pair sums that pair's
 // segment records; the last of these S*P CTAs (one ticket each) writes the terms and the loss.
-constexpr int kReduceThreads = 256;
+constexpr int kReduceThreads = 128;                        // 4 warps = 4 pairs per CTA
 __global__ void __launch_bounds__(kReduceThreads)
 loss_reduce_kernel(const __grid_constant__ ScaleTable tab, const LossWorkspace ws, float* terms,
                    int32_t* __restrict__ n_bad, float* __restrict__ loss_out) {
-    __shared__ double red[kReduceThreads / 32][7];
+    __shared__ float term_sm[3 * DVSOF_MAX_SCALES];
     __shared__ bool is_last;
     pdl_launch_dependents();
     pdl_wait();                                            // the sweep's records are complete and visible
-    const int P = tab.n_pred, pair = blockIdx.x;
-    const int s = pair / P, n = pair - s * P;
-    reduce_pair(tab, s, n, ws.partials, ws.pair_rec, n_bad, red);
+    const int P = tab.n_pred, n_pairs = tab.n_scales * P;
+    const int pair = blockIdx.x * (kReduceThreads / 32) + (threadIdx.x >> 5);
+    if (pair < n_pairs) {                                  // warp-uniform
+        const int s = pair / P;
+        reduce_pair(tab, s, pair - s * P, ws.partials, ws.pair_rec, n_bad);
+    }
     __syncthreads();
-    if (threadIdx.x == 0) is_last = ticket_arrive(ws.tickets) == (unsigned)(tab.n_scales * P) - 1u;
+    if (threadIdx.x == 0) is_last = ticket_arrive(ws.tickets) == gridDim.x - 1u;
     __syncthreads();
     if (!is_last) return;
     __threadfence();                                       // acquire side (the finishing CTA only)
-    reduce_final(tab, ws.pair_rec, terms, loss_out);
+    reduce_final(tab, ws.pair_rec, terms, loss_out, term_sm);
     if (threadIdx.x == 0) ws.tickets[0] = 0u;              // self-resetting
 }
 
@@ -752,12 +741,15 @@ static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTa
         for (int s = 0; s < sc->n_scales; ++s)
             if (sc->W[s] < atoi(e) || sc->H[s] < atoi(e)) tab.use_tma[s] = 0;
     build_maps(sc, &tab, &maps);
-    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
+    const int n_seg = tab.seg_begin[DVSOF_MAX_SCALES], wave = kNumSMs * kSweepWarpsPerSM;
+    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, n_seg < wave ? n_seg : wave, 32, 0,
                                stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws))
         return rc;
     if (!kVal) return DVSOF_OK;
-    return launch_kernel("loss_reduce_kernel", loss_reduce_kernel, tab.n_scales * tab.n_pred, kReduceThreads, 0,
-                         stream, true, tab, ws, terms, n_bad_out, loss);
+    const int pairs_per_cta = kReduceThreads / 32;
+    return launch_kernel("loss_reduce_kernel", loss_reduce_kernel,
+                         (tab.n_scales * tab.n_pred + pairs_per_cta - 1) / pairs_per_cta, kReduceThreads, 0, stream,
+                         true, tab, ws, terms, n_bad_out, loss);
 }
 
 extern "C" int dvsof_warp_loss_forward(const dvsof_loss_scales_t* sc, const int32_t* match_idx,
