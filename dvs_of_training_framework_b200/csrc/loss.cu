@@ -742,7 +742,7 @@ static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTa
             if (sc->W[s] < atoi(e) || sc->H[s] < atoi(e)) tab.use_tma[s] = 0;
     build_maps(sc, &tab, &maps);
     const int n_seg = tab.seg_begin[DVSOF_MAX_SCALES], wave = kNumSMs * kSweepWarpsPerSM;
-    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, n_seg < wave ? n_seg : wave, 32, 0,
+    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, kPersistent && n_seg > wave ? wave : n_seg, 32, 0,
                                stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws))
         return rc;
     if (!kVal) return DVSOF_OK;

@@ -41,6 +41,10 @@ namespace dvsof {
 #ifndef DVSOF_LOSS_MIN_CTAS
 #define DVSOF_LOSS_MIN_CTAS 20            // 1-warp CTAs per SM the register budget is held to
 #endif
+#ifndef DVSOF_LOSS_PERSISTENT
+#define DVSOF_LOSS_PERSISTENT 0           // 1: one wave of warps, each walking segments w, w + grid, ...
+#endif
+constexpr bool kPersistent = DVSOF_LOSS_PERSISTENT != 0;
 constexpr int kGroup = DVSOF_LOSS_GROUP;
 constexpr int kStageRows = 8;                               // rows per ring stage
 constexpr int kRingStages = 2;
@@ -448,11 +452,12 @@ __device__ __forceinline__ void request_stage(const LossMaps& maps, int flags, i
     if (flags & 2) tma_load_3d(dst + 4u * kPrevOff, &maps.prev[s], bar, x0, y0, i_prev);
 }
 
-// Persistent: the grid is one wave of 1-warp CTAs (148 SMs x DVSOF_LOSS_MIN_CTAS); warp w takes
-// segments w, w + grid, w + 2 grid, ...  The ring runs ACROSS segments: while the last stage of a
-// segment is processed, the first stage of the warp's next segment (already decoded, its
-// match_idx entries already loaded) is in flight, so a segment never starts with a dead TMA
-// round trip.
+// One warp (= CTA) per segment.  With DVSOF_LOSS_PERSISTENT the grid is instead one wave of 1-warp
+// CTAs (148 SMs x DVSOF_LOSS_MIN_CTAS), warp w takes segments w, w + grid, ... and the ring runs
+// ACROSS segments (the first stage of the warp's next segment is in flight during the last stage of
+// the current one).  Measured slower on B200 (cfg4 86-97 us vs 74-76 us, gpurun_out/r02l): the
+// hardware's CTA scheduler balances 8-16-row segments better than a static stride, and the
+// compiler's code for the stage body grows by a third inside the outer loop.  Kept for the record.
 template <bool kVal, bool kGrad>
 __global__ void __launch_bounds__(32, DVSOF_LOSS_MIN_CTAS)
 warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_constant__ LossMaps maps,
@@ -527,7 +532,7 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
         asm volatile("" : "+l"(c.next), "+l"(c.grad0), "+l"(c.grad1));  // finished bases: access = base + 32-bit offset
         // ---- the warp's next segment: decoded now, its match_idx entries in flight from here on ----
         const int seg2 = seg + (int)gridDim.x;
-        const bool more = seg2 < n_seg;
+        const bool more = kPersistent && seg2 < n_seg;
         TileCoord tc2 = tc;
         int i_prev2 = 0, i_next2 = 0;
         if (more) {
