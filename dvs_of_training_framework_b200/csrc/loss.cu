@@ -248,8 +248,11 @@ loss_reduce_kernel(const __grid_constant__ ScaleTable tab, const LossWorkspace w
 // factor is exactly 1 (loss.backward() of the unscaled training loss).
 __global__ void __launch_bounds__(256)
 scale_gradients_kernel(const __grid_constant__ ScaleTable tab, const float* __restrict__ factor) {
+    // launched with programmatic serialization: `factor` is an input of the call, so the common
+    // case (d/d(loss) == 1) returns while the kernels before it are still running
     const float f = *factor;
     if (f == 1.f) return;
+    pdl_wait();                                   // the gradients come from the sweep
     for (int s = 0; s < tab.n_scales; ++s) {
         float* g = tab.grad_flow[s];
         const size_t n = (size_t)tab.n_pred * 2 * tab.H[s] * tab.W[s];
@@ -574,16 +577,18 @@ pyramid_chain_kernel(const __grid_constant__ PyramidArgs a, const __grid_constan
 using namespace dvsof;
 
 // Rows per sweep segment (one warp walks 32 columns x R rows): the taller the segment, the better
-// its fixed costs (decode, pointer set-up, halo pairs, record + ticket) are amortised; the shorter,
-// the more warps there are to fill 148 SMs x kSweepWarpsPerSM resident warps.  R = the largest of
-// 32 / 16 / 8 that still leaves two full waves of warps.  DVSOF_LOSS_SEG_ROWS overrides (tuning).
+// its fixed costs (decode, pointer set-up, halo pairs, first TMA round trip, record) are amortised;
+// the shorter, the more warps there are to fill 148 SMs x kSweepWarpsPerSM resident warps and the
+// finer the tail.  R = the largest of 32 / 16 / 8 that leaves four waves of warps -- measured
+// (gpurun_out/r02o): cfg2 22.3 us at R = 8 / 24.7 at 16; cfg3 41.2 / 42.9; cfg4 77.2 / 73.9 / 91.6 (R = 32).
+// DVSOF_LOSS_SEG_ROWS overrides (tuning).
 constexpr int kSweepWarpsPerSM = DVSOF_LOSS_MIN_CTAS;
 static void plan_segments(const dvsof_loss_scales_t* sc, ScaleTable* tab) {
     int64_t warp_rows = 0;
     for (int s = 0; s < sc->n_scales; ++s) warp_rows += (int64_t)sc->n_pred * tab->tiles_x[s] * sc->H[s];
     int R = 8;
     for (int r = 32; r > 8; r >>= 1)
-        if (warp_rows / r >= 2LL * kNumSMs * kSweepWarpsPerSM) { R = r; break; }
+        if (warp_rows / r >= 4LL * kNumSMs * kSweepWarpsPerSM) { R = r; break; }
     if (const char* e = getenv("DVSOF_LOSS_SEG_ROWS")) {
         const int v = atoi(e);
         if (v >= 8 && v <= 4096 && v % 8 == 0) R = v;
@@ -636,8 +641,7 @@ static void build_maps(const dvsof_loss_scales_t* sc, ScaleTable* tab, LossMaps*
     for (int s = 0; s < sc->n_scales; ++s) {
         // no driver entry point / unencodable: plain loads for that part
         if ((tab->use_tma[s] & 1) &&
-            !encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH,
-                         DVSOF_LOSS_FLOW_SPLIT ? 1 : 2))
+            !encode_map3(&maps->flow[s], sc->flow[s], sc->W[s], sc->H[s], 2LL * sc->n_pred, kBoxW, kBoxH, 2))
             tab->use_tma[s] &= ~1;
         if ((tab->use_tma[s] & 2) &&
             !encode_map3(&maps->prev[s], sc->images[s], sc->W[s], sc->H[s], sc->n_images, 32, kStageRows, 1))
@@ -741,8 +745,7 @@ static int launch_sweep(const char* what, const dvsof_loss_scales_t* sc, ScaleTa
         for (int s = 0; s < sc->n_scales; ++s)
             if (sc->W[s] < atoi(e) || sc->H[s] < atoi(e)) tab.use_tma[s] = 0;
     build_maps(sc, &tab, &maps);
-    const int n_seg = tab.seg_begin[DVSOF_MAX_SCALES], wave = kNumSMs * kSweepWarpsPerSM;
-    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, kPersistent && n_seg > wave ? wave : n_seg, 32, 0,
+    if (int rc = launch_kernel(what, warp_loss_ring_kernel<kVal, kGrad>, tab.seg_begin[DVSOF_MAX_SCALES], 32, 0,
                                stream, pdl, tab, maps, match_idx, grad_terms, n_bad_in, bad_per_tile, ws))
         return rc;
     if (!kVal) return DVSOF_OK;
@@ -1027,5 +1030,5 @@ extern "C" int dvsof_scale_gradients(const dvsof_loss_scales_t* sc, const float*
     }
     if (int rc = build_table(&tmp, &tab, true)) return rc;
     return launch_kernel("scale_gradients_kernel", scale_gradients_kernel, kNumSMs * 8, 256, 0,
-                         (cudaStream_t)stream_, false, tab, factor);
+                         (cudaStream_t)stream_, true, tab, factor);
 }

@@ -1,17 +1,19 @@
 // loss_ring.cuh -- the warp-loss sweep (included by loss.cu): utils/loss.py:121-171 for all scales
 // and predictions in one launch, forward terms and analytic backward.
 //
-// Work unit = a SEGMENT of 32 pixel columns x R rows (R = 8, 16 or 32, chosen per launch) of one
-// (scale, prediction), taken by one WARP (= one CTA of a persistent one-wave grid).  The warp walks
-// its segment top to bottom in stages of 8 rows, one pixel column per lane.  Each stage's inputs arrive through TMA
+// Work unit = one WARP = one CTA: a SEGMENT of 32 pixel columns x R rows (R = 8, 16 or 32, chosen
+// per launch) of one (scale, prediction).  The warp walks its segment top to bottom in stages of
+// 8 rows, one pixel column per lane.  Each stage's inputs arrive through TMA
 // (cp.async.bulk.tensor.3d, completion on an mbarrier) into a two-stage ring in shared memory:
-//     flow box   2 channels x 10 rows (y-1 .. y+8) x 36 columns (x0-1 .. x0+34), zero outside the image
+//     flow box   2 channels x 10 rows (y-1 .. y+8) x 40 columns (x0-4 .. x0+35), zero outside the image
 //     prev box   8 rows x 32 columns of the matched `prev` pyramid level
 // while the previous stage is being processed, so staging costs one elected lane a handful of
 // instructions per 8 rows instead of ~25 per row, and there is no CTA-wide barrier anywhere.
 // (W % 4 != 0 or unaligned bases cannot be described by a tensor map: those scales fill the same
-// ring with plain loads.)  The bilinear taps of `next` are a data-dependent gather and go through
-// L1 (LDG); everything else is as in round 1's strip kernel:
+// ring with plain loads.)  One warp per CTA: a persistent one-wave grid with the ring running
+// across segments was measured slower (static stride vs the hardware CTA scheduler, and a third
+// more instructions in the compiler's stage body; commits 1099f6e / 67b5e1a, gpurun_out/r02l-n).
+// The bilinear taps of `next` are a data-dependent gather and go through L1 (LDG).  The arithmetic:
 //   * every neighbour pair of the smoothness term (utils/loss.py:76-90) is owned by the top-left
 //     pixel of its 2x2 block; value AND derivative come from one lg2 + one ex2:
 //         s = d^2 + eps^2,  t = s^(alpha-1),  c(d) = t * s,  c'(d) = 2 alpha d t;
@@ -41,21 +43,14 @@ namespace dvsof {
 #ifndef DVSOF_LOSS_MIN_CTAS
 #define DVSOF_LOSS_MIN_CTAS 20            // 1-warp CTAs per SM the register budget is held to
 #endif
-#ifndef DVSOF_LOSS_PERSISTENT
-#define DVSOF_LOSS_PERSISTENT 0           // 1: one wave of warps, each walking segments w, w + grid, ...
-#endif
-constexpr bool kPersistent = DVSOF_LOSS_PERSISTENT != 0;
 constexpr int kGroup = DVSOF_LOSS_GROUP;
 constexpr int kStageRows = 8;                               // rows per ring stage
 constexpr int kRingStages = 2;
-#ifndef DVSOF_LOSS_BOX_LEFT
-#define DVSOF_LOSS_BOX_LEFT 4             // columns staged left of the segment (1 needed)
-#endif
-#ifndef DVSOF_LOSS_FLOW_SPLIT
-#define DVSOF_LOSS_FLOW_SPLIT 0           // 1: one TMA per flow channel
-#endif
-constexpr int kBoxLeft = DVSOF_LOSS_BOX_LEFT;
-constexpr int kBoxW = kBoxLeft == 1 ? 36 : 40, kBoxH = kStageRows + 2;   // flow box (floats per row, rows)
+// The flow box starts 4 columns left of the segment although only 1 is needed: the innermost TMA
+// coordinate has to be a multiple of 16 bytes (x0 - 1 raised "illegal instruction" on B200,
+// gpurun_out/r02c vs r02d), and x0 is a multiple of 32.
+constexpr int kBoxLeft = 4;
+constexpr int kBoxW = 40, kBoxH = kStageRows + 2;           // flow box (floats per row, rows)
 constexpr int kPlane = kBoxW * kBoxH;                       // one channel of the flow box
 constexpr int kPrevOff = (2 * kPlane + 31) / 32 * 32;       // floats; 128-byte aligned
 constexpr int kStageFloats = (kPrevOff + kStageRows * 32 + 31) / 32 * 32;
@@ -181,22 +176,13 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
         "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
 // the executing CTA's shared window is part of its (1-CTA) cluster window: same 32-bit address
-__device__ __forceinline__ void tma_load_3d_raw(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
-
-__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, unsigned bar, int c0, int c1, int c2) {
-    tma_load_3d_raw(dst, map, bar, c0, c1, c2);
-}
 // the flow box of a stage: columns x0 - kBoxLeft .., rows y0 - 1 .., both channels of prediction n
 __device__ __forceinline__ void tma_load_flow(unsigned dst, const CUtensorMap* map, unsigned bar, int x0, int y0, int n) {
-    if (DVSOF_LOSS_FLOW_SPLIT) {
-        tma_load_3d_raw(dst, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n);
-        tma_load_3d_raw(dst + 4u * kPlane, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n + 1);
-    } else {
-        tma_load_3d_raw(dst, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n);
-    }
+    tma_load_3d(dst, map, bar, x0 - kBoxLeft, y0 - 1, 2 * n);
 }
 
 // Charbonnier pair with the term's normaliser folded into the exponent: with lk = log2(k),
@@ -229,8 +215,6 @@ struct SweepState {
     float2 acc_s;                         // smoothness: sum of k c(d) over all four directions (both channels)
     float2 acc_p;                         // photometric sum (even / odd rows of the row pairs)
     float acc_o, acc_n;                   // border sum, border count
-    float k_ob;                           // |border-term gradient scale g_ob / n_i|, < 0: n_i not read yet
-    bool ob_neg;                          // its sign
 };
 struct SweepConst {
     int H, W;
@@ -238,9 +222,7 @@ struct SweepConst {
     bool x_in;
     float lkh, lkv, lkd;                  // log2 of the smoothness normalisers, -inf where this lane has no such pair
     float lk_h0, lk_d0;                   // the same for the halo column left of the segment (unmasked)
-    float g_sm, k_ph, g_ob;               // d(loss)/d(term) x normaliser of the remaining terms
-    const int32_t* nb_ptr;                // out-of-border counts of this (scale, prediction): nb_count
-    int nb_count;                         // entries to sum (per-tile counts) or 1 (the total)
+    float g_sm, k_ph, k_ob;               // d(loss)/d(term) x normaliser of the remaining terms
     GridNorm gn;
     const float* next;
     float* grad0;                         // this lane's column of the gradient, channel 0 / 1:
@@ -394,15 +376,7 @@ __device__ __forceinline__ void sweep_stage(const float* F, float2* lh_sm, const
                 st.acc_n += m0 + m1;
             }
             if (kGrad) {
-                if (st.k_ob < 0.f) {              // first out-of-border pixel of the segment (warp-uniform)
-                    int nb = 0;
-                    for (int t = lane; t < c.nb_count; t += 32) nb += __ldcg(c.nb_ptr + t);
-                    nb = __reduce_add_sync(0xffffffffu, nb);
-                    st.k_ob = nb > 0 ? fabsf(__fdividef(c.g_ob, (float)nb)) : 0.f;   // loss.py:99-113
-                    st.ob_neg = c.g_ob < 0.f;
-                }
-                const float kob = st.ob_neg ? -st.k_ob : st.k_ob;
-                const float k0 = bad0 ? kob : 0.f, k1 = bad1 ? kob : 0.f;
+                const float k0 = bad0 ? c.k_ob : 0.f, k1 = bad1 ? c.k_ob : 0.f;
                 ox0 = fmaf(k0, b0.der.x, ox0); oy0 = fmaf(k0, b0.der.y, oy0);
                 ox1 = fmaf(k1, b1.der.x, ox1); oy1 = fmaf(k1, b1.der.y, oy1);
             }
@@ -444,20 +418,6 @@ __device__ __forceinline__ void stage_manual_prev(float* F, const float* __restr
     }
 }
 
-// lane 0: arm `bar` for the boxes of one stage and request them (flags: bit 0 flow, bit 1 prev)
-__device__ __forceinline__ void request_stage(const LossMaps& maps, int flags, int s, unsigned bar, unsigned dst,
-                                              int x0, int y0, int n, int i_prev) {
-    mbar_expect_tx(bar, ((flags & 1) ? kFlowBoxBytes : 0u) + ((flags & 2) ? kPrevBoxBytes : 0u));
-    if (flags & 1) tma_load_flow(dst, &maps.flow[s], bar, x0, y0, n);
-    if (flags & 2) tma_load_3d(dst + 4u * kPrevOff, &maps.prev[s], bar, x0, y0, i_prev);
-}
-
-// One warp (= CTA) per segment.  With DVSOF_LOSS_PERSISTENT the grid is instead one wave of 1-warp
-// CTAs (148 SMs x DVSOF_LOSS_MIN_CTAS), warp w takes segments w, w + grid, ... and the ring runs
-// ACROSS segments (the first stage of the warp's next segment is in flight during the last stage of
-// the current one).  Measured slower on B200 (cfg4 86-97 us vs 74-76 us, gpurun_out/r02l): the
-// hardware's CTA scheduler balances 8-16-row segments better than a static stride, and the
-// compiler's code for the stage body grows by a third inside the outer loop.  Kept for the record.
 template <bool kVal, bool kGrad>
 __global__ void __launch_bounds__(32, DVSOF_LOSS_MIN_CTAS)
 warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_constant__ LossMaps maps,
@@ -468,147 +428,122 @@ warp_loss_ring_kernel(const __grid_constant__ ScaleTable tab, const __grid_const
     __shared__ __align__(8) float2 lh_sm[kStageRows];
     pdl_launch_dependents();
     const int lane = threadIdx.x;
-    const int S = tab.n_scales, P = tab.n_pred, n_seg = tab.seg_begin[DVSOF_MAX_SCALES];
+    const TileCoord tc = decode_segment(tab, blockIdx.x);
+    const int S = tab.n_scales, P = tab.n_pred;
+    const int H = tab.H[tc.s], W = tab.W[tc.s];
+    const int plane = H * W;
+    const int rows = min(tab.seg_rows[tc.s], H - tc.y0);
+    const int n_stages = (rows + kStageRows - 1) / kStageRows;
+    const bool tma_flow = (tab.use_tma[tc.s] & 1) != 0, tma_prev = (tab.use_tma[tc.s] & 2) != 0;
+    const bool tma = tma_flow || tma_prev;
+    const unsigned stage_bytes = (tma_flow ? kFlowBoxBytes : 0u) + (tma_prev ? kPrevBoxBytes : 0u);
+    const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
     const unsigned bar0 = smem_u32(&bars[0]), ring0 = smem_u32(&ring[0][0]);
-    int seg = blockIdx.x;
-    TileCoord tc = decode_segment(tab, seg);
-    if (lane == 0) {
+    if (lane < kStageRows) lh_sm[lane] = make_float2(0.f, 0.f);
+    if (tma && lane == 0) {
         mbar_init(bar0, 1);
         mbar_init(bar0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        // the flow is an input of the call: the first box is requested while the prelude (pyramid
-        // levels, match_idx, tile counts) may still be running
-        const int flags = tab.use_tma[tc.s];
-        if (flags) mbar_expect_tx(bar0, ((flags & 1) ? kFlowBoxBytes : 0u) + ((flags & 2) ? kPrevBoxBytes : 0u));
-        if (flags & 1) tma_load_flow(ring0, &maps.flow[tc.s], bar0, tc.x0, tc.y0, tc.n);
+        // the flow is an input of the call: stage 0's box is requested while the prelude (pyramid
+        // levels, match_idx, tile counts, tickets) may still be running
+        mbar_expect_tx(bar0, stage_bytes);
+        if (tma_flow) tma_load_flow(ring0, &maps.flow[tc.s], bar0, tc.x0, tc.y0, tc.n);
     }
     pdl_wait_for(match_idx, n_bad_in);             // both come from the prelude (see pdl_acquire)
-    int i_prev = match_idx[tc.n], i_next = match_idx[P + tc.n];
-    if (lane == 0 && (tab.use_tma[tc.s] & 2))
+    const int i_prev = match_idx[tc.n], i_next = match_idx[P + tc.n];
+    if (tma_prev && lane == 0)
         tma_load_3d(ring0 + 4u * kPrevOff, &maps.prev[tc.s], bar0, tc.x0, tc.y0, i_prev);
-    unsigned buf = 0, parity = 0;                  // ring position; bit b of parity: phase of barrier b
-#pragma unroll 1
-    for (;;) {
-        // ---- this segment ----
-        const int H = tab.H[tc.s], W = tab.W[tc.s];
-        const int plane = H * W;
-        const int rows = min(tab.seg_rows[tc.s], H - tc.y0);
-        const int n_stages = (rows + kStageRows - 1) / kStageRows;
-        const int flags = tab.use_tma[tc.s];
-        const float* flow = tab.flow[tc.s] + (size_t)tc.n * 2 * plane;
-        SweepConst c;
-        c.H = H; c.W = W;
-        c.Hf = (float)H; c.Wf = (float)W;
-        const int x = tc.x0 + lane;
-        c.xf = (float)x;
-        c.x_in = x < W;
-        const bool x_r = x + 1 < W;
-        // log2 of 2 alpha / (4 x element count of the mean) per direction, precomputed on the host
-        // (-inf for a direction without pairs); lanes whose pixel has no such pair: -inf
-        c.lk_h0 = tab.lk[0][tc.s]; c.lk_d0 = tab.lk[2][tc.s];
-        c.lkh = x_r ? c.lk_h0 : -INFINITY;
-        c.lkv = c.x_in ? tab.lk[1][tc.s] : -INFINITY;
-        c.lkd = x_r ? c.lk_d0 : -INFINITY;
-        c.g_sm = c.k_ph = c.g_ob = 0.f;
-        c.nb_ptr = nullptr; c.nb_count = 0;
-        if (kGrad) {
-            // d(loss)/d(term) of this scale: device vector (generic backward) or host coefficients (fused)
-            c.g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
-            const float g_ph = grad_terms ? grad_terms[S + tc.s] : tab.coef[DVSOF_MAX_SCALES + tc.s];
-            const float g_ob = grad_terms ? grad_terms[2 * S + tc.s] : tab.coef[2 * DVSOF_MAX_SCALES + tc.s];
-            c.k_ph = g_ph * tab.norm[3][tc.s];
-            c.g_ob = g_ob * tab.norm[4][tc.s];
-            // n_i of this (scale, prediction), read when the first out-of-border pixel shows up:
-            // per-tile counts to be summed (the fused multiscale pass), or the total
-            const int per = tab.tiles_x[tc.s] * tab.tiles_y[tc.s];
-            c.nb_ptr = bad_per_tile ? n_bad_in + tab.cta_begin[tc.s] + tc.n * per : n_bad_in + tc.s * P + tc.n;
-            c.nb_count = bad_per_tile ? per : 1;
-        }
-        c.gn = GridNorm{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
-        const float* prev = tab.images[tc.s] + (size_t)i_prev * plane;
-        c.next = tab.images[tc.s] + (size_t)i_next * plane;
-        c.grad0 = kGrad ? tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane + x : nullptr;
-        c.grad1 = kGrad ? c.grad0 + plane : nullptr;
-        asm volatile("" : "+l"(c.next), "+l"(c.grad0), "+l"(c.grad1));  // finished bases: access = base + 32-bit offset
-        // ---- the warp's next segment: decoded now, its match_idx entries in flight from here on ----
-        const int seg2 = seg + (int)gridDim.x;
-        const bool more = kPersistent && seg2 < n_seg;
-        TileCoord tc2 = tc;
-        int i_prev2 = 0, i_next2 = 0;
-        if (more) {
-            tc2 = decode_segment(tab, seg2);
-            i_prev2 = match_idx[tc2.n];
-            i_next2 = match_idx[P + tc2.n];
-        }
+    __syncwarp();
 
-        SweepState st;
-        st.a = st.b = f2(0.f);
-        st.acc_s = st.acc_p = f2(0.f);
-        st.acc_o = st.acc_n = 0.f;
-        st.gv_p = st.gda_p = st.gdb_p = f2(0.f);
-        st.k_ob = -1.f;                           // not read yet
-        st.ob_neg = false;
-        const bool has_left = tc.x0 > 0;
-        if (!has_left) {                          // lane 0's halo load reads zeros in the first column block
-            __syncwarp();
-            if (lane < kStageRows) lh_sm[lane] = make_float2(0.f, 0.f);
-            __syncwarp();
+    SweepConst c;
+    c.H = H; c.W = W;
+    c.Hf = (float)H; c.Wf = (float)W;
+    const int x = tc.x0 + lane;
+    c.xf = (float)x;
+    c.x_in = x < W;
+    const bool x_r = x + 1 < W;
+    // log2 of 2 alpha / (4 x element count of the mean) per direction, precomputed on the host
+    // (-inf for a direction without pairs); lanes whose pixel has no such pair: -inf
+    c.lk_h0 = tab.lk[0][tc.s]; c.lk_d0 = tab.lk[2][tc.s];
+    c.lkh = x_r ? c.lk_h0 : -INFINITY;
+    c.lkv = c.x_in ? tab.lk[1][tc.s] : -INFINITY;
+    c.lkd = x_r ? c.lk_d0 : -INFINITY;
+    c.g_sm = c.k_ph = c.k_ob = 0.f;
+    if (kGrad) {
+        // d(loss)/d(term) of this scale: device vector (generic backward) or host coefficients (fused)
+        c.g_sm = grad_terms ? grad_terms[tc.s] : tab.coef[tc.s];
+        const float g_ph = grad_terms ? grad_terms[S + tc.s] : tab.coef[DVSOF_MAX_SCALES + tc.s];
+        const float g_ob = grad_terms ? grad_terms[2 * S + tc.s] : tab.coef[2 * DVSOF_MAX_SCALES + tc.s];
+        c.k_ph = g_ph * tab.norm[3][tc.s];
+        int nb;
+        if (bad_per_tile) {                       // per-tile counts of this (scale, prediction): sum them
+            const int per = tab.tiles_x[tc.s] * tab.tiles_y[tc.s];
+            const int32_t* tb = n_bad_in + tab.cta_begin[tc.s] + tc.n * per;
+            nb = 0;
+            for (int t = lane; t < per; t += 32) nb += __ldcg(tb + t);
+            nb = __reduce_add_sync(0xffffffffu, nb);
+        } else {
+            nb = n_bad_in[tc.s * P + tc.n];
         }
+        c.k_ob = nb > 0 ? __fdividef(g_ob * tab.norm[4][tc.s], (float)nb) : 0.f;   // loss.py:99-113
+    }
+    c.gn = GridNorm{tab.hx[tc.s], tab.hy[tc.s], tab.rx[tc.s], tab.ry[tc.s]};
+    const float* prev = tab.images[tc.s] + (size_t)i_prev * plane;
+    c.next = tab.images[tc.s] + (size_t)i_next * plane;
+    c.grad0 = kGrad ? tab.grad_flow[tc.s] + (size_t)tc.n * 2 * plane + x : nullptr;
+    c.grad1 = kGrad ? c.grad0 + plane : nullptr;
+    asm volatile("" : "+l"(c.next), "+l"(c.grad0), "+l"(c.grad1));  // finished bases: access = base + 32-bit offset
+
+    SweepState st;
+    st.a = st.b = f2(0.f);
+    st.acc_s = st.acc_p = f2(0.f);
+    st.acc_o = st.acc_n = 0.f;
+    st.gv_p = st.gda_p = st.gdb_p = f2(0.f);
+    const bool has_left = tc.x0 > 0;
 #pragma unroll 1
-        for (int j = 0; j < n_stages; ++j) {
-            const int y0 = tc.y0 + j * kStageRows;
-            float* F = ring[buf];
-            // request what comes next into the other buffer: this segment's next stage, or the
-            // first stage of the warp's next segment
-            const bool last = j + 1 == n_stages;
-            const int nflags = last ? (more ? tab.use_tma[tc2.s] : 0) : flags;
-            if (nflags) {
+    for (int j = 0; j < n_stages; ++j) {
+        const int y0 = tc.y0 + j * kStageRows;
+        float* F = ring[j & 1];
+        if (tma) {
+            if (j + 1 < n_stages) {               // request the next stage, then wait for this one
                 __syncwarp();                     // every lane is done with the buffer being refilled
                 if (lane == 0) {
-                    const unsigned nb = buf ^ 1u;
-                    if (last) request_stage(maps, nflags, tc2.s, bar0 + 8u * nb, ring0 + 4u * kStageFloats * nb,
-                                            tc2.x0, tc2.y0, tc2.n, i_prev2);
-                    else request_stage(maps, nflags, tc.s, bar0 + 8u * nb, ring0 + 4u * kStageFloats * nb,
-                                       tc.x0, y0 + kStageRows, tc.n, i_prev);
+                    const unsigned bar = bar0 + 8u * ((j + 1) & 1), dst = ring0 + 4u * kStageFloats * ((j + 1) & 1);
+                    mbar_expect_tx(bar, stage_bytes);
+                    if (tma_flow) tma_load_flow(dst, &maps.flow[tc.s], bar, tc.x0, y0 + kStageRows, tc.n);
+                    if (tma_prev) tma_load_3d(dst + 4u * kPrevOff, &maps.prev[tc.s], bar, tc.x0, y0 + kStageRows, i_prev);
                 }
             }
-            if ((flags & 3) != 3) {               // the parts no tensor map describes: plain loads
-                __syncwarp();
-                if (!(flags & 1)) stage_manual_flow(F, flow, H, W, y0, tc.x0, lane);
-                if (!(flags & 2)) stage_manual_prev(F, prev, H, W, y0, tc.x0, lane);
-                __syncwarp();
-            }
-            if (flags) {
-                mbar_wait(bar0 + 8u * buf, (parity >> buf) & 1u);
-                parity ^= 1u << buf;
-            }
-            if (j == 0) {                         // first row of the segment and the cell row above it
-                const float* fu = F + kBoxW + lane + kBoxLeft;
-                st.a = make_float2(fu[0], fu[kPlane]);
-                st.b = make_float2(fu[1], fu[kPlane + 1]);
-                if (kGrad && tc.y0 > 0) {         // the pairs reaching into row y0 from above
-                    const float2 ua = make_float2(fu[-kBoxW], fu[kPlane - kBoxW]);
-                    const float2 ub = make_float2(fu[1 - kBoxW], fu[kPlane + 1 - kBoxW]);
-                    st.gv_p = charb2k<false, true>(st.a, ua, c.lkv).der;
-                    st.gda_p = charb2k<false, true>(st.b, ua, c.lkd).der;
-                    st.gdb_p = charb2k<false, true>(ub, st.a, c.lkd).der;
-                }
-            }
-            if (y0 + kStageRows < H) sweep_stage<kVal, kGrad, false>(F, lh_sm, c, st, y0, has_left, lane);
-            else sweep_stage<kVal, kGrad, true>(F, lh_sm, c, st, y0, has_left, lane);
-            buf ^= 1u;
         }
-        if (kVal) {
-            // record: [photo, smoothness (normalised, all directions), outborder_sum, n_bad]; summed by
-            // loss_reduce_kernel (loss.cu) after this launch -- no ticket, no fence here
-            float acc[8] = {st.acc_p.x + st.acc_p.y, st.acc_s.x + st.acc_s.y, st.acc_o, st.acc_n, 0.f, 0.f, 0.f, 0.f};
-            warp_sum8(acc, lane);                 // lane 4 i (i < 8) ends up with value bitrev3(i)
-            if ((lane & 19) == 0)                 // lanes 0, 4, 8, 12 hold values 0, 1, 2, 3 in bit-reversed order
-                __stcg(ws.partials + (size_t)seg * kRec + (((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)), acc[0]);
+        if (!tma_flow || !tma_prev) {             // the parts no tensor map describes: plain loads
+            __syncwarp();
+            if (!tma_flow) stage_manual_flow(F, flow, H, W, y0, tc.x0, lane);
+            if (!tma_prev) stage_manual_prev(F, prev, H, W, y0, tc.x0, lane);
+            __syncwarp();
         }
-        if (!more) break;
-        seg = seg2; tc = tc2; i_prev = i_prev2; i_next = i_next2;
+        if (tma) mbar_wait(bar0 + 8u * (j & 1), (unsigned)(j >> 1) & 1u);
+        if (j == 0) {                             // first row of the segment and the cell row above it
+            const float* fu = F + kBoxW + lane + kBoxLeft;
+            st.a = make_float2(fu[0], fu[kPlane]);
+            st.b = make_float2(fu[1], fu[kPlane + 1]);
+            if (kGrad && tc.y0 > 0) {             // the pairs reaching into row y0 from above
+                const float2 ua = make_float2(fu[-kBoxW], fu[kPlane - kBoxW]);
+                const float2 ub = make_float2(fu[1 - kBoxW], fu[kPlane + 1 - kBoxW]);
+                st.gv_p = charb2k<false, true>(st.a, ua, c.lkv).der;
+                st.gda_p = charb2k<false, true>(st.b, ua, c.lkd).der;
+                st.gdb_p = charb2k<false, true>(ub, st.a, c.lkd).der;
+            }
+        }
+        if (y0 + kStageRows < H) sweep_stage<kVal, kGrad, false>(F, lh_sm, c, st, y0, has_left, lane);
+        else sweep_stage<kVal, kGrad, true>(F, lh_sm, c, st, y0, has_left, lane);
     }
+    if (!kVal) return;
+    // record: [photo, smoothness (normalised, all directions), outborder_sum, n_bad]; summed by
+    // loss_reduce_kernel (loss.cu) after this launch -- no ticket, no fence here
+    float acc[8] = {st.acc_p.x + st.acc_p.y, st.acc_s.x + st.acc_s.y, st.acc_o, st.acc_n, 0.f, 0.f, 0.f, 0.f};
+    warp_sum8(acc, lane);
+    if ((lane & 19) == 0)                         // lanes 0, 4, 8, 12 hold the totals of values 0, 1, 2, 3
+        __stcg(ws.partials + (size_t)blockIdx.x * kRec + (((lane >> 3) & 1) * 2 + ((lane >> 2) & 1)), acc[0]);
 }
 
 // Out-of-border pixel count n_i per (scale, prediction) (utils/loss.py:92-113) ahead of the fused
