@@ -4,12 +4,14 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     (N > 1: launched by torchrun, one rank per GPU)
 
-Headline metric (BASELINE.json): encoded ("voxelized") Mevents/s on configs[1] -- MVSEC-shaped
-256x256 events, batch 8, 131072 events/sample.  A step = one pass of the encoder
-over one synthetic batch, inputs resident in HBM, L2 flushed between steps.  The same JSON line
-also carries the warp-loss fwd+bwd samples/s (`warp_loss`), larger workloads (`workloads`), the
-end-to-end number through the public Python API from pinned host buffers (`e2e`), the roofline
-of the dominant kernel and the CPU baseline (oracle port, timed on this box's host cores).
+Headline metric (BASELINE.json): encoded ("voxelized") Mevents/s on the largest single-GPU
+configuration, configs[2] shapes -- MVSEC-shaped 256x256 events, batch 32, 5 M events/sample
+(SURVEY.md 8d cfg3).  A step = one pass of the encoder over one synthetic batch, inputs resident
+in HBM, L2 flushed between steps.  The same JSON line also carries the warp-loss fwd+bwd samples/s
+(`warp_loss`), the other configurations (`workloads`: cfg1, cfg2, cfg2 with the contended event
+distribution, cfg4), the end-to-end number through the public Python API from pinned host buffers
+(`e2e`), the roofline of the dominant kernel and the CPU baselines (oracle ports, timed on this
+box's host cores).
 """
 import argparse
 import json
@@ -32,10 +34,21 @@ CFG = {
     'cfg3': dict(B=32, H=256, W=256, n=5_000_000, T=0.032),
     'cfg4': dict(B=16, H=480, W=640, n=1_048_576, T=0.1),
 }
-HEADLINE = 'cfg2'
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the scatter kernel, from the committed
-# `ncu --set full` capture (profiles/r01_ncu_full_v1_summary.csv)
-TRAFFIC = {'cfg2': 46.15e6}
+HEADLINE = 'cfg3'
+DESCR = {'cfg1': 'DAVIS-shaped 260x346 events, batch 1, 32768 events/sample -> (1,4,272,352)',
+         'cfg2': 'MVSEC-shaped 256x256 events, batch 8, 131072 events/sample -> (8,4,256,256)',
+         'cfg3': 'MVSEC-shaped 256x256 events at high rate, batch 32, 5 M events/sample -> (32,4,256,256)',
+         'cfg4': 'DSEC-shaped 480x640 events, batch 16, 1 M events/sample -> (16,4,480,640)'}
+
+
+def traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` on `workload`, from the
+    committed `ncu --set full` captures (profiles/traffic.json, written by scripts/ncu_traffic.py
+    from the .ncu-rep files named there); None when that pair was not captured."""
+    f = ROOT / 'profiles' / 'traffic.json'
+    if not f.exists():
+        return None
+    return json.loads(f.read_text()).get(workload, {}).get(kernel, {}).get('dram_bytes')
 
 
 def peaks():
@@ -45,13 +58,21 @@ def peaks():
     return 6650.0, 'fallback (B200_PROFILING.md 6.65 TB/s)'
 
 
-def fast_events(seed, B, H, W, n, T, device):
+def fast_events(seed, B, H, W, n, T, device, contended=False):
     """Synthetic events of SURVEY 8d generated on `device` (same distribution as
-    tests/helpers.synth_events; torch device RNG so cfg3's 160 M events take milliseconds)."""
+    tests/helpers.synth_events; torch device RNG so cfg3's 160 M events take milliseconds).
+    contended: 80 % of the events fall on a random 10 % of the pixels (SURVEY 8d's second set)."""
     g = torch.Generator(device=device).manual_seed(seed)
     N = B * n
-    ev = {'x': torch.randint(0, W, (N,), generator=g, device=device),
-          'y': torch.randint(0, H, (N,), generator=g, device=device),
+    x = torch.randint(0, W, (N,), generator=g, device=device)
+    y = torch.randint(0, H, (N,), generator=g, device=device)
+    if contended:
+        hot = torch.randperm(H * W, generator=g, device=device)[:max(1, H * W // 10)]
+        pick = hot[torch.randint(0, hot.numel(), (N,), generator=g, device=device)]
+        use = torch.rand(N, generator=g, device=device) < 0.8
+        x = torch.where(use, pick % W, x)
+        y = torch.where(use, pick // W, y)
+    ev = {'x': x, 'y': y,
           'polarity': (torch.rand(N, generator=g, device=device) < 0.7).long() * 2 - 1,
           'sample_index': torch.arange(B, device=device).repeat_interleave(n)}
     t = torch.rand(B, n, generator=g, device=device) * T
@@ -186,59 +207,94 @@ def bench_codec(name, K, W, dev):
     return {'events': N, 'decode_ms': dec_ms, 'encode_ms': enc_ms, 'bytes': 45 * N}
 
 
-def bench_encoder(name, K, W, dev, seed_off=0):
+def graph_time(fn, dev, iters=100, reps=3):
+    """Warm figure: `iters` back-to-back calls of `fn` captured in ONE CUDA graph and
+    replayed -- no host launch cost, no L2 flush between iterations (inputs that fit the 126 MB L2
+    stay resident).  Returns ms per call (best of `reps` replays)."""
+    side = torch.cuda.Stream(dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            fn()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=side):
+        for _ in range(iters):
+            fn()
+    best = None
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        best = ms if best is None else min(best, ms)
+    return best
+
+
+def bench_encoder(name, K, W, dev, seed_off=0, contended=False):
+    """The encoder through the C ABI on workload `name`: the whole call (a step), the dominant
+    kernel(s) alone with CUDA events on the launching stream, and the graph-captured warm figure."""
     import dvs_of_training_framework_b200 as dv
     L = dv._lib
     c = CFG[name]
     B, H, Wd, n = c['B'], c['H'], c['W'], c['n']
     He, We = dv.extend_size((H, Wd))
-    ev, ts, _ = fast_events(1234 + int(name[3:]) + seed_off, B, H, Wd, n, c['T'], dev)
+    ev, ts, _ = fast_events(1234 + int(name[3:]) + seed_off, B, H, Wd, n, c['T'], dev, contended)
     N = B * n
     out = torch.empty((B, 4, He, We), dtype=torch.float32, device=dev)
     ws = torch.empty(L.load().dvsof_encode_workspace_bytes(N, B, He, We), dtype=torch.uint8, device=dev)
-    status = torch.zeros(1, dtype=torch.int32, device=dev)
-    sp = L.stream_ptr(dev)
+    status = L.status_for(dev).word
+    sp = lambda: L.stream_ptr(dev)  # noqa: E731  (the current stream: differs under graph capture)
     flush = L2Flusher(dev)
+    evp = [L.ptr(ev[k]) for k in ('x', 'y', 'timestamp', 'polarity', 'sample_index')]
+    binned = bool(L.load().dvsof_encode_path(N, B, He, We, ws.numel()))
 
     def prepare():
         L.call('dvsof_encode_prepare', L.ptr(ev['timestamp']), L.ptr(ev['sample_index']), N,
-               L.ptr(ts), B, He, We, L.ptr(out), L.ptr(ws), sp)
+               L.ptr(ts), B, He, We, L.ptr(out), L.ptr(ws), sp())
 
     def scatter():
-        L.call('dvsof_encode_scatter', L.ptr(ev['x']), L.ptr(ev['y']), L.ptr(ev['timestamp']),
-               L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, B, He, We, L.ptr(out),
-               L.ptr(ws), L.ptr(status), sp)
+        L.call('dvsof_encode_scatter', *evp, N, B, He, We, L.ptr(out), L.ptr(ws), L.ptr(status), sp())
+
+    def bin_pass(which):
+        L.call('dvsof_encode_binned_pass', *evp, N, B, He, We, L.ptr(out), L.ptr(ws), ws.numel(),
+               L.ptr(status), which, sp())
 
     def whole():
-        L.call('dvsof_encode_event_image', L.ptr(ev['x']), L.ptr(ev['y']), L.ptr(ev['timestamp']),
-               L.ptr(ev['polarity']), L.ptr(ev['sample_index']), N, L.ptr(ts), B, He, We, L.ptr(out),
-               L.ptr(ws), ws.numel(), L.ptr(status), sp)
+        L.call('dvsof_encode_event_image', *evp, N, L.ptr(ts), B, He, We, L.ptr(out),
+               L.ptr(ws), ws.numel(), L.ptr(status), sp())
 
-    E = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
-    # (1) the step: one library call = prepare (zero + per-sample dt) -> scatter, PDL-chained
-    for _ in range(W):
-        flush(); whole()
-    torch.cuda.synchronize()
-    marks = [(E(), E()) for _ in range(K)]
-    for e0, e1 in marks:
-        flush()
-        e0.record(); whole(); e1.record()
-    torch.cuda.synchronize()
-    step_ms = float(np.mean([e0.elapsed_time(e1) for e0, e1 in marks]))
-    # (2) the dominant kernel alone (events on the launching stream around the scatter launch)
-    for _ in range(W):
-        flush(); prepare(); scatter()
-    torch.cuda.synchronize()
-    marks = [(E(), E()) for _ in range(K)]
-    for k0, k1 in marks:
-        flush(); prepare()
-        k0.record(); scatter(); k1.record()
-    torch.cuda.synchronize()
-    assert int(status.item()) == 0, 'encoder flagged invalid input'
+    def timed(pre, fn):
+        """K event pairs around fn(); pre() (untimed, after the flush) sets up what fn needs."""
+        for _ in range(W):
+            flush(); pre(); fn()
+        torch.cuda.synchronize()
+        marks = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for e0, e1 in marks:
+            flush(); pre()
+            e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        return float(np.mean([e0.elapsed_time(e1) for e0, e1 in marks]))
+
+    # (1) the step: one library call = prepare (zero + per-sample dt) -> the path the library picks
+    step_ms = timed(lambda: None, whole)
     assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved'
-    kern_ms = float(np.mean([k0.elapsed_time(k1) for k0, k1 in marks]))
-    return dict(workload=name, events=N, step_ms=step_ms, kernel_ms=kern_ms,
-                bytes=encoder_bytes(B, He, We, N), launches_per_step=2)
+    # (2) the kernels alone (events on the launching stream around one launch)
+    kern = {'scatter_ms': timed(prepare, scatter)}
+    assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved'
+    if binned:
+        kern['bin_ms'] = timed(prepare, lambda: bin_pass(1))
+        kern['reduce_ms'] = timed(lambda: (prepare(), bin_pass(1)), lambda: bin_pass(2))
+        assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved (binned passes)'
+    L.status_for(dev).check()
+    # (3) warm: 100 graph-captured calls, no flush
+    warm_ms = graph_time(whole, dev)
+    return dict(workload=name, events=N, step_ms=step_ms, kernel_ms=kern['scatter_ms'], kernels=kern,
+                binned=binned, warm_graph_ms=warm_ms, bytes=encoder_bytes(B, He, We, N),
+                launches_per_step=3 if binned else 2, cells=B * 4 * He * We, contended=contended)
 
 
 def bench_loss(name, K, W, dev):
@@ -318,10 +374,17 @@ def bench_loss(name, K, W, dev):
 
     abi_ms = float(np.mean(time_steps(abi_step, K, W, flush)))
     st.check()
+
+    def abi_step_graph():                         # the same calls on whatever stream is current (capture)
+        spg = L.stream_ptr(dev)
+        L.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S], base + 4 * o[S + 2],
+               base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr, L.ptr(st.word), spg)
+        L.call('dvsof_scale_gradients', plan.bwd, L.ptr(one), spg)
+    warm_ms = graph_time(abi_step_graph, dev)
     return dict(workload=name, samples=B, step_ms=step_ms, abi_ms=abi_ms, bytes=loss_bytes(B, H, Wd),
                 fwd_ms=fwd_ms, bwd_ms=bwd_ms, fwd_bytes=16 * px, bwd_bytes=24 * px,
                 fused_ms=fused_ms, fused_with_count_ms=fusedc_ms, fused_bytes=24 * px,
-                launches_per_step=9)
+                warm_graph_ms=warm_ms, launches_per_step=4, pixels=px)
 
 
 def fused_kernels(r, peak):
@@ -331,6 +394,7 @@ def fused_kernels(r, peak):
     frac = lambda b, ms: b / (ms * 1e-3) / 1e9 / peak  # noqa: E731
     return {'c_abi_step_ms': r['abi_ms'], 'c_abi_samples_per_s': r['samples'] / (r['abi_ms'] * 1e-3),
             'c_abi_step_hbm_frac_survey_bytes': frac(r['bytes'], r['abi_ms']),
+            'c_abi_step_warm_graph_ms': r['warm_graph_ms'],
             'fused_ms': r['fused_ms'], 'fused_with_count_ms': r['fused_with_count_ms'],
             'fused_hbm_frac_24B_per_px': frac(r['fused_bytes'], r['fused_ms']),
             'fused_hbm_frac_survey_40B_per_px': frac(r['fwd_bytes'] + r['bwd_bytes'], r['fused_ms']),
@@ -394,7 +458,7 @@ def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
     # every step uploads its batch from pinned host memory; the upload of step k+1 runs on a copy
     # stream during step k (training.DevicePrefetcher), as a prefetching loader does
     import itertools
-    feed = iter(tr.DevicePrefetcher(itertools.repeat(batch, W + K + 1), dev, True))
+    feed = iter(tr.DevicePrefetcher(itertools.repeat(batch, W + K + 4), dev, True))
 
     def step():
         loss, _, _ = tr.process_minibatch(model, next(feed), timers, dev, True, evaluator, [0.5, 1, 1])
@@ -417,7 +481,32 @@ def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
     e1.record()
     torch.cuda.synchronize()
     assert torch.isfinite(loss).item(), 'train step produced a non-finite loss'
-    return dict(samples=per_gpu, step_ms=e0.elapsed_time(e1) / K, params=sum(p.numel() for p in model.parameters()))
+    step_ms = e0.elapsed_time(e1) / K
+    dp = None
+    if world > 1 and not encoded:
+        # data-parallel self-check, outside the timed region: the flat gradient the bucketed NCCL
+        # allreduce leaves on rank 0 == the mean of every rank's local gradient (gathered to rank 0),
+        # for the same weights and each rank's own shard
+        def grads(reduce):
+            red.enabled = reduce
+            red.zero_grad()
+            lo_, _, _ = tr.process_minibatch(model, next(feed), timers, dev, True, evaluator, [0.5, 1, 1])
+            lo_.backward()
+            red.wait()
+            red.enabled = True
+            return torch.cat([b['flat'] for b in red.buckets]).clone()
+        local, reduced = grads(False), grads(True)
+        gathered = [torch.empty_like(local) for _ in range(world)] if rank == 0 else None
+        dist.gather(local, gathered, dst=0)
+        if rank == 0:
+            mean = torch.stack(gathered).mean(0)
+            scale = float(mean.abs().max())
+            err = float((reduced - mean).abs().max())
+            dp = {'max_abs_err': err, 'grad_max_abs': scale, 'rel': err / max(scale, 1e-30),
+                  'ok': bool(err <= 1e-5 * scale + 1e-9), 'elements': int(mean.numel()),
+                  'what': 'allreduced flat gradient on rank 0 vs mean of the per-rank local gradients (dist.gather)'}
+        red.zero_grad()
+    return dict(samples=per_gpu, step_ms=step_ms, params=sum(p.numel() for p in model.parameters()), dp_check=dp)
 
 
 def bench_e2e(name, K, W, dev, compact=False):
@@ -474,38 +563,101 @@ def bench_e2e(name, K, W, dev, compact=False):
     return dict(events=B * n, step_s=dt, h2d=h2d, d2h=d2h)
 
 
-def cpu_encoder_pass(name, threads=None):
-    """One pass of the oracle's torch-CPU port of the reference encoder on the workload."""
+REF_SAMPLES = 8        # the CPU arms run this many of the headline workload's samples per pass
+
+
+def cpu_encoder_pass(name, threads=None, samples=None):
+    """One pass of the oracle's torch-CPU port of the reference encoder on (a sample of) the workload:
+    the first `samples` samples of it, same events per sample, same image size."""
     from oracle import encoder_oracle_torch as eot
     import dvs_of_training_framework_b200 as dv
     c = CFG[name]
+    B = min(samples or c['B'], c['B'])
     # all the host threads this process may use -- torchrun exports OMP_NUM_THREADS=1, which would
     # time the reference on one core
     torch.set_num_threads(threads or len(os.sched_getaffinity(0)))
-    ev, ts, sidx = fast_events(1234 + int(name[3:]), c['B'], c['H'], c['W'], c['n'], c['T'], 'cpu')
+    ev, ts, sidx = fast_events(1234 + int(name[3:]), B, c['H'], c['W'], c['n'], c['T'], 'cpu')
     size = dv.extend_size((c['H'], c['W']))
-    return (lambda: eot.compute_event_image(ev, ts, sidx, size)), c['B'] * c['n']
+    return (lambda: eot.compute_event_image(ev, ts, sidx, size)), B * c['n'], B
 
 
-def cpu_baseline(name, budget_s=12.0):
-    fn, N = cpu_encoder_pass(name)
+def _timed_passes(fn, budget_s):
     fn()
     t0 = time.perf_counter()
     reps = 0
-    while time.perf_counter() - t0 < budget_s:
+    while reps < 1 or time.perf_counter() - t0 < budget_s:
         fn()
         reps += 1
-    dt = (time.perf_counter() - t0) / reps
+    return (time.perf_counter() - t0) / reps, reps
+
+
+def cpu_baseline(name, budget_s=12.0):
+    fn, N, B = cpu_encoder_pass(name, samples=REF_SAMPLES)
+    dt, reps = _timed_passes(fn, budget_s)
     return {'value': N / dt / 1e6, 'unit': 'Mevents/s', 'cores': torch.get_num_threads(),
-            'kind': 'port', 'sample': f'{reps} full passes of {name} ({N} events) in {budget_s:.0f} s, '
-            'oracle/encoder_oracle_torch.py (the reference ATen op sequence, CPU)',
+            'kind': 'port', 'sample': f'{reps} passes over {B} of the {CFG[name]["B"]} samples of {name} ({N} events '
+            f'per pass) in {budget_s:.0f} s, oracle/encoder_oracle_torch.py (the reference ATen op sequence, CPU)',
             'host_cpus': len(os.sched_getaffinity(0))}
+
+
+def cpu_baseline_loss(name, budget_s=8.0):
+    """utils/loss.py:174-214 + autograd on the host cores: the oracle's
+    functional restatement, forward + backward of the weighted loss, all threads and one thread."""
+    from oracle import loss_oracle as lo
+    from tests.helpers import synth_loss_inputs
+    c = CFG[name]
+    B = min(REF_SAMPLES, c['B'])
+    inp = synth_loss_inputs(1234 + int(name[3:]), B, c['H'], c['W'], 3.0)
+
+    def step():
+        fl = [f.clone().requires_grad_() for f in inp['flows']]
+        terms = lo.multiscale_loss(fl, inp['flow_ts'], inp['flow_sample_idx'], inp['images'],
+                                   inp['timestamps'], inp['sample_idx'])
+        lo.combined(terms).backward()
+    out = {}
+    for tag, threads in (('all_threads', len(os.sched_getaffinity(0))), ('one_thread', 1)):
+        torch.set_num_threads(threads)
+        dt, reps = _timed_passes(step, budget_s)
+        out[tag] = {'value': B / dt, 'unit': 'samples/s', 'cores': threads, 'kind': 'port',
+                    'sample': f'{reps} fwd+bwd passes over {B} of the {c["B"]} samples of {name} in {budget_s:.0f} s, '
+                              'oracle/loss_oracle.py (utils/loss.py restated, torch CPU + autograd)'}
+    torch.set_num_threads(len(os.sched_getaffinity(0)))
+    return out
+
+
+def bench_map_events(dev, budget_s=4.0):
+    """The one native component (transformation.cpp:35-85): the rotation remap of a DAVIS event array.
+    GPU: RotationLUT.apply on device-resident events (LUT built once per angle, as RandomRotation
+    does per sample); CPU: the plain C++ restatement oracle/map_events_ref.cpp, single thread like
+    the original (which builds its hash map per call, so the build is inside its time)."""
+    import dvs_of_training_framework_b200 as dv
+    from oracle import encoder_oracle as eo
+    from oracle import map_events_native as mn
+    H, W, n = 260, 346, 1 << 20
+    rng = np.random.default_rng(7)
+    ev = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), np.sort(rng.random(n)),
+                   rng.choice([-1, 1], n), np.zeros(n)], 1).astype(np.float32)
+    src, dst = eo.rotation_lut((H, W), 17.5)
+    mn.build()
+    dt_cpu, reps = _timed_passes(lambda: mn.port_map(ev, (H, W), src, dst), budget_s)
+    ev_d = torch.from_numpy(ev).to(dev)
+    lut = dv.transformation.RotationLUT((H, W), torch.from_numpy(src.view(np.int64)).to(dev),
+                                        torch.from_numpy(dst.view(np.int64)).to(dev), device=dev)
+    out = lut.apply(ev_d)
+    want = mn.port_map(ev, (H, W), src, dst)
+    assert out.shape == want.shape and np.array_equal(out.cpu().numpy(), want), 'map_events differs from the oracle'
+    ms = float(np.mean(time_steps(lambda: lut.apply(ev_d), 10, 3, lambda: None)))
+    return {'workload': f'{n} DAVIS events (260x346) through the 17.5 degree rotation LUT ({src.size} entries)',
+            'gpu_mevents_per_s': n / (ms * 1e-3) / 1e6, 'gpu_ms': ms,
+            'note': 'transformation.RotationLUT.apply: count + scan + write, one host sync for the output size',
+            'cpu_baseline': {'value': n / dt_cpu / 1e6, 'unit': 'Mevents/s', 'cores': 1, 'kind': 'port',
+                             'sample': f'{reps} calls in {budget_s:.0f} s, oracle/map_events_ref.cpp (transformation.cpp:35-85 restated), single thread'}}
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
-    fn, N = cpu_encoder_pass(HEADLINE)
+    fn, N, B = cpu_encoder_pass(HEADLINE, samples=REF_SAMPLES)
     for _ in range(args.warmup):
         fn()
     t0 = time.perf_counter()
@@ -513,16 +665,15 @@ def run_reference(args, rank):
         fn()
     dt = (time.perf_counter() - t0) / args.steps
     v = N / dt / 1e6
-    c = CFG[HEADLINE]
+    sample = (f'each step = {B} of the {CFG[HEADLINE]["B"]} samples of {HEADLINE} ({N} events, same events per sample '
+              'and image size); the reference is Python + torch_scatter and cannot travel: oracle torch-CPU port')
     line = {'impl': 'reference', 'metric': 'encoded Mevents/s', 'value': v, 'unit': 'Mevents/s',
             'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': dt * 1e3,
             'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
             'data': 'synthetic',
-            'config': {'workload': f'{HEADLINE}: MVSEC-shaped 256x256 events, batch {c["B"]}, '
-                                   f'{c["n"]} events/sample -> (B,4,256,256) event image'},
+            'config': {'workload': f'{HEADLINE}: {DESCR[HEADLINE]}'},
             'cpu_baseline': {'value': v, 'unit': 'Mevents/s', 'cores': torch.get_num_threads(),
-                             'kind': 'port', 'sample': f'{args.steps} full passes of {HEADLINE}; the '
-                             'reference is Python+torch_scatter and cannot travel: oracle torch-CPU port'},
+                             'kind': 'port', 'sample': sample},
             'e2e': {'value': v, 'unit': 'Mevents/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     emit(line)
@@ -588,21 +739,32 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def reduce_enc(r):
+        r['step_ms'] = max_over_ranks(r['step_ms'])
+        r['warm_graph_ms'] = max_over_ranks(r['warm_graph_ms'])
+        r['kernels'] = {k: max_over_ranks(v) for k, v in r['kernels'].items()}
+        return r
+
+    def reduce_loss(r):
+        for k in ('step_ms', 'abi_ms', 'fused_ms', 'warm_graph_ms'):
+            r[k] = max_over_ranks(r[k])
+        return r
+
     sync_all()
     with Clocks(local) as clk:
-        head = bench_encoder(HEADLINE, K, W, dev, seed_off=rank)
+        head = reduce_enc(bench_encoder(HEADLINE, K, W, dev, seed_off=rank))
+        torch.cuda.empty_cache()
         sync_all()
-        loss = bench_loss(HEADLINE, K, W, dev)
+        loss = reduce_loss(bench_loss(HEADLINE, K, W, dev))
         sync_all()
     clocks = clk.summary()
-    head_ms = max_over_ranks(head['step_ms'])
-    kern_ms = max_over_ranks(head['kernel_ms'])
-    loss_ms = max_over_ranks(loss['abi_ms'])
-    loss_py_ms = max_over_ranks(loss['step_ms'])
-    e2e = bench_e2e(HEADLINE, max(3, K // 5), 3, dev)
+    e2e_k = max(20, K)
+    e2e = bench_e2e(HEADLINE, e2e_k, 3, dev)
     e2e_s = max_over_ranks(e2e['step_s'])
-    e2e_c = bench_e2e(HEADLINE, max(3, K // 5), 3, dev, compact=True)
+    torch.cuda.empty_cache()
+    e2e_c = bench_e2e(HEADLINE, e2e_k, 3, dev, compact=True)
     e2e_c_s = max_over_ranks(e2e_c['step_s'])
+    torch.cuda.empty_cache()
     sync_all()
     train = None
     if not args.quick:
@@ -616,41 +778,89 @@ def main():
     sync_all()
     extra = {}
     if not args.quick:
-        for name in ('cfg3', 'cfg4'):
-            k2 = max(3, min(K, 10))
-            r = bench_encoder(name, k2, 3, dev, seed_off=rank)
-            r['step_ms'], r['kernel_ms'] = max_over_ranks(r['step_ms']), max_over_ranks(r['kernel_ms'])
-            extra[name] = r
+        k2 = max(3, min(K, 10))
+        for name, kw in (('cfg1', {}), ('cfg2', {}), ('cfg2_contended', {'contended': True}), ('cfg4', {})):
+            extra[name] = reduce_enc(bench_encoder(name[:4], k2, 3, dev, seed_off=rank, **kw))
             torch.cuda.empty_cache()
-            ll = bench_loss(name, k2, 3, dev)
-            ll['step_ms'] = max_over_ranks(ll['step_ms'])
-            extra[name + '_loss'] = ll
+        for name in ('cfg1', 'cfg2', 'cfg4'):
+            extra[name + '_loss'] = reduce_loss(bench_loss(name, k2, 3, dev))
             torch.cuda.empty_cache()
-    codec = bench_codec(HEADLINE, max(3, min(K, 10)), 3, dev) if (rank == 0 and not args.quick) else None
+    solo = rank == 0 and not args.quick
+    codec = bench_codec('cfg2', max(3, min(K, 10)), 3, dev) if solo else None
+    mapev = bench_map_events(dev) if solo else None
     torch.cuda.empty_cache()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
     peak, peak_src = peaks()
+    frac = lambda nbytes, ms: nbytes / (ms * 1e-3) / 1e9 / peak  # noqa: E731
+
+    def encoder_line(name, r):
+        """Workload entry of the encoder: the call, the dominant kernel's roofline, traffic."""
+        dom = 'encode_bin_kernel' if r['binned'] else 'encode_vec4_kernel'
+        dom_ms = r['kernels']['bin_ms'] if r['binned'] else r['kernels']['scatter_ms']
+        # algorithmic bytes of the dominant kernel's launch: the event stream (36 B/event) for the
+        # counting-sort pass (the image is written by pass 2), stream + image for the direct scatter
+        dom_bytes = 36 * r['events'] if r['binned'] else r['bytes']
+        out = {'workload': DESCR[name[:4]] + ('; contended: 80 % of the events on 10 % of the pixels' if r['contended'] else ''),
+               'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6, 'ms_per_step': r['step_ms'],
+               'hbm_frac_step': frac(r['bytes'], r['step_ms']), 'algorithmic_bytes_step': r['bytes'],
+               'path': 'binned (counting sort into 6 B records + per-slab reduction in shared memory)' if r['binned']
+                       else 'direct (RED.ADD / RED.MAX into the L2-resident image)',
+               'warm_graph_ms_per_step': r['warm_graph_ms'],
+               'roofline': {'bound': 'hbm', 'kernel': dom, 'kernel_ms': dom_ms, 'algorithmic_bytes': dom_bytes,
+                            'achieved': dom_bytes / (dom_ms * 1e-3) / 1e9, 'peak': peak, 'unit': 'GB/s',
+                            'frac': frac(dom_bytes, dom_ms), 'traffic': traffic(name[:4], dom)},
+               'kernels_ms': r['kernels']}
+        if r['binned']:
+            out['roofline_pass2'] = {'kernel': 'encode_reduce_kernel', 'kernel_ms': r['kernels']['reduce_ms'],
+                                     'algorithmic_bytes': 6 * r['events'] + 4 * r['cells'],
+                                     'frac': frac(6 * r['events'] + 4 * r['cells'], r['kernels']['reduce_ms']),
+                                     'traffic': traffic(name[:4], 'encode_reduce_kernel'),
+                                     'note': 'reads the 6 B/event records pass 1 wrote, writes the image once'}
+            out['direct_scatter_ms'] = r['kernels']['scatter_ms']
+        else:
+            # this design is bound by L2 atomics, not HBM: two REDs per event against the measured
+            # ceiling for scattered REDs on this part (profiles/r01b_ubench_atomics.json: 190 G/s)
+            out['red_rate_frac_of_measured_ceiling'] = 2 * r['events'] / (dom_ms * 1e-3) / 190e9
+        return out
+
+    def loss_line(name, r):
+        c_ = CFG[name]
+        return {'workload': f'{name}: 4 scales, {c_["H"]}x{c_["W"]}, B={c_["B"]}',
+                'samples_per_s': world * r['samples'] / (r['step_ms'] * 1e-3), 'ms_per_step': r['step_ms'],
+                'api': 'training.combined_loss(...) + loss.backward() (Python + torch.autograd around the C ABI)',
+                'c_abi': {'samples_per_s': world * r['samples'] / (r['abi_ms'] * 1e-3), 'ms_per_step': r['abi_ms'],
+                          'hbm_frac_step': frac(r['bytes'], r['abi_ms']),
+                          'warm_graph_ms_per_step': r['warm_graph_ms']},
+                'python_over_c_abi': r['step_ms'] / r['abi_ms'],
+                'roofline': {'bound': 'hbm', 'kernel': 'warp_loss_ring_kernel<fused>', 'kernel_ms': r['fused_ms'],
+                             'algorithmic_bytes': r['fused_bytes'], 'achieved': r['fused_bytes'] / (r['fused_ms'] * 1e-3) / 1e9,
+                             'peak': peak, 'unit': 'GB/s', 'frac': frac(r['fused_bytes'], r['fused_ms']),
+                             'traffic': traffic(name, 'warp_loss_ring_kernel'),
+                             'note': '24 B/pixel moved by the fused sweep (16 read + 8 written); timed with its reduce kernel'},
+                'kernels': fused_kernels(r, peak)}
+
     c = CFG[HEADLINE]
-    achieved = head['bytes'] / (kern_ms * 1e-3) / 1e9
+    hl = encoder_line(HEADLINE, head)
+    ll = loss_line(HEADLINE, loss)
     line = {
-        'metric': 'encoded Mevents/s', 'value': world * head['events'] / (head_ms * 1e-3) / 1e6,
-        'unit': 'Mevents/s', 'n_gpus': world, 'steps': K, 'warmup': W, 'ms_per_step': head_ms,
-        'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
-        'data': 'synthetic',
-        'config': {'workload': f'{HEADLINE}: MVSEC-shaped 256x256 events, batch {c["B"]}/GPU, '
-                               f'{c["n"]} events/sample -> (B,4,256,256) event image; int64 SoA '
-                               'events (36 B/event) resident in HBM',
-                   'l2': '256 MiB memset between steps (outside the event pairs)',
-                   'validation': 'deferred (device status word, no host sync per call)',
-                   'parallelism': f'replicas x{world} (sharded by sample, no data-path collective)'},
+        'metric': 'encoded Mevents/s', 'value': hl['mevents_per_s'], 'unit': 'Mevents/s', 'n_gpus': world,
+        'steps': K, 'warmup': W, 'ms_per_step': head['step_ms'], 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': f'{HEADLINE}: {DESCR[HEADLINE]}; int64 SoA events (36 B/event) resident in HBM, per GPU',
+                   'l2': '256 MiB memset between steps (outside the event pairs); the input (5.8 GB) exceeds the 126 MB L2 anyway',
+                   'validation': 'deferred (status word in mapped pinned memory, no host sync per call)',
+                   'parallelism': f'replicas x{world} (sharded by sample, no data-path collective)',
+                   'path': hl['path']},
         'clocks': clocks,
-        'roofline': {'bound': 'hbm', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                     'frac': achieved / peak, 'traffic': TRAFFIC.get(HEADLINE), 'kernel': 'encode_vec4_kernel',
-                     'kernel_ms': kern_ms, 'algorithmic_bytes': head['bytes'], 'peak_source': peak_src},
-        'e2e': {'value': world * e2e['events'] / e2e_s / 1e6, 'unit': 'Mevents/s',
+        'roofline': dict(hl['roofline'], peak_source=peak_src, step_frac=hl['hbm_frac_step'],
+                         note='dominant kernel of the step; step_frac = SURVEY 8d bytes of the whole call '
+                              '(36 B/event + 16 B/cell) over the whole call'),
+        'roofline_pass2': hl.get('roofline_pass2'),
+        'warm_graph_ms_per_step': head['warm_graph_ms'],
+        'e2e': {'value': world * e2e['events'] / e2e_s / 1e6, 'unit': 'Mevents/s', 'steps': e2e_k,
                 'h2d_bytes_per_step': e2e['h2d'], 'd2h_bytes_per_step': e2e['d2h'],
                 'api': 'dv.quantize(events, timestamps, sample_idx, imsize) from pinned host tensors; '
                        'two streams, step k D2H overlaps step k+1 H2D',
@@ -658,15 +868,11 @@ def main():
                                          'h2d_bytes_per_step': e2e_c['h2d'], 'd2h_bytes_per_step': e2e_c['d2h'],
                                          'api': 'dv.compute_event_image_compact (int16/bool/fp32 storage form, 9 B/event)'}},
         'gpu_launches': K * head['launches_per_step'],
-        'warp_loss': {'metric': 'warp-loss fwd+bwd samples/s', 'value': world * loss['samples'] / (loss_ms * 1e-3),
-                      'unit': 'samples/s', 'ms_per_step': loss_ms, 'workload': f'{HEADLINE}: 4 scales, 256x256, B={c["B"]}',
-                      'roofline': {'bound': 'hbm', 'achieved': loss['bytes'] / (loss_ms * 1e-3) / 1e9,
-                                   'peak': peak, 'unit': 'GB/s', 'frac': loss['bytes'] / (loss_ms * 1e-3) / 1e9 / peak,
-                                   'note': 'whole training pass through the C ABI, device-resident inputs: dvsof_multiscale_loss_fused (one prelude launch: timestamp match + chained pyramid + border count; then the fused terms-and-gradient sweep, PDL-chained) + dvsof_scale_gradients; bytes = SURVEY 8d figure (separate fwd + bwd + pyramid)'},
-                      'python_api': {'value': world * loss['samples'] / (loss_py_ms * 1e-3), 'unit': 'samples/s',
-                                     'ms_per_step': loss_py_ms,
-                                     'note': 'training.combined_loss(...) + loss.backward() through torch.autograd (same kernels; host-bound: Python + autograd engine per step)'},
-                      'kernels': fused_kernels(loss, peak)},
+        'warp_loss': dict(ll, metric='warp-loss fwd+bwd samples/s', value=ll['samples_per_s'], unit='samples/s',
+                          note='value = the call train_flownet.py makes (Python API); c_abi = the same kernels '
+                               'driven from the C ABI alone: one prelude launch (timestamp match + chained pyramid + '
+                               'border count), the fused terms-and-gradient sweep (TMA-staged), its reduce kernel, '
+                               'and dvsof_scale_gradients, PDL-chained; bytes = SURVEY 8d (separate fwd + bwd + pyramid)'),
         'workloads': {},
     }
     if train is not None:
@@ -675,34 +881,26 @@ def main():
                               'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN convolutions; upsample+reflect-pad and ReLU+BatchNorm through libdvsof), 256x256, 131072 events/sample, '
                                           f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad, fused), '
                                           'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward',
+                              'dp_check': train.get('dp_check'),
                               'storage_form_feed': {'value': world * train['samples'] / (train['encoded_step_ms'] * 1e-3), 'unit': 'samples/s',
                                                     'ms_per_step': train['encoded_step_ms'],
                                                     'note': 'the same step fed with batches in the storage form of utils/dataset.py encode_batch (9 B/event, uint8 images) and dataset.decode_batch on the device: a quarter of the upload'}}
     for name, r in extra.items():
-        if name.endswith('_loss'):
-            line['workloads'][name] = {'samples_per_s': world * r['samples'] / (r['abi_ms'] * 1e-3),
-                                       'ms_per_step': r['abi_ms'],
-                                       'hbm_frac_step': r['bytes'] / (r['abi_ms'] * 1e-3) / 1e9 / peak,
-                                       'python_api_ms_per_step': r['step_ms'],
-                                       'kernels': fused_kernels(r, peak)}
-        else:
-            line['workloads'][name] = {'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6,
-                                       'ms_per_step': r['step_ms'], 'kernel_ms': r['kernel_ms'],
-                                       'hbm_gbs_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9,
-                                       'hbm_frac_kernel': r['bytes'] / (r['kernel_ms'] * 1e-3) / 1e9 / peak,
-                                       # the whole dvsof_encode_event_image call (prepare + the path the
-                                       # library picks: direct scatter, or bin + reduce for dense streams)
-                                       'hbm_frac_step': r['bytes'] / (r['step_ms'] * 1e-3) / 1e9 / peak,
-                                       'note': 'kernel_* = the direct scatter kernel alone; ms_per_step / '
-                                               'hbm_frac_step = the library call on the path it selects'}
+        line['workloads'][name] = loss_line(name[:4], r) if name.endswith('_loss') else encoder_line(name, r)
     if codec is not None:
-        line['workloads']['codec_' + HEADLINE] = {
+        line['workloads']['codec_cfg2'] = {
             'decode_mevents_per_s': codec['events'] / (codec['decode_ms'] * 1e-3) / 1e6, 'decode_ms': codec['decode_ms'],
-            'decode_hbm_frac': codec['bytes'] / (codec['decode_ms'] * 1e-3) / 1e9 / peak,
+            'decode_hbm_frac': frac(codec['bytes'], codec['decode_ms']),
             'encode_mevents_per_s': codec['events'] / (codec['encode_ms'] * 1e-3) / 1e6, 'encode_ms': codec['encode_ms'],
-            'encode_hbm_frac': codec['bytes'] / (codec['encode_ms'] * 1e-3) / 1e9 / peak,
+            'encode_hbm_frac': frac(codec['bytes'], codec['encode_ms']),
             'note': 'dvsof_decode_events / dvsof_encode_events (utils/dataset.py decode_batch / encode_batch, event part), 45 B/event, one GPU (rank 0)'}
-    line['cpu_baseline'] = cpu_baseline(HEADLINE) if world == 1 and not args.quick else None
+    if mapev is not None:
+        line['workloads']['map_events'] = mapev
+    if world == 1 and not args.quick:
+        line['cpu_baseline'] = cpu_baseline(HEADLINE)
+        line['warp_loss']['cpu_baseline'] = cpu_baseline_loss(HEADLINE)
+    else:
+        line['cpu_baseline'] = None
     emit(line)
     if world > 1:
         dist.destroy_process_group()

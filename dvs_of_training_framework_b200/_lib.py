@@ -47,6 +47,9 @@ _SIGNATURES = {
                                        C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_encode_scatter': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_int32, C.c_int32]
                              + [C.c_void_p] * 4),
+    'dvsof_encode_path': (C.c_int, [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_size_t]),
+    'dvsof_encode_binned_pass': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                           C.c_void_p, C.c_size_t, C.c_void_p, C.c_int32, C.c_void_p]),
     'dvsof_encode_event_image_compact': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p,
                                                     C.c_int64, C.c_int32, C.c_int32] + [C.c_void_p] * 4),
     'dvsof_count_image': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
@@ -163,56 +166,53 @@ def require_cuda(t, name, dtype=None):
 
 
 class Status:
-    """Device status word the kernels OR error bits into.
+    """Status word the kernels OR error bits into.  It lives in pinned HOST memory that the device
+    addresses directly (unified addressing: the device pointer of a pinned allocation is its host
+    pointer), so looking at it is a plain memory read -- no copy, no event, no CUDA call -- and a
+    kernel only touches it when it has an error to report.
 
     mode 'sync'     -- check right after the call (reference behaviour: AssertionError raised
-                       by the call itself; one host sync per call);
-    mode 'deferred' -- the word is copied to pinned host memory asynchronously after each call and
-                       looked at when that copy has LANDED (event query at the next call, never a
-                       wait), or at `flush(wait=True)` / `synchronize()`: no sync on the hot path,
-                       errors surface one or two calls late.
+                       by the call itself; one stream synchronisation per call);
+    mode 'deferred' -- nothing happens after a call; the word is looked at before the next call
+                       (`flush`: whatever finished kernels have reported by then) and at
+                       `flush(wait=True)` / `synchronize()`: no sync on the hot path, errors
+                       surface one or two calls late.
     """
     mode = 'sync'
 
     def __init__(self, device):
-        self.word = torch.zeros(1, dtype=torch.int32, device=device)
+        self.device = torch.device(device)
         self.host = torch.zeros(1, dtype=torch.int32).pin_memory()
-        self.event = torch.cuda.Event()
-        self.pending = False
+        self.word = self.host                        # what the kernels are handed (`_lib.ptr(st.word)`)
+        self._np = self.host.numpy()                 # plain memory view for the hot path
 
     def _raise(self, bits, exc):
         raise exc('; '.join(t for b, t in _ST_TEXT.items() if bits & b))
 
-    def check(self, exc=AssertionError):
-        bits = int(self.word.item()) & 0xffffffff
-        self.pending = False
+    def _look(self, exc):
+        bits = int(self._np[0]) & 0xffffffff
         if bits:
-            self.word.zero_()
+            torch.cuda.current_stream(self.device).synchronize()    # let every reporter finish first
+            bits = int(self._np[0]) & 0xffffffff
+            self._np[0] = 0
             self._raise(bits, exc)
+
+    def check(self, exc=AssertionError):
+        torch.cuda.current_stream(self.device).synchronize()
+        self._look(exc)
 
     def after_call(self, exc=AssertionError):
         if Status.mode == 'sync':
             self.check(exc)
-        else:
-            self.host.copy_(self.word, non_blocking=True)
-            self.event.record()
-            self.pending = True
 
     def flush(self, exc=AssertionError, wait=False):
-        if not self.pending:
-            return
         if wait:
-            self.event.synchronize()
-        elif not self.event.query():
-            return                                   # still in flight: look again at the next call
-        self.pending = False
-        bits = int(self.host[0]) & 0xffffffff
-        if bits:
-            self.word.zero_()
-            self._raise(bits, exc)
+            self.check(exc)
+        else:
+            self._look(exc)
 
     def synchronize(self, exc=AssertionError):
-        self.flush(exc, wait=True)
+        self.check(exc)
 
 
 _status = {}

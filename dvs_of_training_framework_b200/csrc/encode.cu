@@ -390,7 +390,8 @@ extern "C" int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const fl
     return encode_scatter_impl(a, (cudaStream_t)stream_, false);
 }
 
-static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream);
+static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream,
+                              int passes);
 
 extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, const float* t,
                                         const int64_t* p, const int64_t* b, int64_t n,
@@ -409,13 +410,14 @@ extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, cons
     if (int rc = launch_prepare(t, b, n, timestamps, B, H, W, out, workspace, !binned, stream)) return rc;
     if (n == 0) return DVSOF_OK;
     const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(workspace), (int)B, H, W, out, status};
-    if (binned) return encode_binned_impl(a, plan, workspace, stream);
+    if (binned) return encode_binned_impl(a, plan, workspace, stream, 3);
     static const bool no_pdl = getenv("DVSOF_NO_PDL") != nullptr;
     // scatter is released while prepare still runs; it blocks in griddepcontrol.wait
     return encode_scatter_impl(a, stream, !no_pdl);
 }
 
-static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream) {
+static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream,
+                              int passes) {
     char* ws = static_cast<char*>(workspace);
     const int64_t* ends = reinterpret_cast<const int64_t*>(ws + plan.off_ends);
     uint16_t* codes = reinterpret_cast<uint16_t*>(ws + plan.off_codes);
@@ -434,18 +436,47 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     }
     if (plan.max_chunks > INT32_MAX || (int64_t)a.B * plan.T > INT32_MAX)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_binned: grid too large");
-    if (int rc = launch_kernel("encode_bin_kernel", encode_bin_kernel, (int)plan.max_chunks, kBinThreads,
-                               kBinStageBytes, stream, true, a.x, a.y, a.t, a.p, a.b, a.n, ends, a.B, a.H,
-                               a.W, plan.r_log2, plan.T, codes, ts, table, a.status))
-        return rc;
+    if (passes & 1)
+        if (int rc = launch_kernel("encode_bin_kernel", encode_bin_kernel, (int)plan.max_chunks, kBinThreads,
+                                   kBinStageBytes, stream, passes == 3, a.x, a.y, a.t, a.p, a.b, a.n, ends, a.B, a.H,
+                                   a.W, plan.r_log2, plan.T, codes, ts, table, a.status))
+            return rc;
+    if (!(passes & 2)) return DVSOF_OK;
+    const bool chained = passes == 3;
     // runs hold ~kBinChunk / T records: one record per lane and batch when that is at most two warps' worth
     if (kBinChunk / plan.T <= 64)
         return launch_kernel("encode_reduce_kernel<1>", encode_reduce_kernel<1>, a.B * plan.T, kRedThreads,
-                             (size_t)plan.cells * 8, stream, true, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                             (size_t)plan.cells * 8, stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                              plan.r_log2, plan.T, a.out);
     return launch_kernel("encode_reduce_kernel", encode_reduce_kernel<kRedBatchLong>, a.B * plan.T, kRedThreads,
-                         (size_t)plan.cells * 8, stream, true, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                         (size_t)plan.cells * 8, stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                          plan.r_log2, plan.T, a.out);
+}
+
+// 1 when dvsof_encode_event_image takes the binned path for these sizes and this workspace, else 0
+extern "C" int dvsof_encode_path(int64_t n, int64_t B, int32_t H, int32_t W, size_t workspace_bytes) {
+    if (n <= 0 || B <= 0 || H <= 0 || W <= 0) return 0;
+    const BinPlan plan = make_bin_plan(n, B, H, W);
+    return use_binned(plan, n, B, H, W, workspace_bytes) ? 1 : 0;
+}
+
+// One pass of the binned path alone (kernel-level timing, bench.py): which = 1 the counting sort
+// of the event chunks into records, 2 the per-slab reduction of those records into the image.  The
+// per-sample bounds (dvsof_encode_prepare) and, for pass 2, the records of an earlier pass 1 must be
+// in `workspace`.  Fails when the sizes do not admit the binned path.
+extern "C" int dvsof_encode_binned_pass(const int64_t* x, const int64_t* y, const float* t,
+                                        const int64_t* p, const int64_t* b, int64_t n, int64_t B,
+                                        int32_t H, int32_t W, float* out, void* workspace,
+                                        size_t workspace_bytes, uint32_t* status, int32_t which,
+                                        void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    if (n <= 0 || !x || !y || !p || !t || !b || (which != 1 && which != 2))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_binned_pass: bad arguments");
+    const BinPlan plan = make_bin_plan(n, B, H, W);
+    if (!plan.ok || workspace_bytes < plan.total)
+        return fail(DVSOF_ERR_WORKSPACE, "encode_binned_pass: sizes / workspace do not admit the binned path");
+    const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(workspace), (int)B, H, W, out, status};
+    return encode_binned_impl(a, plan, workspace, (cudaStream_t)stream_, which);
 }
 
 extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const float* t,

@@ -39,11 +39,50 @@ def combined_loss(evaluator, flows, flow_ts, flow_sample_idx, images, timestamps
         loss, flat = evaluator.combined(flows, flow_ts, flow_sample_idx, images, timestamps,
                                         sample_idx, weights)
         S = flat.numel() // 3
-        parts = flat.unbind(0)
-        return loss, (tuple(parts[:S]), tuple(parts[S:2 * S]), tuple(parts[2 * S:]))
+        if flat.requires_grad:                      # generic path: autograd-connected scalars
+            parts = flat.unbind(0)
+            return loss, (tuple(parts[:S]), tuple(parts[S:2 * S]), tuple(parts[2 * S:]))
+        host = _HostTerms(flat)                     # logging values: fetched once, when first looked at
+        return loss, tuple(_TermGroup(host, k * S, (k + 1) * S) for k in range(3))
     terms = evaluator(flows, flow_ts, flow_sample_idx, images, timestamps, sample_idx)
     loss = sum(map(lambda v, w: w * mean(v), terms, weights))
     return loss, terms
+
+
+class _HostTerms:
+    """The 3*S detached terms of the fused pass, copied to the host in ONE transfer the first time
+    any of them is looked at (the reference's logging does 12 `.item()` calls = 12 syncs)."""
+
+    def __init__(self, flat):
+        self.flat, self._host = flat, None
+
+    def __getitem__(self, i):
+        if self._host is None:
+            self._host = self.flat.detach().cpu()
+        return self._host[i]
+
+
+class _TermGroup:
+    """One of (smoothness, photometric, outborder): a sequence of S 0-dim tensors, as the
+    reference's tuples, materialised on demand."""
+
+    def __init__(self, host, lo, hi):
+        self._h, self._lo, self._hi = host, lo, hi
+
+    def __len__(self):
+        return self._hi - self._lo
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return tuple(self[j] for j in range(*i.indices(len(self))))
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        return self._h[self._lo + i]
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
 
 
 def predictions2tag(predictions):

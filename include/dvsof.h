@@ -79,6 +79,17 @@ int dvsof_encode_scatter(const int64_t* x, const int64_t* y, const float* t,
                          const int64_t* polarity, const int64_t* sample_index, int64_t n_events,
                          int64_t n_samples, int32_t H, int32_t W, float* out,
                          const void* workspace, uint32_t* status, void* stream);
+/* Which path dvsof_encode_event_image takes for these sizes and this workspace: 0 = direct
+ * scatter (L2 atomics), 1 = binned (counting sort into records + per-slab reduction). */
+int dvsof_encode_path(int64_t n_events, int64_t n_samples, int32_t H, int32_t W, size_t workspace_bytes);
+/* One pass of the binned path alone (kernel-level timing): which = 1 the counting sort of the
+ * event chunks into 6-byte records, 2 the per-slab reduction of the records into the image.
+ * `workspace` must hold the per-sample bounds (dvsof_encode_prepare) and, for pass 2, the records
+ * of an earlier pass 1; DVSOF_ERR_WORKSPACE when the sizes do not admit the binned path. */
+int dvsof_encode_binned_pass(const int64_t* x, const int64_t* y, const float* t,
+                             const int64_t* polarity, const int64_t* sample_index, int64_t n_events,
+                             int64_t n_samples, int32_t H, int32_t W, float* out, void* workspace,
+                             size_t workspace_bytes, uint32_t* status, int32_t which, void* stream);
 
 /* Compact storage-form entry point: consumes the on-disk/encoded batch layout directly
  * (utils/dataset.py:286-289 encode_batch: x,y int16, polarity bool, timestamp fp32) plus
