@@ -17,7 +17,7 @@ import subprocess
 import sys
 from pathlib import Path
 
-UNIT = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9, 'Tbyte': 1e12}
+UNIT = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9, 'Tbyte': 1e12, 'ns': 1e-3, 'us': 1, 'ms': 1e3, 's': 1e6}
 
 
 def raw_rows(report):
@@ -45,7 +45,7 @@ def main():
                 return float(r[i].replace(',', '')) * UNIT.get(units[i], 1)
             rd, wr = val('dram__bytes_read.sum'), val('dram__bytes_write.sum')
             entry[name] = {'dram_bytes': rd + wr, 'dram_bytes_read': rd, 'dram_bytes_write': wr,
-                           'duration_us_under_ncu': float(r[col['gpu__time_duration.sum']].replace(',', '')),
+                           'duration_us_under_ncu': val('gpu__time_duration.sum'),
                            'grid': r[col['launch__grid_size']], 'source': str(report)}
     out_path.write_text(json.dumps(table, indent=1, sort_keys=True) + '\n')
     for w in table:
