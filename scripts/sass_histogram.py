@@ -56,7 +56,7 @@ def main():
         text += [f'{c:6d}  {o}' for o, c in root.most_common()]
         text += ['# full opcodes of interest:']
         text += [f'{c:6d}  {o}' for o, c in sorted(full.items())
-                 if re.match(r'(RED|ATOM|ATOMS|ATOMG|UBLKCP|UTMA|SYNCS|ACQBULK|MUFU|F(FMA|MUL|ADD)2|LDG|STG|LDS|STS|BAR|CCTL|MEMBAR)', o)]
+                 if re.match(r'(RED|REDG|ATOM|ATOMS|ATOMG|UBLKCP|UTMA|SYNCS|ACQBULK|MUFU|F(FMA|MUL|ADD)2|LDG|STG|LDS|STS|BAR|CCTL|MEMBAR)', o)]
         body = '\n'.join(text) + '\n'
         if a.out:
             short = re.sub(r'[^A-Za-z0-9_]+', '_', re.sub(r'\(.*', '', d).replace('dvsof::', '').replace('void ', ''))[:80]
