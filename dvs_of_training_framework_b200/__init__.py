@@ -8,6 +8,7 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
     transformation.map                                      <- utils/transformation (native ext)
     eval.flow_error_dense                                   <- utils/eval.py:6-50
     dataset.encode_batch / decode_batch (+ _info)          <- utils/dataset.py:201-373
+    dataset.collate_wrapper                                 <- utils/dataset.py:961-1020
 
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
 CPU fallback."""
@@ -18,12 +19,12 @@ from .data import (EventCrop, RandomRotation, augment_events, frame_generator, f
                    get_count_image, rotation_lut)
 from . import transformation  # noqa: F401
 from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
-from .dataset import (decode_batch, decode_batch_info, decode_events, decode_quantized_batch,  # noqa: F401
+from .dataset import (collate_wrapper, decode_batch, decode_batch_info, decode_events, decode_quantized_batch,  # noqa: F401
                       encode_batch, encode_batch_info, encode_quantized_batch, quantize_batch)
 
 __all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
            'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets', 'augment_events', 'rotation_lut',
            'transformation', 'flow_error_dense', 'flow_error_dense_device',
-           'encode_batch', 'decode_batch', 'encode_batch_info', 'decode_batch_info', 'decode_events',
+           'collate_wrapper', 'encode_batch', 'decode_batch', 'encode_batch_info', 'decode_batch_info', 'decode_events',
            'quantize_batch', 'encode_quantized_batch', 'decode_quantized_batch']

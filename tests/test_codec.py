@@ -280,3 +280,74 @@ def test_quantized_batch_codec_from_device_and_quantize_batch():
     assert torch.equal(q2['data'], q['data']) and q2['size'] == B
     host = dv.encode_quantized_batch(q2)
     assert host['data'].shape == (B * 4,) + tuple(dv.extend_size((H, W))) and host['data'].is_pinned()
+
+
+# ---- batch assembly: collate_wrapper (utils/dataset.py:961-1020), host code, runs without a GPU ----
+def _collate_samples(g, name):
+    n = int(g[f'{name}.n'])
+    out = []
+    for i in range(n):
+        ev = {k[len(f'{name}.in{i}.ev_'):]: g[k] for k in g.files if k.startswith(f'{name}.in{i}.ev_')}
+        aug = (i, g[f'{name}.in{i}.ts'].size - 1, 1, np.array([0, 0, 260, 346]), 0, np.array([False]))
+        out.append((ev, g[f'{name}.in{i}.ts'], g[f'{name}.in{i}.images'].astype(np.float32), aug))
+    return out
+
+
+@pytest.mark.parametrize('name', ['pair', 'mixed', 'with_empty'])
+def test_collate_wrapper_matches_reference(golden, name):
+    """The batch the reference's own collate_wrapper builds from the same per-sample tuples
+    (tests/golden/make_golden_collate.py; 'pair' is the batch of tests/dataset/test_dataset.py:260-297)."""
+    from dvs_of_training_framework_b200.dataset import collate_wrapper
+    g = np.load(golden / 'collate.npz')
+    batch = collate_wrapper(_collate_samples(g, name))
+    assert batch['size'] == int(g[f'{name}.n'])
+    assert set(batch['events']) == {'x', 'y', 'timestamp', 'polarity', 'element_index', 'sample_index'}
+    for k, v in batch['events'].items():
+        want = torch.tensor(g[f'{name}.ev_{k}'])
+        assert v.dtype == want.dtype and torch.equal(v, want), k
+    for k in ('timestamps', 'sample_idx'):
+        want = torch.tensor(g[f'{name}.{k}'])
+        assert batch[k].dtype == want.dtype and torch.equal(batch[k], want), k
+    assert batch['images'].dtype == torch.float32
+    assert torch.equal(batch['images'], torch.tensor(g[f'{name}.images_u8']).float())
+    for k, v in batch['augmentation_params'].items():
+        want = torch.tensor(g[f'{name}.aug_{k}'])
+        assert v.dtype == want.dtype and torch.equal(v, want), k
+
+
+@pytest.mark.parametrize('name', ['pair', 'mixed'])
+def test_collate_wrapper_encoded_equals_reference_encode_batch(golden, name):
+    """encoded=True == the reference's encode_batch of the reference's collated batch."""
+    from dvs_of_training_framework_b200.dataset import collate_wrapper
+    g = np.load(golden / 'collate.npz')
+    enc = collate_wrapper(_collate_samples(g, name), encoded=True)
+    for k, v in enc['events'].items():
+        want = torch.tensor(g[f'{name}.enc_ev_{k}'])
+        assert v.dtype == want.dtype and torch.equal(v, want), k
+    for k in ('elements_per_sample', 'timestamps'):
+        want = torch.tensor(g[f'{name}.enc_{k}'])
+        assert enc[k].dtype == want.dtype and torch.equal(enc[k], want), k
+    assert enc['images'].dtype == torch.uint8 and torch.equal(enc['images'], torch.tensor(g[f'{name}.images_u8']))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('name', ['pair', 'mixed'])
+def test_encoded_collate_through_device_prefetcher_equals_reference_batch(golden, name):
+    """Device-side batch assembly: the storage-form batch of
+    collate_wrapper(encoded=True) uploaded and widened on the device by training.DevicePrefetcher is
+    the batch the reference's collate_wrapper builds (int64 events with sample_index, float32 images)."""
+    from dvs_of_training_framework_b200 import training as tr
+    from dvs_of_training_framework_b200.dataset import collate_wrapper
+    g = np.load(golden / 'collate.npz')
+    enc = collate_wrapper(_collate_samples(g, name), encoded=True)
+    assert enc['events']['x'].is_pinned()
+    (dev_batch,) = list(tr.DevicePrefetcher([enc], 'cuda', True))
+    for k in ('x', 'y', 'timestamp', 'polarity', 'element_index', 'sample_index'):
+        want = torch.tensor(g[f'{name}.ev_{k}'])
+        got = dev_batch['events'][k]
+        assert got.is_cuda and got.dtype == want.dtype and torch.equal(got.cpu(), want), k
+    assert torch.equal(dev_batch['timestamps'].cpu(), torch.tensor(g[f'{name}.timestamps']))
+    assert torch.equal(dev_batch['sample_idx'].cpu(), torch.tensor(g[f'{name}.sample_idx']))
+    assert dev_batch['images'].dtype == torch.float32
+    assert torch.equal(dev_batch['images'].cpu(), torch.tensor(g[f'{name}.images_u8']).float())
+    assert dev_batch['global_size'] == int(g[f'{name}.n'])
