@@ -402,31 +402,20 @@ def fused_kernels(r, peak):
             'fwd_hbm_frac': frac(r['fwd_bytes'], r['fwd_ms']), 'bwd_hbm_frac': frac(r['bwd_bytes'], r['bwd_ms'])}
 
 
-def make_train_batch(B, H, W, n, T, seed):
-    """A collated batch (utils/dataset.py:961-1020 layout) in pinned host memory."""
-    ev, ts, sidx = fast_events(seed, B, H, W, n, T, 'cpu')
-    ev['element_index'] = torch.zeros_like(ev['x'])
+def make_train_samples(B, H, W, n, T, seed):
+    """B per-sample tuples (events dict, timestamps, images) as DatasetImpl.__getitem__ returns them
+    (utils/dataset.py:776-797): int64 x / y / polarity / element_index, float32 timestamp, two
+    grey frames -- the input of `collate_wrapper`."""
+    ev, ts, _ = fast_events(seed, B, H, W, n, T, 'cpu')
     g = torch.Generator().manual_seed(seed)
-    images = torch.randint(0, 256, (2 * B, 1, H, W), generator=g).float()
-    pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
-    return {'events': {k: pin(v) for k, v in ev.items()}, 'timestamps': pin(ts), 'sample_idx': pin(sidx),
-            'images': pin(images), 'augmentation_params': None, 'size': B}
-
-
-def encode_host_batch(batch):
-    """The storage form of a collated host batch (utils/dataset.py:240-305 `encode_batch`, what
-    scripts/prepare_batches.py writes and PreprocessedDataloader reads), in pinned memory."""
-    ev = batch['events']
-    B = int(batch['size'])
-    per = batch['timestamps'].numel() // B
-    pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
-    counts = torch.bincount(ev['sample_index'], minlength=B)           # one element per sample here
-    return {'events': {'x': pin(ev['x'].to(torch.int16)), 'y': pin(ev['y'].to(torch.int16)),
-                       'timestamp': pin(ev['timestamp']), 'polarity': pin(ev['polarity'] > 0),
-                       'events_per_element': pin(counts)},
-            'elements_per_sample': pin(torch.full((B,), per - 1, dtype=torch.uint8)),
-            'timestamps': pin(batch['timestamps']), 'images': pin(batch['images'].to(torch.uint8)),
-            'augmentation_params': None}
+    images = torch.randint(0, 256, (2 * B, H, W), generator=g, dtype=torch.uint8).numpy()
+    out = []
+    for b in range(B):
+        sl = slice(b * n, (b + 1) * n)
+        events = {'x': ev['x'][sl].numpy(), 'y': ev['y'][sl].numpy(), 'timestamp': ev['timestamp'][sl].numpy(),
+                  'polarity': ev['polarity'][sl].numpy(), 'element_index': np.zeros(n, dtype=np.int64)}
+        out.append((events, ts[2 * b:2 * b + 2].numpy().astype(np.float64), images[2 * b:2 * b + 2].astype(np.float32)))
+    return out
 
 
 def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
@@ -450,9 +439,11 @@ def bench_train_step(K, W, dev, world, per_gpu=32, encoded=False):
     # gradient views carry the parameters' strides, training.GradientAllreducer)
     opt = torch.optim.AdamW(model.parameters(), lr=1e-5, amsgrad=True, fused=True)
     evaluator = dv.init_losses((c['H'], c['W']), per_gpu, model, dev, 1)
-    batch = make_train_batch(per_gpu, c['H'], c['W'], c['n'], c['T'], 1234 + 5 + rank)
-    if encoded:             # 9 B/event + uint8 images cross PCIe, dataset.decode_batch expands on device
-        batch = encode_host_batch(batch)
+    # the batch as the loader's collate_fn hands it over: dv.collate_wrapper of per-sample tuples, in the
+    # reference's int64 layout (36 B/event + float32 images) or, encoded=True, assembled directly in the
+    # storage form (9 B/event + uint8 images; widened by dataset.decode_batch on the device)
+    batch = dv.collate_wrapper(make_train_samples(per_gpu, c['H'], c['W'], c['n'], c['T'], 1234 + 5 + rank),
+                               encoded=encoded)
     timers = dv.timer.FakeTimer()
     model.train()
     # every step uploads its batch from pinned host memory; the upload of step k+1 runs on a copy
@@ -876,15 +867,16 @@ def main():
         'workloads': {},
     }
     if train is not None:
-        line['train_step'] = {'metric': 'train-step samples/s', 'value': world * train['samples'] / (train['step_ms'] * 1e-3),
-                              'unit': 'samples/s', 'ms_per_step': train['step_ms'],
+        line['train_step'] = {'metric': 'train-step samples/s', 'value': world * train['samples'] / (train['encoded_step_ms'] * 1e-3),
+                              'unit': 'samples/s', 'ms_per_step': train['encoded_step_ms'],
                               'workload': f'EV-FlowNet ({train["params"]} params, fp32/TF32 cuDNN convolutions; upsample+reflect-pad and ReLU+BatchNorm through libdvsof), 256x256, 131072 events/sample, '
-                                          f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad, fused), '
-                                          'H2D of every batch from pinned memory, prefetched one step ahead on a copy stream; flat-bucket NCCL allreduce overlapped with backward',
+                                          f'{train["samples"]} samples/GPU (global {world * train["samples"]}), AdamW(amsgrad, fused); every batch comes from '
+                                          'dv.collate_wrapper(samples, encoded=True) in pinned memory (9 B/event, uint8 frames), is uploaded one step ahead on a copy '
+                                          'stream and widened on the device (training.DevicePrefetcher); flat-bucket NCCL allreduce overlapped with backward',
                               'dp_check': train.get('dp_check'),
-                              'storage_form_feed': {'value': world * train['samples'] / (train['encoded_step_ms'] * 1e-3), 'unit': 'samples/s',
-                                                    'ms_per_step': train['encoded_step_ms'],
-                                                    'note': 'the same step fed with batches in the storage form of utils/dataset.py encode_batch (9 B/event, uint8 images) and dataset.decode_batch on the device: a quarter of the upload'}}
+                              'int64_feed': {'value': world * train['samples'] / (train['step_ms'] * 1e-3), 'unit': 'samples/s',
+                                             'ms_per_step': train['step_ms'],
+                                             'note': 'the same step fed with dv.collate_wrapper(samples) in the reference layout (int64 events, 36 B/event, float32 frames): four times the upload'}}
     for name, r in extra.items():
         line['workloads'][name] = loss_line(name[:4], r) if name.endswith('_loss') else encoder_line(name, r)
     if codec is not None:

@@ -9,6 +9,8 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
     eval.flow_error_dense                                   <- utils/eval.py:6-50
     dataset.encode_batch / decode_batch (+ _info)          <- utils/dataset.py:201-373
     dataset.collate_wrapper                                 <- utils/dataset.py:961-1020
+    preprocessed.PreprocessedDataloader / select_*_ranges /
+         join_batches / read_encoded_batch                  <- utils/dataset.py:19-198,400-425,505-549,799-954
 
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
 CPU fallback."""
@@ -18,6 +20,8 @@ from .loss import Loss, Losses, charbonier_loss, init_losses, interpolate  # noq
 from .data import (EventCrop, RandomRotation, augment_events, frame_generator, frame_offsets,  # noqa: F401
                    get_count_image, rotation_lut)
 from . import transformation  # noqa: F401
+from . import preprocessed  # noqa: F401
+from .preprocessed import PreprocessedDataloader, join_batches, select_encoded_ranges  # noqa: F401
 from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
 from .dataset import (collate_wrapper, decode_batch, decode_batch_info, decode_events, decode_quantized_batch,  # noqa: F401
                       encode_batch, encode_batch_info, encode_quantized_batch, quantize_batch)
