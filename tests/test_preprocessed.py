@@ -181,3 +181,44 @@ def test_loader_on_device_returns_the_decoded_training_batch(tmp_path):
     for k in ev:
         assert torch.equal(staged['events'][k], ev[k]), k
     assert torch.equal(staged['images'], got['images'])
+
+
+def test_dataloader_factories_keep_the_reference_wiring(tmp_path, golden):
+    """utils/dataloader.py:31-108: parameter objects, the preprocessed branch (positioned with
+    set_index) and the DataLoader branch with this package's collate_wrapper as collate_fn."""
+    from pathlib import Path
+    from types import SimpleNamespace
+    from dvs_of_training_framework_b200 import dataloader as dl
+    from dvs_of_training_framework_b200.dataset import collate_wrapper
+    args = SimpleNamespace(shape=[256, 256], mbs=2, num_workers=0, min_sequence_length=1, max_sequence_length=1,
+                           dynamic_sample_length=False, data_path=Path('/data'), cl=6, is_raw=True, cache_size=0)
+    tp, vp = dl.get_trainset_params(args), dl.get_valset_params(args)
+    assert tp.path == Path('/data/outdoor_day2') and tp.augmentation and tp.infinite and tp.shuffle
+    assert tp.collate_fn is collate_wrapper and tp.preprocessed_dataset_path is None and tp.collapse_length == 6
+    assert vp.path == Path('/data/outdoor_day1') and not vp.augmentation and not vp.infinite and vp.collapse_length == 1
+    assert dl.choose_collate_function(False) is None
+    assert dl.get_trainset_params(args, encoded=True).collate_fn.keywords == {'encoded': True}
+    # preprocessed branch
+    _write(tmp_path, _fixture_parts())
+    tp.preprocessed_dataset_path, tp.cache_dir = tmp_path, None
+    ld = dl.get_dataloader(tp, sample_idx=2, opener=_opener, suffix='.npz')
+    assert isinstance(ld, pp.PreprocessedDataloader) and ld.batch_size == 2
+    assert next(ld)['events']['x'].tolist()[:3] == [4, 6, 7]           # starts at sample 2, wraps to sample 0
+    # DataLoader branch over a map-style dataset of reference-shaped samples
+    g = np.load(golden / 'collate.npz')
+
+    class TwoSamples(torch.utils.data.Dataset):
+        def __init__(self, **kw):
+            self.kw = kw
+
+        def __len__(self):
+            return 2
+
+        def __getitem__(self, i):
+            ev = {k[len(f'pair.in{i}.ev_'):]: g[k] for k in g.files if k.startswith(f'pair.in{i}.ev_')}
+            return ev, g[f'pair.in{i}.ts'], g[f'pair.in{i}.images'].astype(np.float32), \
+                (i, 1, 1, np.array([0, 0, 260, 346]), 0, np.array([False]))
+    vp.pin_memory = False
+    batch = next(iter(dl.get_dataloader(vp, dataset_classes=(TwoSamples, None))))
+    assert batch['size'] == 2 and torch.equal(batch['events']['sample_index'], torch.tensor(g['pair.ev_sample_index']))
+    assert torch.equal(batch['events']['x'], torch.tensor(g['pair.ev_x']))
