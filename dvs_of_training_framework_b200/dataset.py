@@ -234,9 +234,10 @@ def collate_wrapper(batch, encoded=False):
     n_samples = len(batch)
     counts = [int(sample[0]['x'].size) for sample in batch]
     total = sum(counts)
-    timestamps = torch.tensor(np.hstack([np.asarray(s[1]) for s in batch]), dtype=torch.float32)
+    pin = (lambda t: t.pin_memory()) if torch.cuda.is_available() else (lambda t: t)
+    timestamps = pin(torch.tensor(np.hstack([np.asarray(s[1]) for s in batch]), dtype=torch.float32))
     frames = [np.asarray(s[1]).size for s in batch]
-    sample_idx = torch.tensor(np.repeat(np.arange(n_samples), frames), dtype=torch.long)
+    sample_idx = pin(torch.tensor(np.repeat(np.arange(n_samples), frames), dtype=torch.long))
     images_np = np.vstack([s[2] for s in batch])
     aug = _augmentation_info(batch)
     if not encoded:
@@ -279,6 +280,6 @@ def collate_wrapper(batch, encoded=False):
     images = _pinned((images_np.shape[0], 1) + images_np.shape[1:], torch.uint8)
     images.numpy()[:, 0] = images_np                                              # images.to(torch.uint8), :235
     return {'events': {'x': x, 'y': y, 'timestamp': t, 'polarity': p,
-                       'events_per_element': torch.tensor(epe, dtype=torch.int64)},
-            'timestamps': timestamps, 'elements_per_sample': torch.tensor(elements, dtype=torch.uint8),
+                       'events_per_element': pin(torch.tensor(epe, dtype=torch.int64))},
+            'timestamps': timestamps, 'elements_per_sample': pin(torch.tensor(elements, dtype=torch.uint8)),
             'images': images, 'augmentation_params': aug}
