@@ -152,11 +152,41 @@ def ptr(t):
     return C.c_void_p(t.data_ptr()) if t is not None and t.numel() else C.c_void_p(0)
 
 
+def _index(device):
+    i = device.index if isinstance(device, torch.device) else torch.device(device).index
+    return torch.cuda.current_device() if i is None else i
+
+
+def raw_stream(device):
+    """The current stream of `device` as an integer handle (torch.cuda.current_stream(...).cuda_stream
+    without building the Stream object: ~0.3 us instead of ~10 us on the hot path)."""
+    return torch._C._cuda_getCurrentRawStream(_index(device))
+
+
 def stream_ptr(device):
-    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    return C.c_void_p(raw_stream(device))
+
+
+class on_device:
+    """`with torch.cuda.device(dev)` that does nothing when `dev` already is the current device."""
+    __slots__ = ('idx', 'ctx')
+
+    def __init__(self, device):
+        self.idx, self.ctx = _index(device), None
+
+    def __enter__(self):
+        if torch.cuda.current_device() != self.idx:
+            self.ctx = torch.cuda.device(self.idx)
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
 
 
 def require_cuda(t, name, dtype=None):
+    if isinstance(t, torch.Tensor) and t.is_cuda and (dtype is None or t.dtype is dtype) and t.is_contiguous():
+        return t                                                  # the hot path
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise RuntimeError(f'{name}: expected a CUDA tensor (libdvsof has no CPU path), got '
                            f'{type(t).__name__}{"" if not isinstance(t, torch.Tensor) else " on " + str(t.device)}')

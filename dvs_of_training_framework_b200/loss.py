@@ -93,7 +93,7 @@ class _WarpLoss(torch.autograd.Function):
         levels, flows = tensors[:n_scales], tensors[n_scales:]
         dev = flows[0].device
         P = flows[0].shape[0]
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             sc = _scale_struct(flows, levels)
             lib = _lib.load()
             ws = torch.empty(lib.dvsof_loss_workspace_bytes(sc), dtype=torch.uint8, device=dev)
@@ -178,19 +178,25 @@ class _FusedTrainingLoss(torch.autograd.Function):
         D, _, H, W = images.shape
         plan = owner._plan(dev, flows[0].shape[0], D, H, W, flows)
         S, o = plan.S, plan.offs
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
-            gbuf = torch.empty(plan.gtotal, dtype=torch.float32, device=dev)
+            # one gradient tensor per scale, straight from the caching allocator (an empty() costs a
+            # third of a view of a shared buffer)
+            grads = [torch.empty_like(f) for f in flows]
             base = buf.data_ptr()
-            plan.fill(plan.bwd, base, flows, gbuf.data_ptr())
+            sc = plan.bwd
+            for s in range(S):
+                sc.flow[s] = flows[s].data_ptr()
+                sc.images[s] = base + 4 * o[s]
+                sc.grad_flow[s] = grads[s].data_ptr()
             fr = _fill_frames(plan, images, flow_ts, flow_sample_idx, timestamps, sample_idx)
             st = _lib.status_for(dev)
             st.flush()
-            _lib.call('dvsof_multiscale_loss_fused', plan.bwd, fr, coef, base + 4 * o[S],
+            _lib.call('dvsof_multiscale_loss_fused', sc, fr, coef, base + 4 * o[S],
                       base + 4 * o[S + 2], base + 4 * o[S + 3], base + 4 * o[S + 1], plan.ws_ptr,
                       _lib.ptr(st.word), _lib.stream_ptr(dev))
             st.after_call()                                              # loss.py:193 asserts
-        ctx.plan, ctx.gbuf, ctx.buf, ctx.shapes = plan, gbuf, buf, [f.shape for f in flows]
+        ctx.plan, ctx.grads, ctx.buf = plan, grads, buf
         loss = buf[o[S + 3]:o[S + 3] + 1].view(())
         terms = buf[o[S + 2]:o[S + 2] + 3 * S]
         ctx.mark_non_differentiable(terms)
@@ -198,20 +204,19 @@ class _FusedTrainingLoss(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_loss, _grad_terms):
-        plan, gbuf = ctx.plan, ctx.gbuf
-        if gbuf is None:
+        plan, grads = ctx.plan, ctx.grads
+        if grads is None:
             raise RuntimeError('the fused training loss stores its gradient once: a second backward '
                                '(retain_graph) needs Losses.__call__ / Losses.terms')
-        dev = gbuf.device
+        dev = grads[0].device
         grad_loss = _f32(grad_loss, 'grad_loss')
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             sc = plan.bwd       # only the gradient pointers are read by the rescale
             for s in range(plan.S):
-                sc.grad_flow[s] = gbuf.data_ptr() + 4 * plan.goffs[s]
+                sc.grad_flow[s] = grads[s].data_ptr()
             _lib.call('dvsof_scale_gradients', sc, _lib.ptr(grad_loss), _lib.stream_ptr(dev))
-        grads = tuple(gbuf[g:g + n].view(shp) for g, n, shp in zip(plan.goffs, plan.gsizes, ctx.shapes))
-        ctx.gbuf = ctx.buf = None
-        return (None,) * 7 + grads
+        ctx.grads = ctx.buf = None
+        return (None,) * 7 + tuple(grads)
 
 
 class _MultiscaleLoss(torch.autograd.Function):
@@ -224,7 +229,7 @@ class _MultiscaleLoss(torch.autograd.Function):
         D, _, H, W = images.shape
         plan = owner._plan(dev, flows[0].shape[0], D, H, W, flows)
         S = plan.S
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             # one allocation per call: what backward needs (levels, match_idx, n_bad) cannot live
             # in a buffer shared between calls
             buf = torch.empty(plan.total, dtype=torch.float32, device=dev)
@@ -247,7 +252,7 @@ class _MultiscaleLoss(torch.autograd.Function):
         buf, flows = ctx.saved_tensors[0], ctx.saved_tensors[1:]
         dev, S, o = buf.device, plan.S, plan.offs
         grad_terms = grad_terms.contiguous()
-        with torch.cuda.device(dev):
+        with _lib.on_device(dev):
             gbuf = torch.empty(plan.gtotal, dtype=torch.float32, device=dev)
             base = buf.data_ptr()
             plan.fill(plan.bwd, base, flows, gbuf.data_ptr())
@@ -315,7 +320,7 @@ class Losses:
         shapes = tuple((f.shape[-2], f.shape[-1]) for f in flows)
         # the plan owns the reduction workspace (tile records, tickets, per-tile counts): one per
         # stream, or two calls with equal shapes on different streams would share the tickets
-        key = (dev, torch.cuda.current_stream(dev).cuda_stream, P, D, H, W, shapes)
+        key = (dev, _lib.raw_stream(dev), P, D, H, W, shapes)
         plan = self._plans.get(key)
         if plan is None:
             plan = self._plans[key] = _Plan(dev, P, D, H, W, shapes)
