@@ -72,8 +72,10 @@ def decode_batch_info(encoded_batch_info):
     timestamps = encoded_batch_info['timestamps']
     eps = encoded_batch_info['elements_per_sample']
     batch_size = eps.numel()
+    # :322-324; a sample with e elements has e + 1 frames, so the length is known from `timestamps`
+    # (without output_size= the op reads it back from the device: a host sync per batch)
     sample_idx = torch.repeat_interleave(torch.arange(batch_size, dtype=torch.int64, device=eps.device),
-                                         eps.to(torch.int64) + 1)                 # :322-324
+                                         eps.to(torch.int64) + 1, output_size=timestamps.numel())
     return {'timestamps': timestamps.to(torch.float32),
             'sample_idx': sample_idx,
             'images': encoded_batch_info['images'].to(torch.float32),

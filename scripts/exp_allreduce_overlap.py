@@ -47,6 +47,12 @@ def main():
         step()
     torch.cuda.synchronize()
     dist.barrier()
+    import time
+    t0 = time.perf_counter()
+    for _ in range(10):
+        step()
+    torch.cuda.synchronize()
+    step_ms = (time.perf_counter() - t0) * 100
     from torch.profiler import ProfilerActivity, profile
     with profile(activities=[ProfilerActivity.CUDA]) as prof:
         for _ in range(4):
@@ -68,10 +74,10 @@ def main():
         tot = sum(b - a for a, b in nccl)
         ov = sum(covered(a, b) for a, b in nccl)
         span = (max(b for _, b in comp) - min(a for a, _ in comp)) if comp else 0
-        out = {'world': world, 'steps_profiled': 4, 'nccl_kernels': len(nccl), 'nccl_kernel_us_total': tot,
+        out = {'world': world, 'step_ms_unprofiled': step_ms, 'steps_profiled': 4, 'nccl_kernels': len(nccl), 'nccl_kernel_us_total': tot,
                'nccl_us_overlapped_by_compute_kernels': ov, 'overlap_fraction': ov / tot if tot else None,
                'compute_span_us': span, 'compute_busy_us': sum(b - a for a, b in merged),
-               'top_kernels_us': sorted(((e.name[:60], round(e.device_time_total)) for e in prof.key_averages()
+               'top_kernels_us': sorted(((e.key[:60], round(e.device_time_total)) for e in prof.key_averages()
                                         if e.device_time_total > 0), key=lambda kv: -kv[1])[:12]}
         print(json.dumps(out))
     dist.destroy_process_group()
