@@ -430,7 +430,7 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(encode_reduce_kernel<kRedBatchLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(encode_reduce_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
+            e = cudaFuncSetAttribute(encode_reduce_kernel<kRedBatchShort>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_binned smem attr: %s", cudaGetErrorString(e));
         device_setup_done(configured, dev);
     }
@@ -445,7 +445,7 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     const bool chained = passes == 3;
     // runs hold ~kBinChunk / T records: one record per lane and batch when that is at most two warps' worth
     if (kBinChunk / plan.T <= 64)
-        return launch_kernel("encode_reduce_kernel<1>", encode_reduce_kernel<1>, a.B * plan.T, kRedThreads,
+        return launch_kernel("encode_reduce_kernel<short>", encode_reduce_kernel<kRedBatchShort>, a.B * plan.T, kRedThreads,
                              (size_t)plan.cells * 8, stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                              plan.r_log2, plan.T, a.out);
     return launch_kernel("encode_reduce_kernel", encode_reduce_kernel<kRedBatchLong>, a.B * plan.T, kRedThreads,

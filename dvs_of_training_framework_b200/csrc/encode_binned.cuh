@@ -42,9 +42,13 @@ namespace dvsof {
 constexpr int kBinChunk = DVSOF_BIN_CHUNK;       // events per pass-1 chunk
 constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread, DVSOF_BIN_INFLIGHT at a time
 #ifndef DVSOF_RED_BATCH
-#define DVSOF_RED_BATCH 4
+#define DVSOF_RED_BATCH 5
 #endif
 constexpr int kRedBatchLong = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
+#ifndef DVSOF_RED_BATCH_SHORT
+#define DVSOF_RED_BATCH_SHORT -1
+#endif
+constexpr int kRedBatchShort = DVSOF_RED_BATCH_SHORT;   // the same for short runs (wide images); 0 = four runs per warp at a time, -1 = the lean loop (default); the long-run batch: -k = the lean loop with k records per lane and run
 constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
 constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
 #ifndef DVSOF_RED_THREADS
@@ -261,7 +265,18 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
     const int R = 1 << r_log2, cells = R * W * 2;
     unsigned* cnt = slab;
     int* key = reinterpret_cast<int*>(slab + cells);
-    for (int i = threadIdx.x; i < cells; i += kRedThreads) { cnt[i] = 0u; key[i] = INT_MIN; }
+    {   // cells is a multiple of 4 (W * 2 * R with W % 2 == 0 ... checked: falls back to scalar stores otherwise)
+        if ((cells & 3) == 0) {
+            uint4* c4 = reinterpret_cast<uint4*>(cnt);
+            int4* k4 = reinterpret_cast<int4*>(key);
+            for (int i = threadIdx.x; i < cells / 4; i += kRedThreads) {
+                c4[i] = make_uint4(0u, 0u, 0u, 0u);
+                k4[i] = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
+            }
+        } else {
+            for (int i = threadIdx.x; i < cells; i += kRedThreads) { cnt[i] = 0u; key[i] = INT_MIN; }
+        }
+    }
     chunk_prefix<kRedThreads>(ends, n_samples, prefix);   // ends with __syncthreads()
     const int cb = prefix[s], nc = prefix[s + 1] - prefix[s];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -272,8 +287,111 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
     // 32 chunks, and the batch after the current one is requested before the current one is
     // applied.  Everything that steers the loop is warp-uniform.
     constexpr int kWarps = kRedThreads / 32;
-    constexpr unsigned kStep = 32 * kRedBatch;
+    constexpr unsigned kStep = 32 * (kRedBatch > 0 ? kRedBatch : 1);
     const int my_n = nc > warp ? (nc - warp + kWarps - 1) / kWarps : 0;
+    if constexpr (kRedBatch < 0) {
+        // Short runs, the lean way: no software pipelining at all -- 16 warps x 4 CTAs per SM are
+        // enough loads in flight, and a run of ~34 records costs ~30 instructions instead of ~100.
+        for (int k0 = 0; k0 < my_n; k0 += 32) {
+            unsigned lo = 0, hi = 0;
+            if (k0 + lane < my_n) {
+                const uint32_t* row = table + (size_t)(cb + (k0 + lane) * kWarps + warp) * (T + 1) + tile;
+                lo = __ldg(row); hi = __ldg(row + 1);
+            }
+            const int m = min(32, my_n - k0);
+            const uint16_t* cg = codes_g + (size_t)(cb + k0 * kWarps + warp) * kBinChunk;
+            const float* tg = ts_g + (size_t)(cb + k0 * kWarps + warp) * kBinChunk;
+            constexpr size_t kStride = (size_t)kWarps * kBinChunk;       // records between two chunks of a warp
+            auto apply = [&](unsigned c, float t) {
+                if (c != 0xffffffffu) {
+                    atomicAdd(&cnt[c], 1u);                      // scatter_sum, net.py:147-148
+                    atomicMax(&key[c], ordered_key(t));          // scatter_max of the raw t, net.py:149
+                }
+            };
+            // kLR runs x kLP records per lane in flight (short runs: 2 x 2 = 64 records cover 34 +- 6;
+            // long runs of ~128: 2 x 5)
+            constexpr int kLR = 2, kLP = kRedBatch == -1 ? 2 : -kRedBatch;
+            for (int j = 0; j < m; j += kLR) {
+                unsigned ra[kLR], rb[kLR];
+#pragma unroll
+                for (int q = 0; q < kLR; ++q) {
+                    ra[q] = __shfl_sync(0xffffffffu, lo, (j + q) & 31);
+                    rb[q] = __shfl_sync(0xffffffffu, hi, (j + q) & 31);
+                    if (j + q >= m) rb[q] = ra[q];
+                }
+                const uint16_t* c0 = cg + j * kStride;
+                const float* t0 = tg + j * kStride;
+                unsigned code[kLR * kLP];
+                float tv[kLR * kLP];
+#pragma unroll
+                for (int q = 0; q < kLR; ++q)
+#pragma unroll
+                    for (int u = 0; u < kLP; ++u) {
+                        const unsigned i = ra[q] + u * 32 + lane;
+                        code[q * kLP + u] = 0xffffffffu;
+                        if (i < rb[q]) {
+                            code[q * kLP + u] = __ldcs(c0 + q * kStride + i);
+                            tv[q * kLP + u] = __ldcs(t0 + q * kStride + i);
+                        }
+                    }
+#pragma unroll
+                for (int u = 0; u < kLR * kLP; ++u) apply(code[u], tv[u]);
+#pragma unroll
+                for (int q = 0; q < kLR; ++q)                      // rare: a run longer than 32 kLP records
+                    for (unsigned i = ra[q] + 32 * kLP + lane; __any_sync(0xffffffffu, i < rb[q]); i += 32)
+                        if (i < rb[q]) apply(__ldcs(c0 + q * kStride + i), __ldcs(t0 + q * kStride + i));
+            }
+        }
+    } else if constexpr (kRedBatch == 0) {
+        // Short runs (wide images: kBinChunk / T ~ 34 records): FOUR runs per warp at a time, 8 lanes
+        // and up to kGT records per lane each, the next four requested before the current ones are
+        // applied.  A slab's CTA is a chain of DRAM round trips (table entry -> records -> atomics);
+        // with one run in flight per warp it was 16-32 of them per warp (82 us for cfg4's 1920 slabs).
+        constexpr int kGT = 6, kG = 4;                        // 48 records cover a run of 34 +- 6
+        const int grp = lane >> 3, sub = lane & 7;
+        for (int k0 = 0; k0 < my_n; k0 += 32) {
+            unsigned lo = 0, hi = 0;
+            if (k0 + lane < my_n) {
+                const uint32_t* row = table + (size_t)(cb + (k0 + lane) * kWarps + warp) * (T + 1) + tile;
+                lo = __ldg(row); hi = __ldg(row + 1);
+            }
+            const int m = min(32, my_n - k0);
+            unsigned a = 0, b = 0, na = 0, nb = 0;             // record range of this group's run (current / next)
+            size_t base = 0, nbase = 0;
+            auto fetch = [&](int j0, unsigned& ra, unsigned& rb, size_t& rbase, unsigned* code, float* tv) {
+                const int j = j0 + grp;
+                ra = __shfl_sync(0xffffffffu, lo, j & 31);
+                rb = __shfl_sync(0xffffffffu, hi, j & 31);
+                if (j >= m) rb = ra;
+                rbase = (size_t)(cb + (k0 + j) * kWarps + warp) * kBinChunk;
+#pragma unroll
+                for (int u = 0; u < kGT; ++u) {
+                    const unsigned i = ra + u * 8 + sub;
+                    code[u] = 0xffffffffu;
+                    if (i < rb) { code[u] = __ldcs(codes_g + rbase + i); tv[u] = __ldcs(ts_g + rbase + i); }
+                }
+            };
+            auto apply = [&](unsigned c, float t) {
+                if (c != 0xffffffffu) {
+                    atomicAdd(&cnt[c], 1u);                      // scatter_sum, net.py:147-148
+                    atomicMax(&key[c], ordered_key(t));          // scatter_max of the raw t, net.py:149
+                }
+            };
+            unsigned code[kGT], ncode[kGT];
+            float tv[kGT], ntv[kGT];
+            fetch(0, a, b, base, code, tv);
+            for (int j0 = 0; j0 < m; j0 += kG) {
+                if (j0 + kG < m) fetch(j0 + kG, na, nb, nbase, ncode, ntv);
+#pragma unroll
+                for (int u = 0; u < kGT; ++u) apply(code[u], tv[u]);
+                for (unsigned i = a + kGT * 8 + sub; __any_sync(0xffffffffu, i < b); i += 8)   // rare: a run above 48 records
+                    if (i < b) apply(__ldcs(codes_g + base + i), __ldcs(ts_g + base + i));
+#pragma unroll
+                for (int u = 0; u < kGT; ++u) { code[u] = ncode[u]; tv[u] = ntv[u]; }
+                a = na; b = nb; base = nbase;
+            }
+        }
+    } else {
     for (int k0 = 0; k0 < my_n; k0 += 32) {
         unsigned lo = 0, hi = 0;
         if (k0 + lane < my_n) {
@@ -313,15 +431,17 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
             }
         }
     }
+    }
     __syncthreads();
     const float2 nd = sd[s];
     const int y0 = tile << r_log2;
     const size_t plane = (size_t)H * W;
     float* o = out + (size_t)s * 4 * plane;
-    for (int i = threadIdx.x; i < R * W; i += kRedThreads) {
-        const int row = i / W, xx = i - row * W, yy = y0 + row;
-        if (yy >= H) break;
-        const size_t px = (size_t)yy * W + xx;
+    // the slab's rows are whole image rows: its pixels are contiguous in every output plane
+    const int n_px = min(R, H - y0) * W;
+    float* o0 = o + (size_t)y0 * W;
+    for (int i = threadIdx.x; i < n_px; i += kRedThreads) {
+        const size_t px = (size_t)i;
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
             const int k = key[2 * i + c];
@@ -330,8 +450,8 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
                 tn = __fdiv_rn(__fsub_rn(key_to_float(k), nd.x), nd.y);          // net.py:141
                 if (__float_as_int(tn) <= 0) tn = 0.f;                           // max against the zero plane
             }
-            o[c * plane + px] = (float)cnt[2 * i + c];
-            o[(c + 2) * plane + px] = tn;
+            o0[c * plane + px] = (float)cnt[2 * i + c];
+            o0[(c + 2) * plane + px] = tn;
         }
     }
 }
