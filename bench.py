@@ -297,6 +297,35 @@ def bench_encoder(name, K, W, dev, seed_off=0, contended=False):
                 launches_per_step=3 if binned else 2, cells=B * 4 * He * We, contended=contended)
 
 
+def bench_encoder_compact(name, K, W, dev):
+    """The storage-form entry (utils/dataset.py:286-289: x, y int16, polarity bool, t fp32 = 9 B/event)
+    through the C ABI on workload `name`; its own roofline: 9 N + 8 (B + 1) + 16 B H' W' bytes."""
+    import dvs_of_training_framework_b200 as dv
+    L = dv._lib
+    c = CFG[name]
+    B, H, Wd, n = c['B'], c['H'], c['W'], c['n']
+    He, We = dv.extend_size((H, Wd))
+    ev, ts, _ = fast_events(1234 + int(name[3:]), B, H, Wd, n, c['T'], dev)
+    N = B * n
+    x, y = ev['x'].to(torch.int16), ev['y'].to(torch.int16)
+    p, t = (ev['polarity'] > 0).view(torch.uint8), ev['timestamp']
+    begin = torch.arange(B + 1, device=dev, dtype=torch.int64) * n
+    del ev
+    out = torch.empty((B, 4, He, We), dtype=torch.float32, device=dev)
+    ws = torch.empty(L.load().dvsof_encode_workspace_bytes(N, B, He, We), dtype=torch.uint8, device=dev)
+    st = L.status_for(dev)
+    binned = bool(L.load().dvsof_encode_path(N, B, He, We, ws.numel()))
+
+    def whole():
+        L.call('dvsof_encode_event_image_compact', L.ptr(x), L.ptr(y), L.ptr(t), L.ptr(p), L.ptr(begin), N,
+               L.ptr(ts), B, He, We, L.ptr(out), L.ptr(ws), ws.numel(), L.ptr(st.word), L.stream_ptr(dev))
+    ms = float(np.mean(time_steps(whole, K, W, L2Flusher(dev))))
+    assert int(out[:, :2].sum(dtype=torch.float64).item()) == N, 'event count not conserved'
+    st.check()
+    return dict(events=N, step_ms=ms, warm_graph_ms=graph_time(whole, dev), binned=binned,
+                bytes=9 * N + 8 * (B + 1) + 16 * B * He * We)
+
+
 def bench_loss(name, K, W, dev):
     """fwd+bwd of the multiscale loss the way the train loop calls it
     (training.combined_loss -> Losses.terms -> one library call; loss.backward() -> one call)."""
@@ -776,6 +805,13 @@ def main():
         for name in ('cfg1', 'cfg2', 'cfg4'):
             extra[name + '_loss'] = reduce_loss(bench_loss(name, k2, 3, dev))
             torch.cuda.empty_cache()
+    compact = {}
+    if not args.quick:
+        for name in ('cfg2', 'cfg3'):
+            r = bench_encoder_compact(name, max(3, min(K, 10)), 3, dev)
+            r['step_ms'] = max_over_ranks(r['step_ms'])
+            compact[name] = r
+            torch.cuda.empty_cache()
     solo = rank == 0 and not args.quick
     codec = bench_codec('cfg2', max(3, min(K, 10)), 3, dev) if solo else None
     mapev = bench_map_events(dev) if solo else None
@@ -879,6 +915,15 @@ def main():
                                              'note': 'the same step fed with dv.collate_wrapper(samples) in the reference layout (int64 events, 36 B/event, float32 frames): four times the upload'}}
     for name, r in extra.items():
         line['workloads'][name] = loss_line(name[:4], r) if name.endswith('_loss') else encoder_line(name, r)
+    for name, r in compact.items():
+        line['workloads'][name + '_compact'] = {
+            'workload': DESCR[name] + '; storage form (int16 x, y / bool polarity / fp32 t = 9 B/event, per-sample prefix)',
+            'mevents_per_s': world * r['events'] / (r['step_ms'] * 1e-3) / 1e6, 'ms_per_step': r['step_ms'],
+            'warm_graph_ms_per_step': r['warm_graph_ms'], 'algorithmic_bytes_step': r['bytes'],
+            'hbm_frac_step': frac(r['bytes'], r['step_ms']),
+            'path': 'binned' if r['binned'] else 'direct',
+            'note': 'dvsof_encode_event_image_compact; its own roofline (9 N + 8 (B + 1) + 16 B H W bytes), '
+                    'never mixed with the 36 B/event form'}
     if codec is not None:
         line['workloads']['codec_cfg2'] = {
             'decode_mevents_per_s': codec['events'] / (codec['decode_ms'] * 1e-3) / 1e6, 'decode_ms': codec['decode_ms'],

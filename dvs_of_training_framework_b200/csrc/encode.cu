@@ -290,6 +290,8 @@ static int encode_grid(int64_t work_items, int threads, int ctas_per_sm) {
 struct EncodeArgs {
     const int64_t *x, *y; const float* t; const int64_t *p, *b; int64_t n;
     const float2* sd; int B, H, W; float* out; uint32_t* status;
+    // the storage form (binned path only): x, y int16, polarity uint8; ends = sample_begin + 1
+    const void *cx = nullptr, *cy = nullptr, *cp = nullptr; const int64_t* cends = nullptr;
 };
 
 template <typename K>
@@ -419,14 +421,17 @@ extern "C" int dvsof_encode_event_image(const int64_t* x, const int64_t* y, cons
 static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* workspace, cudaStream_t stream,
                               int passes) {
     char* ws = static_cast<char*>(workspace);
-    const int64_t* ends = reinterpret_cast<const int64_t*>(ws + plan.off_ends);
+    const bool compact = a.cx != nullptr;
+    const int64_t* ends = compact ? a.cends : reinterpret_cast<const int64_t*>(ws + plan.off_ends);
     uint16_t* codes = reinterpret_cast<uint16_t*>(ws + plan.off_codes);
     float* ts = reinterpret_cast<float*>(ws + plan.off_ts);
     uint32_t* table = reinterpret_cast<uint32_t*>(ws + plan.off_table);
     static unsigned long long configured = 0;            // one bit per device (attributes are per device)
     int dev = 0;
     if (needs_device_setup(configured, &dev)) {
-        cudaError_t e = cudaFuncSetAttribute(encode_bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
+        cudaError_t e = cudaFuncSetAttribute(encode_bin_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(encode_bin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBinStageBytes);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(encode_reduce_kernel<kRedBatchLong>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBinSlabBytesMax);
         if (e == cudaSuccess)
@@ -436,11 +441,17 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     }
     if (plan.max_chunks > INT32_MAX || (int64_t)a.B * plan.T > INT32_MAX)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_binned: grid too large");
-    if (passes & 1)
-        if (int rc = launch_kernel("encode_bin_kernel", encode_bin_kernel, (int)plan.max_chunks, kBinThreads,
-                                   kBinStageBytes, stream, passes == 3, a.x, a.y, a.t, a.p, a.b, a.n, ends, a.B, a.H,
-                                   a.W, plan.r_log2, plan.T, codes, ts, table, a.status))
+    if (passes & 1) {
+        if (int rc = compact
+                ? launch_kernel("encode_bin_kernel<compact>", encode_bin_kernel<true>, (int)plan.max_chunks, kBinThreads,
+                                kBinStageBytes, stream, passes == 3, a.cx, a.cy, a.t, a.cp, (const int64_t*)nullptr, a.n,
+                                ends, a.B, a.H, a.W, plan.r_log2, plan.T, codes, ts, table, a.status)
+                : launch_kernel("encode_bin_kernel", encode_bin_kernel<false>, (int)plan.max_chunks, kBinThreads,
+                                kBinStageBytes, stream, passes == 3, (const void*)a.x, (const void*)a.y, a.t,
+                                (const void*)a.p, a.b, a.n, ends, a.B, a.H, a.W, plan.r_log2, plan.T, codes, ts, table,
+                                a.status))
             return rc;
+    }
     if (!(passes & 2)) return DVSOF_OK;
     const bool chained = passes == 3;
     // runs hold ~kBinChunk / T records: one record per lane and batch when that is at most two warps' worth
@@ -484,12 +495,18 @@ extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t*
                                                 const int64_t* sample_begin, int64_t n,
                                                 const float* timestamps, int64_t B, int32_t H,
                                                 int32_t W, float* out, void* workspace,
-                                                uint32_t* status, void* stream_) {
+                                                size_t workspace_bytes, uint32_t* status, void* stream_) {
     if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    if (workspace_bytes < make_bin_plan(0, B, H, W).total)
+        return fail(DVSOF_ERR_WORKSPACE, "encode_compact: workspace of %zu bytes is too small", workspace_bytes);
     cudaStream_t stream = (cudaStream_t)stream_;
-    const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
-    cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
-    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
+    const BinPlan plan = make_bin_plan(n, B, H, W);
+    const bool binned = n > 0 && use_binned(plan, n, B, H, W, workspace_bytes);
+    if (!binned) {                                   // binned: pass 2 writes every output cell
+        const size_t out_bytes = (size_t)B * 4 * H * W * sizeof(float);
+        cudaError_t e = cudaMemsetAsync(out, 0, out_bytes, stream);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode memset: %s", cudaGetErrorString(e));
+    }
     if (n == 0) return DVSOF_OK;
     if (!x || !y || !t || !polarity01 || !sample_begin || !timestamps)
         return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_compact: null event array");
@@ -497,6 +514,13 @@ extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t*
     sample_bounds_compact_kernel<<<(int)((B + 127) / 128), 128, 0, stream>>>(
         sample_begin, t, n, timestamps, (int)B, sd, status);
     if (int rc = check_launch("sample_bounds_compact_kernel")) return rc;
+    if (binned) {
+        // the same two passes as the int64 form; pass 1 reads 9 B/event instead of 36 and takes the
+        // sample of a chunk from the prefix (ends[s] = sample_begin[s + 1])
+        EncodeArgs a{nullptr, nullptr, t, nullptr, nullptr, n, sd, (int)B, H, W, out, status};
+        a.cx = x; a.cy = y; a.cp = polarity01; a.cends = sample_begin + 1;
+        return encode_binned_impl(a, plan, workspace, stream, 3);
+    }
     const bool vec = aligned16(x) && aligned16(y) && aligned16(t) &&
                      ((reinterpret_cast<uintptr_t>(polarity01) & 7u) == 0);
     if (vec) {

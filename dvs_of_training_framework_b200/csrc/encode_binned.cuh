@@ -136,9 +136,12 @@ namespace dvsof {
 // ---------------------------------------------------------------------------------------
 // pass 1: partition one chunk of one sample by tile (counting sort in shared memory)
 // ---------------------------------------------------------------------------------------
+// kCompact: the storage form of utils/dataset.py:286-289 -- x, y int16, polarity uint8 (non-zero =
+// positive), no sample_index array (a chunk's sample is known from `ends` = the per-sample prefix).
+template <bool kCompact>
 __global__ void __launch_bounds__(kBinThreads, DVSOF_BIN_MIN_CTAS)
-encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
-                  const float* __restrict__ t, const int64_t* __restrict__ p,
+encode_bin_kernel(const void* __restrict__ x_, const void* __restrict__ y_,
+                  const float* __restrict__ t, const void* __restrict__ p_,
                   const int64_t* __restrict__ b, int64_t n, const int64_t* __restrict__ ends,
                   int n_samples, int H, int W, int r_log2, int T,
                   uint16_t* __restrict__ codes_g, float* __restrict__ ts_g,
@@ -187,7 +190,17 @@ encode_bin_kernel(const int64_t* __restrict__ x, const int64_t* __restrict__ y,
             const int64_t i = e0 + (int64_t)(k + j) * kBinThreads + threadIdx.x;
             ok[j] = i < e1;
             if (ok[j]) {
-                xi[j] = __ldcs(x + i); yi[j] = __ldcs(y + i); pi[j] = __ldcs(p + i); bi[j] = __ldcs(b + i);
+                if (kCompact) {
+                    xi[j] = __ldcs(static_cast<const int16_t*>(x_) + i);
+                    yi[j] = __ldcs(static_cast<const int16_t*>(y_) + i);
+                    pi[j] = __ldcs(static_cast<const uint8_t*>(p_) + i) ? 1 : -1;
+                    bi[j] = s;
+                } else {
+                    xi[j] = __ldcs(static_cast<const int64_t*>(x_) + i);
+                    yi[j] = __ldcs(static_cast<const int64_t*>(y_) + i);
+                    pi[j] = __ldcs(static_cast<const int64_t*>(p_) + i);
+                    bi[j] = __ldcs(b + i);
+                }
                 tv[k + j] = __ldcs(t + i);
             }
         }

@@ -47,7 +47,7 @@ def compute_event_image(events, timestamps, sample_idx, imsize, device='cuda',
     n = ev['x'].numel()
     for k in _EVENT_KEYS:
         assert ev[k].numel() == n, f"events['{k}'] has {ev[k].numel()} entries, expected {n}"
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         st = _lib.status_for(dev)
         st.flush()
         ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(n, bs, H, W), dtype=torch.uint8, device=dev)
@@ -81,13 +81,13 @@ def compute_event_image_compact(x, y, timestamp, polarity, events_per_sample, ti
     n = x.numel()
     H, W = int(imsize[0]), int(imsize[1])
     out = torch.empty((bs, 4, H, W), dtype=torch.float32, device=dev)
-    with torch.cuda.device(dev):
+    with _lib.on_device(dev):
         st = _lib.status_for(dev)
         st.flush()
-        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(0, bs, H, W), dtype=torch.uint8, device=dev)
+        ws = torch.empty(_lib.load().dvsof_encode_workspace_bytes(n, bs, H, W), dtype=torch.uint8, device=dev)
         _lib.call('dvsof_encode_event_image_compact', _lib.ptr(x), _lib.ptr(y), _lib.ptr(t),
                   _lib.ptr(p), _lib.ptr(begin), n, _lib.ptr(timestamps), bs, H, W, _lib.ptr(out),
-                  _lib.ptr(ws), _lib.ptr(st.word), _lib.stream_ptr(dev))
+                  _lib.ptr(ws), ws.numel(), _lib.ptr(st.word), _lib.stream_ptr(dev))
         if n:
             st.after_call()
     return out

@@ -101,6 +101,8 @@ int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const f
                                      const int64_t* sample_begin, int64_t n_events,
                                      const float* timestamps, int64_t n_samples,
                                      int32_t H, int32_t W, float* out, void* workspace,
+                                     size_t workspace_bytes, /* dvsof_encode_workspace_bytes(n_events, ...) admits
+                                                              * the binned path for dense streams; (0, ...) = direct only */
                                      uint32_t* status, void* stream);
 
 /* ---------------------------------------------------------------------------------------

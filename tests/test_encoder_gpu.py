@@ -117,6 +117,31 @@ def test_compact_storage_form_equals_decoded_form():
     assert np.array_equal(got.cpu().numpy(), want)
 
 
+@pytest.mark.parametrize('H,W', [(64, 96), (272, 640)])
+def test_compact_storage_form_binned_equals_direct_and_oracle(monkeypatch, H, W):
+    """The storage form on both device paths (a dense, ragged stream with an empty sample: the
+    library picks the binned path by itself once the stream is large; here it is forced both ways)
+    against the oracle on the decoded events, and against the int64 entry point."""
+    B, n = 3, 400_000
+    ev, ts, sidx = synth_events(23 + W, B, H, W, n, ragged=True, contended=True)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    eps = torch.bincount(ev['sample_index'], minlength=B)
+    args = (ev['x'].to(torch.int16).cuda(), ev['y'].to(torch.int16).cuda(), ev['timestamp'].cuda(),
+            (ev['polarity'] > 0).cuda(), eps.cuda(), ts.cuda(), (H, W))
+    outs = {}
+    for p in ('direct', 'binned'):
+        monkeypatch.setenv('DVSOF_ENCODE_PATH', p)
+        outs[p] = dv.compute_event_image_compact(*args)
+    assert torch.equal(outs['direct'], outs['binned'])
+    assert np.array_equal(outs['binned'].cpu().numpy(), want)
+    monkeypatch.delenv('DVSOF_ENCODE_PATH')
+    big, tsb, sidxb = synth_events(5, 2, 64, 64, 2_200_000)                # >= 4 M events: default = binned
+    got = dv.compute_event_image_compact(big['x'].to(torch.int16).cuda(), big['y'].to(torch.int16).cuda(),
+                                         big['timestamp'].cuda(), (big['polarity'] > 0).cuda(),
+                                         torch.bincount(big['sample_index'], minlength=2).cuda(), tsb.cuda(), (64, 64))
+    assert torch.equal(got, dv.compute_event_image(_cuda(big), tsb.cuda(), sidxb.cuda(), (64, 64)))
+
+
 def test_full_size_properties_cfg3_like():
     """At sizes the oracle cannot finish quickly: size-independent checks (count conservation,
     linearity over a split of the stream, max of maxima)."""
