@@ -53,6 +53,9 @@ _SIGNATURES = {
     'dvsof_encode_event_image_compact': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p,
                                                     C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                                     C.c_size_t, C.c_void_p, C.c_void_p]),
+    'dvsof_encode_static_max_samples': (C.c_int64, []),
+    'dvsof_encode_event_image_static': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p, C.c_int64,
+                                                   C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_count_image': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
                                     C.c_void_p, C.c_void_p, C.c_void_p]),
     'dvsof_compact_workspace_bytes': (C.c_size_t, [C.c_int64]),

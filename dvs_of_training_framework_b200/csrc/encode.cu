@@ -534,3 +534,64 @@ extern "C" int dvsof_encode_event_image_compact(const int16_t* x, const int16_t*
     }
     return check_launch("encode_compact_kernel");
 }
+
+// ---------------------------------------------------------------------------------------
+// dvsof_encode_event_image_static: the direct path of dvsof_encode_event_image for callers that
+// cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  Its only
+// scratch, the per-sample (start, dt) pairs and exclusive ends that encode_prepare_kernel writes,
+// lives in a file-scope device array instead of a caller workspace: 64 KiB held by every GPU that
+// loads the library, until exit.  No counterpart in the reference; see include/dvsof.h.
+//
+// The array's name is a host-side stand-in in host code, not a device address: the address comes
+// from cudaGetSymbolAddress, once per device, with that device current.  Every word the scatter
+// reads (sd[0..B)) is rewritten by the prepare kernel of the same call, so nothing has to start at
+// zero and the previous call's contents are never seen.  All calls on one device share the array:
+// two calls that overlap on the GPU (different streams) race on it.
+// ---------------------------------------------------------------------------------------
+constexpr int64_t kStaticMaxSamples = DVSOF_STATIC_MAX_SAMPLES;
+constexpr size_t kStaticScratchBytes = (size_t)kStaticMaxSamples * (sizeof(float2) + sizeof(int64_t));
+static __device__ __align__(256) unsigned char g_encode_static_scratch[kStaticScratchBytes];
+
+static int static_scratch_address(void** out) {
+    constexpr int kMaxDevices = 64;
+    static void* address[kMaxDevices] = {};              // per device ordinal; a race repeats the lookup
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "encode_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kMaxDevices)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode_static: device ordinal %d not supported (max %d)", dev, kMaxDevices - 1);
+    void* p = __atomic_load_n(&address[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress(&p, g_encode_static_scratch);
+        if (e != cudaSuccess || !p)
+            return fail(DVSOF_ERR_CUDA, "encode_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        __atomic_store_n(&address[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return DVSOF_OK;
+}
+
+extern "C" int dvsof_encode_event_image_static(const int64_t* x, const int64_t* y, const float* t,
+                                               const int64_t* p, const int64_t* b, int64_t n,
+                                               const float* timestamps, int64_t B, int32_t H, int32_t W,
+                                               float* out, uint32_t* status, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, out, status)) return rc;
+    if (B > kStaticMaxSamples)
+        return fail(DVSOF_ERR_WORKSPACE, "encode_static: %lld samples exceed the static scratch (at most %lld); "
+                    "use dvsof_encode_event_image with a caller workspace", (long long)B, (long long)kStaticMaxSamples);
+    if (n > 0 && (!x || !y || !p || !t || !b || !timestamps))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "encode: null event array");
+    static_assert(kStaticScratchBytes % 256 == 0, "sd | ends layout of make_bin_plan");
+    if (make_bin_plan(0, B, H, W).total > kStaticScratchBytes)
+        return fail(DVSOF_ERR_WORKSPACE, "encode_static: scratch layout exceeds the static array");
+    void* scratch = nullptr;
+    if (int rc = static_scratch_address(&scratch)) return rc;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (int rc = launch_prepare(t, b, n, timestamps, B, H, W, out, scratch, true, stream)) return rc;
+    if (n == 0) return DVSOF_OK;
+    const EncodeArgs a{x, y, t, p, b, n, reinterpret_cast<const float2*>(scratch), (int)B, H, W, out, status};
+    static const bool no_pdl = getenv("DVSOF_NO_PDL") != nullptr;
+    return encode_scatter_impl(a, stream, !no_pdl);
+}
+
+extern "C" int64_t dvsof_encode_static_max_samples(void) { return kStaticMaxSamples; }

@@ -105,6 +105,27 @@ int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const f
                                                               * the binned path for dense streams; (0, ...) = direct only */
                                      uint32_t* status, void* stream);
 
+/* dvsof_encode_event_image without a caller workspace and without any allocation.  NO COUNTERPART
+ * IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and the same (bit-identical) result as dvsof_encode_event_image on its direct
+ * path; the per-sample scratch (16 B per sample) lives in a static __device__ array of
+ * DVSOF_STATIC_MAX_SAMPLES * 16 B = 64 KiB that every GPU loading the library holds until exit.
+ * n_samples > DVSOF_STATIC_MAX_SAMPLES: DVSOF_ERR_WORKSPACE (use the workspace form).  The call
+ * makes no cudaMalloc / cudaFree / allocating library call.  All calls on one device share the
+ * array (it keeps the last call's contents; each call rewrites every word it reads): calls that
+ * overlap on the GPU, e.g. on two streams, race -- keep them stream-ordered. */
+#define DVSOF_STATIC_MAX_SAMPLES 4096
+int64_t dvsof_encode_static_max_samples(void);
+int dvsof_encode_event_image_static(const int64_t* x, const int64_t* y, const float* t,
+                                    const int64_t* polarity, const int64_t* sample_index, /* [dev] N */
+                                    int64_t n_events,
+                                    const float* timestamps, /* [dev] 2*B */
+                                    int64_t n_samples, int32_t H, int32_t W,
+                                    float* out,        /* [dev] B*4*H*W */
+                                    uint32_t* status,  /* [dev] */
+                                    void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Event transforms.
  * ------------------------------------------------------------------------------------- */
