@@ -326,6 +326,50 @@ def bench_encoder_compact(name, K, W, dev):
                 bytes=9 * N + 8 * (B + 1) + 16 * B * He * We)
 
 
+VOXEL_BINS = {'cfg1': 5, 'cfg2': 9, 'cfg3': 9, 'cfg4': 15}      # BASELINE.json configs: 5 / 9 / 15 bins
+
+
+def bench_voxel(name, K, W, dev, cpu_budget_s=3.0):
+    """EXTENSION (not in the reference, parity unpinned): the temporal-bilinear voxel grid of
+    csrc/voxel.cuh through the C ABI on workload `name` with BASELINE.json's bin count; its own
+    roofline: 36 N + 8 B + 4 C B H' W' bytes.  The CPU figure beside it is oracle/voxel_oracle.py
+    (numpy, one thread) on a bounded sample."""
+    import dvs_of_training_framework_b200 as dv
+    L = dv._lib
+    c = CFG[name]
+    B, H, Wd, n, C = c['B'], c['H'], c['W'], c['n'], VOXEL_BINS[name]
+    He, We = dv.extend_size((H, Wd))
+    ev, ts, sidx = fast_events(4321 + int(name[3:]), B, H, Wd, n, c['T'], dev)
+    N = B * n
+    out = torch.empty((B, C, He, We), dtype=torch.float32, device=dev)
+    ws = torch.empty(L.load().dvsof_voxel_workspace_bytes(N, B, He, We, C), dtype=torch.uint8, device=dev)
+    st = L.status_for(dev)
+    binned = bool(L.load().dvsof_voxel_path(N, B, He, We, C, ws.numel()))
+    ptrs = [L.ptr(ev[k]) for k in ('x', 'y', 'timestamp', 'polarity', 'sample_index')]
+
+    def whole():
+        L.call('dvsof_encode_voxel_grid', *ptrs, N, L.ptr(ts), B, C, He, We, L.ptr(out), L.ptr(ws), ws.numel(),
+               L.ptr(st.word), L.stream_ptr(dev))
+    ms = float(np.mean(time_steps(whole, K, W, L2Flusher(dev))))
+    net = float(out.sum(dtype=torch.float64).item())
+    assert abs(net - float(ev['polarity'].sum().item())) <= 1e-4 * N, 'polarity sum not conserved'
+    st.check()
+    # CPU: the oracle on the first sample's events (bounded), checked against the device result
+    from oracle import voxel_oracle as vo
+    m = min(n, 500_000)
+    sub = {k: v[:m].cpu().numpy() for k, v in ev.items()}
+    t0, passes = time.perf_counter(), 0
+    while passes == 0 or time.perf_counter() - t0 < cpu_budget_s:
+        vo.voxel_grid(sub, ts[:2].cpu().numpy(), sidx[:2].cpu().numpy(), (He, We), C)
+        passes += 1
+    cpu_s = (time.perf_counter() - t0) / passes
+    return dict(events=N, step_ms=ms, warm_graph_ms=graph_time(whole, dev), binned=binned, bins=C,
+                bytes=36 * N + 8 * B + 4 * C * B * He * We,
+                cpu={'value': m / cpu_s / 1e6, 'unit': 'Mevents/s', 'cores': 1, 'kind': 'port',
+                     'sample': f'{passes} passes over the first {m} events of sample 0 in {cpu_budget_s:.0f} s, '
+                               'oracle/voxel_oracle.py (numpy)'})
+
+
 def bench_loss(name, K, W, dev):
     """fwd+bwd of the multiscale loss the way the train loop calls it
     (training.combined_loss -> Losses.terms -> one library call; loss.backward() -> one call)."""
@@ -813,6 +857,11 @@ def main():
             compact[name] = r
             torch.cuda.empty_cache()
     solo = rank == 0 and not args.quick
+    voxel = {}
+    if solo:
+        for name in ('cfg2', 'cfg3', 'cfg4'):
+            voxel[name] = bench_voxel(name, max(3, min(K, 10)), 3, dev)
+            torch.cuda.empty_cache()
     codec = bench_codec('cfg2', max(3, min(K, 10)), 3, dev) if solo else None
     mapev = bench_map_events(dev) if solo else None
     torch.cuda.empty_cache()
@@ -924,6 +973,15 @@ def main():
             'path': 'binned' if r['binned'] else 'direct',
             'note': 'dvsof_encode_event_image_compact; its own roofline (9 N + 8 (B + 1) + 16 B H W bytes), '
                     'never mixed with the 36 B/event form'}
+    for name, r in voxel.items():
+        line['workloads'][f"{name}_voxel_{r['bins']}bins"] = {
+            'workload': DESCR[name].split(' -> ')[0] + f" -> temporal-bilinear voxel grid, {r['bins']} bins",
+            'extension': 'not in the reference (its encoder is the 4-channel event image); parity unpinned, '
+                         'checked against oracle/voxel_oracle.py (published definition, Zhu et al. CVPR 2019)',
+            'mevents_per_s': r['events'] / (r['step_ms'] * 1e-3) / 1e6, 'ms_per_step': r['step_ms'],
+            'warm_graph_ms_per_step': r['warm_graph_ms'], 'algorithmic_bytes_step': r['bytes'],
+            'hbm_frac_step': frac(r['bytes'], r['step_ms']), 'path': 'binned' if r['binned'] else 'direct',
+            'cpu_baseline': r['cpu'], 'note': 'dvsof_encode_voxel_grid, one GPU (rank 0); 36 N + 8 B + 4 C B H W bytes'}
     if codec is not None:
         line['workloads']['codec_cfg2'] = {
             'decode_mevents_per_s': codec['events'] / (codec['decode_ms'] * 1e-3) / 1e6, 'decode_ms': codec['decode_ms'],

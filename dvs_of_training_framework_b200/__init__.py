@@ -15,7 +15,8 @@ e-sha/dvs_of_training_framework behind the reference's own Python signatures.
 Everything computes in libdvsof.so (hand-written CUDA, C ABI in include/dvsof.h); there is no
 CPU fallback."""
 from . import _lib  # noqa: F401
-from .encoder import compute_event_image, compute_event_image_compact, extend_size, quantize  # noqa: F401
+from .encoder import (compute_event_image, compute_event_image_compact, compute_voxel_grid, extend_size,  # noqa: F401
+                      quantize)
 from .loss import Loss, Losses, charbonier_loss, init_losses, interpolate  # noqa: F401
 from .data import (EventCrop, RandomRotation, augment_events, frame_generator, frame_offsets,  # noqa: F401
                    get_count_image, rotation_lut)
@@ -26,7 +27,7 @@ from .eval import flow_error_dense, flow_error_dense_device  # noqa: F401
 from .dataset import (collate_wrapper, decode_batch, decode_batch_info, decode_events, decode_quantized_batch,  # noqa: F401
                       encode_batch, encode_batch_info, encode_quantized_batch, quantize_batch)
 
-__all__ = ['compute_event_image', 'compute_event_image_compact', 'extend_size', 'quantize',
+__all__ = ['compute_event_image', 'compute_event_image_compact', 'compute_voxel_grid', 'extend_size', 'quantize',
            'Loss', 'Losses', 'charbonier_loss', 'init_losses', 'interpolate',
            'EventCrop', 'RandomRotation', 'get_count_image', 'frame_generator', 'frame_offsets', 'augment_events', 'rotation_lut',
            'transformation', 'flow_error_dense', 'flow_error_dense_device',

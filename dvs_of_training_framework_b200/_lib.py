@@ -53,6 +53,11 @@ _SIGNATURES = {
     'dvsof_encode_event_image_compact': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p,
                                                     C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
                                                     C.c_size_t, C.c_void_p, C.c_void_p]),
+    'dvsof_voxel_workspace_bytes': (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32]),
+    'dvsof_voxel_path': (C.c_int, [C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_size_t]),
+    'dvsof_encode_voxel_grid': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p, C.c_int64, C.c_int32,
+                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_size_t,
+                                           C.c_void_p, C.c_void_p]),
     'dvsof_encode_static_max_samples': (C.c_int64, []),
     'dvsof_encode_event_image_static': (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_void_p, C.c_int64,
                                                    C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),

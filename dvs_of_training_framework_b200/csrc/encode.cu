@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include "common.cuh"
 #include "encode_binned.cuh"
+#include "voxel.cuh"
 
 namespace dvsof {
 
@@ -595,3 +596,91 @@ extern "C" int dvsof_encode_event_image_static(const int64_t* x, const int64_t* 
 }
 
 extern "C" int64_t dvsof_encode_static_max_samples(void) { return kStaticMaxSamples; }
+
+// ---------------------------------------------------------------------------------------
+// Voxel grid (extension, csrc/voxel.cuh): same stream, same per-sample bounds, C temporal bins.
+// ---------------------------------------------------------------------------------------
+static bool voxel_use_binned(const BinPlan& plan, int64_t n, int64_t B, int H, int W, size_t workspace_bytes) {
+    if (!plan.ok || workspace_bytes < plan.total) return false;
+    const int ov = encode_path_override();
+    if (ov == 1) return false;
+    if (ov == 2) return true;
+    const int64_t pixels = B * (int64_t)H * W;
+    const bool many_ctas = B * (int64_t)plan.T >= 2 * 3 * kNumSMs;
+    return n >= (4 << 20) && n >= (many_ctas ? 3 : 8) * pixels;
+}
+
+extern "C" size_t dvsof_voxel_workspace_bytes(int64_t n_events, int64_t n_samples, int32_t H, int32_t W,
+                                              int32_t n_bins) {
+    return make_voxel_plan(n_events, n_samples, H, W, n_bins).total;
+}
+
+extern "C" int dvsof_voxel_path(int64_t n, int64_t B, int32_t H, int32_t W, int32_t C, size_t workspace_bytes) {
+    if (n <= 0 || B <= 0 || H <= 0 || W <= 0) return 0;
+    return voxel_use_binned(make_voxel_plan(n, B, H, W, C), n, B, H, W, workspace_bytes) ? 1 : 0;
+}
+
+extern "C" int dvsof_encode_voxel_grid(const int64_t* x, const int64_t* y, const float* t,
+                                       const int64_t* p, const int64_t* b, int64_t n,
+                                       const float* timestamps, int64_t B, int32_t C, int32_t H, int32_t W,
+                                       float* out, void* workspace, size_t workspace_bytes,
+                                       uint32_t* status, void* stream_) {
+    if (int rc = check_encode_args(n, B, H, W, out, workspace, status)) return rc;
+    if (C < 1 || C > kVoxelMaxBins)
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "voxel: n_bins = %d outside [1, %d]", C, kVoxelMaxBins);
+    if (n > 0 && (!x || !y || !p || !t || !b || !timestamps))
+        return fail(DVSOF_ERR_INVALID_ARGUMENT, "voxel: null event array");
+    if (workspace_bytes < make_bin_plan(0, B, H, W).total)
+        return fail(DVSOF_ERR_WORKSPACE, "voxel: workspace of %zu bytes is too small", workspace_bytes);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const BinPlan plan = make_voxel_plan(n, B, H, W, C);
+    const bool binned = n > 0 && voxel_use_binned(plan, n, B, H, W, workspace_bytes);
+    // the prepare kernel zeroes "4 planes" of H * W' cells: hand it the C planes as one wide image
+    // (it only uses the product); binned: pass 2 writes every cell
+    {
+        const size_t n_floats = binned ? 0 : (size_t)B * C * H * W;
+        int64_t grid = (int64_t)((n_floats / 4 + kPrepThreads * 8 - 1) / (kPrepThreads * 8));
+        if (grid > kNumSMs * 8) grid = kNumSMs * 8;
+        if (grid < B) grid = B < kNumSMs * 8 ? B : kNumSMs * 8;
+        if (grid < 1) grid = 1;
+        const BinPlan base = make_bin_plan(0, B, H, W);
+        if (int rc = launch_kernel("encode_prepare_kernel", encode_prepare_kernel, (int)grid, kPrepThreads, 0, stream,
+                                   false, b, t, n, timestamps, (int)B, reinterpret_cast<float2*>(workspace),
+                                   reinterpret_cast<int64_t*>(static_cast<char*>(workspace) + base.off_ends),
+                                   out, n_floats))
+            return rc;
+    }
+    if (n == 0) return DVSOF_OK;
+    const float2* sd = reinterpret_cast<const float2*>(workspace);
+    if (!binned) {
+        const bool vec = aligned16(x) && aligned16(y) && aligned16(t) && aligned16(p) && aligned16(b);
+        if (vec)
+            return launch_kernel("voxel_direct_kernel<vec>", voxel_direct_kernel<true>, encode_grid((n >> 2) + 1, 256, 64),
+                                 256, 0, stream, true, x, y, t, p, b, n, sd, (int)B, (int)C, H, W, out, status);
+        return launch_kernel("voxel_direct_kernel", voxel_direct_kernel<false>, encode_grid(n, 256, 8), 256, 0,
+                             stream, true, x, y, t, p, b, n, sd, (int)B, (int)C, H, W, out, status);
+    }
+    // pass 1 of the event-image path as it is (the records do not depend on C), then the voxel pass 2
+    const EncodeArgs a{x, y, t, p, b, n, sd, (int)B, H, W, out, status};
+    if (int rc = encode_binned_impl(a, plan, workspace, stream, 1)) return rc;
+    char* ws = static_cast<char*>(workspace);
+    const size_t slab = (size_t)plan.R * W * C * sizeof(float);
+    static unsigned long long configured = 0;
+    int dev = 0;
+    if (needs_device_setup(configured, &dev)) {
+        cudaError_t e = cudaFuncSetAttribute(voxel_reduce_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVoxelSlabMax);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(voxel_reduce_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kVoxelSlabMax);
+        if (e != cudaSuccess) return fail(DVSOF_ERR_CUDA, "voxel smem attr: %s", cudaGetErrorString(e));
+        device_setup_done(configured, dev);
+    }
+    const uint16_t* codes = reinterpret_cast<const uint16_t*>(ws + plan.off_codes);
+    const float* ts = reinterpret_cast<const float*>(ws + plan.off_ts);
+    const uint32_t* table = reinterpret_cast<const uint32_t*>(ws + plan.off_table);
+    const int64_t* ends = reinterpret_cast<const int64_t*>(ws + plan.off_ends);
+    if (kBinChunk / plan.T <= 64)
+        return launch_kernel("voxel_reduce_kernel<2>", voxel_reduce_kernel<2>, (int)(B * plan.T), kVoxelRedThreads, slab,
+                             stream, true, codes, ts, table, ends, sd, (int)B, (int)C, H, W, plan.r_log2, plan.T, out);
+    return launch_kernel("voxel_reduce_kernel<5>", voxel_reduce_kernel<5>, (int)(B * plan.T), kVoxelRedThreads, slab,
+                         stream, true, codes, ts, table, ends, sd, (int)B, (int)C, H, W, plan.r_log2, plan.T, out);
+}

@@ -97,3 +97,33 @@ def quantize(events, timestamps, sample_idx, imsize):
     """EV_FlowNet/net.py:197-205 `Model.quantize`: encode at the x16-extended size, no grad."""
     with torch.no_grad():
         return compute_event_image(events, timestamps, sample_idx, extend_size(imsize))
+
+
+def compute_voxel_grid(events, timestamps, sample_idx, imsize, n_bins):
+    """EXTENSION -- not in the reference (its network input is `compute_event_image`): the
+    temporal-bilinear voxel grid (B, n_bins, H, W) fp32 that BASELINE.json's "bins" configs name
+    (Zhu et al., CVPR 2019): `t* = (n_bins - 1) (t - start) / dt` with the event image's start / dt
+    (EV_FlowNet/net.py:136-141), `out[b, k, y, x] = sum p * max(0, 1 - |t* - k|)`.  Same event
+    dictionary, timestamps and sample_idx as `compute_event_image`; CUDA tensors only."""
+    assert len(imsize) == 2 and timestamps.ndim == 1 and sample_idx.ndim == 1
+    timestamps = _lib.require_cuda(timestamps, 'timestamps', torch.float32)
+    dev = timestamps.device
+    bs = timestamps.numel() // 2
+    assert bs * 2 == timestamps.numel() and sample_idx.numel() == timestamps.numel()
+    H, W, C = int(imsize[0]), int(imsize[1]), int(n_bins)
+    ev = {k: _lib.require_cuda(events[k], f"events['{k}']", torch.float32 if k == 'timestamp' else torch.int64)
+          for k in _EVENT_KEYS}
+    n = ev['x'].numel()
+    for k in _EVENT_KEYS:
+        assert ev[k].numel() == n, f"events['{k}'] has {ev[k].numel()} entries, expected {n}"
+    out = torch.empty((bs, C, H, W), dtype=torch.float32, device=dev)
+    with _lib.on_device(dev):
+        st = _lib.status_for(dev)
+        st.flush()
+        ws = torch.empty(_lib.load().dvsof_voxel_workspace_bytes(n, bs, H, W, C), dtype=torch.uint8, device=dev)
+        _lib.call('dvsof_encode_voxel_grid', _lib.ptr(ev['x']), _lib.ptr(ev['y']), _lib.ptr(ev['timestamp']),
+                  _lib.ptr(ev['polarity']), _lib.ptr(ev['sample_index']), n, _lib.ptr(timestamps), bs, C, H, W,
+                  _lib.ptr(out), _lib.ptr(ws), ws.numel(), _lib.ptr(st.word), _lib.stream_ptr(dev))
+        if n:
+            st.after_call()
+    return out

@@ -105,6 +105,26 @@ int dvsof_encode_event_image_compact(const int16_t* x, const int16_t* y, const f
                                                               * the binned path for dense streams; (0, ...) = direct only */
                                      uint32_t* status, void* stream);
 
+/* EXTENSION, NO COUNTERPART IN THE REFERENCE (whose network input is the 4-channel event image
+ * above): the temporal-bilinear voxel grid that BASELINE.json's north_star and configs ("5 / 9 / 15
+ * bins") name, by its published definition (Zhu et al., CVPR 2019, eq. 1-3):
+ *   t* = (n_bins - 1) * (t - start[b]) / dt[b]        start, dt as for the event image (net.py:136-141)
+ *   out[b, k, y, x] = sum of polarity * max(0, 1 - |t* - k|) over the events of pixel (x, y) of sample b.
+ * out (B, n_bins, H, W) fp32 is fully overwritten; same validation bits, same two device paths
+ * (direct: two fp32 reductions per event; binned: pass 1 of the event-image path, then a
+ * [n_bins][rows x W] shared-memory slab per (sample, row band)).  fp32 sums in no fixed order:
+ * within ~1e-7 of the absolute sum of a voxel's weights of the exact result.  1 <= n_bins <= 64.
+ * workspace: dvsof_voxel_workspace_bytes(N, B, H, W, n_bins); (0, ...) selects the direct path.
+ * dvsof_voxel_path: 0 = direct, 1 = binned for these sizes and this workspace.  Parity unpinned. */
+size_t dvsof_voxel_workspace_bytes(int64_t n_events, int64_t n_samples, int32_t H, int32_t W, int32_t n_bins);
+int dvsof_voxel_path(int64_t n_events, int64_t n_samples, int32_t H, int32_t W, int32_t n_bins,
+                     size_t workspace_bytes);
+int dvsof_encode_voxel_grid(const int64_t* x, const int64_t* y, const float* t,
+                            const int64_t* polarity, const int64_t* sample_index, /* [dev] N */
+                            int64_t n_events, const float* timestamps /* [dev] 2*B */, int64_t n_samples,
+                            int32_t n_bins, int32_t H, int32_t W, float* out /* [dev] B*n_bins*H*W */,
+                            void* workspace, size_t workspace_bytes, uint32_t* status, void* stream);
+
 /* dvsof_encode_event_image without a caller workspace and without any allocation.  NO COUNTERPART
  * IN THE REFERENCE: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
