@@ -142,6 +142,38 @@ def test_compact_storage_form_binned_equals_direct_and_oracle(monkeypatch, H, W)
     assert torch.equal(got, dv.compute_event_image(_cuda(big), tsb.cuda(), sidxb.cuda(), (64, 64)))
 
 
+@pytest.mark.parametrize('case', ['offset', 'dense', 'shuffled', 'mixed', 'inf'])
+def test_binned_record_formats_bitwise(monkeypatch, case):
+    """Timestamp layouts on the binned path, whose pass 2 keeps the maximum of the RAW t under an
+    order-preserving integer key: a large time offset (coarse fp32 steps, many equal keys), a dense
+    burst, timestamps in random order, a jump in step size mid-stream, infinite timestamps.  Every
+    one bit-identical to the direct path and the oracle.  (Written with the packed 4-byte record
+    experiment of profiles/r02zf_packed_records_negative.*: it passed these and measured slower.)"""
+    B, H, W, n = 3, 64, 96, 300_000
+    ev, ts, sidx = synth_events(91, B, H, W, n, ragged=(case == 'mixed'))
+    if case == 'offset':
+        ev['timestamp'] = (ev['timestamp'] + 100.0).float()
+        ts = (ts + 100.0).float()
+    elif case == 'dense':
+        ev['timestamp'] = (ev['timestamp'] * 0.01 + 0.02).float()       # 300 k events in 0.32 ms
+    elif case == 'shuffled':
+        perm = torch.cat([torch.randperm(n) + b * n for b in range(B)])
+        ev['timestamp'] = ev['timestamp'][perm].contiguous()
+    elif case == 'mixed':                                                 # the first half coarse, the rest fine steps
+        m = ev['timestamp'].numel() // 2
+        ev['timestamp'][:m] = (ev['timestamp'][:m] + 8.0).float() - 8.0
+    elif case == 'inf':
+        ev['timestamp'][1000] = float('inf')
+        ev['timestamp'][5000] = float('-inf')
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    outs = {}
+    for p in ('direct', 'binned'):
+        monkeypatch.setenv('DVSOF_ENCODE_PATH', p)
+        outs[p] = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert torch.equal(outs['direct'], outs['binned'])
+    assert np.array_equal(outs['binned'].cpu().numpy(), want, equal_nan=True)
+
+
 def test_full_size_properties_cfg3_like():
     """At sizes the oracle cannot finish quickly: size-independent checks (count conservation,
     linearity over a split of the stream, max of maxima)."""
