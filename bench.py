@@ -858,7 +858,7 @@ def main():
             torch.cuda.empty_cache()
     solo = rank == 0 and not args.quick
     voxel = {}
-    if solo:
+    if solo and world == 1:                       # extension lines: single-GPU runs only
         for name in ('cfg2', 'cfg3', 'cfg4'):
             voxel[name] = bench_voxel(name, max(3, min(K, 10)), 3, dev)
             torch.cuda.empty_cache()
