@@ -181,6 +181,51 @@ encode_bin_kernel(const void* __restrict__ x_, const void* __restrict__ y_,
     static_assert(kPer % kFly == 0, "whole load steps");
     unsigned packed[kPer];                            // rank | tile | code, 0xffffffff = dropped
     float tv[kPer];
+    // Storage form, full chunk on a 16-event boundary of 16-byte aligned arrays: a thread takes two
+    // groups of 8 CONSECUTIVE events with 16-byte loads (x, y: 8 x int16; t: 2 x float4; polarity:
+    // 8 bytes).  The scalar loop below keeps one 2-byte load per lane in flight -- 64 B per warp
+    // instruction, far too little outstanding traffic to cover the DRAM latency at 9 B/event.  The
+    // order inside a run is free, so the other event-to-thread mapping changes nothing downstream.
+    bool vec8 = false;
+    if constexpr (kCompact) {
+        static_assert(kPer == 16, "two groups of 8 events per thread");
+        vec8 = e1 - e0 == kBinChunk && ((e0 & 15) == 0) &&
+               ((reinterpret_cast<uintptr_t>(x_) | reinterpret_cast<uintptr_t>(y_) |
+                 reinterpret_cast<uintptr_t>(t) | reinterpret_cast<uintptr_t>(p_)) & 15u) == 0;
+        if (vec8) {                                   // CTA-uniform
+            uint4 xv[2], yv[2];
+            uint2 pv[2];
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                const int64_t eb = e0 + (int64_t)g * (kBinChunk / 2) + 8 * threadIdx.x;
+                xv[g] = __ldcs(reinterpret_cast<const uint4*>(static_cast<const int16_t*>(x_) + eb));
+                yv[g] = __ldcs(reinterpret_cast<const uint4*>(static_cast<const int16_t*>(y_) + eb));
+                pv[g] = __ldcs(reinterpret_cast<const uint2*>(static_cast<const uint8_t*>(p_) + eb));
+                const float4 ta = __ldcs(reinterpret_cast<const float4*>(t + eb));
+                const float4 tb = __ldcs(reinterpret_cast<const float4*>(t + eb) + 1);
+                tv[8 * g + 0] = ta.x; tv[8 * g + 1] = ta.y; tv[8 * g + 2] = ta.z; tv[8 * g + 3] = ta.w;
+                tv[8 * g + 4] = tb.x; tv[8 * g + 5] = tb.y; tv[8 * g + 6] = tb.z; tv[8 * g + 7] = tb.w;
+            }
+#pragma unroll
+            for (int g = 0; g < 2; ++g) {
+                const unsigned xw[4] = {xv[g].x, xv[g].y, xv[g].z, xv[g].w};
+                const unsigned yw[4] = {yv[g].x, yv[g].y, yv[g].z, yv[g].w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int xi = (int)(short)((j & 1) ? (xw[j >> 1] >> 16) : (xw[j >> 1] & 0xffffu));
+                    const int yi = (int)(short)((j & 1) ? (yw[j >> 1] >> 16) : (yw[j >> 1] & 0xffffu));
+                    const unsigned pb = (((j < 4) ? pv[g].x : pv[g].y) >> (8 * (j & 3))) & 0xffu;
+                    packed[8 * g + j] = 0xffffffffu;
+                    if ((unsigned)xi >= (unsigned)W || (unsigned)yi >= (unsigned)H) { flags |= DVSOF_ST_BAD_PIXEL; continue; }
+                    const unsigned yy = (unsigned)yi, tile = yy >> r_log2;
+                    const unsigned code = (((yy & ((1u << r_log2) - 1u)) * (unsigned)W + (unsigned)xi) << 1) | (pb ? 0u : 1u);
+                    const unsigned rank = atomicAdd(&hist[tile], 1u);
+                    packed[8 * g + j] = (rank << 20) | (tile << 13) | code;
+                }
+            }
+        }
+    }
+    if (!vec8)
 #pragma unroll
     for (int k = 0; k < kPer; k += kFly) {            // kFly events in flight per thread and step
         int64_t xi[kFly], yi[kFly], pi[kFly], bi[kFly];

@@ -841,6 +841,10 @@ static bool plan_chain(const dvsof_loss_scales_t* sc, const dvsof_loss_frames_t*
     const int last_rows = sc->H[sc->n_scales - 1];
     int slabs = kNumSMs / (fr->n_images > 0 ? fr->n_images : 1);
     slabs = slabs > 16 ? 16 : slabs;
+    if (const char* e = getenv("DVSOF_PYR_SLABS")) {            // tuning: slabs per frame
+        const int v = atoi(e);
+        if (v >= 1 && v <= 64) slabs = v;
+    }
     slabs = slabs > last_rows / 4 ? last_rows / 4 : slabs;
     a->slabs = slabs < 1 ? 1 : slabs;
     // warps per CTA: about four 2-row x 128-column tasks of the last level each (every warp pays the
