@@ -455,13 +455,13 @@ static int encode_binned_impl(const EncodeArgs& a, const BinPlan& plan, void* wo
     }
     if (!(passes & 2)) return DVSOF_OK;
     const bool chained = passes == 3;
-    // runs hold ~kBinChunk / T records: one record per lane and batch when that is at most two warps' worth
+    // runs hold ~kBinChunk / T records: two records per lane and run in flight when that is at most two warps' worth
     if (kBinChunk / plan.T <= 64)
         return launch_kernel("encode_reduce_kernel<short>", encode_reduce_kernel<kRedBatchShort>, a.B * plan.T, kRedThreads,
-                             (size_t)plan.cells * 8, stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                             reduce_smem_bytes(plan.cells), stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                              plan.r_log2, plan.T, a.out);
     return launch_kernel("encode_reduce_kernel", encode_reduce_kernel<kRedBatchLong>, a.B * plan.T, kRedThreads,
-                         (size_t)plan.cells * 8, stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
+                         reduce_smem_bytes(plan.cells), stream, chained, codes, ts, table, ends, a.sd, a.B, a.H, a.W,
                          plan.r_log2, plan.T, a.out);
 }
 

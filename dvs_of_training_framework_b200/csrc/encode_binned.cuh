@@ -11,7 +11,7 @@
 //   pass 1 (bin):    a CTA takes a chunk of kBinChunk consecutive events of ONE sample, counting-
 //                    sorts them by tile (band of 2^r rows) in shared memory (one shared atomic per
 //                    event: histogram and rank inside the tile's run at once) and writes them back
-//                    as 6-byte records {u16 cell-in-tile, f32 t} -- contiguous per (chunk, tile)
+//                    as 6-byte records {u16 cell-in-tile, s32 order-preserving key of t} -- contiguous per (chunk, tile)
 //                    run -- plus the chunk's run table.  HBM: 36 B read + 6 B written per event.
 //   pass 2 (reduce): a CTA owns one (sample, tile): its slab of {u32 count, s32 max-key} lives in
 //                    shared memory; it streams its runs of every chunk of the sample (6 B/event),
@@ -42,13 +42,17 @@ namespace dvsof {
 constexpr int kBinChunk = DVSOF_BIN_CHUNK;       // events per pass-1 chunk
 constexpr int kBinThreads = DVSOF_BIN_THREADS;   // pass-1 CTA: 16 events per thread, DVSOF_BIN_INFLIGHT at a time
 #ifndef DVSOF_RED_BATCH
-#define DVSOF_RED_BATCH 5
+#define DVSOF_RED_BATCH 4
 #endif
-constexpr int kRedBatchLong = DVSOF_RED_BATCH;          // pass-2 loads in flight per lane
 #ifndef DVSOF_RED_BATCH_SHORT
-#define DVSOF_RED_BATCH_SHORT -1
+#define DVSOF_RED_BATCH_SHORT 2
 #endif
-constexpr int kRedBatchShort = DVSOF_RED_BATCH_SHORT;   // the same for short runs (wide images); 0 = four runs per warp at a time, -1 = the lean loop (default); the long-run batch: -k = the lean loop with k records per lane and run
+#ifndef DVSOF_RED_RUNS
+#define DVSOF_RED_RUNS 2
+#endif
+constexpr int kRedBatchLong = DVSOF_RED_BATCH;          // pass 2: records per lane and run in flight (runs of ~128 records)
+constexpr int kRedBatchShort = DVSOF_RED_BATCH_SHORT;   // the same for short runs (wide images: ~34 records)
+constexpr int kRedRuns = DVSOF_RED_RUNS;                // runs in flight per warp
 constexpr int kBinMaxTiles = 128;     // tiles (row bands) per sample
 constexpr int kBinMaxSamples = 512;   // samples per batch on this path (per-CTA chunk lookup)
 #ifndef DVSOF_RED_THREADS
@@ -292,7 +296,7 @@ encode_bin_kernel(const void* __restrict__ x_, const void* __restrict__ y_,
         if (packed[k] == 0xffffffffu) continue;
         const unsigned pos = cursor[(packed[k] >> 13) & 127u] + (packed[k] >> 20);
         codes_s[pos] = (uint16_t)(packed[k] & 0x1fffu);
-        ts_s[pos] = tv[k];
+        ts_s[pos] = __int_as_float(ordered_key(tv[k]));      // pass 2 takes the maximum of the keys as they are
     }
     __syncthreads();
     const unsigned total = hist[T];
@@ -305,151 +309,73 @@ encode_bin_kernel(const void* __restrict__ x_, const void* __restrict__ y_,
 }
 
 // ---------------------------------------------------------------------------------------
-// pass 2: one CTA per (sample, tile): shared-memory slab, then one coalesced write of the bands
+// pass 2: one CTA per (sample, tile): shared-memory slab of {u32 count} and {s32 max key} per cell,
+// then one coalesced write of the four plane bands.
+// The chunks of the sample are dealt to the 16 warps round-robin (k-th chunk of warp w = k * 16 + w:
+// every warp works even when a sample has few chunks); a lane holds the run bounds of one of the warp's
+// next 32 chunks; kLR runs x kLP records per lane are requested, then applied -- no software pipeline,
+// 16 warps x 3 CTAs per SM keep enough loads in flight.  Written for the instruction count (the first
+// version of this loop compiled to 53 instructions per record under its 42-register budget: the
+// shared-memory base and the key array's offset re-derived per record, a branch around each pair of
+// atomics, two 64-bit address computations per load, ten moves per batch of the software pipeline):
+//   * the key array sits at a FIXED distance behind the counts (kKeyOffsetBytes): one address, one
+//     immediate offset;
+//   * both atomics are unconditional (slab_apply), no divergence regions;
+//   * a run is addressed once; its records are 32 apart at immediate offsets; pass 1 delivers the key.
+// What bounds it (profiles/r02zj_*): the shared-memory atomics themselves.  With the record loads
+// replaced by hashed cell numbers the kernel still takes 206 of its 286 us at cfg3 (5.3 lane-atomics
+// per clock and SM; scripts/ubench_atomics.cu reaches 11 in isolation with 64 warps per SM); forcing
+// every lane of a warp onto its own bank gains 10 %; 40 % fewer instructions, splitting each slab over
+// a cluster of 2-4 CTAs against the 2.3-round tail, more or fewer records in flight: no change.
 // ---------------------------------------------------------------------------------------
 #ifndef DVSOF_RED_MIN_CTAS
 #define DVSOF_RED_MIN_CTAS 3
 #endif
-template <int kRedBatch>                       // records per lane and batch: 4 for runs of ~128, 1 for short runs (wide images)
+constexpr unsigned kKeyOffsetBytes = kBinSlabBytesMax / 2;       // cells <= 8192 counts of 4 bytes
+// at least 32 cells: lanes without a record touch cell `lane` (slab_apply)
+inline size_t reduce_smem_bytes(int cells) { return (size_t)kKeyOffsetBytes + (size_t)(cells < 32 ? 32 : cells) * 4; }
+
+// One record into the slab.  EVERY lane executes both atomics: ptxas wraps a predicated shared atomic
+// in a divergence region (BSSY / BRA / BSYNC: four instructions per atomic), so a lane without a
+// record adds 0 to, and maximises INT_MIN into, cell `lane` -- no-ops on 32 distinct banks.
+__device__ __forceinline__ void slab_apply(unsigned* cnt, unsigned code, int key, unsigned inc) {
+    unsigned* a = cnt + code;
+    atomicAdd(a, inc);                                                       // scatter_sum, net.py:147-148
+    atomicMax(reinterpret_cast<int*>(a + kKeyOffsetBytes / 4), key);         // scatter_max (key of the raw t), net.py:149
+}
+
+template <int kLP>                                   // records per lane and run in flight (kLR runs at a time)
 __global__ void __launch_bounds__(kRedThreads, DVSOF_RED_MIN_CTAS)
 encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restrict__ ts_g,
                      const uint32_t* __restrict__ table, const int64_t* __restrict__ ends,
                      const float2* __restrict__ sd, int n_samples, int H, int W, int r_log2, int T,
                      float* __restrict__ out) {
-    extern __shared__ __align__(16) unsigned slab[];   // [cells] counts, then [cells] max keys
+    extern __shared__ __align__(16) unsigned slab[];   // [cells] counts ... [kKeyOffsetBytes:] [cells] max keys
     __shared__ int prefix[kBinMaxSamples + 1];
-    pdl_wait_for(codes_g, ts_g, table, ends, sd);                                       // records + tables come from pass 1
     const int s = blockIdx.x / T, tile = blockIdx.x - s * T;
     const int R = 1 << r_log2, cells = R * W * 2;
     unsigned* cnt = slab;
-    int* key = reinterpret_cast<int*>(slab + cells);
-    {   // cells is a multiple of 4 (W * 2 * R with W % 2 == 0 ... checked: falls back to scalar stores otherwise)
-        if ((cells & 3) == 0) {
-            uint4* c4 = reinterpret_cast<uint4*>(cnt);
-            int4* k4 = reinterpret_cast<int4*>(key);
-            for (int i = threadIdx.x; i < cells / 4; i += kRedThreads) {
-                c4[i] = make_uint4(0u, 0u, 0u, 0u);
-                k4[i] = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
-            }
-        } else {
-            for (int i = threadIdx.x; i < cells; i += kRedThreads) { cnt[i] = 0u; key[i] = INT_MIN; }
-        }
-    }
-    chunk_prefix<kRedThreads>(ends, n_samples, prefix);   // ends with __syncthreads()
-    const int cb = prefix[s], nc = prefix[s + 1] - prefix[s];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // Runs are short (kBinChunk / T records, one batch of 32 x kRedBatch), so a warp's time is the
-    // latency of one dependent trip to DRAM per run unless the next run is already in flight:
-    // chunks are dealt to the warps round-robin (k-th chunk of warp w = k * kWarps + w: every warp
-    // works even when a sample has few chunks), a lane holds the bounds of one of the warp's next
-    // 32 chunks, and the batch after the current one is requested before the current one is
-    // applied.  Everything that steers the loop is warp-uniform.
-    constexpr int kWarps = kRedThreads / 32;
-    constexpr unsigned kStep = 32 * (kRedBatch > 0 ? kRedBatch : 1);
-    const int my_n = nc > warp ? (nc - warp + kWarps - 1) / kWarps : 0;
-    if constexpr (kRedBatch < 0) {
-        // Short runs, the lean way: no software pipelining at all -- 16 warps x 4 CTAs per SM are
-        // enough loads in flight, and a run of ~34 records costs ~30 instructions instead of ~100.
-        for (int k0 = 0; k0 < my_n; k0 += 32) {
-            unsigned lo = 0, hi = 0;
-            if (k0 + lane < my_n) {
-                const uint32_t* row = table + (size_t)(cb + (k0 + lane) * kWarps + warp) * (T + 1) + tile;
-                lo = __ldg(row); hi = __ldg(row + 1);
-            }
-            const int m = min(32, my_n - k0);
-            const uint16_t* cg = codes_g + (size_t)(cb + k0 * kWarps + warp) * kBinChunk;
-            const float* tg = ts_g + (size_t)(cb + k0 * kWarps + warp) * kBinChunk;
-            constexpr size_t kStride = (size_t)kWarps * kBinChunk;       // records between two chunks of a warp
-            auto apply = [&](unsigned c, float t) {
-                if (c != 0xffffffffu) {
-                    atomicAdd(&cnt[c], 1u);                      // scatter_sum, net.py:147-148
-                    atomicMax(&key[c], ordered_key(t));          // scatter_max of the raw t, net.py:149
-                }
-            };
-            // kLR runs x kLP records per lane in flight (short runs: 2 x 2 = 64 records cover 34 +- 6;
-            // long runs of ~128: 2 x 5)
-            constexpr int kLR = 2, kLP = kRedBatch == -1 ? 2 : -kRedBatch;
-            for (int j = 0; j < m; j += kLR) {
-                unsigned ra[kLR], rb[kLR];
-#pragma unroll
-                for (int q = 0; q < kLR; ++q) {
-                    ra[q] = __shfl_sync(0xffffffffu, lo, (j + q) & 31);
-                    rb[q] = __shfl_sync(0xffffffffu, hi, (j + q) & 31);
-                    if (j + q >= m) rb[q] = ra[q];
-                }
-                const uint16_t* c0 = cg + j * kStride;
-                const float* t0 = tg + j * kStride;
-                unsigned code[kLR * kLP];
-                float tv[kLR * kLP];
-#pragma unroll
-                for (int q = 0; q < kLR; ++q)
-#pragma unroll
-                    for (int u = 0; u < kLP; ++u) {
-                        const unsigned i = ra[q] + u * 32 + lane;
-                        code[q * kLP + u] = 0xffffffffu;
-                        if (i < rb[q]) {
-                            code[q * kLP + u] = __ldcs(c0 + q * kStride + i);
-                            tv[q * kLP + u] = __ldcs(t0 + q * kStride + i);
-                        }
-                    }
-#pragma unroll
-                for (int u = 0; u < kLR * kLP; ++u) apply(code[u], tv[u]);
-#pragma unroll
-                for (int q = 0; q < kLR; ++q)                      // rare: a run longer than 32 kLP records
-                    for (unsigned i = ra[q] + 32 * kLP + lane; __any_sync(0xffffffffu, i < rb[q]); i += 32)
-                        if (i < rb[q]) apply(__ldcs(c0 + q * kStride + i), __ldcs(t0 + q * kStride + i));
-            }
-        }
-    } else if constexpr (kRedBatch == 0) {
-        // Short runs (wide images: kBinChunk / T ~ 34 records): FOUR runs per warp at a time, 8 lanes
-        // and up to kGT records per lane each, the next four requested before the current ones are
-        // applied.  A slab's CTA is a chain of DRAM round trips (table entry -> records -> atomics);
-        // with one run in flight per warp it was 16-32 of them per warp (82 us for cfg4's 1920 slabs).
-        constexpr int kGT = 6, kG = 4;                        // 48 records cover a run of 34 +- 6
-        const int grp = lane >> 3, sub = lane & 7;
-        for (int k0 = 0; k0 < my_n; k0 += 32) {
-            unsigned lo = 0, hi = 0;
-            if (k0 + lane < my_n) {
-                const uint32_t* row = table + (size_t)(cb + (k0 + lane) * kWarps + warp) * (T + 1) + tile;
-                lo = __ldg(row); hi = __ldg(row + 1);
-            }
-            const int m = min(32, my_n - k0);
-            unsigned a = 0, b = 0, na = 0, nb = 0;             // record range of this group's run (current / next)
-            size_t base = 0, nbase = 0;
-            auto fetch = [&](int j0, unsigned& ra, unsigned& rb, size_t& rbase, unsigned* code, float* tv) {
-                const int j = j0 + grp;
-                ra = __shfl_sync(0xffffffffu, lo, j & 31);
-                rb = __shfl_sync(0xffffffffu, hi, j & 31);
-                if (j >= m) rb = ra;
-                rbase = (size_t)(cb + (k0 + j) * kWarps + warp) * kBinChunk;
-#pragma unroll
-                for (int u = 0; u < kGT; ++u) {
-                    const unsigned i = ra + u * 8 + sub;
-                    code[u] = 0xffffffffu;
-                    if (i < rb) { code[u] = __ldcs(codes_g + rbase + i); tv[u] = __ldcs(ts_g + rbase + i); }
-                }
-            };
-            auto apply = [&](unsigned c, float t) {
-                if (c != 0xffffffffu) {
-                    atomicAdd(&cnt[c], 1u);                      // scatter_sum, net.py:147-148
-                    atomicMax(&key[c], ordered_key(t));          // scatter_max of the raw t, net.py:149
-                }
-            };
-            unsigned code[kGT], ncode[kGT];
-            float tv[kGT], ntv[kGT];
-            fetch(0, a, b, base, code, tv);
-            for (int j0 = 0; j0 < m; j0 += kG) {
-                if (j0 + kG < m) fetch(j0 + kG, na, nb, nbase, ncode, ntv);
-#pragma unroll
-                for (int u = 0; u < kGT; ++u) apply(code[u], tv[u]);
-                for (unsigned i = a + kGT * 8 + sub; __any_sync(0xffffffffu, i < b); i += 8)   // rare: a run above 48 records
-                    if (i < b) apply(__ldcs(codes_g + base + i), __ldcs(ts_g + base + i));
-#pragma unroll
-                for (int u = 0; u < kGT; ++u) { code[u] = ncode[u]; tv[u] = ntv[u]; }
-                a = na; b = nb; base = nbase;
-            }
+    int* key = reinterpret_cast<int*>(slab + kKeyOffsetBytes / 4);
+    if ((cells & 3) == 0) {                            // private: zeroed while pass 1 still runs
+        uint4* c4 = reinterpret_cast<uint4*>(cnt);
+        int4* k4 = reinterpret_cast<int4*>(key);
+        for (int i = threadIdx.x; i < cells / 4; i += kRedThreads) {
+            c4[i] = make_uint4(0u, 0u, 0u, 0u);
+            k4[i] = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
         }
     } else {
+        for (int i = threadIdx.x; i < cells; i += kRedThreads) { cnt[i] = 0u; key[i] = INT_MIN; }
+    }
+    pdl_wait_for(codes_g, ts_g, table, ends, sd);      // records + tables come from pass 1
+    chunk_prefix<kRedThreads>(ends, n_samples, prefix);   // ends with __syncthreads()
+    const int cb = prefix[s], nc = prefix[s + 1] - prefix[s];
+    const int lane = threadIdx.x & 31;
+    constexpr int kWarps = kRedThreads / 32;
+    const int warp = threadIdx.x >> 5;
+    constexpr int kLR = kRedRuns;
+    constexpr size_t kStride = (size_t)kWarps * kBinChunk;        // records between two chunks of a warp
+    const int my_n = nc > warp ? (nc - warp + kWarps - 1) / kWarps : 0;
+    const int* keys_g = reinterpret_cast<const int*>(ts_g);
     for (int k0 = 0; k0 < my_n; k0 += 32) {
         unsigned lo = 0, hi = 0;
         if (k0 + lane < my_n) {
@@ -457,59 +383,66 @@ encode_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restri
             lo = __ldg(row); hi = __ldg(row + 1);
         }
         const int m = min(32, my_n - k0);
-        int j = -1;
-        unsigned i0 = 0, h = 0;
-        auto advance = [&]() {                            // next batch: same run, or the next non-empty one
-            i0 += kStep;
-            while (i0 >= h && ++j < m) { i0 = __shfl_sync(0xffffffffu, lo, j); h = __shfl_sync(0xffffffffu, hi, j); }
-        };
-        auto load = [&](unsigned* code, float* tv) {
-            const size_t base = (size_t)(cb + (k0 + j) * kWarps + warp) * kBinChunk;
+        const size_t base0 = (size_t)(cb + k0 * kWarps + warp) * kBinChunk + lane;
+        for (int j = 0; j < m; j += kLR) {
+            const uint16_t* cp[kLR];
+            const int* kp[kLR];
+            int left[kLR];                               // records of the run from this lane's first one on
 #pragma unroll
-            for (int u = 0; u < kRedBatch; ++u) {
-                const unsigned i = i0 + u * 32 + lane;
-                code[u] = 0xffffffffu;
-                if (i < h) { code[u] = __ldcs(codes_g + base + i); tv[u] = __ldcs(ts_g + base + i); }
+            for (int q = 0; q < kLR; ++q) {
+                const unsigned a = __shfl_sync(0xffffffffu, lo, (j + q) & 31);
+                const unsigned b = __shfl_sync(0xffffffffu, hi, (j + q) & 31);
+                const size_t first = base0 + (size_t)(j + q) * kStride + a;
+                cp[q] = codes_g + first;
+                kp[q] = keys_g + first;
+                left[q] = (j + q < m) ? (int)(b - a) - lane : 0;
             }
-        };
-        unsigned code[kRedBatch], ncode[kRedBatch];
-        float tv[kRedBatch], ntv[kRedBatch];
-        advance();
-        if (j < m) load(code, tv);
-        while (j < m) {
-            advance();
-            if (j < m) load(ncode, ntv);
+            unsigned code[kLR * kLP];
+            int kv[kLR * kLP];
 #pragma unroll
-            for (int u = 0; u < kRedBatch; ++u) {
-                if (code[u] != 0xffffffffu) {
-                    atomicAdd(&cnt[code[u]], 1u);                // scatter_sum, net.py:147-148
-                    atomicMax(&key[code[u]], ordered_key(tv[u]));   // scatter_max of the raw t, net.py:149
+            for (int q = 0; q < kLR; ++q)
+#pragma unroll
+                for (int u = 0; u < kLP; ++u) {
+                    code[q * kLP + u] = (unsigned)lane; kv[q * kLP + u] = INT_MIN;
+                    if (u * 32 < left[q]) {
+                        code[q * kLP + u] = __ldcs(cp[q] + u * 32);
+                        kv[q * kLP + u] = __ldcs(kp[q] + u * 32);
+                    }
                 }
-                code[u] = ncode[u]; tv[u] = ntv[u];
-            }
+#pragma unroll
+            for (int q = 0; q < kLR; ++q)
+#pragma unroll
+                for (int u = 0; u < kLP; ++u) slab_apply(cnt, code[q * kLP + u], kv[q * kLP + u], u * 32 < left[q] ? 1u : 0u);
+#pragma unroll
+            for (int q = 0; q < kLR; ++q)                    // a run longer than 32 kLP records
+                for (int off = 32 * kLP; __any_sync(0xffffffffu, off < left[q]); off += 32) {
+                    const bool v = off < left[q];
+                    unsigned c = (unsigned)lane; int k = INT_MIN;
+                    if (v) { c = __ldcs(cp[q] + off); k = __ldcs(kp[q] + off); }
+                    slab_apply(cnt, c, k, v ? 1u : 0u);
+                }
         }
-    }
     }
     __syncthreads();
     const float2 nd = sd[s];
     const int y0 = tile << r_log2;
     const size_t plane = (size_t)H * W;
-    float* o = out + (size_t)s * 4 * plane;
-    // the slab's rows are whole image rows: its pixels are contiguous in every output plane
-    const int n_px = min(R, H - y0) * W;
-    float* o0 = o + (size_t)y0 * W;
+    const int n_px = min(R, H - y0) * W;               // whole image rows: contiguous in every output plane
+    float* o0 = out + (size_t)s * 4 * plane + (size_t)y0 * W;
     for (int i = threadIdx.x; i < n_px; i += kRedThreads) {
-        const size_t px = (size_t)i;
+        const uint2 c2 = *reinterpret_cast<const uint2*>(cnt + 2 * i);
+        const int2 k2 = *reinterpret_cast<const int2*>(key + 2 * i);
+        const unsigned cc[2] = {c2.x, c2.y};
+        const int kk[2] = {k2.x, k2.y};
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            const int k = key[2 * i + c];
             float tn = 0.f;
-            if (k != INT_MIN) {
-                tn = __fdiv_rn(__fsub_rn(key_to_float(k), nd.x), nd.y);          // net.py:141
-                if (__float_as_int(tn) <= 0) tn = 0.f;                           // max against the zero plane
+            if (kk[c] != INT_MIN) {
+                tn = __fdiv_rn(__fsub_rn(key_to_float(kk[c]), nd.x), nd.y);          // net.py:141
+                if (__float_as_int(tn) <= 0) tn = 0.f;                               // max against the zero plane
             }
-            o0[c * plane + px] = (float)cnt[2 * i + c];
-            o0[(c + 2) * plane + px] = tn;
+            o0[c * plane + i] = (float)cc[c];
+            o0[(c + 2) * plane + i] = tn;
         }
     }
 }

@@ -156,7 +156,8 @@ voxel_reduce_kernel(const uint16_t* __restrict__ codes_g, const float* __restric
     const float bins_m1 = (float)(C - 1);
     auto apply = [&](unsigned c, float t) {
         if (c == 0xffffffffu) return;
-        const VoxelTaps v = voxel_taps(t, nd, bins_m1, (c & 1u) ? -1.f : 1.f);     // code bit 0: 1 = negative
+        // the records carry the order-preserving key of t (encode_binned.cuh): back to the raw t
+        const VoxelTaps v = voxel_taps(key_to_float(__float_as_int(t)), nd, bins_m1, (c & 1u) ? -1.f : 1.f);     // code bit 0: 1 = negative
         float* px = vslab + (c >> 1);
         if ((unsigned)v.k0 < (unsigned)C) atomicAdd(px + v.k0 * npx, v.w0);
         if ((unsigned)(v.k0 + 1) < (unsigned)C && v.w1 != 0.f) atomicAdd(px + (v.k0 + 1) * npx, v.w1);
