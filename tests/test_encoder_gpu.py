@@ -295,3 +295,30 @@ def test_deferred_validation_reports_without_blocking():
         st.synchronize()                                                         # clean again
     finally:
         _lib.Status.mode = old
+
+
+@pytest.mark.parametrize('B', [512, 513])
+def test_many_samples_at_the_binned_path_limit(monkeypatch, B):
+    """The binned path looks a chunk's sample up in a per-CTA table of at most 512 samples
+    (csrc/encode_binned.cuh kBinMaxSamples); one more and the call must take the direct path even
+    when the binned one is asked for -- same image either way."""
+    H, W, n = 16, 32, 300
+    ev, ts, sidx = synth_events(77, B, H, W, n, ragged=True)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    lib = dv._lib.load()
+    N = ev['x'].numel()
+    monkeypatch.setenv('DVSOF_ENCODE_PATH', 'binned')
+    assert lib.dvsof_encode_path(N, B, H, W, lib.dvsof_encode_workspace_bytes(N, B, H, W)) == (1 if B <= 512 else 0)
+    got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert np.array_equal(got.cpu().numpy(), want)
+
+
+def test_narrow_image_binned_path(monkeypatch):
+    """Slabs with fewer than 32 cells per polarity row (W = 8): lanes without a record park their
+    no-op atomics on cell `lane` of the slab (csrc/encode_binned.cuh slab_apply)."""
+    B, H, W, n = 2, 40, 8, 9000
+    ev, ts, sidx = synth_events(5, B, H, W, n)
+    want = eo.compute_event_image(np_events(ev), ts.numpy(), sidx.numpy(), (H, W))
+    monkeypatch.setenv('DVSOF_ENCODE_PATH', 'binned')
+    got = dv.compute_event_image(_cuda(ev), ts.cuda(), sidx.cuda(), (H, W))
+    assert np.array_equal(got.cpu().numpy(), want)

@@ -110,3 +110,14 @@ def test_full_size_binned_path_against_direct():
     net = torch.zeros(B, H, W, device='cuda')
     net.view(-1).index_add_(0, (ev['sample_index'] * H + ev['y']) * W + ev['x'], ev['polarity'].float())
     assert torch.allclose(binned.sum(1), net, rtol=0, atol=1e-3)
+
+
+def test_bin_count_limits(path):
+    """64 bins (the maximum) and a slab too large for shared memory (640 wide x 64 bins: 160 KB per row
+    pair... the plan refuses and the call takes the direct path even when the binned one is asked for)."""
+    ev, ts, sidx = synth_events(31, 2, 24, 40, 6000)
+    _check(ev, ts, sidx, 24, 40, 64)
+    lib = dv._lib.load()
+    assert lib.dvsof_voxel_path(10 ** 7, 2, 480, 1280, 64, lib.dvsof_voxel_workspace_bytes(10 ** 7, 2, 480, 1280, 64)) == 0
+    ev, ts, sidx = synth_events(32, 1, 8, 1280, 4000)
+    _check(ev, ts, sidx, 8, 1280, 64)

@@ -76,3 +76,9 @@ def test_static_entry_empty_stream_gives_zeros():
               _lib.ptr(out), _lib.ptr(status), _lib.stream_ptr(torch.device('cuda', 0)))
     torch.cuda.synchronize()
     assert not out.any() and int(status) == 0
+
+
+@pytest.mark.gpu
+def test_static_entry_at_its_sample_limit():
+    torch.cuda.set_device(0)
+    _encode_both(12, 4096, 8, 16, 50, check_no_alloc=True)
