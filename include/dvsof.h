@@ -4,7 +4,8 @@
  *
  * Conventions
  *  - every pointer marked [dev] is a device pointer owned by the caller; the library
- *    allocates nothing and keeps no global state (re-entrant, stream-ordered);
+ *    allocates nothing and keeps no global state (re-entrant, stream-ordered) -- the one exception
+ *    is dvsof_encode_event_image_static below, which says so;
  *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *  - return value: 0 = DVSOF_OK, negative = host-side argument / launch error, text
  *    available from dvsof_last_error() (thread-local);
