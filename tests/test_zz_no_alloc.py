@@ -47,7 +47,8 @@ def _encode_both(seed, B, H, W, n, check_no_alloc):
     torch.cuda.synchronize()
     assert torch.cuda.memory_allocated() == torch_bytes
     if check_no_alloc:              # the first call on a device may load the module lazily
-        assert torch.cuda.mem_get_info()[0] == free_before, 'device memory changed across the call'
+        # a cudaMalloc shows up in whole 2 MiB pages; anything smaller is not ours
+        assert free_before - torch.cuda.mem_get_info()[0] < (1 << 20), 'device memory shrank across the call'
     assert status.tolist() == [0, 0]
     assert want[:, :2].sum().item() == N        # the comparison is not between two empty images
     assert torch.equal(got, want)
