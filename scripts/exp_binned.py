@@ -19,12 +19,14 @@ if __name__ == '__main__':
     res = {'lib': os.environ.get('DVSOF_LIB', 'default'), 'old_reduce': bool(os.environ.get('DVSOF_REDUCE_OLD'))}
     for name in sys.argv[1:] or ['cfg3', 'cfg4']:
         c = bench.CFG[name]
-        r = bench.bench_encoder(name, 10, 3, dev)
-        ev, ts, sidx = bench.fast_events(1234 + int(name[3:]), c['B'], c['H'], c['W'], c['n'], c['T'], dev)
+        contended = bool(os.environ.get('DVSOF_EXP_CONTENDED'))       # 80 % of the events on 10 % of the pixels
+        r = bench.bench_encoder(name, 10, 3, dev, contended=contended)
+        ev, ts, sidx = bench.fast_events(1234 + int(name[3:]), c['B'], c['H'], c['W'], c['n'], c['T'], dev, contended)
         size = dv.extend_size((c['H'], c['W']))
         ok = bool(torch.equal(dv.compute_event_image(ev, ts, sidx, size), torch_ref(ev, ts, c['B'], *size)))
         res[name] = {'step_us': round(r['step_ms'] * 1e3, 1), 'bin_us': round(r['kernels'].get('bin_ms', 0) * 1e3, 1),
-                     'reduce_us': round(r['kernels'].get('reduce_ms', 0) * 1e3, 1), 'exact': ok}
+                     'reduce_us': round(r['kernels'].get('reduce_ms', 0) * 1e3, 1),
+                     'direct_us': round(r['kernels']['scatter_ms'] * 1e3, 1), 'contended': contended, 'exact': ok}
         del ev
         torch.cuda.empty_cache()
     print(json.dumps(res))
